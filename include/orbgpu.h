@@ -1,0 +1,273 @@
+/*
+ * orbgpu.h -- C ABI of liborbgpu, the B200 (sm_100a) implementation of ORB-SLAM2's
+ * data-parallel front end.  This is the drop-in boundary for the hot path of
+ * shishiteng/AR_ORBSLAM2: every entry point replaces one reference interface, cited as
+ * "ref:" (paths relative to the reference checkout, ORB_SLAM2/...).
+ *
+ * Conventions
+ *   - plain C types only: pointers, sizes, POD structs.  No C++ or torch types.
+ *   - every function returns ORB_OK (0) or a negative orb_status; nothing throws.
+ *     orb_last_error() returns a thread-local message for the last failure.
+ *   - a handle may be used by one thread at a time; distinct handles are independent
+ *     (each owns its CUDA stream and device buffers), matching the reference where the
+ *     stereo Frame constructor runs two extractor objects concurrently (ref: src/Frame.cc:83-86).
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails with
+ *     ORB_ERR_CUDA.
+ *   - "loc" flags say where caller buffers live (ORB_HOST / ORB_DEVICE).
+ */
+#ifndef ORBGPU_H_
+#define ORBGPU_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBGPU_ABI_VERSION 1
+
+typedef enum orb_status {
+    ORB_OK = 0,
+    ORB_ERR_INVALID = -1,      /* bad argument (null pointer, size out of range ...)            */
+    ORB_ERR_CUDA = -2,         /* CUDA runtime error or no device                               */
+    ORB_ERR_TOO_SMALL = -3,    /* image so small that the reference divides by zero
+                                  (ref: src/ORBextractor.cc:530-532,753-756)                    */
+    ORB_ERR_CAPACITY = -4,     /* caller buffer or internal pool too small; nothing truncated
+                                  silently                                                      */
+    ORB_ERR_EMPTY = -5,        /* stereo: no accepted match (ref: src/Frame.cc:630 indexes an
+                                  empty vector there)                                           */
+    ORB_ERR_NCCL = -6
+} orb_status;
+
+enum { ORB_HOST = 0, ORB_DEVICE = 1 };
+
+/* ref: cv::KeyPoint as filled by src/ORBextractor.cc:786-813,1035-1043 (28 bytes). */
+typedef struct orb_keypoint {
+    float x, y;        /* pt, level-0 pixel coordinates (pt *= scale, ref :1040)             */
+    float size;        /* int(31 * scale[octave]) stored as float (ref :804,812)             */
+    float angle;       /* degrees in [0,360), cv::fastAtan2 (ref :97)                        */
+    float response;    /* FAST score V-1                                                     */
+    int32_t octave;    /* pyramid level                                                      */
+    int32_t class_id;  /* -1                                                                 */
+} orb_keypoint;
+
+/* ref: ORBextractor::ORBextractor(int,float,int,int,int), include/ORBextractor.h:52-53,
+ * configured from the ORBextractor.* yaml keys (src/Tracking.cc:449-464). */
+typedef struct orb_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;       /* 1..ORB_MAX_LEVELS                                              */
+    int32_t ini_th_fast;
+    int32_t min_th_fast;
+    int32_t max_width;     /* largest image this handle will see (buffers are sized once)    */
+    int32_t max_height;
+    int32_t max_batch;     /* frames processed per orb_extract_batch call (>=1)              */
+    int32_t device;        /* CUDA ordinal, -1 = current device                              */
+    int32_t blur_taps;     /* 0: OpenCV>=3.4/4.x 8.8 fixed-point taps {18,34,48,56,48,34,18};
+                              1: OpenCV 2.4 rounded-float taps {18,34,49,55,49,34,18}        */
+} orb_params;
+
+#define ORB_MAX_LEVELS 16
+#define ORB_EDGE_THRESHOLD 19   /* ref: src/ORBextractor.cc:71 */
+
+typedef struct orb_extractor orb_extractor;
+
+/* ---- extractor ------------------------------------------------------------------------- */
+
+/* ref: constructor src/ORBextractor.cc:404-460 (scale tables, per-level quotas, umax). */
+int orb_extractor_create(const orb_params *params, orb_extractor **out);
+void orb_extractor_destroy(orb_extractor *ex);
+
+/* ref: getters include/ORBextractor.h:64-86.  Each array has nlevels entries. */
+int orb_extractor_tables(const orb_extractor *ex, float *scale, float *inv_scale,
+                         float *sigma2, float *inv_sigma2, int32_t *features_per_level);
+
+/* ref: ORBextractor::operator()(InputArray image, InputArray mask, vector<KeyPoint>&,
+ * OutputArray descriptors), src/ORBextractor.cc:985-1045.  8-bit single channel image,
+ * `pitch` bytes per row.  The mask is ignored by the reference (include/ORBextractor.h:60)
+ * and has no parameter here.  Writes n keypoints (level-major order, exactly the
+ * reference's) and n x 32 descriptor bytes; n can exceed nfeatures, so
+ * `capacity` should be >= nfeatures + 4*nlevels; ORB_ERR_CAPACITY if n > capacity.
+ * An empty image (width or height 0) returns ORB_OK with *n_out = 0 (ref :987-988).  */
+int orb_extract(orb_extractor *ex, const uint8_t *image, int width, int height, int pitch,
+                int image_loc, orb_keypoint *keypoints, uint8_t *descriptors, int capacity,
+                int *n_out);
+
+/* Batched form of the same call for independent frames (frame-sharded throughput, the
+ * reference runs one operator() per Frame: src/Frame.cc:252-258).  `images` is one buffer
+ * of `batch` frames, frame b at images + b*frame_stride.  Outputs: frame b's keypoints at
+ * keypoints + b*capacity, descriptors at descriptors + b*capacity*32, count in n_out[b].
+ * image_loc / out_loc choose host or device residency of the caller's buffers.  With
+ * device outputs the call is asynchronous on the handle's stream (see orb_extractor_sync). */
+int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int width,
+                      int height, int pitch, size_t frame_stride, int image_loc,
+                      orb_keypoint *keypoints, uint8_t *descriptors, int capacity,
+                      int32_t *n_out, int out_loc);
+int orb_extractor_sync(orb_extractor *ex);
+/* cudaStream_t of the handle as an opaque pointer (for event timing on the launching stream). */
+void *orb_extractor_stream(orb_extractor *ex);
+/* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
+int64_t orb_extractor_launch_count(const orb_extractor *ex);
+
+/* ref: public member std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:88), read
+ * by Frame::ComputeStereoMatches (src/Frame.cc:476,566,578,583).  Geometry of level `level`
+ * of batch slot `slot` after the last extract call: interior size, and the device pointer /
+ * pitch of the interior's first pixel.  The plane carries the reference's 19-pixel
+ * BORDER_REFLECT_101 frame (ref :1052-1068) around the interior.                          */
+int orb_pyramid_level(const orb_extractor *ex, int slot, int level, const uint8_t **dev_interior,
+                      int *width, int *height, int *pitch);
+/* Host copy of that level.  with_border=1 copies the (w+38)x(h+38) padded plane.          */
+int orb_pyramid_download(orb_extractor *ex, int slot, int level, int with_border,
+                         uint8_t *dst, int dst_pitch);
+
+/* Stage outputs for parity tests (not used by the shims).
+ * Candidates = what ComputeKeyPointsOctTree feeds DistributeOctTree (ref :786-793): window-
+ * relative x,y and FAST response, in the reference's order (cells row-major, row-major
+ * inside a cell).                                                                          */
+typedef struct orb_candidate { int16_t x, y; int32_t response; } orb_candidate;
+int orb_debug_candidates(orb_extractor *ex, int slot, int level, orb_candidate *out,
+                         int capacity, int *n_out);
+/* 7x7 sigma=2 Gaussian of a level exactly as ref :1024-1026 (clone + GaussianBlur,
+ * BORDER_REFLECT_101), produced by the same device routine the descriptor kernel uses.    */
+int orb_debug_blur_level(orb_extractor *ex, int slot, int level, uint8_t *dst, int dst_pitch);
+
+/* ---- Hamming matching ------------------------------------------------------------------ */
+
+/* ref: ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:1650-1666.  n pairs of 32-byte
+ * descriptors -> n distances.  (Device kernel; the host shim's static DescriptorDistance
+ * for a single pair is plain popcount.)                                                    */
+int orb_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, int loc);
+
+/* Brute-force top-2 (best and second best with strict '<', first candidate wins ties; the
+ * inner loop shared by ref src/ORBmatcher.cc:205-226,573-599, src/Marker.cc:314-349).
+ * For each of nq queries scans db rows [0,ndb) in order.  Outputs are 4 arrays of nq:
+ * best distance/index and second distance/index (256 / -1 when absent).  idx_base is added
+ * to reported indices (keyframe-range shards).  loc applies to all buffers.               */
+int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t ndb,
+                     int64_t idx_base, int32_t *best_dist, int64_t *best_idx,
+                     int32_t *second_dist, int64_t *second_idx, int loc);
+
+/* Merge of per-shard top-2 lists in shard order, identical to one scan over the
+ * concatenated database.  parts laid out [shard][nq].                         */
+int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx,
+                   const int32_t *second_dist, const int64_t *second_idx,
+                   int32_t *out_best_dist, int64_t *out_best_idx, int32_t *out_second_dist,
+                   int64_t *out_second_idx, int loc);
+
+/* Measured popc32 issue rate of the device (Gpopc32/s), the matching roofline denominator
+ * (SURVEY 8d).                                                                             */
+int orb_measure_popc_rate(double *gpopc_per_s);
+
+/* ---- frame feature index + tracking matchers ------------------------------------------- */
+
+/* ref: the parts of Frame that the matchers read: mvKeysUn, mDescriptors, mvuRight, the
+ * 64x48 grid (include/Frame.h:39-40,161-163; src/Frame.cc:235-250,332-397) and the
+ * static image bounds / grid scales.                                                       */
+typedef struct orb_frame_desc {
+    int32_t n;                     /* number of keypoints                                  */
+    const orb_keypoint *keys_un;   /* mvKeysUn (host)                                      */
+    const uint8_t *descriptors;    /* n x 32 (host)                                        */
+    const float *u_right;          /* mvuRight or NULL (= all -1)                          */
+    float min_x, max_x, min_y, max_y;      /* mnMinX ...                                   */
+    int32_t nlevels;
+    const float *scale_factors;    /* mvScaleFactors, nlevels entries                      */
+} orb_frame_desc;
+
+typedef struct orb_frame orb_frame;
+int orb_frame_create(const orb_frame_desc *desc, orb_frame **out);
+void orb_frame_destroy(orb_frame *f);
+
+/* ref: Frame::GetFeaturesInArea, src/Frame.cc:332-385 -- indices in the reference's
+ * traversal order (ix outer, iy inner, insertion order).                                   */
+int orb_frame_features_in_area(orb_frame *f, float x, float y, float r, int min_level,
+                               int max_level, int32_t *indices, int capacity, int *n_out);
+
+/* ref: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:405-523.
+ * prev_matched: n1 x 2 floats, updated in place (ref :518-520).  matches12: n1 ints.       */
+int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matched,
+                                  int32_t *matches12, int window_size, float nnratio,
+                                  int check_orientation, int *nmatches);
+
+/* ref: ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th),
+ * src/ORBmatcher.cc:45-129.  Map points are passed flat, already filtered the way
+ * Frame::isInFrustum leaves them (mbTrackInView etc.).                                     */
+typedef struct orb_track_points {
+    int32_t n;
+    const uint8_t *in_view;        /* mbTrackInView && !isBad()                            */
+    const float *proj_x, *proj_y, *proj_xr;   /* mTrackProjX/Y/XR                          */
+    const int32_t *level;          /* mnTrackScaleLevel                                    */
+    const float *view_cos;         /* mTrackViewCos                                        */
+    const uint8_t *descriptors;    /* GetDescriptor(), n x 32                              */
+} orb_track_points;
+/* claimed[i] != 0 : F.mvpMapPoints[i] && Observations()>0 on entry (ref :87-89).
+ * assigned[i]: out, index of the map point written to F.mvpMapPoints[i] or -1.             */
+int orb_search_by_projection_points(orb_frame *f, const orb_track_points *pts,
+                                    const uint8_t *claimed, float th, float nnratio,
+                                    int32_t *assigned, int *nmatches);
+
+/* ref: ORBmatcher::SearchByProjection(Frame &Cur, const Frame &Last, th, bMono),
+ * src/ORBmatcher.cc:1331-1473.  The projection (ref :1362-1379) is done by the caller or by
+ * orb_project_points; here each Last feature i with a valid map point carries its projected
+ * (u,v), 1/z, last octave and descriptor.                                                  */
+typedef struct orb_last_points {
+    int32_t n;
+    const uint8_t *valid;          /* pMP && !mvbOutlier && invzc>=0 && in image bounds     */
+    const float *u, *v, *invz;
+    const int32_t *octave;         /* LastFrame.mvKeys[i].octave                            */
+    const float *angle;            /* LastFrame.mvKeysUn[i].angle                           */
+    const uint8_t *descriptors;
+} orb_last_points;
+int orb_search_by_projection_last(orb_frame *cur, const orb_last_points *pts,
+                                  const uint8_t *claimed, float th, int forward, int backward,
+                                  float mbf, int check_orientation, int32_t *assigned,
+                                  int *nmatches);
+
+/* ref: ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...), src/ORBmatcher.cc:159-288.
+ * The two DBoW2::FeatureVectors are passed as CSR over the common node ids in ascending
+ * order (the merge-join of ref :180-264 done by the caller): group g holds KF feature
+ * indices kf_idx[kf_off[g]..kf_off[g+1]) and F indices f_idx[f_off[g]..f_off[g+1]).
+ * kf_valid[i] = map point exists and is not bad.  matches[j] = KF feature index whose map
+ * point is written to vpMapPointMatches[j], or -1.                                         */
+int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *kf_off,
+                      const int32_t *kf_idx, const int32_t *f_off, const int32_t *f_idx,
+                      const uint8_t *kf_valid, float nnratio, int check_orientation,
+                      int32_t *matches, int *nmatches);
+
+/* ref: ORBmatcher::ComputeThreeMaxima + the rotation binning, src/ORBmatcher.cc:238-245,
+ * 1604-1645 (factor = 1/HISTO_LENGTH quirk kept).  keep[i]=1 if pair i survives.           */
+int orb_rot_hist_filter(const float *angle_a, const float *angle_b, int n, uint8_t *keep);
+
+/* ---- stereo ---------------------------------------------------------------------------- */
+
+/* ref: Frame::ComputeStereoMatches, src/Frame.cc:471-643.  left/right are the two extractor
+ * handles whose pyramids (slot `slot`) hold the current pair; keypoints/descriptors are the
+ * outputs of the two orb_extract calls (host).  mb is Frame::mb (= mbf/fx) as the reference
+ * intends it.  Outputs mvuRight / mvDepth (n_left floats, -1 where unmatched).             */
+int orb_stereo_match(orb_extractor *left, orb_extractor *right, int slot,
+                     const orb_keypoint *keys_left, const uint8_t *desc_left, int n_left,
+                     const orb_keypoint *keys_right, const uint8_t *desc_right, int n_right,
+                     float mbf, float mb, float *u_right, float *depth, int *n_matched);
+
+/* ---- sharded descriptor database (relocalisation brute force) --------------- */
+
+typedef struct orb_db orb_db;
+/* Shard [row_begin,row_end) of a global database of 32-byte descriptors, resident in HBM. */
+int orb_db_create(int64_t row_begin, int64_t row_end, int device, orb_db **out);
+void orb_db_destroy(orb_db *db);
+int orb_db_upload(orb_db *db, int64_t first_row, const uint8_t *rows, int64_t nrows, int loc);
+/* Deterministic synthetic fill (splitmix64 of the global row index) directly on the device. */
+int orb_db_fill_synthetic(orb_db *db, uint64_t seed);
+int orb_db_row(orb_db *db, int64_t global_row, uint8_t *out32);
+uint8_t *orb_db_device_ptr(orb_db *db);
+/* Local top-2 of nq queries against the shard; outputs are device or host per loc.        */
+int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist,
+                 int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc);
+
+const char *orb_last_error(void);
+int orb_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBGPU_H_ */

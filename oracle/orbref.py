@@ -1,0 +1,146 @@
+"""ORACLE -- TEST INFRASTRUCTURE ONLY.  ctypes binding of oracle/liborbref.so.
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from ar_orbslam2_b200._abi import CANDIDATE_DTYPE, KEYPOINT_DTYPE, OrbParams, ptr
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liborbref.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+    return _LIB
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"orbref {what} failed: {rc}")
+
+
+class RefExtractor:
+    """CPU restatement of ORB_SLAM2::ORBextractor (ORB_SLAM2/src/ORBextractor.cc)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, blur_taps=0):
+        self.params = OrbParams(nfeatures, scale_factor, nlevels, ini_th, min_th, 0, 0, 1, -1, blur_taps)
+        self.h = C.c_void_p()
+        _check(lib().orbref_extractor_create(C.byref(self.params), C.byref(self.h)), "create")
+        self.nlevels = nlevels
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orbref_extractor_destroy(self.h)
+            self.h = None
+
+    def set_trig_mode(self, mode):
+        lib().orbref_extractor_set_trig_mode(self.h, mode)
+
+    def tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        per = np.zeros(n, np.int32)
+        umax = np.zeros(16, np.int32)
+        _check(lib().orbref_extractor_tables(self.h, ptr(sc), ptr(isc), ptr(s2), ptr(is2), ptr(per), ptr(umax)), "tables")
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, per_level=per, umax=umax)
+
+    def extract(self, img: np.ndarray, capacity=None, check=True):
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w = img.shape if img.ndim == 2 else (0, 0)
+        cap = capacity or (self.params.nfeatures + 64 * self.nlevels + 4096)
+        kps = np.zeros(cap, KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        rc = lib().orbref_extract(self.h, ptr(img), w, h, img.strides[0] if img.ndim == 2 and h else 0,
+                                  ptr(kps), ptr(desc), cap, C.byref(n))
+        if check:
+            _check(rc, "extract")
+            return kps[: n.value].copy(), desc[: n.value].copy()
+        return rc, kps[: n.value].copy(), desc[: n.value].copy()
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        _check(lib().orbref_level_size(self.h, level, C.byref(w), C.byref(h)), "level_size")
+        return w.value, h.value
+
+    def pyramid_level(self, level, with_border=False):
+        w, h = self.level_size(level)
+        if with_border:
+            w, h = w + 38, h + 38
+        out = np.zeros((h, w), np.uint8)
+        _check(lib().orbref_pyramid_download(self.h, level, int(with_border), ptr(out), w), "pyramid")
+        return out
+
+    def candidates(self, level):
+        cap = 1 << 20
+        out = np.zeros(cap, CANDIDATE_DTYPE)
+        n = C.c_int()
+        _check(lib().orbref_debug_candidates(self.h, level, ptr(out), cap, C.byref(n)), "candidates")
+        return out[: n.value].copy()
+
+    def blurred_level(self, level):
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        _check(lib().orbref_debug_blur_level(self.h, level, ptr(out), w), "blur")
+        return out
+
+
+def resize_linear(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orbref_resize_linear(ptr(src), src.shape[1], src.shape[0], src.strides[0], ptr(dst), dw, dh, dw)
+    return dst
+
+
+def gaussian_blur7(src: np.ndarray, taps=0) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros_like(src)
+    lib().orbref_gaussian_blur7(ptr(src), src.shape[1], src.shape[0], src.strides[0], ptr(dst), dst.strides[0], taps)
+    return dst
+
+
+def fast(img: np.ndarray, threshold: int) -> np.ndarray:
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = img.size // 4 + 16
+    out = np.zeros(cap, CANDIDATE_DTYPE)
+    n = C.c_int()
+    _check(lib().orbref_fast(ptr(img), img.shape[1], img.shape[0], img.strides[0], threshold, ptr(out), cap, C.byref(n)), "fast")
+    return out[: n.value].copy()
+
+
+def fast_atan2(y: np.ndarray, x: np.ndarray) -> np.ndarray:
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().orbref_fast_atan2(ptr(y), ptr(x), y.size, ptr(out))
+    return out
+
+
+def sincos(angle_rad: np.ndarray, mode=0):
+    a = np.ascontiguousarray(angle_rad, np.float32)
+    s = np.zeros_like(a)
+    c = np.zeros_like(a)
+    lib().orbref_sincos(ptr(a), a.size, ptr(s), ptr(c), mode)
+    return s, c
+
+
+def make_border(interior: np.ndarray, border=19) -> np.ndarray:
+    h, w = interior.shape
+    plane = np.zeros((h + 2 * border, w + 2 * border), np.uint8)
+    plane[border:border + h, border:border + w] = interior
+    lib().orbref_make_border(ptr(plane), w, h, plane.strides[0], border)
+    return plane
