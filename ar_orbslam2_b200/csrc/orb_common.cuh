@@ -1,0 +1,47 @@
+// liborbgpu internals: error plumbing and small device helpers shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/orbgpu.h"
+
+namespace orbgpu {
+
+void set_error(const char *fmt, ...);
+
+#define ORB_CUDA_TRY(expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            orbgpu::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                  \
+                              cudaGetErrorString(_e));                                       \
+            return ORB_ERR_CUDA;                                                             \
+        }                                                                                    \
+    } while (0)
+
+#define ORB_REQUIRE(cond, code, ...)                                                         \
+    do {                                                                                     \
+        if (!(cond)) {                                                                       \
+            orbgpu::set_error(__VA_ARGS__);                                                  \
+            return (code);                                                                   \
+        }                                                                                    \
+    } while (0)
+
+// BORDER_REFLECT_101 index (gfedcb|abcdefgh|gfedcba); valid for |overshoot| < n
+__host__ __device__ __forceinline__ int reflect101(int p, int n) {
+    if (p < 0) p = -p;
+    if (p >= n) p = 2 * (n - 1) - p;
+    return p;
+}
+
+// 256-bit Hamming distance of two descriptors held as 8 x u32
+__device__ __forceinline__ int hamming256(const uint32_t a[8], const uint32_t b[8]) {
+    int d = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) d += __popc(a[i] ^ b[i]);
+    return d;
+}
+
+}  // namespace orbgpu

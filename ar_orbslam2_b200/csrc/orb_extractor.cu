@@ -1,0 +1,1313 @@
+// liborbgpu -- ORB extractor for sm_100a.
+//
+// Replaces ORB_SLAM2::ORBextractor (ref: ORB_SLAM2/src/ORBextractor.cc, include/ORBextractor.h)
+// behind the C ABI of include/orbgpu.h.  A batch of B independent frames runs through
+//   k_pyr_level0 / k_pyr_resize   8-level padded pyramid        (ref ComputePyramid        :1047-1072)
+//   k_fast_cells                  FAST-9 per 30-px cell, 20/7    (ref ComputeKeyPointsOctTree:735-796)
+//   k_octree                      quadtree distribution          (ref DistributeOctTree      :525-733)
+//   k_describe                    IC_Angle + 7x7 blur + rBRIEF   (ref :73-144, 1016-1044)
+// with every intermediate resident in HBM/L2; the only host traffic is the source frames in and
+// 60 B per keypoint out.  Integer arithmetic reproduces OpenCV's fixed point exactly; the few fp32
+// steps use explicit round-to-nearest intrinsics so nothing is contracted into an FMA.
+#include "orb_common.cuh"
+#include "orb_pattern.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace orbgpu {
+
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+constexpr int EDGE = ORB_EDGE_THRESHOLD;   // 19
+constexpr int XOFF = 32;                   // interior column 0 sits at byte 32 of a plane row
+constexpr int MAX_INI = 64;                // max initial quadtree nodes (image aspect ratio)
+constexpr int FAST_TILE_MAX = 72;          // cell (<60) + 6 halo, rounded up
+constexpr int FAST_THREADS = 256;
+constexpr int OCT_THREADS = 512;
+constexpr int DESC_WARPS = 8;
+
+enum { ERRF_CAND_OVERFLOW = 1, ERRF_NODE_OVERFLOW = 2, ERRF_OUT_OVERFLOW = 4 };
+
+struct ResizeTap {   // one destination column/row of cv::resize INTER_LINEAR
+    int16_t s0, s1, a0, a1;
+};
+
+struct LevelGeom {
+    int w, h, pitch;             // interior size, bytes per padded row
+    long long plane_off;         // byte offset of the padded plane inside a frame's pyramid block
+    long long interior_off;      // byte offset of interior pixel (0,0)
+    int tap_x_off, tap_y_off;    // offsets into the ResizeTap pool (level >= 1)
+    // FAST cell grid (ref :742-773)
+    int maxBX, maxBY, wCell, hCell, ncx, ncy, cell_begin;
+    // quadtree (ref :530-549)
+    int quota, nIni;
+    float hX;
+    int ini_x[MAX_INI + 1];
+    int win_w, win_h;            // maxBorder - minBorder
+    int cand_off, cand_cap;      // into the per-frame candidate pool (elements)
+    int kept_off, kept_cap;      // into the per-frame kept pool
+    float scale;                 // mvScaleFactor[level]
+    float size;                  // (float)(int)(31*scale)
+};
+
+struct Geom {
+    int nlevels, width, height;
+    int total_cells;
+    int cand_frame, kept_frame;          // pool elements per frame
+    long long pyr_frame;                 // pyramid bytes per frame
+    int max_nodes;                       // smem sizing for k_octree
+    int ini_th, min_th, blur_taps;
+    LevelGeom lv[ORB_MAX_LEVELS];
+};
+
+struct Kept {   // a keypoint retained by the quadtree, level coordinates
+    int16_t x, y;
+    int32_t response;
+};
+
+__constant__ int8_t c_pattern[ORB_PATTERN_INTS];
+__constant__ int c_umax[16];
+
+// ------------------------------------------------------------------------------------------
+// Pyramid.  Each thread produces one aligned 32-bit word (4 pixels) of a padded plane row, so
+// stores are always aligned although the interior starts 19 pixels into the plane.
+// ------------------------------------------------------------------------------------------
+__global__ void k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_stride, int spitch,
+                             uint8_t *__restrict__ pyr, const Geom *__restrict__ G) {
+    const LevelGeom &g = G->lv[0];
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = blockIdx.y, b = blockIdx.z;
+    if (word * 4 >= g.pitch) return;
+    const int sy = reflect101(py - EDGE, g.h);
+    const uint8_t *srow = src + (size_t)b * frame_stride + (size_t)sy * spitch;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = word * 4 + k - XOFF;
+        if (x >= -EDGE && x < g.w + EDGE) v |= (uint32_t)srow[reflect101(x, g.w)] << (8 * k);
+    }
+    uint8_t *plane = pyr + (size_t)b * G->pyr_frame + g.plane_off;
+    *reinterpret_cast<uint32_t *>(plane + (size_t)py * g.pitch + word * 4) = v;
+}
+
+__global__ void k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G,
+                             const ResizeTap *__restrict__ taps, int level) {
+    const LevelGeom &g = G->lv[level];
+    const LevelGeom &p = G->lv[level - 1];
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = blockIdx.y, b = blockIdx.z;
+    if (word * 4 >= g.pitch) return;
+    uint8_t *frame = pyr + (size_t)b * G->pyr_frame;
+    const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
+    const uint8_t *s0 = frame + p.interior_off + (size_t)ty.s0 * p.pitch;
+    const uint8_t *s1 = frame + p.interior_off + (size_t)ty.s1 * p.pitch;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = word * 4 + k - XOFF;
+        if (x >= -EDGE && x < g.w + EDGE) {
+            const ResizeTap tx = taps[g.tap_x_off + reflect101(x, g.w)];
+            const int r0 = s0[tx.s0] * tx.a0 + s0[tx.s1] * tx.a1;
+            const int r1 = s1[tx.s0] * tx.a0 + s1[tx.s1] * tx.a1;
+            const int o = (((ty.a0 * (r0 >> 4)) >> 16) + ((ty.a1 * (r1 >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)o << (8 * k);
+        }
+    }
+    *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
+}
+
+// ------------------------------------------------------------------------------------------
+// FAST-9/16 per cell.  One CTA per (cell, frame).  V = arc strength: corner at t
+// <=> V > t, response V-1, 3x3 non-max suppression inside the cell's computed region only.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
+__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+
+__device__ __forceinline__ int fast_arc_strength(const uint8_t *p, int pitch) {
+    const int c = p[0];
+    int d[16];
+    d[0] = c - p[3 * pitch];
+    d[1] = c - p[3 * pitch + 1];
+    d[2] = c - p[2 * pitch + 2];
+    d[3] = c - p[pitch + 3];
+    d[4] = c - p[3];
+    d[5] = c - p[-pitch + 3];
+    d[6] = c - p[-2 * pitch + 2];
+    d[7] = c - p[-3 * pitch + 1];
+    d[8] = c - p[-3 * pitch];
+    d[9] = c - p[-3 * pitch - 1];
+    d[10] = c - p[-2 * pitch - 2];
+    d[11] = c - p[-pitch - 3];
+    d[12] = c - p[-3];
+    d[13] = c - p[pitch - 3];
+    d[14] = c - p[2 * pitch - 2];
+    d[15] = c - p[3 * pitch - 1];
+    int mn3[16], mx3[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        mn3[k] = min3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        mx3[k] = max3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    }
+    int a = -256, bneg = 256;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        a = max(a, min3(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]));
+        bneg = min(bneg, max3(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]));
+    }
+    return max(a, -bneg);
+}
+
+__global__ void __launch_bounds__(FAST_THREADS)
+k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32_t *__restrict__ cand,
+             uint32_t *__restrict__ cand_count, int *__restrict__ err) {
+    __shared__ uint8_t tile[FAST_TILE_MAX * FAST_TILE_MAX];
+    __shared__ uint8_t vmap[(FAST_TILE_MAX - 4) * (FAST_TILE_MAX - 4)];   // computed region + 1 px apron
+    __shared__ uint16_t surv[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
+    __shared__ int s_nsurv, s_nkp, s_base;
+
+    const int b = blockIdx.y;
+    int level = 0;
+    while (level + 1 < G->nlevels && (int)blockIdx.x >= G->lv[level + 1].cell_begin) level++;
+    const LevelGeom &g = G->lv[level];
+    const int cell = blockIdx.x - g.cell_begin;
+    const int ci = cell / g.ncx, cj = cell % g.ncx;
+    const int minB = EDGE - 3;
+    // ROI handed to cv::FAST by the reference (ref :759-773)
+    const int iniX = minB + cj * g.wCell, iniY = minB + ci * g.hCell;
+    const int maxX = min(iniX + g.wCell + 6, g.maxBX), maxY = min(iniY + g.hCell + 6, g.maxBY);
+    const int tw = maxX - iniX, th = maxY - iniY;      // ROI size
+    const int cw = tw - 6, ch = th - 6;                // computed region (ROI minus 3 px rim)
+    const int tid = threadIdx.x;
+
+    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
+    for (int i = tid; i < tw * th; i += FAST_THREADS) {
+        const int y = i / tw, x = i - y * tw;
+        tile[y * FAST_TILE_MAX + x] = img[(size_t)(iniY + y) * g.pitch + iniX + x];
+    }
+    const int vw = cw + 2;
+    for (int i = tid; i < vw * (ch + 2); i += FAST_THREADS) vmap[i] = 0;
+    if (tid == 0) { s_nsurv = 0; s_nkp = 0; }
+    __syncthreads();
+    if (cw <= 0 || ch <= 0) return;
+
+    // pass 1: the 4-compass quick test at the lower threshold; survivors are compacted so the
+    // full 16-pixel evaluation runs on dense warps.
+    const int tq = min(G->ini_th, G->min_th);
+    for (int i = tid; i < cw * ch; i += FAST_THREADS) {
+        const int y = i / cw, x = i - y * cw;
+        const uint8_t *p = &tile[(y + 3) * FAST_TILE_MAX + x + 3];
+        const int c = p[0];
+        const int d0 = c - p[3 * FAST_TILE_MAX], d4 = c - p[3], d8 = c - p[-3 * FAST_TILE_MAX], d12 = c - p[-3];
+        // any 9-arc holds two adjacent compass points
+        const int hi = (d0 > tq) + (d4 > tq) + (d8 > tq) + (d12 > tq);
+        const int lo = (d0 < -tq) + (d4 < -tq) + (d8 < -tq) + (d12 < -tq);
+        if (hi >= 2 || lo >= 2) surv[atomicAdd(&s_nsurv, 1)] = (uint16_t)i;
+    }
+    __syncthreads();
+    const int nsurv = s_nsurv;
+    for (int s = tid; s < nsurv; s += FAST_THREADS) {
+        const int i = surv[s];
+        const int y = i / cw, x = i - y * cw;
+        const int V = fast_arc_strength(&tile[(y + 3) * FAST_TILE_MAX + x + 3], FAST_TILE_MAX);
+        vmap[(y + 1) * vw + x + 1] = (uint8_t)max(V, 0);
+    }
+    __syncthreads();
+
+    // pass 2: NMS + threshold, retry at min_th if the cell is empty (ref :780-784)
+    int thr = G->ini_th;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        for (int s = tid; s < nsurv; s += FAST_THREADS) {
+            const int i = surv[s];
+            const int y = i / cw, x = i - y * cw;
+            const uint8_t *v = &vmap[(y + 1) * vw + x + 1];
+            const int V = v[0];
+            if (V > thr && V > v[-1] && V > v[1] && V > v[-vw - 1] && V > v[-vw] && V > v[-vw + 1] &&
+                V > v[vw - 1] && V > v[vw] && V > v[vw + 1]) {
+                const int k = atomicAdd(&s_nkp, 1);
+                // reuse the tile as the output staging area is not possible (still needed); pack now
+                surv[s] = (uint16_t)(i | 0x8000);
+                (void)k;
+            }
+        }
+        __syncthreads();
+        if (s_nkp > 0 || attempt == 1 || G->min_th == thr) break;
+        thr = G->min_th;
+    }
+    const int nkp = s_nkp;
+    if (nkp == 0) return;
+    uint32_t *cnt = cand_count + (size_t)b * G->nlevels + level;
+    if (tid == 0) s_base = (int)atomicAdd(cnt, (uint32_t)nkp);
+    __syncthreads();
+    if (tid == 0) s_nkp = 0;
+    __syncthreads();
+    uint32_t *out = cand + (size_t)b * G->cand_frame + g.cand_off;
+    for (int s = tid; s < nsurv; s += FAST_THREADS) {
+        const int i = surv[s];
+        if (!(i & 0x8000)) continue;
+        const int ii = i & 0x7fff;
+        const int y = ii / cw, x = ii - y * cw;
+        const int V = vmap[(y + 1) * vw + x + 1];
+        const int slot = s_base + atomicAdd(&s_nkp, 1);
+        if (slot < g.cand_cap) {
+            // window-relative coordinates (ref :789-790): ROI x + j*wCell
+            const uint32_t wx = x + 3 + cj * g.wCell, wy = y + 3 + ci * g.hCell;
+            out[slot] = wx | (wy << 12) | ((uint32_t)(V - 1) << 24);
+        } else {
+            atomicOr(err, ERRF_CAND_OVERFLOW);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Quadtree distribution, one CTA per (level, frame).  The reference's std::list is kept as an
+// array in list order (front -> back).  One "pass" divides a chosen set of nodes in a chosen
+// processing order; children are push_front'ed, so with K children created in the pass the
+// t-th created child lands at position K-1-t and surviving old nodes follow in their old
+// order.  Phase 1 processes every node with >1 keypoints in list order (ref :587-638);
+// phase 2 processes them by (size desc, newest first) and stops as soon as the list holds
+// N nodes (ref :646-709).
+// ------------------------------------------------------------------------------------------
+struct OctSmem {
+    // sized [max_nodes] each; laid out manually in dynamic shared memory
+    uint16_t *x0[2], *y0[2], *x1[2], *y1[2];
+    uint32_t *cnt[2];
+    uint32_t *ccount;     // [4*max_nodes]
+    uint16_t *cpos;       // [4*max_nodes]
+    uint16_t *keptpos;    // [max_nodes]
+    uint8_t *divided;     // [max_nodes]
+    int *scanA;           // [max_nodes] children-per-divided-node / creation base
+    int *scanB;           // [max_nodes] undivided flags / rank
+    unsigned long long *keys;   // [sort_n]
+};
+
+__device__ __forceinline__ int block_exclusive_scan(int *data, int n, int *warp_tot /*[32]*/) {
+    // in-place exclusive scan of data[0..n) by the whole CTA; returns the total.
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int per = (n + nt - 1) / nt;
+    const int beg = min(tid * per, n), end = min(beg + per, n);
+    int sum = 0;
+    for (int i = beg; i < end; i++) sum += data[i];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        int w = tid < (nt >> 5) ? warp_tot[tid] : 0;
+        int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (tid >= o) wi += v;
+        }
+        warp_tot[tid] = wi - w;   // exclusive warp offsets
+        if (tid == 31) warp_tot[32] = wi;
+    }
+    __syncthreads();
+    int run = warp_tot[tid >> 5] + incl - sum;
+    for (int i = beg; i < end; i++) {
+        int v = data[i];
+        data[i] = run;
+        run += v;
+    }
+    const int total = warp_tot[32];
+    __syncthreads();
+    return total;
+}
+
+__device__ __forceinline__ int quadrant_of(int x, int y, int nx0, int ny0, int nx1, int ny1) {
+    // ref DivideNode :472-512.  halfX = ceil((UR.x-UL.x)/2) (exact for these small ints)
+    const int hx = nx0 + ((nx1 - nx0 + 1) >> 1), hy = ny0 + ((ny1 - ny0 + 1) >> 1);
+    return (x < hx ? 0 : 1) + (y < hy ? 0 : 2);
+}
+
+__global__ void __launch_bounds__(OCT_THREADS)
+k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const uint32_t *__restrict__ cand_count,
+         uint16_t *__restrict__ node_of_pool, Kept *__restrict__ kept, uint32_t *__restrict__ kept_count,
+         int *__restrict__ err) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int warp_tot[33];
+    __shared__ int s_nexpand, s_jstar, s_phase, s_done;
+
+    const int level = blockIdx.x, b = blockIdx.y;
+    const LevelGeom &g = G->lv[level];
+    const int MAXN = G->max_nodes;
+    const int tid = threadIdx.x;
+    const int N = g.quota;
+
+    OctSmem S;
+    {
+        unsigned char *p = smem_raw;
+        int sort_n = 1;
+        while (sort_n < MAXN) sort_n <<= 1;
+        S.keys = (unsigned long long *)p; p += sizeof(unsigned long long) * sort_n;
+        S.ccount = (uint32_t *)p; p += 4 * 4 * MAXN;
+        for (int k = 0; k < 2; k++) { S.cnt[k] = (uint32_t *)p; p += 4 * MAXN; }
+        S.scanA = (int *)p; p += 4 * MAXN;
+        S.scanB = (int *)p; p += 4 * MAXN;
+        S.cpos = (uint16_t *)p; p += 2 * 4 * MAXN;
+        for (int k = 0; k < 2; k++) {
+            S.x0[k] = (uint16_t *)p; p += 2 * MAXN;
+            S.y0[k] = (uint16_t *)p; p += 2 * MAXN;
+            S.x1[k] = (uint16_t *)p; p += 2 * MAXN;
+            S.y1[k] = (uint16_t *)p; p += 2 * MAXN;
+        }
+        S.keptpos = (uint16_t *)p; p += 2 * MAXN;
+        S.divided = (uint8_t *)p; p += MAXN;
+    }
+
+    const uint32_t *C = cand + (size_t)b * G->cand_frame + g.cand_off;
+    uint16_t *node_of = node_of_pool + (size_t)b * G->cand_frame + g.cand_off;
+    const int n = min((int)cand_count[(size_t)b * G->nlevels + level], g.cand_cap);
+    Kept *out = kept + (size_t)b * G->kept_frame + g.kept_off;
+    uint32_t *out_n = kept_count + (size_t)b * G->nlevels + level;
+
+    int cur = 0;
+    // ---- initial nodes (ref :530-567)
+    for (int i = tid; i < g.nIni; i += OCT_THREADS) {
+        S.x0[0][i] = (uint16_t)g.ini_x[i]; S.x1[0][i] = (uint16_t)g.ini_x[i + 1];
+        S.y0[0][i] = 0; S.y1[0][i] = (uint16_t)g.win_h;
+        S.cnt[0][i] = 0;
+    }
+    __syncthreads();
+    for (int c = tid; c < n; c += OCT_THREADS) {
+        const int x = C[c] & 0xfff;
+        int node = (int)__fdiv_rn((float)x, g.hX);   // vpIniNodes[kp.pt.x / hX]
+        node = min(node, g.nIni - 1);
+        node_of[c] = (uint16_t)node;
+        atomicAdd(&S.cnt[0][node], 1u);
+    }
+    __syncthreads();
+    // drop empty initial nodes, keep order
+    for (int i = tid; i < g.nIni; i += OCT_THREADS) S.scanA[i] = S.cnt[0][i] > 0 ? 1 : 0;
+    __syncthreads();
+    int m = block_exclusive_scan(S.scanA, g.nIni, warp_tot);
+    for (int i = tid; i < g.nIni; i += OCT_THREADS) {
+        if (S.cnt[0][i] > 0) {
+            const int p = S.scanA[i];
+            S.x0[1][p] = S.x0[0][i]; S.x1[1][p] = S.x1[0][i]; S.y0[1][p] = S.y0[0][i]; S.y1[1][p] = S.y1[0][i];
+            S.cnt[1][p] = S.cnt[0][i];
+        }
+    }
+    __syncthreads();
+    for (int c = tid; c < n; c += OCT_THREADS) node_of[c] = (uint16_t)S.scanA[node_of[c]];
+    cur = 1;
+    if (tid == 0) { s_phase = 1; s_done = 0; }
+    __syncthreads();
+
+    // ---- passes
+    for (int iter = 0; iter < 64; iter++) {
+        const int nxt = cur ^ 1;
+        uint32_t *cnt = S.cnt[cur];
+        const int phase = s_phase;
+        for (int i = tid; i < 4 * m; i += OCT_THREADS) S.ccount[i] = 0;
+        if (tid == 0) { s_nexpand = 0; s_jstar = 0x7fffffff; }
+        __syncthreads();
+        // child occupancy of every divisible node
+        for (int c = tid; c < n; c += OCT_THREADS) {
+            const int a = node_of[c];
+            if (cnt[a] > 1) {
+                const uint32_t pc = C[c];
+                const int q = quadrant_of(pc & 0xfff, (pc >> 12) & 0xfff, S.x0[cur][a], S.y0[cur][a], S.x1[cur][a], S.y1[cur][a]);
+                atomicAdd(&S.ccount[4 * a + q], 1u);
+            }
+        }
+        __syncthreads();
+
+        int K;   // children created in this pass
+        if (phase == 1) {
+            for (int a = tid; a < m; a += OCT_THREADS) {
+                const bool dv = cnt[a] > 1;
+                S.divided[a] = dv;
+                const uint32_t *cc = &S.ccount[4 * a];
+                S.scanA[a] = dv ? (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0) : 0;
+            }
+            __syncthreads();
+            K = block_exclusive_scan(S.scanA, m, warp_tot);
+        } else {
+            // expandable nodes sorted by (size desc, position asc) == reference's sorted vector
+            // walked from the back with (size, creation order) keys.
+            int sort_n = 1;
+            while (sort_n < m) sort_n <<= 1;
+            for (int a = tid; a < sort_n; a += OCT_THREADS) {
+                unsigned long long key = 0;
+                if (a < m) {
+                    S.divided[a] = 0;
+                    if (cnt[a] > 1) key = ((unsigned long long)cnt[a] << 16) | (unsigned long long)(0xffff - a);
+                }
+                S.keys[a] = key;
+            }
+            __syncthreads();
+            for (int k = 2; k <= sort_n; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < sort_n; i += OCT_THREADS) {
+                        const int ixj = i ^ j;
+                        if (ixj > i) {
+                            const unsigned long long A = S.keys[i], B = S.keys[ixj];
+                            const bool desc = (i & k) == 0;
+                            if (desc ? (A < B) : (A > B)) { S.keys[i] = B; S.keys[ixj] = A; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            // sorted index j -> node a_j; running list size after dividing j: m + sum_{i<=j}(k_i - 1)
+            for (int j = tid; j < m; j += OCT_THREADS) {
+                const unsigned long long key = S.keys[j];
+                int kk = 0;
+                if (key) {
+                    const int a = 0xffff - (int)(key & 0xffff);
+                    const uint32_t *cc = &S.ccount[4 * a];
+                    kk = (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0);
+                    S.scanB[j] = kk - 1;
+                } else
+                    S.scanB[j] = 0;
+                S.scanA[j] = kk;
+            }
+            __syncthreads();
+            block_exclusive_scan(S.scanB, m, warp_tot);   // exclusive: growth before j
+            for (int j = tid; j < m; j += OCT_THREADS) {
+                const unsigned long long key = S.keys[j];
+                if (key) {
+                    const int after = m + S.scanB[j] + S.scanA[j] - 1;
+                    if (after >= N) atomicMin(&s_jstar, j);
+                }
+            }
+            __syncthreads();
+            const int jstar = s_jstar;
+            for (int j = tid; j < m; j += OCT_THREADS) {
+                const unsigned long long key = S.keys[j];
+                if (!key || j > jstar) S.scanA[j] = 0;
+            }
+            __syncthreads();
+            K = block_exclusive_scan(S.scanA, m, warp_tot);   // creation base per sorted index
+            // scatter the creation bases from sorted order back to list positions
+            for (int j = tid; j < m; j += OCT_THREADS) {
+                const unsigned long long key = S.keys[j];
+                if (key && j <= jstar) {
+                    const int a = 0xffff - (int)(key & 0xffff);
+                    S.divided[a] = 1;
+                    S.scanB[a] = S.scanA[j];
+                }
+            }
+            __syncthreads();
+            for (int a = tid; a < m; a += OCT_THREADS) S.scanA[a] = S.divided[a] ? S.scanB[a] : 0;
+            __syncthreads();
+        }
+        // rank of undivided nodes
+        for (int a = tid; a < m; a += OCT_THREADS) S.scanB[a] = S.divided[a] ? 0 : 1;
+        __syncthreads();
+        const int U = block_exclusive_scan(S.scanB, m, warp_tot);
+        const int m_new = K + U;
+        if (m_new > MAXN) {
+            if (tid == 0) { atomicOr(err, ERRF_NODE_OVERFLOW); *out_n = 0; }
+            return;
+        }
+        // build the new list
+        for (int a = tid; a < m; a += OCT_THREADS) {
+            const int ax0 = S.x0[cur][a], ay0 = S.y0[cur][a], ax1 = S.x1[cur][a], ay1 = S.y1[cur][a];
+            if (S.divided[a]) {
+                const int hx = ax0 + ((ax1 - ax0 + 1) >> 1), hy = ay0 + ((ay1 - ay0 + 1) >> 1);
+                int t = S.scanA[a];
+                int nexp = 0;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const uint32_t cc = S.ccount[4 * a + q];
+                    if (cc > 0) {
+                        const int pos = K - 1 - t;
+                        t++;
+                        S.cpos[4 * a + q] = (uint16_t)pos;
+                        S.x0[nxt][pos] = (uint16_t)((q & 1) ? hx : ax0);
+                        S.x1[nxt][pos] = (uint16_t)((q & 1) ? ax1 : hx);
+                        S.y0[nxt][pos] = (uint16_t)((q & 2) ? hy : ay0);
+                        S.y1[nxt][pos] = (uint16_t)((q & 2) ? ay1 : hy);
+                        S.cnt[nxt][pos] = cc;
+                        nexp += cc > 1;
+                    }
+                }
+                if (nexp) atomicAdd(&s_nexpand, nexp);
+            } else {
+                const int pos = K + S.scanB[a];
+                S.keptpos[a] = (uint16_t)pos;
+                S.x0[nxt][pos] = (uint16_t)ax0; S.x1[nxt][pos] = (uint16_t)ax1;
+                S.y0[nxt][pos] = (uint16_t)ay0; S.y1[nxt][pos] = (uint16_t)ay1;
+                S.cnt[nxt][pos] = cnt[a];
+            }
+        }
+        __syncthreads();
+        for (int c = tid; c < n; c += OCT_THREADS) {
+            const int a = node_of[c];
+            if (S.divided[a]) {
+                const uint32_t pc = C[c];
+                const int q = quadrant_of(pc & 0xfff, (pc >> 12) & 0xfff, S.x0[cur][a], S.y0[cur][a], S.x1[cur][a], S.y1[cur][a]);
+                node_of[c] = S.cpos[4 * a + q];
+            } else
+                node_of[c] = S.keptpos[a];
+        }
+        __syncthreads();
+        if (tid == 0) {
+            // ref :640-644 and :706-707
+            if (m_new >= N || m_new == m) s_done = 1;
+            else if (phase == 1 && m_new + 3 * s_nexpand > N) s_phase = 2;
+        }
+        __syncthreads();
+        m = m_new;
+        cur = nxt;
+        if (s_done) break;
+    }
+
+    // ---- best keypoint per node (ref :713-730): max response, first in candidate order wins.
+    unsigned long long *best = S.keys;
+    for (int a = tid; a < m; a += OCT_THREADS) best[a] = 0;
+    __syncthreads();
+    for (int c = tid; c < n; c += OCT_THREADS) {
+        const uint32_t pc = C[c];
+        const uint32_t x = pc & 0xfff, y = (pc >> 12) & 0xfff, r = pc >> 24;
+        // candidate order = cells row-major, then row-major inside the cell (ref :758-793)
+        const uint32_t ci = (y - 3) / g.hCell, cj = (x - 3) / g.wCell;
+        const unsigned long long ord = ((unsigned long long)ci << 32) | ((unsigned long long)cj << 24) | ((unsigned long long)y << 12) | x;
+        const unsigned long long key = ((unsigned long long)(r + 1) << 40) | (~ord & 0xffffffffffull);
+        atomicMax(&best[node_of[c]], key);
+    }
+    __syncthreads();
+    for (int a = tid; a < m; a += OCT_THREADS) {
+        const unsigned long long key = best[a];
+        const unsigned long long ord = ~key & 0xffffffffffull;
+        if (a < g.kept_cap) {
+            Kept k;
+            k.x = (int16_t)((ord & 0xfff) + (EDGE - 3));          // += minBorderX (ref :809-810)
+            k.y = (int16_t)(((ord >> 12) & 0xfff) + (EDGE - 3));
+            k.response = (int32_t)(key >> 40) - 1;
+            out[a] = k;
+        }
+    }
+    if (tid == 0) {
+        if (m > g.kept_cap) { atomicOr(err, ERRF_NODE_OVERFLOW); m = g.kept_cap; }
+        *out_n = (uint32_t)m;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Orientation + descriptor, one warp per kept keypoint.  A 43x43 window of the (unblurred) level
+// is staged in shared memory; the intensity-centroid moments come from its central disc, the
+// 7x7 Gaussian is applied separably to the 37x37 patch the 256 rotated test pairs can reach.
+// ------------------------------------------------------------------------------------------
+constexpr int PW = 43;            // patch width (+-21)
+constexpr int PP = 44;            // patch pitch
+constexpr int BW = 37;            // blurred patch (+-18)
+constexpr int BP = 40;
+
+__device__ __forceinline__ float dev_fast_atan2(float y, float x) {
+    // cv::fastAtan2; every operation rounded separately (no FMA)
+    const float p1 = 57.283627f, p3 = -18.667446f, p5 = 8.9140005f, p7 = -2.5397246f;
+    const float eps = 2.2204460492503131e-16f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// glibc sincosf (the reference's cosf/sinf, ref :103-104) restated with unfused double
+// arithmetic; bit-identical to glibc 2.39 on every fp32 angle in [0, 2*pi).
+__device__ __forceinline__ float dev_sincos_poly(double x, double x2, bool alt, int n) {
+    if ((n & 1) == 0) {
+        const double s1c = -0x1.555545995a603p-3, s2c = 0x1.1107605230bc4p-7, s3c = -0x1.994eb3774cf24p-13;
+        const double x3 = __dmul_rn(x, x2);
+        const double s1 = __dadd_rn(s2c, __dmul_rn(x2, s3c));
+        const double x7 = __dmul_rn(x3, x2);
+        const double s = __dadd_rn(x, __dmul_rn(x3, s1c));
+        return __double2float_rn(__dadd_rn(s, __dmul_rn(x7, s1)));
+    }
+    const double sg = alt ? -1.0 : 1.0;
+    const double c0 = sg * 0x1p0, c1c = sg * -0x1.ffffffd0c621cp-2, c2c = sg * 0x1.55553e1068f19p-5,
+                 c3c = sg * -0x1.6c087e89a359dp-10, c4c = sg * 0x1.99343027bf8c3p-16;
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __dadd_rn(c3c, __dmul_rn(x2, c4c));
+    const double c1 = __dadd_rn(c0, __dmul_rn(x2, c1c));
+    const double x6 = __dmul_rn(x4, x2);
+    const double c = __dadd_rn(c1, __dmul_rn(x4, c2c));
+    return __double2float_rn(__dadd_rn(c, __dmul_rn(x6, c2)));
+}
+__device__ __forceinline__ void dev_sincosf(float y, float *sn, float *cs) {
+    double x = (double)y;
+    const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ff;
+    if (top < 0x3f4) {   // |y| < 0.75
+        if (top < 0x398) { *sn = y; *cs = 1.0f; return; }   // |y| < 2^-12
+        const double x2 = __dmul_rn(x, x);
+        *sn = dev_sincos_poly(x, x2, false, 0);
+        *cs = dev_sincos_poly(x, x2, false, 1);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    const bool alt = (n & 2) != 0;
+    const double hpi = alt ? -0x1.921FB54442D18p0 : 0x1.921FB54442D18p0;
+    // reduce_fast uses table[0].hpi: x - n*hpi
+    x = __dsub_rn(x, __dmul_rn((double)n, 0x1.921FB54442D18p0));
+    (void)hpi;
+    const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    const double xs = __dmul_rn(x, sgn), x2 = __dmul_rn(x, x);
+    *sn = dev_sincos_poly(xs, x2, alt, n);
+    *cs = dev_sincos_poly(xs, x2, alt, n ^ 1);
+}
+
+__global__ void __launch_bounds__(DESC_WARPS * 32)
+k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Kept *__restrict__ kept,
+           const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp, uint8_t *__restrict__ out_desc,
+           int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
+    __shared__ uint8_t s_patch[DESC_WARPS][PW * PP];    // raw window; reused for the blurred patch
+    __shared__ uint16_t s_h[DESC_WARPS][PW * BP];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y;
+    // flat slot -> (level, index) over the per-level kept capacities
+    int slot = blockIdx.x * DESC_WARPS + warp;
+    int level = 0;
+    while (level < G->nlevels && slot >= G->lv[level].kept_cap) { slot -= G->lv[level].kept_cap; level++; }
+    if (level >= G->nlevels) return;
+    const uint32_t *kc = kept_count + (size_t)b * G->nlevels;
+    if (slot >= (int)kc[level]) return;
+    int base = 0, total = 0;
+    for (int l = 0; l < G->nlevels; l++) {
+        if (l < level) base += kc[l];
+        total += kc[l];
+    }
+    if (base == 0 && slot == 0 && lane == 0) out_n[b] = total;   // first non-empty level's first warp
+    const int oidx = base + slot;
+    if (oidx >= capacity) {
+        if (lane == 0) atomicOr(err, ERRF_OUT_OVERFLOW);
+        return;
+    }
+    const LevelGeom &g = G->lv[level];
+    const Kept kp = kept[(size_t)b * G->kept_frame + g.kept_off + slot];
+    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
+
+    uint8_t *P = s_patch[warp];
+    const uint8_t *src = img + (ptrdiff_t)(kp.y - 21) * g.pitch + (kp.x - 21);
+    for (int i = lane; i < PW * PW; i += 32) {
+        const int y = i / PW, x = i - y * PW;
+        P[y * PP + x] = src[(ptrdiff_t)y * g.pitch + x];
+    }
+    __syncwarp();
+
+    // ---- IC_Angle (ref :73-98): lanes own columns u = lane-15 .. of the 31-wide disc
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int u = lane - 15, au = abs(u);
+        const uint8_t *c = P + 21 * PP + 21 + u;
+        m10 = u * c[0];
+        for (int v = 1; v <= 15; v++) {
+            if (au <= c_umax[v]) {
+                const int vp = c[v * PP], vm = c[-v * PP];
+                m10 += u * (vp + vm);
+                m01 += v * (vp - vm);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = dev_fast_atan2((float)m01, (float)m10);
+
+    // ---- 7x7 Gaussian, sigma 2: H = sum k*src (16 bit), out = (sum k*H + 32768) >> 16
+    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    uint16_t *H = s_h[warp];
+    for (int i = lane; i < PW * BW; i += 32) {
+        const int y = i / BW, x = i - y * BW;
+        const uint8_t *r = P + y * PP + x;   // covers patch columns x .. x+6
+        H[y * BP + x] = (uint16_t)(k0 * (r[0] + r[6]) + k1 * (r[1] + r[5]) + k2 * (r[2] + r[4]) + k3 * r[3]);
+    }
+    __syncwarp();
+    uint8_t *Bl = P;   // the raw window is dead once H is built (BW*BP <= PW*PP)
+    for (int i = lane; i < BW * BW; i += 32) {
+        const int y = i / BW, x = i - y * BW;
+        const uint16_t *r = H + y * BP + x;
+        const int v = k0 * (r[0] + r[6 * BP]) + k1 * (r[BP] + r[5 * BP]) + k2 * (r[2 * BP] + r[4 * BP]) + k3 * r[3 * BP];
+        Bl[y * BP + x] = (uint8_t)min((v + 32768) >> 16, 255);
+    }
+    __syncwarp();
+
+    // ---- steered BRIEF (ref :101-144): lane computes descriptor byte `lane`
+    float sn, cs;
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);   // ref :100
+    dev_sincosf(__fmul_rn(angle, factorPI), &sn, &cs);
+    const uint8_t *ctr = Bl + 18 * BP + 18;
+    const int8_t *pat = c_pattern + lane * 32;
+    uint32_t val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float x0 = (float)pat[4 * k], y0 = (float)pat[4 * k + 1], x1 = (float)pat[4 * k + 2], y1 = (float)pat[4 * k + 3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sn), __fmul_rn(y0, cs)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, cs), __fmul_rn(y0, sn)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sn), __fmul_rn(y1, cs)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, cs), __fmul_rn(y1, sn)));
+        const int t0 = ctr[r0 * BP + c0], t1 = ctr[r1 * BP + c1];
+        val |= (uint32_t)(t0 < t1) << k;
+    }
+    out_desc[((size_t)b * capacity + oidx) * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orb_keypoint o;
+        o.x = (float)kp.x; o.y = (float)kp.y;
+        if (level != 0) { o.x = __fmul_rn(o.x, g.scale); o.y = __fmul_rn(o.y, g.scale); }   // ref :1035-1041
+        o.size = g.size;
+        o.angle = angle;
+        o.response = (float)kp.response;
+        o.octave = level;
+        o.class_id = -1;
+        out_kp[(size_t)b * capacity + oidx] = o;
+    }
+}
+
+// Full-plane blur with the same arithmetic, for parity tests of the blur in isolation.
+__global__ void k_blur_level(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, int level, int b,
+                             uint8_t *__restrict__ dst, int dpitch) {
+    const LevelGeom &g = G->lv[level];
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= g.w) return;
+    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
+    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    const int kk[7] = {k0, k1, k2, k3, k2, k1, k0};
+    int acc = 0;
+    for (int j = 0; j < 7; j++) {
+        const uint8_t *r = img + (ptrdiff_t)(y + j - 3) * g.pitch + x;   // padded plane == reflect101
+        int hsum = 0;
+        for (int i = 0; i < 7; i++) hsum += kk[i] * r[i - 3];
+        acc += kk[j] * hsum;
+    }
+    dst[(size_t)y * dpitch + x] = (uint8_t)min((acc + 32768) >> 16, 255);
+}
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+// ------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------
+struct orb_extractor {
+    orb_params prm;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> per_level;
+    int umax[16];
+    Geom geom;                 // host copy
+    Geom *d_geom = nullptr;
+    ResizeTap *d_taps = nullptr;
+    size_t taps_cap = 0;
+    uint8_t *d_src = nullptr;  size_t src_bytes = 0;
+    uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
+    uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
+    uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
+    Kept *d_kept = nullptr; size_t kept_elems = 0;
+    orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
+    size_t out_cap_elems = 0;
+    int *d_err = nullptr;
+    int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
+    int last_batch = 0;
+    int64_t launches = 0;
+    size_t oct_smem = 0;
+};
+
+static int cv_round_host(double v) { return (int)std::nearbyint(v); }
+
+static void build_tables(orb_extractor *ex) {
+    // ref ORBextractor::ORBextractor :404-460 (same statements as the reference, float/double mix kept)
+    const orb_params &p = ex->prm;
+    const int nl = p.nlevels;
+    const double scaleFactor = p.scale_factor;
+    ex->scale.assign(nl, 1.f); ex->sigma2.assign(nl, 1.f); ex->inv_scale.assign(nl, 1.f); ex->inv_sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; i++) {
+        ex->scale[i] = (float)(ex->scale[i - 1] * scaleFactor);
+        ex->sigma2[i] = ex->scale[i] * ex->scale[i];
+    }
+    for (int i = 0; i < nl; i++) {
+        ex->inv_scale[i] = 1.0f / ex->scale[i];
+        ex->inv_sigma2[i] = 1.0f / ex->sigma2[i];
+    }
+    ex->per_level.assign(nl, 0);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = p.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; l++) {
+        ex->per_level[l] = cv_round_host(nDesired);
+        sum += ex->per_level[l];
+        nDesired *= factor;
+    }
+    ex->per_level[nl - 1] = std::max(p.nfeatures - sum, 0);
+    int v, v0;
+    const int vmax = (int)std::floor(15 * std::sqrt(2.f) / 2 + 1), vmin = (int)std::ceil(15 * std::sqrt(2.f) / 2);
+    for (v = 0; v < 16; v++) ex->umax[v] = 0;
+    for (v = 0; v <= vmax; ++v) ex->umax[v] = cv_round_host(std::sqrt(225.0 - v * v));
+    for (v = 15, v0 = 0; v >= vmin; --v) {
+        while (ex->umax[v0] == ex->umax[v0 + 1]) ++v0;
+        ex->umax[v] = v0;
+        ++v0;
+    }
+}
+
+// Level geometry for a (width,height) image; returns ORB_ERR_TOO_SMALL where the reference would
+// divide by zero.  taps (optional) receives the resize tables.
+static int compute_geometry(const orb_extractor *ex, int width, int height, Geom *G, std::vector<ResizeTap> *taps) {
+    const orb_params &p = ex->prm;
+    memset(G, 0, sizeof(*G));
+    G->nlevels = p.nlevels; G->width = width; G->height = height;
+    G->ini_th = p.ini_th_fast; G->min_th = p.min_th_fast; G->blur_taps = p.blur_taps;
+    long long off = 0;
+    int cells = 0, cand = 0, kept = 0, maxn = 0, tapoff = 0;
+    if (taps) taps->clear();
+    for (int l = 0; l < p.nlevels; l++) {
+        LevelGeom &g = G->lv[l];
+        g.w = cv_round_host((float)width * ex->inv_scale[l]);      // ref :1049-1051
+        g.h = cv_round_host((float)height * ex->inv_scale[l]);
+        g.pitch = (XOFF + g.w + EDGE + 127) / 128 * 128;
+        g.plane_off = off;
+        g.interior_off = off + (long long)EDGE * g.pitch + XOFF;
+        off += (long long)g.pitch * (g.h + 2 * EDGE);
+        off = (off + 255) / 256 * 256;
+        const int minB = EDGE - 3;
+        g.maxBX = g.w - EDGE + 3; g.maxBY = g.h - EDGE + 3;
+        const float wf = (float)(g.maxBX - minB), hf = (float)(g.maxBY - minB);
+        if (wf < 30.f || hf < 30.f) return ORB_ERR_TOO_SMALL;
+        const int nCols = (int)(wf / 30.f), nRows = (int)(hf / 30.f);                 // ref :753-754
+        g.wCell = (int)std::ceil(wf / nCols); g.hCell = (int)std::ceil(hf / nRows);   // ref :755-756
+        if (g.wCell + 6 > FAST_TILE_MAX || g.hCell + 6 > FAST_TILE_MAX) return ORB_ERR_INVALID;
+        g.ncx = 0; g.ncy = 0;
+        for (int j = 0; j < nCols; j++) if (!(minB + j * g.wCell >= g.maxBX - 6)) g.ncx = j + 1;   // ref :770
+        for (int i = 0; i < nRows; i++) if (!(minB + i * g.hCell >= g.maxBY - 3)) g.ncy = i + 1;   // ref :762
+        g.cell_begin = cells;
+        cells += g.ncx * g.ncy;
+        g.win_w = g.maxBX - minB; g.win_h = g.maxBY - minB;
+        g.quota = ex->per_level[l];
+        g.nIni = (int)std::round(static_cast<float>(g.win_w) / g.win_h);              // ref :530
+        if (g.nIni < 1) return ORB_ERR_TOO_SMALL;
+        if (g.nIni > MAX_INI) return ORB_ERR_INVALID;
+        g.hX = static_cast<float>(g.win_w) / g.nIni;                                  // ref :532
+        for (int i = 0; i <= g.nIni; i++) g.ini_x[i] = (int)(g.hX * static_cast<float>(i));   // ref :541-542
+        if (g.win_w > 4095 || g.win_h > 4095) return ORB_ERR_INVALID;
+        g.cand_off = cand;
+        g.cand_cap = ((g.win_w - 6) * (g.win_h - 6)) / 4 + 64;
+        cand += (g.cand_cap + 63) / 64 * 64;
+        g.kept_off = kept;
+        g.kept_cap = std::max(g.quota + 3, 4 * g.nIni) + 1;
+        kept += g.kept_cap;
+        maxn = std::max(maxn, g.kept_cap);
+        g.scale = ex->scale[l];
+        g.size = (float)(int)(31 * ex->scale[l]);                                     // ref :804
+        if (l > 0) {
+            const LevelGeom &s = G->lv[l - 1];
+            g.tap_x_off = tapoff; g.tap_y_off = tapoff + g.w;
+            tapoff += g.w + g.h;
+            if (taps) {
+                // cv::resize INTER_LINEAR coefficient tables
+                for (int axis = 0; axis < 2; axis++) {
+                    const int dn = axis ? g.h : g.w, sn = axis ? s.h : s.w;
+                    const double sc = 1.0 / ((double)dn / sn);
+                    for (int d = 0; d < dn; d++) {
+                        float f = (float)((d + 0.5) * sc - 0.5);
+                        int si = (int)std::floor(f);
+                        f -= si;
+                        if (si < 0) { f = 0; si = 0; }
+                        if (si >= sn - 1) { f = 0; si = sn - 1; }
+                        ResizeTap t;
+                        t.s0 = (int16_t)si; t.s1 = (int16_t)std::min(si + 1, sn - 1);
+                        t.a0 = (int16_t)cv_round_host((1.f - f) * 2048.f);
+                        t.a1 = (int16_t)cv_round_host(f * 2048.f);
+                        taps->push_back(t);
+                    }
+                }
+            }
+        }
+    }
+    G->total_cells = cells; G->cand_frame = cand; G->kept_frame = kept; G->pyr_frame = off; G->max_nodes = maxn;
+    return ORB_OK;
+}
+
+static size_t octree_smem_bytes(int maxn) {
+    int sort_n = 1;
+    while (sort_n < maxn) sort_n <<= 1;
+    return 8 * (size_t)sort_n + (size_t)maxn * (16 + 8 + 4 + 4 + 8 + 16 + 2 + 1) + 64;
+}
+
+static void free_all(orb_extractor *ex) {
+    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_cand);
+    cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
+    cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err);
+    if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
+    if (ex->stream) cudaStreamDestroy(ex->stream);
+}
+
+static int upload_constants_once() {
+    static std::mutex mu;
+    static std::vector<int> done_devices;
+    std::lock_guard<std::mutex> lk(mu);
+    int dev = 0;
+    ORB_CUDA_TRY(cudaGetDevice(&dev));
+    if (std::find(done_devices.begin(), done_devices.end(), dev) != done_devices.end()) return ORB_OK;
+    static const int pat[ORB_PATTERN_INTS] = {ORB_PATTERN_VALUES};
+    int8_t p8[ORB_PATTERN_INTS];
+    for (int i = 0; i < ORB_PATTERN_INTS; i++) p8[i] = (int8_t)pat[i];
+    ORB_CUDA_TRY(cudaMemcpyToSymbol(c_pattern, p8, sizeof(p8)));
+    done_devices.push_back(dev);
+    return ORB_OK;
+}
+
+static int set_geometry(orb_extractor *ex, int width, int height) {
+    if (ex->geom.width == width && ex->geom.height == height && ex->geom.nlevels == ex->prm.nlevels) return ORB_OK;
+    Geom G;
+    std::vector<ResizeTap> taps;
+    int rc = compute_geometry(ex, width, height, &G, &taps);
+    ORB_REQUIRE(rc == ORB_OK, rc, "image %dx%d: %s", width, height,
+                rc == ORB_ERR_TOO_SMALL ? "a pyramid level is too small for the 30-px cell grid (reference divides by zero)"
+                                        : "unsupported geometry");
+    ORB_REQUIRE(taps.size() <= ex->taps_cap, ORB_ERR_INVALID, "internal: tap pool too small");
+    ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_geom, &G, sizeof(G), cudaMemcpyHostToDevice, ex->stream));
+    if (!taps.empty())
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_taps, taps.data(), taps.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice, ex->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));   // `taps` and G are stack/heap temporaries
+    ex->geom = G;
+    return ORB_OK;
+}
+
+extern "C" {
+
+const char *orb_last_error(void) { return g_err; }
+int orb_abi_version(void) { return ORBGPU_ABI_VERSION; }
+
+int orb_extractor_create(const orb_params *params, orb_extractor **out) {
+    ORB_REQUIRE(params && out, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(params->nlevels >= 1 && params->nlevels <= ORB_MAX_LEVELS, ORB_ERR_INVALID, "nlevels out of range");
+    ORB_REQUIRE(params->nfeatures >= 1 && params->nfeatures <= 60000, ORB_ERR_INVALID, "nfeatures out of range");
+    ORB_REQUIRE(params->scale_factor > 1.0f, ORB_ERR_INVALID, "scale_factor must be > 1");
+    ORB_REQUIRE(params->max_width >= 1 && params->max_height >= 1 && params->max_width <= 4000 && params->max_height <= 4000,
+                ORB_ERR_INVALID, "max_width/max_height out of range");
+    ORB_REQUIRE(params->max_batch >= 1 && params->max_batch <= 4096, ORB_ERR_INVALID, "max_batch out of range");
+    ORB_REQUIRE(params->ini_th_fast >= 1 && params->min_th_fast >= 1 && params->ini_th_fast < 255 && params->min_th_fast < 255,
+                ORB_ERR_INVALID, "FAST thresholds out of range");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback",
+                cudaGetErrorString(e));
+    orb_extractor *ex = new orb_extractor();
+    ex->prm = *params;
+    if (params->device >= 0) {
+        ORB_CUDA_TRY(cudaSetDevice(params->device));
+        ex->device = params->device;
+    } else {
+        ORB_CUDA_TRY(cudaGetDevice(&ex->device));
+    }
+    build_tables(ex);
+    memset(&ex->geom, 0, sizeof(ex->geom));
+    Geom G;
+    int rc = compute_geometry(ex, params->max_width, params->max_height, &G, nullptr);
+    if (rc != ORB_OK) {
+        delete ex;
+        set_error("max image %dx%d: a pyramid level is too small or the geometry is unsupported", params->max_width, params->max_height);
+        return rc;
+    }
+    const size_t B = params->max_batch;
+    rc = upload_constants_once();
+    if (rc != ORB_OK) { delete ex; return rc; }
+#define TRY_ALLOC(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error("%s -> %s", #expr, cudaGetErrorString(_e)); free_all(ex); delete ex; return ORB_ERR_CUDA; } } while (0)
+    TRY_ALLOC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
+    TRY_ALLOC(cudaMemcpyToSymbol(c_umax, ex->umax, sizeof(ex->umax)));
+    TRY_ALLOC(cudaMalloc(&ex->d_geom, sizeof(Geom)));
+    // sizes below are monotone in the image size except the kept pool (aspect dependent): bound it
+    size_t kept_frame = 0;
+    int maxn = 0;
+    for (int l = 0; l < params->nlevels; l++) {
+        int cap = std::max(ex->per_level[l] + 3, 4 * MAX_INI) + 1;
+        kept_frame += cap;
+        maxn = std::max(maxn, cap);
+    }
+    ex->taps_cap = (size_t)(params->max_width + params->max_height + 64) * params->nlevels;
+    TRY_ALLOC(cudaMalloc(&ex->d_taps, ex->taps_cap * sizeof(ResizeTap)));
+    ex->src_bytes = B * (size_t)params->max_height * ((params->max_width + 127) / 128 * 128);
+    TRY_ALLOC(cudaMalloc(&ex->d_src, ex->src_bytes));
+    ex->pyr_bytes = B * (size_t)(G.pyr_frame + 4096 * params->nlevels);
+    TRY_ALLOC(cudaMalloc(&ex->d_pyr, ex->pyr_bytes));
+    TRY_ALLOC(cudaMemsetAsync(ex->d_pyr, 0, ex->pyr_bytes, ex->stream));
+    ex->cand_elems = B * (size_t)(G.cand_frame + 64 * params->nlevels);
+    TRY_ALLOC(cudaMalloc(&ex->d_cand, ex->cand_elems * 4));
+    TRY_ALLOC(cudaMalloc(&ex->d_node_of, ex->cand_elems * 2));
+    TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 2 * sizeof(uint32_t)));
+    ex->kept_elems = B * kept_frame;
+    TRY_ALLOC(cudaMalloc(&ex->d_kept, ex->kept_elems * sizeof(Kept)));
+    ex->out_cap_elems = B * kept_frame;
+    TRY_ALLOC(cudaMalloc(&ex->d_out_kp, ex->out_cap_elems * sizeof(orb_keypoint)));
+    TRY_ALLOC(cudaMalloc(&ex->d_out_desc, ex->out_cap_elems * 32));
+    TRY_ALLOC(cudaMalloc(&ex->d_out_n, B * sizeof(int32_t)));
+    TRY_ALLOC(cudaMalloc(&ex->d_err, sizeof(int)));
+    TRY_ALLOC(cudaMemsetAsync(ex->d_err, 0, sizeof(int), ex->stream));
+    TRY_ALLOC(cudaMallocHost(&ex->h_pinned, (1 + B) * sizeof(int)));
+    ex->oct_smem = octree_smem_bytes(maxn);
+    TRY_ALLOC(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+    TRY_ALLOC(cudaStreamSynchronize(ex->stream));
+#undef TRY_ALLOC
+    *out = ex;
+    return ORB_OK;
+}
+
+void orb_extractor_destroy(orb_extractor *ex) {
+    if (!ex) return;
+    cudaSetDevice(ex->device);
+    cudaStreamSynchronize(ex->stream);
+    free_all(ex);
+    delete ex;
+}
+
+int orb_extractor_tables(const orb_extractor *ex, float *scale, float *inv_scale, float *sigma2, float *inv_sigma2,
+                         int32_t *features_per_level) {
+    ORB_REQUIRE(ex, ORB_ERR_INVALID, "null handle");
+    for (int i = 0; i < ex->prm.nlevels; i++) {
+        if (scale) scale[i] = ex->scale[i];
+        if (inv_scale) inv_scale[i] = ex->inv_scale[i];
+        if (sigma2) sigma2[i] = ex->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = ex->inv_sigma2[i];
+        if (features_per_level) features_per_level[i] = ex->per_level[i];
+    }
+    return ORB_OK;
+}
+
+void *orb_extractor_stream(orb_extractor *ex) { return ex ? (void *)ex->stream : nullptr; }
+int64_t orb_extractor_launch_count(const orb_extractor *ex) { return ex ? ex->launches : 0; }
+
+int orb_extractor_sync(orb_extractor *ex) {
+    ORB_REQUIRE(ex, ORB_ERR_INVALID, "null handle");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+    return ORB_OK;
+}
+
+static int check_err_flags(int flags) {
+    if (flags & ERRF_CAND_OVERFLOW) { set_error("FAST candidate pool overflow"); return ORB_ERR_CAPACITY; }
+    if (flags & ERRF_NODE_OVERFLOW) { set_error("quadtree node pool overflow"); return ORB_ERR_CAPACITY; }
+    if (flags & ERRF_OUT_OVERFLOW) { set_error("more keypoints than `capacity`; n_out holds the required size"); return ORB_ERR_CAPACITY; }
+    return ORB_OK;
+}
+
+int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int width, int height, int pitch,
+                      size_t frame_stride, int image_loc, orb_keypoint *keypoints, uint8_t *descriptors, int capacity,
+                      int32_t *n_out, int out_loc) {
+    ORB_REQUIRE(ex && n_out, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(batch >= 1 && batch <= ex->prm.max_batch, ORB_ERR_INVALID, "batch %d exceeds max_batch %d", batch, ex->prm.max_batch);
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    if (width == 0 || height == 0 || !images) {   // ref :987-988: empty image, silent return
+        if (out_loc == ORB_HOST) for (int b = 0; b < batch; b++) n_out[b] = 0;
+        else ORB_CUDA_TRY(cudaMemsetAsync(n_out, 0, batch * sizeof(int32_t), ex->stream));
+        ex->last_batch = 0;
+        return ORB_OK;
+    }
+    ORB_REQUIRE(width > 0 && height > 0 && pitch >= width, ORB_ERR_INVALID, "bad image geometry");
+    ORB_REQUIRE(width <= ex->prm.max_width && height <= ex->prm.max_height, ORB_ERR_INVALID,
+                "image %dx%d exceeds the handle's max %dx%d", width, height, ex->prm.max_width, ex->prm.max_height);
+    ORB_REQUIRE(capacity >= 1 && keypoints && descriptors, ORB_ERR_INVALID, "output buffers missing");
+    int rc = set_geometry(ex, width, height);
+    if (rc != ORB_OK) return rc;
+    const Geom &G = ex->geom;
+    cudaStream_t st = ex->stream;
+
+    const uint8_t *d_images = images;
+    size_t d_stride = frame_stride;
+    int d_pitch = pitch;
+    if (image_loc == ORB_HOST) {
+        d_pitch = (width + 127) / 128 * 128;
+        d_stride = (size_t)d_pitch * height;
+        if ((size_t)pitch * height == frame_stride || batch == 1) {
+            ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src, d_pitch, images, pitch, width, (size_t)height * (batch == 1 ? 1 : batch),
+                                           cudaMemcpyHostToDevice, st));
+        } else {
+            for (int b = 0; b < batch; b++)
+                ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src + b * d_stride, d_pitch, images + b * frame_stride, pitch, width, height,
+                                               cudaMemcpyHostToDevice, st));
+        }
+        d_images = ex->d_src;
+    }
+    orb_keypoint *o_kp = keypoints;
+    uint8_t *o_desc = descriptors;
+    int32_t *o_n = n_out;
+    if (out_loc == ORB_HOST) {
+        if ((size_t)batch * capacity > ex->out_cap_elems) {
+            // grow the staging buffers to the caller's capacity
+            cudaFree(ex->d_out_kp); cudaFree(ex->d_out_desc);
+            ex->d_out_kp = nullptr; ex->d_out_desc = nullptr;
+            ex->out_cap_elems = (size_t)ex->prm.max_batch * capacity;
+            ORB_CUDA_TRY(cudaMalloc(&ex->d_out_kp, ex->out_cap_elems * sizeof(orb_keypoint)));
+            ORB_CUDA_TRY(cudaMalloc(&ex->d_out_desc, ex->out_cap_elems * 32));
+        }
+        o_kp = ex->d_out_kp; o_desc = ex->d_out_desc; o_n = ex->d_out_n;
+    }
+
+    uint32_t *d_cand_count = ex->d_counts;
+    uint32_t *d_kept_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels;
+    ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
+    ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
+
+    {
+        const LevelGeom &g = G.lv[0];
+        dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
+        k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
+        ex->launches++;
+    }
+    for (int l = 1; l < G.nlevels; l++) {
+        const LevelGeom &g = G.lv[l];
+        dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
+        k_pyr_resize<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
+        ex->launches++;
+    }
+    k_fast_cells<<<dim3(G.total_cells, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_cand, d_cand_count, ex->d_err);
+    ex->launches++;
+    k_octree<<<dim3(G.nlevels, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), st>>>(
+        ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err);
+    ex->launches++;
+    k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
+        ex->d_pyr, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
+    ex->launches++;
+    ORB_CUDA_TRY(cudaGetLastError());
+    ex->last_batch = batch;
+
+    if (out_loc == ORB_HOST) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(keypoints, o_kp, (size_t)batch * capacity * sizeof(orb_keypoint), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(descriptors, o_desc, (size_t)batch * capacity * 32, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaStreamSynchronize(st));
+        for (int b = 0; b < batch; b++) n_out[b] = ex->h_pinned[1 + b];
+        const int flags = ex->h_pinned[0];
+        if (flags) {
+            cudaMemsetAsync(ex->d_err, 0, sizeof(int), st);
+            return check_err_flags(flags);
+        }
+    }
+    return ORB_OK;
+}
+
+int orb_extract(orb_extractor *ex, const uint8_t *image, int width, int height, int pitch, int image_loc,
+                orb_keypoint *keypoints, uint8_t *descriptors, int capacity, int *n_out) {
+    int32_t n = 0;
+    int rc = orb_extract_batch(ex, image, 1, width, height, pitch, (size_t)pitch * height, image_loc, keypoints, descriptors,
+                               capacity, &n, ORB_HOST);
+    if (n_out) *n_out = n;
+    return rc;
+}
+
+/* Error flags raised by device-output (asynchronous) batches; clears them. */
+int orb_extractor_check(orb_extractor *ex) {
+    ORB_REQUIRE(ex, ORB_ERR_INVALID, "null handle");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+    const int flags = ex->h_pinned[0];
+    if (flags) {
+        cudaMemsetAsync(ex->d_err, 0, sizeof(int), ex->stream);
+        return check_err_flags(flags);
+    }
+    return ORB_OK;
+}
+
+int orb_pyramid_level(const orb_extractor *ex, int slot, int level, const uint8_t **dev_interior, int *width, int *height,
+                      int *pitch) {
+    ORB_REQUIRE(ex, ORB_ERR_INVALID, "null handle");
+    ORB_REQUIRE(ex->geom.width > 0, ORB_ERR_INVALID, "no frame extracted yet");
+    ORB_REQUIRE(level >= 0 && level < ex->geom.nlevels && slot >= 0 && slot < ex->prm.max_batch, ORB_ERR_INVALID, "bad level/slot");
+    const LevelGeom &g = ex->geom.lv[level];
+    if (dev_interior) *dev_interior = ex->d_pyr + (size_t)slot * ex->geom.pyr_frame + g.interior_off;
+    if (width) *width = g.w;
+    if (height) *height = g.h;
+    if (pitch) *pitch = g.pitch;
+    return ORB_OK;
+}
+
+int orb_pyramid_download(orb_extractor *ex, int slot, int level, int with_border, uint8_t *dst, int dst_pitch) {
+    const uint8_t *p;
+    int w, h, pitch;
+    int rc = orb_pyramid_level(ex, slot, level, &p, &w, &h, &pitch);
+    if (rc != ORB_OK) return rc;
+    ORB_REQUIRE(dst, ORB_ERR_INVALID, "null dst");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    if (with_border) {
+        p -= (size_t)EDGE * pitch + EDGE;
+        w += 2 * EDGE; h += 2 * EDGE;
+    }
+    ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_pitch, p, pitch, w, h, cudaMemcpyDeviceToHost, ex->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+    return ORB_OK;
+}
+
+int orb_debug_candidates(orb_extractor *ex, int slot, int level, orb_candidate *out, int capacity, int *n_out) {
+    ORB_REQUIRE(ex && out && n_out, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(ex->geom.width > 0 && level >= 0 && level < ex->geom.nlevels && slot >= 0 && slot < ex->prm.max_batch,
+                ORB_ERR_INVALID, "bad level/slot");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    const LevelGeom &g = ex->geom.lv[level];
+    uint32_t n = 0;
+    ORB_CUDA_TRY(cudaMemcpyAsync(&n, ex->d_counts + (size_t)slot * ex->geom.nlevels + level, 4, cudaMemcpyDeviceToHost, ex->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+    n = std::min<uint32_t>(n, g.cand_cap);
+    std::vector<uint32_t> raw(n);
+    if (n) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(raw.data(), ex->d_cand + (size_t)slot * ex->geom.cand_frame + g.cand_off, n * 4ull,
+                                     cudaMemcpyDeviceToHost, ex->stream));
+        ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+    }
+    *n_out = (int)n;
+    ORB_REQUIRE((int)n <= capacity, ORB_ERR_CAPACITY, "candidate buffer too small");
+    // the device list is unordered; restore the reference's order (cells row-major, then row-major)
+    std::vector<std::pair<uint64_t, uint32_t>> keyed(n);
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t x = raw[i] & 0xfff, y = (raw[i] >> 12) & 0xfff;
+        const uint64_t ci = (y - 3) / g.hCell, cj = (x - 3) / g.wCell;
+        keyed[i] = {(ci << 32) | (cj << 24) | ((uint64_t)y << 12) | x, raw[i]};
+    }
+    std::sort(keyed.begin(), keyed.end());
+    for (uint32_t i = 0; i < n; i++) {
+        out[i].x = (int16_t)(keyed[i].second & 0xfff);
+        out[i].y = (int16_t)((keyed[i].second >> 12) & 0xfff);
+        out[i].response = (int32_t)(keyed[i].second >> 24);
+    }
+    return ORB_OK;
+}
+
+int orb_debug_blur_level(orb_extractor *ex, int slot, int level, uint8_t *dst, int dst_pitch) {
+    ORB_REQUIRE(ex && dst, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(ex->geom.width > 0 && level >= 0 && level < ex->geom.nlevels && slot >= 0 && slot < ex->prm.max_batch,
+                ORB_ERR_INVALID, "bad level/slot");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    const LevelGeom &g = ex->geom.lv[level];
+    uint8_t *d_tmp = nullptr;
+    ORB_CUDA_TRY(cudaMalloc(&d_tmp, (size_t)g.w * g.h));
+    k_blur_level<<<dim3((g.w + 127) / 128, g.h), 128, 0, ex->stream>>>(ex->d_pyr, ex->d_geom, level, slot, d_tmp, g.w);
+    ex->launches++;
+    cudaError_t e = cudaMemcpy2DAsync(dst, dst_pitch, d_tmp, g.w, g.w, g.h, cudaMemcpyDeviceToHost, ex->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ex->stream);
+    cudaFree(d_tmp);
+    ORB_CUDA_TRY(e);
+    return ORB_OK;
+}
+
+}  // extern "C"

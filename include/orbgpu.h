@@ -105,6 +105,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
                       orb_keypoint *keypoints, uint8_t *descriptors, int capacity,
                       int32_t *n_out, int out_loc);
 int orb_extractor_sync(orb_extractor *ex);
+/* Device-output batches are asynchronous: overflow conditions they hit are latched on the device.
+ * Synchronises, returns ORB_ERR_CAPACITY if any was raised since the last check, and clears it. */
+int orb_extractor_check(orb_extractor *ex);
 /* cudaStream_t of the handle as an opaque pointer (for event timing on the launching stream). */
 void *orb_extractor_stream(orb_extractor *ex);
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */

@@ -1,0 +1,115 @@
+"""GPU parity: liborbgpu's extractor (through the C ABI) against the CPU oracle, stage by stage and
+end to end, bit-exact.  ref: ORB_SLAM2/src/ORBextractor.cc."""
+import numpy as np
+import pytest
+
+from ar_orbslam2_b200.synth import synth_frame
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [  # (width, height, nfeatures, seed)   SURVEY 8: C1, C2, C3, C1-init
+    (640, 480, 1000, 0),
+    (1241, 376, 2000, 3),
+    (752, 480, 1000, 5),
+    (640, 480, 2000, 11),
+]
+
+
+def _sorted(c):
+    return c
+
+
+@pytest.mark.parametrize("w,h,nf,seed", CONFIGS)
+def test_stages_and_end_to_end(oracle, gpu_lib, w, h, nf, seed):
+    from ar_orbslam2_b200.extractor import ORBextractor
+    img = synth_frame(w, h, seed)
+    ref = oracle.RefExtractor(nf)
+    rk, rd = ref.extract(img)
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    gk, gd = ex(img)
+    # E3 pyramid incl. the 19-px reflect-101 frame
+    for l in range(8):
+        assert ex.level_size(l) == ref.level_size(l)
+        a, b = ex.pyramid_level(l, True), ref.pyramid_level(l, True)
+        assert np.array_equal(a, b), f"pyramid level {l}: {int((a != b).sum())} pixels differ"
+    # E4/E5 FAST candidates in reference order
+    for l in range(8):
+        a, b = ex.candidates(l), ref.candidates(l)
+        assert len(a) == len(b), f"level {l}: {len(a)} candidates vs {len(b)}"
+        assert np.array_equal(a, b), f"level {l}: candidate lists differ"
+    # E8 blur
+    for l in (0, 3, 7):
+        assert np.array_equal(ex.blurred_level(l), ref.blurred_level(l)), f"blur level {l}"
+    # E6/E7/E9/E10 final keypoints + descriptors, exact order
+    assert len(gk) == len(rk), f"{len(gk)} keypoints vs {len(rk)}"
+    for f in ("octave", "x", "y", "response", "size", "class_id"):
+        assert np.array_equal(gk[f], rk[f]), f"keypoint field {f} differs at {np.flatnonzero(gk[f] != rk[f])[:8]}"
+    assert np.array_equal(gk["angle"].view(np.uint32), rk["angle"].view(np.uint32)), "angles differ bitwise"
+    assert np.array_equal(gd, rd), f"{int((gd != rd).any(axis=1).sum())} descriptors differ"
+    ex.close()
+
+
+def test_batch_matches_single(oracle, gpu_lib):
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h = 640, 480
+    frames = np.stack([synth_frame(w, h, s) for s in (21, 22, 23, 24, 25)])
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=5)
+    out = ex.extract_batch(frames)
+    ref = oracle.RefExtractor(1000)
+    for b in range(5):
+        rk, rd = ref.extract(frames[b])
+        gk, gd = out[b]
+        assert len(gk) == len(rk)
+        assert gk.tobytes() == rk.tobytes()
+        assert np.array_equal(gd, rd)
+    ex.close()
+
+
+def test_geometry_change_and_errors(oracle, gpu_lib):
+    from ar_orbslam2_b200 import _lib
+    from ar_orbslam2_b200.extractor import ORBextractor
+    ex = ORBextractor(500, 1.2, 8, 20, 7, max_width=800, max_height=600)
+    ref = oracle.RefExtractor(500)
+    for (w, h, s) in [(800, 600, 1), (320, 240, 2), (641, 479, 3)]:
+        img = synth_frame(w, h, s)
+        gk, gd = ex(img)
+        rk, rd = ref.extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd), (w, h)
+    # empty image: silent, zero keypoints (ref :987-988)
+    k, d = ex(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0
+    # an image whose top level is too small for the 30-px grid: explicit error, as the oracle
+    small = synth_frame(160, 120, 4)
+    rc, _, _ = ref.extract(small, check=False)
+    assert rc == -3
+    with pytest.raises(_lib.OrbGpuError) as ei:
+        ex(small)
+    assert ei.value.code == -3
+    # too large for the handle
+    with pytest.raises(_lib.OrbGpuError):
+        ex(synth_frame(1024, 600, 5))
+    # capacity too small is reported, never truncated silently
+    with pytest.raises(_lib.OrbGpuError) as ei:
+        ex(synth_frame(640, 480, 6), capacity=100)
+    assert ei.value.code == -4
+    ex.close()
+
+
+def test_flat_and_noise_images(oracle, gpu_lib):
+    """Edge cases: no corners at all; dense noise (many FAST hits, threshold-7 retries)."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    ref = oracle.RefExtractor(1000)
+    flat = np.full((480, 640), 77, np.uint8)
+    k, d = ex(flat)
+    assert len(k) == 0 and d.shape == (0, 32)
+    rng = np.random.default_rng(5)
+    noise = rng.integers(0, 256, (480, 640), dtype=np.uint8)
+    gk, gd = ex(noise)
+    rk, rd = ref.extract(noise)
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    soft = (128 + 20 * rng.standard_normal((480, 640))).clip(0, 255).astype(np.uint8)
+    gk, gd = ex(soft)
+    rk, rd = ref.extract(soft)
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    ex.close()
