@@ -10,6 +10,7 @@
 // 60 B per keypoint out.  Integer arithmetic reproduces OpenCV's fixed point exactly; the few fp32
 // steps use explicit round-to-nearest intrinsics so nothing is contracted into an FMA.
 #include "orb_common.cuh"
+#include "orb_internal.cuh"
 #include "orb_pattern.h"
 
 #include <algorithm>
@@ -28,53 +29,6 @@ void set_error(const char *fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
-
-constexpr int EDGE = ORB_EDGE_THRESHOLD;   // 19
-constexpr int XOFF = 32;                   // interior column 0 sits at byte 32 of a plane row
-constexpr int MAX_INI = 64;                // max initial quadtree nodes (image aspect ratio)
-constexpr int FAST_TILE_MAX = 72;          // cell (<60) + 6 halo, rounded up
-constexpr int FAST_THREADS = 256;
-constexpr int OCT_THREADS = 512;
-constexpr int DESC_WARPS = 8;
-
-enum { ERRF_CAND_OVERFLOW = 1, ERRF_NODE_OVERFLOW = 2, ERRF_OUT_OVERFLOW = 4 };
-
-struct ResizeTap {   // one destination column/row of cv::resize INTER_LINEAR
-    int16_t s0, s1, a0, a1;
-};
-
-struct LevelGeom {
-    int w, h, pitch;             // interior size, bytes per padded row
-    long long plane_off;         // byte offset of the padded plane inside a frame's pyramid block
-    long long interior_off;      // byte offset of interior pixel (0,0)
-    int tap_x_off, tap_y_off;    // offsets into the ResizeTap pool (level >= 1)
-    // FAST cell grid (ref :742-773)
-    int maxBX, maxBY, wCell, hCell, ncx, ncy, cell_begin;
-    // quadtree (ref :530-549)
-    int quota, nIni;
-    float hX;
-    int ini_x[MAX_INI + 1];
-    int win_w, win_h;            // maxBorder - minBorder
-    int cand_off, cand_cap;      // into the per-frame candidate pool (elements)
-    int kept_off, kept_cap;      // into the per-frame kept pool
-    float scale;                 // mvScaleFactor[level]
-    float size;                  // (float)(int)(31*scale)
-};
-
-struct Geom {
-    int nlevels, width, height;
-    int total_cells;
-    int cand_frame, kept_frame;          // pool elements per frame
-    long long pyr_frame;                 // pyramid bytes per frame
-    int max_nodes;                       // smem sizing for k_octree
-    int ini_th, min_th, blur_taps;
-    LevelGeom lv[ORB_MAX_LEVELS];
-};
-
-struct Kept {   // a keypoint retained by the quadtree, level coordinates
-    int16_t x, y;
-    int32_t response;
-};
 
 __constant__ int8_t c_pattern[ORB_PATTERN_INTS];
 __constant__ int c_umax[16];
@@ -809,30 +763,20 @@ using namespace orbgpu;
 // ------------------------------------------------------------------------------------------
 // Host side
 // ------------------------------------------------------------------------------------------
-struct orb_extractor {
-    orb_params prm;
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
-    std::vector<int> per_level;
-    int umax[16];
-    Geom geom;                 // host copy
-    Geom *d_geom = nullptr;
-    ResizeTap *d_taps = nullptr;
-    size_t taps_cap = 0;
-    uint8_t *d_src = nullptr;  size_t src_bytes = 0;
-    uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
-    uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
-    uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
-    Kept *d_kept = nullptr; size_t kept_elems = 0;
-    orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
-    size_t out_cap_elems = 0;
-    int *d_err = nullptr;
-    int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
-    int last_batch = 0;
-    int64_t launches = 0;
-    size_t oct_smem = 0;
-};
+static void prof_mark(orb_extractor *ex, int i) {
+    if (ex->profiling) cudaEventRecord(ex->ev[i], ex->stream);
+}
+static void prof_collect(orb_extractor *ex) {
+    if (!ex->profiling || !ex->ev_pending) return;
+    cudaEventSynchronize(ex->ev[ORB_N_STAGES]);
+    for (int i = 0; i < ORB_N_STAGES; i++) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ex->ev[i], ex->ev[i + 1]);
+        ex->stage_ms[i] += ms;
+    }
+    ex->stage_calls++;
+    ex->ev_pending = false;
+}
 
 static int cv_round_host(double v) { return (int)std::nearbyint(v); }
 
@@ -918,6 +862,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
         kept += g.kept_cap;
         maxn = std::max(maxn, g.kept_cap);
         g.scale = ex->scale[l];
+        g.inv_scale = ex->inv_scale[l];
         g.size = (float)(int)(31 * ex->scale[l]);                                     // ref :804
         if (l > 0) {
             const LevelGeom &s = G->lv[l - 1];
@@ -957,8 +902,9 @@ static size_t octree_smem_bytes(int maxn) {
 static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_cand);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
-    cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err);
+    cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
+    for (auto &e : ex->ev) if (e) cudaEventDestroy(e);
     if (ex->stream) cudaStreamDestroy(ex->stream);
 }
 
@@ -1132,6 +1078,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     const Geom &G = ex->geom;
     cudaStream_t st = ex->stream;
 
+    prof_collect(ex);
+    prof_mark(ex, 0);
     const uint8_t *d_images = images;
     size_t d_stride = frame_stride;
     int d_pitch = pitch;
@@ -1168,6 +1116,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
     ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
 
+    prof_mark(ex, 1);
     {
         const LevelGeom &g = G.lv[0];
         dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
@@ -1180,14 +1129,18 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         k_pyr_resize<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
         ex->launches++;
     }
+    prof_mark(ex, 2);
     k_fast_cells<<<dim3(G.total_cells, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_cand, d_cand_count, ex->d_err);
     ex->launches++;
+    prof_mark(ex, 3);
     k_octree<<<dim3(G.nlevels, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), st>>>(
         ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err);
     ex->launches++;
+    prof_mark(ex, 4);
     k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
         ex->d_pyr, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
     ex->launches++;
+    prof_mark(ex, 5);
     ORB_CUDA_TRY(cudaGetLastError());
     ex->last_batch = batch;
 
@@ -1196,6 +1149,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaMemcpyAsync(keypoints, o_kp, (size_t)batch * capacity * sizeof(orb_keypoint), cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaMemcpyAsync(descriptors, o_desc, (size_t)batch * capacity * 32, cudaMemcpyDeviceToHost, st));
+        prof_mark(ex, 6);
+        ex->ev_pending = ex->profiling;
         ORB_CUDA_TRY(cudaStreamSynchronize(st));
         for (int b = 0; b < batch; b++) n_out[b] = ex->h_pinned[1 + b];
         const int flags = ex->h_pinned[0];
@@ -1204,6 +1159,29 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             return check_err_flags(flags);
         }
     }
+    prof_mark(ex, 6);
+    ex->ev_pending = ex->profiling;
+    return ORB_OK;
+}
+
+int orb_extractor_set_profiling(orb_extractor *ex, int on) {
+    ORB_REQUIRE(ex, ORB_ERR_INVALID, "null handle");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    if (on && !ex->ev[0])
+        for (auto &e : ex->ev) ORB_CUDA_TRY(cudaEventCreate(&e));
+    ex->profiling = on != 0;
+    ex->ev_pending = false;
+    for (auto &m : ex->stage_ms) m = 0;
+    ex->stage_calls = 0;
+    return ORB_OK;
+}
+
+int orb_extractor_stage_times(orb_extractor *ex, double *ms, int64_t *calls) {
+    ORB_REQUIRE(ex && ms, ORB_ERR_INVALID, "null argument");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    prof_collect(ex);
+    for (int i = 0; i < ORB_N_STAGES; i++) ms[i] = ex->stage_ms[i];
+    if (calls) *calls = ex->stage_calls;
     return ORB_OK;
 }
 

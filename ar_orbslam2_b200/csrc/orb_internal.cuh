@@ -1,0 +1,91 @@
+// liborbgpu internals shared by the .cu translation units: level geometry, the extractor handle.
+#pragma once
+#include "orb_common.cuh"
+
+#include <vector>
+
+namespace orbgpu {
+
+constexpr int EDGE = ORB_EDGE_THRESHOLD;   // 19
+constexpr int XOFF = 32;                   // interior column 0 sits at byte 32 of a plane row
+constexpr int MAX_INI = 64;                // max initial quadtree nodes (image aspect ratio)
+constexpr int FAST_TILE_MAX = 72;          // cell (<60) + 6 halo, rounded up
+constexpr int FAST_THREADS = 256;
+constexpr int OCT_THREADS = 512;
+constexpr int DESC_WARPS = 8;
+
+enum { ERRF_CAND_OVERFLOW = 1, ERRF_NODE_OVERFLOW = 2, ERRF_OUT_OVERFLOW = 4 };
+
+struct ResizeTap {   // one destination column/row of cv::resize INTER_LINEAR
+    int16_t s0, s1, a0, a1;
+};
+
+struct LevelGeom {
+    int w, h, pitch;             // interior size, bytes per padded row
+    long long plane_off;         // byte offset of the padded plane inside a frame's pyramid block
+    long long interior_off;      // byte offset of interior pixel (0,0)
+    int tap_x_off, tap_y_off;    // offsets into the ResizeTap pool (level >= 1)
+    // FAST cell grid (ref :742-773)
+    int maxBX, maxBY, wCell, hCell, ncx, ncy, cell_begin;
+    // quadtree (ref :530-549)
+    int quota, nIni;
+    float hX;
+    int ini_x[MAX_INI + 1];
+    int win_w, win_h;            // maxBorder - minBorder
+    int cand_off, cand_cap;      // into the per-frame candidate pool (elements)
+    int kept_off, kept_cap;      // into the per-frame kept pool
+    float scale;                 // mvScaleFactor[level]
+    float inv_scale;             // mvInvScaleFactor[level]
+    float size;                  // (float)(int)(31*scale)
+};
+
+struct Geom {
+    int nlevels, width, height;
+    int total_cells;
+    int cand_frame, kept_frame;          // pool elements per frame
+    long long pyr_frame;                 // pyramid bytes per frame
+    int max_nodes;                       // smem sizing for k_octree
+    int ini_th, min_th, blur_taps;
+    LevelGeom lv[ORB_MAX_LEVELS];
+};
+
+struct Kept {   // a keypoint retained by the quadtree, level coordinates
+    int16_t x, y;
+    int32_t response;
+};
+
+}  // namespace orbgpu
+
+struct orb_extractor {
+    orb_params prm;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> per_level;
+    int umax[16];
+    orbgpu::Geom geom;                 // host copy
+    orbgpu::Geom *d_geom = nullptr;
+    orbgpu::ResizeTap *d_taps = nullptr;
+    size_t taps_cap = 0;
+    uint8_t *d_src = nullptr;  size_t src_bytes = 0;
+    uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
+    uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
+    uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
+    orbgpu::Kept *d_kept = nullptr; size_t kept_elems = 0;
+    orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
+    size_t out_cap_elems = 0;
+    int *d_err = nullptr;
+    int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
+    int last_batch = 0;
+    int64_t launches = 0;
+    size_t oct_smem = 0;
+    void *stereo_scratch = nullptr;    // device scratch of orb_stereo_match_batch
+    size_t stereo_scratch_bytes = 0;
+    // optional per-stage timing (CUDA events on the handle's stream)
+    bool profiling = false;
+    cudaEvent_t ev[ORB_N_STAGES + 1] = {};
+    double stage_ms[ORB_N_STAGES] = {};
+    int64_t stage_calls = 0;
+    bool ev_pending = false;
+};
+

@@ -1,0 +1,311 @@
+// liborbgpu -- stereo association for sm_100a.
+//
+// Replaces Frame::ComputeStereoMatches (ref: ORB_SLAM2/src/Frame.cc:471-643).  One warp per left
+// keypoint: row-band Hamming search over the right keypoints (lexicographic (distance, index)
+// warp minimum == the reference's first-best scan), then the 11x11 SAD slide over +-5 px on the
+// keypoint's pyramid level of both extractors, the parabola refinement and the depth.  A second
+// one-CTA kernel per pair applies the median-SAD rejection (ref :629-642).
+#include "orb_common.cuh"
+#include "orb_internal.cuh"
+
+#include <cstring>
+#include <vector>
+
+namespace orbgpu {
+
+constexpr int ST_WARPS = 8;
+constexpr int TH_HIGH = 100;   // ref ORBmatcher.cc:37
+
+struct StereoArgs {
+    const uint8_t *pyrL, *pyrR;
+    const Geom *GL, *GR;
+    int slotL0, slotR0;
+    const orb_keypoint *keysL, *keysR;
+    const uint8_t *descL, *descR;
+    const int32_t *nL, *nR;
+    int capacity;
+    float mbf, mb;
+    float *uRight, *depth;
+    int32_t *sad;          // [batch][capacity] best SAD or -1
+    int32_t *n_matched;    // [batch]
+};
+
+__global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
+    __shared__ float s_IL[ST_WARPS][121];
+    __shared__ uint8_t s_IR[ST_WARPS][11 * 24];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.y;
+    const int iL = blockIdx.x * ST_WARPS + warp;
+    const int N = min(A.nL[b], A.capacity), Nr = min(A.nR[b], A.capacity);
+    if (iL >= A.capacity) return;
+    const size_t o = (size_t)b * A.capacity + iL;
+    if (lane == 0) { A.uRight[o] = -1.0f; A.depth[o] = -1.0f; A.sad[o] = -1; }
+    if (iL >= N) return;
+
+    const orb_keypoint kpL = A.keysL[o];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const float minZ = A.mb, minD = -3.f;
+    const float maxD = __fdiv_rn(A.mbf, minZ);                 // ref :499-501
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (maxU < 0) return;                                      // ref :522-523
+    const int row = (int)vL;                                   // vRowIndices[vL]
+
+    uint32_t dl[8];
+    {
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(A.descL + o * 32);
+#pragma unroll
+        for (int i = 0; i < 8; i++) dl[i] = __ldg(p + i);
+    }
+    // ---- Hamming search in the row band (ref :479-496, 525-552)
+    uint32_t best = 0xffffffffu;   // (dist << 16) | iR
+    const orb_keypoint *KR = A.keysR + (size_t)b * A.capacity;
+    const uint8_t *DR = A.descR + (size_t)b * A.capacity * 32;
+    for (int iR = lane; iR < Nr; iR += 32) {
+        const orb_keypoint kr = KR[iR];
+        const float r = __fmul_rn(2.0f, A.GL->lv[kr.octave].scale);
+        const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
+        if (row < minr || row > maxr) continue;
+        if (kr.octave < levelL - 1 || kr.octave > levelL + 1) continue;
+        if (!(kr.x >= minU && kr.x <= maxU)) continue;
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(DR + (size_t)iR * 32);
+        int d = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) d += __popc(dl[i] ^ __ldg(p + i));
+        best = min(best, ((uint32_t)d << 16) | (uint32_t)iR);
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
+    const int bestDist = best == 0xffffffffu ? TH_HIGH : (int)(best >> 16);
+    if (bestDist >= TH_HIGH) return;
+    const int bestIdxR = best & 0xffff;
+
+    // ---- SAD slide on the pyramid level of the left keypoint (ref :557-595)
+    const float uR0 = KR[bestIdxR].x;
+    const LevelGeom &gl = A.GL->lv[levelL];
+    const LevelGeom &gr = A.GR->lv[levelL];
+    const float sf = gl.inv_scale;
+    const float scaleduL = roundf(__fmul_rn(kpL.x, sf));
+    const float scaledvL = roundf(__fmul_rn(kpL.y, sf));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+    const int w = 5, L = 5;
+    const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+    if (iniu < 0 || endu >= (float)gr.w) return;               // ref :576-579
+
+    const uint8_t *imgL = A.pyrL + (size_t)(A.slotL0 + b) * A.GL->pyr_frame + gl.interior_off;
+    const uint8_t *imgR = A.pyrR + (size_t)(A.slotR0 + b) * A.GR->pyr_frame + gr.interior_off;
+    const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w), xr0 = (int)(scaleduR0 - L - w);
+    float *IL = s_IL[warp];
+    uint8_t *IR = s_IR[warp];
+    for (int i = lane; i < 121; i += 32) {
+        const int y = i / 11, x = i - y * 11;
+        IL[i] = (float)imgL[(ptrdiff_t)(y0 + y) * gl.pitch + xl0 + x];
+    }
+    for (int i = lane; i < 11 * 21; i += 32) {
+        const int y = i / 21, x = i - y * 21;
+        IR[y * 24 + x] = imgR[(ptrdiff_t)(y0 + y) * gr.pitch + xr0 + x];
+    }
+    __syncwarp();
+    const float cL = IL[5 * 11 + 5];
+    float dists[11];
+#pragma unroll
+    for (int k = 0; k < 11; k++) {   // incR = k - 5
+        const float cR = (float)IR[5 * 24 + k + 5];
+        float s = 0.f;
+        for (int i = lane; i < 121; i += 32) {
+            const int y = i / 11, x = i - y * 11;
+            s += fabsf((IL[i] - cL) - ((float)IR[y * 24 + x + k] - cR));   // exact small integers
+        }
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sft);
+        dists[k] = s;
+    }
+    int bestS = 0x7fffffff, bestinc = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++)
+        if (dists[k] < (float)bestS) { bestS = (int)dists[k]; bestinc = k - 5; }
+    if (bestinc == -L || bestinc == L) return;                 // ref :597-598
+    float d1 = 0, d2 = 0, d3 = 0;
+#pragma unroll
+    for (int k = 1; k < 10; k++)
+        if (k == bestinc + 5) { d1 = dists[k - 1]; d2 = dists[k]; d3 = dists[k + 1]; }
+    // ref :605: (dist1-dist3)/(2.0f*(dist1+dist3-2.0f*dist2)); NaN (0/0) passes the +-1 test below
+    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+    if (deltaR < -1 || deltaR > 1) return;
+    float bestuR = __fmul_rn(gl.scale, __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));   // ref :611
+    float disparity = __fsub_rn(uL, bestuR);
+    if (disparity >= 0 && disparity < maxD) {
+        if (disparity <= 0) {
+            disparity = 0.01f;
+            bestuR = __double2float_rn(__dsub_rn((double)uL, 0.01));   // ref :620: float - double literal
+        }
+        if (lane == 0) {
+            A.depth[o] = __fdiv_rn(A.mbf, disparity);
+            A.uRight[o] = bestuR;
+            A.sad[o] = bestS;
+        }
+    }
+}
+
+// Median-SAD rejection (ref :629-642): thDist = 1.5f*1.4f*median, where median is element size/2 of
+// the ascending (SAD, iL) list.
+__global__ void __launch_bounds__(1024) k_stereo_filter(StereoArgs A, int sort_n) {
+    extern __shared__ int s_keys[];
+    __shared__ int s_count;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int N = min(A.nL[b], A.capacity);
+    if (tid == 0) s_count = 0;
+    for (int i = tid; i < sort_n; i += 1024) s_keys[i] = 0x7fffffff;
+    __syncthreads();
+    const int32_t *sad = A.sad + (size_t)b * A.capacity;
+    for (int i = tid; i < N; i += 1024)
+        if (sad[i] >= 0) s_keys[atomicAdd(&s_count, 1)] = sad[i];
+    __syncthreads();
+    const int count = s_count;
+    if (count == 0) {
+        if (tid == 0) A.n_matched[b] = 0;
+        return;
+    }
+    for (int k = 2; k <= sort_n; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < sort_n; i += 1024) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const int a = s_keys[i], c = s_keys[ixj];
+                    const bool asc = (i & k) == 0;
+                    if (asc ? (a > c) : (a < c)) { s_keys[i] = c; s_keys[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    const float median = (float)s_keys[count / 2];
+    const float thDist = __fmul_rn(1.5f * 1.4f, median);
+    __syncthreads();
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    int kept = 0;
+    for (int i = tid; i < N; i += 1024) {
+        if (sad[i] >= 0) {
+            if ((float)sad[i] < thDist) kept++;
+            else { A.uRight[(size_t)b * A.capacity + i] = -1.f; A.depth[(size_t)b * A.capacity + i] = -1.f; }
+        }
+    }
+    if (kept) atomicAdd(&s_count, kept);
+    __syncthreads();
+    if (tid == 0) A.n_matched[b] = s_count;
+}
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+extern "C" {
+
+int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *right, int right_slot, int batch,
+                           const orb_keypoint *keys_left, const uint8_t *desc_left, const int32_t *n_left,
+                           const orb_keypoint *keys_right, const uint8_t *desc_right, const int32_t *n_right, int capacity,
+                           float mbf, float mb, float *u_right, float *depth, int32_t *n_matched, int loc) {
+    ORB_REQUIRE(left && right && keys_left && desc_left && n_left && keys_right && desc_right && n_right && u_right && depth,
+                ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(batch >= 1 && capacity >= 1 && capacity <= 65535, ORB_ERR_INVALID, "bad batch/capacity");
+    ORB_REQUIRE(left->device == right->device, ORB_ERR_INVALID, "left and right extractors must live on one device");
+    ORB_REQUIRE(left->geom.width > 0 && right->geom.width > 0, ORB_ERR_INVALID, "extract the pair before matching");
+    ORB_REQUIRE(left->geom.nlevels == right->geom.nlevels && left->geom.width == right->geom.width &&
+                    left->geom.height == right->geom.height, ORB_ERR_INVALID, "left/right pyramids differ in geometry");
+    ORB_REQUIRE(left_slot >= 0 && left_slot + batch <= left->prm.max_batch && right_slot >= 0 &&
+                    right_slot + batch <= right->prm.max_batch, ORB_ERR_INVALID, "slot range exceeds max_batch");
+    ORB_CUDA_TRY(cudaSetDevice(left->device));
+    cudaStream_t st = left->stream;
+    if (right != left) {   // the right pyramid is produced on the other handle's stream
+        cudaEvent_t ev;
+        ORB_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        ORB_CUDA_TRY(cudaEventRecord(ev, right->stream));
+        ORB_CUDA_TRY(cudaStreamWaitEvent(st, ev, 0));
+        ORB_CUDA_TRY(cudaEventDestroy(ev));
+    }
+    const size_t per = (size_t)batch * capacity;
+    // scratch layout: sad[per] | n_matched[batch] | (host mode) keysL,keysR,descL,descR,nL,nR,uRight,depth
+    size_t need = per * 4 + batch * 4 + 16 * 256;   // every carve() is rounded up to 256 B
+    if (loc == ORB_HOST) need += 2 * per * sizeof(orb_keypoint) + 2 * per * 32 + 2 * batch * 4 + 2 * per * 4 + 1024;
+    if (left->stereo_scratch_bytes < need) {
+        if (left->stereo_scratch) cudaFree(left->stereo_scratch);
+        left->stereo_scratch = nullptr;
+        left->stereo_scratch_bytes = 0;
+        ORB_CUDA_TRY(cudaMalloc(&left->stereo_scratch, need));
+        left->stereo_scratch_bytes = need;
+    }
+    uint8_t *p = (uint8_t *)left->stereo_scratch;
+    auto carve = [&](size_t bytes) { uint8_t *r = p; p += (bytes + 255) / 256 * 256; return r; };
+    StereoArgs A;
+    A.sad = (int32_t *)carve(per * 4);
+    A.n_matched = (int32_t *)carve(batch * 4);
+    A.pyrL = left->d_pyr; A.pyrR = right->d_pyr;
+    A.GL = left->d_geom; A.GR = right->d_geom;
+    A.slotL0 = left_slot; A.slotR0 = right_slot;
+    A.capacity = capacity; A.mbf = mbf; A.mb = mb;
+    if (loc == ORB_HOST) {
+        orb_keypoint *dkl = (orb_keypoint *)carve(per * sizeof(orb_keypoint));
+        orb_keypoint *dkr = (orb_keypoint *)carve(per * sizeof(orb_keypoint));
+        uint8_t *ddl = carve(per * 32), *ddr = carve(per * 32);
+        int32_t *dnl = (int32_t *)carve(batch * 4), *dnr = (int32_t *)carve(batch * 4);
+        float *dur = (float *)carve(per * 4), *ddp = (float *)carve(per * 4);
+        ORB_CUDA_TRY(cudaMemcpyAsync(dkl, keys_left, per * sizeof(orb_keypoint), cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(dkr, keys_right, per * sizeof(orb_keypoint), cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ddl, desc_left, per * 32, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ddr, desc_right, per * 32, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(dnl, n_left, batch * 4, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(dnr, n_right, batch * 4, cudaMemcpyHostToDevice, st));
+        A.keysL = dkl; A.keysR = dkr; A.descL = ddl; A.descR = ddr; A.nL = dnl; A.nR = dnr; A.uRight = dur; A.depth = ddp;
+    } else {
+        A.keysL = keys_left; A.keysR = keys_right; A.descL = desc_left; A.descR = desc_right;
+        A.nL = n_left; A.nR = n_right; A.uRight = u_right; A.depth = depth;
+    }
+    k_stereo_match<<<dim3((capacity + ST_WARPS - 1) / ST_WARPS, batch), ST_WARPS * 32, 0, st>>>(A);
+    int sort_n = 1;
+    while (sort_n < capacity) sort_n <<= 1;
+    if (sort_n * 4 > 48 * 1024)
+        ORB_CUDA_TRY(cudaFuncSetAttribute(k_stereo_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_n * 4));
+    k_stereo_filter<<<batch, 1024, sort_n * 4, st>>>(A, sort_n);
+    left->launches += 2;
+    ORB_CUDA_TRY(cudaGetLastError());
+    if (loc == ORB_HOST) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(u_right, A.uRight, per * 4, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(depth, A.depth, per * 4, cudaMemcpyDeviceToHost, st));
+        if (n_matched) ORB_CUDA_TRY(cudaMemcpyAsync(n_matched, A.n_matched, batch * 4, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    } else if (n_matched) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(n_matched, A.n_matched, batch * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return ORB_OK;
+}
+
+int orb_stereo_match(orb_extractor *left, orb_extractor *right, int slot, const orb_keypoint *keys_left,
+                     const uint8_t *desc_left, int n_left, const orb_keypoint *keys_right, const uint8_t *desc_right,
+                     int n_right, float mbf, float mb, float *u_right, float *depth, int *n_matched) {
+    ORB_REQUIRE(n_left >= 0 && n_right >= 0, ORB_ERR_INVALID, "negative count");
+    if (n_matched) *n_matched = 0;
+    if (n_left == 0) { set_error("no left keypoints"); return ORB_ERR_EMPTY; }
+    // single pair: the arrays are exactly n long, so use separate strides via two capacities = max(n)
+    const int cap = n_left > n_right ? n_left : n_right;
+    ORB_REQUIRE(cap <= 65535, ORB_ERR_INVALID, "too many keypoints");
+    std::vector<orb_keypoint> kl(cap), kr(cap);
+    std::vector<uint8_t> dl((size_t)cap * 32), dr((size_t)cap * 32);
+    std::vector<float> ur(cap), dp(cap);
+    memcpy(kl.data(), keys_left, (size_t)n_left * sizeof(orb_keypoint));
+    memcpy(dl.data(), desc_left, (size_t)n_left * 32);
+    if (n_right) {
+        memcpy(kr.data(), keys_right, (size_t)n_right * sizeof(orb_keypoint));
+        memcpy(dr.data(), desc_right, (size_t)n_right * 32);
+    }
+    int32_t nl = n_left, nr = n_right, nm = 0;
+    int rc = orb_stereo_match_batch(left, slot, right, slot, 1, kl.data(), dl.data(), &nl, kr.data(), dr.data(), &nr, cap, mbf, mb,
+                                    ur.data(), dp.data(), &nm, ORB_HOST);
+    if (rc != ORB_OK) return rc;
+    memcpy(u_right, ur.data(), (size_t)n_left * 4);
+    memcpy(depth, dp.data(), (size_t)n_left * 4);
+    if (n_matched) *n_matched = nm;
+    if (nm == 0) { set_error("no stereo match accepted (the reference indexes an empty vector here, Frame.cc:630)"); return ORB_ERR_EMPTY; }
+    return ORB_OK;
+}
+
+}  // extern "C"

@@ -108,6 +108,14 @@ int orb_extractor_sync(orb_extractor *ex);
 /* Device-output batches are asynchronous: overflow conditions they hit are latched on the device.
  * Synchronises, returns ORB_ERR_CAPACITY if any was raised since the last check, and clears it. */
 int orb_extractor_check(orb_extractor *ex);
+/* Per-stage device time, measured with CUDA events on the handle's stream between the stage
+ * launches of orb_extract_batch.  Stages: 0 host->device copy of the frames, 1 pyramid,
+ * 2 FAST cells, 3 quadtree, 4 orientation+blur+descriptor, 5 device->host copy.
+ * set_profiling(1) resets the accumulators; stage_times returns accumulated milliseconds over
+ * `calls` batches.                                                                          */
+#define ORB_N_STAGES 6
+int orb_extractor_set_profiling(orb_extractor *ex, int on);
+int orb_extractor_stage_times(orb_extractor *ex, double *ms, int64_t *calls);
 /* cudaStream_t of the handle as an opaque pointer (for event timing on the launching stream). */
 void *orb_extractor_stream(orb_extractor *ex);
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
@@ -251,6 +259,17 @@ int orb_stereo_match(orb_extractor *left, orb_extractor *right, int slot,
                      const orb_keypoint *keys_left, const uint8_t *desc_left, int n_left,
                      const orb_keypoint *keys_right, const uint8_t *desc_right, int n_right,
                      float mbf, float mb, float *u_right, float *depth, int *n_matched);
+
+/* Batched / device-resident form: pair b uses pyramid slot left_slot+b of `left` and
+ * right_slot+b of `right` (the two may be the same handle holding 2*batch frames), keypoints at
+ * keys_*[b*capacity], counts n_*[b].  loc = where all caller arrays live; with ORB_DEVICE the
+ * call is asynchronous on left's stream.  n_matched[b] = matches surviving the median test.   */
+int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *right, int right_slot,
+                           int batch, const orb_keypoint *keys_left, const uint8_t *desc_left,
+                           const int32_t *n_left, const orb_keypoint *keys_right,
+                           const uint8_t *desc_right, const int32_t *n_right, int capacity,
+                           float mbf, float mb, float *u_right, float *depth, int32_t *n_matched,
+                           int loc);
 
 /* ---- sharded descriptor database (relocalisation brute force) --------------- */
 

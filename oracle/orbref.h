@@ -19,6 +19,11 @@ int orbref_level_size(const orbref_extractor *ex, int level, int *w, int *h);
 int orbref_pyramid_download(orbref_extractor *ex, int level, int with_border, uint8_t *dst, int dst_pitch);
 int orbref_debug_candidates(orbref_extractor *ex, int level, orb_candidate *out, int capacity, int *n_out);
 int orbref_debug_blur_level(orbref_extractor *ex, int level, uint8_t *dst, int dst_pitch);
+/* Frame::ComputeStereoMatches; sad_out (optional) = best SAD per left keypoint or -1 */
+int orbref_stereo_match(orbref_extractor *left, orbref_extractor *right, const orb_keypoint *keysL,
+                        const uint8_t *descL, int N, const orb_keypoint *keysR, const uint8_t *descR, int Nr,
+                        float mbf, float mb, float *uRight, float *depth, int32_t *sad_out, int *n_matched);
+int orbref_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

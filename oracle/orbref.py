@@ -144,3 +144,26 @@ def make_border(interior: np.ndarray, border=19) -> np.ndarray:
     plane[border:border + h, border:border + w] = interior
     lib().orbref_make_border(ptr(plane), w, h, plane.strides[0], border)
     return plane
+
+
+def stereo_match(left: RefExtractor, right: RefExtractor, keys_l, desc_l, keys_r, desc_r, mbf, mb):
+    """Frame::ComputeStereoMatches on the pyramids held by the two oracle extractors.
+    Returns (rc, uRight, depth, sad, n_matched)."""
+    n_l, n_r = len(keys_l), len(keys_r)
+    kl, kr = np.ascontiguousarray(keys_l), np.ascontiguousarray(keys_r)
+    dl, dr = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    ur = np.zeros(n_l, np.float32)
+    dp = np.zeros(n_l, np.float32)
+    sad = np.zeros(n_l, np.int32)
+    nm = C.c_int()
+    rc = lib().orbref_stereo_match(left.h, right.h, ptr(kl), ptr(dl), n_l, ptr(kr), ptr(dr), n_r, C.c_float(mbf), C.c_float(mb),
+                                   ptr(ur), ptr(dp), ptr(sad), C.byref(nm))
+    return rc, ur, dp, sad, nm.value
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    out = np.zeros(a.shape[0], np.int32)
+    lib().orbref_descriptor_distance(ptr(a), ptr(b), a.shape[0], ptr(out))
+    return out

@@ -10,6 +10,7 @@
 //   * cosf/sinf are the glibc algorithm restated in orbref_cv.h (bit-identical to glibc 2.39).
 #include "orbref.h"
 #include "orbref_cv.h"
+#include "orbref_internal.h"
 #include "../ar_orbslam2_b200/csrc/orb_pattern.h"
 
 #include <algorithm>
@@ -22,47 +23,11 @@ namespace {
 
 const int PATCH_SIZE = 31;        // ref ORBextractor.cc:69
 const int HALF_PATCH_SIZE = 15;   // ref :70
-const int EDGE_THRESHOLD = 19;    // ref :71
 
 const int kPattern[ORB_PATTERN_INTS] = {ORB_PATTERN_VALUES};
 
-struct Cand {       // a cv::KeyPoint as produced by cv::FAST and shifted by ref :786-793
-    float x, y;     // window-relative
-    float response;
-    float angle;
-};
-
-struct Level {
-    int w = 0, h = 0, pitch = 0;          // interior size; pitch of the padded plane
-    std::vector<uint8_t> plane;           // (w+38) x (h+38)
-    std::vector<Cand> cands;              // vToDistributeKeys
-    std::vector<Cand> kept;               // after DistributeOctTree, + minBorder, + angle
-    std::vector<uint8_t> blurred;         // w x h, only if kept non-empty
-    uint8_t *interior() { return plane.data() + (size_t)EDGE_THRESHOLD * pitch + EDGE_THRESHOLD; }
-};
-
-struct Node {   // ref ExtractorNode, include/ORBextractor.h:30-43
-    std::vector<int> keys;        // indices into the candidate array, in vKeys order
-    int ULx, ULy, URx, URy, BLx, BLy, BRx, BRy;
-    std::list<Node>::iterator lit;
-    bool no_more = false;
-    long seq = 0;                 // creation sequence number (oracle tie key)
-};
-
 }  // namespace
 
-struct orbref_extractor {
-    orb_params prm;
-    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
-    std::vector<int> per_level;
-    std::vector<int> umax;
-    std::vector<Level> lv;
-    int trig_mode = 0;            // 0: restated glibc sincosf; 1: host libm cosf/sinf
-    long node_seq = 0;
-
-    void divide(const Node &n, const std::vector<Cand> &c, Node out[4]);
-    std::vector<Cand> distribute(const std::vector<Cand> &c, int minX, int maxX, int minY, int maxY, int N);
-};
 
 // ref ExtractorNode::DivideNode, ORBextractor.cc:470-523
 void orbref_extractor::divide(const Node &n, const std::vector<Cand> &c, Node out[4]) {
