@@ -11,13 +11,14 @@
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <emmintrin.h>
 #include <cstring>
 #include <vector>
 
 namespace orbref {
 
 // cvRound: round-half-to-even (SSE cvtsd2si).  ref call sites: ORBextractor.cc:76,106,110,111,433,451,1050.
-static inline int cv_round(double v) { return (int)std::nearbyint(v); }
+static inline int cv_round(double v) { return _mm_cvtsd_si32(_mm_set_sd(v)); }   // what OpenCV's cvRound compiles to on x86-64
 static inline int cv_floor(double v) { return (int)std::floor(v); }
 static inline int cv_ceil(double v) { return (int)std::ceil(v); }
 
@@ -109,20 +110,27 @@ static inline const int *gauss_taps(int variant) {
 static inline void gaussian_blur7_u8(const uint8_t *src, int w, int h, int spitch, uint8_t *dst,
                                      int dpitch, int taps_variant) {
     const int *k = gauss_taps(taps_variant);
-    std::vector<int> hbuf((size_t)w * h);
+    std::vector<uint16_t> hbuf((size_t)w * h);   // row sums fit 16 bits (256*255)
     for (int y = 0; y < h; y++) {
         const uint8_t *s = src + (size_t)y * spitch;
+        uint16_t *hb = &hbuf[(size_t)y * w];
         for (int x = 0; x < w; x++) {
             int acc = 0;
-            for (int i = 0; i < 7; i++) acc += k[i] * s[reflect101(x + i - 3, w)];
-            hbuf[(size_t)y * w + x] = acc;
+            if (x >= 3 && x < w - 3) {
+                for (int i = 0; i < 7; i++) acc += k[i] * s[x + i - 3];
+            } else {
+                for (int i = 0; i < 7; i++) acc += k[i] * s[reflect101(x + i - 3, w)];
+            }
+            hb[x] = (uint16_t)acc;
         }
     }
     for (int y = 0; y < h; y++) {
         uint8_t *d = dst + (size_t)y * dpitch;
+        const uint16_t *r[7];
+        for (int j = 0; j < 7; j++) r[j] = &hbuf[(size_t)reflect101(y + j - 3, h) * w];
         for (int x = 0; x < w; x++) {
             int acc = 0;
-            for (int j = 0; j < 7; j++) acc += k[j] * hbuf[(size_t)reflect101(y + j - 3, h) * w + x];
+            for (int j = 0; j < 7; j++) acc += k[j] * r[j][x];
             int v = (acc + 32768) >> 16;
             d[x] = (uint8_t)(v > 255 ? 255 : v);
         }
@@ -187,7 +195,14 @@ static inline void fast9_16_nms(const uint8_t *roi, int w, int h, int pitch, int
     std::vector<int> score((size_t)w * h, 0);
     for (int y = 3; y < h - 3; y++)
         for (int x = 3; x < w - 3; x++) {
-            int V = fast_arc_strength(roi + (size_t)y * pitch + x, pitch);
+            const uint8_t *p = roi + (size_t)y * pitch + x;
+            // exact early-out (every 9-arc of the 16-circle holds two adjacent compass points), the
+            // same high-speed test OpenCV's FAST applies before scoring
+            const int c = p[0], d0 = c - p[3 * pitch], d4 = c - p[3], d8 = c - p[-3 * pitch], d12 = c - p[-3];
+            const int hi = (d0 > threshold) + (d4 > threshold) + (d8 > threshold) + (d12 > threshold);
+            const int lo = (d0 < -threshold) + (d4 < -threshold) + (d8 < -threshold) + (d12 < -threshold);
+            if (hi < 2 && lo < 2) continue;
+            int V = fast_arc_strength(p, pitch);
             score[(size_t)y * w + x] = V > threshold ? V - 1 : 0;
         }
     for (int y = 3; y < h - 3; y++)
