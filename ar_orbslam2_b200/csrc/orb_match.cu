@@ -1,0 +1,423 @@
+// liborbgpu -- Hamming matching primitives for sm_100a.
+//
+//   orb_descriptor_distance   ORBmatcher::DescriptorDistance (ref: ORB_SLAM2/src/ORBmatcher.cc:1650-1666)
+//   orb_hamming_top2          brute-force best / second-best scan (the inner loop of ref
+//                             ORBmatcher.cc:205-226, 573-599 and Marker.cc:314-349) -- the C5 shard kernel
+//   orb_top2_merge            merge of per-shard top-2 lists == one scan of the concatenated database
+//   orb_db_*                  keyframe-range shard of a descriptor database resident in HBM
+//   orb_measure_popc_rate     measured POPC issue rate (roofline denominator for matching)
+//
+// One compare = 8 x (XOR + POPC) on 32-bit words.  Queries live in registers (one query per thread),
+// database rows stream through shared memory with cp.async and are read as broadcast 16-byte loads.
+// Tensor cores are deliberately unused: this is bit counting, not a float contraction.
+#include "orb_common.cuh"
+
+#include <algorithm>
+#include <vector>
+
+namespace orbgpu {
+
+constexpr int T2_THREADS = 256;     // queries per CTA
+constexpr int T2_TILE = 256;        // database rows per shared-memory stage (8 KB)
+constexpr int T2_STAGES = 3;
+
+struct Top2 {
+    int32_t d1, d2;
+    int64_t i1, i2;
+};
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// grid = (query blocks, database chunks).  Each CTA scans rows [chunk*rows_per_chunk, ...) in order for
+// its 256 queries and writes one partial top-2 per (chunk, query).
+__global__ void __launch_bounds__(T2_THREADS)
+k_hamming_top2(const uint8_t *__restrict__ queries, int nq, const uint8_t *__restrict__ db, long long ndb,
+               long long rows_per_chunk, int32_t *__restrict__ pd1, int32_t *__restrict__ pd2,
+               int64_t *__restrict__ pi1, int64_t *__restrict__ pi2, long long idx_base) {
+    __shared__ __align__(16) uint4 tile[T2_STAGES][T2_TILE * 2];
+    const int tid = threadIdx.x;
+    const int q = blockIdx.x * T2_THREADS + tid;
+    const long long r0 = (long long)blockIdx.y * rows_per_chunk;
+    const long long r1 = min(r0 + rows_per_chunk, ndb);
+    uint32_t qa[8];
+    {
+        const uint4 *qp = reinterpret_cast<const uint4 *>(queries + (size_t)min(q, nq - 1) * 32);
+        const uint4 a = __ldg(qp), b = __ldg(qp + 1);
+        qa[0] = a.x; qa[1] = a.y; qa[2] = a.z; qa[3] = a.w; qa[4] = b.x; qa[5] = b.y; qa[6] = b.z; qa[7] = b.w;
+    }
+    int d1 = 256, d2 = 256;
+    long long i1 = -1, i2 = -1;
+    const long long nrows = r1 - r0;
+    const int ntiles = nrows > 0 ? (int)((nrows + T2_TILE - 1) / T2_TILE) : 0;
+    const uint4 *src = reinterpret_cast<const uint4 *>(db) + r0 * 2;
+    const long long n16 = nrows * 2;   // 16-byte units in this chunk
+
+    auto issue = [&](int t) {
+        if (t < ntiles) {
+            uint4 *dst = tile[t % T2_STAGES];
+            const long long base = (long long)t * T2_TILE * 2;
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+                const long long u = base + tid + k * T2_THREADS;
+                if (u < n16) cp_async16(dst + tid + k * T2_THREADS, src + u);
+            }
+        }
+        cp_async_commit();
+    };
+    for (int t = 0; t < T2_STAGES - 1; t++) issue(t);
+    for (int t = 0; t < ntiles; t++) {
+        issue(t + T2_STAGES - 1);
+        cp_async_wait<T2_STAGES - 1>();
+        __syncthreads();
+        const uint4 *rows = tile[t % T2_STAGES];
+        const int nr = (int)min((long long)T2_TILE, nrows - (long long)t * T2_TILE);
+        const long long rbase = r0 + (long long)t * T2_TILE;
+#pragma unroll 4
+        for (int r = 0; r < nr; r++) {
+            const uint4 a = rows[2 * r], b = rows[2 * r + 1];   // broadcast: every lane reads the same row
+            const int d = __popc(qa[0] ^ a.x) + __popc(qa[1] ^ a.y) + __popc(qa[2] ^ a.z) + __popc(qa[3] ^ a.w) +
+                          __popc(qa[4] ^ b.x) + __popc(qa[5] ^ b.y) + __popc(qa[6] ^ b.z) + __popc(qa[7] ^ b.w);
+            if (d < d2) {   // strict '<': the first row seen wins ties, as the reference's sequential scan
+                if (d < d1) { d2 = d1; i2 = i1; d1 = d; i1 = rbase + r; }
+                else { d2 = d; i2 = rbase + r; }
+            }
+        }
+        __syncthreads();
+    }
+    if (q < nq) {
+        const size_t o = (size_t)blockIdx.y * nq + q;
+        pd1[o] = d1; pd2[o] = d2;
+        pi1[o] = i1 < 0 ? -1 : i1 + idx_base;
+        pi2[o] = i2 < 0 ? -1 : i2 + idx_base;
+    }
+}
+
+// Lexicographic merge of `nparts` partial top-2 lists per query, parts in database order.  Ties on the
+// distance keep the entry from the earlier part (= lower row index), so the result equals one scan.
+__global__ void k_top2_merge(int nparts, int nq, const int32_t *__restrict__ pd1, const int64_t *__restrict__ pi1,
+                             const int32_t *__restrict__ pd2, const int64_t *__restrict__ pi2, int32_t *__restrict__ od1,
+                             int64_t *__restrict__ oi1, int32_t *__restrict__ od2, int64_t *__restrict__ oi2) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    int d1 = 256, d2 = 256;
+    long long i1 = -1, i2 = -1;
+    for (int p = 0; p < nparts; p++) {
+        const size_t o = (size_t)p * nq + q;
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const int d = k ? pd2[o] : pd1[o];
+            const long long i = k ? pi2[o] : pi1[o];
+            if (i < 0) continue;
+            if (d < d2) {
+                if (d < d1) { d2 = d1; i2 = i1; d1 = d; i1 = i; }
+                else { d2 = d; i2 = i; }
+            }
+        }
+    }
+    od1[q] = d1; oi1[q] = i1; od2[q] = d2; oi2[q] = i2;
+}
+
+__global__ void k_descriptor_distance(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, int n,
+                                      int32_t *__restrict__ dist) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 *pa = reinterpret_cast<const uint4 *>(a + (size_t)i * 32), *pb = reinterpret_cast<const uint4 *>(b + (size_t)i * 32);
+    const uint4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+    dist[i] = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+              __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// splitmix64 of the global 64-bit word index: the device twin of ar_orbslam2_b200/synth.py:synth_descriptors
+__global__ void k_db_fill(unsigned long long *__restrict__ words, long long nwords, long long first_word,
+                          unsigned long long seed) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += stride) {
+        unsigned long long z = seed + (unsigned long long)(first_word + i + 1) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        words[i] = z ^ (z >> 31);
+    }
+}
+
+// POPC micro-benchmark: 8 independent popc chains per thread.
+__global__ void k_popc_rate(unsigned *out, int iters) {
+    unsigned x0 = threadIdx.x, x1 = x0 * 3 + 1, x2 = x0 * 5 + 2, x3 = x0 * 7 + 3, x4 = x0 * 11 + 4, x5 = x0 * 13 + 5,
+             x6 = x0 * 17 + 6, x7 = x0 * 19 + 7;
+    for (int i = 0; i < iters; i++) {
+        x0 = __popc(x0) + 0x10001u; x1 = __popc(x1) + 0x20003u; x2 = __popc(x2) + 0x40005u; x3 = __popc(x3) + 0x80007u;
+        x4 = __popc(x4) + 0x10009u; x5 = __popc(x5) + 0x2000bu; x6 = __popc(x6) + 0x4000du; x7 = __popc(x7) + 0x8000fu;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+}
+
+struct Top2Scratch {
+    void *buf = nullptr;
+    size_t bytes = 0;
+};
+
+// scans db[0..ndb) for nq queries on `st`; all pointers are device pointers
+static int top2_device(const uint8_t *d_q, int nq, const uint8_t *d_db, long long ndb, long long idx_base, int32_t *d_d1,
+                       int64_t *d_i1, int32_t *d_d2, int64_t *d_i2, cudaStream_t st, Top2Scratch *scratch) {
+    int dev = 0, sms = 148;
+    ORB_CUDA_TRY(cudaGetDevice(&dev));
+    ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int qblocks = (nq + T2_THREADS - 1) / T2_THREADS;
+    // enough chunks to fill the machine several times over, but never less than one tile per chunk
+    long long chunks = std::max<long long>(1, (long long)sms * 8 / qblocks);
+    chunks = std::min<long long>(chunks, std::max<long long>(1, (ndb + T2_TILE - 1) / T2_TILE));
+    chunks = std::min<long long>(chunks, 65535);
+    const long long rows_per_chunk = (std::max<long long>(ndb, 1) + chunks - 1) / chunks;
+    chunks = std::max<long long>(1, (ndb + rows_per_chunk - 1) / rows_per_chunk);
+    const size_t per = (size_t)chunks * nq;
+    const size_t need = per * (4 + 4 + 8 + 8) + 1024;
+    if (scratch->bytes < need) {
+        if (scratch->buf) cudaFree(scratch->buf);
+        scratch->buf = nullptr; scratch->bytes = 0;
+        ORB_CUDA_TRY(cudaMalloc(&scratch->buf, need));
+        scratch->bytes = need;
+    }
+    int64_t *pi1 = (int64_t *)scratch->buf, *pi2 = pi1 + per;
+    int32_t *pd1 = (int32_t *)(pi2 + per), *pd2 = pd1 + per;
+    k_hamming_top2<<<dim3(qblocks, (unsigned)chunks), T2_THREADS, 0, st>>>(d_q, nq, d_db, ndb, rows_per_chunk, pd1, pd2, pi1, pi2,
+                                                                          idx_base);
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>((int)chunks, nq, pd1, pi1, pd2, pi2, d_d1, d_i1, d_d2, d_i2);
+    ORB_CUDA_TRY(cudaGetLastError());
+    return ORB_OK;
+}
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+struct orb_db {
+    int device = 0;
+    long long row_begin = 0, row_end = 0;
+    uint8_t *d_rows = nullptr;
+    cudaStream_t stream = nullptr;
+    Top2Scratch scratch;
+    void *d_io = nullptr;      // staging for host-mode queries/results
+    size_t io_bytes = 0;
+    int64_t launches = 0;
+};
+
+namespace {
+struct DevBuf {   // RAII device allocation for the one-shot host-mode entry points
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 1); }
+};
+}  // namespace
+
+extern "C" {
+
+int orb_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, int loc) {
+    ORB_REQUIRE(a && b && dist && n >= 0, ORB_ERR_INVALID, "bad argument");
+    if (n == 0) return ORB_OK;
+    if (loc == ORB_DEVICE) {
+        k_descriptor_distance<<<(n + 127) / 128, 128>>>(a, b, n, dist);
+        ORB_CUDA_TRY(cudaGetLastError());
+        return ORB_OK;
+    }
+    DevBuf da, db, dd;
+    ORB_CUDA_TRY(da.alloc((size_t)n * 32)); ORB_CUDA_TRY(db.alloc((size_t)n * 32)); ORB_CUDA_TRY(dd.alloc((size_t)n * 4));
+    ORB_CUDA_TRY(cudaMemcpy(da.p, a, (size_t)n * 32, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice));
+    k_descriptor_distance<<<(n + 127) / 128, 128>>>((const uint8_t *)da.p, (const uint8_t *)db.p, n, (int32_t *)dd.p);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpy(dist, dd.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return ORB_OK;
+}
+
+int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t ndb, int64_t idx_base, int32_t *best_dist,
+                     int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc) {
+    ORB_REQUIRE(queries && best_dist && best_idx && second_dist && second_idx, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(nq >= 1 && ndb >= 0 && (db || ndb == 0), ORB_ERR_INVALID, "bad sizes");
+    Top2Scratch scratch;
+    int rc;
+    if (loc == ORB_DEVICE) {
+        rc = top2_device(queries, nq, db, ndb, idx_base, best_dist, best_idx, second_dist, second_idx, 0, &scratch);
+        if (rc == ORB_OK && cudaStreamSynchronize(0) != cudaSuccess) rc = ORB_ERR_CUDA;
+        if (scratch.buf) cudaFree(scratch.buf);
+        return rc;
+    }
+    DevBuf dq, ddb, out;
+    ORB_CUDA_TRY(dq.alloc((size_t)nq * 32)); ORB_CUDA_TRY(ddb.alloc((size_t)ndb * 32)); ORB_CUDA_TRY(out.alloc((size_t)nq * 24));
+    ORB_CUDA_TRY(cudaMemcpy(dq.p, queries, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    if (ndb) ORB_CUDA_TRY(cudaMemcpy(ddb.p, db, (size_t)ndb * 32, cudaMemcpyHostToDevice));
+    int64_t *o_i1 = (int64_t *)out.p, *o_i2 = o_i1 + nq;
+    int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
+    rc = top2_device((const uint8_t *)dq.p, nq, (const uint8_t *)ddb.p, ndb, idx_base, o_d1, o_i1, o_d2, o_i2, 0, &scratch);
+    if (rc == ORB_OK) {
+        cudaError_t e = cudaMemcpy(best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { set_error("copy back: %s", cudaGetErrorString(e)); rc = ORB_ERR_CUDA; }
+    }
+    if (scratch.buf) cudaFree(scratch.buf);
+    return rc;
+}
+
+int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx, const int32_t *second_dist,
+                   const int64_t *second_idx, int32_t *out_best_dist, int64_t *out_best_idx, int32_t *out_second_dist,
+                   int64_t *out_second_idx, int loc) {
+    ORB_REQUIRE(nshards >= 1 && nq >= 1 && best_dist && best_idx && second_dist && second_idx && out_best_dist && out_best_idx &&
+                    out_second_dist && out_second_idx, ORB_ERR_INVALID, "bad argument");
+    if (loc == ORB_DEVICE) {
+        k_top2_merge<<<(nq + 127) / 128, 128>>>(nshards, nq, best_dist, best_idx, second_dist, second_idx, out_best_dist,
+                                                out_best_idx, out_second_dist, out_second_idx);
+        ORB_CUDA_TRY(cudaGetLastError());
+        return ORB_OK;
+    }
+    const size_t per = (size_t)nshards * nq;
+    DevBuf in, out;
+    ORB_CUDA_TRY(in.alloc(per * 24)); ORB_CUDA_TRY(out.alloc((size_t)nq * 24));
+    int64_t *i1 = (int64_t *)in.p, *i2 = i1 + per;
+    int32_t *d1 = (int32_t *)(i2 + per), *d2 = d1 + per;
+    ORB_CUDA_TRY(cudaMemcpy(i1, best_idx, per * 8, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(i2, second_idx, per * 8, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d1, best_dist, per * 4, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d2, second_dist, per * 4, cudaMemcpyHostToDevice));
+    int64_t *o_i1 = (int64_t *)out.p, *o_i2 = o_i1 + nq;
+    int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
+    k_top2_merge<<<(nq + 127) / 128, 128>>>(nshards, nq, d1, i1, d2, i2, o_d1, o_i1, o_d2, o_i2);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpy(out_best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(out_second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(out_best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(out_second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    return ORB_OK;
+}
+
+int orb_measure_popc_rate(double *gpopc_per_s) {
+    ORB_REQUIRE(gpopc_per_s, ORB_ERR_INVALID, "null argument");
+    int dev = 0, sms = 148;
+    ORB_CUDA_TRY(cudaGetDevice(&dev));
+    ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int blocks = sms * 8, threads = 256, iters = 20000;
+    DevBuf out;
+    ORB_CUDA_TRY(out.alloc((size_t)blocks * threads * 4));
+    cudaEvent_t e0, e1;
+    ORB_CUDA_TRY(cudaEventCreate(&e0)); ORB_CUDA_TRY(cudaEventCreate(&e1));
+    k_popc_rate<<<blocks, threads>>>((unsigned *)out.p, 2000);   // warm-up
+    double best = 0;
+    for (int rep = 0; rep < 3; rep++) {
+        cudaEventRecord(e0);
+        k_popc_rate<<<blocks, threads>>>((unsigned *)out.p, iters);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); set_error("popc bench: %s", cudaGetErrorString(e)); return ORB_ERR_CUDA; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        best = std::max(best, (double)blocks * threads * iters * 8.0 / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *gpopc_per_s = best;
+    return ORB_OK;
+}
+
+// ---- sharded database ---------------------------------------------------------------------
+
+int orb_db_create(int64_t row_begin, int64_t row_end, int device, orb_db **out) {
+    ORB_REQUIRE(out && row_begin >= 0 && row_end >= row_begin, ORB_ERR_INVALID, "bad row range");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
+    orb_db *db = new orb_db();
+    if (device >= 0) { if (cudaSetDevice(device) != cudaSuccess) { delete db; set_error("cudaSetDevice(%d) failed", device); return ORB_ERR_CUDA; } db->device = device; }
+    else cudaGetDevice(&db->device);
+    db->row_begin = row_begin; db->row_end = row_end;
+    const size_t bytes = (size_t)(row_end - row_begin) * 32;
+    e = cudaMalloc(&db->d_rows, bytes ? bytes : 32);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { set_error("orb_db_create: %s", cudaGetErrorString(e)); if (db->d_rows) cudaFree(db->d_rows); delete db; return ORB_ERR_CUDA; }
+    *out = db;
+    return ORB_OK;
+}
+
+void orb_db_destroy(orb_db *db) {
+    if (!db) return;
+    cudaSetDevice(db->device);
+    cudaStreamSynchronize(db->stream);
+    cudaFree(db->d_rows);
+    if (db->scratch.buf) cudaFree(db->scratch.buf);
+    if (db->d_io) cudaFree(db->d_io);
+    cudaStreamDestroy(db->stream);
+    delete db;
+}
+
+int orb_db_upload(orb_db *db, int64_t first_row, const uint8_t *rows, int64_t nrows, int loc) {
+    ORB_REQUIRE(db && rows && first_row >= db->row_begin && first_row + nrows <= db->row_end && nrows >= 0, ORB_ERR_INVALID,
+                "rows outside the shard");
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    ORB_CUDA_TRY(cudaMemcpyAsync(db->d_rows + (size_t)(first_row - db->row_begin) * 32, rows, (size_t)nrows * 32,
+                                 loc == ORB_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    return ORB_OK;
+}
+
+int orb_db_fill_synthetic(orb_db *db, uint64_t seed) {
+    ORB_REQUIRE(db, ORB_ERR_INVALID, "null handle");
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    const long long nwords = (db->row_end - db->row_begin) * 4;
+    if (nwords > 0) {
+        k_db_fill<<<2048, 256, 0, db->stream>>>((unsigned long long *)db->d_rows, nwords, db->row_begin * 4, seed);
+        db->launches++;
+    }
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    return ORB_OK;
+}
+
+int orb_db_row(orb_db *db, int64_t global_row, uint8_t *out32) {
+    ORB_REQUIRE(db && out32 && global_row >= db->row_begin && global_row < db->row_end, ORB_ERR_INVALID, "row outside the shard");
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    ORB_CUDA_TRY(cudaMemcpy(out32, db->d_rows + (size_t)(global_row - db->row_begin) * 32, 32, cudaMemcpyDeviceToHost));
+    return ORB_OK;
+}
+
+uint8_t *orb_db_device_ptr(orb_db *db) { return db ? db->d_rows : nullptr; }
+void *orb_db_stream(orb_db *db) { return db ? (void *)db->stream : nullptr; }
+int64_t orb_db_launch_count(const orb_db *db) { return db ? db->launches : 0; }
+
+int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist, int64_t *best_idx, int32_t *second_dist,
+                 int64_t *second_idx, int loc) {
+    ORB_REQUIRE(db && queries && nq >= 1 && best_dist && best_idx && second_dist && second_idx, ORB_ERR_INVALID, "bad argument");
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    const long long n = db->row_end - db->row_begin;
+    if (loc == ORB_DEVICE) {
+        int rc = top2_device(queries, nq, db->d_rows, n, db->row_begin, best_dist, best_idx, second_dist, second_idx, db->stream,
+                             &db->scratch);
+        db->launches += 2;
+        return rc;
+    }
+    const size_t need = (size_t)nq * (32 + 24) + 256;
+    if (db->io_bytes < need) {
+        if (db->d_io) cudaFree(db->d_io);
+        db->d_io = nullptr; db->io_bytes = 0;
+        ORB_CUDA_TRY(cudaMalloc(&db->d_io, need));
+        db->io_bytes = need;
+    }
+    int64_t *o_i1 = (int64_t *)db->d_io, *o_i2 = o_i1 + nq;
+    int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
+    uint8_t *dq = (uint8_t *)(o_d2 + nq);
+    dq = (uint8_t *)(((uintptr_t)dq + 15) & ~(uintptr_t)15);
+    ORB_CUDA_TRY(cudaMemcpyAsync(dq, queries, (size_t)nq * 32, cudaMemcpyHostToDevice, db->stream));
+    int rc = top2_device(dq, nq, db->d_rows, n, db->row_begin, o_d1, o_i1, o_d2, o_i2, db->stream, &db->scratch);
+    db->launches += 2;
+    if (rc != ORB_OK) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    return ORB_OK;
+}
+
+}  // extern "C"

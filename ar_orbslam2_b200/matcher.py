@@ -1,0 +1,125 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher (ref: ORB_SLAM2/include/ORBmatcher.h:34-114) over liborbgpu:
+the Hamming distance, the brute-force top-2 scan and the keyframe-range-sharded descriptor database
+(config C5).  The windowed tracking matchers live in tracking.py."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._abi import ORB_DEVICE, ORB_HOST, ptr
+
+TH_HIGH = 100   # ref ORBmatcher.cc:37
+TH_LOW = 50     # ref ORBmatcher.cc:38
+HISTO_LENGTH = 30
+
+
+def DescriptorDistance(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """ORBmatcher::DescriptorDistance (ref ORBmatcher.cc:1650-1666) for n descriptor pairs, on the GPU."""
+    a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    assert a.shape == b.shape
+    out = np.zeros(a.shape[0], np.int32)
+    _lib.check(_lib.lib().orb_descriptor_distance(ptr(a), ptr(b), a.shape[0], ptr(out), ORB_HOST), "orb_descriptor_distance")
+    return out
+
+
+def hamming_top2(queries: np.ndarray, db: np.ndarray, idx_base: int = 0):
+    """Best and second-best database row per query (strict '<', first row wins ties).  Returns
+    (best_dist, best_idx, second_dist, second_idx); 256 / -1 where absent."""
+    q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+    d = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+    nq = q.shape[0]
+    d1, d2 = np.zeros(nq, np.int32), np.zeros(nq, np.int32)
+    i1, i2 = np.zeros(nq, np.int64), np.zeros(nq, np.int64)
+    _lib.check(_lib.lib().orb_hamming_top2(ptr(q), nq, ptr(d), C.c_int64(d.shape[0]), C.c_int64(idx_base), ptr(d1), ptr(i1),
+                                           ptr(d2), ptr(i2), ORB_HOST), "orb_hamming_top2")
+    return d1, i1, d2, i2
+
+
+def top2_merge(best_dist, best_idx, second_dist, second_idx):
+    """Merge [nshards, nq] partial lists (shards in database order) into the single-scan result."""
+    bd = np.ascontiguousarray(best_dist, np.int32)
+    bi = np.ascontiguousarray(best_idx, np.int64)
+    sd = np.ascontiguousarray(second_dist, np.int32)
+    si = np.ascontiguousarray(second_idx, np.int64)
+    ns, nq = bd.shape
+    o = (np.zeros(nq, np.int32), np.zeros(nq, np.int64), np.zeros(nq, np.int32), np.zeros(nq, np.int64))
+    _lib.check(_lib.lib().orb_top2_merge(ns, nq, ptr(bd), ptr(bi), ptr(sd), ptr(si), ptr(o[0]), ptr(o[1]), ptr(o[2]), ptr(o[3]),
+                                         ORB_HOST), "orb_top2_merge")
+    return o
+
+
+def top2_merge_device(nshards, nq, d_bd, d_bi, d_sd, d_si, o_bd, o_bi, o_sd, o_si):
+    vp = C.c_void_p
+    _lib.check(_lib.lib().orb_top2_merge(nshards, nq, vp(d_bd), vp(d_bi), vp(d_sd), vp(d_si), vp(o_bd), vp(o_bi), vp(o_sd),
+                                         vp(o_si), ORB_DEVICE), "orb_top2_merge")
+
+
+def measure_popc_rate() -> float:
+    """Measured POPC throughput of the device in Gpopc32/s (matching roofline denominator)."""
+    v = C.c_double()
+    _lib.check(_lib.lib().orb_measure_popc_rate(C.byref(v)), "orb_measure_popc_rate")
+    return v.value
+
+
+class DescriptorDB:
+    """Shard [row_begin,row_end) of a global descriptor database resident in HBM (keyframe-range sharding,
+    replaces the BoW inverted index of ref KeyFrameDatabase.cc:185 with a brute-force scan)."""
+
+    def __init__(self, row_begin: int, row_end: int, device: int = -1):
+        self._L = _lib.lib()
+        self._L.orb_db_device_ptr.restype = C.c_void_p
+        self._L.orb_db_stream.restype = C.c_void_p
+        self._L.orb_db_launch_count.restype = C.c_int64
+        self._h = C.c_void_p()
+        _lib.check(self._L.orb_db_create(C.c_int64(row_begin), C.c_int64(row_end), device, C.byref(self._h)), "orb_db_create")
+        self.row_begin, self.row_end = row_begin, row_end
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orb_db_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, first_row: int, rows: np.ndarray):
+        rows = np.ascontiguousarray(rows, np.uint8).reshape(-1, 32)
+        _lib.check(self._L.orb_db_upload(self._h, C.c_int64(first_row), ptr(rows), C.c_int64(rows.shape[0]), ORB_HOST), "orb_db_upload")
+
+    def fill_synthetic(self, seed: int):
+        _lib.check(self._L.orb_db_fill_synthetic(self._h, C.c_uint64(seed)), "orb_db_fill_synthetic")
+
+    def row(self, global_row: int) -> np.ndarray:
+        out = np.zeros(32, np.uint8)
+        _lib.check(self._L.orb_db_row(self._h, C.c_int64(global_row), ptr(out)), "orb_db_row")
+        return out
+
+    def rows(self, idx) -> np.ndarray:
+        return np.stack([self.row(int(i)) for i in idx]) if len(idx) else np.zeros((0, 32), np.uint8)
+
+    @property
+    def stream(self) -> int:
+        return self._L.orb_db_stream(self._h)
+
+    @property
+    def launch_count(self) -> int:
+        return self._L.orb_db_launch_count(self._h)
+
+    def query(self, queries: np.ndarray):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+        nq = q.shape[0]
+        d1, d2 = np.zeros(nq, np.int32), np.zeros(nq, np.int32)
+        i1, i2 = np.zeros(nq, np.int64), np.zeros(nq, np.int64)
+        _lib.check(self._L.orb_db_query(self._h, ptr(q), nq, ptr(d1), ptr(i1), ptr(d2), ptr(i2), ORB_HOST), "orb_db_query")
+        return d1, i1, d2, i2
+
+    def query_device(self, d_q: int, nq: int, d_d1: int, d_i1: int, d_d2: int, d_i2: int):
+        """Asynchronous on the shard's stream; raw device pointers."""
+        vp = C.c_void_p
+        _lib.check(self._L.orb_db_query(self._h, vp(d_q), nq, vp(d_d1), vp(d_i1), vp(d_d2), vp(d_i2), ORB_DEVICE), "orb_db_query")

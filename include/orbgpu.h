@@ -282,6 +282,8 @@ int orb_db_upload(orb_db *db, int64_t first_row, const uint8_t *rows, int64_t nr
 int orb_db_fill_synthetic(orb_db *db, uint64_t seed);
 int orb_db_row(orb_db *db, int64_t global_row, uint8_t *out32);
 uint8_t *orb_db_device_ptr(orb_db *db);
+void *orb_db_stream(orb_db *db);                 /* cudaStream_t the shard's kernels run on */
+int64_t orb_db_launch_count(const orb_db *db);
 /* Local top-2 of nq queries against the shard; outputs are device or host per loc.        */
 int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist,
                  int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc);

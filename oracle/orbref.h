@@ -24,6 +24,12 @@ int orbref_stereo_match(orbref_extractor *left, orbref_extractor *right, const o
                         const uint8_t *descL, int N, const orb_keypoint *keysR, const uint8_t *descR, int Nr,
                         float mbf, float mb, float *uRight, float *depth, int32_t *sad_out, int *n_matched);
 int orbref_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist);
+int orbref_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t ndb, int64_t idx_base,
+                        int32_t *best_dist, int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int fast,
+                        int threads);
+void orbref_three_maxima(const int *sizes, int L, int *ind1, int *ind2, int *ind3);
+int orbref_rot_bin(float angle_a, float angle_b);
+int orbref_rot_hist_filter(const float *angle_a, const float *angle_b, int n, uint8_t *keep);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -167,3 +167,22 @@ def descriptor_distance(a: np.ndarray, b: np.ndarray) -> np.ndarray:
     out = np.zeros(a.shape[0], np.int32)
     lib().orbref_descriptor_distance(ptr(a), ptr(b), a.shape[0], ptr(out))
     return out
+
+
+def hamming_top2(queries, db, idx_base=0, fast=False, threads=1):
+    q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+    d = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+    nq = q.shape[0]
+    d1, d2 = np.zeros(nq, np.int32), np.zeros(nq, np.int32)
+    i1, i2 = np.zeros(nq, np.int64), np.zeros(nq, np.int64)
+    lib().orbref_hamming_top2(ptr(q), nq, ptr(d), C.c_int64(d.shape[0]), C.c_int64(idx_base), ptr(d1), ptr(i1), ptr(d2), ptr(i2),
+                              int(fast), threads)
+    return d1, i1, d2, i2
+
+
+def rot_hist_filter(angle_a, angle_b):
+    a = np.ascontiguousarray(angle_a, np.float32)
+    b = np.ascontiguousarray(angle_b, np.float32)
+    keep = np.zeros(a.size, np.uint8)
+    lib().orbref_rot_hist_filter(ptr(a), ptr(b), a.size, ptr(keep))
+    return keep.astype(bool)
