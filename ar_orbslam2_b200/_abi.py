@@ -44,3 +44,31 @@ assert CANDIDATE_DTYPE.itemsize == 8
 
 def ptr(a: np.ndarray, ctype=C.c_void_p):
     return a.ctypes.data_as(ctype)
+
+
+class OrbFrameDesc(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p), ("u_right", C.c_void_p),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("nlevels", C.c_int32), ("scale_factors", C.c_void_p)]
+
+
+class OrbWindowQueries(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("x", C.c_void_p), ("y", C.c_void_p), ("radius", C.c_void_p),
+                ("min_level", C.c_void_p), ("max_level", C.c_void_p), ("strict_levels", C.c_int32),
+                ("stereo_ref", C.c_void_p), ("stereo_tol", C.c_void_p), ("descriptors", C.c_void_p), ("angle", C.c_void_p),
+                ("claims", C.c_void_p)]
+
+
+class OrbTrackPoints(C.Structure):
+    _fields_ = [("n", C.c_int32), ("in_view", C.c_void_p), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p),
+                ("level", C.c_void_p), ("view_cos", C.c_void_p), ("descriptors", C.c_void_p), ("obs_positive", C.c_void_p)]
+
+
+class OrbLastPoints(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p), ("invz", C.c_void_p),
+                ("octave", C.c_void_p), ("angle", C.c_void_p), ("descriptors", C.c_void_p), ("obs_positive", C.c_void_p)]
+
+
+def optr(a):
+    """pointer or NULL"""
+    return None if a is None else a.ctypes.data_as(C.c_void_p)

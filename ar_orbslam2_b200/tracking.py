@@ -1,0 +1,164 @@
+"""Host-side mirror of the tracking-time entry points of ORB_SLAM2::ORBmatcher (ref:
+ORB_SLAM2/include/ORBmatcher.h:42-94) and of the Frame members they read, over liborbgpu.
+
+`Frame` holds what the matchers use of ORB_SLAM2::Frame (mvKeysUn, mDescriptors, mvuRight, the 64x48 grid);
+`ORBmatcher` keeps the reference's method names.  MapPoint / KeyFrame object graphs stay with the caller:
+the methods take the flat arrays the C++ shim gathers under the reference's getters.
+
+The same classes drive the CPU oracle when constructed with `backend=oracle_module` (tests only)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._abi import (KEYPOINT_DTYPE, OrbFrameDesc, OrbLastPoints, OrbTrackPoints, OrbWindowQueries, optr, ptr)
+
+ORB_SELECT_BEST, ORB_SELECT_RATIO_LEVEL = 0, 1
+
+
+class _GpuBackend:
+    prefix = "orb_"
+
+    def __init__(self):
+        self.L = _lib.lib()
+
+    def check(self, rc, what):
+        _lib.check(rc, what)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, np.float32)
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, np.int32)
+
+
+def _u8(a):
+    return None if a is None else np.ascontiguousarray(a, np.uint8)
+
+
+class Frame:
+    """The matcher-facing part of ORB_SLAM2::Frame (ref Frame.h:39-40,161-163; Frame.cc:235-250,332-397)."""
+
+    def __init__(self, keys_un, descriptors, scale_factors, bounds, u_right=None, backend=None):
+        self.B = backend or _GpuBackend()
+        self.keys = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+        self.desc = _u8(descriptors).reshape(-1, 32)
+        self.scale = _f32(scale_factors)
+        self.u_right = _f32(u_right)
+        self.N = len(self.keys)
+        self.bounds = tuple(float(b) for b in bounds)   # mnMinX, mnMaxX, mnMinY, mnMaxY
+        d = OrbFrameDesc(self.N, ptr(self.keys), ptr(self.desc), optr(self.u_right), *self.bounds, len(self.scale), ptr(self.scale))
+        self._h = C.c_void_p()
+        self.B.check(getattr(self.B.L, self.B.prefix + "frame_create")(C.byref(d), C.byref(self._h)), "frame_create")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            fn = getattr(self.B.L, self.B.prefix + "frame_destroy")
+            fn.argtypes = [C.c_void_p]
+            fn.restype = None
+            fn(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def GetFeaturesInArea(self, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.zeros(max(self.N, 1), np.int32)
+        n = C.c_int()
+        self.B.check(getattr(self.B.L, self.B.prefix + "frame_features_in_area")(
+            self._h, C.c_float(x), C.c_float(y), C.c_float(r), int(minLevel), int(maxLevel), ptr(out), len(out), C.byref(n)),
+            "frame_features_in_area")
+        return out[: n.value].copy()
+
+
+class ORBmatcher:
+    """ref ORBmatcher(float nnratio=0.6, bool checkOri=true), ORBmatcher.h:37"""
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, backend=None):
+        self.mfNNratio = float(np.float32(nnratio))
+        self.mbCheckOrientation = bool(checkOri)
+        self.B = backend or _GpuBackend()
+
+    def _fn(self, name):
+        return getattr(self.B.L, self.B.prefix + name)
+
+    def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched: np.ndarray, windowSize=10):
+        """ref ORBmatcher.cc:405-523.  Returns (nmatches, vnMatches12); vbPrevMatched [n1,2] is updated in place."""
+        assert vbPrevMatched.dtype == np.float32 and vbPrevMatched.flags.c_contiguous and vbPrevMatched.shape == (F1.N, 2)
+        m12 = np.full(F1.N, -1, np.int32)
+        nm = C.c_int()
+        self.B.check(self._fn("search_for_initialization")(F1._h, F2._h, ptr(vbPrevMatched), ptr(m12), int(windowSize),
+                                                           C.c_float(self.mfNNratio), int(self.mbCheckOrientation), C.byref(nm)),
+                     "search_for_initialization")
+        return nm.value, m12
+
+    def SearchByProjectionPoints(self, F: Frame, in_view, proj_x, proj_y, proj_xr, level, view_cos, descriptors, th=3.0,
+                                 claimed=None, obs_positive=None):
+        """ref SearchByProjection(Frame&, const vector<MapPoint*>&, th), ORBmatcher.cc:45-129.
+        Returns (nmatches, assigned[F.N]) with assigned[i] = index of the map point put in F.mvpMapPoints[i] or -1."""
+        a = [_u8(in_view), _f32(proj_x), _f32(proj_y), _f32(proj_xr), _i32(level), _f32(view_cos), _u8(descriptors), _u8(obs_positive)]
+        P = OrbTrackPoints(len(a[0]), *[optr(x) for x in a])
+        assigned = np.full(F.N, -1, np.int32)
+        nm = C.c_int()
+        cl = _u8(claimed)
+        self.B.check(self._fn("search_by_projection_points")(F._h, C.byref(P), optr(cl), C.c_float(th), C.c_float(self.mfNNratio),
+                                                             ptr(assigned), C.byref(nm)), "search_by_projection_points")
+        return nm.value, assigned
+
+    def SearchByProjectionLast(self, Cur: Frame, valid, u, v, invz, octave, angle, descriptors, th, forward=False, backward=False,
+                               mbf=0.0, claimed=None, obs_positive=None):
+        """ref SearchByProjection(Frame &Cur, const Frame &Last, th, bMono), ORBmatcher.cc:1331-1473 (after the projection)."""
+        a = [_u8(valid), _f32(u), _f32(v), _f32(invz), _i32(octave), _f32(angle), _u8(descriptors), _u8(obs_positive)]
+        P = OrbLastPoints(len(a[0]), *[optr(x) for x in a])
+        assigned = np.full(Cur.N, -1, np.int32)
+        nm = C.c_int()
+        cl = _u8(claimed)
+        self.B.check(self._fn("search_by_projection_last")(Cur._h, C.byref(P), optr(cl), C.c_float(th), int(forward), int(backward),
+                                                           C.c_float(mbf), int(self.mbCheckOrientation), ptr(assigned), C.byref(nm)),
+                     "search_by_projection_last")
+        return nm.value, assigned
+
+    def SearchWindowed(self, F: Frame, x, y, radius, min_level, max_level, descriptors, select, th_dist, valid=None, strict_levels=False,
+                       stereo_ref=None, stereo_tol=None, angle=None, claims=None, claimed=None, check_orientation=None):
+        """The generic projection-matcher loop (orb_search_windowed): SearchByProjection(Frame,KeyFrame,...) :1475-1602,
+        SearchByProjection(KeyFrame,Scw,...) :290-403, Fuse :828-1103 and SearchBySim3 :1105-1329 map onto it."""
+        a = dict(valid=_u8(valid), x=_f32(x), y=_f32(y), radius=_f32(radius), min_level=_i32(min_level), max_level=_i32(max_level),
+                 stereo_ref=_f32(stereo_ref), stereo_tol=_f32(stereo_tol), descriptors=_u8(descriptors), angle=_f32(angle), claims=_u8(claims))
+        Q = OrbWindowQueries(len(a["x"]), optr(a["valid"]), optr(a["x"]), optr(a["y"]), optr(a["radius"]), optr(a["min_level"]),
+                             optr(a["max_level"]), int(strict_levels), optr(a["stereo_ref"]), optr(a["stereo_tol"]),
+                             optr(a["descriptors"]), optr(a["angle"]), optr(a["claims"]))
+        assigned = np.full(F.N, -1, np.int32)
+        nm = C.c_int()
+        cl = _u8(claimed)
+        ori = self.mbCheckOrientation if check_orientation is None else check_orientation
+        self.B.check(self._fn("search_windowed")(F._h, C.byref(Q), optr(cl), int(select), int(th_dist), C.c_float(self.mfNNratio),
+                                                 int(ori), ptr(assigned), C.byref(nm)), "search_windowed")
+        return nm.value, assigned
+
+    def SearchByBoW(self, KF: Frame, F: Frame, kf_off, kf_idx, f_off, f_idx, kf_valid, f_valid=None, strict_low=False):
+        """ref SearchByBoW(KeyFrame*, Frame&, ...) ORBmatcher.cc:159-288 (strict_low/f_valid: the KF-KF form :525-658).
+        The FeatureVector merge-join is given as CSR groups over the shared vocabulary nodes."""
+        ko, ki, fo, fi = _i32(kf_off), _i32(kf_idx), _i32(f_off), _i32(f_idx)
+        kv, fv = _u8(kf_valid), _u8(f_valid)
+        matches = np.full(F.N, -1, np.int32)
+        nm = C.c_int()
+        self.B.check(self._fn("search_by_bow")(KF._h, F._h, len(ko) - 1, ptr(ko), ptr(ki), ptr(fo), ptr(fi), ptr(kv), optr(fv),
+                                               int(strict_low), C.c_float(self.mfNNratio), int(self.mbCheckOrientation), ptr(matches),
+                                               C.byref(nm)), "search_by_bow")
+        return nm.value, matches
+
+
+def rot_hist_filter(angle_a, angle_b) -> np.ndarray:
+    """Rotation-consistency filter (30-bin histogram with the reference's 1/HISTO_LENGTH factor + ComputeThreeMaxima)."""
+    a, b = _f32(angle_a), _f32(angle_b)
+    keep = np.zeros(a.size, np.uint8)
+    _lib.check(_lib.lib().orb_rot_hist_filter(ptr(a), ptr(b), a.size, ptr(keep)), "orb_rot_hist_filter")
+    return keep.astype(bool)

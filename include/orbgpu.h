@@ -194,6 +194,40 @@ void orb_frame_destroy(orb_frame *f);
 int orb_frame_features_in_area(orb_frame *f, float x, float y, float r, int min_level,
                                int max_level, int32_t *indices, int capacity, int *n_out);
 
+/* Generic windowed matcher: the loop every projection matcher of the reference shares
+ * (ORBmatcher.cc:51-126, 1354-1448, 1491-1578, 312-400 and the Fuse / SearchBySim3 loops):
+ * for each query in order -> GetFeaturesInArea window -> skip claimed features -> optional
+ * stereo gate -> best (and second) Hamming distance in traversal order -> threshold -> assign.
+ * Assignments made by earlier queries are visible to later ones exactly as in the reference:
+ * distances are computed in parallel, claims are resolved in query order on the device.      */
+typedef struct orb_window_queries {
+    int32_t n;
+    const uint8_t *valid;                  /* 0 = the reference `continue`s before the search    */
+    const float *x, *y, *radius;           /* GetFeaturesInArea(x, y, r, ...)                    */
+    const int32_t *min_level, *max_level;  /* its level arguments                                */
+    int32_t strict_levels;                 /* 0: Frame::GetFeaturesInArea rule (filter only if
+                                              minLevel>0 || maxLevel>=0, Frame.cc:353-373);
+                                              1: always skip octave<min || octave>max (the in-loop
+                                              filter of ORBmatcher.cc:378-381, 912-915)          */
+    const float *stereo_ref, *stereo_tol;  /* both NULL = no stereo gate; else a candidate with
+                                              uRight>0 is skipped if |stereo_ref-uRight|>tol     */
+    const uint8_t *descriptors;            /* n x 32                                             */
+    const float *angle;                    /* query keypoint angle (rotation histogram)          */
+    const uint8_t *claims;                 /* NULL = every accepted query blocks its feature for
+                                              later queries; else only where claims[q] != 0
+                                              (MapPoint::Observations()>0, ORBmatcher.cc:87-89)  */
+} orb_window_queries;
+enum { ORB_SELECT_BEST = 0,         /* accept if best <= th_dist (ORBmatcher.cc:1429, 1558, 394)  */
+       ORB_SELECT_RATIO_LEVEL = 1   /* best <= th_dist and not (same octave && best > ratio*second),
+                                       ORBmatcher.cc:118-125                                     */ };
+/* claimed[i] != 0: feature i already holds a blocking map point on entry.  assigned[i] (out) =
+ * index of the query whose map point ends up in mvpMapPoints[i], or -1.  With
+ * check_orientation the 3-maxima rotation filter (ORBmatcher.cc:1451-1470) is applied; nmatches
+ * follows the reference's counting (an overwritten assignment is still counted, F7).          */
+int orb_search_windowed(orb_frame *f, const orb_window_queries *q, const uint8_t *claimed, int select,
+                        int th_dist, float nnratio, int check_orientation, int32_t *assigned,
+                        int *nmatches);
+
 /* ref: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:405-523.
  * prev_matched: n1 x 2 floats, updated in place (ref :518-520).  matches12: n1 ints.       */
 int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matched,
@@ -201,8 +235,7 @@ int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matc
                                   int check_orientation, int *nmatches);
 
 /* ref: ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th),
- * src/ORBmatcher.cc:45-129.  Map points are passed flat, already filtered the way
- * Frame::isInFrustum leaves them (mbTrackInView etc.).                                     */
+ * src/ORBmatcher.cc:45-129.  Map points are passed flat, as Frame::isInFrustum leaves them.  */
 typedef struct orb_track_points {
     int32_t n;
     const uint8_t *in_view;        /* mbTrackInView && !isBad()                            */
@@ -210,6 +243,7 @@ typedef struct orb_track_points {
     const int32_t *level;          /* mnTrackScaleLevel                                    */
     const float *view_cos;         /* mTrackViewCos                                        */
     const uint8_t *descriptors;    /* GetDescriptor(), n x 32                              */
+    const uint8_t *obs_positive;   /* Observations()>0 per point; NULL = all               */
 } orb_track_points;
 /* claimed[i] != 0 : F.mvpMapPoints[i] && Observations()>0 on entry (ref :87-89).
  * assigned[i]: out, index of the map point written to F.mvpMapPoints[i] or -1.             */
@@ -218,32 +252,35 @@ int orb_search_by_projection_points(orb_frame *f, const orb_track_points *pts,
                                     int32_t *assigned, int *nmatches);
 
 /* ref: ORBmatcher::SearchByProjection(Frame &Cur, const Frame &Last, th, bMono),
- * src/ORBmatcher.cc:1331-1473.  The projection (ref :1362-1379) is done by the caller or by
- * orb_project_points; here each Last feature i with a valid map point carries its projected
- * (u,v), 1/z, last octave and descriptor.                                                  */
+ * src/ORBmatcher.cc:1331-1473.  The pose algebra (ref :1341-1379) stays with the caller: each
+ * Last feature i carries its projected (u,v), 1/z, octave, angle and descriptor.
+ * forward/backward = bForward/bBackward of ref :1351-1352.                                  */
 typedef struct orb_last_points {
     int32_t n;
-    const uint8_t *valid;          /* pMP && !mvbOutlier && invzc>=0 && in image bounds     */
+    const uint8_t *valid;          /* pMP && !mvbOutlier && invzc>=0 && inside image bounds */
     const float *u, *v, *invz;
     const int32_t *octave;         /* LastFrame.mvKeys[i].octave                            */
     const float *angle;            /* LastFrame.mvKeysUn[i].angle                           */
     const uint8_t *descriptors;
+    const uint8_t *obs_positive;   /* Observations()>0 per point; NULL = all               */
 } orb_last_points;
 int orb_search_by_projection_last(orb_frame *cur, const orb_last_points *pts,
                                   const uint8_t *claimed, float th, int forward, int backward,
                                   float mbf, int check_orientation, int32_t *assigned,
                                   int *nmatches);
 
-/* ref: ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...), src/ORBmatcher.cc:159-288.
- * The two DBoW2::FeatureVectors are passed as CSR over the common node ids in ascending
- * order (the merge-join of ref :180-264 done by the caller): group g holds KF feature
- * indices kf_idx[kf_off[g]..kf_off[g+1]) and F indices f_idx[f_off[g]..f_off[g+1]).
- * kf_valid[i] = map point exists and is not bad.  matches[j] = KF feature index whose map
- * point is written to vpMapPointMatches[j], or -1.                                         */
+/* ref: ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...), src/ORBmatcher.cc:159-288, and the
+ * KeyFrame-KeyFrame form :525-658.  The two DBoW2::FeatureVectors are passed as CSR over the
+ * common node ids in ascending order (the merge-join of ref :180-264 done by the caller):
+ * group g holds KF feature indices kf_idx[kf_off[g]..kf_off[g+1]) and F indices
+ * f_idx[f_off[g]..f_off[g+1]).  kf_valid[i] = map point exists and is not bad; f_valid (NULL =
+ * all) = second-side validity of the KF-KF form (:577-583).  strict_low=1 selects the KF-KF
+ * threshold `best < TH_LOW` (:601) instead of `<=` (:228).  matches[j] (size f->n) = KF feature
+ * index matched to F feature j, or -1.                                                      */
 int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *kf_off,
                       const int32_t *kf_idx, const int32_t *f_off, const int32_t *f_idx,
-                      const uint8_t *kf_valid, float nnratio, int check_orientation,
-                      int32_t *matches, int *nmatches);
+                      const uint8_t *kf_valid, const uint8_t *f_valid, int strict_low,
+                      float nnratio, int check_orientation, int32_t *matches, int *nmatches);
 
 /* ref: ORBmatcher::ComputeThreeMaxima + the rotation binning, src/ORBmatcher.cc:238-245,
  * 1604-1645 (factor = 1/HISTO_LENGTH quirk kept).  keep[i]=1 if pair i survives.           */

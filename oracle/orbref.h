@@ -30,6 +30,22 @@ int orbref_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64
 void orbref_three_maxima(const int *sizes, int L, int *ind1, int *ind2, int *ind3);
 int orbref_rot_bin(float angle_a, float angle_b);
 int orbref_rot_hist_filter(const float *angle_a, const float *angle_b, int n, uint8_t *keep);
+typedef struct orbref_frame orbref_frame;
+int orbref_frame_create(const orb_frame_desc *d, orbref_frame **out);
+void orbref_frame_destroy(orbref_frame *f);
+int orbref_frame_features_in_area(orbref_frame *f, float x, float y, float r, int min_level, int max_level, int32_t *indices,
+                                  int capacity, int *n_out);
+int orbref_search_for_initialization(orbref_frame *F1, orbref_frame *F2, float *vbPrevMatched, int32_t *vnMatches12,
+                                     int windowSize, float mfNNratio, int mbCheckOrientation, int *nmatches_out);
+int orbref_search_windowed(orbref_frame *F, const orb_window_queries *Q, const uint8_t *claimed_in, int select, int th_dist,
+                           float mfNNratio, int mbCheckOrientation, int32_t *assigned, int *nmatches_out);
+int orbref_search_by_projection_points(orbref_frame *F, const orb_track_points *P, const uint8_t *claimed, float th, float nnratio,
+                                       int32_t *assigned, int *nmatches);
+int orbref_search_by_projection_last(orbref_frame *Cur, const orb_last_points *P, const uint8_t *claimed, float th, int forward,
+                                     int backward, float mbf, int check_orientation, int32_t *assigned, int *nmatches);
+int orbref_search_by_bow(orbref_frame *KF, orbref_frame *F, int ngroups, const int32_t *kf_off, const int32_t *kf_idx,
+                         const int32_t *f_off, const int32_t *f_idx, const uint8_t *kf_valid, const uint8_t *f_valid,
+                         int strict_low, float mfNNratio, int mbCheckOrientation, int32_t *matches, int *nmatches_out);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -186,3 +186,14 @@ def rot_hist_filter(angle_a, angle_b):
     keep = np.zeros(a.size, np.uint8)
     lib().orbref_rot_hist_filter(ptr(a), ptr(b), a.size, ptr(keep))
     return keep.astype(bool)
+
+
+class OracleBackend:
+    """Lets ar_orbslam2_b200.tracking.Frame / ORBmatcher drive the oracle's flat-array matchers (tests only)."""
+    prefix = "orbref_"
+
+    def __init__(self):
+        self.L = lib()
+
+    def check(self, rc, what):
+        _check(rc, what)

@@ -1,0 +1,164 @@
+"""GPU parity for the tracking matchers (ref: ORB_SLAM2/src/ORBmatcher.cc) on the C3 scenario of SURVEY 8(d):
+752x480 frames, frame B = frame A translated by (+7,+4) px.  Match lists must be identical to the oracle."""
+import numpy as np
+import pytest
+
+from ar_orbslam2_b200.synth import SplitMix64, shifted_frame, synth_frame
+
+pytestmark = pytest.mark.gpu
+W, H = 752, 480
+
+
+@pytest.fixture(scope="module")
+def scene(oracle):
+    a = synth_frame(W, H, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    ex = oracle.RefExtractor(2000)
+    ka, da = ex.extract(a)
+    kb, db = ex.extract(b)
+    return dict(ka=ka, da=da, kb=kb, db=db, scale=ex.tables()["scale"])
+
+
+def both(scene, oracle, which):
+    from ar_orbslam2_b200.tracking import Frame
+    k, d = scene["k" + which], scene["d" + which]
+    bounds = (0.0, float(W), 0.0, float(H))
+    return (Frame(k, d, scene["scale"], bounds), Frame(k, d, scene["scale"], bounds, backend=oracle.OracleBackend()))
+
+
+def test_features_in_area(scene, oracle, gpu_lib):
+    g, r = both(scene, oracle, "a")
+    rng = SplitMix64(5)
+    for _ in range(60):
+        x, y = rng.next() % (W + 40) - 20.0, rng.next() % (H + 40) - 20.0
+        rad = 3.0 + rng.next() % 120
+        lo = int(rng.next() % 9) - 1
+        hi = int(rng.next() % 9) - 1
+        a, b = g.GetFeaturesInArea(x, y, rad, lo, hi), r.GetFeaturesInArea(x, y, rad, lo, hi)
+        assert np.array_equal(a, b), (x, y, rad, lo, hi)
+
+
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_for_initialization(scene, oracle, gpu_lib, ori):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    g1, r1 = both(scene, oracle, "a")
+    g2, r2 = both(scene, oracle, "b")
+    prev = np.stack([scene["ka"]["x"], scene["ka"]["y"]], 1).astype(np.float32).copy()
+    pg, pr = prev.copy(), prev.copy()
+    ng, mg = ORBmatcher(0.9, ori).SearchForInitialization(g1, g2, pg, 100)
+    nr, mr = ORBmatcher(0.9, ori, backend=oracle.OracleBackend()).SearchForInitialization(r1, r2, pr, 100)
+    assert nr > 100, "scenario should produce matches"
+    assert ng == nr and np.array_equal(mg, mr) and np.array_equal(pg, pr)
+    # second call, as Tracking does on the next frame, starts from the updated vbPrevMatched
+    ng, mg = ORBmatcher(0.9, ori).SearchForInitialization(g1, g2, pg, 100)
+    nr, mr = ORBmatcher(0.9, ori, backend=oracle.OracleBackend()).SearchForInitialization(r1, r2, pr, 100)
+    assert ng == nr and np.array_equal(mg, mr) and np.array_equal(pg, pr)
+
+
+def _last_points(scene):
+    """Every Last keypoint gets a synthetic map point at depth z = 2 + (hash(i) mod 1000)/100 m; Last pose = I,
+    Cur pose = translation (0.05, 0.02, 0) m; EuRoC intrinsics."""
+    fx = fy = np.float32(435.2); cx, cy = np.float32(367.2), np.float32(252.2)
+    k = scene["ka"]
+    n = len(k)
+    z = np.array([2 + (SplitMix64(i).next() % 1000) / 100 for i in range(n)], np.float32)
+    X = (k["x"] - cx) * z / fx
+    Y = (k["y"] - cy) * z / fy
+    xc, yc = X + np.float32(0.05), Y + np.float32(0.02)
+    invz = (np.float32(1.0) / z).astype(np.float32)
+    u = (fx * xc * invz + cx).astype(np.float32)
+    v = (fy * yc * invz + cy).astype(np.float32)
+    valid = ((u >= 0) & (u <= W) & (v >= 0) & (v <= H)).astype(np.uint8)
+    valid[::17] = 0   # some features without a map point
+    return valid, u, v, invz, k["octave"].astype(np.int32), k["angle"].astype(np.float32), scene["da"]
+
+
+@pytest.mark.parametrize("mode", ["mono", "forward", "backward"])
+def test_search_by_projection_last(scene, oracle, gpu_lib, mode):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    valid, u, v, invz, octv, ang, desc = _last_points(scene)
+    # the "current" frame is frame A itself seen from the translated pose: reuse A's keypoints, with stereo info
+    ur = np.where(np.arange(len(u)) % 3 == 0, scene["ka"]["x"] - 5.0, -1.0).astype(np.float32)
+    from ar_orbslam2_b200.tracking import Frame
+    bounds = (0.0, float(W), 0.0, float(H))
+    g = Frame(scene["ka"], scene["da"], scene["scale"], bounds, u_right=ur)
+    r = Frame(scene["ka"], scene["da"], scene["scale"], bounds, u_right=ur, backend=oracle.OracleBackend())
+    claimed = (np.arange(g.N) % 11 == 0).astype(np.uint8)
+    obs = (np.arange(len(u)) % 5 != 0).astype(np.uint8)
+    kw = dict(th=15.0, forward=mode == "forward", backward=mode == "backward", mbf=40.0, claimed=claimed, obs_positive=obs)
+    ng, ag = ORBmatcher(0.9, True).SearchByProjectionLast(g, valid, u, v, invz, octv, ang, desc, **kw)
+    nr, ar = ORBmatcher(0.9, True, backend=oracle.OracleBackend()).SearchByProjectionLast(r, valid, u, v, invz, octv, ang, desc, **kw)
+    assert nr > 50
+    assert ng == nr and np.array_equal(ag, ar)
+
+
+def test_search_by_projection_points(scene, oracle, gpu_lib):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    g, r = both(scene, oracle, "b")
+    k = scene["ka"]
+    n = len(k)
+    rng = SplitMix64(9)
+    in_view = np.array([rng.next() % 10 != 0 for _ in range(n)], np.uint8)
+    px, py = (k["x"] + 7).astype(np.float32), (k["y"] + 4).astype(np.float32)
+    pxr = (px - 3).astype(np.float32)
+    level = np.clip(k["octave"] + np.array([rng.next() % 3 - 1 for _ in range(n)]), 0, 7).astype(np.int32)
+    vc = np.array([0.999 if rng.next() % 2 else 0.9 for _ in range(n)], np.float32)
+    claimed = (np.arange(g.N) % 13 == 0).astype(np.uint8)
+    obs = (np.arange(n) % 4 != 0).astype(np.uint8)
+    for th in (1.0, 3.0):
+        ng, ag = ORBmatcher(0.8).SearchByProjectionPoints(g, in_view, px, py, pxr, level, vc, scene["da"], th, claimed, obs)
+        nr, ar = ORBmatcher(0.8, backend=oracle.OracleBackend()).SearchByProjectionPoints(r, in_view, px, py, pxr, level, vc, scene["da"], th, claimed, obs)
+        assert nr > 100
+        assert ng == nr and np.array_equal(ag, ar)
+
+
+def test_search_windowed_keyframe_style(scene, oracle, gpu_lib):
+    """strict level filter + TH_LOW + every assignment blocks: SearchByProjection(KeyFrame,Scw,...) / Fuse loops."""
+    from ar_orbslam2_b200.tracking import ORB_SELECT_BEST, ORBmatcher
+    g, r = both(scene, oracle, "b")
+    k = scene["ka"]
+    x, y = (k["x"] + 7).astype(np.float32), (k["y"] + 4).astype(np.float32)
+    pred = k["octave"].astype(np.int32)
+    rad = (4.0 * scene["scale"][pred]).astype(np.float32)
+    kw = dict(select=ORB_SELECT_BEST, th_dist=50, strict_levels=True, check_orientation=False)
+    ng, ag = ORBmatcher(0.6).SearchWindowed(g, x, y, rad, pred - 1, pred, scene["da"], **kw)
+    nr, ar = ORBmatcher(0.6, backend=oracle.OracleBackend()).SearchWindowed(r, x, y, rad, pred - 1, pred, scene["da"], **kw)
+    assert nr > 100 and ng == nr and np.array_equal(ag, ar)
+
+
+@pytest.mark.parametrize("kfkf", [False, True])
+def test_search_by_bow(scene, oracle, gpu_lib, kfkf):
+    """Synthetic FeatureVectors: features are grouped into ~220 'vocabulary nodes' by image position, so that
+    matching features of A and B mostly share a node (the vocabulary file is not in the reference repo)."""
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    gk, rk = both(scene, oracle, "a")
+    gf, rf = both(scene, oracle, "b")
+
+    def groups(k, dx, dy):
+        node = ((k["y"] - dy) // 40).astype(np.int64) * 19 + ((k["x"] - dx) // 40).astype(np.int64)
+        order = np.argsort(node, kind="stable")
+        return node, order
+    na, oa = groups(scene["ka"], 0, 0)
+    nb, ob = groups(scene["kb"], 7, 4)
+    common = np.intersect1d(na, nb)
+    kf_off, f_off, kf_idx, f_idx = [0], [0], [], []
+    for c in common:
+        kf_idx += oa[na[oa] == c].tolist()
+        f_idx += ob[nb[ob] == c].tolist()
+        kf_off.append(len(kf_idx)); f_off.append(len(f_idx))
+    kv = (np.arange(gk.N) % 7 != 0).astype(np.uint8)
+    fv = (np.arange(gf.N) % 9 != 0).astype(np.uint8) if kfkf else None
+    args = (kf_off, kf_idx, f_off, f_idx, kv, fv, kfkf)
+    ng, mg = ORBmatcher(0.7, True).SearchByBoW(gk, gf, *args)
+    nr, mr = ORBmatcher(0.7, True, backend=oracle.OracleBackend()).SearchByBoW(rk, rf, *args)
+    assert nr > 100 and ng == nr and np.array_equal(mg, mr)
+
+
+def test_rot_hist_filter(oracle, gpu_lib):
+    from ar_orbslam2_b200.tracking import rot_hist_filter
+    rng = np.random.default_rng(3)
+    a = rng.uniform(0, 360, 3000).astype(np.float32)
+    b = (a + rng.choice([0, 0, 0, 31, 95, 200], 3000) + rng.normal(0, 4, 3000)).astype(np.float32) % np.float32(360)
+    assert np.array_equal(rot_hist_filter(a, b), oracle.rot_hist_filter(a, b))
+    # the reference's 1/30 factor: only bins 0..12 can ever be hit
+    assert np.array_equal(rot_hist_filter(a[:5], a[:5]), np.ones(5, bool))
