@@ -1,0 +1,170 @@
+// ORACLE -- TEST INFRASTRUCTURE ONLY.
+//
+// A minimal stand-in for the slice of OpenCV that ORB_SLAM2/src/ORBextractor.cc uses, so that the REFERENCE'S OWN
+// SOURCE FILE can be compiled unmodified into oracle/_ref/liborbslam_ref.so (see oracle/Makefile.ref).  The reference
+// needs OpenCV 2.4 C++ (not installed, not vendored); this header supplies cv::Mat / KeyPoint / InputArray plumbing,
+// and the arithmetic primitives (resize, copyMakeBorder, GaussianBlur, FAST, fastAtan2, cvRound) are the models of
+// oracle/orbref_cv.h, which are pinned against cv2 4.13.0 by tests/golden/.  What this buys: the reference's control
+// flow -- cell loop, threshold retry, DistributeOctTree with its std::list bookkeeping, orientation, descriptor,
+// level scaling -- runs from the reference's own code, and tests compare the restated oracle against it.
+#pragma once
+#include "../orbref_cv.h"
+
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <iterator>
+#include <list>
+#include <memory>
+#include <vector>
+
+typedef unsigned char uchar;
+#define CV_PI 3.1415926535897932384626433832795
+#define CV_8U 0
+#define CV_8UC1 0
+#define CV_32F 5
+
+static inline int cvRound(double v) { return orbref::cv_round(v); }
+static inline int cvFloor(double v) { return orbref::cv_floor(v); }
+static inline int cvCeil(double v) { return orbref::cv_ceil(v); }
+
+namespace cv {
+
+enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16, INTER_LINEAR = 1 };
+
+template <typename T> struct Point_ {
+    T x, y;
+    Point_() : x(0), y(0) {}
+    Point_(T _x, T _y) : x(_x), y(_y) {}
+};
+typedef Point_<int> Point2i;
+typedef Point2i Point;
+typedef Point_<float> Point2f;
+static inline Point2f &operator*=(Point2f &a, float b) { a.x = a.x * b; a.y = a.y * b; return a; }
+
+struct Size { int width, height; Size() : width(0), height(0) {} Size(int w, int h) : width(w), height(h) {} };
+struct Rect { int x, y, width, height; Rect(int _x, int _y, int w, int h) : x(_x), y(_y), width(w), height(h) {} };
+
+struct KeyPoint {
+    Point2f pt;
+    float size, angle, response;
+    int octave, class_id;
+    KeyPoint() : size(0), angle(-1), response(0), octave(0), class_id(-1) {}
+    KeyPoint(float x, float y, float _size, float _angle = -1, float _response = 0, int _octave = 0, int _class_id = -1)
+        : pt(x, y), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
+};
+
+struct MatZeros { int rows, cols, type; };
+
+class Mat {
+public:
+    struct Step {
+        size_t v;
+        operator size_t() const { return v; }
+    };
+    int rows, cols;
+    uchar *data;
+    Step step;
+    std::shared_ptr<std::vector<uchar>> buf;
+
+    Mat() : rows(0), cols(0), data(nullptr), step{0} {}
+    Mat(Size sz, int) { alloc(sz.height, sz.width); }
+    Mat(int r, int c, int) { alloc(r, c); }
+    void alloc(int r, int c) {
+        rows = r; cols = c;
+        buf = std::make_shared<std::vector<uchar>>((size_t)r * c);
+        data = buf->data();
+        step.v = (size_t)c;
+    }
+    void create(int r, int c, int) { if (r != rows || c != cols || !data) alloc(r, c); }
+    void release() { rows = cols = 0; data = nullptr; buf.reset(); step.v = 0; }
+    bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    int type() const { return CV_8UC1; }
+    size_t step1() const { return step.v; }
+    Mat operator()(const Rect &r) const { Mat m = *this; m.data = data + (size_t)r.y * step.v + r.x; m.rows = r.height; m.cols = r.width; return m; }
+    Mat rowRange(int a, int b) const { Mat m = *this; m.data = data + (size_t)a * step.v; m.rows = b - a; return m; }
+    Mat colRange(int a, int b) const { Mat m = *this; m.data = data + a; m.cols = b - a; return m; }
+    template <typename T> T &at(int y, int x) { return *(T *)(data + (size_t)y * step.v + x * sizeof(T)); }
+    template <typename T> const T &at(int y, int x) const { return *(const T *)(data + (size_t)y * step.v + x * sizeof(T)); }
+    uchar *ptr(int y = 0) { return data + (size_t)y * step.v; }
+    const uchar *ptr(int y = 0) const { return data + (size_t)y * step.v; }
+    template <typename T> T *ptr(int y = 0) { return (T *)(data + (size_t)y * step.v); }
+    Mat clone() const {
+        Mat m(rows, cols, 0);
+        for (int y = 0; y < rows; y++) std::memcpy(m.ptr(y), ptr(y), cols);
+        return m;
+    }
+    static MatZeros zeros(int r, int c, int t) { return MatZeros{r, c, t}; }
+    // Mat = MatExpr(zeros): keeps the existing buffer when size and type match (cv::Mat::create semantics), which is
+    // how ORBextractor.cc:978 zero-fills a row range of the output descriptor matrix in place.
+    Mat &operator=(const MatZeros &z) {
+        create(z.rows, z.cols, z.type);
+        for (int y = 0; y < rows; y++) std::memset(ptr(y), 0, cols);
+        return *this;
+    }
+};
+
+class _InputArray {
+public:
+    const Mat *m;
+    Mat tmp;
+    _InputArray(const Mat &mat) : m(&mat) {}
+    bool empty() const { return m->empty(); }
+    Mat getMat() const { return *m; }
+};
+class _OutputArray {
+public:
+    Mat *m;
+    _OutputArray(Mat &mat) : m(&mat) {}
+    void create(int r, int c, int t) const { m->create(r, c, t); }
+    void create(Size sz, int t) const { m->create(sz.height, sz.width, t); }
+    void release() const { m->release(); }
+    Mat getMat() const { return *m; }
+};
+typedef const _InputArray &InputArray;
+typedef const _OutputArray &OutputArray;
+
+static inline float fastAtan2(float y, float x) { return orbref::fast_atan2(y, x); }
+
+static inline void FAST(InputArray image, std::vector<KeyPoint> &keypoints, int threshold, bool nonmaxSuppression = true) {
+    (void)nonmaxSuppression;
+    Mat m = image.getMat();
+    std::vector<orbref::FastPoint> pts;
+    orbref::fast9_16_nms(m.data, m.cols, m.rows, (int)m.step.v, threshold, pts);
+    keypoints.clear();
+    for (const orbref::FastPoint &p : pts) keypoints.push_back(KeyPoint((float)p.x, (float)p.y, 7.f, -1.f, (float)p.response));
+}
+
+static inline void resize(InputArray src, OutputArray dst, Size dsize, double = 0, double = 0, int = INTER_LINEAR) {
+    Mat s = src.getMat();
+    dst.create(dsize, s.type());
+    Mat d = dst.getMat();
+    orbref::resize_linear_u8(s.data, s.cols, s.rows, (int)s.step.v, d.data, d.cols, d.rows, (int)d.step.v);
+}
+
+static inline void copyMakeBorder(InputArray src, OutputArray dst, int top, int bottom, int left, int right, int) {
+    Mat s = src.getMat();
+    dst.create(s.rows + top + bottom, s.cols + left + right, s.type());
+    Mat d = dst.getMat();
+    // interior first (a no-op when src already is the interior of dst), then the reflected frame
+    for (int y = 0; y < s.rows; y++)
+        if (d.ptr(y + top) + left != s.ptr(y)) std::memmove(d.ptr(y + top) + left, s.ptr(y), s.cols);
+    assert(top == bottom && left == right && top == left);
+    orbref::make_border_reflect101(d.ptr(top) + left, s.cols, s.rows, (int)d.step.v, top);
+}
+
+static inline void GaussianBlur(InputArray src, OutputArray dst, Size ksize, double sigmaX, double sigmaY = 0, int = BORDER_REFLECT_101) {
+    assert(ksize.width == 7 && ksize.height == 7 && sigmaX == 2 && sigmaY == 2);
+    Mat s = src.getMat().clone();
+    dst.create(s.rows, s.cols, s.type());
+    Mat d = dst.getMat();
+    orbref::gaussian_blur7_u8(s.data, s.cols, s.rows, (int)s.step.v, d.data, (int)d.step.v, 0);
+}
+
+struct KeyPointsFilter {   // only referenced by the dead ComputeKeyPointsOld (ORBextractor.cc:821-974)
+    static void retainBest(std::vector<KeyPoint> &, int) { std::abort(); }
+};
+
+}  // namespace cv

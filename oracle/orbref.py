@@ -197,3 +197,56 @@ class OracleBackend:
 
     def check(self, rc, what):
         _check(rc, what)
+
+
+# ---- oracle/_ref: the reference's own ORBextractor.cc compiled against the stub OpenCV (oracle/Makefile.ref) ----
+_REF = None
+REF_LIB_PATH = os.path.join(_HERE, "_ref", "liborbslam_ref.so")
+
+
+def ref_available() -> bool:
+    if os.path.exists(REF_LIB_PATH):
+        return True
+    if os.path.isdir("/root/reference/ORB_SLAM2/src"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-f", "Makefile.ref"])
+        return True
+    return False
+
+
+def ref_lib():
+    global _REF
+    if _REF is None:
+        _REF = C.CDLL(REF_LIB_PATH)
+    return _REF
+
+
+class ReferenceExtractor:
+    """ORB_SLAM2::ORBextractor from the reference's own source (control flow verbatim), OpenCV primitives = the
+    cv2-pinned models, monotonic allocator so its pointer tie-break equals creation order."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.h = C.c_void_p()
+        ref_lib().ref_extractor_create(nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th, C.byref(self.h))
+        self.cap = nfeatures + 64 * nlevels + 4096
+        self.nlevels = nlevels
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            ref_lib().ref_extractor_destroy(self.h)
+            self.h = None
+
+    def extract(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        kps = np.zeros(self.cap, KEYPOINT_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int()
+        _check(ref_lib().ref_extract(self.h, ptr(img), img.shape[1], img.shape[0], img.strides[0], ptr(kps), ptr(desc), self.cap,
+                                     C.byref(n)), "ref_extract")
+        return kps[: n.value].copy(), desc[: n.value].copy()
+
+    def pyramid_level(self, level):
+        w, h = C.c_int(), C.c_int()
+        ref_lib().ref_pyramid_level(self.h, level, None, 0, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        ref_lib().ref_pyramid_level(self.h, level, ptr(out), w.value, C.byref(w), C.byref(h))
+        return out

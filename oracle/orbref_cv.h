@@ -10,6 +10,7 @@
 // function as ORB_SLAM2/src/<file>:<line>.
 #pragma once
 #include <cmath>
+#include <cstddef>
 #include <cstdint>
 #include <emmintrin.h>
 #include <cstring>
@@ -84,17 +85,17 @@ static inline void resize_linear_u8(const uint8_t *src, int sw, int sh, int spit
 // the padded plane.  ref: ORBextractor.cc:1063-1068.  `interior` points at pixel (0,0).
 static inline void make_border_reflect101(uint8_t *interior, int w, int h, int pitch, int border) {
     for (int y = 0; y < h; y++) {
-        uint8_t *row = interior + (ptrdiff_t)y * pitch;
+        uint8_t *row = interior + (std::ptrdiff_t)y * pitch;
         for (int x = 1; x <= border; x++) {
             row[-x] = row[reflect101(-x, w)];
             row[w - 1 + x] = row[reflect101(w - 1 + x, w)];
         }
     }
     for (int y = 1; y <= border; y++) {
-        std::memcpy(interior + (ptrdiff_t)(-y) * pitch - border,
-                    interior + (ptrdiff_t)reflect101(-y, h) * pitch - border, w + 2 * border);
-        std::memcpy(interior + (ptrdiff_t)(h - 1 + y) * pitch - border,
-                    interior + (ptrdiff_t)reflect101(h - 1 + y, h) * pitch - border, w + 2 * border);
+        std::memcpy(interior + (std::ptrdiff_t)(-y) * pitch - border,
+                    interior + (std::ptrdiff_t)reflect101(-y, h) * pitch - border, w + 2 * border);
+        std::memcpy(interior + (std::ptrdiff_t)(h - 1 + y) * pitch - border,
+                    interior + (std::ptrdiff_t)reflect101(h - 1 + y, h) * pitch - border, w + 2 * border);
     }
 }
 

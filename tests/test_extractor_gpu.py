@@ -113,3 +113,17 @@ def test_flat_and_noise_images(oracle, gpu_lib):
     rk, rd = ref.extract(soft)
     assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
     ex.close()
+
+
+def test_gpu_equals_reference_source(oracle, gpu_lib):
+    """liborbgpu against oracle/_ref (the reference's own ORBextractor.cc, see tests/test_reference_cpu.py)."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref not built")
+    for (w, h, nf, seed) in [(640, 480, 1000, 40), (1241, 376, 2000, 41)]:
+        img = synth_frame(w, h, seed)
+        ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+        gk, gd = ex(img)
+        rk, rd = oracle.ReferenceExtractor(nf).extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+        ex.close()
