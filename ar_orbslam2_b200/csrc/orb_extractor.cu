@@ -30,7 +30,9 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
-__constant__ int8_t c_pattern[ORB_PATTERN_INTS];
+// the 256 test pairs; lane l of a descriptor warp reads its own 32 bytes, so this lives in global memory
+// (per-lane addresses would serialise in the constant cache)
+__device__ __align__(16) int8_t d_pattern[ORB_PATTERN_INTS];
 __constant__ int c_umax[16];
 
 // ------------------------------------------------------------------------------------------
@@ -55,8 +57,12 @@ __global__ void k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_strid
     *reinterpret_cast<uint32_t *>(plane + (size_t)py * g.pitch + word * 4) = v;
 }
 
-__global__ void k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G,
-                             const ResizeTap *__restrict__ taps, int level) {
+__global__ void __launch_bounds__(128)
+k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps, int level) {
+    // cv::resize INTER_LINEAR straight into the padded plane (reflect-101 frame included).
+    // A thread makes 4 horizontally adjacent pixels.  Their source pixels span < 12 bytes, so each of the two
+    // source rows is fetched as three aligned words and the taps pick bytes out of registers (PRMT) instead of
+    // issuing 16 byte loads.
     const LevelGeom &g = G->lv[level];
     const LevelGeom &p = G->lv[level - 1];
     const int word = blockIdx.x * blockDim.x + threadIdx.x;
@@ -66,16 +72,44 @@ __global__ void k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__
     const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
     const uint8_t *s0 = frame + p.interior_off + (size_t)ty.s0 * p.pitch;
     const uint8_t *s1 = frame + p.interior_off + (size_t)ty.s1 * p.pitch;
-    uint32_t v = 0;
+    ResizeTap tx[4];
+    int lo = 1 << 30, hi_s0 = 0;
+    bool any = false;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const int x = word * 4 + k - XOFF;
-        if (x >= -EDGE && x < g.w + EDGE) {
-            const ResizeTap tx = taps[g.tap_x_off + reflect101(x, g.w)];
-            const int r0 = s0[tx.s0] * tx.a0 + s0[tx.s1] * tx.a1;
-            const int r1 = s1[tx.s0] * tx.a0 + s1[tx.s1] * tx.a1;
-            const int o = (((ty.a0 * (r0 >> 4)) >> 16) + ((ty.a1 * (r1 >> 4)) >> 16) + 2) >> 2;
-            v |= (uint32_t)o << (8 * k);
+        const bool in = x >= -EDGE && x < g.w + EDGE;
+        tx[k] = taps[g.tap_x_off + reflect101(in ? x : 0, g.w)];
+        if (!in) { tx[k].a0 = 0; tx[k].a1 = 0; }
+        else { lo = min(lo, (int)tx[k].s0); hi_s0 = max(hi_s0, (int)tx[k].s0); any = true; }
+    }
+    uint32_t v = 0;
+    const int base = lo & ~3;   // interior rows start 32-byte aligned, so base is a word boundary
+    if (any && hi_s0 - base > 7) {
+        // scale factors well above 1.2: the four pixels do not fit the 12-byte window, plain byte loads
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int r0v = s0[tx[k].s0] * tx[k].a0 + s0[tx[k].s1] * tx[k].a1;
+            const int r1v = s1[tx[k].s0] * tx[k].a0 + s1[tx[k].s1] * tx[k].a1;
+            const int o8 = (((ty.a0 * (r0v >> 4)) >> 16) + ((ty.a1 * (r1v >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)o8 << (8 * k);
+        }
+    } else if (any) {
+        const uint32_t *r0 = reinterpret_cast<const uint32_t *>(s0 + base), *r1 = reinterpret_cast<const uint32_t *>(s1 + base);
+        const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
+        const uint32_t c0 = __ldg(r1), c1 = __ldg(r1 + 1), c2 = __ldg(r1 + 2);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            // byte offsets of the two taps inside the 12-byte window (s1 == s0 only where its weight is 0)
+            const int o = (tx[k].a0 | tx[k].a1) ? tx[k].s0 - base : 0;
+            const bool hi = o >= 4;
+            const uint32_t ua = hi ? a1 : a0, ub = hi ? a2 : a1, uc = hi ? c1 : c0, ud = hi ? c2 : c1;
+            const uint32_t sel = (uint32_t)(o & 3) | ((uint32_t)((o & 3) + 1) << 4) | 0x4400u;   // bytes o, o+1
+            const uint32_t pa = __byte_perm(ua, ub, sel), pc = __byte_perm(uc, ud, sel);
+            const int r0v = (int)(pa & 0xff) * tx[k].a0 + (int)((pa >> 8) & 0xff) * tx[k].a1;
+            const int r1v = (int)(pc & 0xff) * tx[k].a0 + (int)((pc >> 8) & 0xff) * tx[k].a1;
+            const int o8 = (((ty.a0 * (r0v >> 4)) >> 16) + ((ty.a1 * (r1v >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)o8 << (8 * k);
         }
     }
     *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
@@ -84,51 +118,69 @@ __global__ void k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__
 // ------------------------------------------------------------------------------------------
 // FAST-9/16 per cell.  One CTA per (cell, frame).  V = arc strength: corner at t
 // <=> V > t, response V-1, 3x3 non-max suppression inside the cell's computed region only.
+//
+// Stages inside the CTA (all in shared memory):
+//   1. the cell's ROI is staged as aligned 32-bit words;
+//   2. every pixel takes the 4-compass test at the lower threshold: a 9-arc always holds two ADJACENT compass
+//      points, so a corner needs two adjacent compass pixels all brighter (type H) or all darker (type L);
+//      ~20% of pixels survive and are compacted with warp ballots;
+//   3. survivors get the exact arc strength on dense warps.  An H survivor can only be a brighter-arc corner,
+//      so one min/max network over sign*d gives its V; the rare pixels that pass both tests are re-evaluated
+//      with the other sign from a second list;
+//   4. threshold + NMS (+ the 20 -> 7 retry when the cell is empty), candidates appended to the level's list.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
 
-__device__ __forceinline__ int fast_arc_strength(const uint8_t *p, int pitch) {
-    const int c = p[0];
+constexpr int FT_PW = 19;                 // tile row pitch in words (76 bytes >= 72 + 3 bytes of alignment slack)
+constexpr int FT_PB = FT_PW * 4;
+constexpr int FV_PB = 72;                 // vmap row pitch in bytes (computed width <= 66, + 2 apron)
+
+struct FastDiv {   // exact n / d for n < 2^32 / d via one multiply-high
+    uint32_t M;
+    int d;
+    __device__ __forceinline__ FastDiv(int dd) : M(dd > 1 ? 0xFFFFFFFFu / (uint32_t)dd + 1u : 0u), d(dd) {}
+    __device__ __forceinline__ int div(int n) const { return d > 1 ? (int)__umulhi((uint32_t)n, M) : n; }
+};
+
+// max over the 16 arcs of 9 consecutive circle pixels of min(sgn * (I(p) - I(q)))
+__device__ __forceinline__ int fast_arc_min(const uint8_t *p, int sgn) {
+    const int cs = sgn * (int)p[0], ns = -sgn;
     int d[16];
-    d[0] = c - p[3 * pitch];
-    d[1] = c - p[3 * pitch + 1];
-    d[2] = c - p[2 * pitch + 2];
-    d[3] = c - p[pitch + 3];
-    d[4] = c - p[3];
-    d[5] = c - p[-pitch + 3];
-    d[6] = c - p[-2 * pitch + 2];
-    d[7] = c - p[-3 * pitch + 1];
-    d[8] = c - p[-3 * pitch];
-    d[9] = c - p[-3 * pitch - 1];
-    d[10] = c - p[-2 * pitch - 2];
-    d[11] = c - p[-pitch - 3];
-    d[12] = c - p[-3];
-    d[13] = c - p[pitch - 3];
-    d[14] = c - p[2 * pitch - 2];
-    d[15] = c - p[3 * pitch - 1];
-    int mn3[16], mx3[16];
+    d[0] = cs + ns * p[3 * FT_PB];
+    d[1] = cs + ns * p[3 * FT_PB + 1];
+    d[2] = cs + ns * p[2 * FT_PB + 2];
+    d[3] = cs + ns * p[FT_PB + 3];
+    d[4] = cs + ns * p[3];
+    d[5] = cs + ns * p[-FT_PB + 3];
+    d[6] = cs + ns * p[-2 * FT_PB + 2];
+    d[7] = cs + ns * p[-3 * FT_PB + 1];
+    d[8] = cs + ns * p[-3 * FT_PB];
+    d[9] = cs + ns * p[-3 * FT_PB - 1];
+    d[10] = cs + ns * p[-2 * FT_PB - 2];
+    d[11] = cs + ns * p[-FT_PB - 3];
+    d[12] = cs + ns * p[-3];
+    d[13] = cs + ns * p[FT_PB - 3];
+    d[14] = cs + ns * p[2 * FT_PB - 2];
+    d[15] = cs + ns * p[3 * FT_PB - 1];
+    int m3[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        mn3[k] = min3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        mx3[k] = max3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-    }
-    int a = -256, bneg = 256;
+    for (int k = 0; k < 16; k++) m3[k] = min3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    int a = -256;
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        a = max(a, min3(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]));
-        bneg = min(bneg, max3(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]));
-    }
-    return max(a, -bneg);
+    for (int k = 0; k < 16; k += 2)
+        a = max3(a, min3(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]), min3(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]));
+    return a;
 }
 
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32_t *__restrict__ cand,
              uint32_t *__restrict__ cand_count, int *__restrict__ err) {
-    __shared__ uint8_t tile[FAST_TILE_MAX * FAST_TILE_MAX];
-    __shared__ uint8_t vmap[(FAST_TILE_MAX - 4) * (FAST_TILE_MAX - 4)];   // computed region + 1 px apron
+    __shared__ uint32_t tileW[FAST_TILE_MAX * FT_PW];
+    __shared__ uint32_t vmapW[(FAST_TILE_MAX - 4) * FV_PB / 4];   // computed region + 1 px apron
     __shared__ uint16_t surv[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
-    __shared__ int s_nsurv, s_nkp, s_base;
+    __shared__ uint16_t surv2[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
+    __shared__ int s_nsurv, s_n2, s_nkp, s_base;
 
     const int b = blockIdx.y;
     int level = 0;
@@ -142,58 +194,93 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32
     const int maxX = min(iniX + g.wCell + 6, g.maxBX), maxY = min(iniY + g.hCell + 6, g.maxBY);
     const int tw = maxX - iniX, th = maxY - iniY;      // ROI size
     const int cw = tw - 6, ch = th - 6;                // computed region (ROI minus 3 px rim)
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
 
-    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
-    for (int i = tid; i < tw * th; i += FAST_THREADS) {
-        const int y = i / tw, x = i - y * tw;
-        tile[y * FAST_TILE_MAX + x] = img[(size_t)(iniY + y) * g.pitch + iniX + x];
+    // ---- 1. stage the ROI; byte (y, x) of the ROI sits at tile[y * FT_PB + x + sft]
+    const int sft = (iniX + XOFF) & 3;
+    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
+    {
+        const int nW = (tw + sft + 3) >> 2;
+        const FastDiv dW(nW);
+        for (int t = tid; t < th * nW; t += FAST_THREADS) {
+            const int y = dW.div(t), w = t - y * nW;
+            tileW[y * FT_PW + w] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * g.pitch) + w);
+        }
+        for (int t = tid; t < (ch + 2) * (FV_PB / 4); t += FAST_THREADS) vmapW[t] = 0;
     }
-    const int vw = cw + 2;
-    for (int i = tid; i < vw * (ch + 2); i += FAST_THREADS) vmap[i] = 0;
-    if (tid == 0) { s_nsurv = 0; s_nkp = 0; }
+    if (tid == 0) { s_nsurv = 0; s_n2 = 0; s_nkp = 0; }
     __syncthreads();
     if (cw <= 0 || ch <= 0) return;
+    const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW) + sft;
+    uint8_t *vmap = reinterpret_cast<uint8_t *>(vmapW);
+    const FastDiv dC(cw);
+    const int npx = cw * ch;
 
-    // pass 1: the 4-compass quick test at the lower threshold; survivors are compacted so the
-    // full 16-pixel evaluation runs on dense warps.
+    // ---- 2. compass test at the lower threshold, ballot-compacted
     const int tq = min(G->ini_th, G->min_th);
-    for (int i = tid; i < cw * ch; i += FAST_THREADS) {
-        const int y = i / cw, x = i - y * cw;
-        const uint8_t *p = &tile[(y + 3) * FAST_TILE_MAX + x + 3];
-        const int c = p[0];
-        const int d0 = c - p[3 * FAST_TILE_MAX], d4 = c - p[3], d8 = c - p[-3 * FAST_TILE_MAX], d12 = c - p[-3];
-        // any 9-arc holds two adjacent compass points
-        const int hi = (d0 > tq) + (d4 > tq) + (d8 > tq) + (d12 > tq);
-        const int lo = (d0 < -tq) + (d4 < -tq) + (d8 < -tq) + (d12 < -tq);
-        if (hi >= 2 || lo >= 2) surv[atomicAdd(&s_nsurv, 1)] = (uint16_t)i;
-    }
-    __syncthreads();
-    const int nsurv = s_nsurv;
-    for (int s = tid; s < nsurv; s += FAST_THREADS) {
-        const int i = surv[s];
-        const int y = i / cw, x = i - y * cw;
-        const int V = fast_arc_strength(&tile[(y + 3) * FAST_TILE_MAX + x + 3], FAST_TILE_MAX);
-        vmap[(y + 1) * vw + x + 1] = (uint8_t)max(V, 0);
+    for (int i0 = 0; i0 < npx; i0 += FAST_THREADS) {
+        const int i = i0 + tid;
+        bool H = false, L = false;
+        if (i < npx) {
+            const int y = dC.div(i), x = i - y * cw;
+            const uint8_t *p = tile + (y + 3) * FT_PB + x + 3;
+            const int c = p[0];
+            const int d0 = c - p[3 * FT_PB], d4 = c - p[3], d8 = c - p[-3 * FT_PB], d12 = c - p[-3];
+            const bool h0 = d0 > tq, h4 = d4 > tq, h8 = d8 > tq, h12 = d12 > tq;
+            const bool l0 = d0 < -tq, l4 = d4 < -tq, l8 = d8 < -tq, l12 = d12 < -tq;
+            H = (h0 && h4) || (h4 && h8) || (h8 && h12) || (h12 && h0);
+            L = (l0 && l4) || (l4 && l8) || (l8 && l12) || (l12 && l0);
+        }
+        const unsigned m1 = __ballot_sync(0xffffffffu, H || L), m2 = __ballot_sync(0xffffffffu, H && L);
+        int base1 = 0, base2 = 0;
+        if (lane == 0) {
+            if (m1) base1 = atomicAdd(&s_nsurv, __popc(m1));
+            if (m2) base2 = atomicAdd(&s_n2, __popc(m2));
+        }
+        base1 = __shfl_sync(0xffffffffu, base1, 0);
+        base2 = __shfl_sync(0xffffffffu, base2, 0);
+        const unsigned lt = (1u << lane) - 1;
+        if (H || L) surv[base1 + __popc(m1 & lt)] = (uint16_t)(i | (H ? 0 : 0x2000));   // bit 13: evaluate as darker type
+        if (H && L) surv2[base2 + __popc(m2 & lt)] = (uint16_t)i;
     }
     __syncthreads();
 
-    // pass 2: NMS + threshold, retry at min_th if the cell is empty (ref :780-784)
+    // ---- 3. exact arc strength of the survivors
+    const int nsurv = s_nsurv, n2 = s_n2;
+    for (int s = tid; s < nsurv; s += FAST_THREADS) {
+        const int code = surv[s], i = code & 0x1fff;
+        const int y = dC.div(i), x = i - y * cw;
+        const int V = fast_arc_min(tile + (y + 3) * FT_PB + x + 3, (code & 0x2000) ? -1 : 1);
+        vmap[(y + 1) * FV_PB + x + 1] = (uint8_t)max(V, 0);
+    }
+    if (n2) {
+        __syncthreads();
+        for (int s = tid; s < n2; s += FAST_THREADS) {   // pixels that passed both compass tests: the darker side
+            const int i = surv2[s];
+            const int y = dC.div(i), x = i - y * cw;
+            const int V = fast_arc_min(tile + (y + 3) * FT_PB + x + 3, -1);
+            uint8_t *v = &vmap[(y + 1) * FV_PB + x + 1];
+            *v = (uint8_t)max((int)*v, V);
+        }
+    }
+    __syncthreads();
+
+    // ---- 4. NMS + threshold, retry at min_th if the cell is empty (ref :780-784)
     int thr = G->ini_th;
     for (int attempt = 0; attempt < 2; attempt++) {
+        int mine = 0;
         for (int s = tid; s < nsurv; s += FAST_THREADS) {
-            const int i = surv[s];
-            const int y = i / cw, x = i - y * cw;
-            const uint8_t *v = &vmap[(y + 1) * vw + x + 1];
+            const int i = surv[s] & 0x1fff;
+            const int y = dC.div(i), x = i - y * cw;
+            const uint8_t *v = &vmap[(y + 1) * FV_PB + x + 1];
             const int V = v[0];
-            if (V > thr && V > v[-1] && V > v[1] && V > v[-vw - 1] && V > v[-vw] && V > v[-vw + 1] &&
-                V > v[vw - 1] && V > v[vw] && V > v[vw + 1]) {
-                const int k = atomicAdd(&s_nkp, 1);
-                // reuse the tile as the output staging area is not possible (still needed); pack now
-                surv[s] = (uint16_t)(i | 0x8000);
-                (void)k;
+            if (V > thr && V > v[-1] && V > v[1] && V > v[-FV_PB - 1] && V > v[-FV_PB] && V > v[-FV_PB + 1] &&
+                V > v[FV_PB - 1] && V > v[FV_PB] && V > v[FV_PB + 1]) {
+                surv[s] = (uint16_t)(surv[s] | 0x8000);
+                mine++;
             }
         }
+        if (mine) atomicAdd(&s_nkp, mine);
         __syncthreads();
         if (s_nkp > 0 || attempt == 1 || G->min_th == thr) break;
         thr = G->min_th;
@@ -207,11 +294,11 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32
     __syncthreads();
     uint32_t *out = cand + (size_t)b * G->cand_frame + g.cand_off;
     for (int s = tid; s < nsurv; s += FAST_THREADS) {
-        const int i = surv[s];
-        if (!(i & 0x8000)) continue;
-        const int ii = i & 0x7fff;
-        const int y = ii / cw, x = ii - y * cw;
-        const int V = vmap[(y + 1) * vw + x + 1];
+        const int code = surv[s];
+        if (!(code & 0x8000)) continue;
+        const int ii = code & 0x1fff;
+        const int y = dC.div(ii), x = ii - y * cw;
+        const int V = vmap[(y + 1) * FV_PB + x + 1];
         const int slot = s_base + atomicAdd(&s_nkp, 1);
         if (slot < g.cand_cap) {
             // window-relative coordinates (ref :789-790): ROI x + j*wCell
@@ -560,7 +647,8 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 // 7x7 Gaussian is applied separably to the 37x37 patch the 256 rotated test pairs can reach.
 // ------------------------------------------------------------------------------------------
 constexpr int PW = 43;            // patch width (+-21)
-constexpr int PP = 44;            // patch pitch
+constexpr int PPW = 13;           // patch row pitch in 32-bit words (odd: conflict-free row-per-lane access)
+constexpr int HPW = 21;           // horizontal-pass row pitch in words (42 x u16)
 constexpr int BW = 37;            // blurred patch (+-18)
 constexpr int BP = 40;
 
@@ -632,8 +720,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Kept *__restrict__ kept,
            const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp, uint8_t *__restrict__ out_desc,
            int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
-    __shared__ uint8_t s_patch[DESC_WARPS][PW * PP];    // raw window; reused for the blurred patch
-    __shared__ uint16_t s_h[DESC_WARPS][PW * BP];
+    __shared__ uint32_t s_patch[DESC_WARPS][PW * PPW];   // raw window (word rows); reused for the blurred patch
+    __shared__ uint32_t s_h[DESC_WARPS][PW * HPW];       // horizontal pass, two 16-bit sums per word
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.y;
@@ -659,23 +747,28 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
     const Kept kp = kept[(size_t)b * G->kept_frame + g.kept_off + slot];
     const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
 
-    uint8_t *P = s_patch[warp];
-    const uint8_t *src = img + (ptrdiff_t)(kp.y - 21) * g.pitch + (kp.x - 21);
-    for (int i = lane; i < PW * PW; i += 32) {
-        const int y = i / PW, x = i - y * PW;
-        P[y * PP + x] = src[(ptrdiff_t)y * g.pitch + x];
+    // ---- stage the 43x43 window.  Rows are copied as aligned 32-bit words (plane rows are 128-byte pitched and
+    // the interior starts at byte 32), so the window starts `sft` bytes into each shared-memory row.
+    uint32_t *PWd = s_patch[warp];
+    const int x0 = kp.x - 21;
+    const int sft = (x0 + XOFF) & 3;
+    const uint8_t *src = img + (ptrdiff_t)(kp.y - 21) * g.pitch + (x0 - sft);
+    for (int t = lane; t < PW * 12; t += 32) {
+        const int y = t / 12, w = t - y * 12;
+        PWd[y * PPW + w] = __ldg(reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)y * g.pitch) + w);
     }
     __syncwarp();
+    const uint8_t *P = reinterpret_cast<const uint8_t *>(PWd);
 
     // ---- IC_Angle (ref :73-98): lanes own columns u = lane-15 .. of the 31-wide disc
     int m10 = 0, m01 = 0;
     if (lane < 31) {
         const int u = lane - 15, au = abs(u);
-        const uint8_t *c = P + 21 * PP + 21 + u;
+        const uint8_t *c = P + 21 * (PPW * 4) + 21 + sft + u;
         m10 = u * c[0];
         for (int v = 1; v <= 15; v++) {
             if (au <= c_umax[v]) {
-                const int vp = c[v * PP], vm = c[-v * PP];
+                const int vp = c[v * (PPW * 4)], vm = c[-v * (PPW * 4)];
                 m10 += u * (vp + vm);
                 m01 += v * (vp - vm);
             }
@@ -688,21 +781,45 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
     }
     const float angle = dev_fast_atan2((float)m01, (float)m10);
 
-    // ---- 7x7 Gaussian, sigma 2: H = sum k*src (16 bit), out = (sum k*H + 32768) >> 16
+    // ---- 7x7 Gaussian, sigma 2: H = sum k*src (16 bit), out = (sum k*H + 32768) >> 16.
+    // Horizontal pass: a lane takes half a row (20 outputs) into registers and slides the 7-tap window there;
+    // vertical pass: a lane walks one column with a 7-deep register window.  ~100 shared loads per lane in total.
     const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
-    uint16_t *H = s_h[warp];
-    for (int i = lane; i < PW * BW; i += 32) {
-        const int y = i / BW, x = i - y * BW;
-        const uint8_t *r = P + y * PP + x;   // covers patch columns x .. x+6
-        H[y * BP + x] = (uint16_t)(k0 * (r[0] + r[6]) + k1 * (r[1] + r[5]) + k2 * (r[2] + r[4]) + k3 * r[3]);
+    uint32_t *HW = s_h[warp];
+    for (int t = lane; t < PW * 2; t += 32) {
+        const int y = t >> 1, half = t & 1;
+        const int b0 = sft + 20 * half, wi = b0 >> 2, sh = (b0 & 3) * 8;
+        const uint32_t *row = PWd + y * PPW + wi;
+        uint32_t w[8], a[7];
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] = row[k];
+#pragma unroll
+        for (int k = 0; k < 7; k++) a[k] = __funnelshift_r(w[k], w[k + 1], sh);
+        int bt[26];
+#pragma unroll
+        for (int i = 0; i < 26; i++) bt[i] = (a[i >> 2] >> (8 * (i & 3))) & 0xff;
+        uint32_t *hrow = HW + y * HPW + 10 * half;
+#pragma unroll
+        for (int j = 0; j < 10; j++) {
+            const int xa = 2 * j, xb = 2 * j + 1;
+            const int ha = k0 * (bt[xa] + bt[xa + 6]) + k1 * (bt[xa + 1] + bt[xa + 5]) + k2 * (bt[xa + 2] + bt[xa + 4]) + k3 * bt[xa + 3];
+            const int hb = k0 * (bt[xb] + bt[xb + 6]) + k1 * (bt[xb + 1] + bt[xb + 5]) + k2 * (bt[xb + 2] + bt[xb + 4]) + k3 * bt[xb + 3];
+            hrow[j] = (uint32_t)ha | ((uint32_t)hb << 16);
+        }
     }
     __syncwarp();
-    uint8_t *Bl = P;   // the raw window is dead once H is built (BW*BP <= PW*PP)
-    for (int i = lane; i < BW * BW; i += 32) {
-        const int y = i / BW, x = i - y * BW;
-        const uint16_t *r = H + y * BP + x;
-        const int v = k0 * (r[0] + r[6 * BP]) + k1 * (r[BP] + r[5 * BP]) + k2 * (r[2 * BP] + r[4 * BP]) + k3 * r[3 * BP];
-        Bl[y * BP + x] = (uint8_t)min((v + 32768) >> 16, 255);
+    uint8_t *Bl = reinterpret_cast<uint8_t *>(PWd);   // the raw window is dead once H is built (BW*BP <= PW*PPW*4)
+    const uint16_t *H = reinterpret_cast<const uint16_t *>(HW);
+    for (int x = lane; x < BW; x += 32) {
+        int h0 = H[x], h1 = H[(HPW * 2) + x], h2 = H[2 * (HPW * 2) + x], h3 = H[3 * (HPW * 2) + x], h4 = H[4 * (HPW * 2) + x],
+            h5 = H[5 * (HPW * 2) + x];
+#pragma unroll 4
+        for (int y = 0; y < BW; y++) {
+            const int h6 = H[(y + 6) * (HPW * 2) + x];
+            const int v = k0 * (h0 + h6) + k1 * (h1 + h5) + k2 * (h2 + h4) + k3 * h3;
+            Bl[y * BP + x] = (uint8_t)min((v + 32768) >> 16, 255);
+            h0 = h1; h1 = h2; h2 = h3; h3 = h4; h4 = h5; h5 = h6;
+        }
     }
     __syncwarp();
 
@@ -711,11 +828,17 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);   // ref :100
     dev_sincosf(__fmul_rn(angle, factorPI), &sn, &cs);
     const uint8_t *ctr = Bl + 18 * BP + 18;
-    const int8_t *pat = c_pattern + lane * 32;
+    uint32_t pw[8];   // this lane's 8 test pairs: 32 signed bytes (x0,y0,x1,y1) x 8
+    {
+        const uint4 *pp = reinterpret_cast<const uint4 *>(d_pattern + lane * 32);
+        const uint4 pa = __ldg(pp), pb = __ldg(pp + 1);
+        pw[0] = pa.x; pw[1] = pa.y; pw[2] = pa.z; pw[3] = pa.w; pw[4] = pb.x; pw[5] = pb.y; pw[6] = pb.z; pw[7] = pb.w;
+    }
     uint32_t val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const float x0 = (float)pat[4 * k], y0 = (float)pat[4 * k + 1], x1 = (float)pat[4 * k + 2], y1 = (float)pat[4 * k + 3];
+        const float x0 = (float)(int8_t)(pw[k] & 0xff), y0 = (float)(int8_t)((pw[k] >> 8) & 0xff);
+        const float x1 = (float)(int8_t)((pw[k] >> 16) & 0xff), y1 = (float)(int8_t)(pw[k] >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sn), __fmul_rn(y0, cs)));
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, cs), __fmul_rn(y0, sn)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sn), __fmul_rn(y1, cs)));
@@ -918,7 +1041,7 @@ static int upload_constants_once() {
     static const int pat[ORB_PATTERN_INTS] = {ORB_PATTERN_VALUES};
     int8_t p8[ORB_PATTERN_INTS];
     for (int i = 0; i < ORB_PATTERN_INTS; i++) p8[i] = (int8_t)pat[i];
-    ORB_CUDA_TRY(cudaMemcpyToSymbol(c_pattern, p8, sizeof(p8)));
+    ORB_CUDA_TRY(cudaMemcpyToSymbol(d_pattern, p8, sizeof(p8)));
     done_devices.push_back(dev);
     return ORB_OK;
 }
