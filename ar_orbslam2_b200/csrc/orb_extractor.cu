@@ -139,7 +139,7 @@ constexpr int FV_PB = 72;                 // vmap row pitch in bytes (computed w
 struct FastDiv {   // exact n / d for n < 2^32 / d via one multiply-high
     uint32_t M;
     int d;
-    __device__ __forceinline__ FastDiv(int dd) : M(dd > 1 ? 0xFFFFFFFFu / (uint32_t)dd + 1u : 0u), d(dd) {}
+    __device__ __forceinline__ FastDiv(int dd, uint32_t magic) : M(magic), d(dd) {}   // magic = 0xFFFFFFFF / d + 1
     __device__ __forceinline__ int div(int n) const { return d > 1 ? (int)__umulhi((uint32_t)n, M) : n; }
 };
 
@@ -174,20 +174,20 @@ __device__ __forceinline__ int fast_arc_min(const uint8_t *p, int sgn) {
 }
 
 __global__ void __launch_bounds__(FAST_THREADS)
-k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32_t *__restrict__ cand,
-             uint32_t *__restrict__ cand_count, int *__restrict__ err) {
+k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const uint32_t *__restrict__ cells,
+             uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count, int *__restrict__ err) {
     __shared__ uint32_t tileW[FAST_TILE_MAX * FT_PW];
     __shared__ uint32_t vmapW[(FAST_TILE_MAX - 4) * FV_PB / 4];   // computed region + 1 px apron
     __shared__ uint16_t surv[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
     __shared__ uint16_t surv2[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
     __shared__ int s_nsurv, s_n2, s_nkp, s_base;
+    __shared__ uint32_t s_magic;
+    __shared__ int s_wsum[FAST_THREADS / 32];
 
     const int b = blockIdx.y;
-    int level = 0;
-    while (level + 1 < G->nlevels && (int)blockIdx.x >= G->lv[level + 1].cell_begin) level++;
+    const uint32_t cinfo = __ldg(cells + blockIdx.x);
+    const int level = cinfo & 15, ci = (cinfo >> 4) & 1023, cj = cinfo >> 14;
     const LevelGeom &g = G->lv[level];
-    const int cell = blockIdx.x - g.cell_begin;
-    const int ci = cell / g.ncx, cj = cell % g.ncx;
     const int minB = EDGE - 3;
     // ROI handed to cv::FAST by the reference (ref :759-773)
     const int iniX = minB + cj * g.wCell, iniY = minB + ci * g.hCell;
@@ -200,48 +200,65 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, uint32
     const int sft = (iniX + XOFF) & 3;
     const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
     {
-        const int nW = (tw + sft + 3) >> 2;
-        const FastDiv dW(nW);
-        for (int t = tid; t < th * nW; t += FAST_THREADS) {
-            const int y = dW.div(t), w = t - y * nW;
-            tileW[y * FT_PW + w] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * g.pitch) + w);
-        }
+        const int nW = (tw + sft + 3) >> 2;   // <= 19 words per row: a warp takes a row
+        if (lane < nW)
+            for (int y = tid >> 5; y < th; y += FAST_THREADS / 32)
+                tileW[y * FT_PW + lane] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * g.pitch) + lane);
         for (int t = tid; t < (ch + 2) * (FV_PB / 4); t += FAST_THREADS) vmapW[t] = 0;
     }
-    if (tid == 0) { s_nsurv = 0; s_n2 = 0; s_nkp = 0; }
+    if (tid == 0) { s_nsurv = 0; s_n2 = 0; s_nkp = 0; s_magic = cw > 1 ? 0xFFFFFFFFu / (uint32_t)cw + 1u : 0u; }
     __syncthreads();
     if (cw <= 0 || ch <= 0) return;
     const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW) + sft;
     uint8_t *vmap = reinterpret_cast<uint8_t *>(vmapW);
-    const FastDiv dC(cw);
+    const FastDiv dC(cw, s_magic);
     const int npx = cw * ch;
 
-    // ---- 2. compass test at the lower threshold, ballot-compacted
+    // ---- 2. compass test at the lower threshold.  Two circularly adjacent compass points beyond the threshold
+    // <=> one of {d0,d8} and one of {d4,d12}:  H = min(max(d0,d8), max(d4,d12)) > t,  L likewise with signs flipped.
+    // A thread keeps one result bit per pixel it owns and the survivors are compacted once per CTA.
     const int tq = min(G->ini_th, G->min_th);
-    for (int i0 = 0; i0 < npx; i0 += FAST_THREADS) {
-        const int i = i0 + tid;
-        bool H = false, L = false;
-        if (i < npx) {
+    unsigned bitsH = 0, bitsL = 0;
+    {
+        int k = 0;
+        for (int i = tid; i < npx; i += FAST_THREADS, k++) {
             const int y = dC.div(i), x = i - y * cw;
             const uint8_t *p = tile + (y + 3) * FT_PB + x + 3;
             const int c = p[0];
             const int d0 = c - p[3 * FT_PB], d4 = c - p[3], d8 = c - p[-3 * FT_PB], d12 = c - p[-3];
-            const bool h0 = d0 > tq, h4 = d4 > tq, h8 = d8 > tq, h12 = d12 > tq;
-            const bool l0 = d0 < -tq, l4 = d4 < -tq, l8 = d8 < -tq, l12 = d12 < -tq;
-            H = (h0 && h4) || (h4 && h8) || (h8 && h12) || (h12 && h0);
-            L = (l0 && l4) || (l4 && l8) || (l8 && l12) || (l12 && l0);
+            const int hv = min(max(d0, d8), max(d4, d12)), lv = max(min(d0, d8), min(d4, d12));
+            bitsH |= (unsigned)(hv > tq) << k;
+            bitsL |= (unsigned)(lv < -tq) << k;
         }
-        const unsigned m1 = __ballot_sync(0xffffffffu, H || L), m2 = __ballot_sync(0xffffffffu, H && L);
-        int base1 = 0, base2 = 0;
-        if (lane == 0) {
-            if (m1) base1 = atomicAdd(&s_nsurv, __popc(m1));
-            if (m2) base2 = atomicAdd(&s_n2, __popc(m2));
+    }
+    {
+        // block-wide exclusive scan of (survivors | both-type << 16) per thread
+        const unsigned any = bitsH | bitsL, both = bitsH & bitsL;
+        const int mine = __popc(any) | (__popc(both) << 16);
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
         }
-        base1 = __shfl_sync(0xffffffffu, base1, 0);
-        base2 = __shfl_sync(0xffffffffu, base2, 0);
-        const unsigned lt = (1u << lane) - 1;
-        if (H || L) surv[base1 + __popc(m1 & lt)] = (uint16_t)(i | (H ? 0 : 0x2000));   // bit 13: evaluate as darker type
-        if (H && L) surv2[base2 + __popc(m2 & lt)] = (uint16_t)i;
+        if (lane == 31) s_wsum[tid >> 5] = incl;
+        __syncthreads();
+        int wbase = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < FAST_THREADS / 32; w++) {
+            const int v = s_wsum[w];
+            if (w < (tid >> 5)) wbase += v;
+            total += v;
+        }
+        int pos = wbase + incl - mine;
+        int p1 = pos & 0xffff, p2 = pos >> 16;
+        for (unsigned m = any; m; m &= m - 1) {
+            const int k = __ffs(m) - 1, i = tid + k * FAST_THREADS;
+            const bool isH = (bitsH >> k) & 1;
+            surv[p1++] = (uint16_t)(i | (isH ? 0 : 0x2000));   // bit 13: evaluate as darker type
+            if ((both >> k) & 1) surv2[p2++] = (uint16_t)i;
+        }
+        if (tid == 0) { s_nsurv = total & 0xffff; s_n2 = total >> 16; }
     }
     __syncthreads();
 
@@ -1023,7 +1040,7 @@ static size_t octree_smem_bytes(int maxn) {
 }
 
 static void free_all(orb_extractor *ex) {
-    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_cand);
+    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_cand);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
@@ -1055,6 +1072,14 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
                 rc == ORB_ERR_TOO_SMALL ? "a pyramid level is too small for the 30-px cell grid (reference divides by zero)"
                                         : "unsupported geometry");
     ORB_REQUIRE(taps.size() <= ex->taps_cap, ORB_ERR_INVALID, "internal: tap pool too small");
+    std::vector<uint32_t> cells;
+    cells.reserve(G.total_cells);
+    for (int l = 0; l < G.nlevels; l++)
+        for (int ci = 0; ci < G.lv[l].ncy; ci++)
+            for (int cj = 0; cj < G.lv[l].ncx; cj++) cells.push_back((uint32_t)l | ((uint32_t)ci << 4) | ((uint32_t)cj << 14));
+    ORB_REQUIRE(cells.size() <= ex->cells_cap && G.lv[0].ncx < 1024 && G.lv[0].ncy < 1024, ORB_ERR_INVALID, "internal: cell table too small");
+    if (!cells.empty())
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_cells, cells.data(), cells.size() * 4, cudaMemcpyHostToDevice, ex->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_geom, &G, sizeof(G), cudaMemcpyHostToDevice, ex->stream));
     if (!taps.empty())
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_taps, taps.data(), taps.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice, ex->stream));
@@ -1116,6 +1141,8 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     }
     ex->taps_cap = (size_t)(params->max_width + params->max_height + 64) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_taps, ex->taps_cap * sizeof(ResizeTap)));
+    ex->cells_cap = (size_t)(params->max_width / 30 + 2) * (params->max_height / 30 + 2) * 4 + 64;   // sum over levels < 3.1x level 0
+    TRY_ALLOC(cudaMalloc(&ex->d_cells, ex->cells_cap * 4));
     ex->src_bytes = B * (size_t)params->max_height * ((params->max_width + 127) / 128 * 128);
     TRY_ALLOC(cudaMalloc(&ex->d_src, ex->src_bytes));
     ex->pyr_bytes = B * (size_t)(G.pyr_frame + 4096 * params->nlevels);
@@ -1253,7 +1280,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->launches++;
     }
     prof_mark(ex, 2);
-    k_fast_cells<<<dim3(G.total_cells, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_cand, d_cand_count, ex->d_err);
+    k_fast_cells<<<dim3(G.total_cells, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_cells, ex->d_cand, d_cand_count, ex->d_err);
     ex->launches++;
     prof_mark(ex, 3);
     k_octree<<<dim3(G.nlevels, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), st>>>(

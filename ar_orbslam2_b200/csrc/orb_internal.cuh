@@ -67,6 +67,8 @@ struct orb_extractor {
     orbgpu::Geom *d_geom = nullptr;
     orbgpu::ResizeTap *d_taps = nullptr;
     size_t taps_cap = 0;
+    uint32_t *d_cells = nullptr;       // per FAST cell: level | ci << 4 | cj << 14
+    size_t cells_cap = 0;
     uint8_t *d_src = nullptr;  size_t src_bytes = 0;
     uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
     uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;

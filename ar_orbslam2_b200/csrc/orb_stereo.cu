@@ -26,9 +26,21 @@ struct StereoArgs {
     int capacity;
     float mbf, mb;
     float *uRight, *depth;
+    int4 *packR;           // [batch][capacity] right keypoints packed by k_stereo_prep
     int32_t *sad;          // [batch][capacity] best SAD or -1
     int32_t *n_matched;    // [batch]
 };
+
+// Row band of every right keypoint (ref :486-496): rows [floor(y - r), ceil(y + r)], r = 2 * scale[octave], packed
+// with its octave and x so the search loop below reads one coalesced 16-byte record per candidate.
+__global__ void k_stereo_prep(StereoArgs A) {
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= min(A.nR[b], A.capacity)) return;
+    const orb_keypoint kr = A.keysR[(size_t)b * A.capacity + i];
+    const float r = __fmul_rn(2.0f, A.GL->lv[kr.octave].scale);
+    const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
+    A.packR[(size_t)b * A.capacity + i] = make_int4(minr, maxr, kr.octave, __float_as_int(kr.x));
+}
 
 __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
     __shared__ float s_IL[ST_WARPS][121];
@@ -61,17 +73,17 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
     uint32_t best = 0xffffffffu;   // (dist << 16) | iR
     const orb_keypoint *KR = A.keysR + (size_t)b * A.capacity;
     const uint8_t *DR = A.descR + (size_t)b * A.capacity * 32;
+    const int4 *PR = A.packR + (size_t)b * A.capacity;
     for (int iR = lane; iR < Nr; iR += 32) {
-        const orb_keypoint kr = KR[iR];
-        const float r = __fmul_rn(2.0f, A.GL->lv[kr.octave].scale);
-        const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
-        if (row < minr || row > maxr) continue;
-        if (kr.octave < levelL - 1 || kr.octave > levelL + 1) continue;
-        if (!(kr.x >= minU && kr.x <= maxU)) continue;
-        const uint32_t *p = reinterpret_cast<const uint32_t *>(DR + (size_t)iR * 32);
-        int d = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) d += __popc(dl[i] ^ __ldg(p + i));
+        const int4 kr = __ldg(PR + iR);   // {minr, maxr, octave, x}
+        if (row < kr.x || row > kr.y) continue;
+        if (kr.z < levelL - 1 || kr.z > levelL + 1) continue;
+        const float uR = __int_as_float(kr.w);
+        if (!(uR >= minU && uR <= maxU)) continue;
+        const uint4 *p = reinterpret_cast<const uint4 *>(DR + (size_t)iR * 32);
+        const uint4 q0 = __ldg(p), q1 = __ldg(p + 1);
+        const int d = __popc(dl[0] ^ q0.x) + __popc(dl[1] ^ q0.y) + __popc(dl[2] ^ q0.z) + __popc(dl[3] ^ q0.w) +
+                      __popc(dl[4] ^ q1.x) + __popc(dl[5] ^ q1.y) + __popc(dl[6] ^ q1.z) + __popc(dl[7] ^ q1.w);
         best = min(best, ((uint32_t)d << 16) | (uint32_t)iR);
     }
 #pragma unroll
@@ -225,7 +237,7 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     }
     const size_t per = (size_t)batch * capacity;
     // scratch layout: sad[per] | n_matched[batch] | (host mode) keysL,keysR,descL,descR,nL,nR,uRight,depth
-    size_t need = per * 4 + batch * 4 + 16 * 256;   // every carve() is rounded up to 256 B
+    size_t need = per * 4 + per * 16 + batch * 4 + 16 * 256;   // every carve() is rounded up to 256 B
     if (loc == ORB_HOST) need += 2 * per * sizeof(orb_keypoint) + 2 * per * 32 + 2 * batch * 4 + 2 * per * 4 + 1024;
     if (left->stereo_scratch_bytes < need) {
         if (left->stereo_scratch) cudaFree(left->stereo_scratch);
@@ -238,6 +250,7 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     auto carve = [&](size_t bytes) { uint8_t *r = p; p += (bytes + 255) / 256 * 256; return r; };
     StereoArgs A;
     A.sad = (int32_t *)carve(per * 4);
+    A.packR = (int4 *)carve(per * 16);
     A.n_matched = (int32_t *)carve(batch * 4);
     A.pyrL = left->d_pyr; A.pyrR = right->d_pyr;
     A.GL = left->d_geom; A.GR = right->d_geom;
@@ -260,13 +273,14 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
         A.keysL = keys_left; A.keysR = keys_right; A.descL = desc_left; A.descR = desc_right;
         A.nL = n_left; A.nR = n_right; A.uRight = u_right; A.depth = depth;
     }
+    k_stereo_prep<<<dim3((capacity + 127) / 128, batch), 128, 0, st>>>(A);
     k_stereo_match<<<dim3((capacity + ST_WARPS - 1) / ST_WARPS, batch), ST_WARPS * 32, 0, st>>>(A);
     int sort_n = 1;
     while (sort_n < capacity) sort_n <<= 1;
     if (sort_n * 4 > 48 * 1024)
         ORB_CUDA_TRY(cudaFuncSetAttribute(k_stereo_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_n * 4));
     k_stereo_filter<<<batch, 1024, sort_n * 4, st>>>(A, sort_n);
-    left->launches += 2;
+    left->launches += 3;
     ORB_CUDA_TRY(cudaGetLastError());
     if (loc == ORB_HOST) {
         ORB_CUDA_TRY(cudaMemcpyAsync(u_right, A.uRight, per * 4, cudaMemcpyDeviceToHost, st));
