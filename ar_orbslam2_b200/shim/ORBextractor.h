@@ -1,0 +1,82 @@
+// Drop-in replacement for ORB_SLAM2/include/ORBextractor.h (ref :45-118): same class name, namespace,
+// constructor, operator(), getters and public mvImagePyramid, so Frame.cc / Tracking.cc / the AR-1.3 copies
+// compile unchanged.  The work happens in liborbgpu (include/orbgpu.h); this header holds no arithmetic.
+//
+// Differences a maintainer should know about:
+//   * the extractor owns CUDA buffers sized for max_width x max_height (defaults fit 1920x1080; larger frames
+//     re-create the handle transparently);
+//   * mvImagePyramid is a host mirror of the device pyramid.  It is refreshed after every call unless
+//     SetMirrorPyramid(false): Frame::ComputeStereoMatches (the only reader, ref Frame.cc:476,566,578,583)
+//     goes through ORBGPU_ComputeStereoMatches, which reads the device pyramid in place;
+//   * without a CUDA device the constructor throws std::runtime_error -- there is no CPU fallback.
+#ifndef ORBEXTRACTOR_H
+#define ORBEXTRACTOR_H
+
+#include <list>
+#include <vector>
+
+#include "cv_compat.h"
+
+struct orb_extractor;
+
+namespace ORB_SLAM2 {
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+    ~ORBextractor();
+    ORBextractor(const ORBextractor &) = delete;
+    ORBextractor &operator=(const ORBextractor &) = delete;
+
+    // Compute the ORB features and descriptors on an image.  Mask is ignored, as in the reference (ref :60).
+    void operator()(cv::InputArray image, cv::InputArray mask, std::vector<cv::KeyPoint> &keypoints,
+                    cv::OutputArray descriptors);
+
+    int inline GetLevels() { return nlevels; }
+    float inline GetScaleFactor() { return scaleFactor; }
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    std::vector<cv::Mat> mvImagePyramid;
+
+    // --- additions (not in the reference)
+    void SetMirrorPyramid(bool on) { mbMirrorPyramid = on; }
+    orb_extractor *Handle() { return mpHandle; }   // for ORBGPU_ComputeStereoMatches
+
+protected:
+    void EnsureHandle(int width, int height);
+
+    int nfeatures;
+    double scaleFactor;   // double, as in the reference (ORBextractor.h:105)
+    int nlevels;
+    int iniThFAST;
+    int minThFAST;
+
+    std::vector<int> mnFeaturesPerLevel;
+    std::vector<float> mvScaleFactor;
+    std::vector<float> mvInvScaleFactor;
+    std::vector<float> mvLevelSigma2;
+    std::vector<float> mvInvLevelSigma2;
+
+    orb_extractor *mpHandle;
+    int mMaxWidth, mMaxHeight;
+    bool mbMirrorPyramid;
+    std::vector<unsigned char> mKpBuf, mDescBuf;
+    std::vector<cv::Mat> mPlanes;   // padded planes backing mvImagePyramid
+};
+
+// ref: void Frame::ComputeStereoMatches(), Frame.cc:471-643, as a free function over the members it touches.
+// mvuRight / mvDepth are resized to mvKeys.size().  Returns false when no match survived (the reference indexes an
+// empty vector there, Frame.cc:630).
+bool ORBGPU_ComputeStereoMatches(ORBextractor *left, ORBextractor *right, const std::vector<cv::KeyPoint> &mvKeys,
+                                 const cv::Mat &mDescriptors, const std::vector<cv::KeyPoint> &mvKeysRight,
+                                 const cv::Mat &mDescriptorsRight, float mbf, float mb, std::vector<float> &mvuRight,
+                                 std::vector<float> &mvDepth);
+
+}  // namespace ORB_SLAM2
+
+#endif

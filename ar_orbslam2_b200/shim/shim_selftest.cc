@@ -1,0 +1,52 @@
+// Exercises the C++ drop-in shim the way Frame's stereo constructor does (ref Frame.cc:66-122): two extractors
+// from two threads, then the stereo association.  Reads frames from raw files, writes results for the Python test
+// to compare with the oracle.  usage: shim_selftest W H left.raw right.raw nfeatures out_prefix
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ORBextractor.h"
+
+static std::vector<unsigned char> slurp(const char *p, size_t n) {
+    std::vector<unsigned char> b(n);
+    FILE *f = fopen(p, "rb");
+    if (!f || fread(b.data(), 1, n, f) != n) { fprintf(stderr, "cannot read %s\n", p); exit(2); }
+    fclose(f);
+    return b;
+}
+static void dump(const std::string &p, const void *d, size_t n) {
+    FILE *f = fopen(p.c_str(), "wb");
+    fwrite(d, 1, n, f);
+    fclose(f);
+}
+
+int main(int argc, char **argv) {
+    if (argc < 7) return 2;
+    const int W = atoi(argv[1]), H = atoi(argv[2]), nf = atoi(argv[5]);
+    std::vector<unsigned char> L = slurp(argv[3], (size_t)W * H), R = slurp(argv[4], (size_t)W * H);
+    cv::Mat imLeft(H, W, CV_8UC1, L.data(), W), imRight(H, W, CV_8UC1, R.data(), W);
+    ORB_SLAM2::ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);
+    std::vector<cv::KeyPoint> kL, kR;
+    cv::Mat dL, dR;
+    std::thread tl([&] { exL(imLeft, cv::Mat(), kL, dL); });     // ref Frame.cc:83-86
+    std::thread tr([&] { exR(imRight, cv::Mat(), kR, dR); });
+    tl.join(); tr.join();
+    std::vector<float> uR, depth;
+    const float mbf = 386.1448f, mb = mbf / 718.856f;
+    const bool ok = ORB_SLAM2::ORBGPU_ComputeStereoMatches(&exL, &exR, kL, dL, kR, dR, mbf, mb, uR, depth);
+    const std::string pre = argv[6];
+    dump(pre + "_kl.bin", kL.data(), kL.size() * sizeof(cv::KeyPoint));
+    dump(pre + "_kr.bin", kR.data(), kR.size() * sizeof(cv::KeyPoint));
+    dump(pre + "_dl.bin", dL.data, (size_t)dL.rows * 32);
+    dump(pre + "_dr.bin", dR.data, (size_t)dR.rows * 32);
+    dump(pre + "_ur.bin", uR.data(), uR.size() * 4);
+    dump(pre + "_dp.bin", depth.data(), depth.size() * 4);
+    // the host mirror of level 3 incl. the byte 7 px into the left border, as Frame.cc:583 may touch
+    const cv::Mat &l3 = exL.mvImagePyramid[3];
+    dump(pre + "_l3.bin", l3.data - 19 * l3.step - 19, (size_t)(l3.rows + 38) * l3.step);
+    printf("shim ok=%d nL=%zu nR=%zu scale1=%.9g levels=%d l3=%dx%d step=%zu\n", (int)ok, kL.size(), kR.size(), exL.GetScaleFactors()[1],
+           exL.GetLevels(), l3.cols, l3.rows, l3.step);
+    return 0;
+}
