@@ -1,8 +1,10 @@
 """Loader for liborbgpu.so (the C ABI of include/orbgpu.h).  Fails loudly when the library is
 missing: there is no CPU fallback for any compute entry point."""
+import atexit
 import ctypes as C
 import os
 import subprocess
+import weakref
 
 from ._abi import OrbParams
 
@@ -43,3 +45,21 @@ def lib():
 def check(rc, what):
     if rc != 0:
         raise OrbGpuError(rc, what, lib().orb_last_error().decode(errors="replace"))
+
+
+# Handles that are still alive when the interpreter exits are closed here, before the CUDA runtime's own exit
+# handlers run: destroying them from __del__ during late shutdown would call into a torn-down runtime.
+_live = weakref.WeakSet()
+
+
+def register(obj):
+    _live.add(obj)
+
+
+@atexit.register
+def _close_all():
+    for o in list(_live):
+        try:
+            o.close()
+        except Exception:
+            pass

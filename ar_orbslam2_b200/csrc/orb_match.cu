@@ -386,6 +386,19 @@ uint8_t *orb_db_device_ptr(orb_db *db) { return db ? db->d_rows : nullptr; }
 void *orb_db_stream(orb_db *db) { return db ? (void *)db->stream : nullptr; }
 int64_t orb_db_launch_count(const orb_db *db) { return db ? db->launches : 0; }
 
+int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx, const int32_t *second_dist,
+                      const int64_t *second_idx, int32_t *out_best_dist, int64_t *out_best_idx, int32_t *out_second_dist,
+                      int64_t *out_second_idx) {
+    ORB_REQUIRE(db && nshards >= 1 && nq >= 1 && best_dist && best_idx && second_dist && second_idx && out_best_dist && out_best_idx &&
+                    out_second_dist && out_second_idx, ORB_ERR_INVALID, "bad argument");
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, db->stream>>>(nshards, nq, best_dist, best_idx, second_dist, second_idx, out_best_dist,
+                                                           out_best_idx, out_second_dist, out_second_idx);
+    db->launches++;
+    ORB_CUDA_TRY(cudaGetLastError());
+    return ORB_OK;
+}
+
 int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist, int64_t *best_idx, int32_t *second_dist,
                  int64_t *second_idx, int loc) {
     ORB_REQUIRE(db && queries && nq >= 1 && best_dist && best_idx && second_dist && second_idx, ORB_ERR_INVALID, "bad argument");

@@ -27,6 +27,7 @@ class ORBextractor:
         _lib.check(self._L.orb_extractor_tables(self._h, ptr(self._scale), ptr(self._inv_scale), ptr(self._sigma2),
                                                 ptr(self._inv_sigma2), ptr(self._per_level)), "orb_extractor_tables")
         self.default_capacity = nfeatures + 4 * nlevels + 256
+        _lib.register(self)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:

@@ -76,6 +76,7 @@ class DescriptorDB:
         self._h = C.c_void_p()
         _lib.check(self._L.orb_db_create(C.c_int64(row_begin), C.c_int64(row_end), device, C.byref(self._h)), "orb_db_create")
         self.row_begin, self.row_end = row_begin, row_end
+        _lib.register(self)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -123,3 +124,9 @@ class DescriptorDB:
         """Asynchronous on the shard's stream; raw device pointers."""
         vp = C.c_void_p
         _lib.check(self._L.orb_db_query(self._h, vp(d_q), nq, vp(d_d1), vp(d_i1), vp(d_d2), vp(d_i2), ORB_DEVICE), "orb_db_query")
+
+    def merge_top2_device(self, nshards: int, nq: int, d_bd: int, d_bi: int, d_sd: int, d_si: int, o_bd: int, o_bi: int, o_sd: int, o_si: int):
+        """[nshards, nq] partial lists (device pointers, shard order) -> single-scan result, on the shard's stream."""
+        vp = C.c_void_p
+        _lib.check(self._L.orb_db_merge_top2(self._h, nshards, nq, vp(d_bd), vp(d_bi), vp(d_sd), vp(d_si), vp(o_bd), vp(o_bi), vp(o_sd),
+                                             vp(o_si)), "orb_db_merge_top2")

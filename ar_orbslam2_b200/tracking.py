@@ -54,6 +54,7 @@ class Frame:
         d = OrbFrameDesc(self.N, ptr(self.keys), ptr(self.desc), optr(self.u_right), *self.bounds, len(self.scale), ptr(self.scale))
         self._h = C.c_void_p()
         self.B.check(getattr(self.B.L, self.B.prefix + "frame_create")(C.byref(d), C.byref(self._h)), "frame_create")
+        _lib.register(self)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:

@@ -156,13 +156,142 @@ def workload_config(batch_pairs):
             "parallelism": "independent frames sharded one batch per GPU, no collective"}
 
 
+def bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier):
+    """Config C5 shape: brute-force top-2 of 2000 queries against a descriptor database sharded by row range, one shard of
+    `--db-rows` rows per GPU (weak scaling; > L2), local scan + all-gather of the partial top-2 + merge.  Gcompares/s is
+    the whole-job rate; the roofline is the measured POPC issue rate (8 popc32 per compare)."""
+    from ar_orbslam2_b200.matcher import DescriptorDB, measure_popc_rate
+    from ar_orbslam2_b200.synth import synth_queries
+    rows, nq, reps = args.db_rows, 2000, 5
+    db = DescriptorDB(rank * rows, (rank + 1) * rows, device=local)
+    db.fill_synthetic(7)
+    q_host = synth_queries(lambda idx: db.rows([rank * rows + int(i) % rows for i in idx]), rows, nq, 3)
+    q = torch.from_numpy(q_host).to(dev)
+    if world > 1:
+        dist.broadcast(q, 0)            # every rank searches the same queries
+    st = torch.cuda.ExternalStream(db.stream, device=dev)
+    loc = [torch.zeros(nq, dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
+    out = [torch.zeros(nq, dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
+    packed = torch.zeros((4, nq), dtype=torch.int64, device=dev)
+    gathered = torch.zeros((world, 4, nq), dtype=torch.int64, device=dev)
+    parts = [torch.zeros((world, nq), dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
+
+    def one():
+        db.query_device(q.data_ptr(), nq, *[t.data_ptr() for t in loc])
+        if world == 1:
+            return
+        with torch.cuda.stream(st):
+            packed[0].copy_(loc[0]); packed[1].copy_(loc[1]); packed[2].copy_(loc[2]); packed[3].copy_(loc[3])
+            dist.all_gather_into_tensor(gathered, packed)
+            for k in range(4):
+                parts[k].copy_(gathered[:, k])   # preallocated: nothing is allocated on the library's stream
+            db.merge_top2_device(world, nq, *[t.data_ptr() for t in parts], *[t.data_ptr() for t in out])
+
+    for _ in range(2):
+        one()
+    st.synchronize()
+    l0 = db.launch_count
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    s.record(st)
+    for _ in range(reps):
+        one()
+    e.record(st)
+    e.synchronize()
+    barrier()
+    ms = reduce_max(s.elapsed_time(e))
+    res = out if world > 1 else loc
+    planted_found = bool((res[0][0::2] <= 40).all().item())
+    popc = measure_popc_rate()
+    gcmp = world * rows * nq * reps / (ms * 1e-3) / 1e9
+    r = {"gcompares_per_s": gcmp, "queries": nq, "db_rows_per_gpu": rows, "db_bytes_per_gpu": rows * 32, "ms_per_query_batch": ms / reps,
+         "popc_peak_gpopc32_per_s_measured": popc, "frac_of_popc_peak": gcmp * 8 / (popc * world), "launches": int(db.launch_count - l0),
+         "exchange": "none" if world == 1 else "nccl all_gather of 64 KB/rank + device merge", "planted_queries_found": planted_found}
+    db.close()
+    return r
+
+
+def bench_c1(args, torch, dev, local):
+    """Config C1: monocular 640x480, nFeatures 1000 -- device-resident batched extraction, frames/s."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.synth import synth_frame
+    w, h, nb, steps = 640, 480, 512, 5
+    frames = np.stack([synth_frame(w, h, 300 + i) for i in range(16)])
+    d_img = torch.from_numpy(np.ascontiguousarray(np.tile(frames, (nb // 16, 1, 1)))).to(dev)   # 157 MB > L2
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb, device=local)
+    cap = ex.default_capacity
+    d_k = torch.zeros((nb, cap, 28), dtype=torch.uint8, device=dev)
+    d_d = torch.zeros((nb, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(nb, dtype=torch.int32, device=dev)
+    st = torch.cuda.ExternalStream(ex.stream, device=dev)
+    run = lambda: ex.extract_batch_device(d_img.data_ptr(), nb, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap, d_n.data_ptr())
+    for _ in range(3):
+        run()
+    ex.check()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record(st)
+    for _ in range(steps):
+        run()
+    e.record(st)
+    e.synchronize()
+    ms = s.elapsed_time(e)
+    r = {"frames_per_s": nb * steps / (ms * 1e-3), "workload": "640x480, 1000 features, batch 512 device-resident",
+         "keypoints_per_frame": float(d_n.sum().item()) / nb}
+    ex.close()
+    return r
+
+
+_KEEP = []   # library handles must outlive every pinned buffer that was copied on their streams: torch's pinned-memory
+             # allocator records an event on those streams when such a buffer is freed.  They are closed at interpreter exit.
+
+
+class Lane:
+    """One extractor handle with its device-resident outputs and pinned host result buffers (one CUDA stream)."""
+
+    def __init__(self, torch, dev, local, B, host_frames):
+        from ar_orbslam2_b200.extractor import ORBextractor
+        NF = 2 * B
+        self.B, self.NF, self.host = B, NF, host_frames
+        self.ex = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=NF, device=local)
+        _KEEP.append(self.ex)
+        cap = self.cap = self.ex.default_capacity
+        self.stream = torch.cuda.ExternalStream(self.ex.stream, device=dev)
+        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)
+        zp = lambda shape, dt: torch.zeros(shape, dtype=dt).pin_memory()
+        self.d_in = torch.empty((NF, H, W), dtype=torch.uint8, device=dev)
+        self.d = dict(kps=z((NF, cap, 28), torch.uint8), desc=z((NF, cap, 32), torch.uint8), n=z(NF, torch.int32),
+                      ur=z((B, cap), torch.float32), dp=z((B, cap), torch.float32), nm=z(B, torch.int32))
+        self.h = {k: zp(tuple(v.shape), v.dtype) for k, v in self.d.items()}
+        self.mb = float(np.float32(MBF) / np.float32(FX))
+        self.torch = torch
+
+    def step_device(self, src):
+        """left+right extraction of B pairs (frames 0..B-1 left, B..2B-1 right) + ComputeStereoMatches, all on the device."""
+        from ar_orbslam2_b200.stereo import stereo_match_batch_device
+        d, B, cap = self.d, self.B, self.cap
+        self.ex.extract_batch_device(src.data_ptr(), self.NF, W, H, W, W * H, d["kps"].data_ptr(), d["desc"].data_ptr(), cap,
+                                     d["n"].data_ptr())
+        stereo_match_batch_device(self.ex, 0, self.ex, B, B, d["kps"].data_ptr(), d["desc"].data_ptr(), d["n"].data_ptr(),
+                                  d["kps"][B:].data_ptr(), d["desc"][B:].data_ptr(), d["n"][B:].data_ptr(), cap, MBF, self.mb,
+                                  d["ur"].data_ptr(), d["dp"].data_ptr(), d["nm"].data_ptr())
+
+    def enqueue_e2e(self):
+        """pinned host frames -> device -> results back in pinned host memory; asynchronous on this lane's stream."""
+        with self.torch.cuda.stream(self.stream):
+            self.d_in.copy_(self.host, non_blocking=True)
+            self.step_device(self.d_in)
+            for k in self.d:
+                self.h[k].copy_(self.d[k], non_blocking=True)
+
+    def d2h_bytes(self):
+        return sum(t.numel() * t.element_size() for t in self.h.values())
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
     from ar_orbslam2_b200 import _lib
-    from ar_orbslam2_b200.extractor import ORBextractor
-    from ar_orbslam2_b200.stereo import stereo_match_batch_device
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -182,79 +311,45 @@ def run_ours(args):
         l, r = pairs[b % len(pairs)]
         hv[b] = l
         hv[B + b] = r
-    ex = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=NF, device=local)
-    cap = ex.default_capacity
-    stream = torch.cuda.ExternalStream(ex.stream, device=dev)
+    lanes = [Lane(torch, dev, local, B, host), Lane(torch, dev, local, B, host)]   # two lanes: copies overlap compute in the e2e arm
+    A = lanes[0]
+    ex, stream = A.ex, A.stream
     d_img = host.to(dev)
-    d_kps = torch.zeros((NF, cap, 28), dtype=torch.uint8, device=dev)
-    d_desc = torch.zeros((NF, cap, 32), dtype=torch.uint8, device=dev)
-    d_n = torch.zeros(NF, dtype=torch.int32, device=dev)
-    d_ur = torch.zeros((B, cap), dtype=torch.float32, device=dev)
-    d_dp = torch.zeros((B, cap), dtype=torch.float32, device=dev)
-    d_nm = torch.zeros(B, dtype=torch.int32, device=dev)
-    h_n = torch.zeros(NF, dtype=torch.int32).pin_memory()
-    h_kps = torch.zeros((NF, cap, 28), dtype=torch.uint8).pin_memory()
-    h_desc = torch.zeros((NF, cap, 32), dtype=torch.uint8).pin_memory()
-    h_ur = torch.zeros((B, cap), dtype=torch.float32).pin_memory()
-    h_dp = torch.zeros((B, cap), dtype=torch.float32).pin_memory()
-    h_nm = torch.zeros(B, dtype=torch.int32).pin_memory()
-    mb = float(np.float32(MBF) / np.float32(FX))
     torch.cuda.synchronize()
-
-    def step_device(src):
-        ex.extract_batch_device(src.data_ptr(), NF, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
-        stereo_match_batch_device(ex, 0, ex, B, B, d_kps.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(),
-                                  d_kps[B:].data_ptr(), d_desc[B:].data_ptr(), d_n[B:].data_ptr(), cap, MBF, mb,
-                                  d_ur.data_ptr(), d_dp.data_ptr(), d_nm.data_ptr())
-
-    d_in2 = torch.empty_like(d_img)
-
-    def step_e2e():
-        with torch.cuda.stream(stream):
-            d_in2.copy_(host, non_blocking=True)
-            step_device(d_in2)
-            h_n.copy_(d_n, non_blocking=True)
-            h_kps.copy_(d_kps, non_blocking=True)
-            h_desc.copy_(d_desc, non_blocking=True)
-            h_ur.copy_(d_ur, non_blocking=True)
-            h_dp.copy_(d_dp, non_blocking=True)
-            h_nm.copy_(d_nm, non_blocking=True)
-        stream.synchronize()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        s.record(stream)
-        for _ in range(steps):
-            fn()
-        e.record(stream)
-        e.synchronize()
-        barrier()
-        ms = s.elapsed_time(e)
+    def reduce_max(ms):
         if world > 1:
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
         return ms
 
-    # ---- device-resident arm
+    # ---- device-resident arm: inputs already in HBM, CUDA events on the library's stream
     for _ in range(max(args.warmup, 3)):
-        step_device(d_img)
+        A.step_device(d_img)
     ex.check()
-    n_kp = int(d_n.sum().item())
-    n_matched = int(d_nm.sum().item())
+    n_kp = int(A.d["n"].sum().item())
+    n_matched = int(A.d["nm"].sum().item())
     L = _lib.lib()
     L.orb_extractor_set_profiling(ex._h, 1)
     launches0 = ex.launch_count
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms = timed(lambda: step_device(d_img), args.steps)
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    s.record(stream)
+    for _ in range(args.steps):
+        A.step_device(d_img)
+    e.record(stream)
+    e.synchronize()
+    barrier()
+    ms = reduce_max(s.elapsed_time(e))
     clocks = sampler.stop() if rank == 0 else None
     launches = ex.launch_count - launches0
     stage_ms = (C.c_double * 6)()
@@ -262,21 +357,44 @@ def run_ours(args):
     L.orb_extractor_stage_times(ex._h, stage_ms, C.byref(calls))
     L.orb_extractor_set_profiling(ex._h, 0)
     ex.check()
-    frames_total = NF * args.steps * world
-    value = frames_total / (ms * 1e-3)
+    value = NF * args.steps * world / (ms * 1e-3)
 
-    # ---- end-to-end arm (pinned host frames in, host keypoints/descriptors/depth out)
-    for _ in range(2):
-        step_e2e()
-    e2e_steps = max(3, args.steps // 2)
+    # ---- end-to-end arm: every step copies its frames from pinned host memory and its results back.  Two lanes
+    # alternate so that one lane's PCIe copies overlap the other lane's kernels; a lane is synchronised before reuse
+    # (its host results are consumed), so at most two steps are in flight.
+    for i in range(4):
+        lanes[i % 2].stream.synchronize()
+        lanes[i % 2].enqueue_e2e()
+    e2e_steps = max(4, args.steps)
     barrier()
+    s2, e2, join = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event()
     t0 = time.perf_counter()
-    ms_e2e = timed(step_e2e, e2e_steps)
+    s2.record(lanes[0].stream)
+    lanes[1].stream.wait_event(s2)
+    for i in range(e2e_steps):
+        ln = lanes[i % 2]
+        ln.stream.synchronize()
+        ln.enqueue_e2e()
+    join.record(lanes[1].stream)
+    lanes[0].stream.wait_event(join)
+    e2.record(lanes[0].stream)
+    e2.synchronize()
     wall_e2e = time.perf_counter() - t0
+    barrier()
+    ms_e2e = reduce_max(s2.elapsed_time(e2))
     e2e_value = NF * e2e_steps * world / (ms_e2e * 1e-3)
-    h2d = host.numel()
-    d2h = sum(t.numel() * t.element_size() for t in (h_n, h_kps, h_desc, h_ur, h_dp, h_nm))
-    assert int(h_n.sum().item()) == n_kp, "e2e arm produced different keypoint counts"
+    h2d, d2h = host.numel(), A.d2h_bytes()
+    for ln in lanes:
+        assert int(ln.h["n"].sum().item()) == n_kp, "e2e arm produced different keypoint counts"
+    # the handles stay open until interpreter exit (ar_orbslam2_b200._lib closes them from atexit): torch's pinned-memory
+    # allocator records an event on every stream a pinned buffer was copied on when that buffer is freed, so the
+    # library streams must outlive the buffers.
+
+    extra = {}
+    if not os.environ.get("ORB_BENCH_SKIP_HAMMING"):
+        extra["hamming"] = bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier)
+    if rank == 0 and not os.environ.get("ORB_BENCH_SKIP_C1"):
+        extra["c1_mono"] = bench_c1(args, torch, dev, local)
 
     if rank != 0:
         if world > 1:
@@ -324,7 +442,8 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(B),
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e / e2e_steps, "wall_s": wall_e2e},
+                "ms_per_step": ms_e2e / e2e_steps, "wall_s": wall_e2e, "steps": e2e_steps,
+                "pipeline": "two extractor handles alternate; a handle is synchronised before reuse"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -335,10 +454,11 @@ def run_ours(args):
         "stage_ms_per_step": dict({STAGES[i]: per_call[i] for i in range(6)},
                                   stereo_match=ms / args.steps - sum(per_call)),
         "keypoints_per_frame": kp_per_frame, "stereo_matches_per_pair": n_matched / B,
+        "extra": extra,
         "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{sample_pairs} synthetic stereo pairs x{reps} through the oracle, one pair per thread"},
     }
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -352,6 +472,7 @@ def main():
     ap.add_argument("--batch", type=int, default=144, help="stereo pairs per step per GPU")
     ap.add_argument("--distinct", type=int, default=16, help="distinct synthetic pairs tiled into the batch")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
+    ap.add_argument("--db-rows", type=int, default=8_000_000, help="descriptor-database rows per GPU for the Hamming leg (256 MB)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -325,6 +325,12 @@ int64_t orb_db_launch_count(const orb_db *db);
 int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist,
                  int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc);
 
+/* Device-resident merge of [nshards][nq] partial lists (e.g. the result of an all-gather across ranks), asynchronous
+ * on the shard's stream -- the exchange step of the sharded search.                                  */
+int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx,
+                      const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
+                      int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
+
 const char *orb_last_error(void);
 int orb_abi_version(void);
 
