@@ -124,8 +124,9 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    sample_pairs = max(cores, 8)
-    pairs = make_pairs(sample_pairs, 1000)
+    sample_pairs = 4 * max(cores, 8)
+    pairs = make_pairs(min(sample_pairs, 32), 1000)
+    pairs = [pairs[i % len(pairs)] for i in range(sample_pairs)]
     for _ in range(args.warmup):
         cpu_reference_run(pairs[: max(1, cores // 2)], cores)
     t_total, frames = 0.0, 0
