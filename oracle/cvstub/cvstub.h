@@ -67,44 +67,97 @@ public:
     int rows, cols;
     uchar *data;
     Step step;
+    int type_;
+    size_t esz;
     std::shared_ptr<std::vector<uchar>> buf;
 
-    Mat() : rows(0), cols(0), data(nullptr), step{0} {}
-    Mat(Size sz, int) { alloc(sz.height, sz.width); }
-    Mat(int r, int c, int) { alloc(r, c); }
-    void alloc(int r, int c) {
-        rows = r; cols = c;
-        buf = std::make_shared<std::vector<uchar>>((size_t)r * c);
+    Mat() : rows(0), cols(0), data(nullptr), step{0}, type_(CV_8UC1), esz(1) {}
+    Mat(Size sz, int t) { alloc(sz.height, sz.width, t); }
+    Mat(int r, int c, int t) { alloc(r, c, t); }
+    void alloc(int r, int c, int t = CV_8UC1) {
+        rows = r; cols = c; type_ = t; esz = (t == CV_32F) ? 4 : 1;
+        buf = std::make_shared<std::vector<uchar>>((size_t)r * c * esz);
         data = buf->data();
-        step.v = (size_t)c;
+        step.v = (size_t)c * esz;
     }
-    void create(int r, int c, int) { if (r != rows || c != cols || !data) alloc(r, c); }
+    void create(int r, int c, int t) { if (r != rows || c != cols || t != type_ || !data) alloc(r, c, t); }
     void release() { rows = cols = 0; data = nullptr; buf.reset(); step.v = 0; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-    int type() const { return CV_8UC1; }
-    size_t step1() const { return step.v; }
-    Mat operator()(const Rect &r) const { Mat m = *this; m.data = data + (size_t)r.y * step.v + r.x; m.rows = r.height; m.cols = r.width; return m; }
+    int type() const { return type_; }
+    size_t step1() const { return step.v / esz; }
+    Mat operator()(const Rect &r) const { Mat m = *this; m.data = data + (size_t)r.y * step.v + r.x * esz; m.rows = r.height; m.cols = r.width; return m; }
     Mat rowRange(int a, int b) const { Mat m = *this; m.data = data + (size_t)a * step.v; m.rows = b - a; return m; }
-    Mat colRange(int a, int b) const { Mat m = *this; m.data = data + a; m.cols = b - a; return m; }
+    Mat colRange(int a, int b) const { Mat m = *this; m.data = data + a * esz; m.cols = b - a; return m; }
+    Mat row(int a) const { return rowRange(a, a + 1); }
+    Mat col(int a) const { return colRange(a, a + 1); }
     template <typename T> T &at(int y, int x) { return *(T *)(data + (size_t)y * step.v + x * sizeof(T)); }
     template <typename T> const T &at(int y, int x) const { return *(const T *)(data + (size_t)y * step.v + x * sizeof(T)); }
+    template <typename T> T &at(int i) { return cols == 1 ? at<T>(i, 0) : at<T>(0, i); }
+    template <typename T> const T &at(int i) const { return cols == 1 ? at<T>(i, 0) : at<T>(0, i); }
     uchar *ptr(int y = 0) { return data + (size_t)y * step.v; }
     const uchar *ptr(int y = 0) const { return data + (size_t)y * step.v; }
     template <typename T> T *ptr(int y = 0) { return (T *)(data + (size_t)y * step.v); }
+    template <typename T> const T *ptr(int y = 0) const { return (const T *)(data + (size_t)y * step.v); }
     Mat clone() const {
-        Mat m(rows, cols, 0);
-        for (int y = 0; y < rows; y++) std::memcpy(m.ptr(y), ptr(y), cols);
+        Mat m(rows, cols, type_);
+        for (int y = 0; y < rows; y++) std::memcpy(m.ptr(y), ptr(y), cols * esz);
         return m;
     }
+    void copyTo(Mat &m) const { m = clone(); }
     static MatZeros zeros(int r, int c, int t) { return MatZeros{r, c, t}; }
     // Mat = MatExpr(zeros): keeps the existing buffer when size and type match (cv::Mat::create semantics), which is
     // how ORBextractor.cc:978 zero-fills a row range of the output descriptor matrix in place.
     Mat &operator=(const MatZeros &z) {
         create(z.rows, z.cols, z.type);
-        for (int y = 0; y < rows; y++) std::memset(ptr(y), 0, cols);
+        for (int y = 0; y < rows; y++) std::memset(ptr(y), 0, cols * esz);
         return *this;
     }
+    // ---- CV_32F algebra used by ORBmatcher.cc (products accumulate in double like cv::gemm, results are float)
+    Mat t() const {
+        Mat m(cols, rows, CV_32F);
+        for (int y = 0; y < rows; y++) for (int x = 0; x < cols; x++) m.at<float>(x, y) = at<float>(y, x);
+        return m;
+    }
+    double dot(const Mat &o) const {
+        double s = 0;
+        for (int y = 0; y < rows; y++) for (int x = 0; x < cols; x++) s += (double)at<float>(y, x) * o.at<float>(y, x);
+        return s;
+    }
 };
+static inline Mat operator*(const Mat &a, const Mat &b) {
+    assert(a.cols == b.rows && a.type() == CV_32F);
+    Mat m(a.rows, b.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < b.cols; x++) {
+            double s = 0;
+            for (int k = 0; k < a.cols; k++) s += (double)a.at<float>(y, k) * b.at<float>(k, x);
+            m.at<float>(y, x) = (float)s;
+        }
+    return m;
+}
+#define CVSTUB_EW(OP)                                                                                      \
+    static inline Mat operator OP(const Mat &a, const Mat &b) {                                            \
+        assert(a.rows == b.rows && a.cols == b.cols);                                                      \
+        Mat m(a.rows, a.cols, CV_32F);                                                                     \
+        for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = a.at<float>(y, x) OP b.at<float>(y, x); \
+        return m;                                                                                          \
+    }
+CVSTUB_EW(+)
+CVSTUB_EW(-)
+#undef CVSTUB_EW
+static inline Mat operator*(const Mat &a, double s) {
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = (float)(a.at<float>(y, x) * s);
+    return m;
+}
+static inline Mat operator*(double s, const Mat &a) { return a * s; }
+static inline Mat operator/(const Mat &a, double s) {
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = (float)(a.at<float>(y, x) / s);
+    return m;
+}
+static inline Mat operator-(const Mat &a) { return a * -1.0; }
+static inline double norm(const Mat &a) { return std::sqrt(a.dot(a)); }
 
 class _InputArray {
 public:

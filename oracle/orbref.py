@@ -250,3 +250,83 @@ class ReferenceExtractor:
         out = np.zeros((h.value, w.value), np.uint8)
         ref_lib().ref_pyramid_level(self.h, level, ptr(out), w.value, C.byref(w), C.byref(h))
         return out
+
+
+# ---- oracle/_ref matcher: the reference's own ORBmatcher.cc compiled against stub Frame/KeyFrame/MapPoint ----
+REF_MATCHER_PATH = os.path.join(_HERE, "_ref", "liborbmatcher_ref.so")
+_REFM = None
+
+
+def ref_matcher_available() -> bool:
+    if os.path.exists(REF_MATCHER_PATH):
+        return True
+    if os.path.isdir("/root/reference/ORB_SLAM2/src"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-f", "Makefile.ref"])
+        return True
+    return False
+
+
+class ReferenceSourceBackend:
+    """Drives ar_orbslam2_b200.tracking.Frame / ORBmatcher through the reference's compiled ORBmatcher.cc for the entry
+    points whose flat signature is identical (frame_create, features_in_area, search_for_initialization,
+    search_by_projection_points)."""
+    prefix = "refm_"
+
+    def __init__(self):
+        global _REFM
+        if _REFM is None:
+            _REFM = C.CDLL(REF_MATCHER_PATH)
+        self.L = _REFM
+
+    def check(self, rc, what):
+        _check(rc, what)
+
+
+def refm_search_by_bow(kf, f, kf_off, kf_idx, f_off, f_idx, kf_valid, f_valid, kfkf, nnratio, check_ori):
+    """kf, f: tracking.Frame objects created with ReferenceSourceBackend."""
+    L = kf.B.L
+    ko, ki, fo, fi = (np.ascontiguousarray(a, np.int32) for a in (kf_off, kf_idx, f_off, f_idx))
+    kv = np.ascontiguousarray(kf_valid, np.uint8)
+    matches = np.full(f.N, -1, np.int32)
+    nm = C.c_int()
+    if kfkf:
+        fv = None if f_valid is None else np.ascontiguousarray(f_valid, np.uint8)
+        L.refm_search_by_bow_kfkf(kf._h, f._h, len(ko) - 1, ptr(ko), ptr(ki), ptr(fo), ptr(fi), ptr(kv),
+                                  None if fv is None else ptr(fv), C.c_float(nnratio), int(check_ori), ptr(matches), C.byref(nm))
+    else:
+        L.refm_search_by_bow(kf._h, f._h, len(ko) - 1, ptr(ko), ptr(ki), ptr(fo), ptr(fi), ptr(kv), C.c_float(nnratio), int(check_ori),
+                             ptr(matches), C.byref(nm))
+    return nm.value, matches
+
+
+def refm_search_by_projection_last(cur, last, world_xyz, has_point, obs_positive, claimed, Tcw_cur, Tcw_last, fx, fy, cx, cy, mbf, mb, th,
+                                   mono, nnratio, check_ori):
+    """Reference SearchByProjection(Cur, Last, th, bMono).  Returns dict with assigned, nmatches and the projection the
+    reference computed (u, v, invz, valid, forward, backward)."""
+    L = cur.B.L
+    n = last.N
+    xyz = np.ascontiguousarray(world_xyz, np.float32)
+    hp = np.ascontiguousarray(has_point, np.uint8)
+    ob = None if obs_positive is None else np.ascontiguousarray(obs_positive, np.uint8)
+    cl = None if claimed is None else np.ascontiguousarray(claimed, np.uint8)
+    tc, tl = np.ascontiguousarray(Tcw_cur, np.float32), np.ascontiguousarray(Tcw_last, np.float32)
+    assigned = np.full(cur.N, -1, np.int32)
+    u, v, iz = (np.zeros(n, np.float32) for _ in range(3))
+    valid = np.zeros(n, np.uint8)
+    nm, fw, bw = C.c_int(), C.c_int(), C.c_int()
+    f = C.c_float
+    L.refm_search_by_projection_last(cur._h, last._h, ptr(xyz), ptr(hp), None if ob is None else ptr(ob), None if cl is None else ptr(cl),
+                                     ptr(tc), ptr(tl), f(fx), f(fy), f(cx), f(cy), f(mbf), f(mb), f(th), int(mono), f(nnratio), int(check_ori),
+                                     ptr(assigned), C.byref(nm), ptr(u), ptr(v), ptr(iz), ptr(valid), C.byref(fw), C.byref(bw))
+    return dict(assigned=assigned, nmatches=nm.value, u=u, v=v, invz=iz, valid=valid, forward=bool(fw.value), backward=bool(bw.value))
+
+
+def refm_descriptor_distance(a, b):
+    global _REFM
+    if _REFM is None:
+        _REFM = C.CDLL(REF_MATCHER_PATH)
+    a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    out = np.zeros(a.shape[0], np.int32)
+    _REFM.refm_descriptor_distance(ptr(a), ptr(b), a.shape[0], ptr(out))
+    return out

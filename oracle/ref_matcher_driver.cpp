@@ -1,0 +1,271 @@
+// ORACLE -- TEST INFRASTRUCTURE ONLY.  C entry points around the reference's own ORB_SLAM2::ORBmatcher, compiled from
+// /root/reference/ORB_SLAM2/src/ORBmatcher.cc (unmodified) against oracle/refstub/slam_stub.h + oracle/cvstub
+// (see oracle/Makefile.ref).  Each function builds the stub Frame / KeyFrame / MapPoint objects from the same flat
+// arrays the C ABI of include/orbgpu.h takes, calls the reference method, and flattens the result the same way, so
+// tests can compare reference source == restated oracle == GPU.
+#include "ORBmatcher.h"
+#include "../include/orbgpu.h"
+
+#include <cstring>
+#include <memory>
+
+using namespace ORB_SLAM2;
+
+float Frame::fx, Frame::fy, Frame::cx, Frame::cy;
+float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
+
+struct refm_frame {
+    Frame F;
+    orb_frame_desc d;
+};
+
+static cv::Mat desc_row(const uint8_t *p) {
+    cv::Mat m(1, 32, CV_8UC1);
+    memcpy(m.data, p, 32);
+    return m;
+}
+
+static void set_statics(const refm_frame *f) {   // the reference keeps the image bounds / grid scale in statics (Frame.h:161-162,191-194)
+    Frame::mnMinX = f->d.min_x; Frame::mnMaxX = f->d.max_x; Frame::mnMinY = f->d.min_y; Frame::mnMaxY = f->d.max_y;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);   // ref Frame.cc:217-218
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);
+}
+
+// KeyFrame view of the same data (ref KeyFrame.cc:31-63 copies these members from the Frame)
+static std::unique_ptr<KeyFrame> as_keyframe(const refm_frame *f) {
+    std::unique_ptr<KeyFrame> k(new KeyFrame());
+    k->N = f->F.N; k->mvKeysUn = f->F.mvKeysUn; k->mvuRight = f->F.mvuRight; k->mDescriptors = f->F.mDescriptors;
+    k->mvScaleFactors = f->F.mvScaleFactors; k->mfLogScaleFactor = f->F.mfLogScaleFactor;
+    k->mvpMapPoints.assign(k->N, nullptr);
+    k->mnMinX = (int)f->d.min_x; k->mnMaxX = (int)f->d.max_x; k->mnMinY = (int)f->d.min_y; k->mnMaxY = (int)f->d.max_y;
+    k->mfGridElementWidthInv = Frame::mfGridElementWidthInv; k->mfGridElementHeightInv = Frame::mfGridElementHeightInv;
+    k->mGrid.resize(FRAME_GRID_COLS);
+    for (int i = 0; i < FRAME_GRID_COLS; i++) {
+        k->mGrid[i].resize(FRAME_GRID_ROWS);
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) k->mGrid[i][j] = f->F.mGrid[i][j];
+    }
+    return k;
+}
+
+extern "C" {
+
+int refm_frame_create(const orb_frame_desc *d, refm_frame **out) {
+    refm_frame *f = new refm_frame();
+    f->d = *d;
+    Frame &F = f->F;
+    F.N = d->n;
+    F.mvKeysUn.resize(d->n);
+    for (int i = 0; i < d->n; i++) {
+        const orb_keypoint &k = d->keys_un[i];
+        cv::KeyPoint kp(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id);
+        F.mvKeysUn[i] = kp;
+    }
+    F.mvKeys = F.mvKeysUn;
+    F.mvuRight.assign(d->n, -1.0f);
+    if (d->u_right) F.mvuRight.assign(d->u_right, d->u_right + d->n);
+    F.mDescriptors = cv::Mat(d->n > 0 ? d->n : 1, 32, CV_8UC1);
+    if (d->n) memcpy(F.mDescriptors.data, d->descriptors, (size_t)d->n * 32);
+    F.mvpMapPoints.assign(d->n, nullptr);
+    F.mvbOutlier.assign(d->n, false);
+    F.mvScaleFactors.assign(d->scale_factors, d->scale_factors + d->nlevels);
+    F.mfLogScaleFactor = log(d->nlevels > 1 ? d->scale_factors[1] : 1.2f);
+    set_statics(f);
+    F.AssignFeaturesToGrid();
+    *out = f;
+    return 0;
+}
+void refm_frame_destroy(refm_frame *f) { delete f; }
+
+int refm_frame_features_in_area(refm_frame *f, float x, float y, float r, int min_level, int max_level, int32_t *indices, int capacity,
+                                int *n_out) {
+    set_statics(f);
+    std::vector<size_t> v = f->F.GetFeaturesInArea(x, y, r, min_level, max_level);
+    *n_out = (int)v.size();
+    if ((int)v.size() > capacity) return ORB_ERR_CAPACITY;
+    for (size_t i = 0; i < v.size(); i++) indices[i] = (int32_t)v[i];
+    return 0;
+}
+
+// ref ORBmatcher::SearchForInitialization, ORBmatcher.cc:405-523
+int refm_search_for_initialization(refm_frame *f1, refm_frame *f2, float *prev_matched, int32_t *matches12, int window_size, float nnratio,
+                                   int check_orientation, int *nmatches) {
+    set_statics(f2);
+    std::vector<cv::Point2f> prev(f1->F.N);
+    for (int i = 0; i < f1->F.N; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    *nmatches = matcher.SearchForInitialization(f1->F, f2->F, prev, m12, window_size);
+    for (int i = 0; i < f1->F.N; i++) {
+        matches12[i] = m12[i];
+        prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
+    }
+    return 0;
+}
+
+// ref ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th), ORBmatcher.cc:45-129
+int refm_search_by_projection_points(refm_frame *f, const orb_track_points *P, const uint8_t *claimed, float th, float nnratio,
+                                     int32_t *assigned, int *nmatches) {
+    set_statics(f);
+    Frame &F = f->F;
+    std::vector<std::unique_ptr<MapPoint>> store;
+    std::vector<MapPoint *> pts(P->n);
+    for (int i = 0; i < P->n; i++) {
+        std::unique_ptr<MapPoint> m(new MapPoint());
+        m->id = i;
+        m->mbTrackInView = P->in_view[i] != 0;
+        m->mTrackProjX = P->proj_x[i]; m->mTrackProjY = P->proj_y[i]; m->mTrackProjXR = P->proj_xr[i];
+        m->mnTrackScaleLevel = P->level[i]; m->mTrackViewCos = P->view_cos[i];
+        m->descriptor = desc_row(P->descriptors + (size_t)i * 32);
+        m->nObs = P->obs_positive ? (P->obs_positive[i] ? 1 : 0) : 1;
+        pts[i] = m.get();
+        store.push_back(std::move(m));
+    }
+    MapPoint pre;      // a map point that already sits in the frame with observations (blocks the feature, ref :87-89)
+    pre.id = -2; pre.nObs = 1;
+    for (int i = 0; i < F.N; i++) F.mvpMapPoints[i] = (claimed && claimed[i]) ? &pre : nullptr;
+    ORBmatcher matcher(nnratio, true);
+    *nmatches = matcher.SearchByProjection(F, pts, th);
+    for (int i = 0; i < F.N; i++) {
+        MapPoint *m = F.mvpMapPoints[i];
+        assigned[i] = (m && m->id >= 0) ? m->id : -1;
+        F.mvpMapPoints[i] = nullptr;
+    }
+    return 0;
+}
+
+// ref ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono), ORBmatcher.cc:1331-1473.
+// world_xyz: n x 3 map point positions of the Last features (has_point[i]=0: no map point / outlier); Tcw_cur, Tcw_last:
+// row-major 4x4.  Also returns what the reference computes on the way -- u, v, invz, valid (ref :1362-1379) and the
+// forward/backward flags (:1351-1352) -- so the same numbers can be handed to the flat C ABI.
+int refm_search_by_projection_last(refm_frame *cur, refm_frame *last, const float *world_xyz, const uint8_t *has_point,
+                                   const uint8_t *obs_positive, const uint8_t *claimed, const float *Tcw_cur, const float *Tcw_last,
+                                   float fx, float fy, float cx, float cy, float mbf, float mb, float th, int mono, float nnratio,
+                                   int check_orientation, int32_t *assigned, int *nmatches, float *u_out, float *v_out,
+                                   float *invz_out, uint8_t *valid_out, int *forward_out, int *backward_out) {
+    set_statics(cur);
+    Frame &C = cur->F;
+    Frame &L = last->F;
+    Frame::fx = fx; Frame::fy = fy; Frame::cx = cx; Frame::cy = cy;
+    C.mTcw = cv::Mat(4, 4, CV_32F); L.mTcw = cv::Mat(4, 4, CV_32F);
+    memcpy(C.mTcw.data, Tcw_cur, 64); memcpy(L.mTcw.data, Tcw_last, 64);
+    C.mbf = mbf; C.mb = mb;
+    const int n = L.N;
+    std::vector<std::unique_ptr<MapPoint>> store;
+    for (int i = 0; i < n; i++) {
+        L.mvpMapPoints[i] = nullptr;
+        L.mvbOutlier[i] = false;
+        if (!has_point[i]) continue;
+        std::unique_ptr<MapPoint> m(new MapPoint());
+        m->id = i;
+        m->worldPos = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; k++) m->worldPos.at<float>(k) = world_xyz[3 * i + k];
+        m->descriptor = desc_row(L.mDescriptors.ptr(i));
+        m->nObs = obs_positive ? (obs_positive[i] ? 1 : 0) : 1;
+        L.mvpMapPoints[i] = m.get();
+        store.push_back(std::move(m));
+    }
+    MapPoint pre;
+    pre.id = -2; pre.nObs = 1;
+    for (int i = 0; i < C.N; i++) C.mvpMapPoints[i] = (claimed && claimed[i]) ? &pre : nullptr;
+
+    // the projection exactly as the reference writes it (ORBmatcher.cc:1341-1379), for the flat interface
+    {
+        const cv::Mat Rcw = C.mTcw.rowRange(0, 3).colRange(0, 3);
+        const cv::Mat tcw = C.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat twc = -Rcw.t() * tcw;
+        const cv::Mat Rlw = L.mTcw.rowRange(0, 3).colRange(0, 3);
+        const cv::Mat tlw = L.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat tlc = Rlw * twc + tlw;
+        const bool bMono = mono != 0;
+        *forward_out = tlc.at<float>(2) > C.mb && !bMono;
+        *backward_out = -tlc.at<float>(2) > C.mb && !bMono;
+        for (int i = 0; i < n; i++) {
+            valid_out[i] = 0; u_out[i] = v_out[i] = invz_out[i] = 0;
+            MapPoint *pMP = L.mvpMapPoints[i];
+            if (!pMP) continue;
+            cv::Mat x3Dw = pMP->GetWorldPos();
+            cv::Mat x3Dc = Rcw * x3Dw + tcw;
+            const float xc = x3Dc.at<float>(0);
+            const float yc = x3Dc.at<float>(1);
+            const float invzc = 1.0 / x3Dc.at<float>(2);
+            if (invzc < 0) continue;
+            float u = Frame::fx * xc * invzc + Frame::cx;
+            float v = Frame::fy * yc * invzc + Frame::cy;
+            if (u < Frame::mnMinX || u > Frame::mnMaxX) continue;
+            if (v < Frame::mnMinY || v > Frame::mnMaxY) continue;
+            valid_out[i] = 1; u_out[i] = u; v_out[i] = v; invz_out[i] = invzc;
+        }
+    }
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    *nmatches = matcher.SearchByProjection(C, L, th, mono != 0);
+    for (int i = 0; i < C.N; i++) {
+        MapPoint *m = C.mvpMapPoints[i];
+        assigned[i] = (m && m->id >= 0) ? m->id : -1;
+        C.mvpMapPoints[i] = nullptr;
+    }
+    for (int i = 0; i < n; i++) L.mvpMapPoints[i] = nullptr;
+    return 0;
+}
+
+static void fill_featvec(DBoW2::FeatureVector &fv, int ngroups, const int32_t *off, const int32_t *idx) {
+    fv.clear();
+    for (int g = 0; g < ngroups; g++) {
+        std::vector<unsigned int> v(idx + off[g], idx + off[g + 1]);
+        if (!v.empty()) fv[(DBoW2::NodeId)g] = v;
+    }
+}
+
+// ref ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&), ORBmatcher.cc:159-288
+int refm_search_by_bow(refm_frame *kf, refm_frame *f, int ngroups, const int32_t *kf_off, const int32_t *kf_idx, const int32_t *f_off,
+                       const int32_t *f_idx, const uint8_t *kf_valid, float nnratio, int check_orientation, int32_t *matches,
+                       int *nmatches) {
+    set_statics(f);
+    std::unique_ptr<KeyFrame> K = as_keyframe(kf);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    for (int i = 0; i < K->N; i++)
+        if (kf_valid[i]) {
+            std::unique_ptr<MapPoint> m(new MapPoint());
+            m->id = i;
+            K->mvpMapPoints[i] = m.get();
+            store.push_back(std::move(m));
+        }
+    fill_featvec(K->mFeatVec, ngroups, kf_off, kf_idx);
+    fill_featvec(f->F.mFeatVec, ngroups, f_off, f_idx);
+    std::vector<MapPoint *> out;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    *nmatches = matcher.SearchByBoW(K.get(), f->F, out);
+    for (int i = 0; i < f->F.N; i++) matches[i] = out[i] ? out[i]->id : -1;
+    return 0;
+}
+
+// ref ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&), ORBmatcher.cc:525-658.  Output flattened the way
+// orb_search_by_bow reports it: matches[idx2] = idx1.
+int refm_search_by_bow_kfkf(refm_frame *kf1, refm_frame *kf2, int ngroups, const int32_t *off1, const int32_t *idx1, const int32_t *off2,
+                            const int32_t *idx2, const uint8_t *valid1, const uint8_t *valid2, float nnratio, int check_orientation,
+                            int32_t *matches, int *nmatches) {
+    set_statics(kf2);
+    std::unique_ptr<KeyFrame> K1 = as_keyframe(kf1), K2 = as_keyframe(kf2);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    for (int i = 0; i < K1->N; i++)
+        if (valid1[i]) { std::unique_ptr<MapPoint> m(new MapPoint()); m->id = i; K1->mvpMapPoints[i] = m.get(); store.push_back(std::move(m)); }
+    for (int i = 0; i < K2->N; i++)
+        if (!valid2 || valid2[i]) { std::unique_ptr<MapPoint> m(new MapPoint()); m->id = i; K2->mvpMapPoints[i] = m.get(); store.push_back(std::move(m)); }
+    fill_featvec(K1->mFeatVec, ngroups, off1, idx1);
+    fill_featvec(K2->mFeatVec, ngroups, off2, idx2);
+    std::vector<MapPoint *> out;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    *nmatches = matcher.SearchByBoW(K1.get(), K2.get(), out);
+    for (int i = 0; i < K2->N; i++) matches[i] = -1;
+    for (int i1 = 0; i1 < K1->N; i1++)
+        if (out[i1]) matches[out[i1]->id] = i1;
+    return 0;
+}
+
+// ref ORBmatcher::DescriptorDistance, ORBmatcher.cc:1650-1666
+int refm_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist) {
+    for (int i = 0; i < n; i++) dist[i] = ORBmatcher::DescriptorDistance(desc_row(a + (size_t)i * 32), desc_row(b + (size_t)i * 32));
+    return 0;
+}
+
+}  // extern "C"

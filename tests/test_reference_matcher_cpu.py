@@ -1,0 +1,135 @@
+"""CPU test (no GPU): the flat-array matcher oracle against oracle/_ref/liborbmatcher_ref.so -- the reference's OWN
+ORBmatcher.cc compiled unmodified against stub Frame / KeyFrame / MapPoint classes (oracle/refstub, oracle/Makefile.ref).
+Match lists, counts and the updated vbPrevMatched must be identical.  This pins M1, M2, M3, M6, M7, M8 and the
+GetFeaturesInArea traversal (S1) of SURVEY 8(a) to the reference's source."""
+import numpy as np
+import pytest
+
+from ar_orbslam2_b200.synth import SplitMix64, shifted_frame, synth_descriptors, synth_frame
+
+W, H = 752, 480
+FX = FY = np.float32(435.2)
+CX, CY = np.float32(367.2), np.float32(252.2)
+
+
+@pytest.fixture(scope="module")
+def ref(oracle):
+    if not oracle.ref_matcher_available():
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    return oracle
+
+
+@pytest.fixture(scope="module")
+def scene(oracle):
+    a = synth_frame(W, H, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    ex = oracle.RefExtractor(2000)
+    ka, da = ex.extract(a)
+    kb, db = ex.extract(b)
+    return dict(ka=ka, da=da, kb=kb, db=db, scale=ex.tables()["scale"])
+
+
+def frames(scene, ref, which, u_right=None):
+    from ar_orbslam2_b200.tracking import Frame
+    k, d = scene["k" + which], scene["d" + which]
+    bounds = (0.0, float(W), 0.0, float(H))
+    return (Frame(k, d, scene["scale"], bounds, u_right=u_right, backend=ref.OracleBackend()),
+            Frame(k, d, scene["scale"], bounds, u_right=u_right, backend=ref.ReferenceSourceBackend()))
+
+
+def test_descriptor_distance(ref):
+    a, b = synth_descriptors(4000, 1), synth_descriptors(4000, 2)
+    assert np.array_equal(ref.descriptor_distance(a, b), ref.refm_descriptor_distance(a, b))
+
+
+def test_features_in_area(scene, ref):
+    o, r = frames(scene, ref, "a")
+    rng = SplitMix64(5)
+    for _ in range(200):
+        x, y = rng.next() % (W + 40) - 20.0, rng.next() % (H + 40) - 20.0
+        rad = 3.0 + rng.next() % 120
+        lo, hi = int(rng.next() % 9) - 1, int(rng.next() % 9) - 1
+        assert np.array_equal(o.GetFeaturesInArea(x, y, rad, lo, hi), r.GetFeaturesInArea(x, y, rad, lo, hi))
+
+
+@pytest.mark.parametrize("ori,ratio", [(True, 0.9), (False, 0.9), (True, 0.6)])
+def test_search_for_initialization(scene, ref, ori, ratio):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    o1, r1 = frames(scene, ref, "a")
+    o2, r2 = frames(scene, ref, "b")
+    prev = np.stack([scene["ka"]["x"], scene["ka"]["y"]], 1).astype(np.float32).copy()
+    po, pr = prev.copy(), prev.copy()
+    for _ in range(2):   # second call starts from the updated vbPrevMatched, as Tracking does
+        no, mo = ORBmatcher(ratio, ori, backend=ref.OracleBackend()).SearchForInitialization(o1, o2, po, 100)
+        nr, mr = ORBmatcher(ratio, ori, backend=ref.ReferenceSourceBackend()).SearchForInitialization(r1, r2, pr, 100)
+        assert nr > 50 and no == nr and np.array_equal(mo, mr) and np.array_equal(po, pr)
+
+
+def test_search_by_projection_points(scene, ref):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    ur = np.where(np.arange(len(scene["kb"])) % 3 == 0, scene["kb"]["x"] - 5.0, -1.0).astype(np.float32)
+    o, r = frames(scene, ref, "b", ur)
+    k = scene["ka"]
+    n = len(k)
+    rng = SplitMix64(9)
+    in_view = np.array([rng.next() % 10 != 0 for _ in range(n)], np.uint8)
+    px, py = (k["x"] + 7).astype(np.float32), (k["y"] + 4).astype(np.float32)
+    pxr = (px - 6).astype(np.float32)
+    level = np.clip(k["octave"] + np.array([rng.next() % 3 - 1 for _ in range(n)]), 0, 7).astype(np.int32)
+    vc = np.array([0.999 if rng.next() % 2 else 0.9 for _ in range(n)], np.float32)
+    claimed = (np.arange(o.N) % 13 == 0).astype(np.uint8)
+    obs = (np.arange(n) % 4 != 0).astype(np.uint8)
+    for th, ratio in ((1.0, 0.8), (3.0, 0.8), (3.0, 0.6)):
+        no, ao = ORBmatcher(ratio, backend=ref.OracleBackend()).SearchByProjectionPoints(o, in_view, px, py, pxr, level, vc, scene["da"], th, claimed, obs)
+        nr, ar = ORBmatcher(ratio, backend=ref.ReferenceSourceBackend()).SearchByProjectionPoints(r, in_view, px, py, pxr, level, vc, scene["da"], th, claimed, obs)
+        assert nr > 100 and no == nr and np.array_equal(ao, ar), (th, ratio)
+
+
+@pytest.mark.parametrize("mono,tz", [(True, 0.0), (False, 0.3), (False, -0.3), (False, 0.0)])
+def test_search_by_projection_last(scene, ref, mono, tz):
+    """Last = frame A with a synthetic map point per feature, Cur = frame A's features seen from a translated
+    pose; forward / backward / neither by the z translation vs the baseline mb."""
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    k = scene["ka"]
+    n = len(k)
+    ur = np.where(np.arange(n) % 3 == 0, k["x"] - 5.0, -1.0).astype(np.float32)
+    oc, rc = frames(scene, ref, "a", ur)
+    ol, rl = frames(scene, ref, "a")
+    z = np.array([2 + (SplitMix64(i).next() % 1000) / 100 for i in range(n)], np.float32)
+    xyz = np.stack([(k["x"] - CX) * z / FX, (k["y"] - CY) * z / FY, z], 1).astype(np.float32)
+    has = (np.arange(n) % 17 != 0).astype(np.uint8)
+    obs = (np.arange(n) % 5 != 0).astype(np.uint8)
+    claimed = (np.arange(n) % 11 == 0).astype(np.uint8)
+    Tc = np.eye(4, dtype=np.float32); Tc[:3, 3] = (0.05, 0.02, tz)
+    Tl = np.eye(4, dtype=np.float32)
+    mbf, mb, th = 40.0, 0.11, 15.0
+    R = ref.refm_search_by_projection_last(rc, rl, xyz, has, obs, claimed, Tc, Tl, FX, FY, CX, CY, mbf, mb, th, mono, 0.9, True)
+    assert R["nmatches"] > 50
+    assert R["forward"] == ((not mono) and -tz > mb) and R["backward"] == ((not mono) and tz > mb)   # ref :1351-1352
+    no, ao = ORBmatcher(0.9, True, backend=ref.OracleBackend()).SearchByProjectionLast(
+        oc, R["valid"], R["u"], R["v"], R["invz"], k["octave"].astype(np.int32), k["angle"], scene["da"], th,
+        forward=R["forward"], backward=R["backward"], mbf=mbf, claimed=claimed, obs_positive=obs)
+    assert no == R["nmatches"] and np.array_equal(ao, R["assigned"])
+
+
+@pytest.mark.parametrize("kfkf", [False, True])
+def test_search_by_bow(scene, ref, kfkf):
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    ok, rk = frames(scene, ref, "a")
+    of, rf = frames(scene, ref, "b")
+
+    def groups(k, dx, dy):
+        node = ((k["y"] - dy) // 40).astype(np.int64) * 19 + ((k["x"] - dx) // 40).astype(np.int64)
+        return node, np.argsort(node, kind="stable")
+    na, oa = groups(scene["ka"], 0, 0)
+    nb, ob = groups(scene["kb"], 7, 4)
+    kf_off, f_off, kf_idx, f_idx = [0], [0], [], []
+    for c in np.intersect1d(na, nb):
+        kf_idx += oa[na[oa] == c].tolist(); f_idx += ob[nb[ob] == c].tolist()
+        kf_off.append(len(kf_idx)); f_off.append(len(f_idx))
+    kv = (np.arange(ok.N) % 7 != 0).astype(np.uint8)
+    fv = (np.arange(of.N) % 9 != 0).astype(np.uint8) if kfkf else None
+    for ori in (True, False):
+        no, mo = ORBmatcher(0.7, ori, backend=ref.OracleBackend()).SearchByBoW(ok, of, kf_off, kf_idx, f_off, f_idx, kv, fv, kfkf)
+        nr, mr = ref.refm_search_by_bow(rk, rf, kf_off, kf_idx, f_off, f_idx, kv, fv, kfkf, 0.7, ori)
+        assert nr > 100 and no == nr and np.array_equal(mo, mr)

@@ -162,3 +162,29 @@ def test_rot_hist_filter(oracle, gpu_lib):
     assert np.array_equal(rot_hist_filter(a, b), oracle.rot_hist_filter(a, b))
     # the reference's 1/30 factor: only bins 0..12 can ever be hit
     assert np.array_equal(rot_hist_filter(a[:5], a[:5]), np.ones(5, bool))
+
+
+def test_gpu_equals_reference_source_matchers(scene, oracle, gpu_lib):
+    """liborbgpu directly against the reference's compiled ORBmatcher.cc (oracle/_ref), see tests/test_reference_matcher_cpu.py."""
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+    if not oracle.ref_matcher_available():
+        pytest.skip("oracle/_ref not built")
+    bounds = (0.0, float(W), 0.0, float(H))
+    mk = lambda which, be: Frame(scene["k" + which], scene["d" + which], scene["scale"], bounds, backend=be)
+    g1, g2 = mk("a", None), mk("b", None)
+    rb = oracle.ReferenceSourceBackend()
+    r1, r2 = mk("a", rb), mk("b", rb)
+    prev = np.stack([scene["ka"]["x"], scene["ka"]["y"]], 1).astype(np.float32).copy()
+    pg, pr = prev.copy(), prev.copy()
+    ng, mg = ORBmatcher(0.9, True).SearchForInitialization(g1, g2, pg, 100)
+    nr, mr = ORBmatcher(0.9, True, backend=rb).SearchForInitialization(r1, r2, pr, 100)
+    assert nr > 100 and ng == nr and np.array_equal(mg, mr) and np.array_equal(pg, pr)
+    k = scene["ka"]
+    n = len(k)
+    in_view = (np.arange(n) % 10 != 0).astype(np.uint8)
+    px, py = (k["x"] + 7).astype(np.float32), (k["y"] + 4).astype(np.float32)
+    args = (in_view, px, py, (px - 6).astype(np.float32), k["octave"].astype(np.int32), np.full(n, 0.9, np.float32), scene["da"], 3.0,
+            (np.arange(g2.N) % 13 == 0).astype(np.uint8), (np.arange(n) % 4 != 0).astype(np.uint8))
+    ng, ag = ORBmatcher(0.8).SearchByProjectionPoints(g2, *args)
+    nr, ar = ORBmatcher(0.8, backend=rb).SearchByProjectionPoints(r2, *args)
+    assert nr > 100 and ng == nr and np.array_equal(ag, ar)
