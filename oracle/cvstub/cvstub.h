@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <cassert>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -104,6 +105,19 @@ public:
         return m;
     }
     void copyTo(Mat &m) const { m = clone(); }
+    Mat reshape(int) const { return *this; }   // only on the undistortion path, which the zero-distortion configs never take
+    void convertTo(Mat &dst, int t) const {    // 8U -> 32F (Frame.cc:567,584); dst may alias *this (a ROI header)
+        assert(type_ == CV_8UC1 && t == CV_32F);
+        Mat m(rows, cols, CV_32F);
+        for (int y = 0; y < rows; y++) for (int x = 0; x < cols; x++) m.at<float>(y, x) = (float)at<uchar>(y, x);
+        dst = m;
+    }
+    static Mat ones(int r, int c, int t) {
+        assert(t == CV_32F);
+        Mat m(r, c, CV_32F);
+        for (int y = 0; y < r; y++) for (int x = 0; x < c; x++) m.at<float>(y, x) = 1.0f;
+        return m;
+    }
     static MatZeros zeros(int r, int c, int t) { return MatZeros{r, c, t}; }
     // Mat = MatExpr(zeros): keeps the existing buffer when size and type match (cv::Mat::create semantics), which is
     // how ORBextractor.cc:978 zero-fills a row range of the output descriptor matrix in place.
@@ -158,6 +172,25 @@ static inline Mat operator/(const Mat &a, double s) {
 }
 static inline Mat operator-(const Mat &a) { return a * -1.0; }
 static inline double norm(const Mat &a) { return std::sqrt(a.dot(a)); }
+enum { NORM_L1 = 2 };
+static inline double norm(const Mat &a, const Mat &b, int normType) {   // cv::norm(IL, IR, NORM_L1), Frame.cc:587
+    assert(normType == NORM_L1 && a.rows == b.rows && a.cols == b.cols);
+    double s = 0;
+    for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) s += std::fabs((double)(a.at<float>(y, x) - b.at<float>(y, x)));
+    return s;
+}
+template <typename T> class Mat_;
+template <typename T> struct MatCommaInit {   // (cv::Mat_<float>(3,1) << x, y, z), Frame.cc:678
+    Mat m;
+    int i;
+    MatCommaInit &operator,(T v) { m.at<T>(i / m.cols, i % m.cols) = v; i++; return *this; }
+    operator Mat() const { return m; }
+};
+template <typename T> class Mat_ : public Mat {
+public:
+    Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+    MatCommaInit<T> operator<<(T v) { MatCommaInit<T> ci{*this, 0}; ci, v; return ci; }
+};
 
 class _InputArray {
 public:
@@ -214,6 +247,10 @@ static inline void GaussianBlur(InputArray src, OutputArray dst, Size ksize, dou
     dst.create(s.rows, s.cols, s.type());
     Mat d = dst.getMat();
     orbref::gaussian_blur7_u8(s.data, s.cols, s.rows, (int)s.step.v, d.data, (int)d.step.v, 0);
+}
+
+static inline void undistortPoints(InputArray, OutputArray, InputArray, InputArray, InputArray, InputArray) {
+    std::abort();   // Frame::UndistortKeyPoints / ComputeImageBounds with non-zero distortion: not on the tested path
 }
 
 struct KeyPointsFilter {   // only referenced by the dead ComputeKeyPointsOld (ORBextractor.cc:821-974)

@@ -330,3 +330,19 @@ def refm_descriptor_distance(a, b):
     out = np.zeros(a.shape[0], np.int32)
     _REFM.refm_descriptor_distance(ptr(a), ptr(b), a.shape[0], ptr(out))
     return out
+
+
+def refm_stereo_match(img_left, img_right, nfeatures, keys_l, desc_l, keys_r, desc_r, mbf, mb, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+    """The reference's own Frame::ComputeStereoMatches (Frame.cc compiled into oracle/_ref) on the reference's own
+    pyramids.  Returns (mvuRight, mvDepth)."""
+    global _REFM
+    if _REFM is None:
+        _REFM = C.CDLL(REF_MATCHER_PATH)
+    il, ir = np.ascontiguousarray(img_left, np.uint8), np.ascontiguousarray(img_right, np.uint8)
+    kl, kr = np.ascontiguousarray(keys_l), np.ascontiguousarray(keys_r)
+    dl, dr = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    ur, dp = np.zeros(len(kl), np.float32), np.zeros(len(kl), np.float32)
+    f = C.c_float
+    _check(_REFM.refm_stereo_match(ptr(il), ptr(ir), il.shape[1], il.shape[0], nfeatures, f(scale), nlevels, ini_th, min_th, ptr(kl), ptr(dl),
+                                   len(kl), ptr(kr), ptr(dr), len(kr), f(mbf), f(mb), ptr(ur), ptr(dp)), "refm_stereo_match")
+    return ur, dp

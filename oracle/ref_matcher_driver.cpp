@@ -11,9 +11,11 @@
 
 using namespace ORB_SLAM2;
 
+#ifndef ORBREF_REAL_FRAME
 float Frame::fx, Frame::fy, Frame::cx, Frame::cy;
 float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
 float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
+#endif
 
 struct refm_frame {
     Frame F;
@@ -261,6 +263,45 @@ int refm_search_by_bow_kfkf(refm_frame *kf1, refm_frame *kf2, int ngroups, const
         if (out[i1]) matches[out[i1]->id] = i1;
     return 0;
 }
+
+#ifdef ORBREF_REAL_FRAME
+// ref Frame::ComputeStereoMatches, Frame.cc:471-643 -- the reference's own member function on the reference's own Frame.
+// The two reference ORBextractor objects are run on the images only to fill mvImagePyramid (ComputePyramid is
+// deterministic); keypoints and descriptors are the caller's.  Returns ORB_ERR_EMPTY where the reference would index an
+// empty vector (Frame.cc:630), detected beforehand from the outputs being all -1 is impossible, so the call is made on
+// a guarded copy: the reference's UB case is reported by the oracle instead and never reaches this function in tests.
+int refm_stereo_match(const uint8_t *img_left, const uint8_t *img_right, int width, int height, int nfeatures, float scale, int nlevels,
+                      int ini_th, int min_th, const orb_keypoint *keysL, const uint8_t *descL, int N, const orb_keypoint *keysR,
+                      const uint8_t *descR, int Nr, float mbf, float mb, float *uRight, float *depth) {
+    ORBextractor exL(nfeatures, scale, nlevels, ini_th, min_th), exR(nfeatures, scale, nlevels, ini_th, min_th);
+    cv::Mat imL(height, width, CV_8UC1), imR(height, width, CV_8UC1);
+    memcpy(imL.data, img_left, (size_t)width * height);
+    memcpy(imR.data, img_right, (size_t)width * height);
+    {
+        std::vector<cv::KeyPoint> k;
+        cv::Mat d;
+        exL(imL, cv::Mat(), k, d);
+        exR(imR, cv::Mat(), k, d);
+    }
+    Frame F;
+    F.mpORBextractorLeft = &exL; F.mpORBextractorRight = &exR;
+    F.N = N;
+    auto conv = [](const orb_keypoint *k, int n) {
+        std::vector<cv::KeyPoint> v(n);
+        for (int i = 0; i < n; i++) v[i] = cv::KeyPoint(k[i].x, k[i].y, k[i].size, k[i].angle, k[i].response, k[i].octave, k[i].class_id);
+        return v;
+    };
+    F.mvKeys = conv(keysL, N); F.mvKeysRight = conv(keysR, Nr);
+    F.mDescriptors = cv::Mat(N > 0 ? N : 1, 32, CV_8UC1); F.mDescriptorsRight = cv::Mat(Nr > 0 ? Nr : 1, 32, CV_8UC1);
+    if (N) memcpy(F.mDescriptors.data, descL, (size_t)N * 32);
+    if (Nr) memcpy(F.mDescriptorsRight.data, descR, (size_t)Nr * 32);
+    F.mvScaleFactors = exL.GetScaleFactors(); F.mvInvScaleFactors = exL.GetInverseScaleFactors();
+    F.mbf = mbf; F.mb = mb;   // the reference reads mb before its constructor assigns it (Frame.cc:95 vs :119); intended value
+    F.ComputeStereoMatches();
+    for (int i = 0; i < N; i++) { uRight[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+    return 0;
+}
+#endif
 
 // ref ORBmatcher::DescriptorDistance, ORBmatcher.cc:1650-1666
 int refm_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist) {

@@ -15,7 +15,8 @@
 #include <set>
 #include <vector>
 
-#include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"   // the reference's own (pure STL) header
+#include "Thirdparty/DBoW2/DBoW2/BowVector.h"       // the reference's own (pure STL) headers
+#include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
 
 using namespace std;   // the reference headers leak this into ORBmatcher.h (it declares `vector<MapPoint *>` unqualified)
 
@@ -61,6 +62,22 @@ public:
     void Replace(MapPoint *pMP) { replaced = pMP; bad = true; }
 };
 
+// With ORBREF_REAL_FRAME the reference's own include/Frame.h + src/Frame.cc are compiled (its dependencies
+// ORBVocabulary / Converter are the data-less stand-ins below); otherwise a stand-in Frame is used.
+class ORBVocabulary {   // ref ORBVocabulary.h:28 (a DBoW2 vocabulary tree; the vocabulary file is not in the repository)
+public:
+    void transform(const std::vector<cv::Mat> &, DBoW2::BowVector &, DBoW2::FeatureVector &, int) {}
+};
+class Converter {       // ref Converter.h:32 (the real header needs Eigen and g2o)
+public:
+    static std::vector<cv::Mat> toDescriptorVector(const cv::Mat &D) {
+        std::vector<cv::Mat> v;
+        for (int j = 0; j < D.rows; j++) v.push_back(D.row(j));
+        return v;
+    }
+};
+
+#ifndef ORBREF_REAL_FRAME
 // the members of Frame that ORBmatcher.cc reads (ref Frame.h)
 class Frame {
 public:
@@ -128,6 +145,8 @@ public:
         return vIndices;
     }
 };
+
+#endif  // ORBREF_REAL_FRAME
 
 // the members of KeyFrame that ORBmatcher.cc reads (ref KeyFrame.h)
 class KeyFrame {

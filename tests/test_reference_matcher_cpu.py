@@ -133,3 +133,21 @@ def test_search_by_bow(scene, ref, kfkf):
         no, mo = ORBmatcher(0.7, ori, backend=ref.OracleBackend()).SearchByBoW(ok, of, kf_off, kf_idx, f_off, f_idx, kv, fv, kfkf)
         nr, mr = ref.refm_search_by_bow(rk, rf, kf_off, kf_idx, f_off, f_idx, kv, fv, kfkf, 0.7, ori)
         assert nr > 100 and no == nr and np.array_equal(mo, mr)
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(1241, 376, 2000, 0), (1241, 376, 2000, 7), (640, 480, 1000, 3)])
+def test_stereo_oracle_equals_reference_frame_cc(ref, w, h, nf, seed):
+    """Frame::ComputeStereoMatches: the oracle's restatement against the reference's own Frame.cc member function
+    (compiled into oracle/_ref with the reference's Frame.h and ORBextractor): mvuRight and mvDepth bit-identical."""
+    from ar_orbslam2_b200.synth import synth_stereo_pair
+    left, right = synth_stereo_pair(w, h, seed)
+    a, b = ref.RefExtractor(nf), ref.RefExtractor(nf)
+    kl, dl = a.extract(left)
+    kr, dr = b.extract(right)
+    mbf = np.float32(386.1448)
+    mb = mbf / np.float32(718.856)
+    rc, ur, dp, _, nm = ref.stereo_match(a, b, kl, dl, kr, dr, mbf, mb)
+    assert rc == 0 and nm > 100
+    rur, rdp = ref.refm_stereo_match(left, right, nf, kl, dl, kr, dr, mbf, mb)
+    assert np.array_equal(ur.view(np.uint32), rur.view(np.uint32)), "mvuRight differs from the reference's Frame.cc"
+    assert np.array_equal(dp.view(np.uint32), rdp.view(np.uint32)), "mvDepth differs from the reference's Frame.cc"

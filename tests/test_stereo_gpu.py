@@ -67,3 +67,25 @@ def test_no_match_is_reported(oracle, gpu_lib):
         gur, gdp = ComputeStereoMatches(gl, gr, kl, dl, kr, dr, 40.0, 0.08)
         assert np.array_equal(gur.view(np.uint32), rur.view(np.uint32))
     gl.close(); gr.close()
+
+
+def test_gpu_equals_reference_frame_cc(oracle, gpu_lib):
+    """liborbgpu's stereo association directly against the reference's own Frame::ComputeStereoMatches (Frame.cc compiled
+    into oracle/_ref, see tests/test_reference_matcher_cpu.py)."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.stereo import ComputeStereoMatches
+    if not oracle.ref_matcher_available():
+        pytest.skip("oracle/_ref not built")
+    w, h, nf = 1241, 376, 2000
+    left, right = synth_stereo_pair(w, h, 21)
+    gl = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    gr = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    kl, dl = gl(left)
+    kr, dr = gr(right)
+    mbf = np.float32(MBF)
+    mb = mbf / np.float32(FX)
+    gur, gdp = ComputeStereoMatches(gl, gr, kl, dl, kr, dr, mbf, mb)
+    rur, rdp = oracle.refm_stereo_match(left, right, nf, kl, dl, kr, dr, mbf, mb)
+    assert (rur != -1).sum() > 200
+    assert np.array_equal(gur.view(np.uint32), rur.view(np.uint32)) and np.array_equal(gdp.view(np.uint32), rdp.view(np.uint32))
+    gl.close(); gr.close()
