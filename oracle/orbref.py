@@ -346,3 +346,37 @@ def refm_stereo_match(img_left, img_right, nfeatures, keys_l, desc_l, keys_r, de
     _check(_REFM.refm_stereo_match(ptr(il), ptr(ir), il.shape[1], il.shape[0], nfeatures, f(scale), nlevels, ini_th, min_th, ptr(kl), ptr(dl),
                                    len(kl), ptr(kr), ptr(dr), len(kr), f(mbf), f(mb), ptr(ur), ptr(dp)), "refm_stereo_match")
     return ur, dp
+
+
+def refm_search_by_projection_kf(cur, kf, world_xyz, usable, max_dist, min_dist, claimed, Tcw_cur, fx, fy, cx, cy, th, orb_dist, nnratio, check_ori):
+    """Reference SearchByProjection(Frame&, KeyFrame*, set<MapPoint*>, th, ORBdist), ORBmatcher.cc:1475-1602."""
+    L = cur.B.L
+    n = kf.N
+    a = [np.ascontiguousarray(world_xyz, np.float32), np.ascontiguousarray(usable, np.uint8), np.ascontiguousarray(max_dist, np.float32),
+         np.ascontiguousarray(min_dist, np.float32), np.ascontiguousarray(claimed, np.uint8), np.ascontiguousarray(Tcw_cur, np.float32)]
+    assigned = np.full(cur.N, -1, np.int32)
+    u, v = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    lvl, valid = np.zeros(n, np.int32), np.zeros(n, np.uint8)
+    nm = C.c_int()
+    f = C.c_float
+    _check(L.refm_search_by_projection_kf(cur._h, kf._h, *[ptr(x) for x in a], f(fx), f(fy), f(cx), f(cy), f(th), int(orb_dist), f(nnratio),
+                                          int(check_ori), ptr(assigned), C.byref(nm), ptr(u), ptr(v), ptr(lvl), ptr(valid)), "refm kf")
+    return dict(assigned=assigned, nmatches=nm.value, u=u, v=v, level=lvl, valid=valid)
+
+
+def refm_search_by_projection_sim3(kf, Scw, world_xyz, normal_xyz, usable, max_dist, min_dist, claimed, fx, fy, cx, cy, th, nnratio):
+    """Reference SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th), ORBmatcher.cc:290-403."""
+    L = kf.B.L
+    xyz = np.ascontiguousarray(world_xyz, np.float32)
+    n = xyz.shape[0]
+    a = [np.ascontiguousarray(normal_xyz, np.float32), np.ascontiguousarray(usable, np.uint8), np.ascontiguousarray(max_dist, np.float32),
+         np.ascontiguousarray(min_dist, np.float32), np.ascontiguousarray(claimed, np.uint8)]
+    S = np.ascontiguousarray(Scw, np.float32)
+    assigned = np.full(kf.N, -1, np.int32)
+    u, v = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    lvl, valid = np.zeros(n, np.int32), np.zeros(n, np.uint8)
+    nm = C.c_int()
+    f = C.c_float
+    _check(L.refm_search_by_projection_sim3(kf._h, ptr(S), n, ptr(xyz), *[ptr(x) for x in a], f(fx), f(fy), f(cx), f(cy), int(th), f(nnratio),
+                                            ptr(assigned), C.byref(nm), ptr(u), ptr(v), ptr(lvl), ptr(valid)), "refm sim3")
+    return dict(assigned=assigned, nmatches=nm.value, u=u, v=v, level=lvl, valid=valid)

@@ -210,6 +210,139 @@ int refm_search_by_projection_last(refm_frame *cur, refm_frame *last, const floa
     return 0;
 }
 
+// ref ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist),
+// ORBmatcher.cc:1475-1602 (relocalisation refinement).  KF map point i sits at world_xyz[i] with distance-invariance range
+// [min_dist, max_dist]; usable[i]=0: no point / bad / already found.  Also returns the per-point quantities the reference
+// computes before its candidate loop (:1499-1531) for the flat interface: valid, u, v, predicted level.
+int refm_search_by_projection_kf(refm_frame *cur, refm_frame *kf, const float *world_xyz, const uint8_t *usable, const float *max_dist,
+                                 const float *min_dist, const uint8_t *claimed, const float *Tcw_cur, float fx, float fy, float cx, float cy,
+                                 float th, int orb_dist, float nnratio, int check_orientation, int32_t *assigned, int *nmatches,
+                                 float *u_out, float *v_out, int32_t *level_out, uint8_t *valid_out) {
+    set_statics(cur);
+    Frame &C = cur->F;
+    Frame::fx = fx; Frame::fy = fy; Frame::cx = cx; Frame::cy = cy;
+    C.mTcw = cv::Mat(4, 4, CV_32F);
+    memcpy(C.mTcw.data, Tcw_cur, 64);
+    std::unique_ptr<KeyFrame> K = as_keyframe(kf);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    std::set<MapPoint *> already;
+    for (int i = 0; i < K->N; i++) {
+        if (!usable[i]) continue;
+        std::unique_ptr<MapPoint> m(new MapPoint());
+        m->id = i;
+        m->worldPos = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; k++) m->worldPos.at<float>(k) = world_xyz[3 * i + k];
+        m->mfMaxDistance = max_dist[i]; m->mfMinDistance = min_dist[i];
+        m->descriptor = desc_row(K->mDescriptors.ptr(i));
+        K->mvpMapPoints[i] = m.get();
+        store.push_back(std::move(m));
+    }
+    MapPoint pre;
+    pre.id = -2; pre.nObs = 1;
+    for (int i = 0; i < C.N; i++) C.mvpMapPoints[i] = (claimed && claimed[i]) ? &pre : nullptr;
+    {   // ref :1479-1531
+        const cv::Mat Rcw = C.mTcw.rowRange(0, 3).colRange(0, 3);
+        const cv::Mat tcw = C.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat Ow = -Rcw.t() * tcw;
+        for (int i = 0; i < K->N; i++) {
+            valid_out[i] = 0; u_out[i] = v_out[i] = 0; level_out[i] = 0;
+            MapPoint *pMP = K->mvpMapPoints[i];
+            if (!pMP) continue;
+            cv::Mat x3Dw = pMP->GetWorldPos();
+            cv::Mat x3Dc = Rcw * x3Dw + tcw;
+            const float xc = x3Dc.at<float>(0);
+            const float yc = x3Dc.at<float>(1);
+            const float invzc = 1.0 / x3Dc.at<float>(2);
+            const float u = Frame::fx * xc * invzc + Frame::cx;
+            const float v = Frame::fy * yc * invzc + Frame::cy;
+            if (u < Frame::mnMinX || u > Frame::mnMaxX) continue;
+            if (v < Frame::mnMinY || v > Frame::mnMaxY) continue;
+            cv::Mat PO = x3Dw - Ow;
+            float dist3D = cv::norm(PO);
+            const float maxDistance = pMP->GetMaxDistanceInvariance();
+            const float minDistance = pMP->GetMinDistanceInvariance();
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            valid_out[i] = 1; u_out[i] = u; v_out[i] = v;
+            level_out[i] = pMP->PredictScale(dist3D, C.mfLogScaleFactor);
+        }
+    }
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    *nmatches = matcher.SearchByProjection(C, K.get(), already, th, orb_dist);
+    for (int i = 0; i < C.N; i++) {
+        MapPoint *m = C.mvpMapPoints[i];
+        assigned[i] = (m && m->id >= 0) ? m->id : -1;
+        C.mvpMapPoints[i] = nullptr;
+    }
+    return 0;
+}
+
+// ref ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, vector<MapPoint*> &vpMatched, th),
+// ORBmatcher.cc:290-403 (loop closing).  n candidate points (position, normal, distance range); claimed[idx] = vpMatched[idx] != NULL
+// on entry.  Returns the reference's pre-loop quantities (:311-360) for the flat interface.
+int refm_search_by_projection_sim3(refm_frame *kf, const float *Scw, int n, const float *world_xyz, const float *normal_xyz,
+                                   const uint8_t *usable, const float *max_dist, const float *min_dist, const uint8_t *claimed,
+                                   float fx, float fy, float cx, float cy, int th, float nnratio, int32_t *assigned, int *nmatches,
+                                   float *u_out, float *v_out, int32_t *level_out, uint8_t *valid_out) {
+    set_statics(kf);
+    std::unique_ptr<KeyFrame> K = as_keyframe(kf);
+    K->fx = fx; K->fy = fy; K->cx = cx; K->cy = cy;
+    std::vector<std::unique_ptr<MapPoint>> store;
+    std::vector<MapPoint *> pts(n);
+    MapPoint badpt;
+    badpt.bad = true;
+    for (int i = 0; i < n; i++) {
+        if (!usable[i]) { pts[i] = &badpt; continue; }
+        std::unique_ptr<MapPoint> m(new MapPoint());
+        m->id = i;
+        m->worldPos = cv::Mat(3, 1, CV_32F); m->normal = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; k++) { m->worldPos.at<float>(k) = world_xyz[3 * i + k]; m->normal.at<float>(k) = normal_xyz[3 * i + k]; }
+        m->mfMaxDistance = max_dist[i]; m->mfMinDistance = min_dist[i];
+        m->descriptor = desc_row(kf->F.mDescriptors.ptr(i % kf->F.N));   // descriptor of the matching feature, as the scenario plants it
+        pts[i] = m.get();
+        store.push_back(std::move(m));
+    }
+    MapPoint pre;
+    pre.id = -2;
+    std::vector<MapPoint *> matched(K->N, nullptr);
+    for (int i = 0; i < K->N; i++) if (claimed && claimed[i]) matched[i] = &pre;
+    cv::Mat S(4, 4, CV_32F);
+    memcpy(S.data, Scw, 64);
+    {   // ref :298-360
+        cv::Mat sRcw = S.rowRange(0, 3).colRange(0, 3);
+        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+        cv::Mat Rcw = sRcw / scw;
+        cv::Mat tcw = S.rowRange(0, 3).col(3) / scw;
+        cv::Mat Ow = -Rcw.t() * tcw;
+        for (int i = 0; i < n; i++) {
+            valid_out[i] = 0; u_out[i] = v_out[i] = 0; level_out[i] = 0;
+            MapPoint *pMP = pts[i];
+            if (pMP->isBad()) continue;
+            cv::Mat p3Dw = pMP->GetWorldPos();
+            cv::Mat p3Dc = Rcw * p3Dw + tcw;
+            if (p3Dc.at<float>(2) < 0.0) continue;
+            const float invz = 1 / p3Dc.at<float>(2);
+            const float x = p3Dc.at<float>(0) * invz;
+            const float y = p3Dc.at<float>(1) * invz;
+            const float u = fx * x + cx;
+            const float v = fy * y + cy;
+            if (!K->IsInImage(u, v)) continue;
+            const float maxDistance = pMP->GetMaxDistanceInvariance();
+            const float minDistance = pMP->GetMinDistanceInvariance();
+            cv::Mat PO = p3Dw - Ow;
+            const float dist = cv::norm(PO);
+            if (dist < minDistance || dist > maxDistance) continue;
+            cv::Mat Pn = pMP->GetNormal();
+            if (PO.dot(Pn) < 0.5 * dist) continue;
+            valid_out[i] = 1; u_out[i] = u; v_out[i] = v;
+            level_out[i] = pMP->PredictScale(dist, K->mfLogScaleFactor);
+        }
+    }
+    ORBmatcher matcher(nnratio, true);
+    *nmatches = matcher.SearchByProjection(K.get(), S, pts, matched, th);
+    for (int i = 0; i < K->N; i++) assigned[i] = (matched[i] && matched[i]->id >= 0) ? matched[i]->id : -1;
+    return 0;
+}
+
 static void fill_featvec(DBoW2::FeatureVector &fv, int ngroups, const int32_t *off, const int32_t *idx) {
     fv.clear();
     for (int g = 0; g < ngroups; g++) {

@@ -151,3 +151,73 @@ def test_stereo_oracle_equals_reference_frame_cc(ref, w, h, nf, seed):
     rur, rdp = ref.refm_stereo_match(left, right, nf, kl, dl, kr, dr, mbf, mb)
     assert np.array_equal(ur.view(np.uint32), rur.view(np.uint32)), "mvuRight differs from the reference's Frame.cc"
     assert np.array_equal(dp.view(np.uint32), rdp.view(np.uint32)), "mvDepth differs from the reference's Frame.cc"
+
+
+def _world_points(k, depth_seed=0):
+    n = len(k)
+    z = np.array([2 + (SplitMix64(i + depth_seed).next() % 1000) / 100 for i in range(n)], np.float32)
+    xyz = np.stack([(k["x"] - CX) * z / FX, (k["y"] - CY) * z / FY, z], 1).astype(np.float32)
+    return xyz, z
+
+
+def kf_projection_case(scene, ref, backend_frames):
+    """SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) scenario shared by the CPU and GPU tests: KF = frame A
+    with a map point per feature, current frame = frame A's features seen from a translated pose."""
+    k = scene["ka"]
+    n = len(k)
+    xyz, z = _world_points(k)
+    usable = (np.arange(n) % 9 != 0).astype(np.uint8)
+    # distance-invariance range chosen so that PredictScale lands on the feature's own octave +-1
+    maxd = (z * np.float32(1.2) ** k["octave"]).astype(np.float32)
+    mind = (maxd / np.float32(1.2) ** 8).astype(np.float32)
+    claimed = (np.arange(n) % 14 == 0).astype(np.uint8)
+    Tc = np.eye(4, dtype=np.float32); Tc[:3, 3] = (0.03, -0.02, 0.1)
+    return dict(xyz=xyz, usable=usable, maxd=maxd, mind=mind, claimed=claimed, Tc=Tc)
+
+
+@pytest.mark.parametrize("th,orbdist,ori", [(10.0, 100, True), (3.0, 64, True), (10.0, 100, False)])
+def test_search_by_projection_keyframe(scene, ref, th, orbdist, ori):
+    from ar_orbslam2_b200.tracking import ORB_SELECT_BEST, ORBmatcher
+    oc, rc = frames(scene, ref, "a")
+    _, rk = frames(scene, ref, "a")
+    c = kf_projection_case(scene, ref, None)
+    R = ref.refm_search_by_projection_kf(rc, rk, c["xyz"], c["usable"], c["maxd"], c["mind"], c["claimed"], c["Tc"], FX, FY, CX, CY, th, orbdist, 0.9, ori)
+    assert R["nmatches"] > 100 and R["valid"].sum() > 500
+    lvl = R["level"]
+    assert lvl[R["valid"] == 1].min() >= 0 and lvl[R["valid"] == 1].max() <= 7
+    radius = (np.float32(th) * scene["scale"][np.clip(lvl, 0, 7)]).astype(np.float32)
+    k = scene["ka"]
+    no, ao = ORBmatcher(0.9, ori, backend=ref.OracleBackend()).SearchWindowed(
+        oc, R["u"], R["v"], radius, lvl - 1, lvl + 1, scene["da"], ORB_SELECT_BEST, orbdist, valid=R["valid"], angle=k["angle"], claimed=c["claimed"])
+    assert no == R["nmatches"] and np.array_equal(ao, R["assigned"])
+
+
+def sim3_projection_case(scene):
+    k = scene["ka"]
+    n = len(k)
+    xyz, z = _world_points(k, 7)
+    nrm = -xyz / np.linalg.norm(xyz, axis=1, keepdims=True)          # facing the camera at the origin ...
+    nrm[::6] *= -1                                                    # ... except some, which fail the 60-degree test
+    usable = (np.arange(n) % 8 != 0).astype(np.uint8)
+    maxd = (z * np.float32(1.2) ** k["octave"] * np.float32(0.999)).astype(np.float32)
+    mind = (maxd / np.float32(1.2) ** 8).astype(np.float32)
+    claimed = (np.arange(n) % 12 == 0).astype(np.uint8)
+    S = np.eye(4, dtype=np.float32) * np.float32(1.0); S[:3, 3] = (0.02, 0.01, 0.05)
+    S[:3, :] *= np.float32(1.1)                                       # a similarity with scale 1.1
+    return dict(xyz=xyz, nrm=nrm.astype(np.float32), usable=usable, maxd=maxd, mind=mind, claimed=claimed, S=S)
+
+
+@pytest.mark.parametrize("th", [10, 4])
+def test_search_by_projection_sim3(scene, ref, th):
+    from ar_orbslam2_b200.tracking import ORB_SELECT_BEST, ORBmatcher
+    ok, rk = frames(scene, ref, "a")
+    c = sim3_projection_case(scene)
+    R = ref.refm_search_by_projection_sim3(rk, c["S"], c["xyz"], c["nrm"], c["usable"], c["maxd"], c["mind"], c["claimed"], FX, FY, CX, CY, th, 0.9)
+    assert R["nmatches"] > 100
+    lvl = R["level"]
+    assert lvl[R["valid"] == 1].min() >= 0 and lvl[R["valid"] == 1].max() <= 7
+    radius = (np.float32(th) * scene["scale"][np.clip(lvl, 0, 7)]).astype(np.float32)
+    no, ao = ORBmatcher(0.9, False, backend=ref.OracleBackend()).SearchWindowed(
+        ok, R["u"], R["v"], radius, lvl - 1, lvl, scene["da"], ORB_SELECT_BEST, 50, valid=R["valid"], strict_levels=True, claimed=c["claimed"],
+        check_orientation=False)
+    assert no == R["nmatches"] and np.array_equal(ao, R["assigned"])

@@ -188,3 +188,36 @@ def test_gpu_equals_reference_source_matchers(scene, oracle, gpu_lib):
     ng, ag = ORBmatcher(0.8).SearchByProjectionPoints(g2, *args)
     nr, ar = ORBmatcher(0.8, backend=rb).SearchByProjectionPoints(r2, *args)
     assert nr > 100 and ng == nr and np.array_equal(ag, ar)
+
+
+def test_gpu_windowed_equals_reference_kf_and_sim3(scene, oracle, gpu_lib):
+    """orb_search_windowed on the GPU against the reference's SearchByProjection(Frame&, KeyFrame*, ...) (ORBmatcher.cc:1475) and
+    SearchByProjection(KeyFrame*, Scw, ...) (:290), both run from the compiled reference source (oracle/_ref)."""
+    import test_reference_matcher_cpu as T
+    from ar_orbslam2_b200.tracking import ORB_SELECT_BEST, Frame, ORBmatcher
+    if not oracle.ref_matcher_available():
+        pytest.skip("oracle/_ref not built")
+    bounds = (0.0, float(W), 0.0, float(H))
+    rb = oracle.ReferenceSourceBackend()
+    g = Frame(scene["ka"], scene["da"], scene["scale"], bounds)
+    rc = Frame(scene["ka"], scene["da"], scene["scale"], bounds, backend=rb)
+    rk = Frame(scene["ka"], scene["da"], scene["scale"], bounds, backend=rb)
+    k = scene["ka"]
+    c = T.kf_projection_case(scene, oracle, None)
+    for th, orbdist, ori in ((10.0, 100, True), (3.0, 64, True)):
+        R = oracle.refm_search_by_projection_kf(rc, rk, c["xyz"], c["usable"], c["maxd"], c["mind"], c["claimed"], c["Tc"], T.FX, T.FY, T.CX, T.CY,
+                                                th, orbdist, 0.9, ori)
+        lvl = R["level"]
+        radius = (np.float32(th) * scene["scale"][np.clip(lvl, 0, 7)]).astype(np.float32)
+        ng, ag = ORBmatcher(0.9, ori).SearchWindowed(g, R["u"], R["v"], radius, lvl - 1, lvl + 1, scene["da"], ORB_SELECT_BEST, orbdist,
+                                                     valid=R["valid"], angle=k["angle"], claimed=c["claimed"])
+        assert R["nmatches"] > 100 and ng == R["nmatches"] and np.array_equal(ag, R["assigned"])
+    c = T.sim3_projection_case(scene)
+    for th in (10, 4):
+        R = oracle.refm_search_by_projection_sim3(rk, c["S"], c["xyz"], c["nrm"], c["usable"], c["maxd"], c["mind"], c["claimed"], T.FX, T.FY, T.CX,
+                                                  T.CY, th, 0.9)
+        lvl = R["level"]
+        radius = (np.float32(th) * scene["scale"][np.clip(lvl, 0, 7)]).astype(np.float32)
+        ng, ag = ORBmatcher(0.9, False).SearchWindowed(g, R["u"], R["v"], radius, lvl - 1, lvl, scene["da"], ORB_SELECT_BEST, 50, valid=R["valid"],
+                                                       strict_levels=True, claimed=c["claimed"], check_orientation=False)
+        assert R["nmatches"] > 100 and ng == R["nmatches"] and np.array_equal(ag, R["assigned"])
