@@ -246,6 +246,37 @@ _KEEP = []   # library handles must outlive every pinned buffer that was copied 
              # allocator records an event on those streams when such a buffer is freed.  They are closed at interpreter exit.
 
 
+def bench_latency(args):
+    """Single-frame latency through the blocking host API (what a tracking thread sees): orb_extract on one 640x480 frame
+    (1000 features) and one KITTI-shaped stereo frame (two handles + orb_stereo_match), host image in, host results out."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.stereo import ComputeStereoMatches
+    from ar_orbslam2_b200.synth import synth_frame, synth_stereo_pair
+    out = {}
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    img = synth_frame(640, 480, 5)
+    for _ in range(5):
+        ex(img)
+    t = []
+    for _ in range(30):
+        t0 = time.perf_counter(); ex(img); t.append(time.perf_counter() - t0)
+    out["c1_extract_ms_median"] = 1e3 * float(np.median(t))
+    exl = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H)
+    exr = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H)
+    l, r = synth_stereo_pair(W, H, 9)
+    mb = float(np.float32(MBF) / np.float32(FX))
+    t = []
+    for i in range(35):
+        t0 = time.perf_counter()
+        kl, dl = exl(l); kr, dr = exr(r)
+        ComputeStereoMatches(exl, exr, kl, dl, kr, dr, MBF, mb)
+        if i >= 5:
+            t.append(time.perf_counter() - t0)
+    out["c2_stereo_frame_ms_median"] = 1e3 * float(np.median(t))
+    out["note"] = "wall clock around blocking calls incl. pageable host copies and the python wrapper; sequential left/right"
+    return out
+
+
 class Lane:
     """One extractor handle with its device-resident outputs and pinned host result buffers (one CUDA stream)."""
 
@@ -396,6 +427,7 @@ def run_ours(args):
         extra["hamming"] = bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier)
     if rank == 0 and not os.environ.get("ORB_BENCH_SKIP_C1"):
         extra["c1_mono"] = bench_c1(args, torch, dev, local)
+        extra["latency"] = bench_latency(args)
 
     if rank != 0:
         if world > 1:
