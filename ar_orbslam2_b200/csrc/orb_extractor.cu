@@ -658,17 +658,8 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
     }
 }
 
+// fp32 helpers of the descriptor stage.
 // ------------------------------------------------------------------------------------------
-// Orientation + descriptor, one warp per kept keypoint.  A 43x43 window of the (unblurred) level
-// is staged in shared memory; the intensity-centroid moments come from its central disc, the
-// 7x7 Gaussian is applied separably to the 37x37 patch the 256 rotated test pairs can reach.
-// ------------------------------------------------------------------------------------------
-constexpr int PW = 43;            // patch width (+-21)
-constexpr int PPW = 13;           // patch row pitch in 32-bit words (odd: conflict-free row-per-lane access)
-constexpr int HPW = 21;           // horizontal-pass row pitch in words (42 x u16)
-constexpr int BW = 37;            // blurred patch (+-18)
-constexpr int BP = 40;
-
 __device__ __forceinline__ float dev_fast_atan2(float y, float x) {
     // cv::fastAtan2; every operation rounded separately (no FMA)
     const float p1 = 57.283627f, p3 = -18.667446f, p5 = 8.9140005f, p7 = -2.5397246f;
@@ -733,13 +724,64 @@ __device__ __forceinline__ void dev_sincosf(float y, float *sn, float *cs) {
     *cs = dev_sincos_poly(xs, x2, alt, n ^ 1);
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32)
-k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Kept *__restrict__ kept,
-           const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp, uint8_t *__restrict__ out_desc,
-           int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
-    __shared__ uint32_t s_patch[DESC_WARPS][PW * PPW];   // raw window (word rows); reused for the blurred patch
-    __shared__ uint32_t s_h[DESC_WARPS][PW * HPW];       // horizontal pass, two 16-bit sums per word
+// ------------------------------------------------------------------------------------------
+// 7x7 Gaussian (sigma 2) of whole levels (ref :1024-1026: GaussianBlur on a clone of the level, BORDER_REFLECT_101 --
+// the padded plane already holds that reflection).  SURVEY A.3: H = sum k*src (16 bit), out = (sum k*H + 32768) >> 16.
+// A thread owns 4 horizontally adjacent pixels (one aligned word) and walks down BLUR_ROWS rows keeping the last
+// seven horizontal sums in registers; every source row is fetched as three aligned words.
+// ------------------------------------------------------------------------------------------
+constexpr int BLUR_ROWS = 16;
 
+__global__ void __launch_bounds__(128)
+k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const Geom *__restrict__ G, int level) {
+    const LevelGeom &g = G->lv[level];
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x;     // word column of the interior
+    const int x0 = wx * 4;
+    if (x0 >= g.w) return;
+    const int y0 = blockIdx.y * BLUR_ROWS, b = blockIdx.z;
+    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    const uint8_t *src = pyr + (size_t)b * G->pyr_frame + g.interior_off + x0 - 4;
+    uint8_t *dst = blur + (size_t)b * G->pyr_frame + g.interior_off + x0;
+    int h[7][4];
+#pragma unroll
+    for (int r = 0; r < BLUR_ROWS + 6; r++) {
+        const int y = y0 + r - 3;                              // source row; rows -3.. and ..H+2 live in the 19-px frame
+        if (y < g.h + 3) {
+            const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)y * g.pitch);
+            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+            int bt[12];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                bt[i] = (w0 >> (8 * i)) & 0xff; bt[4 + i] = (w1 >> (8 * i)) & 0xff; bt[8 + i] = (w2 >> (8 * i)) & 0xff;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++)                        // pixel x0+j reads bytes j+1 .. j+7 of the 12-byte window
+                h[r % 7][j] = k0 * (bt[j + 1] + bt[j + 7]) + k1 * (bt[j + 2] + bt[j + 6]) + k2 * (bt[j + 3] + bt[j + 5]) + k3 * bt[j + 4];
+        }
+        if (r >= 6) {
+            const int yo = y0 + r - 6;
+            if (yo < g.h) {
+                uint32_t o = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int v = k0 * (h[(r - 6) % 7][j] + h[r % 7][j]) + k1 * (h[(r - 5) % 7][j] + h[(r - 1) % 7][j]) +
+                                  k2 * (h[(r - 4) % 7][j] + h[(r - 2) % 7][j]) + k3 * h[(r - 3) % 7][j];
+                    o |= (uint32_t)min((v + 32768) >> 16, 255) << (8 * j);
+                }
+                *reinterpret_cast<uint32_t *>(dst + (ptrdiff_t)yo * g.pitch) = o;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Orientation + descriptor, one warp per kept keypoint, no shared memory: the intensity-centroid moments read the
+// 31x31 disc of the level straight from L1/L2 (lane = column), the 256 rotated test pairs sample the blurred plane.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(DESC_WARPS * 32)
+k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, const Geom *__restrict__ G,
+           const Kept *__restrict__ kept, const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp,
+           uint8_t *__restrict__ out_desc, int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.y;
     // flat slot -> (level, index) over the per-level kept capacities
@@ -762,30 +804,18 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
     }
     const LevelGeom &g = G->lv[level];
     const Kept kp = kept[(size_t)b * G->kept_frame + g.kept_off + slot];
-    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
-
-    // ---- stage the 43x43 window.  Rows are copied as aligned 32-bit words (plane rows are 128-byte pitched and
-    // the interior starts at byte 32), so the window starts `sft` bytes into each shared-memory row.
-    uint32_t *PWd = s_patch[warp];
-    const int x0 = kp.x - 21;
-    const int sft = (x0 + XOFF) & 3;
-    const uint8_t *src = img + (ptrdiff_t)(kp.y - 21) * g.pitch + (x0 - sft);
-    for (int t = lane; t < PW * 12; t += 32) {
-        const int y = t / 12, w = t - y * 12;
-        PWd[y * PPW + w] = __ldg(reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)y * g.pitch) + w);
-    }
-    __syncwarp();
-    const uint8_t *P = reinterpret_cast<const uint8_t *>(PWd);
+    const size_t plane = (size_t)b * G->pyr_frame + g.interior_off + (ptrdiff_t)kp.y * g.pitch + kp.x;
 
     // ---- IC_Angle (ref :73-98): lanes own columns u = lane-15 .. of the 31-wide disc
     int m10 = 0, m01 = 0;
     if (lane < 31) {
         const int u = lane - 15, au = abs(u);
-        const uint8_t *c = P + 21 * (PPW * 4) + 21 + sft + u;
+        const uint8_t *c = pyr + plane + u;
         m10 = u * c[0];
+#pragma unroll
         for (int v = 1; v <= 15; v++) {
             if (au <= c_umax[v]) {
-                const int vp = c[v * (PPW * 4)], vm = c[-v * (PPW * 4)];
+                const int vp = c[v * g.pitch], vm = c[-v * g.pitch];
                 m10 += u * (vp + vm);
                 m01 += v * (vp - vm);
             }
@@ -798,53 +828,12 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
     }
     const float angle = dev_fast_atan2((float)m01, (float)m10);
 
-    // ---- 7x7 Gaussian, sigma 2: H = sum k*src (16 bit), out = (sum k*H + 32768) >> 16.
-    // Horizontal pass: a lane takes half a row (20 outputs) into registers and slides the 7-tap window there;
-    // vertical pass: a lane walks one column with a 7-deep register window.  ~100 shared loads per lane in total.
-    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
-    uint32_t *HW = s_h[warp];
-    for (int t = lane; t < PW * 2; t += 32) {
-        const int y = t >> 1, half = t & 1;
-        const int b0 = sft + 20 * half, wi = b0 >> 2, sh = (b0 & 3) * 8;
-        const uint32_t *row = PWd + y * PPW + wi;
-        uint32_t w[8], a[7];
-#pragma unroll
-        for (int k = 0; k < 8; k++) w[k] = row[k];
-#pragma unroll
-        for (int k = 0; k < 7; k++) a[k] = __funnelshift_r(w[k], w[k + 1], sh);
-        int bt[26];
-#pragma unroll
-        for (int i = 0; i < 26; i++) bt[i] = (a[i >> 2] >> (8 * (i & 3))) & 0xff;
-        uint32_t *hrow = HW + y * HPW + 10 * half;
-#pragma unroll
-        for (int j = 0; j < 10; j++) {
-            const int xa = 2 * j, xb = 2 * j + 1;
-            const int ha = k0 * (bt[xa] + bt[xa + 6]) + k1 * (bt[xa + 1] + bt[xa + 5]) + k2 * (bt[xa + 2] + bt[xa + 4]) + k3 * bt[xa + 3];
-            const int hb = k0 * (bt[xb] + bt[xb + 6]) + k1 * (bt[xb + 1] + bt[xb + 5]) + k2 * (bt[xb + 2] + bt[xb + 4]) + k3 * bt[xb + 3];
-            hrow[j] = (uint32_t)ha | ((uint32_t)hb << 16);
-        }
-    }
-    __syncwarp();
-    uint8_t *Bl = reinterpret_cast<uint8_t *>(PWd);   // the raw window is dead once H is built (BW*BP <= PW*PPW*4)
-    const uint16_t *H = reinterpret_cast<const uint16_t *>(HW);
-    for (int x = lane; x < BW; x += 32) {
-        int h0 = H[x], h1 = H[(HPW * 2) + x], h2 = H[2 * (HPW * 2) + x], h3 = H[3 * (HPW * 2) + x], h4 = H[4 * (HPW * 2) + x],
-            h5 = H[5 * (HPW * 2) + x];
-#pragma unroll 4
-        for (int y = 0; y < BW; y++) {
-            const int h6 = H[(y + 6) * (HPW * 2) + x];
-            const int v = k0 * (h0 + h6) + k1 * (h1 + h5) + k2 * (h2 + h4) + k3 * h3;
-            Bl[y * BP + x] = (uint8_t)min((v + 32768) >> 16, 255);
-            h0 = h1; h1 = h2; h2 = h3; h3 = h4; h4 = h5; h5 = h6;
-        }
-    }
-    __syncwarp();
-
     // ---- steered BRIEF (ref :101-144): lane computes descriptor byte `lane`
     float sn, cs;
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);   // ref :100
     dev_sincosf(__fmul_rn(angle, factorPI), &sn, &cs);
-    const uint8_t *ctr = Bl + 18 * BP + 18;
+    const uint8_t *ctr = blur + plane;
+    const int BP = g.pitch;
     uint32_t pw[8];   // this lane's 8 test pairs: 32 signed bytes (x0,y0,x1,y1) x 8
     {
         const uint4 *pp = reinterpret_cast<const uint4 *>(d_pattern + lane * 32);
@@ -875,25 +864,6 @@ k_describe(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Ke
         o.class_id = -1;
         out_kp[(size_t)b * capacity + oidx] = o;
     }
-}
-
-// Full-plane blur with the same arithmetic, for parity tests of the blur in isolation.
-__global__ void k_blur_level(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, int level, int b,
-                             uint8_t *__restrict__ dst, int dpitch) {
-    const LevelGeom &g = G->lv[level];
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= g.w) return;
-    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off;
-    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
-    const int kk[7] = {k0, k1, k2, k3, k2, k1, k0};
-    int acc = 0;
-    for (int j = 0; j < 7; j++) {
-        const uint8_t *r = img + (ptrdiff_t)(y + j - 3) * g.pitch + x;   // padded plane == reflect101
-        int hsum = 0;
-        for (int i = 0; i < 7; i++) hsum += kk[i] * r[i - 3];
-        acc += kk[j] * hsum;
-    }
-    dst[(size_t)y * dpitch + x] = (uint8_t)min((acc + 32768) >> 16, 255);
 }
 
 }  // namespace orbgpu
@@ -1040,7 +1010,7 @@ static size_t octree_smem_bytes(int maxn) {
 }
 
 static void free_all(orb_extractor *ex) {
-    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_cand);
+    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
@@ -1148,6 +1118,8 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     ex->pyr_bytes = B * (size_t)(G.pyr_frame + 4096 * params->nlevels);
     TRY_ALLOC(cudaMalloc(&ex->d_pyr, ex->pyr_bytes));
     TRY_ALLOC(cudaMemsetAsync(ex->d_pyr, 0, ex->pyr_bytes, ex->stream));
+    TRY_ALLOC(cudaMalloc(&ex->d_blur, ex->pyr_bytes));   // blurred levels, same plane geometry
+    TRY_ALLOC(cudaMemsetAsync(ex->d_blur, 0, ex->pyr_bytes, ex->stream));
     ex->cand_elems = B * (size_t)(G.cand_frame + 64 * params->nlevels);
     TRY_ALLOC(cudaMalloc(&ex->d_cand, ex->cand_elems * 4));
     TRY_ALLOC(cudaMalloc(&ex->d_node_of, ex->cand_elems * 2));
@@ -1287,8 +1259,14 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err);
     ex->launches++;
     prof_mark(ex, 4);
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom &g = G.lv[l];
+        dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, batch);
+        k_blur_planes<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_blur, ex->d_geom, l);
+        ex->launches++;
+    }
     k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
-        ex->d_pyr, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
+        ex->d_pyr, ex->d_blur, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
     ex->launches++;
     prof_mark(ex, 5);
     ORB_CUDA_TRY(cudaGetLastError());
@@ -1427,14 +1405,10 @@ int orb_debug_blur_level(orb_extractor *ex, int slot, int level, uint8_t *dst, i
                 ORB_ERR_INVALID, "bad level/slot");
     ORB_CUDA_TRY(cudaSetDevice(ex->device));
     const LevelGeom &g = ex->geom.lv[level];
-    uint8_t *d_tmp = nullptr;
-    ORB_CUDA_TRY(cudaMalloc(&d_tmp, (size_t)g.w * g.h));
-    k_blur_level<<<dim3((g.w + 127) / 128, g.h), 128, 0, ex->stream>>>(ex->d_pyr, ex->d_geom, level, slot, d_tmp, g.w);
-    ex->launches++;
-    cudaError_t e = cudaMemcpy2DAsync(dst, dst_pitch, d_tmp, g.w, g.w, g.h, cudaMemcpyDeviceToHost, ex->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ex->stream);
-    cudaFree(d_tmp);
-    ORB_CUDA_TRY(e);
+    // the blurred planes of the last extraction are resident; hand back the interior of the requested one
+    ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_pitch, ex->d_blur + (size_t)slot * ex->geom.pyr_frame + g.interior_off, g.pitch, g.w, g.h,
+                                   cudaMemcpyDeviceToHost, ex->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
     return ORB_OK;
 }
 

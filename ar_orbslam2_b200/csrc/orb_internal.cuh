@@ -71,6 +71,7 @@ struct orb_extractor {
     size_t cells_cap = 0;
     uint8_t *d_src = nullptr;  size_t src_bytes = 0;
     uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
+    uint8_t *d_blur = nullptr;         // 7x7 Gaussian of every level (same plane layout as d_pyr)
     uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
     uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
     orbgpu::Kept *d_kept = nullptr; size_t kept_elems = 0;
