@@ -743,12 +743,21 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
     const uint8_t *src = pyr + (size_t)b * G->pyr_frame + g.interior_off + x0 - 4;
     uint8_t *dst = blur + (size_t)b * G->pyr_frame + g.interior_off + x0;
     int h[7][4];
+    // source rows -3.. and ..H+2 live in the 19-px frame.  Row indices are clamped (not predicated) and the next row's
+    // words are requested before the current row is consumed; rows past H+2 only feed outputs that are never stored.
+    uint32_t n0, n1, n2;
+    {
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)min(y0 - 3, g.h + 2) * g.pitch);
+        n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2);
+    }
 #pragma unroll
     for (int r = 0; r < BLUR_ROWS + 6; r++) {
-        const int y = y0 + r - 3;                              // source row; rows -3.. and ..H+2 live in the 19-px frame
-        if (y < g.h + 3) {
-            const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)y * g.pitch);
-            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+        const uint32_t w0 = n0, w1 = n1, w2 = n2;
+        if (r + 1 < BLUR_ROWS + 6) {
+            const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)min(y0 + r - 2, g.h + 2) * g.pitch);
+            n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2);
+        }
+        {
             int bt[12];
 #pragma unroll
             for (int i = 0; i < 4; i++) {

@@ -8,6 +8,7 @@
 #include "orb_common.cuh"
 #include "orb_internal.cuh"
 
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -27,19 +28,76 @@ struct StereoArgs {
     float mbf, mb;
     float *uRight, *depth;
     int4 *packR;           // [batch][capacity] right keypoints packed by k_stereo_prep
+    int *rowoff;           // [batch][nrows + 1] CSR of the row table (ref vRowIndices, Frame.cc:479-496)
+    int *rowlist;          // [batch][list_cap] right keypoint indices per image row
+    int nrows, list_cap;
     int32_t *sad;          // [batch][capacity] best SAD or -1
     int32_t *n_matched;    // [batch]
 };
 
-// Row band of every right keypoint (ref :486-496): rows [floor(y - r), ceil(y + r)], r = 2 * scale[octave], packed
-// with its octave and x so the search loop below reads one coalesced 16-byte record per candidate.
-__global__ void k_stereo_prep(StereoArgs A) {
-    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= min(A.nR[b], A.capacity)) return;
-    const orb_keypoint kr = A.keysR[(size_t)b * A.capacity + i];
-    const float r = __fmul_rn(2.0f, A.GL->lv[kr.octave].scale);
-    const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
-    A.packR[(size_t)b * A.capacity + i] = make_int4(minr, maxr, kr.octave, __float_as_int(kr.x));
+// The reference's row table (ref :479-496): right keypoint iR is a candidate for every image row in
+// [floor(y - r), ceil(y + r)], r = 2 * scale[octave].  One CTA per pair builds it as CSR in three passes over the right
+// keypoints (count with shared atomics, block scan, fill) and packs {minr, maxr, octave, x} per keypoint.  The order
+// inside a row is arbitrary: the search below takes the minimum of (distance, index), which is the reference's
+// first-best-in-index-order result.
+constexpr int ROWTAB_THREADS = 1024;
+__global__ void __launch_bounds__(ROWTAB_THREADS) k_stereo_rowtable(StereoArgs A) {
+    extern __shared__ int s_row[];          // [nrows + 1] counts, then offsets, then cursors
+    __shared__ int s_warp[33];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const int Nr = min(A.nR[b], A.capacity), nrows = A.nrows;
+    for (int i = tid; i <= nrows; i += ROWTAB_THREADS) s_row[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < Nr; i += ROWTAB_THREADS) {
+        const orb_keypoint kr = A.keysR[(size_t)b * A.capacity + i];
+        const float r = __fmul_rn(2.0f, A.GL->lv[kr.octave].scale);
+        const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
+        A.packR[(size_t)b * A.capacity + i] = make_int4(minr, maxr, kr.octave, __float_as_int(kr.x));
+        for (int y = max(minr, 0); y <= min(maxr, nrows - 1); y++) atomicAdd(&s_row[y], 1);
+    }
+    __syncthreads();
+    // exclusive scan of s_row[0..nrows) in place
+    int carry = 0;
+    for (int base = 0; base < nrows; base += ROWTAB_THREADS) {
+        const int i = base + tid;
+        const int v = i < nrows ? s_row[i] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[tid >> 5] = incl;
+        __syncthreads();
+        if (tid < 32) {
+            const int w = s_warp[tid];
+            int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, wi, o);
+                if (tid >= o) wi += t;
+            }
+            s_warp[tid] = wi - w;
+            if (tid == 31) s_warp[32] = wi;
+        }
+        __syncthreads();
+        if (i < nrows) s_row[i] = carry + s_warp[tid >> 5] + incl - v;
+        carry += s_warp[32];
+        __syncthreads();
+    }
+    if (tid == 0) s_row[nrows] = carry;
+    __syncthreads();
+    int *off = A.rowoff + (size_t)b * (nrows + 1);
+    for (int i = tid; i <= nrows; i += ROWTAB_THREADS) off[i] = s_row[i];
+    __syncthreads();
+    int *list = A.rowlist + (size_t)b * A.list_cap;
+    for (int i = tid; i < Nr; i += ROWTAB_THREADS) {
+        const int4 k = A.packR[(size_t)b * A.capacity + i];
+        for (int y = max(k.x, 0); y <= min(k.y, nrows - 1); y++) {
+            const int pos = atomicAdd(&s_row[y], 1);     // s_row doubles as the fill cursor
+            if (pos < A.list_cap) list[pos] = i;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
@@ -48,7 +106,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.y;
     const int iL = blockIdx.x * ST_WARPS + warp;
-    const int N = min(A.nL[b], A.capacity), Nr = min(A.nR[b], A.capacity);
+    const int N = min(A.nL[b], A.capacity);
     if (iL >= A.capacity) return;
     const size_t o = (size_t)b * A.capacity + iL;
     if (lane == 0) { A.uRight[o] = -1.0f; A.depth[o] = -1.0f; A.sad[o] = -1; }
@@ -74,9 +132,13 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
     const orb_keypoint *KR = A.keysR + (size_t)b * A.capacity;
     const uint8_t *DR = A.descR + (size_t)b * A.capacity * 32;
     const int4 *PR = A.packR + (size_t)b * A.capacity;
-    for (int iR = lane; iR < Nr; iR += 32) {
-        const int4 kr = __ldg(PR + iR);   // {minr, maxr, octave, x}
-        if (row < kr.x || row > kr.y) continue;
+    if (row < 0 || row >= A.nrows) return;
+    const int *off = A.rowoff + (size_t)b * (A.nrows + 1);
+    const int lo = off[row], hi = min(off[row + 1], A.list_cap);
+    const int *list = A.rowlist + (size_t)b * A.list_cap;
+    for (int j = lo + lane; j < hi; j += 32) {                    // vCandidates = vRowIndices[vL]
+        const int iR = list[j];
+        const int4 kr = __ldg(PR + iR);                           // {minr, maxr, octave, x}
         if (kr.z < levelL - 1 || kr.z > levelL + 1) continue;
         const float uR = __int_as_float(kr.w);
         if (!(uR >= minU && uR <= maxU)) continue;
@@ -237,7 +299,10 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     }
     const size_t per = (size_t)batch * capacity;
     // scratch layout: sad[per] | n_matched[batch] | (host mode) keysL,keysR,descL,descR,nL,nR,uRight,depth
-    size_t need = per * 4 + per * 16 + batch * 4 + 16 * 256;   // every carve() is rounded up to 256 B
+    const int nrows = left->geom.lv[0].h;
+    // a right keypoint is listed in rows floor(y-r)..ceil(y+r), r = 2*scale: at most 2*ceil(2*scale_max)+3 rows
+    const int list_cap = capacity * (2 * (int)std::ceil(2.0f * left->scale.back()) + 3);
+    size_t need = per * 4 + per * 16 + batch * 4 + (size_t)batch * (nrows + 1) * 4 + (size_t)batch * list_cap * 4 + 16 * 256;   // every carve() is rounded up to 256 B
     if (loc == ORB_HOST) need += 2 * per * sizeof(orb_keypoint) + 2 * per * 32 + 2 * batch * 4 + 2 * per * 4 + 1024;
     if (left->stereo_scratch_bytes < need) {
         if (left->stereo_scratch) cudaFree(left->stereo_scratch);
@@ -251,6 +316,9 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     StereoArgs A;
     A.sad = (int32_t *)carve(per * 4);
     A.packR = (int4 *)carve(per * 16);
+    A.rowoff = (int *)carve((size_t)batch * (nrows + 1) * 4);
+    A.rowlist = (int *)carve((size_t)batch * list_cap * 4);
+    A.nrows = nrows; A.list_cap = list_cap;
     A.n_matched = (int32_t *)carve(batch * 4);
     A.pyrL = left->d_pyr; A.pyrR = right->d_pyr;
     A.GL = left->d_geom; A.GR = right->d_geom;
@@ -273,7 +341,7 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
         A.keysL = keys_left; A.keysR = keys_right; A.descL = desc_left; A.descR = desc_right;
         A.nL = n_left; A.nR = n_right; A.uRight = u_right; A.depth = depth;
     }
-    k_stereo_prep<<<dim3((capacity + 127) / 128, batch), 128, 0, st>>>(A);
+    k_stereo_rowtable<<<batch, ROWTAB_THREADS, (nrows + 1) * sizeof(int), st>>>(A);
     k_stereo_match<<<dim3((capacity + ST_WARPS - 1) / ST_WARPS, batch), ST_WARPS * 32, 0, st>>>(A);
     int sort_n = 1;
     while (sort_n < capacity) sort_n <<= 1;
