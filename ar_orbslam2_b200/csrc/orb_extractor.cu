@@ -58,8 +58,8 @@ __global__ void k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_strid
 }
 
 __global__ void __launch_bounds__(128)
-k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps, int level) {
-    // cv::resize INTER_LINEAR straight into the padded plane (reflect-101 frame included).
+k_pyr_resize_generic(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps, int level) {
+    // cv::resize INTER_LINEAR straight into the padded plane (reflect-101 frame included); any scale factor.
     // A thread makes 4 horizontally adjacent pixels.  Their source pixels span < 12 bytes, so each of the two
     // source rows is fetched as three aligned words and the taps pick bytes out of registers (PRMT) instead of
     // issuing 16 byte loads.
@@ -113,6 +113,49 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
         }
     }
     *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
+}
+
+// Fast path of the same resize for scale factors up to ~1.5 (every level of the reference's 1.2 pyramid): the host
+// precomputes, per aligned output word (4 pixels of the padded row, reflection and plane limits already resolved), one
+// 128-bit record { tap offset o (3 bits) | a0 (12) | a1 (12) } x 4 plus the word index of the 12-byte source window,
+// so a thread issues 1 + 6 loads for two output rows of 4 pixels and selects source bytes with PRMT.
+__global__ void __launch_bounds__(128)
+k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
+             const uint4 *__restrict__ wtab, int level) {
+    const LevelGeom &g = G->lv[level];
+    const LevelGeom &p = G->lv[level - 1];
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.z;
+    if (word * 4 >= g.pitch) return;
+    uint8_t *frame = pyr + (size_t)b * G->pyr_frame;
+    const uint4 T = __ldg(wtab + g.wtab_off + word);
+    const uint32_t t[4] = {T.x, T.y, T.z, T.w};
+    const int base_word = (int)((T.x >> 27) | ((T.y >> 27) << 5));
+    const int rows = g.h + 2 * EDGE;
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++) {
+        const int py = blockIdx.y * 2 + rr;
+        if (py >= rows) break;
+        const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
+        const uint32_t *r0 = reinterpret_cast<const uint32_t *>(frame + p.interior_off + (size_t)ty.s0 * p.pitch) + base_word;
+        const uint32_t *r1 = reinterpret_cast<const uint32_t *>(frame + p.interior_off + (size_t)ty.s1 * p.pitch) + base_word;
+        const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
+        const uint32_t c0 = __ldg(r1), c1 = __ldg(r1 + 1), c2 = __ldg(r1 + 2);
+        uint32_t v = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int o = t[k] & 7, wa0 = (t[k] >> 3) & 0xfff, wa1 = (t[k] >> 15) & 0xfff;
+            const bool hi = o >= 4;
+            const uint32_t ua = hi ? a1 : a0, ub = hi ? a2 : a1, uc = hi ? c1 : c0, ud = hi ? c2 : c1;
+            const uint32_t sel = (uint32_t)(o & 3) | ((uint32_t)((o & 3) + 1) << 4) | 0x4400u;   // bytes o, o+1 of the window
+            const uint32_t pa = __byte_perm(ua, ub, sel), pc = __byte_perm(uc, ud, sel);
+            const int r0v = (int)(pa & 0xff) * wa0 + (int)((pa >> 8) & 0xff) * wa1;
+            const int r1v = (int)(pc & 0xff) * wa0 + (int)((pc >> 8) & 0xff) * wa1;
+            const int o8 = (((ty.a0 * (r0v >> 4)) >> 16) + ((ty.a1 * (r1v >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)o8 << (8 * k);
+        }
+        *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1019,7 +1062,7 @@ static size_t octree_smem_bytes(int maxn) {
 }
 
 static void free_all(orb_extractor *ex) {
-    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
+    cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_wtab); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
@@ -1051,6 +1094,40 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
                 rc == ORB_ERR_TOO_SMALL ? "a pyramid level is too small for the 30-px cell grid (reference divides by zero)"
                                         : "unsupported geometry");
     ORB_REQUIRE(taps.size() <= ex->taps_cap, ORB_ERR_INVALID, "internal: tap pool too small");
+    // per-output-word resize records (fast path); a level whose 4-pixel source span exceeds the 12-byte window keeps
+    // the generic kernel
+    std::vector<uint4> wtab;
+    for (int l = 1; l < G.nlevels; l++) {
+        LevelGeom &g = G.lv[l];
+        g.wtab_off = (int)wtab.size();
+        g.fast_resize = 1;
+        const int nwords = g.pitch / 4;
+        for (int w = 0; w < nwords; w++) {
+            int lo = 1 << 30, hi = 0;
+            ResizeTap tx[4];
+            bool in[4];
+            for (int k = 0; k < 4; k++) {
+                const int x = w * 4 + k - XOFF;
+                in[k] = x >= -EDGE && x < g.w + EDGE;
+                tx[k] = taps[g.tap_x_off + reflect101(in[k] ? x : 0, g.w)];
+                if (in[k]) { lo = std::min(lo, (int)tx[k].s0); hi = std::max(hi, (int)tx[k].s0); }
+            }
+            uint32_t rec[4] = {0, 0, 0, 0};
+            int base = 0;
+            if (lo != (1 << 30)) {
+                base = lo & ~3;
+                if (hi - base > 7 || base / 4 >= 1024) g.fast_resize = 0;
+                for (int k = 0; k < 4; k++)
+                    if (in[k]) rec[k] = (uint32_t)((tx[k].s0 - base) & 7) | ((uint32_t)tx[k].a0 << 3) | ((uint32_t)tx[k].a1 << 15);
+            }
+            rec[0] |= (uint32_t)((base / 4) & 31) << 27;
+            rec[1] |= (uint32_t)(((base / 4) >> 5) & 31) << 27;
+            wtab.push_back(make_uint4(rec[0], rec[1], rec[2], rec[3]));
+        }
+    }
+    ORB_REQUIRE(wtab.size() <= ex->wtab_cap, ORB_ERR_INVALID, "internal: resize word table too small");
+    if (!wtab.empty())
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_wtab, wtab.data(), wtab.size() * sizeof(uint4), cudaMemcpyHostToDevice, ex->stream));
     std::vector<uint32_t> cells;
     cells.reserve(G.total_cells);
     for (int l = 0; l < G.nlevels; l++)
@@ -1120,6 +1197,8 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     }
     ex->taps_cap = (size_t)(params->max_width + params->max_height + 64) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_taps, ex->taps_cap * sizeof(ResizeTap)));
+    ex->wtab_cap = (size_t)((params->max_width + XOFF + EDGE + 127) / 128 * 32 + 32) * params->nlevels;
+    TRY_ALLOC(cudaMalloc(&ex->d_wtab, ex->wtab_cap * sizeof(uint4)));
     ex->cells_cap = (size_t)(params->max_width / 30 + 2) * (params->max_height / 30 + 2) * 4 + 64;   // sum over levels < 3.1x level 0
     TRY_ALLOC(cudaMalloc(&ex->d_cells, ex->cells_cap * 4));
     ex->src_bytes = B * (size_t)params->max_height * ((params->max_width + 127) / 128 * 128);
@@ -1256,8 +1335,13 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     }
     for (int l = 1; l < G.nlevels; l++) {
         const LevelGeom &g = G.lv[l];
-        dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
-        k_pyr_resize<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
+        if (g.fast_resize) {
+            dim3 grid((g.pitch / 4 + 127) / 128, (g.h + 2 * EDGE + 1) / 2, batch);
+            k_pyr_resize<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+        } else {
+            dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
+            k_pyr_resize_generic<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
+        }
         ex->launches++;
     }
     prof_mark(ex, 2);

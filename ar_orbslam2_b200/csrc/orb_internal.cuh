@@ -25,6 +25,7 @@ struct LevelGeom {
     long long plane_off;         // byte offset of the padded plane inside a frame's pyramid block
     long long interior_off;      // byte offset of interior pixel (0,0)
     int tap_x_off, tap_y_off;    // offsets into the ResizeTap pool (level >= 1)
+    int wtab_off, fast_resize;   // per-output-word resize records (fast path) and whether the level may use them
     // FAST cell grid (ref :742-773)
     int maxBX, maxBY, wCell, hCell, ncx, ncy, cell_begin;
     // quadtree (ref :530-549)
@@ -67,6 +68,8 @@ struct orb_extractor {
     orbgpu::Geom *d_geom = nullptr;
     orbgpu::ResizeTap *d_taps = nullptr;
     size_t taps_cap = 0;
+    uint4 *d_wtab = nullptr;           // per-output-word resize records
+    size_t wtab_cap = 0;
     uint32_t *d_cells = nullptr;       // per FAST cell: level | ci << 4 | cj << 14
     size_t cells_cap = 0;
     uint8_t *d_src = nullptr;  size_t src_bytes = 0;

@@ -127,3 +127,18 @@ def test_gpu_equals_reference_source(oracle, gpu_lib):
         rk, rd = oracle.ReferenceExtractor(nf).extract(img)
         assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
         ex.close()
+
+
+@pytest.mark.parametrize("scale,nlevels,w,h", [(2.0, 4, 800, 600), (1.5, 5, 800, 600), (1.1, 8, 640, 480), (1.2, 1, 320, 240)])
+def test_other_scale_factors(oracle, gpu_lib, scale, nlevels, w, h):
+    """Non-default pyramids: scale 2.0 / 1.5 exercise the generic resize kernel (source span beyond the 12-byte window)."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    img = synth_frame(w, h, 61)
+    ex = ORBextractor(800, scale, nlevels, 20, 7, max_width=w, max_height=h)
+    ref = oracle.RefExtractor(800, scale, nlevels)
+    gk, gd = ex(img)
+    rk, rd = ref.extract(img)
+    for l in range(nlevels):
+        assert np.array_equal(ex.pyramid_level(l, True), ref.pyramid_level(l, True)), l
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    ex.close()
