@@ -1,0 +1,25 @@
+#!/usr/bin/env python3
+"""Smallest end-to-end case for compute-sanitizer: one stereo frame through extraction, stereo association, the tracking
+matchers and a tiny brute-force scan.  usage: compute-sanitizer --tool memcheck python tools/sanitize_case.py"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from ar_orbslam2_b200.extractor import ORBextractor
+from ar_orbslam2_b200.matcher import hamming_top2
+from ar_orbslam2_b200.stereo import ComputeStereoMatches
+from ar_orbslam2_b200.synth import synth_descriptors, synth_stereo_pair
+from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+
+w, h, nf = 641, 377, 600          # odd sizes on purpose
+l, r = synth_stereo_pair(w, h, 3)
+a = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+b = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+kl, dl = a(l); kr, dr = b(r)
+ur, dp = ComputeStereoMatches(a, b, kl, dl, kr, dr, 386.1448, 0.537, allow_empty=True)
+sc = a.GetScaleFactors()
+f1 = Frame(kl, dl, sc, (0, w, 0, h)); f2 = Frame(kr, dr, sc, (0, w, 0, h))
+prev = np.stack([kl["x"], kl["y"]], 1).astype(np.float32).copy()
+n, m = ORBmatcher(0.9, True).SearchForInitialization(f1, f2, prev, 100)
+n2, asg = ORBmatcher(0.8).SearchByProjectionPoints(f2, np.ones(len(kl), np.uint8), kl["x"], kl["y"], kl["x"] - 3, kl["octave"], np.full(len(kl), 0.9, np.float32), dl, 3.0)
+d = hamming_top2(synth_descriptors(33, 1), synth_descriptors(1000, 2))
+print("ok", len(kl), len(kr), int((ur != -1).sum()), n, n2, int(d[0].min()))
