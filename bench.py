@@ -446,7 +446,7 @@ def run_ours(args):
         "pyramid": P + S_px,                       # read the source once, write the 8 levels once
         "fast_cells": S_px + 4 * 6 * kp_per_frame,  # read the 8 levels once, write ~6 candidates per kept keypoint
         "octree": 4 * 6 * kp_per_frame + 8 * kp_per_frame,
-        "describe": 43 * 43 * kp_per_frame + 60 * kp_per_frame,
+        "describe": 2 * S_px + 60 * kp_per_frame,   # blur: read the 8 levels, write the 8 blurred levels; then 60 B per keypoint
     }
     kern = {k: per_call[STAGES.index(k)] for k in alg}
     dom = max(kern, key=kern.get)
