@@ -269,14 +269,14 @@ k_resolve_windowed(FrameDev f, WinQ Q, const int *off, const int *cand_idx, cons
         int dec = 0;
         for (int a = lane; a < na; a += 32) {
             const int b = acc_bin[a];
-            if (b != i1 && b != i2 && b != i3) { holder[acc_feat[a]] = -1; dec++; }   // ref :1463-1467
+            if (b != i1 && b != i2 && b != i3) { holder[acc_feat[a]] = -3; dec++; }   // ref :1463-1467 (set to NULL)
         }
         if (dec) atomicAdd(&s_nm, dec);
         __syncwarp();
         nm -= s_nm;
     }
     __syncwarp();
-    for (int i = lane; i < f.n; i += 32) assigned[i] = holder[i] >= 0 ? holder[i] : -1;
+    for (int i = lane; i < f.n; i += 32) assigned[i] = holder[i] >= 0 ? holder[i] : (holder[i] == -3 ? -2 : -1);
     if (lane == 0) *nmatches = nm;
 }
 

@@ -1,0 +1,33 @@
+// GPU bodies for the tracking-thread entry points of ORB_SLAM2::ORBmatcher (ref: ORB_SLAM2/include/ORBmatcher.h:42-94).
+// Meant to be compiled INSIDE the reference tree (it includes the reference's Frame.h / KeyFrame.h / MapPoint.h): each
+// function gathers the flat arrays liborbgpu wants under the reference's own getters, calls the C ABI and writes the
+// results back exactly where the reference method writes them.  ORBmatcher.cc keeps its class; a maintainer replaces the
+// body of the corresponding method by a one-line call.
+#ifndef ORBMATCHER_GPU_H
+#define ORBMATCHER_GPU_H
+
+#include <vector>
+
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "MapPoint.h"
+
+namespace ORB_SLAM2 {
+namespace orbgpu_shim {
+
+// ref ORBmatcher::SearchByProjection(Frame &F, const std::vector<MapPoint*> &vpMapPoints, const float th), ORBmatcher.cc:45-129
+int SearchByProjection(Frame &F, const std::vector<MapPoint *> &vpMapPoints, float th, float mfNNratio);
+
+// ref ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono), :1331-1473
+int SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, float th, bool bMono, bool mbCheckOrientation);
+
+// ref ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f>&, vector<int>&, int windowSize), :405-523
+int SearchForInitialization(Frame &F1, Frame &F2, std::vector<cv::Point2f> &vbPrevMatched, std::vector<int> &vnMatches12,
+                            int windowSize, float mfNNratio, bool mbCheckOrientation);
+
+// ref ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint*> &vpMapPointMatches), :159-288
+int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatches, float mfNNratio, bool mbCheckOrientation);
+
+}  // namespace orbgpu_shim
+}  // namespace ORB_SLAM2
+#endif

@@ -115,7 +115,7 @@ class ORBmatcher:
         return nm.value, assigned
 
     def SearchByProjectionLast(self, Cur: Frame, valid, u, v, invz, octave, angle, descriptors, th, forward=False, backward=False,
-                               mbf=0.0, claimed=None, obs_positive=None):
+                               mbf=0.0, claimed=None, obs_positive=None, raw=False):
         """ref SearchByProjection(Frame &Cur, const Frame &Last, th, bMono), ORBmatcher.cc:1331-1473 (after the projection)."""
         a = [_u8(valid), _f32(u), _f32(v), _f32(invz), _i32(octave), _f32(angle), _u8(descriptors), _u8(obs_positive)]
         P = OrbLastPoints(len(a[0]), *[optr(x) for x in a])
@@ -125,10 +125,16 @@ class ORBmatcher:
         self.B.check(self._fn("search_by_projection_last")(Cur._h, C.byref(P), optr(cl), C.c_float(th), int(forward), int(backward),
                                                            C.c_float(mbf), int(self.mbCheckOrientation), ptr(assigned), C.byref(nm)),
                      "search_by_projection_last")
-        return nm.value, assigned
+        return nm.value, self._fold(assigned, raw)
+
+    @staticmethod
+    def _fold(assigned, raw):
+        """The C ABI reports -2 where the rotation filter reset an assignment to NULL and -1 where the feature was never
+        written; callers that only want the final holder get both as -1."""
+        return assigned if raw else np.where(assigned < 0, -1, assigned).astype(np.int32)
 
     def SearchWindowed(self, F: Frame, x, y, radius, min_level, max_level, descriptors, select, th_dist, valid=None, strict_levels=False,
-                       stereo_ref=None, stereo_tol=None, angle=None, claims=None, claimed=None, check_orientation=None):
+                       stereo_ref=None, stereo_tol=None, angle=None, claims=None, claimed=None, check_orientation=None, raw=False):
         """The generic projection-matcher loop (orb_search_windowed): SearchByProjection(Frame,KeyFrame,...) :1475-1602,
         SearchByProjection(KeyFrame,Scw,...) :290-403, Fuse :828-1103 and SearchBySim3 :1105-1329 map onto it."""
         a = dict(valid=_u8(valid), x=_f32(x), y=_f32(y), radius=_f32(radius), min_level=_i32(min_level), max_level=_i32(max_level),
@@ -142,7 +148,7 @@ class ORBmatcher:
         ori = self.mbCheckOrientation if check_orientation is None else check_orientation
         self.B.check(self._fn("search_windowed")(F._h, C.byref(Q), optr(cl), int(select), int(th_dist), C.c_float(self.mfNNratio),
                                                  int(ori), ptr(assigned), C.byref(nm)), "search_windowed")
-        return nm.value, assigned
+        return nm.value, self._fold(assigned, raw)
 
     def SearchByBoW(self, KF: Frame, F: Frame, kf_off, kf_idx, f_off, f_idx, kf_valid, f_valid=None, strict_low=False):
         """ref SearchByBoW(KeyFrame*, Frame&, ...) ORBmatcher.cc:159-288 (strict_low/f_valid: the KF-KF form :525-658).

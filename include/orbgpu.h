@@ -221,7 +221,8 @@ enum { ORB_SELECT_BEST = 0,         /* accept if best <= th_dist (ORBmatcher.cc:
        ORB_SELECT_RATIO_LEVEL = 1   /* best <= th_dist and not (same octave && best > ratio*second),
                                        ORBmatcher.cc:118-125                                     */ };
 /* claimed[i] != 0: feature i already holds a blocking map point on entry.  assigned[i] (out) =
- * index of the query whose map point ends up in mvpMapPoints[i], or -1.  With
+ * index of the query whose map point ends up in mvpMapPoints[i]; -1 = the call never wrote
+ * mvpMapPoints[i]; -2 = the call wrote it and the rotation filter then reset it to NULL.  With
  * check_orientation the 3-maxima rotation filter (ORBmatcher.cc:1451-1470) is applied; nmatches
  * follows the reference's counting (an overwritten assignment is still counted, F7).          */
 int orb_search_windowed(orb_frame *f, const orb_window_queries *q, const uint8_t *claimed, int select,

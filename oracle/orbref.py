@@ -380,3 +380,23 @@ def refm_search_by_projection_sim3(kf, Scw, world_xyz, normal_xyz, usable, max_d
     _check(L.refm_search_by_projection_sim3(kf._h, ptr(S), n, ptr(xyz), *[ptr(x) for x in a], f(fx), f(fy), f(cx), f(cy), int(th), f(nnratio),
                                             ptr(assigned), C.byref(nm), ptr(u), ptr(v), ptr(lvl), ptr(valid)), "refm sim3")
     return dict(assigned=assigned, nmatches=nm.value, u=u, v=v, level=lvl, valid=valid)
+
+
+REF_SHIM_PATH = os.path.join(_HERE, "_ref", "liborbmatcher_shim.so")
+_SHIM = None
+
+
+class ShimBackend:
+    """Same driver as ReferenceSourceBackend, but SearchForInitialization / SearchByProjection x2 / SearchByBoW go through the
+    PRODUCT's C++ shim (ar_orbslam2_b200/shim/ORBmatcher_gpu.cc over liborbgpu) compiled against the reference's Frame.h.
+    Needs a GPU."""
+    prefix = "refm_"
+
+    def __init__(self):
+        global _SHIM
+        if _SHIM is None:
+            _SHIM = C.CDLL(REF_SHIM_PATH)
+        self.L = _SHIM
+
+    def check(self, rc, what):
+        _check(rc, what)

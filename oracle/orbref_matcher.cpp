@@ -309,13 +309,13 @@ int orbref_search_windowed(orbref_frame *F, const orb_window_queries *Q, const u
         for (int i = 0; i < HISTO_LENGTH; i++) {
             if (i != ind1 && i != ind2 && i != ind3) {
                 for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
-                    holder[rotHist[i][j]] = -1;
+                    holder[rotHist[i][j]] = -3;   // the reference writes NULL here
                     nmatches--;
                 }
             }
         }
     }
-    for (int i = 0; i < F->N; i++) assigned[i] = holder[i] >= 0 ? holder[i] : -1;
+    for (int i = 0; i < F->N; i++) assigned[i] = holder[i] >= 0 ? holder[i] : (holder[i] == -3 ? -2 : -1);
     *nmatches_out = nmatches;
     return ORB_OK;
 }

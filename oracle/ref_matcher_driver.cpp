@@ -5,6 +5,9 @@
 // tests can compare reference source == restated oracle == GPU.
 #include "ORBmatcher.h"
 #include "../include/orbgpu.h"
+#ifdef USE_GPU_SHIM   // same driver, but the four tracking entry points go through the product shim (ar_orbslam2_b200/shim)
+#include "ORBmatcher_gpu.h"
+#endif
 
 #include <cstring>
 #include <memory>
@@ -97,7 +100,11 @@ int refm_search_for_initialization(refm_frame *f1, refm_frame *f2, float *prev_m
     for (int i = 0; i < f1->F.N; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
     std::vector<int> m12;
     ORBmatcher matcher(nnratio, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchForInitialization(f1->F, f2->F, prev, m12, window_size, nnratio, check_orientation != 0);
+#else
     *nmatches = matcher.SearchForInitialization(f1->F, f2->F, prev, m12, window_size);
+#endif
     for (int i = 0; i < f1->F.N; i++) {
         matches12[i] = m12[i];
         prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
@@ -127,7 +134,11 @@ int refm_search_by_projection_points(refm_frame *f, const orb_track_points *P, c
     pre.id = -2; pre.nObs = 1;
     for (int i = 0; i < F.N; i++) F.mvpMapPoints[i] = (claimed && claimed[i]) ? &pre : nullptr;
     ORBmatcher matcher(nnratio, true);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByProjection(F, pts, th, nnratio);
+#else
     *nmatches = matcher.SearchByProjection(F, pts, th);
+#endif
     for (int i = 0; i < F.N; i++) {
         MapPoint *m = F.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -200,7 +211,11 @@ int refm_search_by_projection_last(refm_frame *cur, refm_frame *last, const floa
         }
     }
     ORBmatcher matcher(nnratio, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByProjection(C, L, th, mono != 0, check_orientation != 0);
+#else
     *nmatches = matcher.SearchByProjection(C, L, th, mono != 0);
+#endif
     for (int i = 0; i < C.N; i++) {
         MapPoint *m = C.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -369,7 +384,11 @@ int refm_search_by_bow(refm_frame *kf, refm_frame *f, int ngroups, const int32_t
     fill_featvec(f->F.mFeatVec, ngroups, f_off, f_idx);
     std::vector<MapPoint *> out;
     ORBmatcher matcher(nnratio, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByBoW(K.get(), f->F, out, nnratio, check_orientation != 0);
+#else
     *nmatches = matcher.SearchByBoW(K.get(), f->F, out);
+#endif
     for (int i = 0; i < f->F.N; i++) matches[i] = out[i] ? out[i]->id : -1;
     return 0;
 }

@@ -37,3 +37,71 @@ def test_cpp_shim_stereo_frame(oracle, gpu_lib, tmp_path):
     assert np.array_equal(g("ur", np.uint32), ur.view(np.uint32)) and np.array_equal(g("dp", np.uint32), dp.view(np.uint32))
     # mvImagePyramid mirror keeps the reference's padded-plane layout (19-px reflect border around the ROI)
     assert np.array_equal(g("l3", np.uint8), rl.pyramid_level(3, True).ravel())
+
+
+def test_cpp_matcher_shim_equals_reference(oracle, gpu_lib):
+    """ar_orbslam2_b200/shim/ORBmatcher_gpu.cc -- the reference-side binding of INTEGRATION.md section 4 -- compiled against the
+    reference's own Frame.h (oracle/_ref/liborbmatcher_shim.so) and driven exactly like the reference's compiled ORBmatcher.cc
+    (liborbmatcher_ref.so): SearchForInitialization, SearchByProjection(Frame,MapPoints), SearchByProjection(Cur,Last),
+    SearchByBoW must leave the same results in the reference's data structures."""
+    import test_reference_matcher_cpu as T
+    from ar_orbslam2_b200.synth import SplitMix64, shifted_frame, synth_frame
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+    if not (oracle.ref_matcher_available() and os.path.exists(oracle.REF_SHIM_PATH)):
+        pytest.skip("oracle/_ref shim library not built")
+    W, H = T.W, T.H
+    a = synth_frame(W, H, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    ex = oracle.RefExtractor(2000)
+    ka, da = ex.extract(a)
+    kb, db = ex.extract(b)
+    scale = ex.tables()["scale"]
+    bounds = (0.0, float(W), 0.0, float(H))
+    rb, sb = oracle.ReferenceSourceBackend(), oracle.ShimBackend()
+    mk = lambda k, d, be, ur=None: Frame(k, d, scale, bounds, u_right=ur, backend=be)
+    # SearchForInitialization
+    r1, r2, s1, s2 = mk(ka, da, rb), mk(kb, db, rb), mk(ka, da, sb), mk(kb, db, sb)
+    prev = np.stack([ka["x"], ka["y"]], 1).astype(np.float32).copy()
+    pr, ps = prev.copy(), prev.copy()
+    nr, mr = ORBmatcher(0.9, True, backend=rb).SearchForInitialization(r1, r2, pr, 100)
+    ns, ms = ORBmatcher(0.9, True, backend=sb).SearchForInitialization(s1, s2, ps, 100)
+    assert nr > 100 and ns == nr and np.array_equal(ms, mr) and np.array_equal(ps, pr)
+    # SearchByProjection(Frame, MapPoints)
+    n = len(ka)
+    ur = np.where(np.arange(len(kb)) % 3 == 0, kb["x"] - 5.0, -1.0).astype(np.float32)
+    rf, sf = mk(kb, db, rb, ur), mk(kb, db, sb, ur)
+    rng = SplitMix64(9)
+    in_view = np.array([rng.next() % 10 != 0 for _ in range(n)], np.uint8)
+    px, py = (ka["x"] + 7).astype(np.float32), (ka["y"] + 4).astype(np.float32)
+    args = (in_view, px, py, (px - 6).astype(np.float32), ka["octave"].astype(np.int32), np.full(n, 0.9, np.float32), da, 3.0,
+            (np.arange(len(kb)) % 13 == 0).astype(np.uint8), (np.arange(n) % 4 != 0).astype(np.uint8))
+    nr, ar = ORBmatcher(0.8, backend=rb).SearchByProjectionPoints(rf, *args)
+    ns, as_ = ORBmatcher(0.8, backend=sb).SearchByProjectionPoints(sf, *args)
+    assert nr > 100 and ns == nr and np.array_equal(as_, ar)
+    # SearchByProjection(Cur, Last): the shim runs the reference's pose algebra itself
+    ura = np.where(np.arange(n) % 3 == 0, ka["x"] - 5.0, -1.0).astype(np.float32)
+    z = np.array([2 + (SplitMix64(i).next() % 1000) / 100 for i in range(n)], np.float32)
+    xyz = np.stack([(ka["x"] - T.CX) * z / T.FX, (ka["y"] - T.CY) * z / T.FY, z], 1).astype(np.float32)
+    has, obs, claimed = (np.arange(n) % 17 != 0).astype(np.uint8), (np.arange(n) % 5 != 0).astype(np.uint8), (np.arange(n) % 11 == 0).astype(np.uint8)
+    Tl = np.eye(4, dtype=np.float32)
+    for mono, tz in ((True, 0.0), (False, 0.3), (False, -0.3)):
+        Tc = np.eye(4, dtype=np.float32); Tc[:3, 3] = (0.05, 0.02, tz)
+        R = oracle.refm_search_by_projection_last(mk(ka, da, rb, ura), mk(ka, da, rb), xyz, has, obs, claimed, Tc, Tl, T.FX, T.FY, T.CX, T.CY, 40.0, 0.11,
+                                                  15.0, mono, 0.9, True)
+        S = oracle.refm_search_by_projection_last(mk(ka, da, sb, ura), mk(ka, da, sb), xyz, has, obs, claimed, Tc, Tl, T.FX, T.FY, T.CX, T.CY, 40.0, 0.11,
+                                                  15.0, mono, 0.9, True)
+        assert R["nmatches"] > 50 and S["nmatches"] == R["nmatches"] and np.array_equal(S["assigned"], R["assigned"])
+    # SearchByBoW(KeyFrame, Frame)
+    def groups(k, dx, dy):
+        node = ((k["y"] - dy) // 40).astype(np.int64) * 19 + ((k["x"] - dx) // 40).astype(np.int64)
+        return node, np.argsort(node, kind="stable")
+    na, oa = groups(ka, 0, 0)
+    nb, ob = groups(kb, 7, 4)
+    kf_off, f_off, kf_idx, f_idx = [0], [0], [], []
+    for c in np.intersect1d(na, nb):
+        kf_idx += oa[na[oa] == c].tolist(); f_idx += ob[nb[ob] == c].tolist()
+        kf_off.append(len(kf_idx)); f_off.append(len(f_idx))
+    kv = (np.arange(n) % 7 != 0).astype(np.uint8)
+    nr, mr = oracle.refm_search_by_bow(mk(ka, da, rb), mk(kb, db, rb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
+    ns, ms = oracle.refm_search_by_bow(mk(ka, da, sb), mk(kb, db, sb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
+    assert nr > 100 and ns == nr and np.array_equal(ms, mr)
