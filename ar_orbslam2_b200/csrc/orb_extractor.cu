@@ -179,6 +179,12 @@ constexpr int FT_PW = 19;                 // tile row pitch in words (76 bytes >
 constexpr int FT_PB = FT_PW * 4;
 constexpr int FV_PB = 72;                 // vmap row pitch in bytes (computed width <= 66, + 2 apron)
 
+struct FastLevel {   // what k_fast_cells needs of one level, passed by value
+    int level, nlevels, ini_th, min_th;
+    int pitch, maxBX, maxBY, wCell, hCell, cand_off, cand_cap, cand_frame;
+    long long interior_off, pyr_frame;
+};
+
 struct FastDiv {   // exact n / d for n < 2^32 / d via one multiply-high
     uint32_t M;
     int d;
@@ -217,20 +223,19 @@ __device__ __forceinline__ int fast_arc_min(const uint8_t *p, int sgn) {
 }
 
 __global__ void __launch_bounds__(FAST_THREADS)
-k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const uint32_t *__restrict__ cells,
-             uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count, int *__restrict__ err) {
+k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
+             int *__restrict__ err) {
+    // one launch per level, grid = (cell columns, cell rows, frames): the cell's geometry comes from the kernel
+    // parameters (constant bank), so nothing has to be fetched from global memory before the ROI itself
     __shared__ uint32_t tileW[FAST_TILE_MAX * FT_PW];
-    __shared__ uint32_t vmapW[(FAST_TILE_MAX - 4) * FV_PB / 4];   // computed region + 1 px apron
+    __shared__ uint4 vmapQ[(FAST_TILE_MAX - 4) * FV_PB / 16];   // computed region + 1 px apron
     __shared__ uint16_t surv[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
     __shared__ uint16_t surv2[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
     __shared__ int s_nsurv, s_n2, s_nkp, s_base;
     __shared__ uint32_t s_magic;
     __shared__ int s_wsum[FAST_THREADS / 32];
 
-    const int b = blockIdx.y;
-    const uint32_t cinfo = __ldg(cells + blockIdx.x);
-    const int level = cinfo & 15, ci = (cinfo >> 4) & 1023, cj = cinfo >> 14;
-    const LevelGeom &g = G->lv[level];
+    const int b = blockIdx.z, ci = blockIdx.y, cj = blockIdx.x, level = g.level;
     const int minB = EDGE - 3;
     // ROI handed to cv::FAST by the reference (ref :759-773)
     const int iniX = minB + cj * g.wCell, iniY = minB + ci * g.hCell;
@@ -241,26 +246,26 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const 
 
     // ---- 1. stage the ROI; byte (y, x) of the ROI sits at tile[y * FT_PB + x + sft]
     const int sft = (iniX + XOFF) & 3;
-    const uint8_t *img = pyr + (size_t)b * G->pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
+    const uint8_t *img = pyr + (size_t)b * g.pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
     {
         const int nW = (tw + sft + 3) >> 2;   // <= 19 words per row: a warp takes a row
         if (lane < nW)
             for (int y = tid >> 5; y < th; y += FAST_THREADS / 32)
                 tileW[y * FT_PW + lane] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * g.pitch) + lane);
-        for (int t = tid; t < (ch + 2) * (FV_PB / 4); t += FAST_THREADS) vmapW[t] = 0;
+        for (int t = tid; t < ((ch + 2) * FV_PB + 15) / 16; t += FAST_THREADS) vmapQ[t] = make_uint4(0, 0, 0, 0);
     }
     if (tid == 0) { s_nsurv = 0; s_n2 = 0; s_nkp = 0; s_magic = cw > 1 ? 0xFFFFFFFFu / (uint32_t)cw + 1u : 0u; }
     __syncthreads();
     if (cw <= 0 || ch <= 0) return;
     const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW) + sft;
-    uint8_t *vmap = reinterpret_cast<uint8_t *>(vmapW);
+    uint8_t *vmap = reinterpret_cast<uint8_t *>(vmapQ);
     const FastDiv dC(cw, s_magic);
     const int npx = cw * ch;
 
     // ---- 2. compass test at the lower threshold.  Two circularly adjacent compass points beyond the threshold
     // <=> one of {d0,d8} and one of {d4,d12}:  H = min(max(d0,d8), max(d4,d12)) > t,  L likewise with signs flipped.
     // A thread keeps one result bit per pixel it owns and the survivors are compacted once per CTA.
-    const int tq = min(G->ini_th, G->min_th);
+    const int tq = min(g.ini_th, g.min_th);
     unsigned bitsH = 0, bitsL = 0;
     {
         int k = 0;
@@ -326,7 +331,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const 
     __syncthreads();
 
     // ---- 4. NMS + threshold, retry at min_th if the cell is empty (ref :780-784)
-    int thr = G->ini_th;
+    int thr = g.ini_th;
     for (int attempt = 0; attempt < 2; attempt++) {
         int mine = 0;
         for (int s = tid; s < nsurv; s += FAST_THREADS) {
@@ -342,17 +347,17 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const 
         }
         if (mine) atomicAdd(&s_nkp, mine);
         __syncthreads();
-        if (s_nkp > 0 || attempt == 1 || G->min_th == thr) break;
-        thr = G->min_th;
+        if (s_nkp > 0 || attempt == 1 || g.min_th == thr) break;
+        thr = g.min_th;
     }
     const int nkp = s_nkp;
     if (nkp == 0) return;
-    uint32_t *cnt = cand_count + (size_t)b * G->nlevels + level;
+    uint32_t *cnt = cand_count + (size_t)b * g.nlevels + level;
     if (tid == 0) s_base = (int)atomicAdd(cnt, (uint32_t)nkp);
     __syncthreads();
     if (tid == 0) s_nkp = 0;
     __syncthreads();
-    uint32_t *out = cand + (size_t)b * G->cand_frame + g.cand_off;
+    uint32_t *out = cand + (size_t)b * g.cand_frame + g.cand_off;
     for (int s = tid; s < nsurv; s += FAST_THREADS) {
         const int code = surv[s];
         if (!(code & 0x8000)) continue;
@@ -1345,8 +1350,16 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->launches++;
     }
     prof_mark(ex, 2);
-    k_fast_cells<<<dim3(G.total_cells, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_cells, ex->d_cand, d_cand_count, ex->d_err);
-    ex->launches++;
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom &g = G.lv[l];
+        FastLevel fl;
+        fl.level = l; fl.nlevels = G.nlevels; fl.ini_th = G.ini_th; fl.min_th = G.min_th;
+        fl.pitch = g.pitch; fl.maxBX = g.maxBX; fl.maxBY = g.maxBY; fl.wCell = g.wCell; fl.hCell = g.hCell;
+        fl.cand_off = g.cand_off; fl.cand_cap = g.cand_cap; fl.cand_frame = G.cand_frame;
+        fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
+        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
+        ex->launches++;
+    }
     prof_mark(ex, 3);
     k_octree<<<dim3(G.nlevels, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), st>>>(
         ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err);
