@@ -159,81 +159,100 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
 }
 
 // ------------------------------------------------------------------------------------------
-// FAST-9/16 per cell.  One CTA per (cell, frame).  V = arc strength: corner at t
+// FAST-9/16 per cell.  One CTA per (cell, frame), one launch per level.  V = arc strength: corner at t
 // <=> V > t, response V-1, 3x3 non-max suppression inside the cell's computed region only.
 //
-// Stages inside the CTA (all in shared memory):
-//   1. the cell's ROI is staged as aligned 32-bit words;
-//   2. every pixel takes the 4-compass test at the lower threshold: a 9-arc always holds two ADJACENT compass
-//      points, so a corner needs two adjacent compass pixels all brighter (type H) or all darker (type L);
-//      ~20% of pixels survive and are compacted with warp ballots;
-//   3. survivors get the exact arc strength on dense warps.  An H survivor can only be a brighter-arc corner,
-//      so one min/max network over sign*d gives its V; the rare pixels that pass both tests are re-evaluated
-//      with the other sign from a second list;
-//   4. threshold + NMS (+ the 20 -> 7 retry when the cell is empty), candidates appended to the level's list.
+// Stages inside the CTA (all in dynamic shared memory sized for the level's cell):
+//   1. the cell's ROI is staged as aligned 32-bit words (cp.async);
+//   2. every pixel takes the 4-compass test at the current threshold: a 9-arc always holds two ADJACENT compass
+//      points, so a corner needs one of {up, down} and one of {left, right} brighter (type H) or darker (type L)
+//      than the centre by more than t.  A thread tests one aligned word = 4 pixels with 16x2 SIMD min/max
+//      (VIMNMX.S16x2) and leaves a flag word; a block scan then compacts the H and the L survivors into two lists;
+//   3. survivors get the exact arc strength on dense warps, two same-type survivors per thread in the two 16-bit
+//      lanes (VIMNMX3.S16x2); a pixel on both lists takes the larger of the two;
+//   4. threshold + NMS; candidates appended to the level's list.
+// The cell runs at iniThFAST first and repeats 2-4 at minThFAST only when it came up empty (ref :775-784): a pixel
+// that fails the compass test at t has V <= t, so it can neither be a corner at t nor suppress one.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
-__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+constexpr int FAST_T = FAST_THREADS;
+constexpr int FT_PW = 19;                 // tile row pitch in words (76 bytes >= 72 + 3 bytes of alignment slack); compile-time
+constexpr int FT_PB = FT_PW * 4;          // so that the 16 circle offsets are immediates
+constexpr int FV_PB = 72;                 // score-map row pitch in bytes (computed width <= 66, + 2 apron)
 
-constexpr int FT_PW = 19;                 // tile row pitch in words (76 bytes >= 72 + 3 bytes of alignment slack)
-constexpr int FT_PB = FT_PW * 4;
-constexpr int FV_PB = 72;                 // vmap row pitch in bytes (computed width <= 66, + 2 apron)
-
-struct FastLevel {   // what k_fast_cells needs of one level, passed by value
+struct FastLevel {   // what k_fast_cells needs of one level, passed by value (constant bank)
     int level, nlevels, ini_th, min_th;
     int pitch, maxBX, maxBY, wCell, hCell, cand_off, cand_cap, cand_frame;
+    int off_vmap, off_flags, off_survH, off_survL;   // byte offsets into dynamic shared memory (16-aligned)
     long long interior_off, pyr_frame;
 };
+
+// magic[d] = floor((2^32 - 1) / d) + 1: n / d == umulhi(n, magic[d]) for the small n used here (d = 0, 1 unused)
+struct FastMagic { uint32_t m[80]; };
+static constexpr FastMagic make_fast_magic() {
+    FastMagic t{};
+    for (int d = 2; d < 80; d++) t.m[d] = 0xFFFFFFFFu / (uint32_t)d + 1u;
+    return t;
+}
+__constant__ FastMagic c_fast_magic = make_fast_magic();
 
 struct FastDiv {   // exact n / d for n < 2^32 / d via one multiply-high
     uint32_t M;
     int d;
-    __device__ __forceinline__ FastDiv(int dd, uint32_t magic) : M(magic), d(dd) {}   // magic = 0xFFFFFFFF / d + 1
+    __device__ __forceinline__ explicit FastDiv(int dd) : M(c_fast_magic.m[dd]), d(dd) {}
     __device__ __forceinline__ int div(int n) const { return d > 1 ? (int)__umulhi((uint32_t)n, M) : n; }
 };
 
-// max over the 16 arcs of 9 consecutive circle pixels of min(sgn * (I(p) - I(q)))
-__device__ __forceinline__ int fast_arc_min(const uint8_t *p, int sgn) {
-    const int cs = sgn * (int)p[0], ns = -sgn;
-    int d[16];
-    d[0] = cs + ns * p[3 * FT_PB];
-    d[1] = cs + ns * p[3 * FT_PB + 1];
-    d[2] = cs + ns * p[2 * FT_PB + 2];
-    d[3] = cs + ns * p[FT_PB + 3];
-    d[4] = cs + ns * p[3];
-    d[5] = cs + ns * p[-FT_PB + 3];
-    d[6] = cs + ns * p[-2 * FT_PB + 2];
-    d[7] = cs + ns * p[-3 * FT_PB + 1];
-    d[8] = cs + ns * p[-3 * FT_PB];
-    d[9] = cs + ns * p[-3 * FT_PB - 1];
-    d[10] = cs + ns * p[-2 * FT_PB - 2];
-    d[11] = cs + ns * p[-FT_PB - 3];
-    d[12] = cs + ns * p[-3];
-    d[13] = cs + ns * p[FT_PB - 3];
-    d[14] = cs + ns * p[2 * FT_PB - 2];
-    d[15] = cs + ns * p[3 * FT_PB - 1];
-    int m3[16];
+static size_t fast_smem_layout(FastLevel &fl) {
+    const int tw = fl.wCell + 6, th = fl.hCell + 6;
+    (void)tw;
+    const int nwc = (fl.wCell + 3) / 4 + 1;             // words per computed row, worst alignment
+    size_t off = (size_t)th * FT_PB;
+    auto carve = [&](size_t bytes) { off = (off + 15) & ~(size_t)15; const size_t o = off; off += bytes; return (int)o; };
+    fl.off_vmap = carve((size_t)(fl.hCell + 2) * FV_PB + 16);
+    fl.off_flags = carve((size_t)fl.hCell * nwc * 4);
+    fl.off_survH = carve((size_t)fl.wCell * fl.hCell * 2);
+    fl.off_survL = carve((size_t)fl.wCell * fl.hCell * 2);
+    return (off + 15) & ~(size_t)15;
+}
+
+// Two same-type survivors in the 16-bit lanes.  Lane value 256 + s*(I(p) - I(q_k)), s = +1 (brighter centre) or -1:
+// always in [1, 511], so packed adds never carry between lanes.  Returns 256 + V per lane.
+template <bool DARK>
+__device__ __forceinline__ uint32_t fast_arc_pair(const uint8_t *p0, const uint8_t *p1) {
+    constexpr int PB = FT_PB;
+    const uint32_t cp = __byte_perm(p0[0], p1[0], 0x5410);
+    const uint32_t base = DARK ? 0x01000100u - cp : 0x01000100u + cp;
+    const int off[16] = {3 * PB, 3 * PB + 1, 2 * PB + 2, PB + 3, 3, -PB + 3, -2 * PB + 2, -3 * PB + 1,
+                         -3 * PB, -3 * PB - 1, -2 * PB - 2, -PB - 3, -3, PB - 3, 2 * PB - 2, 3 * PB - 1};
+    uint32_t e[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) m3[k] = min3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-    int a = -256;
+    for (int k = 0; k < 16; k++) {
+        const uint32_t q = __byte_perm(p0[off[k]], p1[off[k]], 0x5410);
+        e[k] = DARK ? base + q : base - q;
+    }
+    uint32_t m3[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    uint32_t a = 0;
 #pragma unroll
     for (int k = 0; k < 16; k += 2)
-        a = max3(a, min3(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]), min3(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]));
+        a = __vimax3_s16x2(a, __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]),
+                           __vimin3_s16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]));
     return a;
 }
 
-__global__ void __launch_bounds__(FAST_THREADS)
+__global__ void __launch_bounds__(FAST_T)
 k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
              int *__restrict__ err) {
-    // one launch per level, grid = (cell columns, cell rows, frames): the cell's geometry comes from the kernel
-    // parameters (constant bank), so nothing has to be fetched from global memory before the ROI itself
-    __shared__ uint32_t tileW[FAST_TILE_MAX * FT_PW];
-    __shared__ uint4 vmapQ[(FAST_TILE_MAX - 4) * FV_PB / 16];   // computed region + 1 px apron
-    __shared__ uint16_t surv[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
-    __shared__ uint16_t surv2[(FAST_TILE_MAX - 6) * (FAST_TILE_MAX - 6)];
-    __shared__ int s_nsurv, s_n2, s_nkp, s_base;
-    __shared__ uint32_t s_magic;
-    __shared__ int s_wsum[FAST_THREADS / 32];
+    extern __shared__ __align__(16) unsigned char fsm[];
+    __shared__ int s_nkp, s_base;
+    __shared__ int s_wsum[FAST_T / 32];
+
+    uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
+    uint8_t *vmap = fsm + g.off_vmap;                                   // computed region + 1 px apron
+    uint32_t *flags = reinterpret_cast<uint32_t *>(fsm + g.off_flags);  // per word: bit 8j+7 = pixel j is H, 8j+6 = L
+    uint16_t *survH = reinterpret_cast<uint16_t *>(fsm + g.off_survH);  // code = y << 7 | x (computed-region coords)
+    uint16_t *survL = reinterpret_cast<uint16_t *>(fsm + g.off_survL);  // bit 14: also on the H list; bit 15: kept
 
     const int b = blockIdx.z, ci = blockIdx.y, cj = blockIdx.x, level = g.level;
     const int minB = EDGE - 3;
@@ -242,113 +261,135 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     const int maxX = min(iniX + g.wCell + 6, g.maxBX), maxY = min(iniY + g.hCell + 6, g.maxBY);
     const int tw = maxX - iniX, th = maxY - iniY;      // ROI size
     const int cw = tw - 6, ch = th - 6;                // computed region (ROI minus 3 px rim)
-    const int tid = threadIdx.x, lane = tid & 31;
-
-    // ---- 1. stage the ROI; byte (y, x) of the ROI sits at tile[y * FT_PB + x + sft]
-    const int sft = (iniX + XOFF) & 3;
-    const uint8_t *img = pyr + (size_t)b * g.pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
-    {
-        const int nW = (tw + sft + 3) >> 2;   // <= 19 words per row: a warp takes a row
-        if (lane < nW)
-            for (int y = tid >> 5; y < th; y += FAST_THREADS / 32)
-                tileW[y * FT_PW + lane] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * g.pitch) + lane);
-        for (int t = tid; t < ((ch + 2) * FV_PB + 15) / 16; t += FAST_THREADS) vmapQ[t] = make_uint4(0, 0, 0, 0);
-    }
-    if (tid == 0) { s_nsurv = 0; s_n2 = 0; s_nkp = 0; s_magic = cw > 1 ? 0xFFFFFFFFu / (uint32_t)cw + 1u : 0u; }
-    __syncthreads();
     if (cw <= 0 || ch <= 0) return;
+    const int tid = threadIdx.x, lane = tid & 31;
+    constexpr int TPW = FT_PW, TPB = FT_PB, VPB = FV_PB;
+
+    // ---- 1. stage the ROI; byte (y, x) of the ROI sits at tile byte y * TPB + x + sft
+    const int sft = (iniX + XOFF) & 3;
+    {
+        const uint8_t *img = pyr + (size_t)b * g.pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
+        const int nW = (tw + sft + 3) >> 2;
+        const FastDiv dW(nW);
+        const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tileW);
+        for (int i = tid; i < th * nW; i += FAST_T) {
+            const int y = dW.div(i), w = i - y * nW;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(tile_s + (uint32_t)(y * TPW + w) * 4u),
+                         "l"(img + (size_t)y * g.pitch + w * 4));
+        }
+        asm volatile("cp.async.commit_group;");
+        uint4 *vq = reinterpret_cast<uint4 *>(vmap);
+        for (int t = tid; t < ((ch + 2) * VPB + 15) / 16; t += FAST_T) vq[t] = make_uint4(0, 0, 0, 0);
+        if (tid == 0) s_nkp = 0;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
     const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW) + sft;
-    uint8_t *vmap = reinterpret_cast<uint8_t *>(vmapQ);
-    const FastDiv dC(cw, s_magic);
-    const int npx = cw * ch;
 
-    // ---- 2. compass test at the lower threshold.  Two circularly adjacent compass points beyond the threshold
-    // <=> one of {d0,d8} and one of {d4,d12}:  H = min(max(d0,d8), max(d4,d12)) > t,  L likewise with signs flipped.
-    // A thread keeps one result bit per pixel it owns and the survivors are compacted once per CTA.
-    const int tq = min(g.ini_th, g.min_th);
-    unsigned bitsH = 0, bitsL = 0;
-    {
-        int k = 0;
-        for (int i = tid; i < npx; i += FAST_THREADS, k++) {
-            const int y = dC.div(i), x = i - y * cw;
-            const uint8_t *p = tile + (y + 3) * FT_PB + x + 3;
-            const int c = p[0];
-            const int d0 = c - p[3 * FT_PB], d4 = c - p[3], d8 = c - p[-3 * FT_PB], d12 = c - p[-3];
-            const int hv = min(max(d0, d8), max(d4, d12)), lv = max(min(d0, d8), min(d4, d12));
-            bitsH |= (unsigned)(hv > tq) << k;
-            bitsL |= (unsigned)(lv < -tq) << k;
+    // words of a tile row that hold computed pixels: bytes [3 + sft, 3 + sft + cw)
+    const int w0 = (3 + sft) >> 2, nWc = ((2 + sft + cw) >> 2) - w0 + 1;
+    const FastDiv dU(nWc);
+    const int nunits = ch * nWc;
+
+    int thr = g.ini_th, nH = 0, nL = 0;
+    for (;;) {
+        // ---- 2. compass test at thr, 4 pixels per thread and step.  Lanes: A = (px0, px2), B = (px1, px3).
+        //   H <=> c - max(min(U, D), min(L, R)) > t        L <=> min(max(U, D), max(L, R)) - c > t
+        int cnt = 0;   // H survivors | L survivors << 16 of this thread
+        {
+            const uint32_t tb = (uint32_t)thr * 0x00010001u + 0x80008000u;
+            for (int u = tid; u < nunits; u += FAST_T) {
+                const int yy = dU.div(u), w = u - yy * nWc + w0;
+                const uint32_t *r = tileW + (yy + 3) * TPW + w;
+                const uint32_t C = r[0], P = r[-1], N = r[1], U = r[-3 * TPW], D = r[3 * TPW];
+                const uint32_t cA = __byte_perm(C, 0, 0x4240), cB = __byte_perm(C, 0, 0x4341);
+                const uint32_t uA = __byte_perm(U, 0, 0x4240), uB = __byte_perm(U, 0, 0x4341);
+                const uint32_t dA = __byte_perm(D, 0, 0x4240), dB = __byte_perm(D, 0, 0x4341);
+                const uint32_t lA = __byte_perm(P, 0, 0x4341), lB = __byte_perm(P, C, 0x0402) & 0x00ff00ffu;
+                const uint32_t rA = __byte_perm(C, N, 0x0503) & 0x00ff00ffu, rB = __byte_perm(N, 0, 0x4240);
+                const uint32_t mA = __vmaxs2(__vmins2(uA, dA), __vmins2(lA, rA)), mB = __vmaxs2(__vmins2(uB, dB), __vmins2(lB, rB));
+                const uint32_t nA = __vmins2(__vmaxs2(uA, dA), __vmaxs2(lA, rA)), nB = __vmins2(__vmaxs2(uB, dB), __vmaxs2(lB, rB));
+                // lane bit 15 set <=> NOT a survivor (no carries between lanes: every lane stays in [0x7f01, 0x81fe])
+                const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
+                const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
+                const int lo = 3 + sft - 4 * w, hi = lo + cw;                                         // valid bytes [lo, hi)
+                const uint32_t vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
+                const uint32_t f = (~Hb & vm) | ((~Lb & vm) >> 1);
+                flags[u] = f;
+                cnt += __popc(f & 0x80808080u) + (__popc(f & 0x40404040u) << 16);
+            }
         }
-    }
-    {
-        // block-wide exclusive scan of (survivors | both-type << 16) per thread
-        const unsigned any = bitsH | bitsL, both = bitsH & bitsL;
-        const int mine = __popc(any) | (__popc(both) << 16);
-        int incl = mine;
+        {
+            // block-wide exclusive scan of the per-thread counts, then every thread appends its survivors
+            int incl = cnt;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        if (lane == 31) s_wsum[tid >> 5] = incl;
-        __syncthreads();
-        int wbase = 0, total = 0;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            if (lane == 31) s_wsum[tid >> 5] = incl;
+            __syncthreads();
+            int wbase = 0, total = 0;
 #pragma unroll
-        for (int w = 0; w < FAST_THREADS / 32; w++) {
-            const int v = s_wsum[w];
-            if (w < (tid >> 5)) wbase += v;
-            total += v;
+            for (int w = 0; w < FAST_T / 32; w++) {
+                const int v = s_wsum[w];
+                if (w < (tid >> 5)) wbase += v;
+                total += v;
+            }
+            const int pos = wbase + incl - cnt;
+            int pH = pos & 0xffff, pL = pos >> 16;
+            nH = total & 0xffff; nL = total >> 16;
+            for (int u = tid; u < nunits; u += FAST_T) {
+                const uint32_t f = flags[u];
+                if (!f) continue;
+                const int yy = dU.div(u), w = u - yy * nWc + w0;
+                const int code0 = (yy << 7) + 4 * w - 3 - sft;       // + j = code of pixel j
+                for (uint32_t m = f & 0x80808080u; m; m &= m - 1) survH[pH++] = (uint16_t)(code0 + ((__ffs(m) - 1) >> 3));
+                for (uint32_t m = f & 0x40404040u; m; m &= m - 1) {
+                    const int bit = __ffs(m) - 1;
+                    survL[pL++] = (uint16_t)((code0 + (bit >> 3)) | (((f >> (bit + 1)) & 1) << 14));
+                }
+            }
         }
-        int pos = wbase + incl - mine;
-        int p1 = pos & 0xffff, p2 = pos >> 16;
-        for (unsigned m = any; m; m &= m - 1) {
-            const int k = __ffs(m) - 1, i = tid + k * FAST_THREADS;
-            const bool isH = (bitsH >> k) & 1;
-            surv[p1++] = (uint16_t)(i | (isH ? 0 : 0x2000));   // bit 13: evaluate as darker type
-            if ((both >> k) & 1) surv2[p2++] = (uint16_t)i;
-        }
-        if (tid == 0) { s_nsurv = total & 0xffff; s_n2 = total >> 16; }
-    }
-    __syncthreads();
-
-    // ---- 3. exact arc strength of the survivors
-    const int nsurv = s_nsurv, n2 = s_n2;
-    for (int s = tid; s < nsurv; s += FAST_THREADS) {
-        const int code = surv[s], i = code & 0x1fff;
-        const int y = dC.div(i), x = i - y * cw;
-        const int V = fast_arc_min(tile + (y + 3) * FT_PB + x + 3, (code & 0x2000) ? -1 : 1);
-        vmap[(y + 1) * FV_PB + x + 1] = (uint8_t)max(V, 0);
-    }
-    if (n2) {
         __syncthreads();
-        for (int s = tid; s < n2; s += FAST_THREADS) {   // pixels that passed both compass tests: the darker side
-            const int i = surv2[s];
-            const int y = dC.div(i), x = i - y * cw;
-            const int V = fast_arc_min(tile + (y + 3) * FT_PB + x + 3, -1);
-            uint8_t *v = &vmap[(y + 1) * FV_PB + x + 1];
-            *v = (uint8_t)max((int)*v, V);
-        }
-    }
-    __syncthreads();
 
-    // ---- 4. NMS + threshold, retry at min_th if the cell is empty (ref :780-784)
-    int thr = g.ini_th;
-    for (int attempt = 0; attempt < 2; attempt++) {
+        // ---- 3. exact arc strength of the survivors, two per thread
+        for (int s = tid; 2 * s < nH; s += FAST_T) {
+            const int c0 = survH[2 * s], c1 = 2 * s + 1 < nH ? survH[2 * s + 1] : c0;
+            const int y0 = c0 >> 7, x0 = c0 & 127, y1 = c1 >> 7, x1 = c1 & 127;
+            const uint32_t a = fast_arc_pair<false>(tile + (y0 + 3) * TPB + x0 + 3, tile + (y1 + 3) * TPB + x1 + 3);
+            vmap[(y0 + 1) * VPB + x0 + 1] = (uint8_t)max((int)(a & 0xffff) - 256, 0);
+            vmap[(y1 + 1) * VPB + x1 + 1] = (uint8_t)max((int)(a >> 16) - 256, 0);
+        }
+        __syncthreads();
+        for (int s = tid; 2 * s < nL; s += FAST_T) {
+            const int c0 = survL[2 * s] & 0x3fff, c1 = 2 * s + 1 < nL ? survL[2 * s + 1] & 0x3fff : c0;
+            const int y0 = c0 >> 7, x0 = c0 & 127, y1 = c1 >> 7, x1 = c1 & 127;
+            const uint32_t a = fast_arc_pair<true>(tile + (y0 + 3) * TPB + x0 + 3, tile + (y1 + 3) * TPB + x1 + 3);
+            uint8_t *v0 = &vmap[(y0 + 1) * VPB + x0 + 1], *v1 = &vmap[(y1 + 1) * VPB + x1 + 1];
+            *v0 = (uint8_t)max((int)(a & 0xffff) - 256, (int)*v0);     // old value: 0, this pixel's brighter-arc V, or
+            *v1 = (uint8_t)max((int)(a >> 16) - 256, (int)*v1);        // what the first attempt left (the same V)
+        }
+        __syncthreads();
+
+        // ---- 4. threshold + NMS over both lists (a pixel on both is judged on the H list)
         int mine = 0;
-        for (int s = tid; s < nsurv; s += FAST_THREADS) {
-            const int i = surv[s] & 0x1fff;
-            const int y = dC.div(i), x = i - y * cw;
-            const uint8_t *v = &vmap[(y + 1) * FV_PB + x + 1];
+        for (int s = tid; s < nH + nL; s += FAST_T) {
+            uint16_t *e = s < nH ? &survH[s] : &survL[s - nH];
+            const int code = *e;
+            if (code & 0x4000) continue;
+            const uint8_t *v = &vmap[((code >> 7) + 1) * VPB + (code & 127) + 1];
             const int V = v[0];
-            if (V > thr && V > v[-1] && V > v[1] && V > v[-FV_PB - 1] && V > v[-FV_PB] && V > v[-FV_PB + 1] &&
-                V > v[FV_PB - 1] && V > v[FV_PB] && V > v[FV_PB + 1]) {
-                surv[s] = (uint16_t)(surv[s] | 0x8000);
+            if (V > thr && V > v[-1] && V > v[1] && V > v[-VPB - 1] && V > v[-VPB] && V > v[-VPB + 1] &&
+                V > v[VPB - 1] && V > v[VPB] && V > v[VPB + 1]) {
+                *e = (uint16_t)(code | 0x8000);
                 mine++;
             }
         }
         if (mine) atomicAdd(&s_nkp, mine);
         __syncthreads();
-        if (s_nkp > 0 || attempt == 1 || g.min_th == thr) break;
-        thr = g.min_th;
+        if (s_nkp > 0 || thr == g.min_th) break;
+        thr = g.min_th;   // empty cell: once more at the lower threshold (ref :780-784)
     }
     const int nkp = s_nkp;
     if (nkp == 0) return;
@@ -358,12 +399,11 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     if (tid == 0) s_nkp = 0;
     __syncthreads();
     uint32_t *out = cand + (size_t)b * g.cand_frame + g.cand_off;
-    for (int s = tid; s < nsurv; s += FAST_THREADS) {
-        const int code = surv[s];
+    for (int s = tid; s < nH + nL; s += FAST_T) {
+        const int code = s < nH ? survH[s] : survL[s - nH];
         if (!(code & 0x8000)) continue;
-        const int ii = code & 0x1fff;
-        const int y = dC.div(ii), x = ii - y * cw;
-        const int V = vmap[(y + 1) * FV_PB + x + 1];
+        const int y = (code >> 7) & 127, x = code & 127;
+        const int V = vmap[(y + 1) * VPB + x + 1];
         const int slot = s_base + atomicAdd(&s_nkp, 1);
         if (slot < g.cand_cap) {
             // window-relative coordinates (ref :789-790): ROI x + j*wCell
@@ -1357,7 +1397,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         fl.pitch = g.pitch; fl.maxBX = g.maxBX; fl.maxBY = g.maxBY; fl.wCell = g.wCell; fl.hCell = g.hCell;
         fl.cand_off = g.cand_off; fl.cand_cap = g.cand_cap; fl.cand_frame = G.cand_frame;
         fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
-        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_THREADS, 0, st>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
+        const size_t smem = fast_smem_layout(fl);
+        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, st>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
         ex->launches++;
     }
     prof_mark(ex, 3);

@@ -10,7 +10,7 @@ constexpr int EDGE = ORB_EDGE_THRESHOLD;   // 19
 constexpr int XOFF = 32;                   // interior column 0 sits at byte 32 of a plane row
 constexpr int MAX_INI = 64;                // max initial quadtree nodes (image aspect ratio)
 constexpr int FAST_TILE_MAX = 72;          // cell (<60) + 6 halo, rounded up
-constexpr int FAST_THREADS = 256;
+constexpr int FAST_THREADS = 64;           // measured 32..256 on B200: 32-128 within 5%, 256 is 1.8x slower (per-warp fixed costs)
 constexpr int OCT_THREADS = 512;
 constexpr int DESC_WARPS = 8;
 
