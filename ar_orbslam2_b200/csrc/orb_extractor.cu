@@ -163,7 +163,7 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
 // <=> V > t, response V-1, 3x3 non-max suppression inside the cell's computed region only.
 //
 // Stages inside the CTA (all in dynamic shared memory sized for the level's cell):
-//   1. the cell's ROI is staged as aligned 32-bit words (cp.async);
+//   1. the cell's ROI is staged as aligned 16-byte chunks (cp.async);
 //   2. every pixel takes the 4-compass test at the current threshold: a 9-arc always holds two ADJACENT compass
 //      points, so a corner needs one of {up, down} and one of {left, right} brighter (type H) or darker (type L)
 //      than the centre by more than t.  A thread tests one aligned word = 4 pixels with 16x2 SIMD min/max
@@ -175,8 +175,8 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
 // that fails the compass test at t has V <= t, so it can neither be a corner at t nor suppress one.
 // ------------------------------------------------------------------------------------------
 constexpr int FAST_T = FAST_THREADS;
-constexpr int FT_PW = 19;                 // tile row pitch in words (76 bytes >= 72 + 3 bytes of alignment slack); compile-time
-constexpr int FT_PB = FT_PW * 4;          // so that the 16 circle offsets are immediates
+constexpr int FT_PW = 20;                 // tile row pitch in words: 80 bytes >= 65 (cell < 60, + 6) + 15 bytes of alignment
+constexpr int FT_PB = FT_PW * 4;          // slack; compile-time so that the 16 circle offsets are immediates
 constexpr int FV_PB = 72;                 // score-map row pitch in bytes (computed width <= 66, + 2 apron)
 
 struct FastLevel {   // what k_fast_cells needs of one level, passed by value (constant bank)
@@ -266,16 +266,16 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     constexpr int TPW = FT_PW, TPB = FT_PB, VPB = FV_PB;
 
     // ---- 1. stage the ROI; byte (y, x) of the ROI sits at tile byte y * TPB + x + sft
-    const int sft = (iniX + XOFF) & 3;
+    const int sft = (iniX + XOFF) & 15;   // plane rows are 128-byte aligned and interior column 0 sits at byte XOFF
     {
         const uint8_t *img = pyr + (size_t)b * g.pyr_frame + g.interior_off + (ptrdiff_t)iniY * g.pitch + (iniX - sft);
-        const int nW = (tw + sft + 3) >> 2;
-        const FastDiv dW(nW);
+        const int nQ = (tw + sft + 15) >> 4;   // <= 5 chunks per row
+        const FastDiv dQ(nQ);
         const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tileW);
-        for (int i = tid; i < th * nW; i += FAST_T) {
-            const int y = dW.div(i), w = i - y * nW;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(tile_s + (uint32_t)(y * TPW + w) * 4u),
-                         "l"(img + (size_t)y * g.pitch + w * 4));
+        for (int i = tid; i < th * nQ; i += FAST_T) {
+            const int y = dQ.div(i), q = i - y * nQ;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(y * TPB + q * 16)),
+                         "l"(img + (size_t)y * g.pitch + q * 16));
         }
         asm volatile("cp.async.commit_group;");
         uint4 *vq = reinterpret_cast<uint4 *>(vmap);
@@ -1047,7 +1047,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
         if (wf < 30.f || hf < 30.f) return ORB_ERR_TOO_SMALL;
         const int nCols = (int)(wf / 30.f), nRows = (int)(hf / 30.f);                 // ref :753-754
         g.wCell = (int)std::ceil(wf / nCols); g.hCell = (int)std::ceil(hf / nRows);   // ref :755-756
-        if (g.wCell + 6 > FAST_TILE_MAX || g.hCell + 6 > FAST_TILE_MAX) return ORB_ERR_INVALID;
+        if (g.wCell + 6 + 15 > FT_PB || g.hCell + 6 > FAST_TILE_MAX) return ORB_ERR_INVALID;
         g.ncx = 0; g.ncy = 0;
         for (int j = 0; j < nCols; j++) if (!(minB + j * g.wCell >= g.maxBX - 6)) g.ncx = j + 1;   // ref :770
         for (int i = 0; i < nRows; i++) if (!(minB + i * g.hCell >= g.maxBY - 3)) g.ncy = i + 1;   // ref :762
