@@ -49,7 +49,11 @@ def ptr(a: np.ndarray, ctype=C.c_void_p):
 class OrbFrameDesc(C.Structure):
     _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p), ("u_right", C.c_void_p),
                 ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
-                ("nlevels", C.c_int32), ("scale_factors", C.c_void_p)]
+                ("nlevels", C.c_int32), ("scale_factors", C.c_void_p), ("keyframe_view", C.c_int32)]
+
+
+class OrbReprojGate(C.Structure):
+    _fields_ = [("ur", C.c_void_p), ("inv_level_sigma2", C.c_void_p), ("chi2_mono", C.c_double), ("chi2_stereo", C.c_double)]
 
 
 class OrbWindowQueries(C.Structure):

@@ -32,7 +32,7 @@ struct FrameDev {
     const uint8_t *desc;
     const int *cell_off;   // [GRID_COLS*GRID_ROWS + 1], cell = ix*GRID_ROWS + iy
     const int *cell_idx;   // keypoint indices, ascending inside a cell (= insertion order)
-    float minX, minY, invW, invH;
+    float minX, minY, invW, invH;   // minX/minY as GetFeaturesInArea sees them (truncated to int for a KeyFrame view)
 };
 
 struct WinQ {   // device view of orb_window_queries
@@ -45,6 +45,9 @@ struct WinQ {   // device view of orb_window_queries
     const uint8_t *desc;
     const float *angle;
     const uint8_t *claims;
+    const float *gate_ur;          // reprojection-error gate of Fuse (ref ORBmatcher.cc:917-945); gate_inv_sigma2 == NULL = off
+    const float *gate_inv_sigma2;
+    double gate_mono, gate_stereo;
 };
 
 __device__ __forceinline__ int warp_excl_scan(int v, int lane, int *total) {
@@ -81,6 +84,35 @@ __device__ __forceinline__ int hamming_rows(const uint8_t *a, const uint8_t *b) 
 // Frame::GetFeaturesInArea (ref Frame.cc:332-385) for one query by one warp.  Lanes own grid cells in traversal
 // order (ix outer, iy inner); a warp prefix sum per 32-cell round keeps the output in the reference's order.
 // FILL=false: returns the count.  FILL=true: writes (index, distance) pairs at out_idx/out_dist.
+struct WinTest {   // one query's admission test for a feature of the window's cells
+    float x, y, r, sref, stol, gur;
+    int minL, maxL;
+    bool check, strict, stereo, gate;
+    const float *inv_sigma2;
+    double chi_mono, chi_stereo;
+    __device__ __forceinline__ bool ok(const FrameDev &f, int idx) const {
+        const int oct = f.octave[idx];
+        if (strict) { if (oct < minL || oct > maxL) return false; }
+        else if (check) { if (oct < minL || (maxL >= 0 && oct > maxL)) return false; }
+        const float kx = f.x[idx], ky = f.y[idx];
+        if (!(fabsf(__fsub_rn(kx, x)) < r && fabsf(__fsub_rn(ky, y)) < r)) return false;
+        if (stereo) {
+            const float ur = f.uRight[idx];
+            if (ur > 0 && fabsf(__fsub_rn(sref, ur)) > stol) return false;
+        }
+        if (gate) {   // ref :917-945: squared reprojection error, scaled by the level's inverse sigma^2, against chi^2 (double compare)
+            const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky), kr = f.uRight[idx];
+            float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+            if (kr >= 0) {
+                const float er = __fsub_rn(gur, kr);
+                e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                if ((double)__fmul_rn(e2, inv_sigma2[oct]) > chi_stereo) return false;
+            } else if ((double)__fmul_rn(e2, inv_sigma2[oct]) > chi_mono) return false;
+        }
+        return true;
+    }
+};
+
 template <bool FILL>
 __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int lane, int *out_idx, int *out_dist) {
     const float x = Q.x[q], y = Q.y[q], r = Q.radius[q];
@@ -94,10 +126,15 @@ __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int la
     const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
     if (cy1 < 0) return 0;
     if (cx1 < cx0 || cy1 < cy0) return 0;
-    const bool check = (minL > 0) || (maxL >= 0);
-    const bool strict = Q.strict_levels != 0;
-    const bool stereo = Q.stereo_ref != nullptr;
-    const float sref = stereo ? Q.stereo_ref[q] : 0.f, stol = stereo ? Q.stereo_tol[q] : 0.f;
+    WinTest T;
+    T.x = x; T.y = y; T.r = r; T.minL = minL; T.maxL = maxL;
+    T.check = (minL > 0) || (maxL >= 0);
+    T.strict = Q.strict_levels != 0;
+    T.stereo = Q.stereo_ref != nullptr;
+    T.sref = T.stereo ? Q.stereo_ref[q] : 0.f; T.stol = T.stereo ? Q.stereo_tol[q] : 0.f;
+    T.gate = Q.gate_inv_sigma2 != nullptr;
+    T.gur = T.gate && Q.gate_ur ? Q.gate_ur[q] : 0.f;
+    T.inv_sigma2 = Q.gate_inv_sigma2; T.chi_mono = Q.gate_mono; T.chi_stereo = Q.gate_stereo;
     const int ny = cy1 - cy0 + 1, ncells = (cx1 - cx0 + 1) * ny;
     const uint8_t *qd = Q.desc + (size_t)q * 32;
     int base = 0;
@@ -111,17 +148,7 @@ __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int la
         int cnt = 0;
         unsigned pass = 0;   // cells hold few keypoints; longer cells fall back to re-testing
         for (int e = beg; e < end; e++) {
-            const int idx = f.cell_idx[e];
-            const int oct = f.octave[idx];
-            bool ok = true;
-            if (strict) ok = !(oct < minL || oct > maxL);
-            else if (check) ok = !(oct < minL || (maxL >= 0 && oct > maxL));
-            if (ok) ok = fabsf(__fsub_rn(f.x[idx], x)) < r && fabsf(__fsub_rn(f.y[idx], y)) < r;
-            if (ok && stereo) {
-                const float ur = f.uRight[idx];
-                if (ur > 0 && fabsf(__fsub_rn(sref, ur)) > stol) ok = false;
-            }
-            if (ok) { if (e - beg < 32) pass |= 1u << (e - beg); cnt++; }
+            if (T.ok(f, f.cell_idx[e])) { if (e - beg < 32) pass |= 1u << (e - beg); cnt++; }
         }
         int total;
         const int off = warp_excl_scan(cnt, lane, &total);
@@ -131,17 +158,7 @@ __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int la
                 bool ok;
                 const int idx = f.cell_idx[e];
                 if (e - beg < 32) ok = (pass >> (e - beg)) & 1;
-                else {
-                    const int oct = f.octave[idx];
-                    ok = true;
-                    if (strict) ok = !(oct < minL || oct > maxL);
-                    else if (check) ok = !(oct < minL || (maxL >= 0 && oct > maxL));
-                    if (ok) ok = fabsf(__fsub_rn(f.x[idx], x)) < r && fabsf(__fsub_rn(f.y[idx], y)) < r;
-                    if (ok && stereo) {
-                        const float ur = f.uRight[idx];
-                        if (ur > 0 && fabsf(__fsub_rn(sref, ur)) > stol) ok = false;
-                    }
-                }
+                else ok = T.ok(f, idx);
                 if (ok) {
                     out_idx[w] = idx;
                     out_dist[w] = hamming_rows(qd, f.desc + (size_t)idx * 32);
@@ -406,6 +423,102 @@ k_resolve_bow(FrameDev kf, FrameDev f, int nentries, const int *kf_idx, const in
     if (lane == 0) *nmatches = nm;
 }
 
+// Fuse / SearchBySim3 candidate loop (ref ORBmatcher.cc:895-951, 1052-1072, 1191-1213, 1271-1293): independent queries,
+// closest descriptor of the window, the first one in traversal order on ties.  One warp per query over its CSR list.
+__global__ void k_window_best(int nq, const int *off, const int *cand_idx, const int *cand_dist, int *best_idx, int *best_dist) {
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const int o = off[q], n = off[q + 1] - o;
+    unsigned long long key = ~0ull;
+    for (int j = lane; j < n; j += 32) key = min(key, ((unsigned long long)(uint32_t)cand_dist[o + j] << 32) | (uint32_t)j);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
+    if (lane == 0) {
+        best_idx[q] = key == ~0ull ? -1 : cand_idx[o + (int)(uint32_t)key];
+        best_dist[q] = key == ~0ull ? 0x7fffffff : (int)(key >> 32);
+    }
+}
+
+// SearchForTriangulation (ref ORBmatcher.cc:660-826): one warp per KF1 feature of a shared vocabulary node, lanes over
+// the node's KF2 features.  The running `dist>bestDist` test only ever rejects candidates that lose anyway, so the result
+// is the admissible candidate of least distance, the LAST one in node order on ties (`dist>bestDist` lets equals through).
+struct TriArgs {
+    float F[9];
+    float ex, ey;
+    const float *sigma2, *scale2;   // pKF2->mvLevelSigma2, pKF2->mvScaleFactors
+    int only_stereo;
+};
+__global__ void k_triangulate(FrameDev k1, FrameDev k2, int nent, const int *idx1, const int *ent_o2, const int *ent_n2,
+                              const int *idx2, const uint8_t *usable1, const uint8_t *usable2, TriArgs A, int *m12) {
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (e >= nent) return;
+    const int i1 = idx1[e];
+    if (!usable1[i1]) return;                                            // ref :704-708
+    const bool st1 = k1.uRight[i1] >= 0;
+    if (A.only_stereo && !st1) return;                                   // ref :712-714
+    const float x1 = k1.x[i1], y1 = k1.y[i1];
+    // epipolar line l = x1' F12 (ref :143-145), plain fp32 multiplies and adds in source order
+    const float a = __fadd_rn(__fadd_rn(__fmul_rn(x1, A.F[0]), __fmul_rn(y1, A.F[3])), A.F[6]);
+    const float b = __fadd_rn(__fadd_rn(__fmul_rn(x1, A.F[1]), __fmul_rn(y1, A.F[4])), A.F[7]);
+    const float c = __fadd_rn(__fadd_rn(__fmul_rn(x1, A.F[2]), __fmul_rn(y1, A.F[5])), A.F[8]);
+    const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+    const uint8_t *d1 = k1.desc + (size_t)i1 * 32;
+    const int o2 = ent_o2[e], n2 = ent_n2[e];
+    uint32_t key = SENT;
+    for (int j = lane; j < n2; j += 32) {
+        const int i2 = idx2[o2 + j];
+        if (!usable2[i2]) continue;                                      // ref :726-730
+        const bool st2 = k2.uRight[i2] >= 0;
+        if (A.only_stereo && !st2) continue;                             // ref :734-736
+        const int dist = hamming_rows(d1, k2.desc + (size_t)i2 * 32);
+        if (dist > TH_LOW_M) continue;                                   // ref :742
+        const float x2 = k2.x[i2], y2 = k2.y[i2];
+        const int oct = k2.octave[i2];
+        if (!st1 && !st2) {                                              // ref :747-753: too close to the epipole
+            const float dx = __fsub_rn(A.ex, x2), dy = __fsub_rn(A.ey, y2);
+            if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.0f, A.scale2[oct])) continue;
+        }
+        if (den == 0) continue;                                          // ref :151-152
+        const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, x2), __fmul_rn(b, y2)), c);
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if (!((double)dsqr < __dmul_rn(3.84, (double)A.sigma2[oct]))) continue;   // ref :156
+        key = min(key, ((uint32_t)dist << 16) | (uint32_t)(0xffff - j));
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
+    if (lane == 0 && key != SENT) m12[i1] = idx2[o2 + (0xffff - (int)(key & 0xffff))];
+}
+
+// rotation-consistency filter of SearchForTriangulation (ref :764-775, 796-814) and the final count
+__global__ void __launch_bounds__(1024) k_tri_filter(FrameDev k1, FrameDev k2, int *m12, int check_ori, int *nmatches) {
+    __shared__ int hist[HISTO];
+    __shared__ int ind[3];
+    __shared__ int s_n;
+    const int tid = threadIdx.x;
+    if (tid < HISTO) hist[tid] = 0;
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    if (check_ori) {
+        for (int i = tid; i < k1.n; i += 1024)
+            if (m12[i] >= 0) atomicAdd(&hist[rot_bin(k1.angle[i], k2.angle[m12[i]])], 1);
+        __syncthreads();
+        if (tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
+        __syncthreads();
+    }
+    int cnt = 0;
+    for (int i = tid; i < k1.n; i += 1024) {
+        if (m12[i] < 0) continue;
+        if (check_ori) {
+            const int bin = rot_bin(k1.angle[i], k2.angle[m12[i]]);
+            if (bin != ind[0] && bin != ind[1] && bin != ind[2]) { m12[i] = -1; continue; }
+        }
+        cnt++;
+    }
+    if (cnt) atomicAdd(&s_n, cnt);
+    __syncthreads();
+    if (tid == 0) *nmatches = s_n;
+}
+
 __global__ void __launch_bounds__(1024) k_rot_hist_filter(const float *a, const float *b, int n, uint8_t *keep) {
     __shared__ int hist[HISTO];
     __shared__ int ind[3];
@@ -535,7 +648,8 @@ int orb_frame_create(const orb_frame_desc *d, orb_frame **out) {
         if (rc == ORB_OK) rc = upload(didx, idx.data(), idx.size(), st);
         if (rc == ORB_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = ORB_ERR_CUDA;
         if (rc != ORB_OK) { cudaFree(f->d_static); cudaStreamDestroy(f->stream); delete f; return rc; }
-        f->dev = FrameDev{n, dx, dy, da, du, doct, dd, doff, didx, f->minX, f->minY, invW, invH};
+        const bool kfv = d->keyframe_view != 0;   // the grid above was filled with the Frame's float bounds either way
+        f->dev = FrameDev{n, dx, dy, da, du, doct, dd, doff, didx, kfv ? (float)(int)f->minX : f->minX, kfv ? (float)(int)f->minY : f->minY, invW, invH};
     }
     *out = f;
     return ORB_OK;
@@ -568,6 +682,9 @@ struct HostQueries {
     const uint8_t *desc = nullptr;
     const float *angle = nullptr;
     const uint8_t *claims = nullptr;
+    const float *gate_ur = nullptr, *gate_inv_sigma2 = nullptr;   // optional reprojection gate (n and nlevels entries)
+    int gate_levels = 0;
+    double gate_mono = 0, gate_stereo = 0;
 };
 
 // Phase 1 of every windowed search: upload queries, count candidates, scan, fill (idx, dist) lists.
@@ -590,6 +707,9 @@ int build_window_lists(orb_frame *f, const HostQueries &H, size_t extra_bytes, W
         Q.desc = ar.take<uint8_t>((size_t)n * 32);
         Q.angle = H.angle ? ar.take<float>(n) : nullptr;
         Q.claims = H.claims ? ar.take<uint8_t>(n) : nullptr;
+        Q.gate_ur = H.gate_inv_sigma2 ? ar.take<float>(n) : nullptr;
+        Q.gate_inv_sigma2 = H.gate_inv_sigma2 ? ar.take<float>(H.gate_levels) : nullptr;
+        Q.gate_mono = H.gate_mono; Q.gate_stereo = H.gate_stereo;
         WL->off = ar.take<int>(n + 1);
         return Q;
     };
@@ -608,6 +728,10 @@ int build_window_lists(orb_frame *f, const HostQueries &H, size_t extra_bytes, W
     ORB_TRY(upload((uint8_t *)Q.desc, H.desc, (size_t)n * 32, st));
     if (H.angle) ORB_TRY(upload((float *)Q.angle, H.angle, n, st));
     if (H.claims) ORB_TRY(upload((uint8_t *)Q.claims, H.claims, n, st));
+    if (H.gate_inv_sigma2) {
+        ORB_TRY(upload((float *)Q.gate_ur, H.gate_ur, n, st));
+        ORB_TRY(upload((float *)Q.gate_inv_sigma2, H.gate_inv_sigma2, H.gate_levels, st));
+    }
     const int blocks = (n * 32 + 255) / 256;
     if (n) k_window_count<<<blocks, 256, 0, st>>>(f->dev, Q, counts);
     k_scan_counts<<<1, 1024, 0, st>>>(counts, n, WL->off);
@@ -849,6 +973,94 @@ int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *k
     int nm = 0;
     ORB_CUDA_TRY(cudaMemcpyAsync(matches, d_matches, (size_t)f->n * 4, cudaMemcpyDeviceToHost, st));
     if (nent) ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    if (nmatches) *nmatches = nm;
+    return ORB_OK;
+}
+
+int orb_search_window_best(orb_frame *f, const orb_window_queries *q, const orb_reproj_gate *gate, int32_t *best_idx,
+                           int32_t *best_dist) {
+    ORB_REQUIRE(f && q && best_idx && best_dist, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(q->n >= 0 && (q->n == 0 || (q->x && q->y && q->radius && q->min_level && q->max_level && q->descriptors)),
+                ORB_ERR_INVALID, "incomplete query set");
+    ORB_REQUIRE((q->stereo_ref == nullptr) == (q->stereo_tol == nullptr), ORB_ERR_INVALID, "stereo_ref and stereo_tol go together");
+    ORB_REQUIRE(!gate || (gate->ur && gate->inv_level_sigma2), ORB_ERR_INVALID, "incomplete reprojection gate");
+    ORB_CUDA_TRY(cudaSetDevice(f->device));
+    const int n = q->n;
+    for (int i = 0; i < n; i++) { best_idx[i] = -1; best_dist[i] = 0x7fffffff; }
+    if (n == 0 || f->n == 0) return ORB_OK;
+    HostQueries H;
+    H.n = n; H.valid = q->valid; H.x = q->x; H.y = q->y; H.radius = q->radius; H.min_level = q->min_level; H.max_level = q->max_level;
+    H.strict_levels = q->strict_levels; H.stereo_ref = q->stereo_ref; H.stereo_tol = q->stereo_tol; H.desc = q->descriptors;
+    if (gate) {
+        H.gate_ur = gate->ur; H.gate_inv_sigma2 = gate->inv_level_sigma2; H.gate_levels = f->nlevels;
+        H.gate_mono = gate->chi2_mono; H.gate_stereo = gate->chi2_stereo;
+    }
+    WinQ Q; WindowLists WL; uint8_t *extra;
+    ORB_TRY(build_window_lists(f, H, (size_t)n * 8 + 512, &Q, &WL, &extra));
+    Arena ar; ar.base = extra;
+    int *d_idx = ar.take<int>(n), *d_dist = ar.take<int>(n);
+    cudaStream_t st = f->stream;
+    k_window_best<<<(n * 32 + 255) / 256, 256, 0, st>>>(n, WL.off, WL.idx, WL.dist, d_idx, d_dist);
+    f->launches++;
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_idx, d_idx, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, d_dist, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
+}
+
+int orb_search_for_triangulation(orb_frame *kf1, orb_frame *kf2, int ngroups, const int32_t *off1, const int32_t *idx1,
+                                 const int32_t *off2, const int32_t *idx2, const uint8_t *usable1, const uint8_t *usable2,
+                                 const float *F12, float ex, float ey, const float *level_sigma2, int only_stereo,
+                                 int check_orientation, int32_t *matches12, int *nmatches) {
+    ORB_REQUIRE(kf1 && kf2 && matches12 && F12 && level_sigma2 && ngroups >= 0 &&
+                    (ngroups == 0 || (off1 && idx1 && off2 && idx2 && usable1 && usable2)),
+                ORB_ERR_INVALID, "bad argument");
+    ORB_REQUIRE(kf1->device == kf2->device, ORB_ERR_INVALID, "frames on different devices");
+    ORB_CUDA_TRY(cudaSetDevice(kf1->device));
+    if (nmatches) *nmatches = 0;
+    for (int i = 0; i < kf1->n; i++) matches12[i] = -1;
+    if (ngroups == 0 || kf1->n == 0 || kf2->n == 0) return ORB_OK;
+    const int nent = off1[ngroups], nent2 = off2[ngroups];
+    if (nent == 0 || nent2 == 0) return ORB_OK;
+    std::vector<int> ent_o2(nent), ent_n2(nent);
+    for (int g = 0; g < ngroups; g++) {
+        ORB_REQUIRE(off2[g + 1] - off2[g] < 65536, ORB_ERR_INVALID, "vocabulary node with more than 65535 features");
+        for (int a = off1[g]; a < off1[g + 1]; a++) {
+            ORB_REQUIRE(idx1[a] >= 0 && idx1[a] < kf1->n, ORB_ERR_INVALID, "KF1 feature index out of range");
+            ent_o2[a] = off2[g]; ent_n2[a] = off2[g + 1] - off2[g];
+        }
+    }
+    for (int b = 0; b < nent2; b++) ORB_REQUIRE(idx2[b] >= 0 && idx2[b] < kf2->n, ORB_ERR_INVALID, "KF2 feature index out of range");
+    orb_frame *f = kf1;   // scratch and stream of the first key frame
+    Arena ar;
+    int *d_idx1 = nullptr, *d_o2 = nullptr, *d_n2 = nullptr, *d_idx2 = nullptr, *d_m12 = nullptr, *d_nm = nullptr;
+    float *d_sigma = nullptr, *d_scale = nullptr;
+    uint8_t *d_u1 = nullptr, *d_u2 = nullptr;
+    for (int phase = 0; phase < 2; phase++) {
+        ar.used = 0;
+        d_idx1 = ar.take<int>(nent); d_o2 = ar.take<int>(nent); d_n2 = ar.take<int>(nent); d_idx2 = ar.take<int>(nent2);
+        d_m12 = ar.take<int>(kf1->n); d_nm = ar.take<int>(1);
+        d_sigma = ar.take<float>(kf2->nlevels); d_scale = ar.take<float>(kf2->nlevels);
+        d_u1 = ar.take<uint8_t>(kf1->n); d_u2 = ar.take<uint8_t>(kf2->n);
+        if (phase == 0) { ORB_TRY(ensure_scratch(f, ar.used + 1024)); ar.base = (uint8_t *)f->d_scratch; }
+    }
+    cudaStream_t st = f->stream;
+    ORB_TRY(upload(d_idx1, idx1, nent, st)); ORB_TRY(upload(d_o2, ent_o2.data(), nent, st)); ORB_TRY(upload(d_n2, ent_n2.data(), nent, st));
+    ORB_TRY(upload(d_idx2, idx2, nent2, st)); ORB_TRY(upload(d_u1, usable1, kf1->n, st)); ORB_TRY(upload(d_u2, usable2, kf2->n, st));
+    ORB_TRY(upload(d_sigma, level_sigma2, kf2->nlevels, st)); ORB_TRY(upload(d_scale, kf2->scale.data(), kf2->nlevels, st));
+    ORB_CUDA_TRY(cudaMemsetAsync(d_m12, 0xff, (size_t)kf1->n * 4, st));
+    TriArgs A;
+    for (int i = 0; i < 9; i++) A.F[i] = F12[i];
+    A.ex = ex; A.ey = ey; A.sigma2 = d_sigma; A.scale2 = d_scale; A.only_stereo = only_stereo;
+    k_triangulate<<<(nent * 32 + 255) / 256, 256, 0, st>>>(kf1->dev, kf2->dev, nent, d_idx1, d_o2, d_n2, d_idx2, d_u1, d_u2, A, d_m12);
+    k_tri_filter<<<1, 1024, 0, st>>>(kf1->dev, kf2->dev, d_m12, check_orientation, d_nm);
+    f->launches += 2;
+    ORB_CUDA_TRY(cudaGetLastError());
+    int nm = 0;
+    ORB_CUDA_TRY(cudaMemcpyAsync(matches12, d_m12, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
     if (nmatches) *nmatches = nm;
     return ORB_OK;

@@ -1,7 +1,9 @@
 // See ORBmatcher_gpu.h.  Line references are to ORB_SLAM2/src/ORBmatcher.cc of the reference.
 #include "ORBmatcher_gpu.h"
 
+#include <cmath>
 #include <cstring>
+#include <set>
 #include <stdexcept>
 #include <string>
 
@@ -22,7 +24,8 @@ struct GpuFrame {
     std::vector<orb_keypoint> keys;
     std::vector<uint8_t> desc;
     template <class KeyVec>
-    GpuFrame(const KeyVec &keysUn, const cv::Mat &descriptors, const std::vector<float> &uRight, const std::vector<float> &scaleFactors) {
+    GpuFrame(const KeyVec &keysUn, const cv::Mat &descriptors, const std::vector<float> &uRight, const std::vector<float> &scaleFactors,
+             bool keyframeView = false) {
         const int n = (int)keysUn.size();
         keys.resize(n);
         desc.resize((size_t)n * 32 + 32);
@@ -37,6 +40,7 @@ struct GpuFrame {
         d.u_right = ((int)uRight.size() == n && n > 0) ? uRight.data() : nullptr;
         d.min_x = Frame::mnMinX; d.max_x = Frame::mnMaxX; d.min_y = Frame::mnMinY; d.max_y = Frame::mnMaxY;
         d.nlevels = (int)scaleFactors.size(); d.scale_factors = scaleFactors.data();
+        d.keyframe_view = keyframeView ? 1 : 0;
         Check(orb_frame_create(&d, &h), "orb_frame_create");
     }
     ~GpuFrame() { orb_frame_destroy(h); }
@@ -170,6 +174,286 @@ int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatc
     for (int i = 0; i < F.N; i++)
         if (matches[i] >= 0) vpMapPointMatches[i] = vpMapPointsKF[matches[i]];   // :232
     return nmatches;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// LocalMapping / LoopClosing matchers.  The candidate loops run on the GPU (orb_search_window_best,
+// orb_search_for_triangulation); the projection algebra before them and the map bookkeeping after them are the
+// reference's statements, kept in the reference's order.
+// ---------------------------------------------------------------------------------------------------------------
+static const int TH_HIGH = 100, TH_LOW = 50;   // :37-38
+
+// Window queries gathered for the points that pass the geometric tests.
+struct WindowSet {
+    std::vector<uint8_t> valid, desc;
+    std::vector<float> u, v, ur, radius;
+    std::vector<int32_t> minL, maxL, bestIdx, bestDist;
+    explicit WindowSet(int n) : valid(n, 0), desc((size_t)n * 32 + 32, 0), u(n, 0.f), v(n, 0.f), ur(n, 0.f), radius(n, 0.f), minL(n, 0),
+                                maxL(n, 0), bestIdx(n, -1), bestDist(n, 0x7fffffff) {}
+    void Set(int i, float uu, float vv, float uur, int level, float r, MapPoint *pMP) {
+        valid[i] = 1; u[i] = uu; v[i] = vv; ur[i] = uur; radius[i] = r; minL[i] = level - 1; maxL[i] = level;
+        cv::Mat d = pMP->GetDescriptor();
+        std::memcpy(&desc[(size_t)i * 32], d.ptr(0), 32);
+    }
+    void Search(KeyFrame *pKF, bool reprojGate) {
+        const int n = (int)valid.size();
+        if (n == 0 || pKF->N == 0) return;
+        GpuFrame g(pKF->mvKeysUn, pKF->mDescriptors, pKF->mvuRight, pKF->mvScaleFactors, true);
+        orb_window_queries Q;
+        std::memset(&Q, 0, sizeof(Q));
+        Q.n = n; Q.valid = valid.data(); Q.x = u.data(); Q.y = v.data(); Q.radius = radius.data(); Q.min_level = minL.data();
+        Q.max_level = maxL.data(); Q.strict_levels = 1; Q.descriptors = desc.data();
+        orb_reproj_gate G = {ur.data(), pKF->mvInvLevelSigma2.data(), 5.99, 7.8};   // :930, :943
+        Check(orb_search_window_best(g.h, &Q, reprojGate ? &G : NULL, bestIdx.data(), bestDist.data()), "orb_search_window_best");
+    }
+};
+
+// PredictScale is not clamped in this fork (MapPoint.cc:357-366); the reference then indexes mvScaleFactors out of range.
+static bool LevelOk(int level, const KeyFrame *pKF) { return level >= 0 && level < (int)pKF->mvScaleFactors.size(); }
+
+int SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> > &vMatchedPairs,
+                           bool bOnlyStereo, bool mbCheckOrientation) {
+    const DBoW2::FeatureVector &vFeatVec1 = pKF1->mFeatVec;
+    const DBoW2::FeatureVector &vFeatVec2 = pKF2->mFeatVec;
+    // epipole in the second image, :667-673
+    cv::Mat Cw = pKF1->GetCameraCenter();
+    cv::Mat R2w = pKF2->GetRotation();
+    cv::Mat t2w = pKF2->GetTranslation();
+    cv::Mat C2 = R2w * Cw + t2w;
+    const float invz = 1.0f / C2.at<float>(2);
+    const float ex = pKF2->fx * C2.at<float>(0) * invz + pKF2->cx;
+    const float ey = pKF2->fy * C2.at<float>(1) * invz + pKF2->cy;
+
+    vMatchedPairs.clear();
+    if (pKF1->N == 0 || pKF2->N == 0) return 0;
+    std::vector<int32_t> off1(1, 0), off2(1, 0), idx1, idx2;   // the merge-join of :695-786 as CSR
+    DBoW2::FeatureVector::const_iterator f1it = vFeatVec1.begin(), f2it = vFeatVec2.begin();
+    const DBoW2::FeatureVector::const_iterator f1end = vFeatVec1.end(), f2end = vFeatVec2.end();
+    while (f1it != f1end && f2it != f2end) {
+        if (f1it->first == f2it->first) {
+            idx1.insert(idx1.end(), f1it->second.begin(), f1it->second.end());
+            idx2.insert(idx2.end(), f2it->second.begin(), f2it->second.end());
+            off1.push_back((int32_t)idx1.size()); off2.push_back((int32_t)idx2.size());
+            f1it++; f2it++;
+        } else if (f1it->first < f2it->first) f1it = vFeatVec1.lower_bound(f2it->first);
+        else f2it = vFeatVec2.lower_bound(f1it->first);
+    }
+    std::vector<uint8_t> usable1(pKF1->N), usable2(pKF2->N);
+    for (int i = 0; i < pKF1->N; i++) usable1[i] = pKF1->GetMapPoint(i) == NULL;   // :704-708
+    for (int i = 0; i < pKF2->N; i++) usable2[i] = pKF2->GetMapPoint(i) == NULL;   // :726-730
+    float F[9];
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) F[r * 3 + c] = F12.at<float>(r, c);
+    GpuFrame g1(pKF1->mvKeysUn, pKF1->mDescriptors, pKF1->mvuRight, pKF1->mvScaleFactors, true);
+    GpuFrame g2(pKF2->mvKeysUn, pKF2->mDescriptors, pKF2->mvuRight, pKF2->mvScaleFactors, true);
+    std::vector<int32_t> m12(pKF1->N, -1);
+    int nmatches = 0;
+    Check(orb_search_for_triangulation(g1.h, g2.h, (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), usable1.data(),
+                                       usable2.data(), F, ex, ey, pKF2->mvLevelSigma2.data(), bOnlyStereo, mbCheckOrientation, m12.data(),
+                                       &nmatches), "orb_search_for_triangulation");
+    vMatchedPairs.reserve(nmatches);                                   // :817-825
+    for (size_t i = 0, iend = m12.size(); i < iend; i++) {
+        if (m12[i] < 0) continue;
+        vMatchedPairs.push_back(std::make_pair(i, (size_t)m12[i]));
+    }
+    return nmatches;
+}
+
+int Fuse(KeyFrame *pKF, const std::vector<MapPoint *> &vpMapPoints, float th) {
+    cv::Mat Rcw = pKF->GetRotation();
+    cv::Mat tcw = pKF->GetTranslation();
+    const float &fx = pKF->fx;
+    const float &fy = pKF->fy;
+    const float &cx = pKF->cx;
+    const float &cy = pKF->cy;
+    const float &bf = pKF->mbf;
+    cv::Mat Ow = pKF->GetCameraCenter();
+    const int nMPs = (int)vpMapPoints.size();
+    WindowSet W(nMPs);
+    for (int i = 0; i < nMPs; i++) {                                   // the geometry of :846-893 (none of it changes during the loop)
+        MapPoint *pMP = vpMapPoints[i];
+        if (!pMP) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0f) continue;
+        const float invz = 1 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz;
+        const float y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float ur = u - bf * invz;
+        const float maxDistance = pMP->GetMaxDistanceInvariance();
+        const float minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist3D = cv::norm(PO);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist3D) continue;
+        int nPredictedLevel = pMP->PredictScale(dist3D, pKF->mfLogScaleFactor);
+        if (!LevelOk(nPredictedLevel, pKF)) continue;
+        W.Set(i, u, v, ur, nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
+    }
+    W.Search(pKF, true);
+    int nFused = 0;
+    for (int i = 0; i < nMPs; i++) {                                   // the reference's loop order; state-dependent tests evaluated here
+        MapPoint *pMP = vpMapPoints[i];
+        if (!pMP) continue;
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;          // :851-852
+        if (!W.valid[i]) continue;
+        const int bestDist = W.bestDist[i], bestIdx = W.bestIdx[i];
+        if (bestDist <= TH_LOW) {                                      // :954-973
+            MapPoint *pMPinKF = pKF->GetMapPoint(bestIdx);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) {
+                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                    else pMPinKF->Replace(pMP);
+                }
+            } else {
+                pMP->AddObservation(pKF, bestIdx);
+                pKF->AddMapPoint(pMP, bestIdx);
+            }
+            nFused++;
+        }
+    }
+    return nFused;
+}
+
+int Fuse(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *> &vpPoints, float th, std::vector<MapPoint *> &vpReplacePoint) {
+    const float &fx = pKF->fx;
+    const float &fy = pKF->fy;
+    const float &cx = pKF->cx;
+    const float &cy = pKF->cy;
+    // decompose Scw, :989-994
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    const std::set<MapPoint *> spAlreadyFound = pKF->GetMapPoints();   // :997
+    const int nPoints = (int)vpPoints.size();
+    WindowSet W(nPoints);
+    for (int iMP = 0; iMP < nPoints; iMP++) {                          // :1004-1048
+        MapPoint *pMP = vpPoints[iMP];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;       // neither changes inside this function
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0f) continue;
+        const float invz = 1.0 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz;
+        const float y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance();
+        const float minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist3D = cv::norm(PO);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist3D) continue;
+        const int nPredictedLevel = pMP->PredictScale(dist3D, pKF->mfLogScaleFactor);
+        if (!LevelOk(nPredictedLevel, pKF)) continue;
+        W.Set(iMP, u, v, 0.f, nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
+    }
+    W.Search(pKF, false);
+    int nFused = 0;
+    for (int iMP = 0; iMP < nPoints; iMP++) {                          // :1075-1090, in order: AddMapPoint changes GetMapPoint for later points
+        if (!W.valid[iMP]) continue;
+        MapPoint *pMP = vpPoints[iMP];
+        const int bestDist = W.bestDist[iMP], bestIdx = W.bestIdx[iMP];
+        if (bestDist <= TH_LOW) {
+            MapPoint *pMPinKF = pKF->GetMapPoint(bestIdx);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) vpReplacePoint[iMP] = pMPinKF;
+            } else {
+                pMP->AddObservation(pKF, bestIdx);
+                pKF->AddMapPoint(pMP, bestIdx);
+            }
+            nFused++;
+        }
+    }
+    return nFused;
+}
+
+int SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint *> &vpMatches12, const float &s12, const cv::Mat &R12,
+                 const cv::Mat &t12, float th) {
+    const float &fx = pKF1->fx;
+    const float &fy = pKF1->fy;
+    const float &cx = pKF1->cx;
+    const float &cy = pKF1->cy;
+    // camera 1 / 2 from world and the similarity between them, :1113-1123
+    cv::Mat R1w = pKF1->GetRotation();
+    cv::Mat t1w = pKF1->GetTranslation();
+    cv::Mat R2w = pKF2->GetRotation();
+    cv::Mat t2w = pKF2->GetTranslation();
+    cv::Mat sR12 = s12 * R12;
+    cv::Mat sR21 = (1.0 / s12) * R12.t();
+    cv::Mat t21 = -sR21 * t12;
+    const std::vector<MapPoint *> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size();
+    const std::vector<MapPoint *> vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {                                     // :1134-1144
+        MapPoint *pMP = vpMatches12[i];
+        if (pMP) {
+            vbAlreadyMatched1[i] = true;
+            int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+            if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+        }
+    }
+    // both directions share one shape: project the map points of KF `a` into KF `b` (:1150-1226 and :1229-1305)
+    struct Dir {
+        static void Gather(const std::vector<MapPoint *> &pts, const std::vector<bool> &already, const cv::Mat &Raw, const cv::Mat &taw,
+                           const cv::Mat &sRba, const cv::Mat &tba, KeyFrame *pKFb, float fx, float fy, float cx, float cy, float th,
+                           WindowSet &W) {
+            for (int i = 0, n = (int)pts.size(); i < n; i++) {
+                MapPoint *pMP = pts[i];
+                if (!pMP || already[i]) continue;
+                if (pMP->isBad()) continue;
+                cv::Mat p3Dw = pMP->GetWorldPos();
+                cv::Mat p3Dca = Raw * p3Dw + taw;
+                cv::Mat p3Dcb = sRba * p3Dca + tba;
+                if (p3Dcb.at<float>(2) < 0.0) continue;
+                const float invz = 1.0 / p3Dcb.at<float>(2);
+                const float x = p3Dcb.at<float>(0) * invz;
+                const float y = p3Dcb.at<float>(1) * invz;
+                const float u = fx * x + cx;
+                const float v = fy * y + cy;
+                if (!pKFb->IsInImage(u, v)) continue;
+                const float maxDistance = pMP->GetMaxDistanceInvariance();
+                const float minDistance = pMP->GetMinDistanceInvariance();
+                const float dist3D = cv::norm(p3Dcb);
+                if (dist3D < minDistance || dist3D > maxDistance) continue;
+                const int nPredictedLevel = pMP->PredictScale(dist3D, pKFb->mfLogScaleFactor);
+                if (!LevelOk(nPredictedLevel, pKFb)) continue;
+                W.Set(i, u, v, 0.f, nPredictedLevel, th * pKFb->mvScaleFactors[nPredictedLevel], pMP);
+            }
+        }
+    };
+    WindowSet W1(N1), W2(N2);
+    Dir::Gather(vpMapPoints1, vbAlreadyMatched1, R1w, t1w, sR21, t21, pKF2, fx, fy, cx, cy, th, W1);
+    Dir::Gather(vpMapPoints2, vbAlreadyMatched2, R2w, t2w, sR12, t12, pKF1, fx, fy, cx, cy, th, W2);
+    W1.Search(pKF2, false);
+    W2.Search(pKF1, false);
+    std::vector<int> vnMatch1(N1, -1), vnMatch2(N2, -1);
+    for (int i1 = 0; i1 < N1; i1++)
+        if (W1.valid[i1] && W1.bestDist[i1] <= TH_HIGH) vnMatch1[i1] = W1.bestIdx[i1];   // :1222-1225
+    for (int i2 = 0; i2 < N2; i2++)
+        if (W2.valid[i2] && W2.bestDist[i2] <= TH_HIGH) vnMatch2[i2] = W2.bestIdx[i2];   // :1301-1304
+    int nFound = 0;                                                    // :1308-1326
+    for (int i1 = 0; i1 < N1; i1++) {
+        int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) {
+                vpMatches12[i1] = vpMapPoints2[idx2];
+                nFound++;
+            }
+        }
+    }
+    return nFound;
 }
 
 }  // namespace orbgpu_shim

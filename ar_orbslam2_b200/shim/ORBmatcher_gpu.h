@@ -6,6 +6,7 @@
 #ifndef ORBMATCHER_GPU_H
 #define ORBMATCHER_GPU_H
 
+#include <utility>
 #include <vector>
 
 #include "Frame.h"
@@ -27,6 +28,21 @@ int SearchForInitialization(Frame &F1, Frame &F2, std::vector<cv::Point2f> &vbPr
 
 // ref ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint*> &vpMapPointMatches), :159-288
 int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatches, float mfNNratio, bool mbCheckOrientation);
+
+// ---- LocalMapping / LoopClosing matchers (M9) ----
+// ref ORBmatcher::SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, vector<pair<size_t,size_t>>&, bool bOnlyStereo), :660-826
+int SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> > &vMatchedPairs,
+                           bool bOnlyStereo, bool mbCheckOrientation);
+
+// ref ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, const float th), :828-978
+int Fuse(KeyFrame *pKF, const std::vector<MapPoint *> &vpMapPoints, float th);
+
+// ref ORBmatcher::Fuse(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, float th, vector<MapPoint*> &vpReplacePoint), :980-1103
+int Fuse(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *> &vpPoints, float th, std::vector<MapPoint *> &vpReplacePoint);
+
+// ref ORBmatcher::SearchBySim3(KeyFrame*, KeyFrame*, vector<MapPoint*> &vpMatches12, s12, R12, t12, th), :1105-1329
+int SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint *> &vpMatches12, const float &s12, const cv::Mat &R12,
+                 const cv::Mat &t12, float th);
 
 }  // namespace orbgpu_shim
 }  // namespace ORB_SLAM2

@@ -13,7 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._abi import (KEYPOINT_DTYPE, OrbFrameDesc, OrbLastPoints, OrbTrackPoints, OrbWindowQueries, optr, ptr)
+from ._abi import (KEYPOINT_DTYPE, OrbFrameDesc, OrbLastPoints, OrbReprojGate, OrbTrackPoints, OrbWindowQueries, optr, ptr)
 
 ORB_SELECT_BEST, ORB_SELECT_RATIO_LEVEL = 0, 1
 
@@ -43,7 +43,7 @@ def _u8(a):
 class Frame:
     """The matcher-facing part of ORB_SLAM2::Frame (ref Frame.h:39-40,161-163; Frame.cc:235-250,332-397)."""
 
-    def __init__(self, keys_un, descriptors, scale_factors, bounds, u_right=None, backend=None):
+    def __init__(self, keys_un, descriptors, scale_factors, bounds, u_right=None, backend=None, keyframe_view=False):
         self.B = backend or _GpuBackend()
         self.keys = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
         self.desc = _u8(descriptors).reshape(-1, 32)
@@ -51,7 +51,8 @@ class Frame:
         self.u_right = _f32(u_right)
         self.N = len(self.keys)
         self.bounds = tuple(float(b) for b in bounds)   # mnMinX, mnMaxX, mnMinY, mnMaxY
-        d = OrbFrameDesc(self.N, ptr(self.keys), ptr(self.desc), optr(self.u_right), *self.bounds, len(self.scale), ptr(self.scale))
+        d = OrbFrameDesc(self.N, ptr(self.keys), ptr(self.desc), optr(self.u_right), *self.bounds, len(self.scale), ptr(self.scale),
+                         1 if keyframe_view else 0)
         self._h = C.c_void_p()
         self.B.check(getattr(self.B.L, self.B.prefix + "frame_create")(C.byref(d), C.byref(self._h)), "frame_create")
         _lib.register(self)
@@ -161,6 +162,35 @@ class ORBmatcher:
                                                int(strict_low), C.c_float(self.mfNNratio), int(self.mbCheckOrientation), ptr(matches),
                                                C.byref(nm)), "search_by_bow")
         return nm.value, matches
+
+    def SearchWindowBest(self, F: Frame, x, y, radius, min_level, max_level, descriptors, valid=None, strict_levels=True,
+                         gate_ur=None, inv_level_sigma2=None, chi2_mono=5.99, chi2_stereo=7.8):
+        """The candidate loop of Fuse (ORBmatcher.cc:895-951, 1052-1072) and SearchBySim3 (:1191-1213, 1271-1293): independent
+        queries, closest descriptor of the window.  gate_ur + inv_level_sigma2 switch on Fuse's reprojection-error gate
+        (:917-945).  Returns (best_idx[n], best_dist[n]); the caller applies TH_LOW / TH_HIGH and the map bookkeeping."""
+        a = dict(valid=_u8(valid), x=_f32(x), y=_f32(y), radius=_f32(radius), min_level=_i32(min_level), max_level=_i32(max_level),
+                 descriptors=_u8(descriptors))
+        n = len(a["x"])
+        Q = OrbWindowQueries(n, optr(a["valid"]), optr(a["x"]), optr(a["y"]), optr(a["radius"]), optr(a["min_level"]),
+                             optr(a["max_level"]), int(strict_levels), None, None, optr(a["descriptors"]), None, None)
+        best_idx, best_dist = np.full(n, -1, np.int32), np.zeros(n, np.int32)
+        gur, inv = _f32(gate_ur), _f32(inv_level_sigma2)
+        G = OrbReprojGate(optr(gur), optr(inv), float(chi2_mono), float(chi2_stereo)) if inv is not None else None
+        self.B.check(self._fn("search_window_best")(F._h, C.byref(Q), C.byref(G) if G is not None else None, ptr(best_idx),
+                                                    ptr(best_dist)), "search_window_best")
+        return best_idx, best_dist
+
+    def SearchForTriangulation(self, KF1: Frame, KF2: Frame, off1, idx1, off2, idx2, usable1, usable2, F12, ex, ey, level_sigma2,
+                               bOnlyStereo=False):
+        """ref SearchForTriangulation, ORBmatcher.cc:660-826 (+ CheckDistEpipolarLine :140-157).  Returns (nmatches, vMatches12)."""
+        o1, i1, o2, i2 = _i32(off1), _i32(idx1), _i32(off2), _i32(idx2)
+        u1, u2, F, s2 = _u8(usable1), _u8(usable2), _f32(F12).reshape(9), _f32(level_sigma2)
+        m12 = np.full(KF1.N, -1, np.int32)
+        nm = C.c_int()
+        self.B.check(self._fn("search_for_triangulation")(KF1._h, KF2._h, len(o1) - 1, ptr(o1), ptr(i1), ptr(o2), ptr(i2), ptr(u1), ptr(u2),
+                                                          ptr(F), C.c_float(ex), C.c_float(ey), ptr(s2), int(bOnlyStereo),
+                                                          int(self.mbCheckOrientation), ptr(m12), C.byref(nm)), "search_for_triangulation")
+        return nm.value, m12
 
 
 def rot_hist_filter(angle_a, angle_b) -> np.ndarray:

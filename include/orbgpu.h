@@ -183,6 +183,10 @@ typedef struct orb_frame_desc {
     float min_x, max_x, min_y, max_y;      /* mnMinX ...                                   */
     int32_t nlevels;
     const float *scale_factors;    /* mvScaleFactors, nlevels entries                      */
+    int32_t keyframe_view;         /* 1 = window queries see the bounds as KeyFrame does: its
+                                      mnMinX/mnMinY are `int` copies of the Frame's floats
+                                      (KeyFrame.h:190-193, KeyFrame.cc:41-46) while mGrid and the
+                                      cell scales are the Frame's own (KeyFrame.cc:55-62)     */
 } orb_frame_desc;
 
 typedef struct orb_frame orb_frame;
@@ -286,6 +290,39 @@ int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *k
 /* ref: ORBmatcher::ComputeThreeMaxima + the rotation binning, src/ORBmatcher.cc:238-245,
  * 1604-1645 (factor = 1/HISTO_LENGTH quirk kept).  keep[i]=1 if pair i survives.           */
 int orb_rot_hist_filter(const float *angle_a, const float *angle_b, int n, uint8_t *keep);
+
+/* ---- mapping / loop-closing matchers (LocalMapping and LoopClosing threads) ------------- */
+
+/* ref: the candidate loops of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>&, th)
+ * (src/ORBmatcher.cc:895-951), Fuse(KeyFrame*, Scw, ...) (:1052-1072) and SearchBySim3
+ * (:1191-1213, :1271-1293).  Every query is independent (these loops never look at what an
+ * earlier query took): window -> in-loop level filter -> optional reprojection-error gate ->
+ * closest descriptor, first one in traversal order on ties (`dist<bestDist`).  The caller keeps
+ * the projection algebra, the final threshold (TH_LOW / TH_HIGH) and the map bookkeeping that
+ * follows (:954-973, :1075-1088, :1301-1326).
+ * best_idx[q] = -1, best_dist[q] = INT32_MAX when the window holds no admissible feature.      */
+typedef struct orb_reproj_gate {   /* ref :917-945 */
+    const float *ur;               /* per query: u - bf*invz                                   */
+    const float *inv_level_sigma2; /* pKF->mvInvLevelSigma2, one per pyramid level             */
+    double chi2_mono, chi2_stereo; /* 5.99 and 7.8 in the reference (compared in double)       */
+} orb_reproj_gate;
+int orb_search_window_best(orb_frame *f, const orb_window_queries *q, const orb_reproj_gate *gate,
+                           int32_t *best_idx, int32_t *best_dist);
+
+/* ref: ORBmatcher::SearchForTriangulation, src/ORBmatcher.cc:660-826, with
+ * CheckDistEpipolarLine :140-157.  The FeatureVector merge-join (:695-786) is passed as CSR over
+ * the common vocabulary nodes like orb_search_by_bow.  usable1[i] / usable2[i] = the key frame
+ * holds no map point at that feature (:704-708, :726-730).  F12: 9 floats, row major.  (ex, ey):
+ * projection of KF1's centre into KF2 (:667-673).  level_sigma2: pKF2->mvLevelSigma2;
+ * pKF2->mvScaleFactors comes from kf2's orb_frame.  matches12[i1] (size kf1->n) = matched feature
+ * of KF2 or -1 (the reference's vMatches12; vMatchedPairs is its non-negative entries in order).
+ * This fork never sets vbMatched2 (:778-781), so a KF2 feature may serve several KF1 features;
+ * that is reproduced.                                                                           */
+int orb_search_for_triangulation(orb_frame *kf1, orb_frame *kf2, int ngroups, const int32_t *off1,
+                                 const int32_t *idx1, const int32_t *off2, const int32_t *idx2,
+                                 const uint8_t *usable1, const uint8_t *usable2, const float *F12,
+                                 float ex, float ey, const float *level_sigma2, int only_stereo,
+                                 int check_orientation, int32_t *matches12, int *nmatches);
 
 /* ---- stereo ---------------------------------------------------------------------------- */
 

@@ -46,6 +46,12 @@ int orbref_search_by_projection_last(orbref_frame *Cur, const orb_last_points *P
 int orbref_search_by_bow(orbref_frame *KF, orbref_frame *F, int ngroups, const int32_t *kf_off, const int32_t *kf_idx,
                          const int32_t *f_off, const int32_t *f_idx, const uint8_t *kf_valid, const uint8_t *f_valid,
                          int strict_low, float mfNNratio, int mbCheckOrientation, int32_t *matches, int *nmatches_out);
+int orbref_search_window_best(orbref_frame *F, const orb_window_queries *Q, const orb_reproj_gate *gate, int32_t *best_idx,
+                              int32_t *best_dist);
+int orbref_search_for_triangulation(orbref_frame *KF1, orbref_frame *KF2, int ngroups, const int32_t *off1, const int32_t *idx1,
+                                    const int32_t *off2, const int32_t *idx2, const uint8_t *usable1, const uint8_t *usable2,
+                                    const float *F12, float ex, float ey, const float *level_sigma2, int only_stereo,
+                                    int check_orientation, int32_t *matches12, int *nmatches);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -400,3 +400,42 @@ class ShimBackend:
 
     def check(self, rc, what):
         _check(rc, what)
+
+
+def _c(a, dt):
+    return np.ascontiguousarray(a, dt)
+
+
+def refm_fuse(kf, variant, Rcw, tcw, Scw, world_xyz, normal_xyz, present, max_dist, min_dist, desc, nobs, in_kf, kf_mp_obs, fx, fy, cx, cy,
+              mbf, th):
+    """ORBmatcher::Fuse (variant 0: :828-978, variant 1: the Sim3 overload :980-1103) with its map bookkeeping, through the
+    library of kf's backend (reference source or the product shim).  Returns the final state as a dict of arrays."""
+    L = kf.B.L
+    xyz = _c(world_xyz, np.float32)
+    n = xyz.shape[0]
+    a = [_c(Rcw, np.float32), _c(tcw, np.float32), _c(Scw, np.float32)]
+    b = [xyz, _c(normal_xyz, np.float32), _c(present, np.uint8), _c(max_dist, np.float32), _c(min_dist, np.float32), _c(desc, np.uint8),
+         _c(nobs, np.int32), _c(in_kf, np.int32), _c(kf_mp_obs, np.int32)]
+    kf_state, kfmp_repl = np.zeros(kf.N, np.int32), np.zeros(kf.N, np.int32)
+    pt_obs, pt_repl = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    nf = C.c_int()
+    f = C.c_float
+    _check(L.refm_fuse(kf._h, int(variant), *[ptr(x) for x in a], n, *[ptr(x) for x in b], f(fx), f(fy), f(cx), f(cy), f(mbf), f(th),
+                       ptr(kf_state), ptr(pt_obs), ptr(pt_repl), ptr(kfmp_repl), C.byref(nf)), "refm_fuse")
+    return dict(kf_state=kf_state, pt_obs=pt_obs, pt_repl=pt_repl, kfmp_repl=kfmp_repl, nfused=nf.value)
+
+
+def refm_search_by_sim3(kf1, kf2, s12, R12, t12, R1w, t1w, R2w, t2w, has1, world1, maxd1, mind1, desc1, has2, world2, maxd2, mind2, desc2,
+                        pre12, fx, fy, cx, cy, th):
+    """ORBmatcher::SearchBySim3, ORBmatcher.cc:1105-1329, through the library of kf1's backend.  Returns (nFound, matches12)."""
+    L = kf1.B.L
+    poses = [_c(x, np.float32) for x in (R12, t12, R1w, t1w, R2w, t2w)]
+    s1 = [_c(has1, np.uint8), _c(world1, np.float32), _c(maxd1, np.float32), _c(mind1, np.float32), _c(desc1, np.uint8)]
+    s2 = [_c(has2, np.uint8), _c(world2, np.float32), _c(maxd2, np.float32), _c(mind2, np.float32), _c(desc2, np.uint8)]
+    pre = _c(pre12, np.int32)
+    m12 = np.full(kf1.N, -1, np.int32)
+    nf = C.c_int()
+    f = C.c_float
+    _check(L.refm_search_by_sim3(kf1._h, kf2._h, f(s12), *[ptr(x) for x in poses], *[ptr(x) for x in s1], *[ptr(x) for x in s2], ptr(pre),
+                                 f(fx), f(fy), f(cx), f(cy), f(th), ptr(m12), C.byref(nf)), "refm_search_by_sim3")
+    return nf.value, m12

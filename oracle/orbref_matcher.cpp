@@ -179,6 +179,9 @@ int orbref_frame_create(const orb_frame_desc *d, orbref_frame **out) {
         int gx, gy;
         if (f->PosInGrid(f->mvKeysUn[i], gx, gy)) f->mGrid[gx][gy].push_back(i);
     }
+    if (d->keyframe_view) {   // KeyFrame keeps `int` copies of the bounds (KeyFrame.h:190-193) next to the Frame's grid and cell scales
+        f->mnMinX = (float)(int)f->mnMinX; f->mnMaxX = (float)(int)f->mnMaxX; f->mnMinY = (float)(int)f->mnMinY; f->mnMaxY = (float)(int)f->mnMaxY;
+    }
     *out = f;
     return ORB_OK;
 }
@@ -412,6 +415,124 @@ int orbref_search_by_bow(orbref_frame *KF, orbref_frame *F, int ngroups, const i
             if (i == ind1 || i == ind2 || i == ind3) continue;
             for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
                 matches[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    *nmatches_out = nmatches;
+    return ORB_OK;
+}
+
+// The candidate loop shared by Fuse (ORBmatcher.cc:895-951 with the reprojection gate :917-945; :1052-1072 without) and
+// SearchBySim3 (:1191-1213, :1271-1293): independent queries, `dist<bestDist`, no claims.  See orb_search_window_best.
+int orbref_search_window_best(orbref_frame *F, const orb_window_queries *Q, const orb_reproj_gate *gate, int32_t *best_idx,
+                              int32_t *best_dist) {
+    for (int q = 0; q < Q->n; q++) {
+        best_idx[q] = -1; best_dist[q] = INT_MAX;
+        if (Q->valid && !Q->valid[q]) continue;
+        const float u = Q->x[q], v = Q->y[q], radius = Q->radius[q];
+        const std::vector<size_t> vIndices = F->GetFeaturesInArea(u, v, radius, Q->min_level[q], Q->max_level[q], Q->strict_levels != 0);
+        if (vIndices.empty()) continue;
+        const uint8_t *dMP = Q->descriptors + (size_t)q * 32;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+            const size_t idx = *vit;
+            const orb_keypoint &kp = F->mvKeysUn[idx];
+            const int kpLevel = kp.octave;
+            if (Q->stereo_ref && F->mvuRight[idx] > 0) {
+                const float er = fabs(Q->stereo_ref[q] - F->mvuRight[idx]);
+                if (er > Q->stereo_tol[q]) continue;
+            }
+            if (gate) {
+                if (F->mvuRight[idx] >= 0) {   // ref :917-931
+                    const float kpx = kp.x, kpy = kp.y, kpr = F->mvuRight[idx];
+                    const float ex = u - kpx, ey = v - kpy, er = gate->ur[q] - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * gate->inv_level_sigma2[kpLevel] > gate->chi2_stereo) continue;
+                } else {                       // ref :932-945
+                    const float kpx = kp.x, kpy = kp.y;
+                    const float ex = u - kpx, ey = v - kpy;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * gate->inv_level_sigma2[kpLevel] > gate->chi2_mono) continue;
+                }
+            }
+            const int dist = descriptor_distance(dMP, F->desc(idx));
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        best_idx[q] = bestIdx; best_dist[q] = bestDist;
+    }
+    return ORB_OK;
+}
+
+// ref ORBmatcher::CheckDistEpipolarLine, ORBmatcher.cc:140-157
+static bool CheckDistEpipolarLine(const orb_keypoint &kp1, const orb_keypoint &kp2, const float *F12, const float *mvLevelSigma2) {
+    const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+    const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+    const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+    const float num = a * kp2.x + b * kp2.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * mvLevelSigma2[kp2.octave];
+}
+
+// ref ORBmatcher::SearchForTriangulation, ORBmatcher.cc:660-826 (this fork never sets vbMatched2)
+int orbref_search_for_triangulation(orbref_frame *KF1, orbref_frame *KF2, int ngroups, const int32_t *off1, const int32_t *idx1v,
+                                    const int32_t *off2, const int32_t *idx2v, const uint8_t *usable1, const uint8_t *usable2,
+                                    const float *F12, float ex, float ey, const float *level_sigma2, int bOnlyStereo,
+                                    int mbCheckOrientation, int32_t *vMatches12, int *nmatches_out) {
+    int nmatches = 0;
+    std::vector<bool> vbMatched2(KF2->N, false);
+    for (int i = 0; i < KF1->N; i++) vMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    for (int g = 0; g < ngroups; g++) {
+        for (int i1 = off1[g]; i1 < off1[g + 1]; i1++) {
+            const size_t idx1 = idx1v[i1];
+            if (!usable1[idx1]) continue;
+            const bool bStereo1 = KF1->mvuRight[idx1] >= 0;
+            if (bOnlyStereo)
+                if (!bStereo1) continue;
+            const orb_keypoint &kp1 = KF1->mvKeysUn[idx1];
+            const uint8_t *d1 = KF1->desc(idx1);
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            for (int i2 = off2[g]; i2 < off2[g + 1]; i2++) {
+                const size_t idx2 = idx2v[i2];
+                if (vbMatched2[idx2] || !usable2[idx2]) continue;
+                const bool bStereo2 = KF2->mvuRight[idx2] >= 0;
+                if (bOnlyStereo)
+                    if (!bStereo2) continue;
+                const int dist = descriptor_distance(d1, KF2->desc(idx2));
+                if (dist > TH_LOW || dist > bestDist) continue;
+                const orb_keypoint &kp2 = KF2->mvKeysUn[idx2];
+                if (!bStereo1 && !bStereo2) {
+                    const float distex = ex - kp2.x;
+                    const float distey = ey - kp2.y;
+                    if (distex * distex + distey * distey < 100 * KF2->mvScaleFactors[kp2.octave]) continue;
+                }
+                if (CheckDistEpipolarLine(kp1, kp2, F12, level_sigma2)) { bestIdx2 = (int)idx2; bestDist = dist; }
+            }
+            if (bestIdx2 >= 0) {
+                const orb_keypoint &kp2 = KF2->mvKeysUn[bestIdx2];
+                vMatches12[idx1] = bestIdx2;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = kp1.angle - kp2.angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back((int)idx1);
+                }
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        rot_filter(rotHist, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                vMatches12[rotHist[i][j]] = -1;
                 nmatches--;
             }
         }

@@ -42,6 +42,10 @@ static std::unique_ptr<KeyFrame> as_keyframe(const refm_frame *f) {
     std::unique_ptr<KeyFrame> k(new KeyFrame());
     k->N = f->F.N; k->mvKeysUn = f->F.mvKeysUn; k->mvuRight = f->F.mvuRight; k->mDescriptors = f->F.mDescriptors;
     k->mvScaleFactors = f->F.mvScaleFactors; k->mfLogScaleFactor = f->F.mfLogScaleFactor;
+    for (size_t i = 0; i < k->mvScaleFactors.size(); i++) {   // ref ORBextractor.cc:417-428 via KeyFrame.cc:38-40
+        k->mvLevelSigma2.push_back(k->mvScaleFactors[i] * k->mvScaleFactors[i]);
+        k->mvInvLevelSigma2.push_back(1.0f / k->mvLevelSigma2[i]);
+    }
     k->mvpMapPoints.assign(k->N, nullptr);
     k->mnMinX = (int)f->d.min_x; k->mnMaxX = (int)f->d.max_x; k->mnMinY = (int)f->d.min_y; k->mnMaxY = (int)f->d.max_y;
     k->mfGridElementWidthInv = Frame::mfGridElementWidthInv; k->mfGridElementHeightInv = Frame::mfGridElementHeightInv;
@@ -454,6 +458,156 @@ int refm_stereo_match(const uint8_t *img_left, const uint8_t *img_right, int wid
     return 0;
 }
 #endif
+
+static void set_pose(KeyFrame *K, const float *R9, const float *t3) {
+    K->Rcw = cv::Mat(3, 3, CV_32F); K->tcw = cv::Mat(3, 1, CV_32F);
+    memcpy(K->Rcw.data, R9, 36); memcpy(K->tcw.data, t3, 12);
+    K->Ow = -K->Rcw.t() * K->tcw;   // ref KeyFrame.cc:79
+}
+static cv::Mat vec3(const float *p) { cv::Mat m(3, 1, CV_32F); memcpy(m.data, p, 12); return m; }
+
+// ref ORBmatcher::SearchForTriangulation, ORBmatcher.cc:660-826.  Same signature as orb_search_for_triangulation; KF2 is given an
+// identity pose and unit intrinsics and KF1's centre is put at (ex, ey, 1), so the reference's own epipole arithmetic (:667-673)
+// returns exactly (ex, ey).
+int refm_search_for_triangulation(refm_frame *kf1, refm_frame *kf2, int ngroups, const int32_t *off1, const int32_t *idx1, const int32_t *off2,
+                                  const int32_t *idx2, const uint8_t *usable1, const uint8_t *usable2, const float *F12, float ex, float ey,
+                                  const float *level_sigma2, int only_stereo, int check_orientation, int32_t *matches12, int *nmatches) {
+    set_statics(kf2);
+    std::unique_ptr<KeyFrame> K1 = as_keyframe(kf1), K2 = as_keyframe(kf2);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    for (int i = 0; i < K1->N; i++)
+        if (!usable1[i]) { store.emplace_back(new MapPoint()); K1->mvpMapPoints[i] = store.back().get(); }
+    for (int i = 0; i < K2->N; i++)
+        if (!usable2[i]) { store.emplace_back(new MapPoint()); K2->mvpMapPoints[i] = store.back().get(); }
+    fill_featvec(K1->mFeatVec, ngroups, off1, idx1);
+    fill_featvec(K2->mFeatVec, ngroups, off2, idx2);
+    const float I9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, z3[3] = {0, 0, 0};
+    set_pose(K1.get(), I9, z3); set_pose(K2.get(), I9, z3);
+    K1->Ow = cv::Mat(3, 1, CV_32F);
+    K1->Ow.at<float>(0) = ex; K1->Ow.at<float>(1) = ey; K1->Ow.at<float>(2) = 1.0f;
+    K2->fx = K2->fy = 1.0f; K2->cx = K2->cy = 0.0f;
+    K2->mvLevelSigma2.assign(level_sigma2, level_sigma2 + K2->mvScaleFactors.size());
+    cv::Mat F(3, 3, CV_32F);
+    memcpy(F.data, F12, 36);
+    std::vector<std::pair<size_t, size_t>> pairs;
+    ORBmatcher matcher(0.6f, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchForTriangulation(K1.get(), K2.get(), F, pairs, only_stereo != 0, check_orientation != 0);
+#else
+    *nmatches = matcher.SearchForTriangulation(K1.get(), K2.get(), F, pairs, only_stereo != 0);
+#endif
+    for (int i = 0; i < K1->N; i++) matches12[i] = -1;
+    for (size_t k = 0; k < pairs.size(); k++) matches12[pairs[k].first] = (int32_t)pairs[k].second;
+    return 0;
+}
+
+// Scenario for the two ORBmatcher::Fuse overloads (ORBmatcher.cc:828-978 and :980-1103) with the map bookkeeping they do.
+// Points: present[i] 0 = NULL entry, 1 = good, 2 = bad; in_kf[i] >= 0 = the point is already observed by the key frame at that feature.
+// kf_mp_obs[idx] >= 0 = the key frame holds some other map point there with that many observations (id 1000000+idx).
+// Outputs: kf_state[idx] = id at that feature afterwards (-1 none); pt_obs[i] = feature the point observes in the key frame (-1 none);
+// pt_repl[i] = id that replaced point i (variant 0) / vpReplacePoint[i] (variant 1); kfmp_repl[idx] = id that replaced the pre-existing point.
+int refm_fuse(refm_frame *kf, int variant, const float *Rcw9, const float *tcw3, const float *Scw16, int n, const float *world_xyz,
+              const float *normal_xyz, const uint8_t *present, const float *max_dist, const float *min_dist, const uint8_t *desc,
+              const int32_t *nobs, const int32_t *in_kf, const int32_t *kf_mp_obs, float fx, float fy, float cx, float cy, float mbf, float th,
+              int32_t *kf_state, int32_t *pt_obs, int32_t *pt_repl, int32_t *kfmp_repl, int *nfused) {
+    set_statics(kf);
+    std::unique_ptr<KeyFrame> K = as_keyframe(kf);
+    K->fx = fx; K->fy = fy; K->cx = cx; K->cy = cy; K->mbf = mbf;
+    set_pose(K.get(), Rcw9, tcw3);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    std::vector<MapPoint *> pts(n, nullptr), pre(K->N, nullptr);
+    for (int idx = 0; idx < K->N; idx++)
+        if (kf_mp_obs[idx] >= 0) {
+            store.emplace_back(new MapPoint());
+            MapPoint *m = store.back().get();
+            m->id = 1000000 + idx; m->nObs = kf_mp_obs[idx]; m->observations[K.get()] = idx;
+            K->mvpMapPoints[idx] = m; pre[idx] = m;
+        }
+    for (int i = 0; i < n; i++) {
+        if (!present[i]) continue;
+        store.emplace_back(new MapPoint());
+        MapPoint *m = store.back().get();
+        m->id = i; m->bad = present[i] == 2; m->nObs = nobs[i];
+        m->worldPos = vec3(world_xyz + 3 * i); m->normal = vec3(normal_xyz + 3 * i);
+        m->mfMaxDistance = max_dist[i]; m->mfMinDistance = min_dist[i];
+        m->descriptor = desc_row(desc + (size_t)i * 32);
+        if (in_kf[i] >= 0) { m->observations[K.get()] = in_kf[i]; K->mvpMapPoints[in_kf[i]] = m; }
+        pts[i] = m;
+    }
+    std::vector<MapPoint *> repl(n, nullptr);
+    ORBmatcher matcher(0.6f, true);
+    if (variant == 0) {
+#ifdef USE_GPU_SHIM
+        *nfused = orbgpu_shim::Fuse(K.get(), pts, th);
+#else
+        *nfused = matcher.Fuse(K.get(), pts, th);
+#endif
+    } else {
+        cv::Mat S(4, 4, CV_32F);
+        memcpy(S.data, Scw16, 64);
+#ifdef USE_GPU_SHIM
+        *nfused = orbgpu_shim::Fuse(K.get(), S, pts, th, repl);
+#else
+        *nfused = matcher.Fuse(K.get(), S, pts, th, repl);
+#endif
+    }
+    for (int idx = 0; idx < K->N; idx++) {
+        kf_state[idx] = K->mvpMapPoints[idx] ? K->mvpMapPoints[idx]->id : -1;
+        kfmp_repl[idx] = (pre[idx] && pre[idx]->replaced) ? pre[idx]->replaced->id : -1;
+    }
+    for (int i = 0; i < n; i++) {
+        pt_obs[i] = -1; pt_repl[i] = -1;
+        if (!pts[i]) continue;
+        if (pts[i]->observations.count(K.get())) pt_obs[i] = (int32_t)pts[i]->observations[K.get()];
+        MapPoint *r = variant == 0 ? pts[i]->replaced : repl[i];
+        if (r) pt_repl[i] = r->id;
+    }
+    return 0;
+}
+
+// ref ORBmatcher::SearchBySim3, ORBmatcher.cc:1105-1329.  has1/has2: 0 = no map point at the feature, 1 = good, 2 = bad.
+// pre12[i1] >= 0: vpMatches12[i1] holds KF2's map point of that feature on entry.  matches12[i1] = feature of KF2 whose map point
+// ends up in vpMatches12[i1], or -1.
+int refm_search_by_sim3(refm_frame *kf1, refm_frame *kf2, float s12, const float *R12, const float *t12, const float *R1w, const float *t1w,
+                        const float *R2w, const float *t2w, const uint8_t *has1, const float *world1, const float *maxd1, const float *mind1,
+                        const uint8_t *desc1, const uint8_t *has2, const float *world2, const float *maxd2, const float *mind2,
+                        const uint8_t *desc2, const int32_t *pre12, float fx, float fy, float cx, float cy, float th, int32_t *matches12,
+                        int *nfound) {
+    set_statics(kf1);
+    std::unique_ptr<KeyFrame> K1 = as_keyframe(kf1), K2 = as_keyframe(kf2);
+    K1->fx = fx; K1->fy = fy; K1->cx = cx; K1->cy = cy;
+    K2->fx = fx; K2->fy = fy; K2->cx = cx; K2->cy = cy;
+    set_pose(K1.get(), R1w, t1w); set_pose(K2.get(), R2w, t2w);
+    std::vector<std::unique_ptr<MapPoint>> store;
+    auto fill = [&](KeyFrame *K, const uint8_t *has, const float *world, const float *maxd, const float *mind, const uint8_t *desc) {
+        for (int i = 0; i < K->N; i++) {
+            if (!has[i]) continue;
+            store.emplace_back(new MapPoint());
+            MapPoint *m = store.back().get();
+            m->id = i; m->bad = has[i] == 2;
+            m->worldPos = vec3(world + 3 * i);
+            m->mfMaxDistance = maxd[i]; m->mfMinDistance = mind[i];
+            m->descriptor = desc_row(desc + (size_t)i * 32);
+            m->observations[K] = i;
+            K->mvpMapPoints[i] = m;
+        }
+    };
+    fill(K1.get(), has1, world1, maxd1, mind1, desc1);
+    fill(K2.get(), has2, world2, maxd2, mind2, desc2);
+    std::vector<MapPoint *> m12(K1->N, nullptr);
+    for (int i = 0; i < K1->N; i++)
+        if (pre12[i] >= 0) m12[i] = K2->mvpMapPoints[pre12[i]];
+    cv::Mat R(3, 3, CV_32F), t = vec3(t12);
+    memcpy(R.data, R12, 36);
+    ORBmatcher matcher(0.6f, true);
+#ifdef USE_GPU_SHIM
+    *nfound = orbgpu_shim::SearchBySim3(K1.get(), K2.get(), m12, s12, R, t, th);
+#else
+    *nfound = matcher.SearchBySim3(K1.get(), K2.get(), m12, s12, R, t, th);
+#endif
+    for (int i = 0; i < K1->N; i++) matches12[i] = m12[i] ? m12[i]->id : -1;
+    return 0;
+}
 
 // ref ORBmatcher::DescriptorDistance, ORBmatcher.cc:1650-1666
 int refm_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist) {
