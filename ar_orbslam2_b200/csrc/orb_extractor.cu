@@ -39,22 +39,43 @@ __constant__ int c_umax[16];
 // Pyramid.  Each thread produces one aligned 32-bit word (4 pixels) of a padded plane row, so
 // stores are always aligned although the interior starts 19 pixels into the plane.
 // ------------------------------------------------------------------------------------------
-__global__ void k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_stride, int spitch,
-                             uint8_t *__restrict__ pyr, const Geom *__restrict__ G) {
+// Level 0: the caller's image (any pitch, rows not aligned) into the padded plane.  A thread makes 16 output bytes; where
+// all 16 lie strictly inside the image it reads five aligned source words and shifts them into place, elsewhere (the
+// reflected frame, the zero margin up to the pitch) it goes byte by byte.
+constexpr int L0_ROWS = 4;
+__global__ void __launch_bounds__(128)
+k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_stride, int spitch, uint8_t *__restrict__ pyr, const Geom *__restrict__ G) {
     const LevelGeom &g = G->lv[0];
-    const int word = blockIdx.x * blockDim.x + threadIdx.x;
-    const int py = blockIdx.y, b = blockIdx.z;
-    if (word * 4 >= g.pitch) return;
-    const int sy = reflect101(py - EDGE, g.h);
-    const uint8_t *srow = src + (size_t)b * frame_stride + (size_t)sy * spitch;
-    uint32_t v = 0;
+    const int q = blockIdx.x * 32 + (threadIdx.x & 31);                     // 16-byte chunk of the plane row
+    const int py = (blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5)) * L0_ROWS, b = blockIdx.z;
+    if (q * 16 >= g.pitch) return;
+    const int x0 = q * 16 - XOFF, rows = g.h + 2 * EDGE;
+    const uint8_t *sframe = src + (size_t)b * frame_stride;
+    uint8_t *plane = pyr + (size_t)b * G->pyr_frame + g.plane_off + (size_t)q * 16;
+    const bool inside = x0 >= 16 && x0 + 19 <= g.w;                          // the 20 bytes the aligned reads may touch
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int x = word * 4 + k - XOFF;
-        if (x >= -EDGE && x < g.w + EDGE) v |= (uint32_t)srow[reflect101(x, g.w)] << (8 * k);
+    for (int r = 0; r < L0_ROWS; r++) {
+        if (py + r >= rows) break;
+        const uint8_t *srow = sframe + (size_t)reflect101(py + r - EDGE, g.h) * spitch;
+        uint4 v;
+        if (inside) {
+            const uint8_t *p = srow + x0;
+            const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
+            const uint32_t *w = reinterpret_cast<const uint32_t *>(p - ((uintptr_t)p & 3u));
+            const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2), w3 = __ldg(w + 3), w4 = sh ? __ldg(w + 4) : 0u;
+            v.x = __funnelshift_r(w0, w1, sh); v.y = __funnelshift_r(w1, w2, sh);
+            v.z = __funnelshift_r(w2, w3, sh); v.w = __funnelshift_r(w3, w4, sh);
+        } else {
+            uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const int x = x0 + k;
+                if (x >= -EDGE && x < g.w + EDGE) o[k >> 2] |= (uint32_t)srow[reflect101(x, g.w)] << (8 * (k & 3));
+            }
+            v = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        *reinterpret_cast<uint4 *>(plane + (size_t)(py + r) * g.pitch) = v;
     }
-    uint8_t *plane = pyr + (size_t)b * G->pyr_frame + g.plane_off;
-    *reinterpret_cast<uint32_t *>(plane + (size_t)py * g.pitch + word * 4) = v;
 }
 
 __global__ void __launch_bounds__(128)
@@ -115,10 +136,14 @@ k_pyr_resize_generic(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, cons
     *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
 }
 
-// Fast path of the same resize for scale factors up to ~1.5 (every level of the reference's 1.2 pyramid): the host
-// precomputes, per aligned output word (4 pixels of the padded row, reflection and plane limits already resolved), one
-// 128-bit record { tap offset o (3 bits) | a0 (12) | a1 (12) } x 4 plus the word index of the 12-byte source window,
-// so a thread issues 1 + 6 loads for two output rows of 4 pixels and selects source bytes with PRMT.
+// Fast path of the same resize (every level of the reference's 1.2 pyramid; any scale factor up to ~2).  The host
+// precomputes, per aligned output word (4 pixels of the padded row, reflection and plane limits already resolved), two
+// 128-bit records: the four weight pairs as 16x2 words {a0 | a1 << 16}, and four PRMT selectors that pull the four
+// pixels' two source bytes out of a 12-byte source window plus the window's word index.  A thread owns one output word
+// column and walks PYR_ROWS plane rows.  cv::resize interpolates horizontally first, and a source row serves the output
+// row above and the one below, so the horizontally interpolated source rows are kept in registers across output rows:
+// ~1.2 source rows (3 aligned loads, 4 PRMT, 4 IDP2A) per output row instead of 2.
+constexpr int PYR_ROWS = 8;
 __global__ void __launch_bounds__(128)
 k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
              const uint4 *__restrict__ wtab, int level) {
@@ -128,33 +153,43 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
     const int b = blockIdx.z;
     if (word * 4 >= g.pitch) return;
     uint8_t *frame = pyr + (size_t)b * G->pyr_frame;
-    const uint4 T = __ldg(wtab + g.wtab_off + word);
-    const uint32_t t[4] = {T.x, T.y, T.z, T.w};
-    const int base_word = (int)((T.x >> 27) | ((T.y >> 27) << 5));
-    const int rows = g.h + 2 * EDGE;
-#pragma unroll
-    for (int rr = 0; rr < 2; rr++) {
-        const int py = blockIdx.y * 2 + rr;
+    const uint4 Wt = __ldg(wtab + 2 * (g.wtab_off + word)), St = __ldg(wtab + 2 * (g.wtab_off + word) + 1);
+    const uint8_t *srcw = frame + p.interior_off + (size_t)St.z * 4;       // the window's first word in source row 0
+    uint8_t *dst = frame + g.plane_off + (size_t)word * 4;
+    const int rows = g.h + 2 * EDGE, py0 = blockIdx.y * PYR_ROWS;
+    int rA = -1, rB = -1;
+    uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
+    auto hrow = [&](int sy, uint32_t *h) {   // (S[x]*a0 + S[x+1]*a1) >> 4 of source row sy for the four pixels
+        const uint32_t *r = reinterpret_cast<const uint32_t *>(srcw + (size_t)sy * p.pitch);
+        const uint32_t a0 = __ldg(r), a1 = __ldg(r + 1), a2 = __ldg(r + 2);
+        const uint32_t x01 = __byte_perm(__byte_perm(a0, a1, St.x), a2, St.x >> 16);
+        const uint32_t x23 = __byte_perm(__byte_perm(a0, a1, St.y), a2, St.y >> 16);
+        h[0] = __dp2a_lo(Wt.x, x01, 0u) >> 4; h[1] = __dp2a_hi(Wt.y, x01, 0u) >> 4;
+        h[2] = __dp2a_lo(Wt.z, x23, 0u) >> 4; h[3] = __dp2a_hi(Wt.w, x23, 0u) >> 4;
+    };
+#pragma unroll 2
+    for (int rr = 0; rr < PYR_ROWS; rr++) {
+        const int py = py0 + rr;
         if (py >= rows) break;
         const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
-        const uint32_t *r0 = reinterpret_cast<const uint32_t *>(frame + p.interior_off + (size_t)ty.s0 * p.pitch) + base_word;
-        const uint32_t *r1 = reinterpret_cast<const uint32_t *>(frame + p.interior_off + (size_t)ty.s1 * p.pitch) + base_word;
-        const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
-        const uint32_t c0 = __ldg(r1), c1 = __ldg(r1 + 1), c2 = __ldg(r1 + 2);
+        const int s0 = ty.s0, s1 = ty.s1;
+        uint32_t n0[4], n1[4];
+        if (s0 == rA) { n0[0] = hA[0]; n0[1] = hA[1]; n0[2] = hA[2]; n0[3] = hA[3]; }
+        else if (s0 == rB) { n0[0] = hB[0]; n0[1] = hB[1]; n0[2] = hB[2]; n0[3] = hB[3]; }
+        else hrow(s0, n0);
+        if (s1 == s0) { n1[0] = n0[0]; n1[1] = n0[1]; n1[2] = n0[2]; n1[3] = n0[3]; }
+        else if (s1 == rB) { n1[0] = hB[0]; n1[1] = hB[1]; n1[2] = hB[2]; n1[3] = hB[3]; }
+        else if (s1 == rA) { n1[0] = hA[0]; n1[1] = hA[1]; n1[2] = hA[2]; n1[3] = hA[3]; }
+        else hrow(s1, n1);
+        rA = s0; rB = s1;
+        const uint32_t A0 = (uint32_t)ty.a0 << 16, A1 = (uint32_t)ty.a1 << 16;   // umulhi(a << 16, h) == (a * h) >> 16
         uint32_t v = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const int o = t[k] & 7, wa0 = (t[k] >> 3) & 0xfff, wa1 = (t[k] >> 15) & 0xfff;
-            const bool hi = o >= 4;
-            const uint32_t ua = hi ? a1 : a0, ub = hi ? a2 : a1, uc = hi ? c1 : c0, ud = hi ? c2 : c1;
-            const uint32_t sel = (uint32_t)(o & 3) | ((uint32_t)((o & 3) + 1) << 4) | 0x4400u;   // bytes o, o+1 of the window
-            const uint32_t pa = __byte_perm(ua, ub, sel), pc = __byte_perm(uc, ud, sel);
-            const int r0v = (int)(pa & 0xff) * wa0 + (int)((pa >> 8) & 0xff) * wa1;
-            const int r1v = (int)(pc & 0xff) * wa0 + (int)((pc >> 8) & 0xff) * wa1;
-            const int o8 = (((ty.a0 * (r0v >> 4)) >> 16) + ((ty.a1 * (r1v >> 4)) >> 16) + 2) >> 2;
-            v |= (uint32_t)o8 << (8 * k);
+            hA[k] = n0[k]; hB[k] = n1[k];
+            v |= ((__umulhi(A0, n0[k]) + __umulhi(A1, n1[k]) + 2u) >> 2) << (8 * k);
         }
-        *reinterpret_cast<uint32_t *>(frame + g.plane_off + (size_t)py * g.pitch + word * 4) = v;
+        *reinterpret_cast<uint32_t *>(dst + (size_t)py * g.pitch) = v;
     }
 }
 
@@ -1139,35 +1174,49 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
                 rc == ORB_ERR_TOO_SMALL ? "a pyramid level is too small for the 30-px cell grid (reference divides by zero)"
                                         : "unsupported geometry");
     ORB_REQUIRE(taps.size() <= ex->taps_cap, ORB_ERR_INVALID, "internal: tap pool too small");
-    // per-output-word resize records (fast path); a level whose 4-pixel source span exceeds the 12-byte window keeps
-    // the generic kernel
+    // per-output-word resize records (fast path), two uint4 per word: weights and byte selectors (see k_pyr_resize).  A
+    // level where some pixel's two source bytes do not fit the selectors' reach keeps the generic kernel.
     std::vector<uint4> wtab;
     for (int l = 1; l < G.nlevels; l++) {
         LevelGeom &g = G.lv[l];
-        g.wtab_off = (int)wtab.size();
+        g.wtab_off = (int)wtab.size() / 2;
         g.fast_resize = 1;
         const int nwords = g.pitch / 4;
         for (int w = 0; w < nwords; w++) {
-            int lo = 1 << 30, hi = 0;
+            int lo = 1 << 30;
             ResizeTap tx[4];
             bool in[4];
             for (int k = 0; k < 4; k++) {
                 const int x = w * 4 + k - XOFF;
                 in[k] = x >= -EDGE && x < g.w + EDGE;
                 tx[k] = taps[g.tap_x_off + reflect101(in[k] ? x : 0, g.w)];
-                if (in[k]) { lo = std::min(lo, (int)tx[k].s0); hi = std::max(hi, (int)tx[k].s0); }
+                if (in[k]) lo = std::min(lo, (int)tx[k].s0);
             }
-            uint32_t rec[4] = {0, 0, 0, 0};
+            uint32_t wt[4] = {0, 0, 0, 0}, o[4] = {0, 0, 0, 0};
             int base = 0;
             if (lo != (1 << 30)) {
-                base = lo & ~3;
-                if (hi - base > 7 || base / 4 >= 1024) g.fast_resize = 0;
+                base = lo & ~3;   // interior rows start 32-byte aligned, so this is a word boundary of the source row
                 for (int k = 0; k < 4; k++)
-                    if (in[k]) rec[k] = (uint32_t)((tx[k].s0 - base) & 7) | ((uint32_t)tx[k].a0 << 3) | ((uint32_t)tx[k].a1 << 15);
+                    if (in[k]) {
+                        o[k] = (uint32_t)(tx[k].s0 - base);   // the taps are bytes o, o+1 of the window (s1 == s0 only where a1 == 0)
+                        wt[k] = (uint32_t)(uint16_t)tx[k].a0 | ((uint32_t)(uint16_t)tx[k].a1 << 16);
+                        if (o[k] + 1 > 11u) g.fast_resize = 0;
+                    }
             }
-            rec[0] |= (uint32_t)((base / 4) & 31) << 27;
-            rec[1] |= (uint32_t)(((base / 4) >> 5) & 31) << 27;
-            wtab.push_back(make_uint4(rec[0], rec[1], rec[2], rec[3]));
+            // x01 = PRMT(PRMT(w0, w1, selA), w2, selB) = window bytes {o0, o0+1, o1, o1+1}: a byte below 8 comes from the first
+            // PRMT (kept in place by the second), one from 8 up straight from w2.  x23 likewise for pixels 2 and 3.  (Inside
+            // the reflected frame the offsets are not monotone in k, so every pixel gets the full 12-byte reach.)
+            auto selectors = [](uint32_t oa, uint32_t ob) {
+                uint32_t selA = 0, selB = 0;
+                const uint32_t want[4] = {oa, oa + 1, ob, ob + 1};
+                for (int i = 0; i < 4; i++) {
+                    if (want[i] < 8) { selA |= want[i] << (4 * i); selB |= (uint32_t)i << (4 * i); }
+                    else selB |= (4u + ((want[i] - 8) & 3)) << (4 * i);
+                }
+                return selA | (selB << 16);
+            };
+            wtab.push_back(make_uint4(wt[0], wt[1], wt[2], wt[3]));
+            wtab.push_back(make_uint4(selectors(o[0], o[1]), selectors(o[2], o[3]), (uint32_t)(base / 4), 0u));
         }
     }
     ORB_REQUIRE(wtab.size() <= ex->wtab_cap, ORB_ERR_INVALID, "internal: resize word table too small");
@@ -1242,7 +1291,7 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     }
     ex->taps_cap = (size_t)(params->max_width + params->max_height + 64) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_taps, ex->taps_cap * sizeof(ResizeTap)));
-    ex->wtab_cap = (size_t)((params->max_width + XOFF + EDGE + 127) / 128 * 32 + 32) * params->nlevels;
+    ex->wtab_cap = 2 * (size_t)((params->max_width + XOFF + EDGE + 127) / 128 * 32 + 32) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_wtab, ex->wtab_cap * sizeof(uint4)));
     ex->cells_cap = (size_t)(params->max_width / 30 + 2) * (params->max_height / 30 + 2) * 4 + 64;   // sum over levels < 3.1x level 0
     TRY_ALLOC(cudaMalloc(&ex->d_cells, ex->cells_cap * 4));
@@ -1374,15 +1423,19 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     prof_mark(ex, 1);
     {
         const LevelGeom &g = G.lv[0];
-        dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
+        dim3 grid((g.pitch / 16 + 31) / 32, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
         k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
         ex->launches++;
     }
     for (int l = 1; l < G.nlevels; l++) {
         const LevelGeom &g = G.lv[l];
         if (g.fast_resize) {
-            dim3 grid((g.pitch / 4 + 127) / 128, (g.h + 2 * EDGE + 1) / 2, batch);
-            k_pyr_resize<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            const int nw = g.pitch / 4;
+            int bx = 128;   // CTA width that wastes the fewest threads on this level's row
+            for (int c = 96; c >= 32; c -= 32)
+                if ((nw + c - 1) / c * c < (nw + bx - 1) / bx * bx) bx = c;
+            dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + PYR_ROWS - 1) / PYR_ROWS, batch);
+            k_pyr_resize<<<grid, bx, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
         } else {
             dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
             k_pyr_resize_generic<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);

@@ -129,9 +129,10 @@ def test_gpu_equals_reference_source(oracle, gpu_lib):
         ex.close()
 
 
-@pytest.mark.parametrize("scale,nlevels,w,h", [(2.0, 4, 800, 600), (1.5, 5, 800, 600), (1.1, 8, 640, 480), (1.2, 1, 320, 240)])
+@pytest.mark.parametrize("scale,nlevels,w,h", [(3.0, 3, 1200, 900), (2.5, 3, 1000, 800), (2.0, 4, 800, 600), (1.5, 5, 800, 600), (1.1, 8, 640, 480), (1.2, 1, 320, 240)])
 def test_other_scale_factors(oracle, gpu_lib, scale, nlevels, w, h):
-    """Non-default pyramids: scale 2.0 / 1.5 exercise the generic resize kernel (source span beyond the 12-byte window)."""
+    """Non-default pyramids: scale 3.0 / 2.5 exercise the generic resize kernel (a pixel's source bytes beyond the reach of the
+    word-record selectors), 2.0 and below the word-record kernel at its widest source windows."""
     from ar_orbslam2_b200.extractor import ORBextractor
     img = synth_frame(w, h, 61)
     ex = ORBextractor(800, scale, nlevels, 20, 7, max_width=w, max_height=h)
