@@ -39,42 +39,55 @@ __constant__ int c_umax[16];
 // Pyramid.  Each thread produces one aligned 32-bit word (4 pixels) of a padded plane row, so
 // stores are always aligned although the interior starts 19 pixels into the plane.
 // ------------------------------------------------------------------------------------------
-// Level 0: the caller's image (any pitch, rows not aligned) into the padded plane.  A thread makes 16 output bytes; where
-// all 16 lie strictly inside the image it reads five aligned source words and shifts them into place, elsewhere (the
-// reflected frame, the zero margin up to the pitch) it goes byte by byte.
+// Level 0: the caller's image (any pitch, rows not aligned) into the padded plane.  Columns of 16 output bytes that lie
+// strictly inside the image are copied by the first grid.x - 1 CTAs of a row group: five aligned source words shifted
+// into place, one 16-byte store per thread.  The columns that touch the reflected frame or the zero margin up to the pitch
+// (three on the left, a handful on the right) go to the last CTA, word by word and byte by byte, so that no warp of the
+// copy carries the slow path.
 constexpr int L0_ROWS = 4;
 __global__ void __launch_bounds__(128)
 k_pyr_level0(const uint8_t *__restrict__ src, size_t frame_stride, int spitch, uint8_t *__restrict__ pyr, const Geom *__restrict__ G) {
     const LevelGeom &g = G->lv[0];
-    const int q = blockIdx.x * 32 + (threadIdx.x & 31);                     // 16-byte chunk of the plane row
-    const int py = (blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5)) * L0_ROWS, b = blockIdx.z;
-    if (q * 16 >= g.pitch) return;
-    const int x0 = q * 16 - XOFF, rows = g.h + 2 * EDGE;
+    const int lane = threadIdx.x & 31, b = blockIdx.z;
+    const int py = (blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5)) * L0_ROWS;
+    const int rows = g.h + 2 * EDGE, nq = g.pitch / 16;
+    const int qL = (XOFF + 16) / 16;                               // first column with x0 >= 16
+    const int qR = max(qL, (g.w - 19 + XOFF) / 16 + 1);            // first column with x0 + 19 > w
     const uint8_t *sframe = src + (size_t)b * frame_stride;
-    uint8_t *plane = pyr + (size_t)b * G->pyr_frame + g.plane_off + (size_t)q * 16;
-    const bool inside = x0 >= 16 && x0 + 19 <= g.w;                          // the 20 bytes the aligned reads may touch
+    uint8_t *plane = pyr + (size_t)b * G->pyr_frame + g.plane_off;
+    if (blockIdx.x + 1 < gridDim.x) {
+        const int q = qL + blockIdx.x * 32 + lane;
+        if (q >= qR) return;
+        const int x0 = q * 16 - XOFF;
 #pragma unroll
-    for (int r = 0; r < L0_ROWS; r++) {
-        if (py + r >= rows) break;
-        const uint8_t *srow = sframe + (size_t)reflect101(py + r - EDGE, g.h) * spitch;
-        uint4 v;
-        if (inside) {
-            const uint8_t *p = srow + x0;
+        for (int r = 0; r < L0_ROWS; r++) {
+            if (py + r >= rows) break;
+            const uint8_t *p = sframe + (size_t)reflect101(py + r - EDGE, g.h) * spitch + x0;
             const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
             const uint32_t *w = reinterpret_cast<const uint32_t *>(p - ((uintptr_t)p & 3u));
             const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2), w3 = __ldg(w + 3), w4 = sh ? __ldg(w + 4) : 0u;
+            uint4 v;
             v.x = __funnelshift_r(w0, w1, sh); v.y = __funnelshift_r(w1, w2, sh);
             v.z = __funnelshift_r(w2, w3, sh); v.w = __funnelshift_r(w3, w4, sh);
-        } else {
-            uint32_t o[4] = {0, 0, 0, 0};
-#pragma unroll
-            for (int k = 0; k < 16; k++) {
-                const int x = x0 + k;
-                if (x >= -EDGE && x < g.w + EDGE) o[k >> 2] |= (uint32_t)srow[reflect101(x, g.w)] << (8 * (k & 3));
-            }
-            v = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4 *>(plane + (size_t)(py + r) * g.pitch + (size_t)q * 16) = v;
         }
-        *reinterpret_cast<uint4 *>(plane + (size_t)(py + r) * g.pitch) = v;
+    } else {
+        const int nwords = (qL + nq - qR) * 4;                     // words of the columns [0, qL) and [qR, nq)
+        for (int i = lane; i < nwords; i += 32) {
+            const int word = i < qL * 4 ? i : qR * 4 + (i - qL * 4);
+#pragma unroll
+            for (int r = 0; r < L0_ROWS; r++) {
+                if (py + r >= rows) break;
+                const uint8_t *srow = sframe + (size_t)reflect101(py + r - EDGE, g.h) * spitch;
+                uint32_t v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int x = word * 4 + k - XOFF;
+                    if (x >= -EDGE && x < g.w + EDGE) v |= (uint32_t)srow[reflect101(x, g.w)] << (8 * k);
+                }
+                *reinterpret_cast<uint32_t *>(plane + (size_t)(py + r) * g.pitch + (size_t)word * 4) = v;
+            }
+        }
     }
 }
 
@@ -862,10 +875,16 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
     const int x0 = wx * 4;
     if (x0 >= g.w) return;
     const int y0 = blockIdx.y * BLUR_ROWS, b = blockIdx.z;
-    const int k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    const uint32_t k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    // taps as byte vectors: horizontal pass = two 4-byte dot products (IDP4A) over bytes j+1..j+4 and j+5..j+8 of the window;
+    // vertical pass = 16-bit x 8-bit dot products (IDP2A) over row PAIRS (H[2m], H[2m+1]) packed into one register
+    const uint32_t KLO = k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), KHI = k2 | (k1 << 8) | (k0 << 16);
+    const uint32_t T01 = k0 | (k1 << 8), T23 = k2 | (k3 << 8), T21 = k2 | (k1 << 8), T10 = k1 | (k0 << 8), T32 = k3 | (k2 << 8),
+                   T12 = k1 | (k2 << 8), T_0 = k0 << 8;
     const uint8_t *src = pyr + (size_t)b * G->pyr_frame + g.interior_off + x0 - 4;
     uint8_t *dst = blur + (size_t)b * G->pyr_frame + g.interior_off + x0;
-    int h[7][4];
+    uint32_t P[4][4];        // ring of row pairs: P[m & 3][j] = H[2m][j] | H[2m+1][j] << 16   (H <= 255 * 256 fits 16 bits)
+    uint32_t hprev[4];       // H of the last even row, waiting for its partner
     // source rows -3.. and ..H+2 live in the 19-px frame.  Row indices are clamped (not predicated) and the next row's
     // words are requested before the current row is consumed; rows past H+2 only feed outputs that are never stored.
     uint32_t n0, n1, n2;
@@ -880,26 +899,45 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
             const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)min(y0 + r - 2, g.h + 2) * g.pitch);
             n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2);
         }
-        {
-            int bt[12];
+        uint32_t hc[4];      // horizontal pass of source row r for pixels x0 .. x0+3: pixel j reads window bytes j+1 .. j+7
+        hc[0] = __dp4a(__funnelshift_r(w1, w2, 8), KHI, __dp4a(__funnelshift_r(w0, w1, 8), KLO, 0u));
+        hc[1] = __dp4a(__funnelshift_r(w1, w2, 16), KHI, __dp4a(__funnelshift_r(w0, w1, 16), KLO, 0u));
+        hc[2] = __dp4a(__funnelshift_r(w1, w2, 24), KHI, __dp4a(__funnelshift_r(w0, w1, 24), KLO, 0u));
+        hc[3] = __dp4a(w2, KHI, __dp4a(w1, KLO, 0u));
+        if (r & 1) {
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                bt[i] = (w0 >> (8 * i)) & 0xff; bt[4 + i] = (w1 >> (8 * i)) & 0xff; bt[8 + i] = (w2 >> (8 * i)) & 0xff;
-            }
+            for (int j = 0; j < 4; j++) P[(r >> 1) & 3][j] = hprev[j] | (hc[j] << 16);
+        } else {
 #pragma unroll
-            for (int j = 0; j < 4; j++)                        // pixel x0+j reads bytes j+1 .. j+7 of the 12-byte window
-                h[r % 7][j] = k0 * (bt[j + 1] + bt[j + 7]) + k1 * (bt[j + 2] + bt[j + 6]) + k2 * (bt[j + 3] + bt[j + 5]) + k3 * bt[j + 4];
+            for (int j = 0; j < 4; j++) hprev[j] = hc[j];
         }
         if (r >= 6) {
-            const int yo = y0 + r - 6;
+            const int t = r - 6;                               // output row of the strip: source rows t .. t+6 = r
+            const int yo = y0 + t;
             if (yo < g.h) {
-                uint32_t o = 0;
+                uint32_t v[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    const int v = k0 * (h[(r - 6) % 7][j] + h[r % 7][j]) + k1 * (h[(r - 5) % 7][j] + h[(r - 1) % 7][j]) +
-                                  k2 * (h[(r - 4) % 7][j] + h[(r - 2) % 7][j]) + k3 * h[(r - 3) % 7][j];
-                    o |= (uint32_t)min((v + 32768) >> 16, 255) << (8 * j);
+                    if ((t & 1) == 0) {                        // rows (t,t+1) (t+2,t+3) (t+4,t+5) are pairs, row t+6 is hc
+                        const int m = t >> 1;
+                        v[j] = __dp2a_lo(P[m & 3][j], T01, 32768u + k0 * hc[j]);
+                        v[j] = __dp2a_lo(P[(m + 1) & 3][j], T23, v[j]);
+                        v[j] = __dp2a_lo(P[(m + 2) & 3][j], T21, v[j]);
+                    } else {                                   // row t is the upper half of pair (t-1,t); then three full pairs
+                        const int m = (t - 1) >> 1;
+                        v[j] = __dp2a_lo(P[m & 3][j], T_0, 32768u);
+                        v[j] = __dp2a_lo(P[(m + 1) & 3][j], T12, v[j]);
+                        v[j] = __dp2a_lo(P[(m + 2) & 3][j], T32, v[j]);
+                        v[j] = __dp2a_lo(P[(m + 3) & 3][j], T10, v[j]);
+                    }
                 }
+                // saturate_cast<uchar>((sum + 32768) >> 16) is byte 2 of each accumulator; the OpenCV 2.4 taps sum to 257, so a
+                // white patch can reach 257 there and is clamped (the 3.x/4.x taps sum to 256 and cannot exceed 255)
+                if (k2 == 49) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) v[j] = min(v[j], 0x00ffffffu);
+                }
+                const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
                 *reinterpret_cast<uint32_t *>(dst + (ptrdiff_t)yo * g.pitch) = o;
             }
         }
@@ -1423,7 +1461,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     prof_mark(ex, 1);
     {
         const LevelGeom &g = G.lv[0];
-        dim3 grid((g.pitch / 16 + 31) / 32, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
+        const int qL = (XOFF + 16) / 16, qR = std::max(qL, (g.w - 19 + XOFF) / 16 + 1);   // as in the kernel
+        dim3 grid((qR - qL + 31) / 32 + 1, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
         k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
         ex->launches++;
     }

@@ -143,3 +143,25 @@ def test_other_scale_factors(oracle, gpu_lib, scale, nlevels, w, h):
         assert np.array_equal(ex.pyramid_level(l, True), ref.pyramid_level(l, True)), l
     assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
     ex.close()
+
+
+def test_opencv24_blur_taps_and_saturation(oracle, gpu_lib):
+    """blur_taps=1 selects OpenCV 2.4's rounded-float Gaussian taps {18,34,49,55,49,34,18}.  They sum to 257, so a saturated
+    patch reaches 257 before saturate_cast: the image holds white blocks to exercise that clamp."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.synth import synth_frame
+    img = synth_frame(640, 480, 12).copy()
+    img[100:180, 200:330] = 255
+    img[300:420, 40:90] = 255
+    img[0:30, 500:640] = 255
+    for taps in (1, 0):
+        ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, blur_taps=taps)
+        ref = oracle.RefExtractor(1000, blur_taps=taps)
+        gk, gd = ex(img)
+        rk, rd = ref.extract(img)
+        for l in range(8):
+            assert np.array_equal(ex.blurred_level(l), ref.blurred_level(l)), (taps, l)
+        if taps == 1:
+            assert ref.blurred_level(0).max() == 255
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+        ex.close()
