@@ -101,7 +101,6 @@ __global__ void __launch_bounds__(ROWTAB_THREADS) k_stereo_rowtable(StereoArgs A
 }
 
 __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
-    __shared__ float s_IL[ST_WARPS][121];
     __shared__ uint8_t s_IR[ST_WARPS][11 * 24];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.y;
@@ -169,31 +168,46 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
     const uint8_t *imgL = A.pyrL + (size_t)(A.slotL0 + b) * A.GL->pyr_frame + gl.interior_off;
     const uint8_t *imgR = A.pyrR + (size_t)(A.slotR0 + b) * A.GR->pyr_frame + gr.interior_off;
     const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w), xr0 = (int)(scaleduR0 - L - w);
-    float *IL = s_IL[warp];
+    // The reference's L1 norm of (IL - IL_centre) - (IR - IR_centre) over the 11x11 window (ref :566-586) is a sum of small
+    // integers, exact in its fp32 arithmetic; here it is an integer SAD.  A lane owns window pixels lane, lane+32, ...; the 21
+    // columns of the right strip go through shared memory because every lane slides over 11 of them.
     uint8_t *IR = s_IR[warp];
-    for (int i = lane; i < 121; i += 32) {
-        const int y = i / 11, x = i - y * 11;
-        IL[i] = (float)imgL[(ptrdiff_t)(y0 + y) * gl.pitch + xl0 + x];
+    int aL[4], irb[4];
+#pragma unroll
+    for (int m = 0; m < 4; m++) {
+        const int i = lane + 32 * m, y = i / 11, x = i - y * 11;
+        irb[m] = y * 24 + x;
+        aL[m] = i < 121 ? (int)imgL[(ptrdiff_t)(y0 + y) * gl.pitch + xl0 + x] : 0;
     }
     for (int i = lane; i < 11 * 21; i += 32) {
         const int y = i / 21, x = i - y * 21;
         IR[y * 24 + x] = imgR[(ptrdiff_t)(y0 + y) * gr.pitch + xr0 + x];
     }
+    const int cL = __shfl_sync(0xffffffffu, aL[1], 60 - 32);   // window pixel 60 = (5, 5)
     __syncwarp();
-    const float cL = IL[5 * 11 + 5];
-    float dists[11];
+    uint32_t acc[11];
 #pragma unroll
     for (int k = 0; k < 11; k++) {   // incR = k - 5
-        const float cR = (float)IR[5 * 24 + k + 5];
-        float s = 0.f;
-        for (int i = lane; i < 121; i += 32) {
-            const int y = i / 11, x = i - y * 11;
-            s += fabsf((IL[i] - cL) - ((float)IR[y * 24 + x + k] - cR));   // exact small integers
-        }
+        const int cRL = (int)IR[5 * 24 + k + 5] - cL;           // |(IL - cL) - (IR - cR)| = |(IL + cR - cL) - IR|
+        uint32_t sum = 0;
 #pragma unroll
-        for (int sft = 16; sft > 0; sft >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sft);
-        dists[k] = s;
+        for (int m = 0; m < 4; m++)
+            if (m < 3 || lane < 121 - 96) sum = __sad(aL[m] + cRL, (int)IR[irb[m] + k], sum);
+        acc[k] = sum;
     }
+    // a window sums to at most 121 * 510 < 2^16: reduce two offsets per register
+    uint32_t pk[6];
+#pragma unroll
+    for (int k = 0; k < 5; k++) pk[k] = acc[2 * k] | (acc[2 * k + 1] << 16);
+    pk[5] = acc[10];
+#pragma unroll
+    for (int sft = 16; sft > 0; sft >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) pk[k] += __shfl_xor_sync(0xffffffffu, pk[k], sft);
+    }
+    float dists[11];
+#pragma unroll
+    for (int k = 0; k < 11; k++) dists[k] = (float)((pk[k >> 1] >> (16 * (k & 1))) & 0xffffu);
     int bestS = 0x7fffffff, bestinc = 0;
 #pragma unroll
     for (int k = 0; k < 11; k++)
