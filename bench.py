@@ -343,7 +343,7 @@ def run_ours(args):
         l, r = pairs[b % len(pairs)]
         hv[b] = l
         hv[B + b] = r
-    lanes = [Lane(torch, dev, local, B, host), Lane(torch, dev, local, B, host)]   # two lanes: copies overlap compute in the e2e arm
+    lanes = [Lane(torch, dev, local, B, host) for _ in range(max(2, args.lanes))]   # lanes: copies overlap compute in the e2e arm
     A = lanes[0]
     ex, stream = A.ex, A.stream
     d_img = host.to(dev)
@@ -391,24 +391,28 @@ def run_ours(args):
     ex.check()
     value = NF * args.steps * world / (ms * 1e-3)
 
-    # ---- end-to-end arm: every step copies its frames from pinned host memory and its results back.  Two lanes
-    # alternate so that one lane's PCIe copies overlap the other lane's kernels; a lane is synchronised before reuse
-    # (its host results are consumed), so at most two steps are in flight.
-    for i in range(4):
-        lanes[i % 2].stream.synchronize()
-        lanes[i % 2].enqueue_e2e()
-    e2e_steps = max(4, args.steps)
+    # ---- end-to-end arm: every step copies its frames from pinned host memory and its results back.  The lanes
+    # take turns so that one lane's PCIe copies overlap the other lanes' kernels; a lane is synchronised before reuse
+    # (its host results are consumed), so at most --lanes steps are in flight.
+    NL = len(lanes)
+    for i in range(2 * NL):
+        lanes[i % NL].stream.synchronize()
+        lanes[i % NL].enqueue_e2e()
+    e2e_steps = max(2 * NL, args.steps)
     barrier()
-    s2, e2, join = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event()
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     s2.record(lanes[0].stream)
-    lanes[1].stream.wait_event(s2)
+    for ln in lanes[1:]:
+        ln.stream.wait_event(s2)
     for i in range(e2e_steps):
-        ln = lanes[i % 2]
+        ln = lanes[i % NL]
         ln.stream.synchronize()
         ln.enqueue_e2e()
-    join.record(lanes[1].stream)
-    lanes[0].stream.wait_event(join)
+    for ln in lanes[1:]:
+        join = torch.cuda.Event()
+        join.record(ln.stream)
+        lanes[0].stream.wait_event(join)
     e2.record(lanes[0].stream)
     e2.synchronize()
     wall_e2e = time.perf_counter() - t0
@@ -476,7 +480,7 @@ def run_ours(args):
         "config": workload_config(B),
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "wall_s": wall_e2e, "steps": e2e_steps,
-                "pipeline": "two extractor handles alternate; a handle is synchronised before reuse"},
+                "pipeline": f"{NL} extractor handles take turns; a handle is synchronised before reuse"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -503,6 +507,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=144, help="stereo pairs per step per GPU")
+    ap.add_argument("--lanes", type=int, default=2, help="e2e arm: steps in flight (each lane = one extractor handle + stream + buffers)")
     ap.add_argument("--distinct", type=int, default=16, help="distinct synthetic pairs tiled into the batch")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
     ap.add_argument("--db-rows", type=int, default=8_000_000, help="descriptor-database rows per GPU for the Hamming leg (256 MB)")
