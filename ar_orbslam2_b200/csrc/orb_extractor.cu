@@ -218,7 +218,7 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
 //      (VIMNMX.S16x2) and leaves a flag word; a block scan then compacts the H and the L survivors into two lists;
 //   3. survivors get the exact arc strength on dense warps, two same-type survivors per thread in the two 16-bit
 //      lanes (VIMNMX3.S16x2); a pixel on both lists takes the larger of the two;
-//   4. threshold + NMS; candidates appended to the level's list.
+//   4. threshold + NMS; what passes is appended to the level's list on the spot (warp-aggregated atomic).
 // The cell runs at iniThFAST first and repeats 2-4 at minThFAST only when it came up empty (ref :775-784): a pixel
 // that fails the compass test at t has V <= t, so it can neither be a corner at t nor suppress one.
 // ------------------------------------------------------------------------------------------
@@ -293,8 +293,7 @@ __global__ void __launch_bounds__(FAST_T)
 k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
              int *__restrict__ err) {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ int s_nkp, s_base;
-    __shared__ int s_wsum[FAST_T / 32];
+    __shared__ int s_nkp, s_cnt;
 
     uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
     uint8_t *vmap = fsm + g.off_vmap;                                   // computed region + 1 px apron
@@ -328,7 +327,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         asm volatile("cp.async.commit_group;");
         uint4 *vq = reinterpret_cast<uint4 *>(vmap);
         for (int t = tid; t < ((ch + 2) * VPB + 15) / 16; t += FAST_T) vq[t] = make_uint4(0, 0, 0, 0);
-        if (tid == 0) s_nkp = 0;
+        if (tid == 0) { s_nkp = 0; s_cnt = 0; }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
@@ -368,25 +367,19 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
             }
         }
         {
-            // block-wide exclusive scan of the per-thread counts, then every thread appends its survivors
+            // list positions: a warp scan of the per-thread counts and one shared-memory atomic per warp for its range (both
+            // counters in one word, H low / L high); the order of the lists is irrelevant
             int incl = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int t = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += t;
             }
-            if (lane == 31) s_wsum[tid >> 5] = incl;
-            __syncthreads();
-            int wbase = 0, total = 0;
-#pragma unroll
-            for (int w = 0; w < FAST_T / 32; w++) {
-                const int v = s_wsum[w];
-                if (w < (tid >> 5)) wbase += v;
-                total += v;
-            }
+            int wbase = 0;
+            if (lane == 31 && incl) wbase = atomicAdd(&s_cnt, incl);
+            wbase = __shfl_sync(0xffffffffu, wbase, 31);
             const int pos = wbase + incl - cnt;
             int pH = pos & 0xffff, pL = pos >> 16;
-            nH = total & 0xffff; nL = total >> 16;
             for (int u = tid; u < nunits; u += FAST_T) {
                 const uint32_t f = flags[u];
                 if (!f) continue;
@@ -400,6 +393,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
             }
         }
         __syncthreads();
+        nH = s_cnt & 0xffff; nL = s_cnt >> 16;
 
         // ---- 3. exact arc strength of the survivors, two per thread
         for (int s = tid; 2 * s < nH; s += FAST_T) {
@@ -420,46 +414,47 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         }
         __syncthreads();
 
-        // ---- 4. threshold + NMS over both lists (a pixel on both is judged on the H list)
-        int mine = 0;
-        for (int s = tid; s < nH + nL; s += FAST_T) {
-            uint16_t *e = s < nH ? &survH[s] : &survL[s - nH];
-            const int code = *e;
-            if (code & 0x4000) continue;
-            const uint8_t *v = &vmap[((code >> 7) + 1) * VPB + (code & 127) + 1];
-            const int V = v[0];
-            if (V > thr && V > v[-1] && V > v[1] && V > v[-VPB - 1] && V > v[-VPB] && V > v[-VPB + 1] &&
-                V > v[VPB - 1] && V > v[VPB] && V > v[VPB + 1]) {
-                *e = (uint16_t)(code | 0x8000);
-                mine++;
+        // ---- 4. threshold + NMS over both lists (a pixel on both is judged on the H list).  Whatever passes is final -- a
+        // cell is only repeated when NOTHING passed -- so it goes straight to the level's candidate list: one global atomic per
+        // warp and step for the range, window-relative coordinates (ref :789-790: ROI x + j*wCell).
+        bool found = false;
+        for (int s0 = 0; s0 < nH + nL; s0 += FAST_T) {
+            const int s = s0 + tid;
+            bool pass = false;
+            int code = 0, V = 0;
+            if (s < nH + nL) {
+                code = s < nH ? survH[s] : survL[s - nH];
+                if (!(code & 0x4000)) {
+                    const uint8_t *v = &vmap[((code >> 7) + 1) * VPB + (code & 127) + 1];
+                    V = v[0];
+                    pass = V > thr && V > v[-1] && V > v[1] && V > v[-VPB - 1] && V > v[-VPB] && V > v[-VPB + 1] &&
+                           V > v[VPB - 1] && V > v[VPB] && V > v[VPB + 1];
+                }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, pass);
+            if (bal) {
+                found = true;
+                int base = 0;
+                if (lane == 0) base = (int)atomicAdd(cand_count + (size_t)b * g.nlevels + level, (uint32_t)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (pass) {
+                    const int slot = base + __popc(bal & ((1u << lane) - 1u));
+                    if (slot < g.cand_cap) {
+                        const uint32_t wx = (code & 127) + 3 + cj * g.wCell, wy = (code >> 7) + 3 + ci * g.hCell;
+                        cand[(size_t)b * g.cand_frame + g.cand_off + slot] = wx | (wy << 12) | ((uint32_t)(V - 1) << 24);
+                    } else {
+                        atomicOr(err, ERRF_CAND_OVERFLOW);
+                    }
+                }
             }
         }
-        if (mine) atomicAdd(&s_nkp, mine);
+        if (found && lane == 0) s_nkp = 1;
+        if (thr == g.min_th) break;
         __syncthreads();
-        if (s_nkp > 0 || thr == g.min_th) break;
+        if (s_nkp) break;
         thr = g.min_th;   // empty cell: once more at the lower threshold (ref :780-784)
-    }
-    const int nkp = s_nkp;
-    if (nkp == 0) return;
-    uint32_t *cnt = cand_count + (size_t)b * g.nlevels + level;
-    if (tid == 0) s_base = (int)atomicAdd(cnt, (uint32_t)nkp);
-    __syncthreads();
-    if (tid == 0) s_nkp = 0;
-    __syncthreads();
-    uint32_t *out = cand + (size_t)b * g.cand_frame + g.cand_off;
-    for (int s = tid; s < nH + nL; s += FAST_T) {
-        const int code = s < nH ? survH[s] : survL[s - nH];
-        if (!(code & 0x8000)) continue;
-        const int y = (code >> 7) & 127, x = code & 127;
-        const int V = vmap[(y + 1) * VPB + x + 1];
-        const int slot = s_base + atomicAdd(&s_nkp, 1);
-        if (slot < g.cand_cap) {
-            // window-relative coordinates (ref :789-790): ROI x + j*wCell
-            const uint32_t wx = x + 3 + cj * g.wCell, wy = y + 3 + ci * g.hCell;
-            out[slot] = wx | (wy << 12) | ((uint32_t)(V - 1) << 24);
-        } else {
-            atomicOr(err, ERRF_CAND_OVERFLOW);
-        }
+        if (tid == 0) s_cnt = 0;
+        __syncthreads();
     }
 }
 
