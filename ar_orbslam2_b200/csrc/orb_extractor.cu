@@ -527,12 +527,12 @@ __device__ __forceinline__ int quadrant_of(int x, int y, int nx0, int ny0, int n
 __global__ void __launch_bounds__(OCT_THREADS)
 k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const uint32_t *__restrict__ cand_count,
          uint16_t *__restrict__ node_of_pool, Kept *__restrict__ kept, uint32_t *__restrict__ kept_count,
-         int *__restrict__ err) {
+         int *__restrict__ err, int level0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int warp_tot[33];
     __shared__ int s_nexpand, s_jstar, s_phase, s_done;
 
-    const int level = blockIdx.x, b = blockIdx.y;
+    const int level = level0 + blockIdx.x, b = blockIdx.y;
     const LevelGeom &g = G->lv[level];
     const int MAXN = G->max_nodes;
     const int tid = threadIdx.x;
@@ -1180,6 +1180,11 @@ static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
     for (auto &e : ex->ev) if (e) cudaEventDestroy(e);
+    for (auto &e : ex->ev_lvl) if (e) cudaEventDestroy(e);
+    if (ex->ev_fast) cudaEventDestroy(ex->ev_fast);
+    if (ex->ev_blur) cudaEventDestroy(ex->ev_blur);
+    if (ex->s_fast) cudaStreamDestroy(ex->s_fast);
+    if (ex->s_blur) cudaStreamDestroy(ex->s_blur);
     if (ex->stream) cudaStreamDestroy(ex->stream);
 }
 
@@ -1312,6 +1317,12 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     if (rc != ORB_OK) { delete ex; return rc; }
 #define TRY_ALLOC(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error("%s -> %s", #expr, cudaGetErrorString(_e)); free_all(ex); delete ex; return ORB_ERR_CUDA; } } while (0)
     TRY_ALLOC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
+    TRY_ALLOC(cudaStreamCreateWithFlags(&ex->s_fast, cudaStreamNonBlocking));
+    TRY_ALLOC(cudaStreamCreateWithFlags(&ex->s_blur, cudaStreamNonBlocking));
+    for (int l = 0; l < params->nlevels; l++) TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_lvl[l], cudaEventDisableTiming));
+    TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_fast, cudaEventDisableTiming));
+    TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_blur, cudaEventDisableTiming));
+    ex->overlap = getenv("ORBGPU_SERIAL") == nullptr;
     TRY_ALLOC(cudaMemcpyToSymbol(c_umax, ex->umax, sizeof(ex->umax)));
     TRY_ALLOC(cudaMalloc(&ex->d_geom, sizeof(Geom)));
     // sizes below are monotone in the image size except the kept pool (aspect dependent): bound it
@@ -1453,17 +1464,13 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
     ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
 
-    prof_mark(ex, 1);
-    {
-        const LevelGeom &g = G.lv[0];
-        const int qL = (XOFF + 16) / 16, qR = std::max(qL, (g.w - 19 + XOFF) / 16 + 1);   // as in the kernel
-        dim3 grid((qR - qL + 31) / 32 + 1, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
-        k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
-        ex->launches++;
-    }
-    for (int l = 1; l < G.nlevels; l++) {
+    auto launch_pyr = [&](int l) {
         const LevelGeom &g = G.lv[l];
-        if (g.fast_resize) {
+        if (l == 0) {
+            const int qL = (XOFF + 16) / 16, qR = std::max(qL, (g.w - 19 + XOFF) / 16 + 1);   // as in the kernel
+            dim3 grid((qR - qL + 31) / 32 + 1, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
+            k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
+        } else if (g.fast_resize) {
             const int nw = g.pitch / 4;
             int bx = 128;   // CTA width that wastes the fewest threads on this level's row
             for (int c = 96; c >= 32; c -= 32)
@@ -1475,9 +1482,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             k_pyr_resize_generic<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
         }
         ex->launches++;
-    }
-    prof_mark(ex, 2);
-    for (int l = 0; l < G.nlevels; l++) {
+    };
+    auto launch_fast = [&](int l, cudaStream_t s) {
         const LevelGeom &g = G.lv[l];
         FastLevel fl;
         fl.level = l; fl.nlevels = G.nlevels; fl.ini_th = G.ini_th; fl.min_th = G.min_th;
@@ -1485,19 +1491,45 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         fl.cand_off = g.cand_off; fl.cand_cap = g.cand_cap; fl.cand_frame = G.cand_frame;
         fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
         const size_t smem = fast_smem_layout(fl);
-        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, st>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
+        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
         ex->launches++;
-    }
-    prof_mark(ex, 3);
-    k_octree<<<dim3(G.nlevels, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), st>>>(
-        ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err);
-    ex->launches++;
-    prof_mark(ex, 4);
-    for (int l = 0; l < G.nlevels; l++) {
+    };
+    auto launch_blur = [&](int l, cudaStream_t s) {
         const LevelGeom &g = G.lv[l];
         dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, batch);
-        k_blur_planes<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_blur, ex->d_geom, l);
+        k_blur_planes<<<grid, 128, 0, s>>>(ex->d_pyr, ex->d_blur, ex->d_geom, l);
         ex->launches++;
+    };
+    auto launch_octree = [&](int l0, int nl, cudaStream_t s) {
+        k_octree<<<dim3(nl, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), s>>>(
+            ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err, l0);
+        ex->launches++;
+    };
+    if (ex->overlap && !ex->profiling) {
+        // level l's FAST cells and blur depend only on level l: they go to two side streams behind an event per level and
+        // overlap the rest of the resize cascade (and each other); the handle's stream joins them where their results are read
+        for (int l = 0; l < G.nlevels; l++) {
+            launch_pyr(l);
+            ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
+            ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
+            launch_fast(l, ex->s_fast);
+            ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
+            launch_blur(l, ex->s_blur);
+        }
+        ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
+        ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));
+        ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fast, 0));
+        launch_octree(0, G.nlevels, st);   // (one launch per level on a side stream was measured: no gain)
+        ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
+    } else {
+        prof_mark(ex, 1);
+        for (int l = 0; l < G.nlevels; l++) launch_pyr(l);
+        prof_mark(ex, 2);
+        for (int l = 0; l < G.nlevels; l++) launch_fast(l, st);
+        prof_mark(ex, 3);
+        launch_octree(0, G.nlevels, st);
+        prof_mark(ex, 4);
+        for (int l = 0; l < G.nlevels; l++) launch_blur(l, st);
     }
     k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
         ex->d_pyr, ex->d_blur, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);

@@ -93,5 +93,10 @@ struct orb_extractor {
     double stage_ms[ORB_N_STAGES] = {};
     int64_t stage_calls = 0;
     bool ev_pending = false;
+    // side streams: FAST and the blur of a level start as soon as that level of the pyramid exists and run beside the
+    // remaining resize launches; both are joined back into `stream` before the quadtree / the descriptors
+    cudaStream_t s_fast = nullptr, s_blur = nullptr;
+    cudaEvent_t ev_lvl[ORB_MAX_LEVELS] = {}, ev_fast = nullptr, ev_blur = nullptr;
+    bool overlap = true;               // off while per-stage profiling is on (stage times need a serial schedule)
 };
 

@@ -297,10 +297,10 @@ class Lane:
         self.mb = float(np.float32(MBF) / np.float32(FX))
         self.torch = torch
 
-    def step_device(self, src):
+    def step_device(self, src, d=None):
         """left+right extraction of B pairs (frames 0..B-1 left, B..2B-1 right) + ComputeStereoMatches, all on the device."""
         from ar_orbslam2_b200.stereo import stereo_match_batch_device
-        d, B, cap = self.d, self.B, self.cap
+        d, B, cap = d or self.d, self.B, self.cap
         self.ex.extract_batch_device(src.data_ptr(), self.NF, W, H, W, W * H, d["kps"].data_ptr(), d["desc"].data_ptr(), cap,
                                      d["n"].data_ptr())
         stereo_match_batch_device(self.ex, 0, self.ex, B, B, d["kps"].data_ptr(), d["desc"].data_ptr(), d["n"].data_ptr(),
@@ -317,6 +317,46 @@ class Lane:
 
     def d2h_bytes(self):
         return sum(t.numel() * t.element_size() for t in self.h.values())
+
+
+class Pipe:
+    """End-to-end pipeline around ONE extractor handle: two copy streams feed it.  Frames of step k+1 travel host->device
+    and results of step k-1 travel device->host while step k computes (inputs and outputs double-buffered); the compute
+    stream never shares the SMs with a second handle's kernels."""
+
+    def __init__(self, torch, dev, lane, host):
+        self.torch, self.lane, self.host = torch, lane, host
+        self.sin, self.sout = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self.d_in = [torch.empty_like(lane.d_in) for _ in range(2)]
+        self.d = [{k: torch.zeros_like(v) for k, v in lane.d.items()} for _ in range(2)]
+        self.h = [{k: torch.zeros(tuple(v.shape), dtype=v.dtype).pin_memory() for k, v in lane.d.items()} for _ in range(2)]
+        ev = lambda: [torch.cuda.Event(), torch.cuda.Event()]
+        self.in_ready, self.in_free, self.out_ready, self.out_free = ev(), ev(), ev(), ev()
+        self.used = [False, False]
+
+    def enqueue(self, k):
+        t, s, cs = self.torch, k % 2, self.lane.stream
+        if self.used[s]:
+            self.sin.wait_event(self.in_free[s])          # the kernels of step k-2 have read this input buffer
+        with t.cuda.stream(self.sin):
+            self.d_in[s].copy_(self.host, non_blocking=True)
+            self.in_ready[s].record(self.sin)
+        cs.wait_event(self.in_ready[s])
+        if self.used[s]:
+            cs.wait_event(self.out_free[s])               # the results of step k-2 have left this output buffer
+        self.lane.step_device(self.d_in[s], self.d[s])
+        self.in_free[s].record(cs)
+        self.out_ready[s].record(cs)
+        self.sout.wait_event(self.out_ready[s])
+        with t.cuda.stream(self.sout):
+            for key in self.d[s]:
+                self.h[s][key].copy_(self.d[s][key], non_blocking=True)
+            self.out_free[s].record(self.sout)
+        self.used[s] = True
+
+    def consume(self, k):
+        """Host side: wait until the results of step k are in pinned memory."""
+        self.out_free[k % 2].synchronize()
 
 
 def run_ours(args):
@@ -368,7 +408,6 @@ def run_ours(args):
     n_kp = int(A.d["n"].sum().item())
     n_matched = int(A.d["nm"].sum().item())
     L = _lib.lib()
-    L.orb_extractor_set_profiling(ex._h, 1)
     launches0 = ex.launch_count
     sampler = ClockSampler(local)
     if rank == 0:
@@ -384,44 +423,79 @@ def run_ours(args):
     ms = reduce_max(s.elapsed_time(e))
     clocks = sampler.stop() if rank == 0 else None
     launches = ex.launch_count - launches0
+    ex.check()
+    value = NF * args.steps * world / (ms * 1e-3)
+    # per-stage device times: a separate, untimed pass with the library's stage events on.  Profiling serialises the
+    # schedule (the timed pass above overlaps each level's FAST and blur with the rest of the resize cascade on side
+    # streams), so the stage times add up to more than ms_per_step.
+    L.orb_extractor_set_profiling(ex._h, 1)
+    sp, ep = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sp.record(stream)
+    for _ in range(args.steps):
+        A.step_device(d_img)
+    ep.record(stream)
+    ep.synchronize()
+    ms_serial = sp.elapsed_time(ep)
     stage_ms = (C.c_double * 6)()
     calls = C.c_int64()
     L.orb_extractor_stage_times(ex._h, stage_ms, C.byref(calls))
     L.orb_extractor_set_profiling(ex._h, 0)
     ex.check()
-    value = NF * args.steps * world / (ms * 1e-3)
 
-    # ---- end-to-end arm: every step copies its frames from pinned host memory and its results back.  The lanes
-    # take turns so that one lane's PCIe copies overlap the other lanes' kernels; a lane is synchronised before reuse
-    # (its host results are consumed), so at most --lanes steps are in flight.
-    NL = len(lanes)
-    for i in range(2 * NL):
-        lanes[i % NL].stream.synchronize()
-        lanes[i % NL].enqueue_e2e()
-    e2e_steps = max(2 * NL, args.steps)
-    barrier()
+    # ---- end-to-end arm: every step copies its frames from pinned host memory and its results back to pinned host memory.
+    # "pipe" (default): one handle computes, two copy streams move step k+1 in and step k-1 out meanwhile.
+    # "lanes": --lanes handles take turns, each doing copy-in, kernels, copy-out on its own stream.
+    # Either way a buffer set is synchronised (its host results are consumed) before it is reused.
+    e2e_steps = max(6, args.steps)
     s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0 = time.perf_counter()
-    s2.record(lanes[0].stream)
-    for ln in lanes[1:]:
-        ln.stream.wait_event(s2)
-    for i in range(e2e_steps):
-        ln = lanes[i % NL]
-        ln.stream.synchronize()
-        ln.enqueue_e2e()
-    for ln in lanes[1:]:
-        join = torch.cuda.Event()
-        join.record(ln.stream)
-        lanes[0].stream.wait_event(join)
-    e2.record(lanes[0].stream)
-    e2.synchronize()
-    wall_e2e = time.perf_counter() - t0
-    barrier()
+    if args.e2e == "pipe":
+        pipe = Pipe(torch, dev, A, host)
+        for k in range(4):
+            if k >= 2:
+                pipe.consume(k - 2)
+            pipe.enqueue(k)
+        barrier()
+        t0 = time.perf_counter()
+        s2.record(pipe.sin)
+        for k in range(e2e_steps):
+            if k >= 2:
+                pipe.consume(k - 2)
+            pipe.enqueue(k)
+        e2.record(pipe.sout)
+        e2.synchronize()
+        wall_e2e = time.perf_counter() - t0
+        barrier()
+        results = pipe.h
+        pipeline = "one extractor handle; frames of step k+1 in and results of step k-1 out on two copy streams while step k computes"
+    else:
+        NL = len(lanes)
+        for i in range(2 * NL):
+            lanes[i % NL].stream.synchronize()
+            lanes[i % NL].enqueue_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        s2.record(lanes[0].stream)
+        for ln in lanes[1:]:
+            ln.stream.wait_event(s2)
+        for i in range(e2e_steps):
+            ln = lanes[i % NL]
+            ln.stream.synchronize()
+            ln.enqueue_e2e()
+        for ln in lanes[1:]:
+            join = torch.cuda.Event()
+            join.record(ln.stream)
+            lanes[0].stream.wait_event(join)
+        e2.record(lanes[0].stream)
+        e2.synchronize()
+        wall_e2e = time.perf_counter() - t0
+        barrier()
+        results = [ln.h for ln in lanes]
+        pipeline = f"{NL} extractor handles take turns; a handle is synchronised before reuse"
     ms_e2e = reduce_max(s2.elapsed_time(e2))
     e2e_value = NF * e2e_steps * world / (ms_e2e * 1e-3)
     h2d, d2h = host.numel(), A.d2h_bytes()
-    for ln in lanes:
-        assert int(ln.h["n"].sum().item()) == n_kp, "e2e arm produced different keypoint counts"
+    for r in results:
+        assert int(r["n"].sum().item()) == n_kp, "e2e arm produced different keypoint counts"
     # the handles stay open until interpreter exit (ar_orbslam2_b200._lib closes them from atexit): torch's pinned-memory
     # allocator records an event on every stream a pinned buffer was copied on when that buffer is freed, so the
     # library streams must outlive the buffers.
@@ -480,7 +554,7 @@ def run_ours(args):
         "config": workload_config(B),
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "wall_s": wall_e2e, "steps": e2e_steps,
-                "pipeline": f"{NL} extractor handles take turns; a handle is synchronised before reuse"},
+                "pipeline": pipeline},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -489,7 +563,8 @@ def run_ours(args):
         "roofline_step": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak,
                           "algorithmic_bytes_per_frame": step_alg_bytes, "formula": "P*(1+2S)+60N (SURVEY 8d)"},
         "stage_ms_per_step": dict({STAGES[i]: per_call[i] for i in range(6)},
-                                  stereo_match=ms / args.steps - sum(per_call)),
+                                  stereo_match=ms_serial / args.steps - sum(per_call)),
+        "ms_per_step_serial_schedule": ms_serial / args.steps,
         "keypoints_per_frame": kp_per_frame, "stereo_matches_per_pair": n_matched / B,
         "extra": extra,
         "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": cores, "kind": "port",
@@ -507,6 +582,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=144, help="stereo pairs per step per GPU")
+    ap.add_argument("--e2e", default="pipe", choices=["pipe", "lanes"], help="end-to-end arm: copy streams around one handle, or handles taking turns")
     ap.add_argument("--lanes", type=int, default=2, help="e2e arm: steps in flight (each lane = one extractor handle + stream + buffers)")
     ap.add_argument("--distinct", type=int, default=16, help="distinct synthetic pairs tiled into the batch")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
