@@ -11,7 +11,7 @@ constexpr int XOFF = 32;                   // interior column 0 sits at byte 32 
 constexpr int MAX_INI = 64;                // max initial quadtree nodes (image aspect ratio)
 constexpr int FAST_TILE_MAX = 72;          // cell (<60) + 6 halo, rounded up
 constexpr int FAST_THREADS = 64;           // measured 32..256 on B200: 32-128 within 5%, 256 is 1.8x slower (per-warp fixed costs)
-constexpr int OCT_THREADS = 512;
+constexpr int OCT_THREADS = 256;           // measured 128 / 256 / 512 / 1024: 0.33 / 0.23 / 0.25 / 0.50 ms per 288 frames
 constexpr int DESC_WARPS = 8;
 
 enum { ERRF_CAND_OVERFLOW = 1, ERRF_NODE_OVERFLOW = 2, ERRF_OUT_OVERFLOW = 4 };
