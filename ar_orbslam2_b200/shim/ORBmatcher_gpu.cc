@@ -176,6 +176,124 @@ int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatc
     return nmatches;
 }
 
+// Relocalisation refinement (Tracking::Relocalization): project the key frame's map points with the current pose and search
+// the current frame; any map point already in the frame blocks its feature (:1544-1545).
+int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const std::set<MapPoint *> &sAlreadyFound, float th, int ORBdist,
+                       bool mbCheckOrientation) {
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat Ow = -Rcw.t() * tcw;
+    const std::vector<MapPoint *> vpMPs = pKF->GetMapPointMatches();
+    const int n = (int)vpMPs.size();
+    if (n == 0 || CurrentFrame.N == 0) return 0;
+    const int nlev = (int)CurrentFrame.mvScaleFactors.size();
+    std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32 + 32, 0), claimed(CurrentFrame.N, 0);
+    std::vector<float> u(n, 0.f), v(n, 0.f), radius(n, 0.f), angle(n, 0.f);
+    std::vector<int32_t> minL(n, 0), maxL(n, 0), assigned(CurrentFrame.N);
+    for (int i = 0; i < n; i++) {                                      // :1491-1531
+        MapPoint *pMP = vpMPs[i];
+        angle[i] = pKF->mvKeysUn[i].angle;
+        if (!pMP) continue;
+        if (pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+        cv::Mat x3Dw = pMP->GetWorldPos();
+        cv::Mat x3Dc = Rcw * x3Dw + tcw;
+        const float xc = x3Dc.at<float>(0);
+        const float yc = x3Dc.at<float>(1);
+        const float invzc = 1.0 / x3Dc.at<float>(2);
+        const float uu = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        const float vv = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (uu < CurrentFrame.mnMinX || uu > CurrentFrame.mnMaxX) continue;
+        if (vv < CurrentFrame.mnMinY || vv > CurrentFrame.mnMaxY) continue;
+        cv::Mat PO = x3Dw - Ow;
+        float dist3D = cv::norm(PO);
+        const float maxDistance = pMP->GetMaxDistanceInvariance();
+        const float minDistance = pMP->GetMinDistanceInvariance();
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        int nPredictedLevel = pMP->PredictScale(dist3D, CurrentFrame.mfLogScaleFactor);
+        if (nPredictedLevel < 0 || nPredictedLevel >= nlev) continue;   // the reference indexes mvScaleFactors out of range here
+        valid[i] = 1; u[i] = uu; v[i] = vv;
+        radius[i] = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+        minL[i] = nPredictedLevel - 1; maxL[i] = nPredictedLevel + 1;   // GetFeaturesInArea's own level arguments (:1533)
+        cv::Mat d = pMP->GetDescriptor();
+        std::memcpy(&desc[(size_t)i * 32], d.ptr(0), 32);
+    }
+    for (int i = 0; i < CurrentFrame.N; i++) claimed[i] = CurrentFrame.mvpMapPoints[i] != NULL;   // :1544-1545
+    GpuFrame g(CurrentFrame.mvKeysUn, CurrentFrame.mDescriptors, CurrentFrame.mvuRight, CurrentFrame.mvScaleFactors);
+    orb_window_queries Q;
+    std::memset(&Q, 0, sizeof(Q));
+    Q.n = n; Q.valid = valid.data(); Q.x = u.data(); Q.y = v.data(); Q.radius = radius.data(); Q.min_level = minL.data();
+    Q.max_level = maxL.data(); Q.strict_levels = 0; Q.descriptors = desc.data(); Q.angle = angle.data();
+    int nmatches = 0;
+    Check(orb_search_windowed(g.h, &Q, claimed.data(), ORB_SELECT_BEST, ORBdist, 0.f, mbCheckOrientation, assigned.data(), &nmatches),
+          "orb_search_windowed");
+    for (int i = 0; i < CurrentFrame.N; i++) {
+        if (assigned[i] >= 0) CurrentFrame.mvpMapPoints[i] = vpMPs[assigned[i]];             // :1559
+        else if (assigned[i] == -2) CurrentFrame.mvpMapPoints[i] = static_cast<MapPoint *>(NULL);   // :1594
+    }
+    return nmatches;
+}
+
+// Loop closing (LoopClosing::ComputeSim3 / SearchAndFuse): project the loop candidates' points with the Sim3 and search the
+// key frame; a feature that already holds a match is skipped (:374-375).
+int SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *> &vpPoints, std::vector<MapPoint *> &vpMatched, int th) {
+    const float &fx = pKF->fx;
+    const float &fy = pKF->fy;
+    const float &cx = pKF->cx;
+    const float &cy = pKF->cy;
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);                  // :298-303
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    std::set<MapPoint *> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(static_cast<MapPoint *>(NULL));
+    const int n = (int)vpPoints.size();
+    if (n == 0 || pKF->N == 0) return 0;
+    const int nlev = (int)pKF->mvScaleFactors.size();
+    std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32 + 32, 0), claimed(pKF->N, 0);
+    std::vector<float> u(n, 0.f), v(n, 0.f), radius(n, 0.f);
+    std::vector<int32_t> minL(n, 0), maxL(n, 0), assigned(pKF->N);
+    for (int iMP = 0; iMP < n; iMP++) {                                // :311-360
+        MapPoint *pMP = vpPoints[iMP];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0) continue;
+        const float invz = 1 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz;
+        const float y = p3Dc.at<float>(1) * invz;
+        const float uu = fx * x + cx;
+        const float vv = fy * y + cy;
+        if (!pKF->IsInImage(uu, vv)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance();
+        const float minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist = cv::norm(PO);
+        if (dist < minDistance || dist > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist) continue;
+        int nPredictedLevel = pMP->PredictScale(dist, pKF->mfLogScaleFactor);
+        if (nPredictedLevel < 0 || nPredictedLevel >= nlev) continue;
+        valid[iMP] = 1; u[iMP] = uu; v[iMP] = vv;
+        radius[iMP] = th * pKF->mvScaleFactors[nPredictedLevel];
+        minL[iMP] = nPredictedLevel - 1; maxL[iMP] = nPredictedLevel;   // the in-loop filter of :378-381
+        cv::Mat d = pMP->GetDescriptor();
+        std::memcpy(&desc[(size_t)iMP * 32], d.ptr(0), 32);
+    }
+    for (int i = 0; i < pKF->N; i++) claimed[i] = vpMatched[i] != NULL;
+    GpuFrame g(pKF->mvKeysUn, pKF->mDescriptors, pKF->mvuRight, pKF->mvScaleFactors, true);
+    orb_window_queries Q;
+    std::memset(&Q, 0, sizeof(Q));
+    Q.n = n; Q.valid = valid.data(); Q.x = u.data(); Q.y = v.data(); Q.radius = radius.data(); Q.min_level = minL.data();
+    Q.max_level = maxL.data(); Q.strict_levels = 1; Q.descriptors = desc.data();
+    int nmatches = 0;
+    Check(orb_search_windowed(g.h, &Q, claimed.data(), ORB_SELECT_BEST, 50 /* TH_LOW */, 0.f, 0, assigned.data(), &nmatches),
+          "orb_search_windowed");
+    for (int i = 0; i < pKF->N; i++)
+        if (assigned[i] >= 0) vpMatched[i] = vpPoints[assigned[i]];   // :396
+    return nmatches;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // LocalMapping / LoopClosing matchers.  The candidate loops run on the GPU (orb_search_window_best,
 // orb_search_for_triangulation); the projection algebra before them and the map bookkeeping after them are the

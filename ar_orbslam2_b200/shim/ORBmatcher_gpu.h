@@ -6,6 +6,7 @@
 #ifndef ORBMATCHER_GPU_H
 #define ORBMATCHER_GPU_H
 
+#include <set>
 #include <utility>
 #include <vector>
 
@@ -28,6 +29,13 @@ int SearchForInitialization(Frame &F1, Frame &F2, std::vector<cv::Point2f> &vbPr
 
 // ref ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint*> &vpMapPointMatches), :159-288
 int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatches, float mfNNratio, bool mbCheckOrientation);
+
+// ref ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist), :1475-1602
+int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const std::set<MapPoint *> &sAlreadyFound, float th, int ORBdist,
+                       bool mbCheckOrientation);
+
+// ref ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, vector<MapPoint*> &vpMatched, int th), :290-403
+int SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *> &vpPoints, std::vector<MapPoint *> &vpMatched, int th);
 
 // ---- LocalMapping / LoopClosing matchers (M9) ----
 // ref ORBmatcher::SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, vector<pair<size_t,size_t>>&, bool bOnlyStereo), :660-826

@@ -286,7 +286,11 @@ int refm_search_by_projection_kf(refm_frame *cur, refm_frame *kf, const float *w
         }
     }
     ORBmatcher matcher(nnratio, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByProjection(C, K.get(), already, th, orb_dist, check_orientation != 0);
+#else
     *nmatches = matcher.SearchByProjection(C, K.get(), already, th, orb_dist);
+#endif
     for (int i = 0; i < C.N; i++) {
         MapPoint *m = C.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -357,7 +361,11 @@ int refm_search_by_projection_sim3(refm_frame *kf, const float *Scw, int n, cons
         }
     }
     ORBmatcher matcher(nnratio, true);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByProjection(K.get(), S, pts, matched, th);
+#else
     *nmatches = matcher.SearchByProjection(K.get(), S, pts, matched, th);
+#endif
     for (int i = 0; i < K->N; i++) assigned[i] = (matched[i] && matched[i]->id >= 0) ? matched[i]->id : -1;
     return 0;
 }

@@ -105,3 +105,32 @@ def test_cpp_matcher_shim_equals_reference(oracle, gpu_lib):
     nr, mr = oracle.refm_search_by_bow(mk(ka, da, rb), mk(kb, db, rb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
     ns, ms = oracle.refm_search_by_bow(mk(ka, da, sb), mk(kb, db, sb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
     assert nr > 100 and ns == nr and np.array_equal(ms, mr)
+
+
+def test_cpp_projection_shims_m4_m5(oracle, gpu_lib):
+    """The shim bodies of SearchByProjection(Frame&, KeyFrame*, set, th, ORBdist) (relocalisation) and
+    SearchByProjection(KeyFrame*, Scw, points, matched, th) (loop closing), compiled against the reference's headers, against
+    the reference's own compiled methods behind the same driver: same assignments and counts."""
+    import test_reference_matcher_cpu as T
+    from ar_orbslam2_b200.synth import shifted_frame, synth_frame
+    from ar_orbslam2_b200.tracking import Frame
+    if not (oracle.ref_matcher_available() and os.path.exists(oracle.REF_SHIM_PATH)):
+        pytest.skip("oracle/_ref shim library not built")
+    W, H = T.W, T.H
+    a = synth_frame(W, H, 31)
+    ex = oracle.RefExtractor(2000)
+    ka, da = ex.extract(a)
+    scene = dict(ka=ka, da=da, scale=ex.tables()["scale"])
+    bounds = (0.0, float(W), 0.0, float(H))
+    rb, sb = oracle.ReferenceSourceBackend(), oracle.ShimBackend()
+    mk = lambda be: Frame(ka, da, scene["scale"], bounds, backend=be)
+    c = T.kf_projection_case(scene, oracle, None)
+    for th, orbdist, ori in ((10.0, 100, True), (3.0, 64, False)):
+        R, S = [oracle.refm_search_by_projection_kf(mk(be), mk(be), c["xyz"], c["usable"], c["maxd"], c["mind"], c["claimed"], c["Tc"],
+                                                    T.FX, T.FY, T.CX, T.CY, th, orbdist, 0.9, ori) for be in (rb, sb)]
+        assert R["nmatches"] > 100 and S["nmatches"] == R["nmatches"] and np.array_equal(S["assigned"], R["assigned"]), (th, orbdist, ori)
+    c = T.sim3_projection_case(scene)
+    for th in (10, 4):
+        R, S = [oracle.refm_search_by_projection_sim3(mk(be), c["S"], c["xyz"], c["nrm"], c["usable"], c["maxd"], c["mind"], c["claimed"],
+                                                      T.FX, T.FY, T.CX, T.CY, th, 0.9) for be in (rb, sb)]
+        assert R["nmatches"] > 100 and S["nmatches"] == R["nmatches"] and np.array_equal(S["assigned"], R["assigned"]), th
