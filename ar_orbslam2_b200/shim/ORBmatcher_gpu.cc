@@ -176,6 +176,39 @@ int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint *> &vpMapPointMatc
     return nmatches;
 }
 
+int SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint *> &vpMatches12, float mfNNratio, bool mbCheckOrientation) {
+    const std::vector<MapPoint *> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const std::vector<MapPoint *> vpMapPoints2 = pKF2->GetMapPointMatches();
+    vpMatches12 = std::vector<MapPoint *>(vpMapPoints1.size(), static_cast<MapPoint *>(NULL));   // :538
+    const int n1 = (int)vpMapPoints1.size(), n2 = (int)vpMapPoints2.size();
+    if (n1 == 0 || n2 == 0) return 0;
+    std::vector<int32_t> off1(1, 0), off2(1, 0), idx1, idx2;           // the merge-join of :551-627 as CSR
+    DBoW2::FeatureVector::const_iterator f1it = pKF1->mFeatVec.begin(), f2it = pKF2->mFeatVec.begin();
+    const DBoW2::FeatureVector::const_iterator f1end = pKF1->mFeatVec.end(), f2end = pKF2->mFeatVec.end();
+    while (f1it != f1end && f2it != f2end) {
+        if (f1it->first == f2it->first) {
+            idx1.insert(idx1.end(), f1it->second.begin(), f1it->second.end());
+            idx2.insert(idx2.end(), f2it->second.begin(), f2it->second.end());
+            off1.push_back((int32_t)idx1.size()); off2.push_back((int32_t)idx2.size());
+            f1it++; f2it++;
+        } else if (f1it->first < f2it->first) f1it = pKF1->mFeatVec.lower_bound(f2it->first);
+        else f2it = pKF2->mFeatVec.lower_bound(f1it->first);
+    }
+    std::vector<uint8_t> valid1(n1), valid2(n2);
+    for (int i = 0; i < n1; i++) valid1[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();   // :561-566
+    for (int i = 0; i < n2; i++) valid2[i] = vpMapPoints2[i] && !vpMapPoints2[i]->isBad();   // :577-583
+    const std::vector<float> none;
+    GpuFrame g1(pKF1->mvKeysUn, pKF1->mDescriptors, none, pKF1->mvScaleFactors, true);
+    GpuFrame g2(pKF2->mvKeysUn, pKF2->mDescriptors, none, pKF2->mvScaleFactors, true);
+    std::vector<int32_t> matches(n2);
+    int nmatches = 0;
+    Check(orb_search_by_bow(g1.h, g2.h, (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), valid1.data(), valid2.data(),
+                            1 /* best < TH_LOW, :601 */, mfNNratio, mbCheckOrientation, matches.data(), &nmatches), "orb_search_by_bow");
+    for (int i2 = 0; i2 < n2; i2++)
+        if (matches[i2] >= 0) vpMatches12[matches[i2]] = vpMapPoints2[i2];   // :605
+    return nmatches;
+}
+
 // Relocalisation refinement (Tracking::Relocalization): project the key frame's map points with the current pose and search
 // the current frame; any map point already in the frame blocks its feature (:1544-1545).
 int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const std::set<MapPoint *> &sAlreadyFound, float th, int ORBdist,

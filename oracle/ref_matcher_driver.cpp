@@ -421,7 +421,11 @@ int refm_search_by_bow_kfkf(refm_frame *kf1, refm_frame *kf2, int ngroups, const
     fill_featvec(K2->mFeatVec, ngroups, off2, idx2);
     std::vector<MapPoint *> out;
     ORBmatcher matcher(nnratio, check_orientation != 0);
+#ifdef USE_GPU_SHIM
+    *nmatches = orbgpu_shim::SearchByBoW(K1.get(), K2.get(), out, nnratio, check_orientation != 0);
+#else
     *nmatches = matcher.SearchByBoW(K1.get(), K2.get(), out);
+#endif
     for (int i = 0; i < K2->N; i++) matches[i] = -1;
     for (int i1 = 0; i1 < K1->N; i1++)
         if (out[i1]) matches[out[i1]->id] = i1;

@@ -105,6 +105,12 @@ def test_cpp_matcher_shim_equals_reference(oracle, gpu_lib):
     nr, mr = oracle.refm_search_by_bow(mk(ka, da, rb), mk(kb, db, rb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
     ns, ms = oracle.refm_search_by_bow(mk(ka, da, sb), mk(kb, db, sb), kf_off, kf_idx, f_off, f_idx, kv, None, False, 0.7, True)
     assert nr > 100 and ns == nr and np.array_equal(ms, mr)
+    # SearchByBoW(KeyFrame, KeyFrame): strict `< TH_LOW`, second-side validity
+    fv = (np.arange(len(kb)) % 9 != 0).astype(np.uint8)
+    for ori in (True, False):
+        nr, mr = oracle.refm_search_by_bow(mk(ka, da, rb), mk(kb, db, rb), kf_off, kf_idx, f_off, f_idx, kv, fv, True, 0.7, ori)
+        ns, ms = oracle.refm_search_by_bow(mk(ka, da, sb), mk(kb, db, sb), kf_off, kf_idx, f_off, f_idx, kv, fv, True, 0.7, ori)
+        assert nr > 100 and ns == nr and np.array_equal(ms, mr)
 
 
 def test_cpp_projection_shims_m4_m5(oracle, gpu_lib):
