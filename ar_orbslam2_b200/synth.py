@@ -109,3 +109,79 @@ def synth_queries(db_rows_fn, n_db: int, nq: int, seed: int) -> np.ndarray:
             rows[i, bit >> 3] ^= np.uint8(1 << (bit & 7))
     q[0::2] = rows
     return q
+
+
+# ---- synthetic bag-of-words vocabulary (the reference's ORBvoc.txt is an external download, ORB_SLAM2/README.md) -----
+
+def synth_vocabulary(k: int = 10, L: int = 3, seed: int = 0, flip_bits: int = 40, stop_fraction: float = 0.02,
+                     dup_fraction: float = 0.05, early_leaf_fraction: float = 0.0):
+    """A full k-ary tree of depth L in the node order DBoW2's create()/loadFromTextFile produce (a node's id is larger
+    than its parent's; children of a node in ascending id).  A child's descriptor is its parent's with `flip_bits`
+    random bit flips, so the descent is decided by real distances; `dup_fraction` of the children copy their left
+    sibling's descriptor (distance ties -> first child must win); `stop_fraction` of the words have weight 0
+    ("stopped" words); `early_leaf_fraction` of the inner nodes below the root are cut to leaves.
+    Returns dict(k, L, parent, descriptors, weight, word_id, is_leaf) with node 0 = root."""
+    rng = np.random.default_rng(seed)
+    parent, desc, depth = [0], [np.zeros(32, np.uint8)], [0]
+    frontier = [0]
+    root_desc = rng.integers(0, 256, 32, dtype=np.uint8)
+    for lvl in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            if lvl > 1 and lvl <= L and early_leaf_fraction > 0 and rng.random() < early_leaf_fraction:
+                continue   # p stays a leaf
+            base = root_desc if p == 0 else desc[p]
+            prev = None
+            for c in range(k):
+                if prev is not None and rng.random() < dup_fraction:
+                    d = prev.copy()
+                else:
+                    bits = np.unpackbits(base.copy())
+                    flips = rng.choice(256, size=flip_bits, replace=False)
+                    bits[flips] ^= 1
+                    d = np.packbits(bits)
+                prev = d
+                parent.append(p); desc.append(d); depth.append(lvl)
+                nxt.append(len(parent) - 1)
+        frontier = nxt
+    n = len(parent)
+    parent = np.asarray(parent, np.int32)
+    desc = np.stack(desc).astype(np.uint8)
+    has_child = np.zeros(n, bool)
+    has_child[parent[1:]] = True
+    is_leaf = ~has_child
+    is_leaf[0] = False
+    word_id = np.zeros(n, np.int32)
+    word_id[is_leaf] = np.arange(int(is_leaf.sum()), dtype=np.int32)      # word ids in node order (loadFromTextFile :1409-1416)
+    weight = np.zeros(n, np.float64)
+    w = rng.uniform(0.5, 12.0, int(is_leaf.sum()))                         # idf-like values
+    w[rng.random(w.shape[0]) < stop_fraction] = 0.0
+    weight[is_leaf] = w
+    return dict(k=k, L=L, parent=parent, descriptors=desc, weight=weight, word_id=word_id, is_leaf=is_leaf)
+
+
+def write_vocabulary_text(path, voc, scoring: int = 0, weighting: int = 0, trailing_newline: bool = True):
+    """ORBvoc.txt format (TemplatedVocabulary::saveToTextFile, TemplatedVocabulary.h:1428-1448): header `k L  scoring
+    weighting`, then per node `parent is_leaf d0 .. d31 weight`."""
+    lines = [f"{voc['k']} {voc['L']}  {scoring} {weighting}"]
+    for i in range(1, voc["parent"].shape[0]):
+        d = " ".join(str(int(x)) for x in voc["descriptors"][i])
+        lines.append(f"{int(voc['parent'][i])} {1 if voc['is_leaf'][i] else 0} {d}  {repr(float(voc['weight'][i]))}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + ("\n" if trailing_newline else ""))
+
+
+def synth_bow_descriptors(voc, n: int, seed: int = 0, flip_bits: int = 30) -> np.ndarray:
+    """n query descriptors: random words of the vocabulary with `flip_bits` bits flipped (so they descend somewhere
+    meaningful), a few exact copies of inner nodes and a few uniformly random rows."""
+    rng = np.random.default_rng(seed + 7919)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    pick = rng.choice(leaves, size=n)
+    out = voc["descriptors"][pick].copy()
+    bits = np.unpackbits(out, axis=1)
+    for i in range(n):
+        bits[i, rng.choice(256, size=flip_bits, replace=False)] ^= 1
+    out = np.packbits(bits, axis=1)
+    nr = max(1, n // 16)
+    out[rng.choice(n, nr, replace=False)] = rng.integers(0, 256, (nr, 32), dtype=np.uint8)
+    return np.ascontiguousarray(out)

@@ -369,6 +369,77 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
                       const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
                       int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
 
+/* ---- bag-of-words vocabulary (DBoW2 transform) --------------------------- */
+
+/* ref: ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (include/ORBVocabulary.h:29),
+ * Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h.  The tree is resident in HBM; Frame::ComputeBoW
+ * (src/Frame.cc:400-407) and KeyFrame::ComputeBoW (src/KeyFrame.cc:62-70) become one
+ * orb_vocab_transform call whose FeatureVector output is already the CSR that orb_search_by_bow /
+ * orb_search_for_triangulation consume.  A vocabulary handle may be shared by threads (the reference
+ * calls the const transform() from Tracking, LocalMapping and LoopClosing): calls serialise on it.  */
+typedef struct orb_vocab orb_vocab;
+
+/* Flat tree, node 0 = root.  A node's children are the nodes naming it as parent, in ascending node id
+ * -- the order loadFromTextFile (:1338-1425) and create() (:596-618) push them, which decides ties
+ * in the descent.  A node without children is a leaf (Node::isLeaf, :328).                        */
+typedef struct orb_vocab_desc {
+    int32_t k, L;                /* branching factor and depth levels (m_k, m_L)                  */
+    int32_t scoring;             /* DBoW2::ScoringType   0 L1_NORM 1 L2_NORM 2 CHI_SQUARE 3 KL 4 BHATTACHARYYA 5 DOT_PRODUCT */
+    int32_t weighting;           /* DBoW2::WeightingType 0 TF_IDF 1 TF 2 IDF 3 BINARY              */
+    int32_t n_nodes;             /* root included                                                  */
+    const int32_t *parent;       /* [n_nodes], parent[0] ignored; parent[i] < i is NOT required    */
+    const uint8_t *descriptors;  /* [n_nodes][32], row 0 ignored                                   */
+    const double *weight;        /* [n_nodes] Node::weight                                         */
+    const int32_t *word_id;      /* [n_nodes] Node::word_id (the reference leaves 0 on non-words)  */
+} orb_vocab_desc;
+
+int orb_vocab_create(const orb_vocab_desc *desc, int device, orb_vocab **out);
+/* ref: TemplatedVocabulary::loadFromTextFile, :1338-1425 (the loader src/System.cc:67-75 uses).  One deliberate
+ * difference: the reference's `while(!f.eof())` loop runs once more on the empty read after the final newline and
+ * then uses `int pid` / `int nIsLeaf` that no extraction has written (undefined behaviour: the reference's own code,
+ * compiled here, either attaches a phantom node to whatever the stack holds or crashes).  Here that empty final read
+ * is not a node, so a file loads the same with or without a trailing newline; any other malformed line is
+ * ORB_ERR_INVALID.                                                                                               */
+int orb_vocab_load_text(const char *path, int device, orb_vocab **out);
+void orb_vocab_destroy(orb_vocab *v);
+/* info[0..5] = k, L, scoring, weighting, nodes (root included), words */
+int orb_vocab_info(const orb_vocab *v, int32_t *info);
+/* Read the tree back in the orb_vocab_desc layout (any pointer may be NULL). */
+int orb_vocab_nodes(const orb_vocab *v, int32_t *parent, uint8_t *descriptors, double *weight, int32_t *word_id);
+
+/* ref: transform(const TDescriptor&, WordId&, WordValue&, NodeId*, int levelsup), :1217-1255: descend from the
+ * root taking at every level the child at the smallest FORB::distance (FORB.cpp:81-101), first child on ties.
+ * node[i] = node reached at level L-levelsup (0 = root when that level is <= 0; when the leaf is shallower than
+ * that level the reference leaves *nid unset -- here it is the leaf).  descriptors: n rows of 32 bytes.          */
+int orb_vocab_transform_features(orb_vocab *v, const uint8_t *descriptors, int n, int loc, int levelsup,
+                                 int32_t *word, int32_t *node, double *weight);
+
+/* ref: transform(const vector<TDescriptor>&, BowVector&, FeatureVector&, int levelsup), :1126-1193, with
+ * BowVector::addWeight / addIfNotExist / normalize (BowVector.cpp:33-88) and FeatureVector::addFeature
+ * (FeatureVector.cpp:30-44).  Frame b's descriptors are rows [b*stride_rows, b*stride_rows + n[b]).  Outputs per
+ * frame b at offset b*capacity (fv_off: b*(capacity+1)); capacity >= max n[b].
+ *   bow_word/bow_value[0..n_bow)  the std::map<WordId, WordValue> in iteration order (ascending word id); values
+ *                                 are accumulated and normalised in double in the reference's order, bit-exact
+ *   fv_node[0..n_fv)              ascending node ids; features of group g = fv_feat[fv_off[g]..fv_off[g+1]),
+ *                                 ascending feature index (push_back order)
+ * Features whose word weight is 0 ("stopped", :1159,1186) appear in neither.  With out_loc == ORB_DEVICE the call
+ * is asynchronous on the vocabulary's stream (orb_vocab_sync).                                                   */
+typedef struct orb_bow_out {
+    int32_t capacity;
+    int32_t *bow_word;   /* [batch][capacity]   */
+    double *bow_value;   /* [batch][capacity]   */
+    int32_t *n_bow;      /* [batch]             */
+    int32_t *fv_node;    /* [batch][capacity]   */
+    int32_t *fv_off;     /* [batch][capacity+1] */
+    int32_t *fv_feat;    /* [batch][capacity]   */
+    int32_t *n_fv;       /* [batch]             */
+} orb_bow_out;
+int orb_vocab_transform(orb_vocab *v, const uint8_t *descriptors, const int32_t *n, int batch,
+                        int stride_rows, int loc, int levelsup, const orb_bow_out *out, int out_loc);
+int orb_vocab_sync(orb_vocab *v);
+void *orb_vocab_stream(orb_vocab *v);
+int64_t orb_vocab_launch_count(const orb_vocab *v);
+
 const char *orb_last_error(void);
 int orb_abi_version(void);
 

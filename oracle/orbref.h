@@ -52,6 +52,17 @@ int orbref_search_for_triangulation(orbref_frame *KF1, orbref_frame *KF2, int ng
                                     const int32_t *off2, const int32_t *idx2, const uint8_t *usable1, const uint8_t *usable2,
                                     const float *F12, float ex, float ey, const float *level_sigma2, int only_stereo,
                                     int check_orientation, int32_t *matches12, int *nmatches);
+/* DBoW2 vocabulary: text loader, tree descent, BowVector / FeatureVector assembly (orbref_bow.cpp) */
+typedef struct orbref_vocab orbref_vocab;
+int orbref_vocab_create(const orb_vocab_desc *d, orbref_vocab **out);
+int orbref_vocab_load_text(const char *path, orbref_vocab **out);
+void orbref_vocab_destroy(orbref_vocab *v);
+int orbref_vocab_info(const orbref_vocab *v, int32_t *info);
+int orbref_vocab_nodes(const orbref_vocab *v, int32_t *parent, uint8_t *desc, double *weight, int32_t *word_id);
+int orbref_vocab_transform_features(const orbref_vocab *v, const uint8_t *desc, int n, int levelsup, int32_t *word,
+                                    int32_t *node, double *weight);
+int orbref_vocab_transform(const orbref_vocab *v, const uint8_t *desc, int n, int levelsup, int capacity, int32_t *bow_word,
+                           double *bow_value, int32_t *n_bow, int32_t *fv_node, int32_t *fv_off, int32_t *fv_feat, int32_t *n_fv);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -439,3 +439,127 @@ def refm_search_by_sim3(kf1, kf2, s12, R12, t12, R1w, t1w, R2w, t2w, has1, world
     _check(L.refm_search_by_sim3(kf1._h, kf2._h, f(s12), *[ptr(x) for x in poses], *[ptr(x) for x in s1], *[ptr(x) for x in s2], ptr(pre),
                                  f(fx), f(fy), f(cx), f(cy), f(th), ptr(m12), C.byref(nf)), "refm_search_by_sim3")
     return nf.value, m12
+
+
+# ---- DBoW2 vocabulary: the restated oracle (orbref_bow.cpp) and the reference's own DBoW2 (oracle/_ref/libdbow2_ref.so) ----
+class _VocabDesc(C.Structure):
+    _fields_ = [("k", C.c_int32), ("L", C.c_int32), ("scoring", C.c_int32), ("weighting", C.c_int32), ("n_nodes", C.c_int32),
+                ("parent", C.c_void_p), ("descriptors", C.c_void_p), ("weight", C.c_void_p), ("word_id", C.c_void_p)]
+
+
+def _bow_outputs(cap):
+    return (np.zeros(cap, np.int32), np.zeros(cap, np.float64), C.c_int32(0), np.zeros(cap, np.int32), np.zeros(cap + 1, np.int32),
+            np.zeros(cap, np.int32), C.c_int32(0))
+
+
+def _bow_pack(o):
+    bw, bv, nb, fn, fo, ff, nf = o
+    g = nf.value
+    return bw[: nb.value].copy(), bv[: nb.value].copy(), fn[:g].copy(), fo[: g + 1].copy(), ff[: fo[g]].copy()
+
+
+class RefVocabulary:
+    """CPU restatement of DBoW2::TemplatedVocabulary<FORB> (text loader, descent, BowVector/FeatureVector assembly)."""
+
+    def __init__(self, path=None, arrays=None, scoring=0, weighting=0):
+        self.h = C.c_void_p()
+        if path is not None:
+            _check(lib().orbref_vocab_load_text(str(path).encode(), C.byref(self.h)), "vocab_load_text")
+        else:
+            a = arrays
+            self._keep = [np.ascontiguousarray(a["parent"], np.int32), np.ascontiguousarray(a["descriptors"], np.uint8),
+                          np.ascontiguousarray(a["weight"], np.float64), np.ascontiguousarray(a["word_id"], np.int32)]
+            d = _VocabDesc(a["k"], a["L"], scoring, weighting, self._keep[0].shape[0], *[x.ctypes.data for x in self._keep])
+            _check(lib().orbref_vocab_create(C.byref(d), C.byref(self.h)), "vocab_create")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orbref_vocab_destroy(self.h)
+            self.h = None
+
+    def info(self):
+        a = np.zeros(6, np.int32)
+        lib().orbref_vocab_info(self.h, ptr(a))
+        return dict(k=int(a[0]), L=int(a[1]), scoring=int(a[2]), weighting=int(a[3]), nodes=int(a[4]), words=int(a[5]))
+
+    def nodes(self):
+        n = self.info()["nodes"]
+        parent, word = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        desc, weight = np.zeros((n, 32), np.uint8), np.zeros(n, np.float64)
+        lib().orbref_vocab_nodes(self.h, ptr(parent), ptr(desc), ptr(weight), ptr(word))
+        return parent, desc, weight, word
+
+    def transform_features(self, desc, levelsup=0):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = d.shape[0]
+        word, node, w = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float64)
+        _check(lib().orbref_vocab_transform_features(self.h, ptr(d), n, levelsup, ptr(word), ptr(node), ptr(w)), "vocab_transform_features")
+        return word, node, w
+
+    def transform(self, desc, levelsup=4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = d.shape[0]
+        o = _bow_outputs(max(n, 1))
+        _check(lib().orbref_vocab_transform(self.h, ptr(d), n, levelsup, max(n, 1), ptr(o[0]), ptr(o[1]), C.byref(o[2]), ptr(o[3]),
+                                            ptr(o[4]), ptr(o[5]), C.byref(o[6])), "vocab_transform")
+        return _bow_pack(o)
+
+
+REF_DBOW_PATH = os.path.join(_HERE, "_ref", "libdbow2_ref.so")
+_REFB = None
+
+
+def ref_dbow_available() -> bool:
+    if os.path.exists(REF_DBOW_PATH):
+        return True
+    if os.path.isdir("/root/reference/ORB_SLAM2/Thirdparty/DBoW2"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-f", "Makefile.ref"])
+        return True
+    return False
+
+
+class ReferenceVocabulary:
+    """The reference's own DBoW2 (TemplatedVocabulary.h, FORB.cpp, BowVector.cpp, FeatureVector.cpp) compiled unmodified."""
+
+    def __init__(self, path):
+        global _REFB
+        if _REFB is None:
+            _REFB = C.CDLL(REF_DBOW_PATH)
+            _REFB.ref_bow_load_text.restype = C.c_void_p
+            _REFB.ref_bow_free.argtypes = [C.c_void_p]
+        self.L = _REFB
+        self.h = C.c_void_p(self.L.ref_bow_load_text(str(path).encode()))
+        if not self.h:
+            raise RuntimeError("reference loadFromTextFile returned false")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_bow_free(self.h)
+            self.h = None
+
+    def info(self):
+        a = np.zeros(6, np.int32)
+        self.L.ref_bow_info(self.h, ptr(a))
+        return dict(k=int(a[0]), L=int(a[1]), scoring=int(a[2]), weighting=int(a[3]), nodes=int(a[4]), words=int(a[5]))
+
+    def nodes(self):
+        n = self.info()["nodes"]
+        parent, word, nch = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        desc, weight = np.zeros((n, 32), np.uint8), np.zeros(n, np.float64)
+        self.L.ref_bow_nodes(self.h, ptr(parent), ptr(desc), ptr(weight), ptr(word), ptr(nch))
+        return parent, desc, weight, word
+
+    def transform_features(self, desc, levelsup=0):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = d.shape[0]
+        word, node, w = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float64)
+        self.L.ref_bow_transform_features(self.h, ptr(d), n, levelsup, ptr(word), ptr(node), ptr(w))
+        return word, node, w
+
+    def transform(self, desc, levelsup=4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = d.shape[0]
+        o = _bow_outputs(max(n, 1))
+        _check(self.L.ref_bow_transform(self.h, ptr(d), n, levelsup, max(n, 1), ptr(o[0]), ptr(o[1]), C.byref(o[2]), ptr(o[3]), ptr(o[4]),
+                                        ptr(o[5]), C.byref(o[6])), "ref_bow_transform")
+        return _bow_pack(o)

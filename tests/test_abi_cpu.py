@@ -59,6 +59,12 @@ def test_no_cpu_fallback(lib):
         DescriptorDB(0, 10)
     with pytest.raises(_lib.OrbGpuError):
         hamming_top2(np.zeros((1, 32), np.uint8), np.zeros((4, 32), np.uint8))
+    from ar_orbslam2_b200.synth import synth_vocabulary
+    from ar_orbslam2_b200.vocabulary import ORBVocabulary
+    voc = synth_vocabulary(3, 2, seed=0)
+    with pytest.raises(_lib.OrbGpuError) as e:
+        ORBVocabulary.from_arrays(3, 2, voc["parent"], voc["descriptors"], voc["weight"], voc["word_id"])
+    assert e.value.code == -2
 
 
 def test_product_path_does_not_touch_the_oracle():
