@@ -185,3 +185,35 @@ def synth_bow_descriptors(voc, n: int, seed: int = 0, flip_bits: int = 30) -> np
     nr = max(1, n // 16)
     out[rng.choice(n, nr, replace=False)] = rng.integers(0, 256, (nr, 32), dtype=np.uint8)
     return np.ascontiguousarray(out)
+
+
+def synth_vocabulary_fast(k: int = 10, L: int = 6, seed: int = 0, flip_prob: float = 0.15):
+    """ORBvoc-sized trees (k=10, L=6: 1.1 M nodes) in seconds: level by level, a child's descriptor = its parent's XOR a
+    random mask with each bit set with probability `flip_prob`.  Same node order and fields as synth_vocabulary."""
+    rng = np.random.default_rng(seed)
+    parents, descs = [np.zeros(1, np.int32)], [rng.integers(0, 256, (1, 32), dtype=np.uint8)]
+    first = 0
+    for lvl in range(1, L + 1):
+        prev = descs[-1]
+        n_prev = prev.shape[0]
+        par = np.repeat(np.arange(first, first + n_prev, dtype=np.int32), k)
+        child = np.repeat(prev, k, axis=0)
+        for s in range(0, child.shape[0], 1 << 17):
+            e = min(child.shape[0], s + (1 << 17))
+            mask = np.packbits(rng.random((e - s, 256), dtype=np.float32) < flip_prob, axis=1)
+            child[s:e] ^= mask
+        first += n_prev
+        parents.append(par)
+        descs.append(child)
+    parent = np.concatenate(parents)
+    desc = np.concatenate(descs)
+    desc[0] = 0
+    n = parent.shape[0]
+    n_leaf = descs[-1].shape[0]
+    is_leaf = np.zeros(n, bool)
+    is_leaf[n - n_leaf:] = True
+    word_id = np.zeros(n, np.int32)
+    word_id[is_leaf] = np.arange(n_leaf, dtype=np.int32)
+    weight = np.zeros(n, np.float64)
+    weight[is_leaf] = rng.uniform(0.5, 12.0, n_leaf)
+    return dict(k=k, L=L, parent=parent, descriptors=desc, weight=weight, word_id=word_id, is_leaf=is_leaf)

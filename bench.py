@@ -242,6 +242,69 @@ def bench_c1(args, torch, dev, local):
     return r
 
 
+def bench_bow(args, torch, dev, local):
+    """SURVEY 8f-1: DBoW2 transform (Frame::ComputeBoW) on an ORBvoc-shaped tree (k=10, L=6, 1.1 M nodes, levelsup 4):
+    `frames` frames x 2000 descriptors per call, device-resident, CUDA events on the vocabulary's stream; the oracle
+    (CPU restatement pinned to the reference's DBoW2) timed on a bounded sample beside it."""
+    from ar_orbslam2_b200.synth import synth_vocabulary_fast
+    from ar_orbslam2_b200.vocabulary import ORBVocabulary
+    voc = synth_vocabulary_fast(10, 6, 0)
+    G = ORBVocabulary.from_arrays(10, 6, voc["parent"], voc["descriptors"], voc["weight"], voc["word_id"], device=local)
+    B, S, steps = 256, 2000, 10
+    rng = np.random.default_rng(5)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    host = voc["descriptors"][rng.choice(leaves, B * S)] ^ np.packbits(rng.random((B * S, 256), dtype=np.float32) < 0.1, axis=1)
+    host = np.ascontiguousarray(host.reshape(B, S, 32))
+    d_desc = torch.from_numpy(host).to(dev)
+    d_n = torch.full((B,), S, dtype=torch.int32, device=dev)
+    bw, fn, ff = (torch.zeros((B, S), dtype=torch.int32, device=dev) for _ in range(3))
+    bv = torch.zeros((B, S), dtype=torch.float64, device=dev)
+    fo = torch.zeros((B, S + 1), dtype=torch.int32, device=dev)
+    nb, nf = torch.zeros(B, dtype=torch.int32, device=dev), torch.zeros(B, dtype=torch.int32, device=dev)
+    st = torch.cuda.ExternalStream(G.stream, device=dev)
+    torch.cuda.synchronize()
+    run = lambda: G.transform_device(d_desc.data_ptr(), d_n.data_ptr(), B, S, 4, S, bw.data_ptr(), bv.data_ptr(), nb.data_ptr(),
+                                     fn.data_ptr(), fo.data_ptr(), ff.data_ptr(), nf.data_ptr())
+    for _ in range(3):
+        run()
+    G.sync()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = G.launch_count
+    s.record(st)
+    for _ in range(steps):
+        run()
+    e.record(st)
+    e.synchronize()
+    ms = s.elapsed_time(e) / steps
+    r = {"frames_per_s": B / (ms * 1e-3), "features_per_s": B * S / (ms * 1e-3), "ms_per_call": ms,
+         "workload": f"{B} frames x {S} descriptors per call, vocabulary k=10 L=6 ({voc['parent'].shape[0]} nodes), levelsup 4",
+         "launches": int(G.launch_count - l0), "words_per_frame": float(nb.float().mean().item()),
+         "hamming_per_feature": 60}
+    # single-frame latency through the blocking host API (what Frame::ComputeBoW costs a tracking thread)
+    import time
+    one = host[0]
+    for _ in range(3):
+        G.transform(one, 4)
+    t = []
+    for _ in range(30):
+        t0 = time.perf_counter(); G.transform(one, 4); t.append(time.perf_counter() - t0)
+    r["host_call_ms_median"] = float(np.median(t) * 1e3)
+    if not args.skip_cpu:
+        from oracle import orbref
+        O = orbref.RefVocabulary(arrays=voc)
+        t0 = time.perf_counter()
+        nfr = 8
+        for b in range(nfr):
+            O.transform(host[b], 4)
+        dt = time.perf_counter() - t0
+        r["cpu_baseline"] = {"frames_per_s": nfr / dt, "cores": 1, "kind": "port", "sample": f"{nfr} frames x {S} descriptors, one thread"}
+        got = G.transform(host[0], 4)
+        want = O.transform(host[0], 4)
+        r["matches_oracle"] = bool(all(a.tobytes() == b.tobytes() for a, b in zip(got, want)))
+    G.close()
+    return r
+
+
 _KEEP = []   # library handles must outlive every pinned buffer that was copied on their streams: torch's pinned-memory
              # allocator records an event on those streams when such a buffer is freed.  They are closed at interpreter exit.
 
@@ -506,6 +569,8 @@ def run_ours(args):
     if rank == 0 and not os.environ.get("ORB_BENCH_SKIP_C1"):
         extra["c1_mono"] = bench_c1(args, torch, dev, local)
         extra["latency"] = bench_latency(args)
+        if not os.environ.get("ORB_BENCH_SKIP_BOW"):
+            extra["bow_transform"] = bench_bow(args, torch, dev, local)
 
     if rank != 0:
         if world > 1:
