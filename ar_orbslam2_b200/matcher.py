@@ -130,3 +130,16 @@ class DescriptorDB:
         vp = C.c_void_p
         _lib.check(self._L.orb_db_merge_top2(self._h, nshards, nq, vp(d_bd), vp(d_bi), vp(d_sd), vp(d_si), vp(o_bd), vp(o_bi), vp(o_sd),
                                              vp(o_si)), "orb_db_merge_top2")
+
+
+def ComputeDistinctiveDescriptors(descriptors: np.ndarray, offsets: np.ndarray):
+    """MapPoint::ComputeDistinctiveDescriptors (ref MapPoint.cc:224-285) for many map points at once, on the GPU: map point
+    p is observed through descriptor rows [offsets[p], offsets[p+1]) (non-bad key frames in mObservations order).
+    Returns (best_row, best_median): the index inside each group of the descriptor with the least median distance to
+    the others (-1 for an empty group)."""
+    d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+    off = np.ascontiguousarray(offsets, np.int32)
+    n = off.shape[0] - 1
+    row, med = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    _lib.check(_lib.lib().orb_distinctive_descriptors(ptr(d), ptr(off), n, ORB_HOST, ptr(row), ptr(med)), "orb_distinctive_descriptors")
+    return row, med

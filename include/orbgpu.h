@@ -369,6 +369,18 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
                       const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
                       int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
 
+/* ---- map-point descriptor selection ------------------------------------------ */
+
+/* ref: MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:224-285: among the N descriptors observing a map
+ * point (the caller gathers `pKF->mDescriptors.row(idx)` of the non-bad key frames in mObservations order, :243-249)
+ * all N*N DescriptorDistances, per row the median `vDists[0.5*(N-1)]` of the sorted row (diagonal 0 included), and
+ * the row with the smallest median, first row on ties (`median < BestMedian`, :272-275).  Any number of map points
+ * per call: point p owns rows [offsets[p], offsets[p+1]).  best_row[p] = index of the chosen row inside its group
+ * (-1 for an empty group: the reference returns early and keeps the old descriptor), best_median[p] = its median.
+ * loc = where all four arrays live; ORB_DEVICE calls are asynchronous on the default stream.                      */
+int orb_distinctive_descriptors(const uint8_t *descriptors, const int32_t *offsets, int npoints, int loc,
+                                int32_t *best_row, int32_t *best_median);
+
 /* ---- bag-of-words vocabulary (DBoW2 transform) --------------------------- */
 
 /* ref: ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (include/ORBVocabulary.h:29),

@@ -75,6 +75,7 @@ public:
     Mat() : rows(0), cols(0), data(nullptr), step{0}, type_(CV_8UC1), esz(1) {}
     Mat(Size sz, int t) { alloc(sz.height, sz.width, t); }
     Mat(int r, int c, int t) { alloc(r, c, t); }
+    Mat(const MatZeros &z) : rows(0), cols(0), data(nullptr), step{0}, type_(CV_8UC1), esz(1) { *this = z; }   // cv::Mat m = cv::Mat::zeros(..), MapPoint.cc:322
     void alloc(int r, int c, int t = CV_8UC1) {
         rows = r; cols = c; type_ = t; esz = (t == CV_32F) ? 4 : 1;
         buf = std::make_shared<std::vector<uchar>>((size_t)r * c * esz);

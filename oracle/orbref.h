@@ -63,6 +63,8 @@ int orbref_vocab_transform_features(const orbref_vocab *v, const uint8_t *desc, 
                                     int32_t *node, double *weight);
 int orbref_vocab_transform(const orbref_vocab *v, const uint8_t *desc, int n, int levelsup, int capacity, int32_t *bow_word,
                            double *bow_value, int32_t *n_bow, int32_t *fv_node, int32_t *fv_off, int32_t *fv_feat, int32_t *n_fv);
+/* MapPoint::ComputeDistinctiveDescriptors (orbref_mappoint.cpp) */
+int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t *off, int npoints, int32_t *best_row, int32_t *best_median);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -563,3 +563,40 @@ class ReferenceVocabulary:
         _check(self.L.ref_bow_transform(self.h, ptr(d), n, levelsup, max(n, 1), ptr(o[0]), ptr(o[1]), C.byref(o[2]), ptr(o[3]), ptr(o[4]),
                                         ptr(o[5]), C.byref(o[6])), "ref_bow_transform")
         return _bow_pack(o)
+
+
+# ---- MapPoint::ComputeDistinctiveDescriptors: the restated oracle and the reference's own MapPoint.cc ----
+def distinctive_descriptors(desc, offsets):
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    off = np.ascontiguousarray(offsets, np.int32)
+    n = off.shape[0] - 1
+    row, med = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    _check(lib().orbref_distinctive_descriptors(ptr(d), ptr(off), n, ptr(row), ptr(med)), "distinctive_descriptors")
+    return row, med
+
+
+REF_MAPPOINT_PATH = os.path.join(_HERE, "_ref", "libmappoint_ref.so")
+_REFMP = None
+
+
+def ref_mappoint_available() -> bool:
+    if os.path.exists(REF_MAPPOINT_PATH):
+        return True
+    if os.path.isdir("/root/reference/ORB_SLAM2/src"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-f", "Makefile.ref"])
+        return True
+    return False
+
+
+def ref_distinctive_descriptors(desc, offsets, bad=None):
+    """The reference's compiled MapPoint::ComputeDistinctiveDescriptors: returns the chosen descriptor (32 bytes) per map point."""
+    global _REFMP
+    if _REFMP is None:
+        _REFMP = C.CDLL(REF_MAPPOINT_PATH)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    off = np.ascontiguousarray(offsets, np.int32)
+    n = off.shape[0] - 1
+    out = np.zeros((n, 32), np.uint8)
+    b = None if bad is None else np.ascontiguousarray(bad, np.uint8)
+    _check(_REFMP.ref_distinctive_descriptors(ptr(d), ptr(off), n, None if b is None else ptr(b), ptr(out)), "ref_distinctive_descriptors")
+    return out
