@@ -369,6 +369,20 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
                       const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
                       int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
 
+/* ---- colour -> grey in front of the extractor ---------------------------------- */
+
+/* ref: cvtColor(mImGray, mImGray, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) in
+ * Tracking::GrabImageStereo / GrabImageRGBD / GrabImageMonocular (src/Tracking.cc:510-526,545-556,567-577).  8-bit
+ * interleaved input with `channels` = 3 or 4; rgb_order = 1 for RGB(A) (mbRGB), 0 for BGR(A).  variant 0 = OpenCV
+ * 3.x/4.x arithmetic `(R*9798 + G*19235 + B*3735 + 16384) >> 15` (pinned against cv2 4.13.0), variant 1 = OpenCV
+ * 2.4's `(R*4899 + G*9617 + B*1868 + 8192) >> 14` (the version the reference was built with; unverifiable here).
+ * `batch` images, image b at src + b*src_stride / dst + b*dst_stride.  loc = where src and dst live; `stream` is a
+ * cudaStream_t (NULL = default stream); ORB_DEVICE calls are asynchronous on it, so the grey image can be handed to
+ * orb_extract_batch(image_loc = ORB_DEVICE) without touching the host.                                           */
+int orb_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, size_t src_stride, int channels,
+                       int rgb_order, int variant, int batch, uint8_t *dst, int dst_pitch, size_t dst_stride, int loc,
+                       void *stream);
+
 /* ---- map-point descriptor selection ------------------------------------------ */
 
 /* ref: MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:224-285: among the N descriptors observing a map

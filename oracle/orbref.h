@@ -65,6 +65,9 @@ int orbref_vocab_transform(const orbref_vocab *v, const uint8_t *desc, int n, in
                            double *bow_value, int32_t *n_bow, int32_t *fv_node, int32_t *fv_off, int32_t *fv_feat, int32_t *n_fv);
 /* MapPoint::ComputeDistinctiveDescriptors (orbref_mappoint.cpp) */
 int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t *off, int npoints, int32_t *best_row, int32_t *best_median);
+/* cv::cvtColor X2GRAY, 8-bit (orbref_color.cpp) */
+int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, int channels, int rgb_order, int variant,
+                          uint8_t *dst, int dst_pitch);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

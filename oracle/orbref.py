@@ -600,3 +600,12 @@ def ref_distinctive_descriptors(desc, offsets, bad=None):
     b = None if bad is None else np.ascontiguousarray(bad, np.uint8)
     _check(_REFMP.ref_distinctive_descriptors(ptr(d), ptr(off), n, None if b is None else ptr(b), ptr(out)), "ref_distinctive_descriptors")
     return out
+
+
+def cvt_color_gray(img, rgb_order=True, variant=0):
+    """cv::cvtColor(img, CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY), 8-bit."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = img.shape
+    out = np.zeros((h, w), np.uint8)
+    _check(lib().orbref_cvt_color_gray(ptr(img), w, h, img.strides[0], ch, int(rgb_order), variant, ptr(out), w), "cvt_color_gray")
+    return out
