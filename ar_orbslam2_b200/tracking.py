@@ -199,3 +199,27 @@ def rot_hist_filter(angle_a, angle_b) -> np.ndarray:
     keep = np.zeros(a.size, np.uint8)
     _lib.check(_lib.lib().orb_rot_hist_filter(ptr(a), ptr(b), a.size, ptr(keep)), "orb_rot_hist_filter")
     return keep.astype(bool)
+
+
+def UndistortKeyPoints(keys: np.ndarray, fx: float, fy: float, cx: float, cy: float, dist_coef) -> np.ndarray:
+    """Frame::UndistortKeyPoints (ref Frame.cc:409-439) on the GPU: keys is a KEYPOINT_DTYPE array (mvKeys); returns mvKeysUn."""
+    import ctypes as C
+    k = np.ascontiguousarray(keys)
+    d = np.ascontiguousarray(dist_coef, np.float32)
+    out = np.zeros_like(k)
+    _lib.check(_lib.lib().orb_undistort_keypoints(ptr(k), k.shape[0], C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), ptr(d),
+                                                  d.shape[0], ptr(out), 0), "orb_undistort_keypoints")
+    return out
+
+
+def ComputeImageBounds(width: int, height: int, fx: float, fy: float, cx: float, cy: float, dist_coef):
+    """Frame::ComputeImageBounds (ref Frame.cc:441-468): (mnMinX, mnMaxX, mnMinY, mnMaxY); the corner undistortion runs on the GPU."""
+    import ctypes as C
+    d = np.ascontiguousarray(dist_coef, np.float32)
+    if d[0] == 0.0:
+        return np.float32(0), np.float32(width), np.float32(0), np.float32(height)
+    m = np.array([[0, 0], [width, 0], [0, height], [width, height]], np.float32)
+    o = np.zeros_like(m)
+    _lib.check(_lib.lib().orb_undistort_points(ptr(m), 4, C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), ptr(d), d.shape[0],
+                                               ptr(o), 0), "orb_undistort_points")
+    return min(o[0, 0], o[2, 0]), max(o[1, 0], o[3, 0]), min(o[0, 1], o[1, 1]), max(o[2, 1], o[3, 1])

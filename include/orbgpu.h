@@ -383,6 +383,17 @@ int orb_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch,
                        int rgb_order, int variant, int batch, uint8_t *dst, int dst_pitch, size_t dst_stride, int loc,
                        void *stream);
 
+/* ref: Frame::UndistortKeyPoints, src/Frame.cc:409-439: cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) over
+ * the key points' pt (everything else of the KeyPoint is copied); `mvKeysUn = mvKeys` when dist_coef[0] == 0.
+ * fx, fy, cx, cy are mK's float entries, dist_coef = mDistCoef (k1, k2, p1, p2 [, k3]; src/Tracking.cc:427-438).
+ * Arithmetic = OpenCV >= 3.x (double precision, 5 iterations, gives up on a point whose radial factor turns negative);
+ * pinned against cv2 4.13.0.  orb_undistort_points is the same on bare (x,y) pairs: the four image corners of
+ * Frame::ComputeImageBounds (src/Frame.cc:441-468).  loc = where the arrays live (ORB_DEVICE: asynchronous, default stream). */
+int orb_undistort_keypoints(const orb_keypoint *keys, int n, float fx, float fy, float cx, float cy,
+                            const float *dist_coef, int ndist, orb_keypoint *keys_un, int loc);
+int orb_undistort_points(const float *xy, int n, float fx, float fy, float cx, float cy,
+                         const float *dist_coef, int ndist, float *xy_un, int loc);
+
 /* ---- map-point descriptor selection ------------------------------------------ */
 
 /* ref: MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:224-285: among the N descriptors observing a map

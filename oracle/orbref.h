@@ -68,6 +68,8 @@ int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t *off, int 
 /* cv::cvtColor X2GRAY, 8-bit (orbref_color.cpp) */
 int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, int channels, int rgb_order, int variant,
                           uint8_t *dst, int dst_pitch);
+/* cv::undistortPoints(src, dst, K, D, noArray(), K) (orbref_undistort.cpp) */
+int orbref_undistort_points(const float *xy, int n, float fx, float fy, float cx, float cy, const float *dist, int ndist, float *out);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

@@ -609,3 +609,13 @@ def cvt_color_gray(img, rgb_order=True, variant=0):
     out = np.zeros((h, w), np.uint8)
     _check(lib().orbref_cvt_color_gray(ptr(img), w, h, img.strides[0], ch, int(rgb_order), variant, ptr(out), w), "cvt_color_gray")
     return out
+
+
+def undistort_points(xy, fx, fy, cx, cy, dist):
+    """cv::undistortPoints(xy, K, dist, None, K) as Frame::UndistortKeyPoints calls it."""
+    p = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    d = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(p)
+    _check(lib().orbref_undistort_points(ptr(p), p.shape[0], C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), ptr(d),
+                                         d.shape[0], ptr(out)), "undistort_points")
+    return out
