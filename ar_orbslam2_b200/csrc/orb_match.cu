@@ -264,6 +264,57 @@ int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t 
     return rc;
 }
 
+// ref: Marker::searchMatches (ORB_SLAM2/src/Marker.cc:314-349) and naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:70-102):
+// brute-force best / second-best of every query (keys2) over the train set (keys1), accepted when
+// `min_dist <= (unsigned int)(sec_dist * 0.8) && min_dist <= 50`; sec_dist stays INT_MAX with fewer than two train rows.
+__global__ void k_ratio_accept(int nq, const int32_t *__restrict__ d1, const int64_t *__restrict__ i1, const int32_t *__restrict__ d2,
+                               const int64_t *__restrict__ i2, double ratio, int max_dist, int32_t *__restrict__ train_idx,
+                               int32_t *__restrict__ dist) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const unsigned int min_dist = i1[q] < 0 ? 0x7fffffffu : (unsigned int)d1[q];
+    const unsigned int sec_dist = i2[q] < 0 ? 0x7fffffffu : (unsigned int)d2[q];
+    const bool ok = i1[q] >= 0 && min_dist <= (unsigned int)(sec_dist * ratio) && min_dist <= (unsigned int)max_dist;
+    train_idx[q] = ok ? (int32_t)i1[q] : -1;
+    dist[q] = i1[q] < 0 ? 0x7fffffff : d1[q];
+}
+
+int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio, int max_dist,
+                             int loc, int32_t *train_idx, int32_t *dist) {
+    ORB_REQUIRE(n_query >= 0 && n_train >= 0 && (n_query == 0 || (query && train_idx && dist)) && (train || n_train == 0), ORB_ERR_INVALID,
+                "bad argument");
+    if (n_query == 0) return ORB_OK;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
+    Top2Scratch scratch;
+    DevBuf dq, dt, tmp, out;
+    const uint8_t *d_q = query, *d_t = train;
+    int32_t *o_idx = train_idx, *o_dist = dist;
+    if (loc == ORB_HOST) {
+        ORB_CUDA_TRY(dq.alloc((size_t)n_query * 32)); ORB_CUDA_TRY(dt.alloc((size_t)n_train * 32)); ORB_CUDA_TRY(out.alloc((size_t)n_query * 8));
+        ORB_CUDA_TRY(cudaMemcpy(dq.p, query, (size_t)n_query * 32, cudaMemcpyHostToDevice));
+        if (n_train) ORB_CUDA_TRY(cudaMemcpy(dt.p, train, (size_t)n_train * 32, cudaMemcpyHostToDevice));
+        d_q = (const uint8_t *)dq.p; d_t = (const uint8_t *)dt.p;
+        o_idx = (int32_t *)out.p; o_dist = o_idx + n_query;
+    }
+    ORB_CUDA_TRY(tmp.alloc((size_t)n_query * 24));
+    int64_t *t_i1 = (int64_t *)tmp.p, *t_i2 = t_i1 + n_query;
+    int32_t *t_d1 = (int32_t *)(t_i2 + n_query), *t_d2 = t_d1 + n_query;
+    int rc = top2_device(d_q, n_query, d_t, n_train, 0, t_d1, t_i1, t_d2, t_i2, 0, &scratch);
+    if (rc == ORB_OK) {
+        k_ratio_accept<<<(n_query + 127) / 128, 128>>>(n_query, t_d1, t_i1, t_d2, t_i2, ratio, max_dist, o_idx, o_dist);
+        cudaError_t e2 = cudaGetLastError();
+        if (e2 == cudaSuccess && loc == ORB_HOST) {
+            e2 = cudaMemcpy(train_idx, o_idx, (size_t)n_query * 4, cudaMemcpyDeviceToHost);
+            if (e2 == cudaSuccess) e2 = cudaMemcpy(dist, o_dist, (size_t)n_query * 4, cudaMemcpyDeviceToHost);
+        } else if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(0);
+        if (e2 != cudaSuccess) { set_error("orb_search_matches_ratio: %s", cudaGetErrorString(e2)); rc = ORB_ERR_CUDA; }
+    }
+    if (scratch.buf) cudaFree(scratch.buf);
+    return rc;
+}
+
 int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx, const int32_t *second_dist,
                    const int64_t *second_idx, int32_t *out_best_dist, int64_t *out_best_idx, int32_t *out_second_dist,
                    int64_t *out_second_idx, int loc) {

@@ -143,3 +143,16 @@ def ComputeDistinctiveDescriptors(descriptors: np.ndarray, offsets: np.ndarray):
     row, med = np.zeros(n, np.int32), np.zeros(n, np.int32)
     _lib.check(_lib.lib().orb_distinctive_descriptors(ptr(d), ptr(off), n, ORB_HOST, ptr(row), ptr(med)), "orb_distinctive_descriptors")
     return row, med
+
+
+def searchMatches(descp1: np.ndarray, descp2: np.ndarray, ratio: float = 0.8, max_dist: int = 50):
+    """Marker::searchMatches (ref Marker.cc:314-349) / naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:70-102) on the GPU: descp1 =
+    train (marker) descriptors, descp2 = query (frame) descriptors.  Returns the DMatch list as arrays
+    (queryIdx, trainIdx, distance) in the reference's push_back order."""
+    t = np.ascontiguousarray(descp1, np.uint8).reshape(-1, 32)
+    q = np.ascontiguousarray(descp2, np.uint8).reshape(-1, 32)
+    idx, dist = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
+    _lib.check(_lib.lib().orb_search_matches_ratio(ptr(t), len(t), ptr(q), len(q), C.c_double(ratio), max_dist, ORB_HOST, ptr(idx),
+                                                   ptr(dist)), "orb_search_matches_ratio")
+    keep = np.nonzero(idx >= 0)[0].astype(np.int32)
+    return keep, idx[keep], dist[keep].astype(np.float32)

@@ -369,6 +369,17 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
                       const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
                       int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
 
+/* ---- marker / AR brute-force matching ------------------------------------------ */
+
+/* ref: Marker::searchMatches (src/Marker.cc:314-349) and naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:70-102): for every
+ * query descriptor (keys2/descp2) the best and second-best train descriptor (keys1/descp1) with strict `<` updates in
+ * train order, accepted when `min_dist <= (unsigned int)(sec_dist * ratio) && min_dist <= max_dist` (0.8 and 50 in the
+ * reference; sec_dist stays INT_MAX with fewer than two train rows).  train_idx[i] = matched train row (DMatch.trainIdx)
+ * or -1, dist[i] = min_dist (DMatch.distance; INT_MAX with no train row).  The caller pushes DMatch(i, train_idx[i], 0,
+ * dist[i]) for the accepted i in ascending order.                                                                 */
+int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio,
+                             int max_dist, int loc, int32_t *train_idx, int32_t *dist);
+
 /* ---- colour -> grey in front of the extractor ---------------------------------- */
 
 /* ref: cvtColor(mImGray, mImGray, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) in

@@ -65,6 +65,8 @@ int orbref_vocab_transform(const orbref_vocab *v, const uint8_t *desc, int n, in
                            double *bow_value, int32_t *n_bow, int32_t *fv_node, int32_t *fv_off, int32_t *fv_feat, int32_t *n_fv);
 /* MapPoint::ComputeDistinctiveDescriptors (orbref_mappoint.cpp) */
 int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t *off, int npoints, int32_t *best_row, int32_t *best_median);
+int orbref_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio, int max_dist,
+                                int32_t *train_idx, int32_t *dist);
 /* cv::cvtColor X2GRAY, 8-bit (orbref_color.cpp) */
 int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, int channels, int rgb_order, int variant,
                           uint8_t *dst, int dst_pitch);

@@ -619,3 +619,13 @@ def undistort_points(xy, fx, fy, cx, cy, dist):
     _check(lib().orbref_undistort_points(ptr(p), p.shape[0], C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), ptr(d),
                                          d.shape[0], ptr(out)), "undistort_points")
     return out
+
+
+def search_matches_ratio(train, query, ratio=0.8, max_dist=50):
+    """Marker::searchMatches / naive_nn_search2 (restatement; parity unpinned, see orbref_mappoint.cpp)."""
+    t = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
+    q = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
+    idx, dist = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
+    _check(lib().orbref_search_matches_ratio(ptr(t), len(t), ptr(q), len(q), C.c_double(ratio), max_dist, ptr(idx), ptr(dist)),
+           "search_matches_ratio")
+    return idx, dist

@@ -49,3 +49,25 @@ extern "C" int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t
     }
     return ORB_OK;
 }
+
+// ref: Marker::searchMatches, ORB_SLAM2/src/Marker.cc:314-349 (= naive_nn_search2, AR-1.3/src/ORBMatcher.cpp:70-102), on flat
+// arrays.  hamdist2 (Marker.cc:351-359) is cv::HammingLUT over 32 bytes = the bit count of the XOR.  PARITY UNPINNED for this
+// function: Marker.cc needs OpenCV's legacy / features2d / calib3d modules and cannot be compiled here; this is a line-by-line
+// restatement.
+extern "C" int orbref_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio,
+                                           int max_dist, int32_t *train_idx, int32_t *dist) {
+    for (int i = 0; i < n_query; i++) {
+        unsigned int min_dist = INT_MAX, sec_dist = INT_MAX;
+        int min_idx = -1, sec_idx = -1;
+        for (int j = 0; j < n_train; j++) {
+            const unsigned int d = (unsigned int)dist256(query + 32 * (size_t)i, train + 32 * (size_t)j);
+            if (d < min_dist) { sec_dist = min_dist; sec_idx = min_idx; min_dist = d; min_idx = j; }
+            else if (d < sec_dist) { sec_dist = d; sec_idx = j; }
+        }
+        (void)sec_idx;
+        const bool ok = min_idx >= 0 && min_dist <= (unsigned int)(sec_dist * ratio) && min_dist <= (unsigned int)max_dist;
+        train_idx[i] = ok ? min_idx : -1;
+        dist[i] = (int32_t)min_dist;
+    }
+    return ORB_OK;
+}

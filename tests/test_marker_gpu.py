@@ -1,0 +1,34 @@
+"""GPU parity of orb_search_matches_ratio (Marker::searchMatches / naive_nn_search2) against the oracle."""
+import numpy as np
+import pytest
+
+from ar_orbslam2_b200.matcher import searchMatches
+from oracle import orbref
+
+pytestmark = pytest.mark.gpu
+
+
+def marker_case(seed, n_train=300, n_query=1200):
+    rng = np.random.default_rng(seed)
+    train = rng.integers(0, 256, (n_train, 32), dtype=np.uint8)
+    if n_train > 10:
+        train[5] = train[4]                                  # duplicate train rows: best == second -> ratio test fails
+    query = rng.integers(0, 256, (n_query, 32), dtype=np.uint8)
+    if n_train:
+        src = rng.integers(0, n_train, n_query // 2)
+        bits = np.unpackbits(train[src], axis=1)
+        for i in range(len(src)):
+            bits[i, rng.choice(256, int(rng.integers(0, 70)), replace=False)] ^= 1
+        query[: len(src)] = np.packbits(bits, axis=1)
+    return train, query
+
+
+@pytest.mark.parametrize("seed,nt,nq", [(0, 300, 1200), (1, 1, 50), (2, 2, 64), (3, 0, 10), (4, 1000, 3000), (5, 257, 1)])
+def test_gpu_equals_oracle(seed, nt, nq):
+    train, query = marker_case(seed, nt, nq)
+    qi, ti, d = searchMatches(train, query)
+    oi, od = orbref.search_matches_ratio(train, query)
+    keep = np.nonzero(oi >= 0)[0]
+    assert np.array_equal(qi, keep) and np.array_equal(ti, oi[keep]) and np.array_equal(d, od[keep].astype(np.float32))
+    if nt >= 2:
+        assert len(keep) > 0 or nq < 20
