@@ -257,7 +257,8 @@ static size_t fast_smem_layout(FastLevel &fl) {
     size_t off = (size_t)th * FT_PB;
     auto carve = [&](size_t bytes) { off = (off + 15) & ~(size_t)15; const size_t o = off; off += bytes; return (int)o; };
     fl.off_vmap = carve((size_t)(fl.hCell + 2) * FV_PB + 16);
-    fl.off_flags = carve((size_t)fl.hCell * nwc * 4);
+    fl.off_flags = 0;   // (the per-word flag array of earlier versions is gone: survivors are appended at test time)
+    (void)nwc;
     fl.off_survH = carve((size_t)fl.wCell * fl.hCell * 2);
     fl.off_survL = carve((size_t)fl.wCell * fl.hCell * 2);
     return (off + 15) & ~(size_t)15;
@@ -297,7 +298,6 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
 
     uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
     uint8_t *vmap = fsm + g.off_vmap;                                   // computed region + 1 px apron
-    uint32_t *flags = reinterpret_cast<uint32_t *>(fsm + g.off_flags);  // per word: bit 8j+7 = pixel j is H, 8j+6 = L
     uint16_t *survH = reinterpret_cast<uint16_t *>(fsm + g.off_survH);  // code = y << 7 | x (computed-region coords)
     uint16_t *survL = reinterpret_cast<uint16_t *>(fsm + g.off_survL);  // bit 14: also on the H list; bit 15: kept
 
@@ -342,7 +342,8 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     for (;;) {
         // ---- 2. compass test at thr, 4 pixels per thread and step.  Lanes: A = (px0, px2), B = (px1, px3).
         //   H <=> c - max(min(U, D), min(L, R)) > t        L <=> min(max(U, D), max(L, R)) - c > t
-        int cnt = 0;   // H survivors | L survivors << 16 of this thread
+        //   A word with survivors takes its range of the two lists with one shared-memory atomic (both counters in one word,
+        //   H low / L high) and writes the codes on the spot; the order of the lists is irrelevant.
         {
             const uint32_t tb = (uint32_t)thr * 0x00010001u + 0x80008000u;
             for (int u = tid; u < nunits; u += FAST_T) {
@@ -361,34 +362,16 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
                 const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
                 const int lo = 3 + sft - 4 * w, hi = lo + cw;                                         // valid bytes [lo, hi)
                 const uint32_t vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
-                const uint32_t f = (~Hb & vm) | ((~Lb & vm) >> 1);
-                flags[u] = f;
-                cnt += __popc(f & 0x80808080u) + (__popc(f & 0x40404040u) << 16);
-            }
-        }
-        {
-            // list positions: a warp scan of the per-thread counts and one shared-memory atomic per warp for its range (both
-            // counters in one word, H low / L high); the order of the lists is irrelevant
-            int incl = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            int wbase = 0;
-            if (lane == 31 && incl) wbase = atomicAdd(&s_cnt, incl);
-            wbase = __shfl_sync(0xffffffffu, wbase, 31);
-            const int pos = wbase + incl - cnt;
-            int pH = pos & 0xffff, pL = pos >> 16;
-            for (int u = tid; u < nunits; u += FAST_T) {
-                const uint32_t f = flags[u];
-                if (!f) continue;
-                const int yy = dU.div(u), w = u - yy * nWc + w0;
-                const int code0 = (yy << 7) + 4 * w - 3 - sft;       // + j = code of pixel j
-                for (uint32_t m = f & 0x80808080u; m; m &= m - 1) survH[pH++] = (uint16_t)(code0 + ((__ffs(m) - 1) >> 3));
-                for (uint32_t m = f & 0x40404040u; m; m &= m - 1) {
-                    const int bit = __ffs(m) - 1;
-                    survL[pL++] = (uint16_t)((code0 + (bit >> 3)) | (((f >> (bit + 1)) & 1) << 14));
+                const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
+                if (fH | fL) {
+                    const int pos = atomicAdd(&s_cnt, __popc(fH) + (__popc(fL) << 16));
+                    int pH = pos & 0xffff, pL = pos >> 16;
+                    const int code0 = (yy << 7) + 4 * w - 3 - sft;       // + j = code of pixel j
+                    for (uint32_t m = fH; m; m &= m - 1) survH[pH++] = (uint16_t)(code0 + ((__ffs(m) - 1) >> 3));
+                    for (uint32_t m = fL; m; m &= m - 1) {
+                        const int bit = __ffs(m) - 1;
+                        survL[pL++] = (uint16_t)((code0 + (bit >> 3)) | (((fH >> bit) & 1) << 14));
+                    }
                 }
             }
         }
@@ -943,33 +926,50 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
 // Orientation + descriptor, one warp per kept keypoint, no shared memory: the intensity-centroid moments read the
 // 31x31 disc of the level straight from L1/L2 (lane = column), the 256 rotated test pairs sample the blurred plane.
 // ------------------------------------------------------------------------------------------
+struct DescLevel {   // what k_describe needs of one level
+    long long interior_off;
+    int cap_end, kept_off, pitch;   // cap_end = sum of kept_cap over levels <= this one (flat slot -> level)
+    float scale, size;
+};
+struct DescParams {   // by value: lives in the constant bank, no dependent global loads before the warp knows its key point
+    int nlevels, kept_frame;
+    long long pyr_frame;
+    DescLevel lv[ORB_MAX_LEVELS];
+};
+
 __global__ void __launch_bounds__(DESC_WARPS * 32)
-k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, const Geom *__restrict__ G,
+k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, const DescParams P,
            const Kept *__restrict__ kept, const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp,
            uint8_t *__restrict__ out_desc, int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.y;
     // flat slot -> (level, index) over the per-level kept capacities
     int slot = blockIdx.x * DESC_WARPS + warp;
+    if (slot >= P.lv[P.nlevels - 1].cap_end) return;
     int level = 0;
-    while (level < G->nlevels && slot >= G->lv[level].kept_cap) { slot -= G->lv[level].kept_cap; level++; }
-    if (level >= G->nlevels) return;
-    const uint32_t *kc = kept_count + (size_t)b * G->nlevels;
-    if (slot >= (int)kc[level]) return;
-    int base = 0, total = 0;
-    for (int l = 0; l < G->nlevels; l++) {
-        if (l < level) base += kc[l];
-        total += kc[l];
+#pragma unroll
+    for (int l = 0; l < ORB_MAX_LEVELS - 1; l++) level += (l < P.nlevels - 1 && slot >= P.lv[l].cap_end);
+    if (level > 0) slot -= P.lv[level - 1].cap_end;
+    // kept counts of all levels: lane l holds level l's, an inclusive warp scan gives this level's output base and the total
+    const uint32_t *kc = kept_count + (size_t)b * P.nlevels;
+    const int mine = lane < P.nlevels ? (int)kc[lane] : 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < ORB_MAX_LEVELS; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
     }
+    if (slot >= __shfl_sync(0xffffffffu, mine, level)) return;
+    const int base = __shfl_sync(0xffffffffu, incl - mine, level), total = __shfl_sync(0xffffffffu, incl, P.nlevels - 1);
     if (base == 0 && slot == 0 && lane == 0) out_n[b] = total;   // first non-empty level's first warp
     const int oidx = base + slot;
     if (oidx >= capacity) {
         if (lane == 0) atomicOr(err, ERRF_OUT_OVERFLOW);
         return;
     }
-    const LevelGeom &g = G->lv[level];
-    const Kept kp = kept[(size_t)b * G->kept_frame + g.kept_off + slot];
-    const size_t plane = (size_t)b * G->pyr_frame + g.interior_off + (ptrdiff_t)kp.y * g.pitch + kp.x;
+    const DescLevel &g = P.lv[level];
+    const Kept kp = kept[(size_t)b * P.kept_frame + g.kept_off + slot];
+    const size_t plane = (size_t)b * P.pyr_frame + g.interior_off + (ptrdiff_t)kp.y * g.pitch + kp.x;
 
     // ---- IC_Angle (ref :73-98): lanes own columns u = lane-15 .. of the 31-wide disc
     int m10 = 0, m01 = 0;
@@ -1531,8 +1531,16 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         prof_mark(ex, 4);
         for (int l = 0; l < G.nlevels; l++) launch_blur(l, st);
     }
+    DescParams dp;
+    dp.nlevels = G.nlevels; dp.kept_frame = G.kept_frame; dp.pyr_frame = G.pyr_frame;
+    for (int l = 0, acc = 0; l < ORB_MAX_LEVELS; l++) {
+        const LevelGeom &lg = G.lv[l < G.nlevels ? l : G.nlevels - 1];
+        if (l < G.nlevels) acc += lg.kept_cap;
+        dp.lv[l].interior_off = lg.interior_off; dp.lv[l].cap_end = acc; dp.lv[l].kept_off = lg.kept_off; dp.lv[l].pitch = lg.pitch;
+        dp.lv[l].scale = lg.scale; dp.lv[l].size = lg.size;
+    }
     k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
-        ex->d_pyr, ex->d_blur, ex->d_geom, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
+        ex->d_pyr, ex->d_blur, dp, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
     ex->launches++;
     prof_mark(ex, 5);
     ORB_CUDA_TRY(cudaGetLastError());
