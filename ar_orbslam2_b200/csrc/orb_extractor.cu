@@ -335,8 +335,16 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
 
     // words of a tile row that hold computed pixels: bytes [3 + sft, 3 + sft + cw)
     const int w0 = (3 + sft) >> 2, nWc = ((2 + sft + cw) >> 2) - w0 + 1;
+    // thread -> (word column w, row group rg): nRg = FAST_T / nWc row groups, the few threads beyond nRg * nWc idle in stage 2
     const FastDiv dU(nWc);
-    const int nunits = ch * nWc;
+    const int nRg = dU.div(FAST_T);
+    const int rg0 = dU.div(tid), w = tid - rg0 * nWc + w0;
+    const int rg = rg0 < nRg ? rg0 : ch;   // idle threads start past the last row
+    uint32_t vm;                           // bytes of this column's words that are computed pixels: [lo, hi)
+    {
+        const int lo = 3 + sft - 4 * w, hi = lo + cw;
+        vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
+    }
 
     int thr = g.ini_th, nH = 0, nL = 0;
     for (;;) {
@@ -346,8 +354,8 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         //   H low / L high) and writes the codes on the spot; the order of the lists is irrelevant.
         {
             const uint32_t tb = (uint32_t)thr * 0x00010001u + 0x80008000u;
-            for (int u = tid; u < nunits; u += FAST_T) {
-                const int yy = dU.div(u), w = u - yy * nWc + w0;
+            // thread = (word column, row group): the column's validity mask and the row pointer step are loop invariants
+            for (int yy = rg; yy < ch; yy += nRg) {
                 const uint32_t *r = tileW + (yy + 3) * TPW + w;
                 const uint32_t C = r[0], P = r[-1], N = r[1], U = r[-3 * TPW], D = r[3 * TPW];
                 const uint32_t cA = __byte_perm(C, 0, 0x4240), cB = __byte_perm(C, 0, 0x4341);
@@ -360,8 +368,6 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
                 // lane bit 15 set <=> NOT a survivor (no carries between lanes: every lane stays in [0x7f01, 0x81fe])
                 const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
                 const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
-                const int lo = 3 + sft - 4 * w, hi = lo + cw;                                         // valid bytes [lo, hi)
-                const uint32_t vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
                 const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
                 if (fH | fL) {
                     const int pos = atomicAdd(&s_cnt, __popc(fH) + (__popc(fL) << 16));
