@@ -179,9 +179,13 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
         irb[m] = y * 24 + x;
         aL[m] = i < 121 ? (int)imgL[(ptrdiff_t)(y0 + y) * gl.pitch + xl0 + x] : 0;
     }
-    for (int i = lane; i < 11 * 21; i += 32) {
-        const int y = i / 21, x = i - y * 21;
-        IR[y * 24 + x] = imgR[(ptrdiff_t)(y0 + y) * gr.pitch + xr0 + x];
+    if (lane < 21) {   // lane = column of the 21-wide right strip: 11 independent row loads, no index arithmetic
+        const uint8_t *pr = imgR + (ptrdiff_t)y0 * gr.pitch + xr0 + lane;
+        uint8_t v[11];
+#pragma unroll
+        for (int y = 0; y < 11; y++) v[y] = pr[(ptrdiff_t)y * gr.pitch];
+#pragma unroll
+        for (int y = 0; y < 11; y++) IR[y * 24 + lane] = v[y];
     }
     const int cL = __shfl_sync(0xffffffffu, aL[1], 60 - 32);   // window pixel 60 = (5, 5)
     __syncwarp();
@@ -205,18 +209,21 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
 #pragma unroll
         for (int k = 0; k < 6; k++) pk[k] += __shfl_xor_sync(0xffffffffu, pk[k], sft);
     }
-    float dists[11];
+    // every lane holds all 11 sums; lane k < 11 takes the k-th and the warp picks the first minimum (ref :588-592: strict '<'
+    // over ascending incR) as the minimum of (sum << 4 | k); the parabola's three samples come back by shuffle
+    uint32_t mine = pk[0];
 #pragma unroll
-    for (int k = 0; k < 11; k++) dists[k] = (float)((pk[k >> 1] >> (16 * (k & 1))) & 0xffffu);
-    int bestS = 0x7fffffff, bestinc = 0;
+    for (int k = 1; k < 6; k++) mine = (lane >> 1) == k ? pk[k] : mine;
+    mine = (mine >> (16 * (lane & 1))) & 0xffffu;
+    uint32_t key = lane < 11 ? (mine << 4) | (uint32_t)lane : 0xffffffffu;
 #pragma unroll
-    for (int k = 0; k < 11; k++)
-        if (dists[k] < (float)bestS) { bestS = (int)dists[k]; bestinc = k - 5; }
+    for (int sft = 8; sft > 0; sft >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, sft));
+    key = __shfl_sync(0xffffffffu, key, 0);   // lanes 16..31 reduced among themselves
+    const int bestS = (int)(key >> 4), bestk = (int)(key & 15u), bestinc = bestk - 5;
     if (bestinc == -L || bestinc == L) return;                 // ref :597-598
-    float d1 = 0, d2 = 0, d3 = 0;
-#pragma unroll
-    for (int k = 1; k < 10; k++)
-        if (k == bestinc + 5) { d1 = dists[k - 1]; d2 = dists[k]; d3 = dists[k + 1]; }
+    const float fm = (float)mine;
+    const float d1 = __shfl_sync(0xffffffffu, fm, bestk - 1), d2 = __shfl_sync(0xffffffffu, fm, bestk),
+                d3 = __shfl_sync(0xffffffffu, fm, bestk + 1);
     // ref :605: (dist1-dist3)/(2.0f*(dist1+dist3-2.0f*dist2)); NaN (0/0) passes the +-1 test below
     const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
     if (deltaR < -1 || deltaR > 1) return;
