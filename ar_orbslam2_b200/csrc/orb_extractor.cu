@@ -34,6 +34,17 @@ void set_error(const char *fmt, ...) {
 // (per-lane addresses would serialise in the constant cache)
 __device__ __align__(16) int8_t d_pattern[ORB_PATTERN_INTS];
 __constant__ int c_umax[16];
+// IC_Angle as word loads: the 31x31 disc of a key point spans 9 aligned words on each of its 31 rows = 279 (row, word)
+// tasks, 9 per lane.  Entry [a][t] (a = alignment of the disc's left edge, t = task) = {u-weights, v-weights (signed bytes,
+// 0 outside the disc)}; the word's address is arithmetic (row t/9 - 15, word t%9) so pixel loads do not wait for the table;
+// tasks 279..287 are no-ops (zero weights, clamped to the last real word).
+constexpr int MOM_TASKS = 288;
+__device__ uint2 d_moment_tab[4 * MOM_TASKS];
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {   // unsigned pixels x signed weights
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // ------------------------------------------------------------------------------------------
 // Pyramid.  Each thread produces one aligned 32-bit word (4 pixels) of a padded plane row, so
@@ -979,17 +990,21 @@ k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, co
 
     // ---- IC_Angle (ref :73-98): lanes own columns u = lane-15 .. of the 31-wide disc
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int u = lane - 15, au = abs(u);
-        const uint8_t *c = pyr + plane + u;
-        m10 = u * c[0];
+    {
+        const int a = (kp.x - 15) & 3;
+        const uint8_t *c = pyr + plane - 15 - a;                      // 4-byte aligned: plane rows are, and so is interior column 0
+        const uint2 *tab = d_moment_tab + a * MOM_TASKS + lane;
+        uint32_t px[MOM_TASKS / 32];
 #pragma unroll
-        for (int v = 1; v <= 15; v++) {
-            if (au <= c_umax[v]) {
-                const int vp = c[v * g.pitch], vm = c[-v * g.pitch];
-                m10 += u * (vp + vm);
-                m01 += v * (vp - vm);
-            }
+        for (int i = 0; i < MOM_TASKS / 32; i++) {
+            const int t = min(lane + 32 * i, 31 * 9 - 1), r = (t * 7282) >> 16, wi = t - 9 * r;   // r = t / 9 for t < 279
+            px[i] = *reinterpret_cast<const uint32_t *>(c + (ptrdiff_t)(r - 15) * g.pitch + 4 * wi);
+        }
+#pragma unroll
+        for (int i = 0; i < MOM_TASKS / 32; i++) {
+            const uint2 e = __ldg(tab + 32 * i);
+            m10 = dp4a_us(px[i], (int)e.x, m10);
+            m01 = dp4a_us(px[i], (int)e.y, m01);
         }
     }
 #pragma unroll
@@ -1330,6 +1345,22 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_blur, cudaEventDisableTiming));
     ex->overlap = getenv("ORBGPU_SERIAL") == nullptr;
     TRY_ALLOC(cudaMemcpyToSymbol(c_umax, ex->umax, sizeof(ex->umax)));
+    {
+        std::vector<uint2> tab(4 * MOM_TASKS);
+        for (int a = 0; a < 4; a++) {
+            for (int t = 31 * 9; t < MOM_TASKS; t++) tab[a * MOM_TASKS + t] = make_uint2(0, 0);   // no-op: zero weights
+            for (int t = 0; t < 31 * 9; t++) {
+                const int v = t / 9 - 15, wi = t % 9, xoff = 4 * wi - 15 - a;
+                uint32_t wu = 0, wv = 0;
+                for (int j = 0; j < 4; j++) {
+                    const int u = xoff + j;
+                    if (abs(u) <= ex->umax[abs(v)]) { wu |= (uint32_t)(uint8_t)(int8_t)u << (8 * j); wv |= (uint32_t)(uint8_t)(int8_t)v << (8 * j); }
+                }
+                tab[a * MOM_TASKS + t] = make_uint2(wu, wv);
+            }
+        }
+        TRY_ALLOC(cudaMemcpyToSymbol(d_moment_tab, tab.data(), tab.size() * sizeof(uint2)));
+    }
     TRY_ALLOC(cudaMalloc(&ex->d_geom, sizeof(Geom)));
     // sizes below are monotone in the image size except the kept pool (aspect dependent): bound it
     size_t kept_frame = 0;
