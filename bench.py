@@ -32,6 +32,12 @@ MBF, FX = 386.1448, 718.856   # ref: ORB_SLAM2/Examples/Stereo/KITTI00-02.yaml:8
 STAGES = ["h2d", "pyramid", "fast_cells", "octree", "describe", "d2h"]
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376), from the committed ncu
+# launch list profiles/r1j_launches.csv (same command as this bench, serial schedule).  Scaled by frames when --batch differs.
+NCU_DRAM_BYTES_PER_288_FRAMES = {"pyramid": (134.5 + 117.2 + 447.6 + 167.7) * 1e6, "fast_cells": (391.9 + 3.0) * 1e6,
+                                 "octree": (15.9 + 10.8) * 1e6, "describe": (475.6 + 193.8 + 840.5 + 31.9) * 1e6}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -623,7 +629,10 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / hbm_peak,
+                     "traffic": NCU_DRAM_BYTES_PER_288_FRAMES.get(dom, 0) * NF / 288.0 or None,
+                     "traffic_source": "profiles/r1j_launches.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches)",
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom]},
         "roofline_step": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak,
                           "algorithmic_bytes_per_frame": step_alg_bytes, "formula": "P*(1+2S)+60N (SURVEY 8d)"},
