@@ -73,6 +73,39 @@ class OrbLastPoints(C.Structure):
                 ("octave", C.c_void_p), ("angle", C.c_void_p), ("descriptors", C.c_void_p), ("obs_positive", C.c_void_p)]
 
 
+class OrbFrustumCamera(C.Structure):
+    _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float),
+                ("max_y", C.c_float), ("mbf", C.c_float), ("log_scale_factor", C.c_float)]
+
+
+class OrbFrustumPoints(C.Structure):
+    _fields_ = [("n", C.c_int32), ("world_pos", C.c_void_p), ("normal", C.c_void_p), ("max_distance", C.c_void_p),
+                ("min_distance", C.c_void_p), ("consider", C.c_void_p)]
+
+
+def frustum_args(cam: dict, world_pos, normal, max_distance, min_distance, consider=None):
+    """(OrbFrustumCamera, OrbFrustumPoints, keep-alive list) from numpy inputs; cam has Rcw[9], tcw[3], Ow[3] and the scalars."""
+    c = OrbFrustumCamera()
+    c.Rcw[:] = [float(x) for x in np.asarray(cam["Rcw"], np.float32).reshape(9)]
+    c.tcw[:] = [float(x) for x in np.asarray(cam["tcw"], np.float32).reshape(3)]
+    c.Ow[:] = [float(x) for x in np.asarray(cam["Ow"], np.float32).reshape(3)]
+    for k in ("fx", "fy", "cx", "cy", "min_x", "max_x", "min_y", "max_y", "mbf", "log_scale_factor"):
+        setattr(c, k, float(np.float32(cam[k])))
+    wp = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+    nr = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    mx = np.ascontiguousarray(max_distance, np.float32)
+    mn = np.ascontiguousarray(min_distance, np.float32)
+    co = None if consider is None else np.ascontiguousarray(consider, np.uint8)
+    p = OrbFrustumPoints(wp.shape[0], wp.ctypes.data, nr.ctypes.data, mx.ctypes.data, mn.ctypes.data, None if co is None else co.ctypes.data)
+    return c, p, [wp, nr, mx, mn, co]
+
+
+def frustum_outputs(n):
+    return (np.zeros(n, np.uint8), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32),
+            np.zeros(n, np.float32))
+
+
 def optr(a):
     """pointer or NULL"""
     return None if a is None else a.ctypes.data_as(C.c_void_p)

@@ -1,0 +1,137 @@
+// liborbgpu: Frame::isInFrustum for all local map points of a frame.
+//
+// ref: ORB_SLAM2/src/Frame.cc:274-330, MapPoint::PredictScale (src/MapPoint.cc:357-366), caller Tracking::SearchLocalPoints
+// (src/Tracking.cc:1527-1539).  One thread per map point.  The cv::Mat algebra of the reference (3x3 * 3x1 products, L2 norm,
+// dot product) accumulates in double and rounds to float, which is written out explicitly here; everything is compiled with
+// --fmad=false.  logf restates glibc's algorithm (sysdeps/ieee754/flt-32/e_logf.c: 16-entry table, degree-3 polynomial in
+// double): verified bit-identical to the host libm for every positive finite float, with and without FMA contraction.
+#include "orb_common.cuh"
+
+using namespace orbgpu;
+
+namespace {
+
+__constant__ double c_logf_tab[16][2] = {
+    {0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2}, {0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2},
+    {0x1.49539f0f010b0p+0, -0x1.01eae7f513a67p-2}, {0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3},
+    {0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3}, {0x1.25e227b0b8ea0p+0, -0x1.1aa2bc79c8100p-3},
+    {0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4}, {0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4},
+    {0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5}, {0x1p+0, 0x0p+0},
+    {0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5},  {0x1.ca4b31f026aa0p-1, 0x1.c5e53aa362eb4p-4},
+    {0x1.b2036576afce6p-1, 0x1.526e57720db08p-3},  {0x1.9c2d163a1aa2dp-1, 0x1.bc2860d224770p-3},
+    {0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2},  {0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2}};
+
+__device__ float glibc_logf(float x) {
+    uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.0f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return -__int_as_float(0x7f800000);                                          // log(+-0) = -inf
+        if (ix == 0x7f800000u) return x;                                                              // log(inf) = inf
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return __int_as_float(0x7fc00000);           // negative or NaN
+        ix = __float_as_uint(__fmul_rn(x, 0x1p23f));                                                  // subnormal: normalise
+        ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (tmp >> 19) & 15, k = (int32_t)tmp >> 23;
+    const uint32_t iz = ix - (tmp & (0x1ffu << 23));
+    const double invc = c_logf_tab[i][0], logc = c_logf_tab[i][1], z = (double)__uint_as_float(iz);
+    const double r = z * invc - 1, y0 = logc + (double)k * 0x1.62e42fefa39efp-1, r2 = r * r;
+    double y = 0x1.5575b0be00b6ap-2 * r + -0x1.ffffef20a4123p-2;
+    y = -0x1.00ea348b88334p-2 * r2 + y;
+    y = y * r2 + (y0 + r);
+    return (float)y;
+}
+
+__global__ void k_is_in_frustum(const orb_frustum_camera cam, int n, const float *__restrict__ wp, const float *__restrict__ nrm,
+                                const float *__restrict__ maxd, const float *__restrict__ mind, const uint8_t *__restrict__ consider,
+                                float limit, uint8_t *__restrict__ in_view, float *__restrict__ px, float *__restrict__ py,
+                                float *__restrict__ pxr, int *__restrict__ level, float *__restrict__ vcos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bool ok = !consider || consider[i];
+    float u = 0, v = 0, ur = 0, vc = 0;
+    int lvl = 0;
+    if (ok) {
+        const float P[3] = {wp[3 * i], wp[3 * i + 1], wp[3 * i + 2]};
+        float Pc[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {   // mRcw * P + mtcw: the product in double (cv::gemm), then a float addition
+            double s = 0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) s += (double)cam.Rcw[3 * r + k] * (double)P[k];
+            Pc[r] = __fadd_rn((float)s, cam.tcw[r]);
+        }
+        ok = !(Pc[2] < 0.0f);                                                         // ref :288-289
+        const float invz = __fdiv_rn(1.0f, Pc[2]);
+        u = __fadd_rn(__fmul_rn(__fmul_rn(cam.fx, Pc[0]), invz), cam.cx);             // ref :293-294
+        v = __fadd_rn(__fmul_rn(__fmul_rn(cam.fy, Pc[1]), invz), cam.cy);
+        ok = ok && !(u < cam.min_x || u > cam.max_x) && !(v < cam.min_y || v > cam.max_y);
+        const float maxDistance = __fmul_rn(1.2f, maxd[i]), minDistance = __fmul_rn(0.8f, mind[i]);
+        const float PO[3] = {__fsub_rn(P[0], cam.Ow[0]), __fsub_rn(P[1], cam.Ow[1]), __fsub_rn(P[2], cam.Ow[2])};
+        double s2 = 0, sd = 0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) { s2 += (double)PO[k] * (double)PO[k]; sd += (double)PO[k] * (double)nrm[3 * i + k]; }
+        const float dist = (float)sqrt(s2);                                           // cv::norm(PO), ref :305
+        ok = ok && !(dist < minDistance || dist > maxDistance);
+        vc = (float)(sd / (double)dist);                                              // PO.dot(Pn)/dist, ref :313
+        ok = ok && !(vc < limit);
+        const float ratio = __fdiv_rn(maxd[i], dist);                                 // MapPoint::PredictScale
+        lvl = (int)ceilf(__fdiv_rn(glibc_logf(ratio), cam.log_scale_factor));
+        ur = __fsub_rn(u, __fmul_rn(cam.mbf, invz));                                  // ref :324
+    }
+    in_view[i] = ok ? 1 : 0;
+    px[i] = ok ? u : 0.0f; py[i] = ok ? v : 0.0f; pxr[i] = ok ? ur : 0.0f; vcos[i] = ok ? vc : 0.0f;
+    level[i] = ok ? lvl : 0;
+}
+
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 1); }
+};
+
+}  // namespace
+
+extern "C" int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float viewing_cos_limit, int loc,
+                                 uint8_t *in_view, float *proj_x, float *proj_y, float *proj_xr, int32_t *level, float *view_cos) {
+    ORB_REQUIRE(cam && pts && pts->n >= 0, ORB_ERR_INVALID, "bad argument");
+    const int n = pts->n;
+    if (n == 0) return ORB_OK;
+    ORB_REQUIRE(pts->world_pos && pts->normal && pts->max_distance && pts->min_distance && in_view && proj_x && proj_y && proj_xr &&
+                    level && view_cos, ORB_ERR_INVALID, "null array");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
+    const int blocks = (n + 127) / 128;
+    if (loc == ORB_DEVICE) {
+        k_is_in_frustum<<<blocks, 128>>>(*cam, n, pts->world_pos, pts->normal, pts->max_distance, pts->min_distance, pts->consider,
+                                         viewing_cos_limit, in_view, proj_x, proj_y, proj_xr, level, view_cos);
+        ORB_CUDA_TRY(cudaGetLastError());
+        return ORB_OK;
+    }
+    // host arrays: one staging buffer in, one out
+    const size_t fin = (size_t)n * 8 * 4, bin = fin + (size_t)n, fout = (size_t)n * 5 * 4, bout = fout + (size_t)n;
+    DevBuf din, dout;
+    ORB_CUDA_TRY(din.alloc(bin));
+    ORB_CUDA_TRY(dout.alloc(bout));
+    float *d_wp = (float *)din.p, *d_nr = d_wp + 3 * (size_t)n, *d_mx = d_nr + 3 * (size_t)n, *d_mn = d_mx + n;
+    uint8_t *d_cons = (uint8_t *)(d_mn + n);
+    ORB_CUDA_TRY(cudaMemcpy(d_wp, pts->world_pos, (size_t)n * 12, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d_nr, pts->normal, (size_t)n * 12, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d_mx, pts->max_distance, (size_t)n * 4, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d_mn, pts->min_distance, (size_t)n * 4, cudaMemcpyHostToDevice));
+    if (pts->consider) ORB_CUDA_TRY(cudaMemcpy(d_cons, pts->consider, (size_t)n, cudaMemcpyHostToDevice));
+    float *o_x = (float *)dout.p, *o_y = o_x + n, *o_xr = o_y + n, *o_vc = o_xr + n;
+    int *o_lv = (int *)(o_vc + n);
+    uint8_t *o_in = (uint8_t *)(o_lv + n);
+    k_is_in_frustum<<<blocks, 128>>>(*cam, n, d_wp, d_nr, d_mx, d_mn, pts->consider ? d_cons : nullptr, viewing_cos_limit, o_in, o_x, o_y,
+                                     o_xr, o_lv, o_vc);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpy(proj_x, o_x, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(proj_y, o_y, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(proj_xr, o_xr, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(view_cos, o_vc, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(level, o_lv, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpy(in_view, o_in, (size_t)n, cudaMemcpyDeviceToHost));
+    return ORB_OK;
+}

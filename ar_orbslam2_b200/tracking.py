@@ -223,3 +223,16 @@ def ComputeImageBounds(width: int, height: int, fx: float, fy: float, cx: float,
     _lib.check(_lib.lib().orb_undistort_points(ptr(m), 4, C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), ptr(d), d.shape[0],
                                                ptr(o), 0), "orb_undistort_points")
     return min(o[0, 0], o[2, 0]), max(o[1, 0], o[3, 0]), min(o[0, 1], o[1, 1]), max(o[2, 1], o[3, 1])
+
+
+def isInFrustum(cam: dict, world_pos, normal, max_distance, min_distance, viewing_cos_limit: float = 0.5, consider=None):
+    """Frame::isInFrustum (ref Frame.cc:274-330) for all local map points of a frame on the GPU (the loop of
+    Tracking::SearchLocalPoints, ref Tracking.cc:1527-1539).  cam: dict with Rcw (3x3), tcw, Ow, fx, fy, cx, cy, min_x, max_x,
+    min_y, max_y, mbf, log_scale_factor.  Returns (in_view, proj_x, proj_y, proj_xr, level, view_cos) = the MapPoint tracking
+    fields, ready for ORBmatcher.SearchByProjectionPoints."""
+    from ._abi import frustum_args, frustum_outputs
+    c, p, keep = frustum_args(cam, world_pos, normal, max_distance, min_distance, consider)
+    o = frustum_outputs(p.n)
+    _lib.check(_lib.lib().orb_is_in_frustum(C.byref(c), C.byref(p), C.c_float(viewing_cos_limit), 0, *[ptr(a) for a in o]),
+               "orb_is_in_frustum")
+    return o

@@ -405,6 +405,33 @@ int orb_undistort_keypoints(const orb_keypoint *keys, int n, float fx, float fy,
 int orb_undistort_points(const float *xy, int n, float fx, float fy, float cx, float cy,
                          const float *dist_coef, int ndist, float *xy_un, int loc);
 
+/* ref: Frame::isInFrustum(MapPoint*, viewingCosLimit), src/Frame.cc:274-330, for all local map points of a frame in one
+ * call (the loop of Tracking::SearchLocalPoints, src/Tracking.cc:1527-1539; the caller keeps its mnLastFrameSeen / isBad
+ * pre-checks and passes consider[i] = 0 for the points it skips).  The camera block is the Frame's mRcw (row major), mtcw,
+ * mOw, the static intrinsics and image bounds, mbf and mfLogScaleFactor; a point is its GetWorldPos(), GetNormal(),
+ * mfMaxDistance and mfMinDistance (the 1.2 / 0.8 factors of Get*DistanceInvariance are applied here).  Outputs are
+ * the MapPoint tracking fields the reference fills (:321-327): in_view = mbTrackInView, proj_x/proj_y/proj_xr =
+ * mTrackProjX/Y/XR, level = mnTrackScaleLevel (MapPoint::PredictScale, src/MapPoint.cc:357-366: this fork does not clamp
+ * it), view_cos = mTrackViewCos -- exactly the arrays orb_track_points takes.  Arithmetic: cv::Mat products and norms
+ * accumulate in double and round to float like cv::gemm / cv::norm, float expressions are evaluated without FMA
+ * contraction, logf is glibc's algorithm (bit-identical to the host libm on every finite float).                      */
+typedef struct orb_frustum_camera {
+    float Rcw[9], tcw[3], Ow[3];
+    float fx, fy, cx, cy;
+    float min_x, max_x, min_y, max_y;
+    float mbf, log_scale_factor;
+} orb_frustum_camera;
+typedef struct orb_frustum_points {
+    int32_t n;
+    const float *world_pos;      /* [n][3] */
+    const float *normal;         /* [n][3] */
+    const float *max_distance;   /* [n] mfMaxDistance */
+    const float *min_distance;   /* [n] mfMinDistance */
+    const uint8_t *consider;     /* [n] or NULL = all */
+} orb_frustum_points;
+int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float viewing_cos_limit, int loc,
+                      uint8_t *in_view, float *proj_x, float *proj_y, float *proj_xr, int32_t *level, float *view_cos);
+
 /* ---- map-point descriptor selection ------------------------------------------ */
 
 /* ref: MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:224-285: among the N descriptors observing a map

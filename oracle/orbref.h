@@ -67,6 +67,9 @@ int orbref_vocab_transform(const orbref_vocab *v, const uint8_t *desc, int n, in
 int orbref_distinctive_descriptors(const uint8_t *desc, const int32_t *off, int npoints, int32_t *best_row, int32_t *best_median);
 int orbref_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio, int max_dist,
                                 int32_t *train_idx, int32_t *dist);
+/* Frame::isInFrustum + MapPoint::PredictScale (orbref_frustum.cpp) */
+int orbref_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float limit, uint8_t *in_view, float *proj_x,
+                         float *proj_y, float *proj_xr, int32_t *level, float *view_cos);
 /* cv::cvtColor X2GRAY, 8-bit (orbref_color.cpp) */
 int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, int channels, int rgb_order, int variant,
                           uint8_t *dst, int dst_pitch);

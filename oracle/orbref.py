@@ -629,3 +629,32 @@ def search_matches_ratio(train, query, ratio=0.8, max_dist=50):
     _check(lib().orbref_search_matches_ratio(ptr(t), len(t), ptr(q), len(q), C.c_double(ratio), max_dist, ptr(idx), ptr(dist)),
            "search_matches_ratio")
     return idx, dist
+
+
+# ---- Frame::isInFrustum: the restated oracle and the reference's compiled Frame.cc ----
+def is_in_frustum(cam, world_pos, normal, max_distance, min_distance, limit=0.5, consider=None):
+    from ar_orbslam2_b200._abi import frustum_args, frustum_outputs
+    c, p, keep = frustum_args(cam, world_pos, normal, max_distance, min_distance, consider)
+    o = frustum_outputs(p.n)
+    _check(lib().orbref_is_in_frustum(C.byref(c), C.byref(p), C.c_float(limit), *[ptr(a) for a in o]), "is_in_frustum")
+    return o
+
+
+def refm_is_in_frustum(frame, Tcw, fx, fy, cx, cy, mbf, log_scale_factor, world_pos, normal, max_distance, min_distance, limit=0.5,
+                       consider=None):
+    """The reference's own Frame::isInFrustum (compiled Frame.cc).  `frame` = a Frame built with ReferenceSourceBackend.
+    Returns (cam15 = mRcw|mtcw|mOw as the reference derived them, outputs)."""
+    from ar_orbslam2_b200._abi import frustum_outputs
+    L = ReferenceSourceBackend().L
+    wp = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+    nr = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    mx, mn = np.ascontiguousarray(max_distance, np.float32), np.ascontiguousarray(min_distance, np.float32)
+    co = None if consider is None else np.ascontiguousarray(consider, np.uint8)
+    T = np.ascontiguousarray(Tcw, np.float32).reshape(4, 4)
+    cam = np.zeros(15, np.float32)
+    o = frustum_outputs(wp.shape[0])
+    f = C.c_float
+    _check(L.refm_is_in_frustum(frame._h, ptr(T), f(fx), f(fy), f(cx), f(cy), f(mbf), f(log_scale_factor), wp.shape[0], ptr(wp), ptr(nr),
+                                ptr(mx), ptr(mn), None if co is None else ptr(co), f(limit), ptr(cam), *[ptr(a) for a in o]),
+           "refm_is_in_frustum")
+    return cam, o

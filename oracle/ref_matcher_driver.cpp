@@ -622,6 +622,41 @@ int refm_search_by_sim3(refm_frame *kf1, refm_frame *kf2, float s12, const float
 }
 
 // ref ORBmatcher::DescriptorDistance, ORBmatcher.cc:1650-1666
+// Frame::isInFrustum (src/Frame.cc:274-330) from the reference's compiled Frame.cc, one call per map point like
+// Tracking::SearchLocalPoints (src/Tracking.cc:1527-1539).  The pose goes through the reference's Frame::SetPose /
+// UpdatePoseMatrices (:260-272); cam_out receives the mRcw / mtcw / mOw it derived so that the flat interfaces see the same
+// camera.  MapPoint::PredictScale is the stub's restatement of src/MapPoint.cc:357-366.
+int refm_is_in_frustum(refm_frame *f, const float *Tcw16, float fx, float fy, float cx, float cy, float mbf, float log_scale_factor,
+                       int n, const float *world_xyz, const float *normal_xyz, const float *max_dist, const float *min_dist,
+                       const uint8_t *consider, float limit, float *cam_out15, uint8_t *in_view, float *proj_x, float *proj_y,
+                       float *proj_xr, int32_t *level, float *view_cos) {
+    set_statics(f);
+    Frame &F = f->F;
+    Frame::fx = fx; Frame::fy = fy; Frame::cx = cx; Frame::cy = cy;
+    F.mbf = mbf; F.mfLogScaleFactor = log_scale_factor;
+    cv::Mat T(4, 4, CV_32F);
+    memcpy(T.data, Tcw16, 64);
+    F.SetPose(T);
+    for (int r = 0; r < 3; r++) {
+        for (int c = 0; c < 3; c++) cam_out15[3 * r + c] = F.mRcw.at<float>(r, c);
+        cam_out15[9 + r] = F.mtcw.at<float>(r);
+        cam_out15[12 + r] = F.mOw.at<float>(r);
+    }
+    for (int i = 0; i < n; i++) {
+        in_view[i] = 0; proj_x[i] = proj_y[i] = proj_xr[i] = view_cos[i] = 0.0f; level[i] = 0;
+        if (consider && !consider[i]) continue;
+        MapPoint m;
+        m.worldPos = cv::Mat(3, 1, CV_32F); m.normal = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; k++) { m.worldPos.at<float>(k) = world_xyz[3 * i + k]; m.normal.at<float>(k) = normal_xyz[3 * i + k]; }
+        m.mfMaxDistance = max_dist[i]; m.mfMinDistance = min_dist[i];
+        if (F.isInFrustum(&m, limit)) {
+            in_view[i] = m.mbTrackInView; proj_x[i] = m.mTrackProjX; proj_y[i] = m.mTrackProjY; proj_xr[i] = m.mTrackProjXR;
+            level[i] = m.mnTrackScaleLevel; view_cos[i] = m.mTrackViewCos;
+        }
+    }
+    return 0;
+}
+
 int refm_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist) {
     for (int i = 0; i < n; i++) dist[i] = ORBmatcher::DescriptorDistance(desc_row(a + (size_t)i * 32), desc_row(b + (size_t)i * 32));
     return 0;
