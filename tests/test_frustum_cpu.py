@@ -28,14 +28,14 @@ def test_oracle_equals_reference_frame_cc(seed):
 
 def glibc_logf_np(x):
     """numpy restatement of glibc's logf (sysdeps/ieee754/flt-32/e_logf.c) = the algorithm of csrc/orb_frustum.cu::glibc_logf."""
-    T = np.array([[0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2], [0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2],
-                  [0x1.49539f0f010b0p+0, -0x1.01eae7f513a67p-2], [0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3],
-                  [0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3], [0x1.25e227b0b8ea0p+0, -0x1.1aa2bc79c8100p-3],
-                  [0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4], [0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4],
-                  [0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5], [1.0, 0.0], [0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5],
-                  [0x1.ca4b31f026aa0p-1, 0x1.c5e53aa362eb4p-4], [0x1.b2036576afce6p-1, 0x1.526e57720db08p-3],
-                  [0x1.9c2d163a1aa2dp-1, 0x1.bc2860d224770p-3], [0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2],
-                  [0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2]])
+    T = np.array([[float.fromhex('0x1.661ec79f8f3bep+0'), float.fromhex('-0x1.57bf7808caadep-2')], [float.fromhex('0x1.571ed4aaf883dp+0'), float.fromhex('-0x1.2bef0a7c06ddbp-2')],
+                  [float.fromhex('0x1.49539f0f010b0p+0'), float.fromhex('-0x1.01eae7f513a67p-2')], [float.fromhex('0x1.3c995b0b80385p+0'), float.fromhex('-0x1.b31d8a68224e9p-3')],
+                  [float.fromhex('0x1.30d190c8864a5p+0'), float.fromhex('-0x1.6574f0ac07758p-3')], [float.fromhex('0x1.25e227b0b8ea0p+0'), float.fromhex('-0x1.1aa2bc79c8100p-3')],
+                  [float.fromhex('0x1.1bb4a4a1a343fp+0'), float.fromhex('-0x1.a4e76ce8c0e5ep-4')], [float.fromhex('0x1.12358f08ae5bap+0'), float.fromhex('-0x1.1973c5a611cccp-4')],
+                  [float.fromhex('0x1.0953f419900a7p+0'), float.fromhex('-0x1.252f438e10c1ep-5')], [1.0, 0.0], [float.fromhex('0x1.e608cfd9a47acp-1'), float.fromhex('0x1.aa5aa5df25984p-5')],
+                  [float.fromhex('0x1.ca4b31f026aa0p-1'), float.fromhex('0x1.c5e53aa362eb4p-4')], [float.fromhex('0x1.b2036576afce6p-1'), float.fromhex('0x1.526e57720db08p-3')],
+                  [float.fromhex('0x1.9c2d163a1aa2dp-1'), float.fromhex('0x1.bc2860d224770p-3')], [float.fromhex('0x1.886e6037841edp-1'), float.fromhex('0x1.1058bc8a07ee1p-2')],
+                  [float.fromhex('0x1.767dcf5534862p-1'), float.fromhex('0x1.4043057b6ee09p-2')]])
     ix = x.view(np.uint32).astype(np.int64)
     tmp = (ix - 0x3f330000) & 0xffffffff
     i = (tmp >> 19) & 15
@@ -43,10 +43,10 @@ def glibc_logf_np(x):
     iz = (ix - (tmp & (0x1ff << 23))) & 0xffffffff
     z = iz.astype(np.uint32).view(np.float32).astype(np.float64)
     r = z * T[i, 0] - 1
-    y0 = T[i, 1] + k.astype(np.float64) * 0x1.62e42fefa39efp-1
+    y0 = T[i, 1] + k.astype(np.float64) * float.fromhex('0x1.62e42fefa39efp-1')
     r2 = r * r
-    y = 0x1.5575b0be00b6ap-2 * r + -0x1.ffffef20a4123p-2
-    y = -0x1.00ea348b88334p-2 * r2 + y
+    y = float.fromhex('0x1.5575b0be00b6ap-2') * r + float.fromhex('-0x1.ffffef20a4123p-2')
+    y = float.fromhex('-0x1.00ea348b88334p-2') * r2 + y
     y = y * r2 + (y0 + r)
     out = y.astype(np.float32)
     out[ix == 0x3f800000] = 0
