@@ -394,6 +394,16 @@ int orb_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch,
                        int rgb_order, int variant, int batch, uint8_t *dst, int dst_pitch, size_t dst_stride, int loc,
                        void *stream);
 
+/* ref: cv::remap(image, rectified, M1, M2, cv::INTER_LINEAR), Examples/ROS/ORB_SLAM2/src/ros_stereo.cc:163-164, with the
+ * CV_32F maps of cv::initUndistortRectifyMap (:107-112): the stereo rectification in front of TrackStereo.  8-bit single
+ * channel; map_x / map_y hold one source coordinate per destination pixel (map_pitch floats per row).  Arithmetic = OpenCV's
+ * fixed-point bilinear remap (1/32-pixel coordinates, 15-bit weights, zero outside the source), pinned against cv2 4.13.0.
+ * `batch` images share the maps (image b at src + b*src_stride / dst + b*dst_stride); loc = where src, maps and dst live;
+ * `stream` is a cudaStream_t (NULL = default), ORB_DEVICE calls are asynchronous on it.                                */
+int orb_remap_linear(const uint8_t *src, int src_width, int src_height, int src_pitch, size_t src_stride,
+                     const float *map_x, const float *map_y, int map_pitch, uint8_t *dst, int dst_width, int dst_height,
+                     int dst_pitch, size_t dst_stride, int batch, int loc, void *stream);
+
 /* ref: Frame::UndistortKeyPoints, src/Frame.cc:409-439: cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) over
  * the key points' pt (everything else of the KeyPoint is copied); `mvKeysUn = mvKeys` when dist_coef[0] == 0.
  * fx, fy, cx, cy are mK's float entries, dist_coef = mDistCoef (k1, k2, p1, p2 [, k3]; src/Tracking.cc:427-438).

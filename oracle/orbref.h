@@ -70,6 +70,9 @@ int orbref_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t
 /* Frame::isInFrustum + MapPoint::PredictScale (orbref_frustum.cpp) */
 int orbref_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float limit, uint8_t *in_view, float *proj_x,
                          float *proj_y, float *proj_xr, int32_t *level, float *view_cos);
+/* cv::remap INTER_LINEAR, 8-bit, CV_32F maps (orbref_remap.cpp) */
+int orbref_remap_linear(const uint8_t *src, int sw, int sh, int spitch, const float *mapx, const float *mapy, int mpitch, uint8_t *dst,
+                        int dw, int dh, int dpitch);
 /* cv::cvtColor X2GRAY, 8-bit (orbref_color.cpp) */
 int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, int channels, int rgb_order, int variant,
                           uint8_t *dst, int dst_pitch);

@@ -658,3 +658,13 @@ def refm_is_in_frustum(frame, Tcw, fx, fy, cx, cy, mbf, log_scale_factor, world_
                                 ptr(mx), ptr(mn), None if co is None else ptr(co), f(limit), ptr(cam), *[ptr(a) for a in o]),
            "refm_is_in_frustum")
     return cam, o
+
+
+def remap_linear(src, map_x, map_y):
+    """cv::remap(src, map_x, map_y, INTER_LINEAR), 8-bit single channel, BORDER_CONSTANT 0."""
+    s = np.ascontiguousarray(src, np.uint8)
+    mx, my = np.ascontiguousarray(map_x, np.float32), np.ascontiguousarray(map_y, np.float32)
+    dh, dw = mx.shape
+    out = np.zeros((dh, dw), np.uint8)
+    _check(lib().orbref_remap_linear(ptr(s), s.shape[1], s.shape[0], s.strides[0], ptr(mx), ptr(my), dw, ptr(out), dw, dh, dw), "remap_linear")
+    return out
