@@ -9,7 +9,8 @@ import weakref
 from ._abi import OrbParams
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liborbgpu.so")
+# ORBGPU_LIB: another build of the same library (A/B timing of a kernel change); never a different implementation
+LIB_PATH = os.environ.get("ORBGPU_LIB") or os.path.join(_HERE, "liborbgpu.so")
 _LIB = None
 
 
@@ -36,6 +37,8 @@ def lib():
         L.orb_extractor_stream.argtypes = [C.c_void_p]
         L.orb_extractor_launch_count.restype = C.c_int64
         L.orb_extractor_launch_count.argtypes = [C.c_void_p]
+        L.orb_extractor_graph_replays.restype = C.c_int64
+        L.orb_extractor_graph_replays.argtypes = [C.c_void_p]
         L.orb_extractor_destroy.argtypes = [C.c_void_p]
         L.orb_extractor_destroy.restype = None
         _LIB = L

@@ -101,6 +101,11 @@ class ORBextractor:
     def launch_count(self) -> int:
         return self._L.orb_extractor_launch_count(self._h)
 
+    @property
+    def graph_replays(self) -> int:
+        """Extractions that ran as one CUDA-graph launch (repeated calls with the same device buffers and geometry)."""
+        return self._L.orb_extractor_graph_replays(self._h)
+
     # --- pyramid (ORBextractor.h:88 mvImagePyramid)
     def level_size(self, level: int, slot: int = 0):
         w, h, p = C.c_int(), C.c_int(), C.c_int()

@@ -374,6 +374,7 @@ def bench_latency(args):
     for _ in range(30):
         t0 = time.perf_counter(); ex(img); t.append(time.perf_counter() - t0)
     out["c1_extract_ms_median"] = 1e3 * float(np.median(t))
+    out["c1_graph_replays"] = int(ex.graph_replays)   # 0 with ORBGPU_NO_GRAPH=1: the same call as 26 plain launches
     exl = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H)
     exr = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H)
     l, r = synth_stereo_pair(W, H, 9)

@@ -120,6 +120,10 @@ int orb_extractor_stage_times(orb_extractor *ex, double *ms, int64_t *calls);
 void *orb_extractor_stream(orb_extractor *ex);
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 int64_t orb_extractor_launch_count(const orb_extractor *ex);
+/* Number of extractions that ran as one CUDA-graph launch: a call that repeats the previous call's arguments (same
+ * device buffers, geometry, batch) is captured once and replayed from then on; kernels inside a replay are counted
+ * by orb_extractor_launch_count as well.  ORBGPU_NO_GRAPH=1 in the environment keeps the plain launches. */
+int64_t orb_extractor_graph_replays(const orb_extractor *ex);
 
 /* ref: public member std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:88), read
  * by Frame::ComputeStereoMatches (src/Frame.cc:476,566,578,583).  Geometry of level `level`

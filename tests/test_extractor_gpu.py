@@ -7,11 +7,12 @@ from ar_orbslam2_b200.synth import synth_frame
 
 pytestmark = pytest.mark.gpu
 
-CONFIGS = [  # (width, height, nfeatures, seed)   SURVEY 8: C1, C2, C3, C1-init
+CONFIGS = [  # (width, height, nfeatures, seed)   SURVEY 8: C1, C2, C3, C1-init, C4
     (640, 480, 1000, 0),
     (1241, 376, 2000, 3),
     (752, 480, 1000, 5),
     (640, 480, 2000, 11),
+    (1920, 1080, 2000, 8),
 ]
 
 
@@ -165,3 +166,43 @@ def test_opencv24_blur_taps_and_saturation(oracle, gpu_lib):
             assert ref.blurred_level(0).max() == 255
         assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
         ex.close()
+
+
+def test_graph_replay_matches_oracle(oracle, gpu_lib, monkeypatch):
+    """Repeated calls at one geometry are captured into a CUDA graph on the second call and replayed afterwards: every
+    replay must still equal the oracle (new frame contents flow through the fixed device buffers), a geometry change must
+    drop the graph, and ORBGPU_NO_GRAPH=1 must keep the plain launches with the same results and launch counts."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    ref = oracle.RefExtractor(1000)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    per_call = None
+    for i, seed in enumerate((31, 32, 33, 34, 35)):
+        img = synth_frame(640, 480, seed)
+        l0 = ex.launch_count
+        gk, gd = ex(img)
+        rk, rd = ref.extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd), f"call {i}"
+        per_call = per_call or ex.launch_count - l0
+        assert ex.launch_count - l0 == per_call == 26       # replays count their kernels as well
+    assert ex.graph_replays == 3                             # call 0 plain, call 1 captured, calls 2-4 replayed
+    img = synth_frame(400, 300, 36)                          # other geometry: graph dropped, plain launches
+    gk, gd = ex(img)
+    rk, rd = ref.extract(img)
+    assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    assert ex.graph_replays == 3
+    for seed in (37, 38, 39):
+        img = synth_frame(400, 300, seed)
+        gk, gd = ex(img)
+        rk, rd = ref.extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    assert ex.graph_replays == 5                             # 37 captured, 38 and 39 replayed
+    ex.close()
+    monkeypatch.setenv("ORBGPU_NO_GRAPH", "1")
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    for seed in (31, 32, 33):
+        img = synth_frame(640, 480, seed)
+        gk, gd = ex(img)
+        rk, rd = ref.extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    assert ex.graph_replays == 0 and ex.launch_count == 3 * 26
+    ex.close()

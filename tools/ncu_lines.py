@@ -16,7 +16,11 @@ for r in csv.reader(out.splitlines()):
         launches.append(cur)
     elif r and r[0] == "Line No":
         hdr = r
-    elif cur is not None and hdr is not None and r and r[0].isdigit():
+    elif cur is not None and hdr is not None and r and r[0].isdigit() and len(r) == len(hdr):
+        try:   # source lines holding quotes (inline asm) can break the CSV row: skip those
+            int(r[hdr.index("# Samples")]), int(r[hdr.index("Instructions Executed")]), int(r[hdr.index("Thread Instructions Executed")])
+        except ValueError:
+            continue
         cur["lines"].append(r)
 iS, iI, iT = hdr.index("# Samples"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 for L in launches:
