@@ -57,6 +57,8 @@ struct Kept {   // a keypoint retained by the quadtree, level coordinates
 
 }  // namespace orbgpu
 
+constexpr size_t ORB_BOUNCE_BYTES = (size_t)1 << 20;
+
 struct orb_extractor {
     orb_params prm;
     int device = 0;
@@ -82,6 +84,7 @@ struct orb_extractor {
     size_t out_cap_elems = 0;
     int *d_err = nullptr;
     int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
+    uint8_t *h_bounce = nullptr;       // pinned landing buffer for the results of small host-output calls
     int last_batch = 0;
     int64_t launches = 0;
     size_t oct_smem = 0;
