@@ -1222,7 +1222,7 @@ static size_t octree_smem_bytes(int maxn) {
 static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_wtab); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
-    cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch);
+    cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch); cudaFree(ex->d_stereo_out);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
     if (ex->h_bounce) cudaFreeHost(ex->h_bounce);
     if (ex->gexec) cudaGraphExecDestroy(ex->gexec);
@@ -1322,6 +1322,19 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_taps, taps.data(), taps.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice, ex->stream));
     ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));   // `taps` and G are stack/heap temporaries
     ex->geom = G;
+    return ORB_OK;
+}
+
+int orbgpu_ensure_out_staging(orb_extractor *ex, int batch, int capacity) {
+    if ((size_t)batch * capacity <= ex->out_cap_elems) return ORB_OK;
+    // grow the staging buffers to the caller's capacity
+    cudaFree(ex->d_out_kp); cudaFree(ex->d_out_desc);
+    ex->d_out_kp = nullptr; ex->d_out_desc = nullptr;
+    if (ex->gexec) { cudaGraphExecDestroy(ex->gexec); ex->gexec = nullptr; }
+    ex->glast = {};
+    ex->out_cap_elems = (size_t)ex->prm.max_batch * capacity;
+    ORB_CUDA_TRY(cudaMalloc(&ex->d_out_kp, ex->out_cap_elems * sizeof(orb_keypoint)));
+    ORB_CUDA_TRY(cudaMalloc(&ex->d_out_desc, ex->out_cap_elems * 32));
     return ORB_OK;
 }
 
@@ -1519,16 +1532,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     uint8_t *o_desc = descriptors;
     int32_t *o_n = n_out;
     if (out_loc == ORB_HOST) {
-        if ((size_t)batch * capacity > ex->out_cap_elems) {
-            // grow the staging buffers to the caller's capacity
-            cudaFree(ex->d_out_kp); cudaFree(ex->d_out_desc);
-            ex->d_out_kp = nullptr; ex->d_out_desc = nullptr;
-            if (ex->gexec) { cudaGraphExecDestroy(ex->gexec); ex->gexec = nullptr; }
-            ex->glast = {};
-            ex->out_cap_elems = (size_t)ex->prm.max_batch * capacity;
-            ORB_CUDA_TRY(cudaMalloc(&ex->d_out_kp, ex->out_cap_elems * sizeof(orb_keypoint)));
-            ORB_CUDA_TRY(cudaMalloc(&ex->d_out_desc, ex->out_cap_elems * 32));
-        }
+        rc = orbgpu_ensure_out_staging(ex, batch, capacity);
+        if (rc != ORB_OK) return rc;
         o_kp = ex->d_out_kp; o_desc = ex->d_out_desc; o_n = ex->d_out_n;
     }
 

@@ -85,6 +85,8 @@ struct orb_extractor {
     int *d_err = nullptr;
     int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
     uint8_t *h_bounce = nullptr;       // pinned landing buffer for the results of small host-output calls
+    float *d_stereo_out = nullptr;     // orb_stereo_frame: uRight[cap] | depth[cap] | n_matched
+    size_t stereo_out_cap = 0;
     int last_batch = 0;
     int64_t launches = 0;
     size_t oct_smem = 0;
@@ -118,3 +120,5 @@ struct orb_extractor {
     int64_t graph_replays = 0;
 };
 
+// grows the handle's device staging for `batch` x `capacity` keypoints + descriptors (drops a captured graph that holds the old pointers)
+int orbgpu_ensure_out_staging(orb_extractor *ex, int batch, int capacity);

@@ -411,4 +411,81 @@ int orb_stereo_match(orb_extractor *left, orb_extractor *right, int slot, const 
     return ORB_OK;
 }
 
+/* One stereo frame through one handle with a single host synchronisation: both images up, both extractions as one batch of
+ * two (a CUDA graph from the third frame on), the association on the device-resident keypoints, all results back through
+ * the pinned landing buffer.  Same results as orb_extract x2 + orb_stereo_match. */
+int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t *image_right, int width, int height,
+                     int pitch_left, int pitch_right, orb_keypoint *keys_left, uint8_t *desc_left, int *n_left,
+                     orb_keypoint *keys_right, uint8_t *desc_right, int *n_right, int capacity, float mbf, float mb,
+                     float *u_right, float *depth, int *n_matched) {
+    ORB_REQUIRE(ex && image_left && image_right && keys_left && desc_left && n_left && keys_right && desc_right && n_right &&
+                    u_right && depth, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(ex->prm.max_batch >= 2, ORB_ERR_INVALID, "orb_stereo_frame needs a handle with max_batch >= 2");
+    ORB_REQUIRE(width > 0 && height > 0 && pitch_left >= width && pitch_right >= width, ORB_ERR_INVALID, "bad image geometry");
+    ORB_REQUIRE(width <= ex->prm.max_width && height <= ex->prm.max_height, ORB_ERR_INVALID,
+                "image %dx%d exceeds the handle's max %dx%d", width, height, ex->prm.max_width, ex->prm.max_height);
+    ORB_REQUIRE(capacity >= 1 && capacity <= 65535, ORB_ERR_INVALID, "bad capacity");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    cudaStream_t st = ex->stream;
+    int rc = orbgpu_ensure_out_staging(ex, 2, capacity);
+    if (rc != ORB_OK) return rc;
+    if (ex->stereo_out_cap < (size_t)capacity) {
+        cudaFree(ex->d_stereo_out);
+        ex->d_stereo_out = nullptr; ex->stereo_out_cap = 0;
+        ORB_CUDA_TRY(cudaMalloc(&ex->d_stereo_out, ((size_t)2 * capacity + 1) * 4));
+        ex->stereo_out_cap = capacity;
+    }
+    // both frames into the handle's source slots 0 and 1 (linear copies when the two pitches agree and fit)
+    int d_pitch = pitch_left;
+    size_t d_stride = (size_t)pitch_left * height;
+    if (pitch_left == pitch_right && 2 * d_stride <= ex->src_bytes) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, image_left, d_stride, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src + d_stride, image_right, d_stride, cudaMemcpyHostToDevice, st));
+    } else {
+        d_pitch = (width + 127) / 128 * 128;
+        d_stride = (size_t)d_pitch * height;
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src, d_pitch, image_left, pitch_left, width, height, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src + d_stride, d_pitch, image_right, pitch_right, width, height, cudaMemcpyHostToDevice, st));
+    }
+    rc = orb_extract_batch(ex, ex->d_src, 2, width, height, d_pitch, d_stride, ORB_DEVICE, ex->d_out_kp, ex->d_out_desc, capacity,
+                           ex->d_out_n, ORB_DEVICE);
+    if (rc != ORB_OK) return rc;
+    float *d_ur = ex->d_stereo_out, *d_dp = d_ur + capacity;
+    int32_t *d_nm = (int32_t *)(d_dp + capacity);
+    rc = orb_stereo_match_batch(ex, 0, ex, 1, 1, ex->d_out_kp, ex->d_out_desc, ex->d_out_n, ex->d_out_kp + capacity,
+                                ex->d_out_desc + (size_t)capacity * 32, ex->d_out_n + 1, capacity, mbf, mb, d_ur, d_dp, d_nm, ORB_DEVICE);
+    if (rc != ORB_OK) return rc;
+    // everything back with asynchronous copies into pinned memory, one synchronisation
+    const size_t kp_bytes = (size_t)2 * capacity * sizeof(orb_keypoint), desc_bytes = (size_t)2 * capacity * 32, f_bytes = (size_t)capacity * 4;
+    const bool bounce = ex->h_bounce && kp_bytes + desc_bytes + 2 * f_bytes + 4 <= ORB_BOUNCE_BYTES;
+    std::vector<uint8_t> big;
+    uint8_t *land = ex->h_bounce;
+    if (!bounce) { big.resize(kp_bytes + desc_bytes + 2 * f_bytes + 4); land = big.data(); }
+    ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, ex->d_out_n, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(land, ex->d_out_kp, kp_bytes, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes, ex->d_out_desc, desc_bytes, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes + desc_bytes, d_ur, 2 * f_bytes + 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    const int flags = ex->h_pinned[0];
+    *n_left = ex->h_pinned[1]; *n_right = ex->h_pinned[2];
+    if (flags) {   // capacity / candidate overflow raised by the extraction kernels
+        cudaMemsetAsync(ex->d_err, 0, sizeof(int), st);
+        set_error("extraction raised error flags 0x%x (capacity %d, needed %d / %d)", flags, capacity, *n_left, *n_right);
+        return ORB_ERR_CAPACITY;
+    }
+    const size_t nl = (size_t)std::min(*n_left, capacity), nr = (size_t)std::min(*n_right, capacity);
+    memcpy(keys_left, land, nl * sizeof(orb_keypoint));
+    memcpy(keys_right, land + (size_t)capacity * sizeof(orb_keypoint), nr * sizeof(orb_keypoint));
+    memcpy(desc_left, land + kp_bytes, nl * 32);
+    memcpy(desc_right, land + kp_bytes + (size_t)capacity * 32, nr * 32);
+    memcpy(u_right, land + kp_bytes + desc_bytes, nl * 4);
+    memcpy(depth, land + kp_bytes + desc_bytes + f_bytes, nl * 4);
+    int32_t nm = 0;
+    memcpy(&nm, land + kp_bytes + desc_bytes + 2 * f_bytes, 4);
+    if (n_matched) *n_matched = nm;
+    if (nm == 0) { set_error("no stereo match accepted (the reference indexes an empty vector here, Frame.cc:630)"); return ORB_ERR_EMPTY; }
+    return ORB_OK;
+}
+
 }  // extern "C"

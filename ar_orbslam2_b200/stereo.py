@@ -9,7 +9,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._abi import ORB_ERR_EMPTY, ptr
+from ._abi import KEYPOINT_DTYPE, ORB_ERR_EMPTY, ptr
 
 
 def ComputeStereoMatches(left, right, keys_left, desc_left, keys_right, desc_right, mbf: float, mb: float, slot: int = 0,
@@ -43,3 +43,28 @@ def stereo_match_batch_device(left, left_slot, right, right_slot, batch, d_keys_
     _lib.check(L.orb_stereo_match_batch(left._h, left_slot, right._h, right_slot, batch, vp(d_keys_l), vp(d_desc_l), vp(d_n_l),
                                         vp(d_keys_r), vp(d_desc_r), vp(d_n_r), capacity, C.c_float(mbf), C.c_float(mb),
                                         vp(d_u_right), vp(d_depth), vp(d_n_matched), 1), "orb_stereo_match_batch")
+
+
+def StereoFrame(extractor, image_left, image_right, mbf: float, mb: float, capacity: int | None = None, allow_empty: bool = False):
+    """The stereo Frame constructor's front end in one call (ref: ORB_SLAM2/src/Frame.cc:83-95: ExtractORB left and right,
+    then ComputeStereoMatches) on ONE handle created with max_batch >= 2: orb_stereo_frame.
+    Returns (keys_left, desc_left, keys_right, desc_right, mvuRight, mvDepth)."""
+    L = _lib.lib()
+    il, ir = image_left, image_right
+    assert il.dtype == np.uint8 and ir.dtype == np.uint8 and il.ndim == 2 and il.shape == ir.shape, "two CV_8UC1 images of one size required"
+    if il.strides[1] != 1:
+        il = np.ascontiguousarray(il)
+    if ir.strides[1] != 1:
+        ir = np.ascontiguousarray(ir)
+    h, w = il.shape
+    cap = capacity or extractor.default_capacity
+    kl, kr = np.zeros(cap, KEYPOINT_DTYPE), np.zeros(cap, KEYPOINT_DTYPE)
+    dl, dr = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
+    ur, dp = np.full(cap, -1, np.float32), np.full(cap, -1, np.float32)
+    nl, nr, nm = C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = L.orb_stereo_frame(extractor._h, ptr(il), ptr(ir), w, h, il.strides[0], ir.strides[0], ptr(kl), ptr(dl), C.byref(nl),
+                            ptr(kr), ptr(dr), C.byref(nr), cap, C.c_float(mbf), C.c_float(mb), ptr(ur), ptr(dp), C.byref(nm))
+    if not (rc == ORB_ERR_EMPTY and allow_empty):
+        _lib.check(rc, "orb_stereo_frame")
+    a, b = nl.value, nr.value
+    return kl[:a].copy(), dl[:a].copy(), kr[:b].copy(), dr[:b].copy(), ur[:a].copy(), dp[:a].copy()

@@ -387,6 +387,15 @@ def bench_latency(args):
         if i >= 5:
             t.append(time.perf_counter() - t0)
     out["c2_stereo_frame_ms_median"] = 1e3 * float(np.median(t))
+    from ar_orbslam2_b200.stereo import StereoFrame
+    ex2 = ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=2)
+    t = []
+    for i in range(35):
+        t0 = time.perf_counter()
+        StereoFrame(ex2, l, r, MBF, mb)
+        if i >= 5:
+            t.append(time.perf_counter() - t0)
+    out["c2_stereo_frame_single_call_ms_median"] = 1e3 * float(np.median(t))   # orb_stereo_frame: one handle, one synchronisation
     out["note"] = "wall clock around blocking calls incl. pageable host copies and the python wrapper; sequential left/right"
     return out
 

@@ -339,6 +339,17 @@ int orb_stereo_match(orb_extractor *left, orb_extractor *right, int slot,
                      const orb_keypoint *keys_right, const uint8_t *desc_right, int n_right,
                      float mbf, float mb, float *u_right, float *depth, int *n_matched);
 
+/* ref: the stereo Frame constructor, src/Frame.cc:62-111: ExtractORB on the left and the right image (two threads, :83-86)
+ * followed by ComputeStereoMatches (:95).  One call, one handle (created with max_batch >= 2), one host synchronisation:
+ * both host images are uploaded into pyramid slots 0 (left) and 1 (right), extracted as one batch of two, associated on the
+ * device-resident keypoints, and all results come back together.  Outputs are those of orb_extract (per camera, `capacity`
+ * entries each) and of orb_stereo_match (u_right / depth: n_left floats).  Same error behaviour: ORB_ERR_CAPACITY with
+ * n_left / n_right holding the required sizes, ORB_ERR_EMPTY when no match survives (ref :630).                      */
+int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t *image_right, int width, int height,
+                     int pitch_left, int pitch_right, orb_keypoint *keys_left, uint8_t *desc_left, int *n_left,
+                     orb_keypoint *keys_right, uint8_t *desc_right, int *n_right, int capacity, float mbf, float mb,
+                     float *u_right, float *depth, int *n_matched);
+
 /* Batched / device-resident form: pair b uses pyramid slot left_slot+b of `left` and
  * right_slot+b of `right` (the two may be the same handle holding 2*batch frames), keypoints at
  * keys_*[b*capacity], counts n_*[b].  loc = where all caller arrays live; with ORB_DEVICE the

@@ -89,3 +89,38 @@ def test_gpu_equals_reference_frame_cc(oracle, gpu_lib):
     assert (rur != -1).sum() > 200
     assert np.array_equal(gur.view(np.uint32), rur.view(np.uint32)) and np.array_equal(gdp.view(np.uint32), rdp.view(np.uint32))
     gl.close(); gr.close()
+
+
+def test_stereo_frame_single_call(oracle, gpu_lib):
+    """orb_stereo_frame (both extractions as one batch of two + association, one synchronisation) against the oracle, over
+    several frames through one handle (plain launches, graph capture, graph replays) and with unequal row pitches."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.stereo import StereoFrame
+    from ar_orbslam2_b200.synth import synth_stereo_pair
+    w, h, nf = 1241, 376, 2000
+    mbf, mb = 386.1448, np.float32(386.1448) / np.float32(718.856)
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=2)
+    for i, seed in enumerate((70, 71, 72, 73)):
+        left, right = synth_stereo_pair(w, h, seed)
+        if i == 3:   # right image as a view with a larger row pitch: the pitched upload path
+            wide = np.zeros((h, w + 39), np.uint8)
+            wide[:, :w] = right
+            right = wide[:, :w]
+        kl, dl, kr, dr, ur, dp = StereoFrame(ex, left, right, mbf, float(mb))
+        rl, rr = oracle.RefExtractor(nf), oracle.RefExtractor(nf)
+        rkl, rdl = rl.extract(np.ascontiguousarray(left))
+        rkr, rdr = rr.extract(np.ascontiguousarray(right))
+        rc, rur, rdp, _, nm = oracle.stereo_match(rl, rr, rkl, rdl, rkr, rdr, mbf, mb)
+        assert rc == 0 and nm > 0
+        assert kl.tobytes() == rkl.tobytes() and kr.tobytes() == rkr.tobytes(), seed
+        assert np.array_equal(dl, rdl) and np.array_equal(dr, rdr), seed
+        assert np.array_equal(ur.view(np.uint32), rur.view(np.uint32)) and np.array_equal(dp.view(np.uint32), rdp.view(np.uint32)), seed
+    assert ex.graph_replays >= 1
+    # capacity too small: reported with the required sizes, nothing truncated silently
+    from ar_orbslam2_b200 import _lib
+    with pytest.raises(_lib.OrbGpuError) as ei:
+        StereoFrame(ex, left, np.ascontiguousarray(right), mbf, float(mb), capacity=500)
+    assert ei.value.code == -4
+    kl2, *_ = StereoFrame(ex, left, np.ascontiguousarray(right), mbf, float(mb))   # the handle is usable afterwards
+    assert kl2.tobytes() == rkl.tobytes()
+    ex.close()
