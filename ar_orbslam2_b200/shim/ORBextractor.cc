@@ -18,12 +18,16 @@ static void Check(int rc, const char *what) {
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
-      mpHandle(nullptr), mMaxWidth(0), mMaxHeight(0), mbMirrorPyramid(true) {
+      mpHandle(nullptr), mpStereoHandle(nullptr), mStereoMaxWidth(0), mStereoMaxHeight(0), mMaxWidth(0), mMaxHeight(0),
+      mbMirrorPyramid(true) {
     mvImagePyramid.resize(nlevels);
     EnsureHandle(1920, 1080);
 }
 
-ORBextractor::~ORBextractor() { orb_extractor_destroy(mpHandle); }
+ORBextractor::~ORBextractor() {
+    orb_extractor_destroy(mpHandle);
+    if (mpStereoHandle) orb_extractor_destroy(mpStereoHandle);
+}
 
 void ORBextractor::EnsureHandle(int width, int height) {
     if (mpHandle && width <= mMaxWidth && height <= mMaxHeight) return;
@@ -51,7 +55,7 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     assert(image.type() == CV_8UC1);                  // ref :991
     EnsureHandle(image.cols, image.rows);
 
-    int capacity = nfeatures + 4 * nlevels + 256, n = 0;
+    int capacity = DefaultCapacity(), n = 0;
     for (;;) {
         mKpBuf.resize((size_t)capacity * sizeof(orb_keypoint));
         mDescBuf.resize((size_t)capacity * 32);
@@ -102,6 +106,53 @@ bool ORBGPU_ComputeStereoMatches(ORBextractor *left, ORBextractor *right, const 
     if (rc == ORB_ERR_EMPTY) return false;
     Check(rc, "orb_stereo_match");
     return true;
+}
+
+orb_extractor *ORBextractor::StereoHandle(int width, int height) {
+    if (mpStereoHandle && width <= mStereoMaxWidth && height <= mStereoMaxHeight) return mpStereoHandle;
+    if (mpStereoHandle) orb_extractor_destroy(mpStereoHandle);
+    mpStereoHandle = nullptr;
+    mStereoMaxWidth = width > mStereoMaxWidth ? width : mStereoMaxWidth;
+    mStereoMaxHeight = height > mStereoMaxHeight ? height : mStereoMaxHeight;
+    orb_params p;
+    std::memset(&p, 0, sizeof(p));
+    p.nfeatures = nfeatures; p.scale_factor = (float)scaleFactor; p.nlevels = nlevels;
+    p.ini_th_fast = iniThFAST; p.min_th_fast = minThFAST;
+    p.max_width = mStereoMaxWidth; p.max_height = mStereoMaxHeight; p.max_batch = 2; p.device = -1; p.blur_taps = 0;
+    Check(orb_extractor_create(&p, &mpStereoHandle), "orb_extractor_create");
+    return mpStereoHandle;
+}
+
+bool ORBGPU_ExtractStereo(ORBextractor *left, const cv::Mat &imLeft, const cv::Mat &imRight, std::vector<cv::KeyPoint> &mvKeys,
+                          cv::Mat &mDescriptors, std::vector<cv::KeyPoint> &mvKeysRight, cv::Mat &mDescriptorsRight, float mbf,
+                          float mb, std::vector<float> &mvuRight, std::vector<float> &mvDepth) {
+    assert(imLeft.type() == CV_8UC1 && imRight.type() == CV_8UC1 && imLeft.cols == imRight.cols && imLeft.rows == imRight.rows);
+    orb_extractor *h = left->StereoHandle(imLeft.cols, imLeft.rows);
+    int capacity = left->DefaultCapacity(), nL = 0, nR = 0, matched = 0, rc = 0;
+    std::vector<unsigned char> kl, kr, dl, dr;
+    for (;;) {
+        kl.resize((size_t)capacity * sizeof(orb_keypoint)); kr.resize(kl.size());
+        dl.resize((size_t)capacity * 32); dr.resize(dl.size());
+        mvuRight.assign(capacity, -1.0f); mvDepth.assign(capacity, -1.0f);
+        rc = orb_stereo_frame(h, imLeft.data, imRight.data, imLeft.cols, imLeft.rows, (int)imLeft.step, (int)imRight.step,
+                              (orb_keypoint *)kl.data(), dl.data(), &nL, (orb_keypoint *)kr.data(), dr.data(), &nR, capacity, mbf, mb,
+                              mvuRight.data(), mvDepth.data(), &matched);
+        if (rc == ORB_ERR_CAPACITY && (nL > capacity || nR > capacity)) { capacity = nL > nR ? nL : nR; continue; }
+        if (rc != ORB_ERR_EMPTY) Check(rc, "orb_stereo_frame");
+        break;
+    }
+    auto fill = [](int n, const std::vector<unsigned char> &k, const std::vector<unsigned char> &d, std::vector<cv::KeyPoint> &keys,
+                   cv::Mat &desc) {
+        keys.resize(n);
+        if (n) std::memcpy((void *)keys.data(), k.data(), (size_t)n * sizeof(orb_keypoint));
+        if (n == 0) { desc.release(); return; }
+        desc.create(n, 32, CV_8U);
+        for (int i = 0; i < n; i++) std::memcpy(desc.ptr(i), d.data() + (size_t)i * 32, 32);
+    };
+    fill(nL, kl, dl, mvKeys, mDescriptors);
+    fill(nR, kr, dr, mvKeysRight, mDescriptorsRight);
+    mvuRight.resize(nL); mvDepth.resize(nL);           // ref :473-474: one entry per left keypoint
+    return rc != ORB_ERR_EMPTY;
 }
 
 }  // namespace ORB_SLAM2

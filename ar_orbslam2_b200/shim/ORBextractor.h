@@ -46,6 +46,8 @@ public:
     // --- additions (not in the reference)
     void SetMirrorPyramid(bool on) { mbMirrorPyramid = on; }
     orb_extractor *Handle() { return mpHandle; }   // for ORBGPU_ComputeStereoMatches
+    int DefaultCapacity() const { return nfeatures + 4 * nlevels + 256; }   // output slots handed to the library (grown on demand)
+    orb_extractor *StereoHandle(int width, int height);   // two-frame handle of ORBGPU_ExtractStereo, created on first use
 
 protected:
     void EnsureHandle(int width, int height);
@@ -63,6 +65,8 @@ protected:
     std::vector<float> mvInvLevelSigma2;
 
     orb_extractor *mpHandle;
+    orb_extractor *mpStereoHandle;
+    int mStereoMaxWidth, mStereoMaxHeight;
     int mMaxWidth, mMaxHeight;
     bool mbMirrorPyramid;
     std::vector<unsigned char> mKpBuf, mDescBuf;
@@ -76,6 +80,16 @@ bool ORBGPU_ComputeStereoMatches(ORBextractor *left, ORBextractor *right, const 
                                  const cv::Mat &mDescriptors, const std::vector<cv::KeyPoint> &mvKeysRight,
                                  const cv::Mat &mDescriptorsRight, float mbf, float mb, std::vector<float> &mvuRight,
                                  std::vector<float> &mvDepth);
+
+// ref: the stereo Frame constructor's front end, Frame.cc:83-95 (ExtractORB on both images in two threads, then
+// ComputeStereoMatches), as ONE library call on a two-frame handle owned by `left` (orb_stereo_frame): both extractions run
+// as one batch, the association reads the device-resident keypoints, the host waits once.  Fills what the three reference
+// calls fill: mvKeys / mDescriptors, mvKeysRight / mDescriptorsRight, mvuRight / mvDepth.  `left` supplies the extractor
+// parameters (the reference builds both extractors with the same ones, Tracking.cc:455-461); mvImagePyramid is not mirrored
+// on this path.  Returns false when no match survived.
+bool ORBGPU_ExtractStereo(ORBextractor *left, const cv::Mat &imLeft, const cv::Mat &imRight, std::vector<cv::KeyPoint> &mvKeys,
+                          cv::Mat &mDescriptors, std::vector<cv::KeyPoint> &mvKeysRight, cv::Mat &mDescriptorsRight, float mbf,
+                          float mb, std::vector<float> &mvuRight, std::vector<float> &mvDepth);
 
 }  // namespace ORB_SLAM2
 

@@ -46,6 +46,20 @@ int main(int argc, char **argv) {
     // the host mirror of level 3 incl. the byte 7 px into the left border, as Frame.cc:583 may touch
     const cv::Mat &l3 = exL.mvImagePyramid[3];
     dump(pre + "_l3.bin", l3.data - 19 * l3.step - 19, (size_t)(l3.rows + 38) * l3.step);
+    // the same frame through the single-call front end (orb_stereo_frame), twice more so that the CUDA-graph replay runs too
+    std::vector<cv::KeyPoint> fkL, fkR;
+    cv::Mat fdL, fdR;
+    std::vector<float> fuR, fdepth;
+    bool fok = true;
+    for (int rep = 0; rep < 3; rep++)
+        fok = ORB_SLAM2::ORBGPU_ExtractStereo(&exL, imLeft, imRight, fkL, fdL, fkR, fdR, mbf, mb, fuR, fdepth) && fok;
+    dump(pre + "_fkl.bin", fkL.data(), fkL.size() * sizeof(cv::KeyPoint));
+    dump(pre + "_fkr.bin", fkR.data(), fkR.size() * sizeof(cv::KeyPoint));
+    dump(pre + "_fdl.bin", fdL.data, (size_t)fdL.rows * 32);
+    dump(pre + "_fdr.bin", fdR.data, (size_t)fdR.rows * 32);
+    dump(pre + "_fur.bin", fuR.data(), fuR.size() * 4);
+    dump(pre + "_fdp.bin", fdepth.data(), fdepth.size() * 4);
+    printf("fused ok=%d\n", (int)fok);
     printf("shim ok=%d nL=%zu nR=%zu scale1=%.9g levels=%d l3=%dx%d step=%zu\n", (int)ok, kL.size(), kR.size(), exL.GetScaleFactors()[1],
            exL.GetLevels(), l3.cols, l3.rows, l3.step);
     return 0;

@@ -35,6 +35,11 @@ def test_cpp_shim_stereo_frame(oracle, gpu_lib, tmp_path):
     assert g("kl", KEYPOINT_DTYPE).tobytes() == kl.tobytes() and g("kr", KEYPOINT_DTYPE).tobytes() == kr.tobytes()
     assert np.array_equal(g("dl", np.uint8).reshape(-1, 32), dl) and np.array_equal(g("dr", np.uint8).reshape(-1, 32), dr)
     assert np.array_equal(g("ur", np.uint32), ur.view(np.uint32)) and np.array_equal(g("dp", np.uint32), dp.view(np.uint32))
+    # ORBGPU_ExtractStereo: the single-call front end leaves the same six results
+    assert "fused ok=1" in out.stdout
+    assert g("fkl", KEYPOINT_DTYPE).tobytes() == kl.tobytes() and g("fkr", KEYPOINT_DTYPE).tobytes() == kr.tobytes()
+    assert np.array_equal(g("fdl", np.uint8).reshape(-1, 32), dl) and np.array_equal(g("fdr", np.uint8).reshape(-1, 32), dr)
+    assert np.array_equal(g("fur", np.uint32), ur.view(np.uint32)) and np.array_equal(g("fdp", np.uint32), dp.view(np.uint32))
     # mvImagePyramid mirror keeps the reference's padded-plane layout (19-px reflect border around the ROI)
     assert np.array_equal(g("l3", np.uint8), rl.pyramid_level(3, True).ravel())
 
