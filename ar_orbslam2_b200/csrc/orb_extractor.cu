@@ -1232,6 +1232,9 @@ static void free_all(orb_extractor *ex) {
     if (ex->ev_blur) cudaEventDestroy(ex->ev_blur);
     if (ex->s_fast) cudaStreamDestroy(ex->s_fast);
     if (ex->s_blur) cudaStreamDestroy(ex->s_blur);
+    for (auto &e : ex->ev_fl) if (e) cudaEventDestroy(e);
+    for (auto &e : ex->ev_ol) if (e) cudaEventDestroy(e);
+    for (auto &q : ex->s_oct) if (q) cudaStreamDestroy(q);
     if (ex->stream) cudaStreamDestroy(ex->stream);
 }
 
@@ -1384,6 +1387,11 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     for (int l = 0; l < params->nlevels; l++) TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_lvl[l], cudaEventDisableTiming));
     TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_fast, cudaEventDisableTiming));
     TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_blur, cudaEventDisableTiming));
+    for (int l = 0; l < ORB_MAX_LEVELS; l++) {
+        TRY_ALLOC(cudaStreamCreateWithFlags(&ex->s_oct[l], cudaStreamNonBlocking));
+        TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_fl[l], cudaEventDisableTiming));
+        TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_ol[l], cudaEventDisableTiming));
+    }
     ex->overlap = getenv("ORBGPU_SERIAL") == nullptr;
     ex->use_graph = getenv("ORBGPU_NO_GRAPH") == nullptr;
     TRY_ALLOC(cudaMemcpyToSymbol(c_umax, ex->umax, sizeof(ex->umax)));
@@ -1581,6 +1589,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err, l0);
         ex->launches++;
     };
+    const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
     auto enqueue = [&]() -> int {   // everything of one extraction between the input copy and the output copy
         ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
         ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
@@ -1592,13 +1601,25 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
                 ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
                 ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
                 launch_fast(l, ex->s_fast);
+                if (small_call) {
+                    // latency mode: level l's quadtree (one CTA per frame, 34 us for a VGA level 0, 200 us for a 1080p one)
+                    // starts on its own stream as soon as that level's candidates exist, beside the rest of the cascade
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_fl[l], ex->s_fast));
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_oct[l], ex->ev_fl[l], 0));
+                    launch_octree(l, 1, ex->s_oct[l]);
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_ol[l], ex->s_oct[l]));
+                }
                 ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
                 launch_blur(l, ex->s_blur);
             }
-            ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
             ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));
-            ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fast, 0));
-            launch_octree(0, G.nlevels, st);   // (one launch per level on a side stream was measured: no gain)
+            if (small_call) {
+                for (int l = 0; l < G.nlevels; l++) ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_ol[l], 0));
+            } else {
+                ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
+                ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fast, 0));
+                launch_octree(0, G.nlevels, st);   // (one launch per level on a side stream was measured at 288 frames: no gain)
+            }
             ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
         } else {
             prof_mark(ex, 1);
@@ -1626,7 +1647,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     const orb_extractor::GraphKey key = {d_images, d_stride, d_pitch, batch, width, height, capacity, o_kp, o_desc, o_n};
     // a graph pays where the launches themselves are the wait (single frames, stereo pairs); large batches measured 1 %
     // slower as a graph than as stream launches (92.5 -> 91.7 k frames/s at 288 frames), so they keep the streams
-    const bool graphable = ex->use_graph && ex->overlap && !ex->profiling && (size_t)batch * width * height <= ((size_t)4 << 20);
+    const bool graphable = ex->use_graph && ex->overlap && !ex->profiling && small_call;
     if (graphable && ex->gexec && key == ex->gkey) {
         ORB_CUDA_TRY(cudaGraphLaunch(ex->gexec, st));
         ex->launches += ex->g_nodes;

@@ -103,6 +103,9 @@ struct orb_extractor {
     cudaStream_t s_fast = nullptr, s_blur = nullptr;
     cudaEvent_t ev_lvl[ORB_MAX_LEVELS] = {}, ev_fast = nullptr, ev_blur = nullptr;
     bool overlap = true;               // off while per-stage profiling is on (stage times need a serial schedule)
+    // small calls (latency mode): the quadtree of level l runs on its own stream as soon as that level's FAST cells are done
+    cudaStream_t s_oct[ORB_MAX_LEVELS] = {};
+    cudaEvent_t ev_fl[ORB_MAX_LEVELS] = {}, ev_ol[ORB_MAX_LEVELS] = {};
     // CUDA graph of one extraction (two memsets + the 26 launches with their fork/join on the side streams): captured the
     // second time a call repeats the previous call's arguments, replayed from then on; any other call runs the plain
     // launches.  One graph launch instead of 28 enqueues + 20 event operations is what a single-frame call waits for.
