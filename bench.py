@@ -141,6 +141,26 @@ def run_reference(args):
         t_total += dt
         frames += n
     v = frames / t_total
+    # beside it, on ONE core (its driver's allocator is process-global): the reference's own ORBextractor.cc compiled unmodified
+    # (oracle/_ref, OpenCV primitives = the cv2-pinned restatements) against the port on the same frames, extraction only
+    ref_src = None
+    try:
+        from oracle import orbref
+        if orbref.ref_available():
+            fr = [pairs[i][0] for i in range(4)]
+            a, b = orbref.ReferenceExtractor(NFEAT), orbref.RefExtractor(NFEAT)
+            a.extract(fr[0]); b.extract(fr[0])
+            t0 = time.perf_counter()
+            for f in fr:
+                a.extract(f)
+            t1 = time.perf_counter()
+            for f in fr:
+                b.extract(f)
+            t2 = time.perf_counter()
+            ref_src = {"reference_source_frames_per_s_1core": len(fr) / (t1 - t0), "port_frames_per_s_1core": len(fr) / (t2 - t1),
+                       "what": "extraction only (no stereo association), 4 frames of 1241x376, one thread each"}
+    except Exception as exc:   # the checker's extra, never a reason to lose the line
+        ref_src = {"unavailable": repr(exc)}
     sample = f"{sample_pairs} synthetic stereo pairs ({2 * sample_pairs} frames) per step, one pair per thread"
     line = {
         "impl": "reference", "metric": "orb_stereo_extract_frames_per_s", "value": v, "unit": "frames/s", "n_gpus": args.gpus,
@@ -149,8 +169,10 @@ def run_reference(args):
         "config": workload_config(sample_pairs),
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference cannot be compiled here (needs OpenCV 2.4 C++/Eigen/Pangolin); this is the oracle, the CPU "
-                "restatement of ORBextractor.cc + Frame::ComputeStereoMatches, on all host cores",
+        "reference_source": ref_src,
+        "note": "the reference's build (cmake + OpenCV 2.4 C++ + Eigen + Pangolin) cannot run here; this is the oracle, the CPU "
+                "restatement of ORBextractor.cc + Frame::ComputeStereoMatches, on all host cores; `reference_source` times the "
+                "reference's own ORBextractor.cc (compiled against the cv2-pinned OpenCV stand-ins) beside the port on one core",
     }
     print(json.dumps(line))
 
