@@ -38,6 +38,17 @@ NCU_DRAM_BYTES_PER_288_FRAMES = {"pyramid": (134.4 + 117.2 + 447.6 + 168.2) * 1e
                                  "octree": (15.9 + 10.9) * 1e6, "describe": (475.5 + 193.6 + 840.5 + 31.9) * 1e6}
 
 
+_JSON_FD = None
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -174,7 +185,7 @@ def run_reference(args):
                 "restatement of ORBextractor.cc + Frame::ComputeStereoMatches, on all host cores; `reference_source` times the "
                 "reference's own ORBextractor.cc (compiled against the cv2-pinned OpenCV stand-ins) beside the port on one core",
     }
-    print(json.dumps(line))
+    emit_json(line)
 
 
 def workload_config(batch_pairs):
@@ -721,7 +732,7 @@ def run_ours(args):
         "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{sample_pairs} synthetic stereo pairs x{reps} through the oracle, one pair per thread"},
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -739,6 +750,13 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
     ap.add_argument("--db-rows", type=int, default=8_000_000, help="descriptor-database rows per GPU for the Hamming leg (256 MB)")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: anything libraries print there at the C level (NCCL's version banner under
+    # torchrun, for one) goes to stderr instead.  The JSON line is written to the saved descriptor.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
