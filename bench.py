@@ -251,14 +251,14 @@ def bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrie
     return r
 
 
-def bench_c1(args, torch, dev, local):
-    """Config C1: monocular 640x480, nFeatures 1000 -- device-resident batched extraction, frames/s."""
+def bench_batched(torch, dev, local, w, h, nfeat, nb, steps, label, seed0, with_stages=False):
+    """Device-resident batched extraction of nb frames of w x h, frames/s (configs C1 and C4)."""
+    from ar_orbslam2_b200 import _lib
     from ar_orbslam2_b200.extractor import ORBextractor
     from ar_orbslam2_b200.synth import synth_frame
-    w, h, nb, steps = 640, 480, 512, 5
-    frames = np.stack([synth_frame(w, h, 300 + i) for i in range(16)])
-    d_img = torch.from_numpy(np.ascontiguousarray(np.tile(frames, (nb // 16, 1, 1)))).to(dev)   # 157 MB > L2
-    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb, device=local)
+    frames = np.stack([synth_frame(w, h, seed0 + i) for i in range(16)])
+    d_img = torch.from_numpy(np.ascontiguousarray(np.tile(frames, (nb // 16, 1, 1)))).to(dev)   # > L2 (126 MB)
+    ex = ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb, device=local)
     cap = ex.default_capacity
     d_k = torch.zeros((nb, cap, 28), dtype=torch.uint8, device=dev)
     d_d = torch.zeros((nb, cap, 32), dtype=torch.uint8, device=dev)
@@ -275,10 +275,32 @@ def bench_c1(args, torch, dev, local):
     e.record(st)
     e.synchronize()
     ms = s.elapsed_time(e)
-    r = {"frames_per_s": nb * steps / (ms * 1e-3), "workload": "640x480, 1000 features, batch 512 device-resident",
+    r = {"frames_per_s": nb * steps / (ms * 1e-3), "workload": label, "ms_per_batch": ms / steps,
          "keypoints_per_frame": float(d_n.sum().item()) / nb}
+    if with_stages:   # serial schedule with the library's stage events: where a batch of large frames spends its time
+        L = _lib.lib()
+        L.orb_extractor_set_profiling(ex._h, 1)
+        for _ in range(steps):
+            run()
+        ex.sync()
+        sm = (C.c_double * 6)()
+        calls = C.c_int64()
+        L.orb_extractor_stage_times(ex._h, sm, C.byref(calls))
+        L.orb_extractor_set_profiling(ex._h, 0)
+        r["stage_ms_per_batch_serial"] = {STAGES[i]: sm[i] / max(calls.value, 1) for i in range(6)}
     ex.close()
     return r
+
+
+def bench_c1(args, torch, dev, local):
+    """Config C1: monocular 640x480, nFeatures 1000 -- device-resident batched extraction, frames/s."""
+    return bench_batched(torch, dev, local, 640, 480, 1000, 512, 5, "640x480, 1000 features, batch 512 device-resident", 300)
+
+
+def bench_c4(args, torch, dev, local):
+    """Config C4: 256 independent 1920x1080 frames, 2000 features, one batch per GPU -- device-resident, frames/s."""
+    return bench_batched(torch, dev, local, 1920, 1080, 2000, 256, 3, "C4: 256 frames of 1920x1080, 2000 features, one batch, device-resident",
+                         500, with_stages=True)
 
 
 def bench_bow(args, torch, dev, local):
@@ -661,6 +683,7 @@ def run_ours(args):
         extra["hamming"] = bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier)
     if rank == 0 and not os.environ.get("ORB_BENCH_SKIP_C1"):
         extra["c1_mono"] = bench_c1(args, torch, dev, local)
+        extra["c4_1080p"] = bench_c4(args, torch, dev, local)
         extra["latency"] = bench_latency(args)
         if not os.environ.get("ORB_BENCH_SKIP_BOW"):
             extra["bow_transform"] = bench_bow(args, torch, dev, local)
