@@ -267,7 +267,7 @@ static size_t fast_smem_layout(FastLevel &fl) {
     size_t off = (size_t)th * FT_PB;
     auto carve = [&](size_t bytes) { off = (off + 15) & ~(size_t)15; const size_t o = off; off += bytes; return (int)o; };
     fl.off_vmap = carve((size_t)(fl.hCell + 3) * FT_PB);   // score map: rows -1 .. ch of the computed region, tile column geometry
-    fl.off_flags = 0;   // (the per-word flag array of earlier versions is gone: survivors are appended at test time)
+    fl.off_flags = 0;
     (void)nwc;
     fl.off_survH = carve((size_t)fl.wCell * fl.hCell * 2);   // one-type survivors: brighter from the bottom, darker from the top
     fl.off_survL = carve((size_t)fl.wCell * fl.hCell * 2);   // survivors of both types
@@ -989,7 +989,7 @@ k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, co
     if (slot >= P.lv[P.nlevels - 1].cap_end) return;
     int level = 0;
 #pragma unroll
-    for (int l = 0; l < ORB_MAX_LEVELS - 1; l++) level += (l < P.nlevels - 1 && slot >= P.lv[l].cap_end);
+    for (int l = 0; l < ORB_MAX_LEVELS - 1; l++) level += (slot >= P.lv[l].cap_end);   // cap_end of the levels beyond nlevels - 2 = the total > slot
     if (level > 0) slot -= P.lv[level - 1].cap_end;
     // kept counts of all levels: lane l holds level l's, an inclusive warp scan gives this level's output base and the total
     const uint32_t *kc = kept_count + (size_t)b * P.nlevels;
@@ -1526,7 +1526,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             // pitched copy from pageable memory goes row by row through the driver (measured 182 us for one 1241x376 frame)
             d_pitch = pitch;
             d_stride = (size_t)pitch * height;
-            ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, images, (size_t)pitch * height * batch, cudaMemcpyHostToDevice, st));
+            // (the last row of a view into a larger buffer holds `width` bytes, not `pitch`)
+            ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, images, (size_t)pitch * height * (batch - 1) + (size_t)pitch * (height - 1) + width,
+                                         cudaMemcpyHostToDevice, st));
         } else {
             d_pitch = (width + 127) / 128 * 128;
             d_stride = (size_t)d_pitch * height;

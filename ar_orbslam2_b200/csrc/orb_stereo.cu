@@ -439,8 +439,9 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
     int d_pitch = pitch_left;
     size_t d_stride = (size_t)pitch_left * height;
     if (pitch_left == pitch_right && 2 * d_stride <= ex->src_bytes) {
-        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, image_left, d_stride, cudaMemcpyHostToDevice, st));
-        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src + d_stride, image_right, d_stride, cudaMemcpyHostToDevice, st));
+        const size_t used = (size_t)pitch_left * (height - 1) + width;   // the last row of a view holds `width` bytes, not `pitch`
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, image_left, used, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src + d_stride, image_right, used, cudaMemcpyHostToDevice, st));
     } else {
         d_pitch = (width + 127) / 128 * 128;
         d_stride = (size_t)d_pitch * height;

@@ -206,3 +206,41 @@ def test_graph_replay_matches_oracle(oracle, gpu_lib, monkeypatch):
         assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
     assert ex.graph_replays == 0 and ex.launch_count == 3 * 33
     ex.close()
+
+
+def test_pitched_host_inputs(oracle, gpu_lib):
+    """Host frames that are views into larger buffers: a row pitch that fits the handle's source slot goes up as one linear
+    copy, a larger one (and a batch whose frames are not contiguous) through pitched copies; results equal the oracle."""
+    import ctypes as C
+    from ar_orbslam2_b200 import _lib
+    from ar_orbslam2_b200._abi import KEYPOINT_DTYPE, ORB_HOST, ptr
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h = 640, 480
+    ref = oracle.RefExtractor(1000)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=3)
+    for extra in (0, 13, 64, 1500):                    # pitch 640 (contiguous), 653 and 704 (linear copy: fit the slot), 2140 (pitched copy)
+        buf = np.zeros((h, w + extra), np.uint8)
+        img = synth_frame(w, h, 90 + extra)
+        off = min(5, extra)
+        buf[:, off:off + w] = img
+        view = buf[:, off:off + w]
+        gk, gd = ex(view)
+        rk, rd = ref.extract(img)
+        assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd), extra
+    # batch of three frames spaced by more than pitch * height (rows of padding between them)
+    B = 3
+    big = np.zeros((B, h + 9, w), np.uint8)
+    imgs = [synth_frame(w, h, 95 + b) for b in range(B)]
+    for b in range(B):
+        big[b, :h] = imgs[b]
+    cap = ex.default_capacity
+    kps = np.zeros((B, cap), KEYPOINT_DTYPE)
+    desc = np.zeros((B, cap, 32), np.uint8)
+    n = np.zeros(B, np.int32)
+    L = _lib.lib()
+    _lib.check(L.orb_extract_batch(ex._h, ptr(big), B, w, h, w, C.c_size_t((h + 9) * w), ORB_HOST, ptr(kps), ptr(desc), cap, ptr(n),
+                                   ORB_HOST), "orb_extract_batch")
+    for b in range(B):
+        rk, rd = ref.extract(imgs[b])
+        assert n[b] == len(rk) and kps[b, : n[b]].tobytes() == rk.tobytes() and np.array_equal(desc[b, : n[b]], rd), b
+    ex.close()
