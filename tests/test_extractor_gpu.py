@@ -113,6 +113,13 @@ def test_flat_and_noise_images(oracle, gpu_lib):
     gk, gd = ex(soft)
     rk, rd = ref.extract(soft)
     assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    # steep wrapping ramps: most pixels are brighter than one compass pair and darker than the other (the both-type list)
+    ramp = ((np.arange(640)[None, :] * 9 + np.arange(480)[:, None] * 11) % 256).astype(np.uint8)
+    gk, gd = ex(ramp)
+    rk, rd = ref.extract(ramp)
+    assert len(rk) > 0 and gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    for l in range(8):
+        assert np.array_equal(ex.candidates(l), ref.candidates(l)), l
     ex.close()
 
 

@@ -23,3 +23,15 @@ n, m = ORBmatcher(0.9, True).SearchForInitialization(f1, f2, prev, 100)
 n2, asg = ORBmatcher(0.8).SearchByProjectionPoints(f2, np.ones(len(kl), np.uint8), kl["x"], kl["y"], kl["x"] - 3, kl["octave"], np.full(len(kl), 0.9, np.float32), dl, 3.0)
 d = hamming_top2(synth_descriptors(33, 1), synth_descriptors(1000, 2))
 print("ok", len(kl), len(kr), int((ur != -1).sum()), n, n2, int(d[0].min()))
+# repeated calls (graph capture + replay, per-level quadtree streams), the single-call stereo front end, a dense-noise frame
+from ar_orbslam2_b200.stereo import StereoFrame
+for _ in range(3):
+    a(l)
+c = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=2)
+for _ in range(3):
+    out = StereoFrame(c, l, r, 386.1448, 0.537, allow_empty=True)
+noise = np.random.default_rng(1).integers(0, 256, (h, w), dtype=np.uint8)
+kn, dn = a(noise)
+ramp = ((np.arange(w)[None, :] * 9 + np.arange(h)[:, None] * 11) % 256).astype(np.uint8)   # steep ramps: both-type compass survivors
+kq, dq = a(ramp)
+print("ok2", a.graph_replays, len(out[0]), len(kn), len(kq))
