@@ -4,6 +4,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <string>
+#include <algorithm>
+#include <chrono>
 #include <thread>
 #include <vector>
 
@@ -60,6 +62,24 @@ int main(int argc, char **argv) {
     dump(pre + "_fur.bin", fuR.data(), fuR.size() * 4);
     dump(pre + "_fdp.bin", fdepth.data(), fdepth.size() * 4);
     printf("fused ok=%d\n", (int)fok);
+    if (argc > 7) {   // latency of the calls a Tracking thread makes, without the host mirror of the pyramid (median of 50)
+        auto med = [](std::vector<double> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
+        auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+        exL.SetMirrorPyramid(false); exR.SetMirrorPyramid(false);
+        std::vector<double> t1, t2, t3;
+        for (int i = 0; i < 55; i++) {
+            double t0 = now();
+            exL(imLeft, cv::Mat(), kL, dL);
+            double ta = now();
+            exR(imRight, cv::Mat(), kR, dR);
+            ORB_SLAM2::ORBGPU_ComputeStereoMatches(&exL, &exR, kL, dL, kR, dR, mbf, mb, uR, depth);
+            double tb = now();
+            ORB_SLAM2::ORBGPU_ExtractStereo(&exL, imLeft, imRight, fkL, fdL, fkR, fdR, mbf, mb, fuR, fdepth);
+            double tc = now();
+            if (i >= 5) { t1.push_back(ta - t0); t2.push_back(tb - t0); t3.push_back(tc - tb); }
+        }
+        printf("latency_us extract=%.1f stereo_three_calls=%.1f stereo_single_call=%.1f\n", med(t1), med(t2), med(t3));
+    }
     printf("shim ok=%d nL=%zu nR=%zu scale1=%.9g levels=%d l3=%dx%d step=%zu\n", (int)ok, kL.size(), kR.size(), exL.GetScaleFactors()[1],
            exL.GetLevels(), l3.cols, l3.rows, l3.step);
     return 0;

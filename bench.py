@@ -451,6 +451,20 @@ def bench_latency(args):
         if i >= 5:
             t.append(time.perf_counter() - t0)
     out["c2_stereo_frame_single_call_ms_median"] = 1e3 * float(np.median(t))   # orb_stereo_frame: one handle, one synchronisation
+    # the same calls from C++ through the drop-in shim classes (what the reference's Tracking thread would wait for)
+    exe = os.path.join(ROOT, "ar_orbslam2_b200", "shim", "shim_selftest")
+    if os.path.exists(exe):
+        import re
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            l.tofile(os.path.join(td, "l.raw")); r.tofile(os.path.join(td, "r.raw"))
+            p = subprocess.run([exe, str(W), str(H), os.path.join(td, "l.raw"), os.path.join(td, "r.raw"), str(NFEAT), os.path.join(td, "o"), "time"],
+                               capture_output=True, text=True)
+        m = re.search(r"latency_us extract=([\d.]+) stereo_three_calls=([\d.]+) stereo_single_call=([\d.]+)", p.stdout)
+        if m:
+            out["cpp_shim_c2_ms_median"] = {"ORBextractor::operator()": float(m.group(1)) / 1e3,
+                                            "two extractions + ORBGPU_ComputeStereoMatches": float(m.group(2)) / 1e3,
+                                            "ORBGPU_ExtractStereo": float(m.group(3)) / 1e3}
     out["note"] = "wall clock around blocking calls incl. pageable host copies and the python wrapper; sequential left/right"
     return out
 
