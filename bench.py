@@ -62,7 +62,7 @@ def make_pairs(n_distinct, seed0):
     return [synth_stereo_pair(W, H, seed0 + i) for i in range(n_distinct)]
 
 
-class ClockSampler:
+class SmiClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -103,6 +103,63 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class ClockSampler:
+    """SM clock and throttle reasons sampled every ~2 ms DURING the timed region through NVML (the timed region of the
+    default run is ~30 ms: nvidia-smi's 100 ms loop sees it once or twice); falls back to the nvidia-smi loop."""
+
+    def __init__(self, gpu_index):
+        self.gpu, self.fallback, self.h, self.nv = gpu_index, None, None, None
+        try:
+            import pynvml as nv
+            import torch
+            nv.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+                self.h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                idx = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[gpu_index].isdigit() else gpu_index
+                self.h = nv.nvmlDeviceGetHandleByIndex(idx)
+            nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.nv = nv
+        except Exception:
+            self.fallback = SmiClockSampler(gpu_index)
+        self.sm, self.bits, self.run, self.th = [], 0, False, None
+
+    def _loop(self):
+        nv = self.nv
+        while self.run:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self.fallback:
+            return self.fallback.start()
+        self.run = True
+        self.th = threading.Thread(target=self._loop, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        if self.fallback:
+            return self.fallback.stop()
+        self.run = False
+        self.th.join()
+        nv = self.nv
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        try:
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+        except Exception:
+            mx = max(self.sm)
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": mx, "reasons": sorted(n for b, n in names.items() if self.bits & b),
+                "samples": len(self.sm), "source": "nvml, 2 ms period inside the timed region"}
 
 
 def cpu_reference_run(pairs, n_threads, repeats=1):
