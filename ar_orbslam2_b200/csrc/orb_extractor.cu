@@ -267,7 +267,7 @@ static size_t fast_smem_layout(FastLevel &fl) {
     size_t off = (size_t)th * FT_PB;
     auto carve = [&](size_t bytes) { off = (off + 15) & ~(size_t)15; const size_t o = off; off += bytes; return (int)o; };
     fl.off_vmap = carve((size_t)(fl.hCell + 3) * FT_PB);   // score map: rows -1 .. ch of the computed region, tile column geometry
-    fl.off_flags = 0;
+    fl.off_flags = carve((size_t)nwc * fl.hCell * 4);   // flagged words of the compass pass, expanded into the lists afterwards
     (void)nwc;
     fl.off_survH = carve((size_t)fl.wCell * fl.hCell * 2);   // one-type survivors: brighter from the bottom, darker from the top
     fl.off_survL = carve((size_t)fl.wCell * fl.hCell * 2);   // survivors of both types
@@ -308,13 +308,14 @@ __global__ void __launch_bounds__(FAST_T)
 k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
              int *__restrict__ err) {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ int s_nkp, s_cnt, s_nB;
+    __shared__ int s_nkp, s_cnt, s_nB, s_nW;
 
     uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
     uint32_t *vmapW = reinterpret_cast<uint32_t *>(fsm + g.off_vmap);   // scores; row r <-> computed row r - 1, tile columns
     uint16_t *surv = reinterpret_cast<uint16_t *>(fsm + g.off_survH);   // code = y << 7 | tile byte column; brighter-type
     uint16_t *survB = reinterpret_cast<uint16_t *>(fsm + g.off_survL);  // from 0 up, darker-type from the top down; both-type
     const int listTop = g.wCell * g.hCell - 1;
+    uint32_t *wlist = reinterpret_cast<uint32_t *>(fsm + g.off_flags);   // code0 | brighter nibble << 16 | darker nibble << 20
 
     const int b = blockIdx.z, ci = blockIdx.y, cj = blockIdx.x, level = g.level;
     const int minB = EDGE - 3;
@@ -345,7 +346,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         asm volatile("cp.async.commit_group;");
         // score rows -1 and ch (the NMS apron); the rows between are cleared by the compass pass below
         if (tid < 2 * TPW) vmapW[tid < TPW ? tid : (ch + 1) * TPW + tid - TPW] = 0;
-        if (tid == 0) { s_nkp = 0; s_cnt = 0; s_nB = 0; }
+        if (tid == 0) { s_nkp = 0; s_cnt = 0; s_nB = 0; s_nW = 0; }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
@@ -395,24 +396,32 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
                 const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
                 const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
                 const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
-                if (fH | fL) {
-                    const uint32_t fB = fH & fL, f1 = (fH | fL) ^ fB, oL = fL & f1;
-                    const int code0 = (yy << 7) + 4 * w;                 // + j = code of pixel j
-                    if (f1) {   // one list array: brighter-type codes grow from the bottom, darker-type from the top
-                        const int pos = atomicAdd(&s_cnt, __popc(f1 ^ oL) + (__popc(oL) << 16));
-                        int pH = pos & 0xffff, pL = listTop - (pos >> 16);
-                        for (uint32_t m = f1; m; m &= m - 1) {
-                            const int bit = __ffs(m) - 1;
-                            const int isL = (oL >> bit) & 1;
-                            surv[isL ? pL : pH] = (uint16_t)(code0 + (bit >> 3));
-                            pH += 1 - isL; pL -= isL;
-                        }
+                if (fH | fL)   // bit 7 of byte j -> nibble bit j (the four partial products land on distinct bits: no carries)
+                    wlist[atomicAdd(&s_nW, 1)] = (uint32_t)((yy << 7) + 4 * w) | ((fH * 0x00204081u) >> 28) << 16 | ((fL * 0x00204081u) >> 28) << 20;
+            }
+        }
+        __syncthreads();
+        // ---- 2b. flagged words -> survivor lists, one word per thread (dense lanes; at compass time ~4 lanes of a warp hold one)
+        for (int t = tid, nW = s_nW; t < nW; t += FAST_T) {
+            const uint32_t e = wlist[t];
+            const int code0 = (int)(e & 0xffff);
+            const uint32_t nH4 = (e >> 16) & 15u, nL4 = (e >> 20) & 15u, fB = nH4 & nL4, f1 = (nH4 | nL4) ^ fB, oL = nL4 & f1;
+            if (f1) {   // one list array: brighter-type codes grow from the bottom, darker-type from the top
+                const int pos = atomicAdd(&s_cnt, __popc(f1 ^ oL) + (__popc(oL) << 16));
+                int pH = pos & 0xffff, pL = listTop - (pos >> 16);
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if ((f1 >> j) & 1) {
+                        const int isL = (oL >> j) & 1;
+                        surv[isL ? pL : pH] = (uint16_t)(code0 + j);
+                        pH += 1 - isL; pL -= isL;
                     }
-                    if (fB) {   // rare: brighter than one compass pair and darker than the other
-                        int pB = atomicAdd(&s_nB, __popc(fB));
-                        for (uint32_t m = fB; m; m &= m - 1) survB[pB++] = (uint16_t)(code0 + ((__ffs(m) - 1) >> 3));
-                    }
-                }
+            }
+            if (fB) {   // rare: brighter than one compass pair and darker than the other
+                int pB = atomicAdd(&s_nB, __popc(fB));
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if ((fB >> j) & 1) survB[pB++] = (uint16_t)(code0 + j);
             }
         }
         __syncthreads();
@@ -477,7 +486,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         __syncthreads();
         if (s_nkp) break;
         thr = g.min_th;   // empty cell: once more at the lower threshold (ref :780-784)
-        if (tid == 0) { s_cnt = 0; s_nB = 0; }
+        if (tid == 0) { s_cnt = 0; s_nB = 0; s_nW = 0; }
         __syncthreads();
     }
 }
