@@ -33,9 +33,9 @@ STAGES = ["h2d", "pyramid", "fast_cells", "octree", "describe", "d2h"]
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376), from the committed ncu
-# launch list profiles/r1l_launches.csv (same command as this bench, serial schedule).  Scaled by frames when --batch differs.
-NCU_DRAM_BYTES_PER_288_FRAMES = {"pyramid": (134.4 + 117.2 + 447.6 + 168.2) * 1e6, "fast_cells": (391.8 + 3.0) * 1e6,
-                                 "octree": (15.9 + 10.9) * 1e6, "describe": (475.5 + 193.6 + 840.5 + 31.9) * 1e6}
+# launch list profiles/r1m_launches.csv (same command as this bench, serial schedule).  Scaled by frames when --batch differs.
+NCU_DRAM_BYTES_PER_288_FRAMES = {"pyramid": (134.4 + 117.3 + 447.6 + 167.9) * 1e6, "fast_cells": (391.8 + 2.7) * 1e6,
+                                 "octree": (15.8 + 10.6) * 1e6, "describe": (475.6 + 193.8 + 840.5 + 31.9) * 1e6}
 
 
 _JSON_FD = None
@@ -828,7 +828,7 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak,
                      "traffic": NCU_DRAM_BYTES_PER_288_FRAMES.get(dom, 0) * NF / 288.0 or None,
-                     "traffic_source": "profiles/r1l_launches.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches)",
+                     "traffic_source": "profiles/r1m_launches.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches)",
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom]},
         "roofline_step": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak,
