@@ -52,6 +52,12 @@ class OrbFrameDesc(C.Structure):
                 ("nlevels", C.c_int32), ("scale_factors", C.c_void_p), ("keyframe_view", C.c_int32)]
 
 
+class OrbFrameSource(C.Structure):
+    _fields_ = [("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("dist_coef", C.c_float * 5),
+                ("ndist", C.c_int32), ("u_right", C.c_void_p), ("u_right_loc", C.c_int32), ("keyframe_view", C.c_int32)]
+
+
 class OrbReprojGate(C.Structure):
     _fields_ = [("ur", C.c_void_p), ("inv_level_sigma2", C.c_void_p), ("chi2_mono", C.c_double), ("chi2_stereo", C.c_double)]
 

@@ -41,6 +41,13 @@ def lib():
         L.orb_extractor_graph_replays.argtypes = [C.c_void_p]
         L.orb_extractor_destroy.argtypes = [C.c_void_p]
         L.orb_extractor_destroy.restype = None
+        for name in ("orb_frame_stream", "orb_get_call_stream"):
+            getattr(L, name).restype = C.c_void_p
+        L.orb_frame_stream.argtypes = [C.c_void_p]
+        L.orb_frame_launch_count.restype = C.c_int64
+        L.orb_frame_launch_count.argtypes = [C.c_void_p]
+        L.orb_frame_size.argtypes = [C.c_void_p]
+        L.orb_set_call_stream.argtypes = [C.c_void_p, C.c_int]
         _LIB = L
     return _LIB
 

@@ -81,6 +81,12 @@ extern "C" int orb_cvt_color_gray(const uint8_t *src, int width, int height, int
     uint8_t *d_dst = dst;
     DevBuf bs, bd;
     cudaStream_t st = (cudaStream_t)stream;
+    if (!st) {   // NULL = the thread's call stream (orb_set_call_stream), never the legacy default stream
+        ThreadCtx *T = nullptr;
+        int rc = orbgpu_thread_ctx(&T, 0, 0);
+        if (rc != ORB_OK) return rc;
+        st = T->stream;
+    }
     const size_t src_bytes = (batch - 1) * src_stride + (size_t)(height - 1) * src_pitch + (size_t)width * channels;
     const size_t dst_bytes = (batch - 1) * dst_stride + (size_t)(height - 1) * dst_pitch + (size_t)width;
     if (loc == ORB_HOST) {

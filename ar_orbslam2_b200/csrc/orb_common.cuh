@@ -44,4 +44,20 @@ __device__ __forceinline__ int hamming256(const uint32_t a[8], const uint32_t b[
     return d;
 }
 
+// Per-thread call context of the stream-less entry points (orb_descriptor_distance, orb_hamming_top2, orb_top2_merge,
+// orb_search_matches_ratio, orb_is_in_frustum, orb_undistort_*, orb_distinctive_descriptors, orb_rot_hist_filter, and
+// orb_cvt_color_gray / orb_remap_linear with stream == NULL): they run on `stream` = the stream set with
+// orb_set_call_stream(), else the thread's own non-blocking stream -- never on the legacy default stream, which would
+// serialise against every other thread of the process.  d_buf / h_buf (pinned) are reusable staging blocks for the
+// host-mode forms: no cudaMalloc / cudaFree per call.
+struct ThreadCtx {
+    int device = -1;
+    cudaStream_t own = nullptr, user = nullptr, stream = nullptr;
+    bool has_user = false;
+    uint8_t *d_buf = nullptr; size_t d_bytes = 0;
+    uint8_t *h_buf = nullptr; size_t h_bytes = 0;
+};
+// context of the calling thread on the current device, with at least d_bytes / h_bytes of staging
+int orbgpu_thread_ctx(ThreadCtx **out, size_t d_bytes, size_t h_bytes);
+
 }  // namespace orbgpu

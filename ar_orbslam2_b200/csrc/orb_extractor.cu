@@ -1237,6 +1237,8 @@ static void free_all(orb_extractor *ex) {
     if (ex->gexec) cudaGraphExecDestroy(ex->gexec);
     for (auto &e : ex->ev) if (e) cudaEventDestroy(e);
     for (auto &e : ex->ev_lvl) if (e) cudaEventDestroy(e);
+    if (ex->ev_pair) cudaEventDestroy(ex->ev_pair);
+    if (ex->ev_pair_done) cudaEventDestroy(ex->ev_pair_done);
     if (ex->ev_fast) cudaEventDestroy(ex->ev_fast);
     if (ex->ev_blur) cudaEventDestroy(ex->ev_blur);
     if (ex->s_fast) cudaStreamDestroy(ex->s_fast);
@@ -1457,7 +1459,26 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaMallocHost(&ex->h_pinned, (1 + B) * sizeof(int)));
     TRY_ALLOC(cudaMallocHost(&ex->h_bounce, ORB_BOUNCE_BYTES));
     ex->oct_smem = octree_smem_bytes(maxn);
-    TRY_ALLOC(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+    {
+        // cudaFuncAttributeMaxDynamicSharedMemorySize is per function and per device, not per handle: keep the largest request
+        // of all live and past handles (a later, smaller handle must not lower it under an earlier one's launches)
+        int optin = 0;
+        TRY_ALLOC(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, ex->device));
+        if (ex->oct_smem + 256 > (size_t)optin) {
+            set_error("nfeatures %d: the quadtree needs %zu bytes of shared memory per CTA, the device offers %d (about 15000 features "
+                      "at 8 levels / scale 1.2)", params->nfeatures, ex->oct_smem, optin);
+            free_all(ex); delete ex;
+            return ORB_ERR_INVALID;
+        }
+        static std::mutex mu;
+        static size_t dev_max[64] = {};
+        std::lock_guard<std::mutex> lk(mu);
+        size_t &cur = dev_max[ex->device & 63];
+        if (ex->oct_smem > cur) {
+            TRY_ALLOC(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+            cur = ex->oct_smem;
+        }
+    }
     TRY_ALLOC(cudaStreamSynchronize(ex->stream));
 #undef TRY_ALLOC
     *out = ex;
@@ -1513,6 +1534,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         if (out_loc == ORB_HOST) for (int b = 0; b < batch; b++) n_out[b] = 0;
         else ORB_CUDA_TRY(cudaMemsetAsync(n_out, 0, batch * sizeof(int32_t), ex->stream));
         ex->last_batch = 0;
+        ex->last_kp = nullptr;
         return ORB_OK;
     }
     ORB_REQUIRE(width > 0 && height > 0 && pitch >= width, ORB_ERR_INVALID, "bad image geometry");
@@ -1700,6 +1722,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     prof_mark(ex, 5);
     ORB_CUDA_TRY(cudaGetLastError());
     ex->last_batch = batch;
+    ex->last_kp = o_kp; ex->last_desc = o_desc; ex->last_n = o_n; ex->last_capacity = capacity;
+    ex->last_counts_valid = false;
 
     if (out_loc == ORB_HOST) {
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -1722,6 +1746,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
                 memcpy(descriptors + (size_t)b * capacity * 32, ex->h_bounce + kp_bytes + (size_t)b * capacity * 32, n * 32);
             }
         for (int b = 0; b < batch; b++) n_out[b] = ex->h_pinned[1 + b];
+        ex->last_counts.assign(ex->h_pinned + 1, ex->h_pinned + 1 + batch);
+        ex->last_counts_valid = true;
         const int flags = ex->h_pinned[0];
         if (flags) {
             cudaMemsetAsync(ex->d_err, 0, sizeof(int), st);

@@ -103,8 +103,11 @@ extern "C" int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustu
     cudaError_t e = cudaGetDeviceCount(&ndev);
     ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
     const int blocks = (n + 127) / 128;
+    ThreadCtx *T = nullptr;
+    { int rc = orbgpu_thread_ctx(&T, 0, 0); if (rc != ORB_OK) return rc; }
+    cudaStream_t st = T->stream;   // the thread's call stream (orb_set_call_stream), never the legacy default stream
     if (loc == ORB_DEVICE) {
-        k_is_in_frustum<<<blocks, 128>>>(*cam, n, pts->world_pos, pts->normal, pts->max_distance, pts->min_distance, pts->consider,
+        k_is_in_frustum<<<blocks, 128, 0, st>>>(*cam, n, pts->world_pos, pts->normal, pts->max_distance, pts->min_distance, pts->consider,
                                          viewing_cos_limit, in_view, proj_x, proj_y, proj_xr, level, view_cos);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
@@ -116,22 +119,23 @@ extern "C" int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustu
     ORB_CUDA_TRY(dout.alloc(bout));
     float *d_wp = (float *)din.p, *d_nr = d_wp + 3 * (size_t)n, *d_mx = d_nr + 3 * (size_t)n, *d_mn = d_mx + n;
     uint8_t *d_cons = (uint8_t *)(d_mn + n);
-    ORB_CUDA_TRY(cudaMemcpy(d_wp, pts->world_pos, (size_t)n * 12, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d_nr, pts->normal, (size_t)n * 12, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d_mx, pts->max_distance, (size_t)n * 4, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d_mn, pts->min_distance, (size_t)n * 4, cudaMemcpyHostToDevice));
-    if (pts->consider) ORB_CUDA_TRY(cudaMemcpy(d_cons, pts->consider, (size_t)n, cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_wp, pts->world_pos, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_nr, pts->normal, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_mx, pts->max_distance, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_mn, pts->min_distance, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (pts->consider) ORB_CUDA_TRY(cudaMemcpyAsync(d_cons, pts->consider, (size_t)n, cudaMemcpyHostToDevice, st));
     float *o_x = (float *)dout.p, *o_y = o_x + n, *o_xr = o_y + n, *o_vc = o_xr + n;
     int *o_lv = (int *)(o_vc + n);
     uint8_t *o_in = (uint8_t *)(o_lv + n);
-    k_is_in_frustum<<<blocks, 128>>>(*cam, n, d_wp, d_nr, d_mx, d_mn, pts->consider ? d_cons : nullptr, viewing_cos_limit, o_in, o_x, o_y,
+    k_is_in_frustum<<<blocks, 128, 0, st>>>(*cam, n, d_wp, d_nr, d_mx, d_mn, pts->consider ? d_cons : nullptr, viewing_cos_limit, o_in, o_x, o_y,
                                      o_xr, o_lv, o_vc);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(proj_x, o_x, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(proj_y, o_y, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(proj_xr, o_xr, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(view_cos, o_vc, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(level, o_lv, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(in_view, o_in, (size_t)n, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(proj_x, o_x, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(proj_y, o_y, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(proj_xr, o_xr, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(view_cos, o_vc, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(level, o_lv, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(in_view, o_in, (size_t)n, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }

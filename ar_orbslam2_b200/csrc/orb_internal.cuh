@@ -87,9 +87,16 @@ struct orb_extractor {
     uint8_t *h_bounce = nullptr;       // pinned landing buffer for the results of small host-output calls
     float *d_stereo_out = nullptr;     // orb_stereo_frame: uRight[cap] | depth[cap] | n_matched
     size_t stereo_out_cap = 0;
+    int stereo_last_capacity = 0;      // capacity of the last orb_stereo_frame call (depth starts that many floats in)
     int last_batch = 0;
+    // where the last extraction left its results (device), for orb_frame_from_extractor: the caller's device buffers or the
+    // handle's own staging; counts on the host when the call was a host-output one
+    const orb_keypoint *last_kp = nullptr; const uint8_t *last_desc = nullptr; const int32_t *last_n = nullptr;
+    int last_capacity = 0;
+    std::vector<int> last_counts; bool last_counts_valid = false;
     int64_t launches = 0;
     size_t oct_smem = 0;
+    cudaEvent_t ev_pair = nullptr, ev_pair_done = nullptr;   // orb_stereo_match_batch with two handles: ordering between their streams
     void *stereo_scratch = nullptr;    // device scratch of orb_stereo_match_batch
     size_t stereo_scratch_bytes = 0;
     // optional per-stage timing (CUDA events on the handle's stream)
@@ -122,6 +129,10 @@ struct orb_extractor {
     bool use_graph = true;             // ORBGPU_NO_GRAPH=1 switches it off
     int64_t graph_replays = 0;
 };
+
+// Frame::UndistortKeyPoints on device arrays, asynchronous on `stream` (orb_undistort.cu)
+int orbgpu_undistort_keypoints_async(const orb_keypoint *keys, int n, float fx, float fy, float cx, float cy, const float *dist_coef,
+                                     int ndist, orb_keypoint *keys_un, cudaStream_t stream);
 
 // grows the handle's device staging for `batch` x `capacity` keypoints + descriptors (drops a captured graph that holds the old pointers)
 int orbgpu_ensure_out_staging(orb_extractor *ex, int batch, int capacity);

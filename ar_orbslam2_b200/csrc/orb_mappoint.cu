@@ -67,8 +67,11 @@ extern "C" int orb_distinctive_descriptors(const uint8_t *descriptors, const int
     cudaError_t e = cudaGetDeviceCount(&ndev);
     ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
     const int blocks = (npoints + DD_WARPS - 1) / DD_WARPS;
+    ThreadCtx *T = nullptr;
+    { int rc = orbgpu_thread_ctx(&T, 0, 0); if (rc != ORB_OK) return rc; }
+    cudaStream_t st = T->stream;   // the thread's call stream (orb_set_call_stream), never the legacy default stream
     if (loc == ORB_DEVICE) {
-        k_distinctive<<<blocks, DD_WARPS * 32>>>(reinterpret_cast<const uint4 *>(descriptors), offsets, npoints, best_row, best_median);
+        k_distinctive<<<blocks, DD_WARPS * 32, 0, st>>>(reinterpret_cast<const uint4 *>(descriptors), offsets, npoints, best_row, best_median);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
     }
@@ -83,11 +86,12 @@ extern "C" int orb_distinctive_descriptors(const uint8_t *descriptors, const int
     ORB_CUDA_TRY(d_off.alloc((size_t)(npoints + 1) * 4));
     ORB_CUDA_TRY(d_row.alloc((size_t)npoints * 4));
     ORB_CUDA_TRY(d_med.alloc((size_t)npoints * 4));
-    ORB_CUDA_TRY(cudaMemcpy(d_desc.p, descriptors, (size_t)total * 32, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d_off.p, offsets, (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice));
-    k_distinctive<<<blocks, DD_WARPS * 32>>>((const uint4 *)d_desc.p, (const int *)d_off.p, npoints, (int *)d_row.p, (int *)d_med.p);
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_desc.p, descriptors, (size_t)total * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_off.p, offsets, (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice, st));
+    k_distinctive<<<blocks, DD_WARPS * 32, 0, st>>>((const uint4 *)d_desc.p, (const int *)d_off.p, npoints, (int *)d_row.p, (int *)d_med.p);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(best_row, d_row.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(best_median, d_med.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_row, d_row.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_median, d_med.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }

@@ -207,11 +207,17 @@ struct orb_db {
 };
 
 namespace {
-struct DevBuf {   // RAII device allocation for the one-shot host-mode entry points
+struct DevBuf {   // RAII device allocation (the popc micro-benchmark only)
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
     cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 1); }
 };
+
+// The one-shot entry points below run on the calling thread's call stream (orb_common.cuh: ThreadCtx) with that thread's
+// reusable device block; host-mode arguments are copied on the same stream.  Nothing touches the legacy default stream.
+thread_local Top2Scratch t_scratch;   // chunk partials of top2_device, per thread (kept across calls)
+
+inline size_t a256(size_t v) { return (v + 255) / 256 * 256; }
 }  // namespace
 
 extern "C" {
@@ -219,18 +225,23 @@ extern "C" {
 int orb_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, int loc) {
     ORB_REQUIRE(a && b && dist && n >= 0, ORB_ERR_INVALID, "bad argument");
     if (n == 0) return ORB_OK;
+    ThreadCtx *T = nullptr;
+    int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? 2 * a256((size_t)n * 32) + a256((size_t)n * 4) : 0, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
     if (loc == ORB_DEVICE) {
-        k_descriptor_distance<<<(n + 127) / 128, 128>>>(a, b, n, dist);
+        k_descriptor_distance<<<(n + 127) / 128, 128, 0, st>>>(a, b, n, dist);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
     }
-    DevBuf da, db, dd;
-    ORB_CUDA_TRY(da.alloc((size_t)n * 32)); ORB_CUDA_TRY(db.alloc((size_t)n * 32)); ORB_CUDA_TRY(dd.alloc((size_t)n * 4));
-    ORB_CUDA_TRY(cudaMemcpy(da.p, a, (size_t)n * 32, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice));
-    k_descriptor_distance<<<(n + 127) / 128, 128>>>((const uint8_t *)da.p, (const uint8_t *)db.p, n, (int32_t *)dd.p);
+    uint8_t *da = T->d_buf, *db = da + a256((size_t)n * 32);
+    int32_t *dd = (int32_t *)(db + a256((size_t)n * 32));
+    ORB_CUDA_TRY(cudaMemcpyAsync(da, a, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(db, b, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    k_descriptor_distance<<<(n + 127) / 128, 128, 0, st>>>(da, db, n, dd);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(dist, dd.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }
 
@@ -238,30 +249,29 @@ int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t 
                      int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc) {
     ORB_REQUIRE(queries && best_dist && best_idx && second_dist && second_idx, ORB_ERR_INVALID, "null argument");
     ORB_REQUIRE(nq >= 1 && ndb >= 0 && (db || ndb == 0), ORB_ERR_INVALID, "bad sizes");
-    Top2Scratch scratch;
-    int rc;
+    ThreadCtx *T = nullptr;
+    const size_t o_db = a256((size_t)nq * 32), o_out = o_db + a256((size_t)ndb * 32);
+    int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? o_out + a256((size_t)nq * 24) : 0, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
     if (loc == ORB_DEVICE) {
-        rc = top2_device(queries, nq, db, ndb, idx_base, best_dist, best_idx, second_dist, second_idx, 0, &scratch);
-        if (rc == ORB_OK && cudaStreamSynchronize(0) != cudaSuccess) rc = ORB_ERR_CUDA;
-        if (scratch.buf) cudaFree(scratch.buf);
+        rc = top2_device(queries, nq, db, ndb, idx_base, best_dist, best_idx, second_dist, second_idx, st, &t_scratch);
+        if (rc == ORB_OK) ORB_CUDA_TRY(cudaStreamSynchronize(st));
         return rc;
     }
-    DevBuf dq, ddb, out;
-    ORB_CUDA_TRY(dq.alloc((size_t)nq * 32)); ORB_CUDA_TRY(ddb.alloc((size_t)ndb * 32)); ORB_CUDA_TRY(out.alloc((size_t)nq * 24));
-    ORB_CUDA_TRY(cudaMemcpy(dq.p, queries, (size_t)nq * 32, cudaMemcpyHostToDevice));
-    if (ndb) ORB_CUDA_TRY(cudaMemcpy(ddb.p, db, (size_t)ndb * 32, cudaMemcpyHostToDevice));
-    int64_t *o_i1 = (int64_t *)out.p, *o_i2 = o_i1 + nq;
+    uint8_t *dq = T->d_buf, *ddb = T->d_buf + o_db;
+    int64_t *o_i1 = (int64_t *)(T->d_buf + o_out), *o_i2 = o_i1 + nq;
     int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
-    rc = top2_device((const uint8_t *)dq.p, nq, (const uint8_t *)ddb.p, ndb, idx_base, o_d1, o_i1, o_d2, o_i2, 0, &scratch);
-    if (rc == ORB_OK) {
-        cudaError_t e = cudaMemcpy(best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) e = cudaMemcpy(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) e = cudaMemcpy(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) e = cudaMemcpy(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) { set_error("copy back: %s", cudaGetErrorString(e)); rc = ORB_ERR_CUDA; }
-    }
-    if (scratch.buf) cudaFree(scratch.buf);
-    return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(dq, queries, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+    if (ndb) ORB_CUDA_TRY(cudaMemcpyAsync(ddb, db, (size_t)ndb * 32, cudaMemcpyHostToDevice, st));
+    rc = top2_device(dq, nq, ddb, ndb, idx_base, o_d1, o_i1, o_d2, o_i2, st, &t_scratch);
+    if (rc != ORB_OK) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
 }
 
 // ref: Marker::searchMatches (ORB_SLAM2/src/Marker.cc:314-349) and naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:70-102):
@@ -284,35 +294,33 @@ int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *q
     ORB_REQUIRE(n_query >= 0 && n_train >= 0 && (n_query == 0 || (query && train_idx && dist)) && (train || n_train == 0), ORB_ERR_INVALID,
                 "bad argument");
     if (n_query == 0) return ORB_OK;
-    int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
-    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
-    Top2Scratch scratch;
-    DevBuf dq, dt, tmp, out;
+    const size_t o_tmp = 0, o_q = a256((size_t)n_query * 24), o_t = o_q + a256((size_t)n_query * 32),
+                 o_out = o_t + a256((size_t)n_train * 32);
+    ThreadCtx *T = nullptr;
+    int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? o_out + a256((size_t)n_query * 8) : o_q, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
     const uint8_t *d_q = query, *d_t = train;
     int32_t *o_idx = train_idx, *o_dist = dist;
     if (loc == ORB_HOST) {
-        ORB_CUDA_TRY(dq.alloc((size_t)n_query * 32)); ORB_CUDA_TRY(dt.alloc((size_t)n_train * 32)); ORB_CUDA_TRY(out.alloc((size_t)n_query * 8));
-        ORB_CUDA_TRY(cudaMemcpy(dq.p, query, (size_t)n_query * 32, cudaMemcpyHostToDevice));
-        if (n_train) ORB_CUDA_TRY(cudaMemcpy(dt.p, train, (size_t)n_train * 32, cudaMemcpyHostToDevice));
-        d_q = (const uint8_t *)dq.p; d_t = (const uint8_t *)dt.p;
-        o_idx = (int32_t *)out.p; o_dist = o_idx + n_query;
+        uint8_t *dq = T->d_buf + o_q, *dt = T->d_buf + o_t;
+        ORB_CUDA_TRY(cudaMemcpyAsync(dq, query, (size_t)n_query * 32, cudaMemcpyHostToDevice, st));
+        if (n_train) ORB_CUDA_TRY(cudaMemcpyAsync(dt, train, (size_t)n_train * 32, cudaMemcpyHostToDevice, st));
+        d_q = dq; d_t = dt;
+        o_idx = (int32_t *)(T->d_buf + o_out); o_dist = o_idx + n_query;
     }
-    ORB_CUDA_TRY(tmp.alloc((size_t)n_query * 24));
-    int64_t *t_i1 = (int64_t *)tmp.p, *t_i2 = t_i1 + n_query;
+    int64_t *t_i1 = (int64_t *)(T->d_buf + o_tmp), *t_i2 = t_i1 + n_query;
     int32_t *t_d1 = (int32_t *)(t_i2 + n_query), *t_d2 = t_d1 + n_query;
-    int rc = top2_device(d_q, n_query, d_t, n_train, 0, t_d1, t_i1, t_d2, t_i2, 0, &scratch);
-    if (rc == ORB_OK) {
-        k_ratio_accept<<<(n_query + 127) / 128, 128>>>(n_query, t_d1, t_i1, t_d2, t_i2, ratio, max_dist, o_idx, o_dist);
-        cudaError_t e2 = cudaGetLastError();
-        if (e2 == cudaSuccess && loc == ORB_HOST) {
-            e2 = cudaMemcpy(train_idx, o_idx, (size_t)n_query * 4, cudaMemcpyDeviceToHost);
-            if (e2 == cudaSuccess) e2 = cudaMemcpy(dist, o_dist, (size_t)n_query * 4, cudaMemcpyDeviceToHost);
-        } else if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(0);
-        if (e2 != cudaSuccess) { set_error("orb_search_matches_ratio: %s", cudaGetErrorString(e2)); rc = ORB_ERR_CUDA; }
+    rc = top2_device(d_q, n_query, d_t, n_train, 0, t_d1, t_i1, t_d2, t_i2, st, &t_scratch);
+    if (rc != ORB_OK) return rc;
+    k_ratio_accept<<<(n_query + 127) / 128, 128, 0, st>>>(n_query, t_d1, t_i1, t_d2, t_i2, ratio, max_dist, o_idx, o_dist);
+    ORB_CUDA_TRY(cudaGetLastError());
+    if (loc == ORB_HOST) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(train_idx, o_idx, (size_t)n_query * 4, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(dist, o_dist, (size_t)n_query * 4, cudaMemcpyDeviceToHost, st));
     }
-    if (scratch.buf) cudaFree(scratch.buf);
-    return rc;
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
 }
 
 int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx, const int32_t *second_dist,
@@ -320,29 +328,32 @@ int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t 
                    int64_t *out_second_idx, int loc) {
     ORB_REQUIRE(nshards >= 1 && nq >= 1 && best_dist && best_idx && second_dist && second_idx && out_best_dist && out_best_idx &&
                     out_second_dist && out_second_idx, ORB_ERR_INVALID, "bad argument");
+    const size_t per = (size_t)nshards * nq;
+    ThreadCtx *T = nullptr;
+    int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? a256(per * 24) + a256((size_t)nq * 24) : 0, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
     if (loc == ORB_DEVICE) {
-        k_top2_merge<<<(nq + 127) / 128, 128>>>(nshards, nq, best_dist, best_idx, second_dist, second_idx, out_best_dist,
-                                                out_best_idx, out_second_dist, out_second_idx);
+        k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>(nshards, nq, best_dist, best_idx, second_dist, second_idx, out_best_dist,
+                                                       out_best_idx, out_second_dist, out_second_idx);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
     }
-    const size_t per = (size_t)nshards * nq;
-    DevBuf in, out;
-    ORB_CUDA_TRY(in.alloc(per * 24)); ORB_CUDA_TRY(out.alloc((size_t)nq * 24));
-    int64_t *i1 = (int64_t *)in.p, *i2 = i1 + per;
+    int64_t *i1 = (int64_t *)T->d_buf, *i2 = i1 + per;
     int32_t *d1 = (int32_t *)(i2 + per), *d2 = d1 + per;
-    ORB_CUDA_TRY(cudaMemcpy(i1, best_idx, per * 8, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(i2, second_idx, per * 8, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d1, best_dist, per * 4, cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(d2, second_dist, per * 4, cudaMemcpyHostToDevice));
-    int64_t *o_i1 = (int64_t *)out.p, *o_i2 = o_i1 + nq;
+    ORB_CUDA_TRY(cudaMemcpyAsync(i1, best_idx, per * 8, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(i2, second_idx, per * 8, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d1, best_dist, per * 4, cudaMemcpyHostToDevice, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d2, second_dist, per * 4, cudaMemcpyHostToDevice, st));
+    int64_t *o_i1 = (int64_t *)(T->d_buf + a256(per * 24)), *o_i2 = o_i1 + nq;
     int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
-    k_top2_merge<<<(nq + 127) / 128, 128>>>(nshards, nq, d1, i1, d2, i2, o_d1, o_i1, o_d2, o_i2);
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>(nshards, nq, d1, i1, d2, i2, o_d1, o_i1, o_d2, o_i2);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(out_best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(out_second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(out_best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost));
-    ORB_CUDA_TRY(cudaMemcpy(out_second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(out_best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(out_second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(out_best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(out_second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }
 

@@ -63,6 +63,12 @@ extern "C" int orb_remap_linear(const uint8_t *src, int src_width, int src_heigh
     cudaError_t e = cudaGetDeviceCount(&ndev);
     ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
     cudaStream_t st = (cudaStream_t)stream;
+    if (!st) {   // NULL = the thread's call stream (orb_set_call_stream), never the legacy default stream
+        ThreadCtx *T = nullptr;
+        int rc = orbgpu_thread_ctx(&T, 0, 0);
+        if (rc != ORB_OK) return rc;
+        st = T->stream;
+    }
     const uint8_t *d_src = src;
     const float *d_mx = map_x, *d_my = map_y;
     uint8_t *d_dst = dst;

@@ -10,6 +10,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 namespace orbgpu {
@@ -302,7 +303,8 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
                            float mbf, float mb, float *u_right, float *depth, int32_t *n_matched, int loc) {
     ORB_REQUIRE(left && right && keys_left && desc_left && n_left && keys_right && desc_right && n_right && u_right && depth,
                 ORB_ERR_INVALID, "null argument");
-    ORB_REQUIRE(batch >= 1 && capacity >= 1 && capacity <= 65535, ORB_ERR_INVALID, "bad batch/capacity");
+    ORB_REQUIRE(batch >= 1 && capacity >= 1, ORB_ERR_INVALID, "bad batch/capacity");
+    ORB_REQUIRE(capacity <= 32768, ORB_ERR_INVALID, "capacity %d: the median filter sorts up to 32768 matches per pair in shared memory", capacity);
     ORB_REQUIRE(left->device == right->device, ORB_ERR_INVALID, "left and right extractors must live on one device");
     ORB_REQUIRE(left->geom.width > 0 && right->geom.width > 0, ORB_ERR_INVALID, "extract the pair before matching");
     ORB_REQUIRE(left->geom.nlevels == right->geom.nlevels && left->geom.width == right->geom.width &&
@@ -312,11 +314,9 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     ORB_CUDA_TRY(cudaSetDevice(left->device));
     cudaStream_t st = left->stream;
     if (right != left) {   // the right pyramid is produced on the other handle's stream
-        cudaEvent_t ev;
-        ORB_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        ORB_CUDA_TRY(cudaEventRecord(ev, right->stream));
-        ORB_CUDA_TRY(cudaStreamWaitEvent(st, ev, 0));
-        ORB_CUDA_TRY(cudaEventDestroy(ev));
+        if (!left->ev_pair) ORB_CUDA_TRY(cudaEventCreateWithFlags(&left->ev_pair, cudaEventDisableTiming));
+        ORB_CUDA_TRY(cudaEventRecord(left->ev_pair, right->stream));
+        ORB_CUDA_TRY(cudaStreamWaitEvent(st, left->ev_pair, 0));
     }
     const size_t per = (size_t)batch * capacity;
     // scratch layout: sad[per] | n_matched[batch] | (host mode) keysL,keysR,descL,descR,nL,nR,uRight,depth
@@ -366,11 +366,23 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     k_stereo_match<<<dim3((capacity + ST_WARPS - 1) / ST_WARPS, batch), ST_WARPS * 32, 0, st>>>(A);
     int sort_n = 1;
     while (sort_n < capacity) sort_n <<= 1;
-    if (sort_n * 4 > 48 * 1024)
-        ORB_CUDA_TRY(cudaFuncSetAttribute(k_stereo_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_n * 4));
+    if (sort_n * 4 > 48 * 1024) {   // per function and device, not per call: raised once to the largest size the check above admits
+        static std::mutex mu;
+        static bool raised[64] = {};
+        std::lock_guard<std::mutex> lk(mu);
+        if (!raised[left->device & 63]) {
+            ORB_CUDA_TRY(cudaFuncSetAttribute(k_stereo_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4));
+            raised[left->device & 63] = true;
+        }
+    }
     k_stereo_filter<<<batch, 1024, sort_n * 4, st>>>(A, sort_n);
     left->launches += 3;
     ORB_CUDA_TRY(cudaGetLastError());
+    if (right != left) {   // the right handle's next extraction must not overwrite its pyramid while these kernels read it
+        if (!left->ev_pair_done) ORB_CUDA_TRY(cudaEventCreateWithFlags(&left->ev_pair_done, cudaEventDisableTiming));
+        ORB_CUDA_TRY(cudaEventRecord(left->ev_pair_done, st));
+        ORB_CUDA_TRY(cudaStreamWaitEvent(right->stream, left->ev_pair_done, 0));
+    }
     if (loc == ORB_HOST) {
         ORB_CUDA_TRY(cudaMemcpyAsync(u_right, A.uRight, per * 4, cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaMemcpyAsync(depth, A.depth, per * 4, cudaMemcpyDeviceToHost, st));
@@ -452,6 +464,7 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
                            ex->d_out_n, ORB_DEVICE);
     if (rc != ORB_OK) return rc;
     float *d_ur = ex->d_stereo_out, *d_dp = d_ur + capacity;
+    ex->stereo_last_capacity = capacity;
     int32_t *d_nm = (int32_t *)(d_dp + capacity);
     rc = orb_stereo_match_batch(ex, 0, ex, 1, 1, ex->d_out_kp, ex->d_out_desc, ex->d_out_n, ex->d_out_kp + capacity,
                                 ex->d_out_desc + (size_t)capacity * 32, ex->d_out_n + 1, capacity, mbf, mb, d_ur, d_dp, d_nm, ORB_DEVICE);
@@ -470,6 +483,8 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
     const int flags = ex->h_pinned[0];
     *n_left = ex->h_pinned[1]; *n_right = ex->h_pinned[2];
+    ex->last_counts.assign(ex->h_pinned + 1, ex->h_pinned + 3);   // orb_frame_from_extractor: counts known on the host
+    ex->last_counts_valid = true;
     if (flags) {   // capacity / candidate overflow raised by the extraction kernels
         cudaMemsetAsync(ex->d_err, 0, sizeof(int), st);
         set_error("extraction raised error flags 0x%x (capacity %d, needed %d / %d)", flags, capacity, *n_left, *n_right);
@@ -486,6 +501,13 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
     memcpy(&nm, land + kp_bytes + desc_bytes + 2 * f_bytes, 4);
     if (n_matched) *n_matched = nm;
     if (nm == 0) { set_error("no stereo match accepted (the reference indexes an empty vector here, Frame.cc:630)"); return ORB_ERR_EMPTY; }
+    return ORB_OK;
+}
+
+int orb_extractor_stereo_result(orb_extractor *ex, const float **dev_u_right, const float **dev_depth) {
+    ORB_REQUIRE(ex && ex->d_stereo_out, ORB_ERR_INVALID, "no orb_stereo_frame result in this handle");
+    if (dev_u_right) *dev_u_right = ex->d_stereo_out;
+    if (dev_depth) *dev_depth = ex->d_stereo_out + ex->stereo_last_capacity;
     return ORB_OK;
 }
 

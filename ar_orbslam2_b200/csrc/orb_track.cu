@@ -3,27 +3,39 @@
 // Replaces the hot loops of ORB_SLAM2::ORBmatcher (ref: ORB_SLAM2/src/ORBmatcher.cc) and the parts of
 // Frame they read (ref: ORB_SLAM2/src/Frame.cc:235-250, 332-397):
 //   orb_frame_*                      mvKeysUn / mDescriptors / mvuRight + the 64x48 grid on the device
+//   orb_frame_from_extractor         the same index built ON the device from an extractor's resident results
 //   orb_search_windowed              the projection-matcher loop (SearchByProjection x4, Fuse, SearchBySim3)
 //   orb_search_for_initialization    ORBmatcher.cc:405-523
 //   orb_search_by_bow                ORBmatcher.cc:159-288, 525-658
 //   orb_rot_hist_filter              ORBmatcher.cc:1604-1645 + the 30-bin rotation histogram
 //
-// Structure: distances for every (query, candidate) pair are computed in parallel, one warp per query, with
-// candidates emitted in the reference's grid traversal order; a single warp then replays the queries in order
-// and resolves the "already claimed" dependencies with warp-level lexicographic (distance, rank) top-2
-// reductions, which is exactly the reference's sequential strict-'<' best/second scan.
+// Structure of one call (latency is what the Tracking thread waits for, so a call is ONE host->device copy, two or
+// three kernels, ONE device->host copy and one synchronisation; no allocation, no stream creation):
+//   1. the caller's flat arrays are packed into the frame's pinned block and go up as one copy (the same block zeroes
+//      the candidate counter);
+//   2. k_window_lists: one warp per query walks the query's grid cells in the reference's traversal order, reserves
+//      a range of the candidate pool with one atomic and writes (feature, distance) pairs in that order;
+//   3. k_resolve_*: the reference's loop is sequential -- a query skips features an EARLIER query took.  That is a
+//      triangular dependency, so it has exactly one fixed point, and a Jacobi iteration "every query picks as if the
+//      picks of the previous sweep were final" reaches it: after sweep k the first k queries are final.  In practice
+//      two or three sweeps (conflicts are rare); every sweep is one thread per query over its short list;
+//   4. rotation histogram / three maxima / bookkeeping in the same kernel, results into one block, one copy down.
 #include "orb_common.cuh"
+#include "orb_internal.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 namespace orbgpu {
 
 constexpr int GRID_COLS = 64, GRID_ROWS = 48;   // ref Frame.h:39-40
+constexpr int NCELL = GRID_COLS * GRID_ROWS;
 constexpr int TH_HIGH_M = 100, TH_LOW_M = 50, HISTO = 30;
-constexpr uint32_t SENT = 0xffffffffu;
+constexpr int RES_THREADS = 1024;
+constexpr int FREE_Q = 0x7fffffff;
 
 struct FrameDev {
     int n;
@@ -35,14 +47,18 @@ struct FrameDev {
     float minX, minY, invW, invH;   // minX/minY as GetFeaturesInArea sees them (truncated to int for a KeyFrame view)
 };
 
-struct WinQ {   // device view of orb_window_queries
+struct WinQ {   // device view of a query set
     int n;
-    const uint8_t *valid;
-    const float *x, *y, *radius;
+    const uint8_t *valid;          // NULL = all
+    const int *valid_if_zero;      // NULL, or query q is valid only where this is 0 (SearchForInitialization: octave 0 only)
+    const float *x, *y;
+    int xy_stride;                 // 1: separate arrays; 2: x[2q], y[2q] interleaved (vbPrevMatched)
+    const float *radius;           // NULL = radius_const
+    float radius_const;
     const int *min_level, *max_level;
     int strict_levels;
     const float *stereo_ref, *stereo_tol;
-    const uint8_t *desc;
+    const uint8_t *desc;           // NULL = no distances (GetFeaturesInArea only)
     const float *angle;
     const uint8_t *claims;
     const float *gate_ur;          // reprojection-error gate of Fuse (ref ORBmatcher.cc:917-945); gate_inv_sigma2 == NULL = off
@@ -61,19 +77,6 @@ __device__ __forceinline__ int warp_excl_scan(int v, int lane, int *total) {
     return incl - v;
 }
 
-__device__ __forceinline__ void top2_push(uint32_t &k1, uint32_t &k2, uint32_t key) {
-    if (key < k1) { k2 = k1; k1 = key; }
-    else if (key < k2) k2 = key;
-}
-__device__ __forceinline__ void warp_top2(uint32_t &k1, uint32_t &k2) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const uint32_t a1 = __shfl_xor_sync(0xffffffffu, k1, o), a2 = __shfl_xor_sync(0xffffffffu, k2, o);
-        const uint32_t n1 = min(k1, a1), n2 = min(max(k1, a1), min(k2, a2));
-        k1 = n1; k2 = n2;
-    }
-}
-
 __device__ __forceinline__ int hamming_rows(const uint8_t *a, const uint8_t *b) {
     const uint4 *pa = reinterpret_cast<const uint4 *>(a), *pb = reinterpret_cast<const uint4 *>(b);
     const uint4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
@@ -81,10 +84,9 @@ __device__ __forceinline__ int hamming_rows(const uint8_t *a, const uint8_t *b) 
            __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
-// Frame::GetFeaturesInArea (ref Frame.cc:332-385) for one query by one warp.  Lanes own grid cells in traversal
-// order (ix outer, iy inner); a warp prefix sum per 32-cell round keeps the output in the reference's order.
-// FILL=false: returns the count.  FILL=true: writes (index, distance) pairs at out_idx/out_dist.
-struct WinTest {   // one query's admission test for a feature of the window's cells
+// One query's admission test for a feature of the window's cells (Frame::GetFeaturesInArea, ref Frame.cc:332-385, plus the
+// in-loop gates of the matchers).
+struct WinTest {
     float x, y, r, sref, stol, gur;
     int minL, maxL;
     bool check, strict, stereo, gate;
@@ -113,22 +115,34 @@ struct WinTest {   // one query's admission test for a feature of the window's c
     }
 };
 
-template <bool FILL>
-__device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int lane, int *out_idx, int *out_dist) {
-    const float x = Q.x[q], y = Q.y[q], r = Q.radius[q];
-    const int minL = Q.min_level[q], maxL = Q.max_level[q];
-    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.minX), r), f.invW)));
-    if (cx0 >= GRID_COLS) return 0;
-    const int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.minX), r), f.invW)));
-    if (cx1 < 0) return 0;
-    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.minY), r), f.invH)));
-    if (cy0 >= GRID_ROWS) return 0;
-    const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
-    if (cy1 < 0) return 0;
-    if (cx1 < cx0 || cy1 < cy0) return 0;
+// hdr[0] = candidate slots reserved so far (upper bounds), hdr[1] = overflow flag, hdr[2] = candidates written
+// One warp per query.  Lanes own grid cells in traversal order (ix outer, iy inner); pass 1 adds up the cells' populations
+// (an upper bound of the list) and reserves that range with one atomic, pass 2 tests the features and writes the admitted
+// ones -- a warp prefix sum per 32-cell round keeps the reference's order.  prune >= 0 drops candidates farther than
+// `prune` bits (a matcher that only ever takes the best candidate under a threshold never looks at them).
+__global__ void __launch_bounds__(256)
+k_window_lists(FrameDev f, WinQ Q, int *__restrict__ q_off, int *__restrict__ q_cnt, int2 *__restrict__ lists, int cap, int *hdr, int prune) {
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= Q.n) return;
+    bool valid = !Q.valid || Q.valid[q];
+    if (valid && Q.valid_if_zero) valid = Q.valid_if_zero[q] == 0;
+    int cx0 = 0, cx1 = -1, cy0 = 0, cy1 = -1;
     WinTest T;
-    T.x = x; T.y = y; T.r = r; T.minL = minL; T.maxL = maxL;
-    T.check = (minL > 0) || (maxL >= 0);
+    if (valid) {
+        const float x = Q.x[(size_t)q * Q.xy_stride], y = Q.y[(size_t)q * Q.xy_stride], r = Q.radius ? Q.radius[q] : Q.radius_const;
+        T.x = x; T.y = y; T.r = r;
+        cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.minX), r), f.invW)));
+        cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.minX), r), f.invW)));
+        cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.minY), r), f.invH)));
+        cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
+        if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0 || cx1 < cx0 || cy1 < cy0) valid = false;
+    }
+    if (!valid) {
+        if (lane == 0) { q_off[q] = 0; q_cnt[q] = 0; }
+        return;
+    }
+    T.minL = Q.min_level[q]; T.maxL = Q.max_level[q];
+    T.check = (T.minL > 0) || (T.maxL >= 0);
     T.strict = Q.strict_levels != 0;
     T.stereo = Q.stereo_ref != nullptr;
     T.sref = T.stereo ? Q.stereo_ref[q] : 0.f; T.stol = T.stereo ? Q.stereo_tol[q] : 0.f;
@@ -136,8 +150,27 @@ __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int la
     T.gur = T.gate && Q.gate_ur ? Q.gate_ur[q] : 0.f;
     T.inv_sigma2 = Q.gate_inv_sigma2; T.chi_mono = Q.gate_mono; T.chi_stereo = Q.gate_stereo;
     const int ny = cy1 - cy0 + 1, ncells = (cx1 - cx0 + 1) * ny;
-    const uint8_t *qd = Q.desc + (size_t)q * 32;
-    int base = 0;
+    // pass 1: upper bound.  Cells of one grid column are consecutive in cell_off, so a column of the window is one range.
+    int ub = 0;
+    for (int c = lane; c <= cx1 - cx0; c += 32) {
+        const int cell = (cx0 + c) * GRID_ROWS + cy0;
+        ub += f.cell_off[cell + ny] - f.cell_off[cell];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ub += __shfl_xor_sync(0xffffffffu, ub, o);
+    if (ub == 0) {
+        if (lane == 0) { q_off[q] = 0; q_cnt[q] = 0; }
+        return;
+    }
+    int off = 0;
+    if (lane == 0) off = atomicAdd(&hdr[0], ub);
+    off = __shfl_sync(0xffffffffu, off, 0);
+    if (off + ub > cap) {
+        if (lane == 0) { hdr[1] = 1; q_off[q] = 0; q_cnt[q] = 0; }
+        return;
+    }
+    const uint8_t *qd = Q.desc ? Q.desc + (size_t)q * 32 : nullptr;
+    int base = off;
     for (int c0 = 0; c0 < ncells; c0 += 32) {
         const int c = c0 + lane;
         int beg = 0, end = 0;
@@ -146,73 +179,34 @@ __device__ int window_candidates(const FrameDev &f, const WinQ &Q, int q, int la
             beg = f.cell_off[cell]; end = f.cell_off[cell + 1];
         }
         int cnt = 0;
-        unsigned pass = 0;   // cells hold few keypoints; longer cells fall back to re-testing
+        unsigned pass = 0;   // cells hold few keypoints; entries beyond the 32nd of a cell are re-tested when written
         for (int e = beg; e < end; e++) {
-            if (T.ok(f, f.cell_idx[e])) { if (e - beg < 32) pass |= 1u << (e - beg); cnt++; }
+            const int idx = f.cell_idx[e];
+            bool ok = T.ok(f, idx);
+            if (ok && prune >= 0 && qd) ok = hamming_rows(qd, f.desc + (size_t)idx * 32) <= prune;
+            if (ok) { if (e - beg < 32) pass |= 1u << (e - beg); cnt++; }
         }
         int total;
-        const int off = warp_excl_scan(cnt, lane, &total);
-        if (FILL && cnt) {
-            int w = base + off;
+        const int o = warp_excl_scan(cnt, lane, &total);
+        if (cnt) {
+            int w = base + o;
             for (int e = beg; e < end; e++) {
-                bool ok;
                 const int idx = f.cell_idx[e];
-                if (e - beg < 32) ok = (pass >> (e - beg)) & 1;
-                else ok = T.ok(f, idx);
-                if (ok) {
-                    out_idx[w] = idx;
-                    out_dist[w] = hamming_rows(qd, f.desc + (size_t)idx * 32);
-                    w++;
+                bool ok;
+                int d = 0;
+                if (e - beg < 32) {
+                    ok = (pass >> (e - beg)) & 1;
+                    if (ok && qd) d = hamming_rows(qd, f.desc + (size_t)idx * 32);
+                } else {
+                    ok = T.ok(f, idx);
+                    if (ok && qd) { d = hamming_rows(qd, f.desc + (size_t)idx * 32); if (prune >= 0 && d > prune) ok = false; }
                 }
+                if (ok) lists[w++] = make_int2(idx, d);
             }
         }
         base += total;
     }
-    return base;
-}
-
-__global__ void k_window_count(FrameDev f, WinQ Q, int *counts) {
-    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (q >= Q.n) return;
-    int n = 0;
-    if (!Q.valid || Q.valid[q]) n = window_candidates<false>(f, Q, q, lane, nullptr, nullptr);
-    if (lane == 0) counts[q] = n;
-}
-__global__ void k_window_fill(FrameDev f, WinQ Q, const int *off, int *cand_idx, int *cand_dist) {
-    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (q >= Q.n) return;
-    if (Q.valid && !Q.valid[q]) return;
-    window_candidates<true>(f, Q, q, lane, cand_idx + off[q], cand_dist + off[q]);
-}
-
-// exclusive scan of counts[0..n) into off[0..n], one CTA
-__global__ void __launch_bounds__(1024) k_scan_counts(const int *counts, int n, int *off) {
-    __shared__ int warp_tot[33];
-    __shared__ int carry;
-    const int tid = threadIdx.x, lane = tid & 31;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + tid;
-        const int v = i < n ? counts[i] : 0;
-        int tot;
-        int ex = warp_excl_scan(v, lane, &tot);
-        if (lane == 31) warp_tot[tid >> 5] = ex + v;
-        __syncthreads();
-        if (tid < 32) {
-            int t;
-            const int w = warp_tot[tid];
-            const int e = warp_excl_scan(w, tid, &t);
-            warp_tot[tid] = e;
-            if (tid == 31) warp_tot[32] = t;
-        }
-        __syncthreads();
-        if (i < n) off[i] = carry + warp_tot[tid >> 5] + ex;
-        __syncthreads();
-        if (tid == 0) carry += warp_tot[32];
-        __syncthreads();
-    }
-    if (tid == 0) off[n] = carry;
+    if (lane == 0) { q_off[q] = off; q_cnt[q] = base - off; atomicAdd(&hdr[2], base - off); }
 }
 
 __device__ __forceinline__ int rot_bin(float a, float b) {   // ref ORBmatcher.cc:238-243, factor = 1/HISTO_LENGTH
@@ -236,125 +230,188 @@ __device__ __forceinline__ void three_maxima(const int *hist, int &ind1, int &in
     else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
 }
 
-// One warp replays the queries in order (ORBmatcher.cc:51-126 / 1354-1448).
-__global__ void __launch_bounds__(32)
-k_resolve_windowed(FrameDev f, WinQ Q, const int *off, const int *cand_idx, const int *cand_dist, int *holder, uint8_t *blocking,
-                   int select, int th_dist, float nnratio, int check_ori, int *acc_feat, int *acc_bin, int *assigned, int *nmatches) {
-    __shared__ int hist[HISTO];
-    __shared__ int s_nm;
-    const int lane = threadIdx.x;
-    if (lane < HISTO) hist[lane] = 0;
-    if (lane == 0) s_nm = 0;
-    __syncwarp();
-    int nm = 0, na = 0;
-    for (int q = 0; q < Q.n; q++) {
-        if (Q.valid && !Q.valid[q]) continue;
-        const int o = off[q], n = off[q + 1] - o;
-        if (n == 0) continue;
-        uint32_t k1 = SENT, k2 = SENT;
-        for (int j = lane; j < n; j += 32) {
-            const int idx = cand_idx[o + j];
-            if (holder[idx] != -1 && blocking[idx]) continue;     // ref :87-89
-            top2_push(k1, k2, ((uint32_t)cand_dist[o + j] << 16) | (uint32_t)j);
-        }
-        warp_top2(k1, k2);
-        if (k1 == SENT) continue;
-        const int bestDist = (int)(k1 >> 16);
-        if (bestDist > th_dist) continue;
-        const int bestIdx = cand_idx[o + (k1 & 0xffff)];
-        if (select == ORB_SELECT_RATIO_LEVEL) {
-            const int bestLevel = f.octave[bestIdx];
-            const int bestLevel2 = k2 == SENT ? -1 : f.octave[cand_idx[o + (k2 & 0xffff)]];
-            const int bestDist2 = k2 == SENT ? 256 : (int)(k2 >> 16);
-            if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) continue;   // ref :120
-        }
-        if (lane == 0) {
-            holder[bestIdx] = q;
-            blocking[bestIdx] = Q.claims ? (Q.claims[q] != 0) : 1;
-            if (check_ori) {
-                const int bin = rot_bin(Q.angle[q], f.angle[bestIdx]);
-                acc_feat[na] = bestIdx; acc_bin[na] = bin;
-                hist[bin]++;
-            }
-        }
-        nm++; na++;
-        __syncwarp();
-    }
-    if (check_ori) {
-        int i1, i2, i3;
-        three_maxima(hist, i1, i2, i3);
-        int dec = 0;
-        for (int a = lane; a < na; a += 32) {
-            const int b = acc_bin[a];
-            if (b != i1 && b != i2 && b != i3) { holder[acc_feat[a]] = -3; dec++; }   // ref :1463-1467 (set to NULL)
-        }
-        if (dec) atomicAdd(&s_nm, dec);
-        __syncwarp();
-        nm -= s_nm;
-    }
-    __syncwarp();
-    for (int i = lane; i < f.n; i += 32) assigned[i] = holder[i] >= 0 ? holder[i] : (holder[i] == -3 ? -2 : -1);
-    if (lane == 0) *nmatches = nm;
+__device__ __forceinline__ int block_sum(int v, int *s_acc) {   // every thread of the CTA calls it; result valid after the barrier
+    __syncthreads();
+    if (threadIdx.x == 0) *s_acc = 0;
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(s_acc, v);
+    __syncthreads();
+    return *s_acc;
 }
 
-// ORBmatcher::SearchForInitialization resolve pass (ref :418-520)
-__global__ void __launch_bounds__(32)
-k_resolve_init(FrameDev f1, FrameDev f2, const int *off, const int *cand_idx, const int *cand_dist, int *matched_dist, int *m21,
-               int *m12, int *qbin, float nnratio, int check_ori, float *prev_matched, int *nmatches) {
+// The query loop of ORBmatcher.cc:51-126 / 1354-1448 / 1491-1578 / 312-400 (see the file header for the sweep scheme).
+//   blocked_by[i]: smallest query index that holds feature i with a blocking map point; -1 = blocked on entry (`claimed`),
+//   FREE_Q = free.  Query q skips feature i iff blocked_by[i] < q -- exactly "an earlier query put a map point with
+//   Observations()>0 there" (ref :87-89, 1406-1408, 1544-1545).
+// out[0] = nmatches, out[1] = sweeps
+__global__ void __launch_bounds__(RES_THREADS)
+k_resolve_windowed(FrameDev f, WinQ Q, const int *__restrict__ q_off, const int *__restrict__ q_cnt, const int2 *__restrict__ lists,
+                   const uint8_t *__restrict__ claimed, int *blocked_by, int *res, int *bins, int *holder, uint8_t *bad, int select,
+                   int th_dist, float nnratio, int check_ori, int *assigned, int *out, const int *hdr) {
     __shared__ int hist[HISTO];
-    __shared__ int s_dec;
-    const int lane = threadIdx.x;
-    if (lane < HISTO) hist[lane] = 0;
-    if (lane == 0) s_dec = 0;
-    __syncwarp();
-    int nm = 0;
-    for (int i1 = 0; i1 < f1.n; i1++) {
-        const int o = off[i1], n = off[i1 + 1] - o;
-        if (n == 0) continue;
-        uint32_t k1 = SENT, k2 = SENT;
-        for (int j = lane; j < n; j += 32) {
-            const int d = cand_dist[o + j];
-            if (matched_dist[cand_idx[o + j]] <= d) continue;   // ref :444-445
-            top2_push(k1, k2, ((uint32_t)d << 16) | (uint32_t)j);
-        }
-        warp_top2(k1, k2);
-        if (k1 == SENT) continue;
-        const int bestDist = (int)(k1 >> 16);
-        if (bestDist > TH_LOW_M) continue;
-        const float second = k2 == SENT ? (float)0x7fffffff : (float)(int)(k2 >> 16);
-        if (!((float)bestDist < __fmul_rn(second, nnratio))) continue;   // ref :461
-        const int b = cand_idx[o + (k1 & 0xffff)];
-        const int prev = m21[b];
-        __syncwarp();   // every lane has read m21[b] before lane 0 overwrites it
-        if (lane == 0) {
-            if (prev >= 0) m12[prev] = -1;
-            m12[i1] = b; m21[b] = i1; matched_dist[b] = bestDist;
-            if (check_ori) {
-                const int bin = rot_bin(f1.angle[i1], f2.angle[b]);
-                qbin[i1] = bin;
-                hist[bin]++;
+    __shared__ int ind[3];
+    __shared__ int s_changed, s_acc;
+    const int tid = threadIdx.x, n = Q.n, nf = f.n;
+    for (int i = tid; i < nf; i += RES_THREADS) blocked_by[i] = (claimed && claimed[i]) ? -1 : FREE_Q;
+    for (int q = tid; q < n; q += RES_THREADS) res[q] = -1;
+    if (tid < HISTO) hist[tid] = 0;
+    __syncthreads();
+    int sweeps = 0;
+    for (;;) {
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        bool changed = false;
+        for (int q = tid; q < n; q += RES_THREADS) {
+            const int cnt = q_cnt[q];
+            int pick = -1;
+            if (cnt) {
+                const int2 *L = lists + q_off[q];
+                int bestDist = 256, bestDist2 = 256, bestIdx = -1, idx2 = -1;
+                for (int j = 0; j < cnt; j++) {
+                    const int2 e = L[j];
+                    if (blocked_by[e.x] < q) continue;
+                    if (e.y < bestDist) { bestDist2 = bestDist; idx2 = bestIdx; bestDist = e.y; bestIdx = e.x; }
+                    else if (e.y < bestDist2) { bestDist2 = e.y; idx2 = e.x; }
+                }
+                if (bestIdx >= 0 && bestDist <= th_dist) {
+                    pick = bestIdx;
+                    if (select == ORB_SELECT_RATIO_LEVEL) {   // ref :118-121
+                        const int bestLevel = f.octave[bestIdx], bestLevel2 = idx2 >= 0 ? f.octave[idx2] : -1;
+                        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) pick = -1;
+                    }
+                }
             }
+            if (pick != res[q]) { res[q] = pick; changed = true; }
         }
-        if (prev >= 0) nm--;
-        nm++;
-        __syncwarp();
+        if (changed) s_changed = 1;
+        sweeps++;
+        __syncthreads();
+        if (!s_changed) break;
+        for (int i = tid; i < nf; i += RES_THREADS) blocked_by[i] = (claimed && claimed[i]) ? -1 : FREE_Q;
+        __syncthreads();
+        for (int q = tid; q < n; q += RES_THREADS) {
+            const int p = res[q];
+            if (p >= 0 && (!Q.claims || Q.claims[q])) atomicMin(&blocked_by[p], q);
+        }
+        __syncthreads();
     }
+    // ---- bookkeeping: who ends up in mvpMapPoints[i] (the last taker), rotation histogram over EVERY accepted query (an
+    // overwritten assignment still counts, F7), three maxima, reset of the takers outside them (ref :1451-1470)
+    for (int i = tid; i < nf; i += RES_THREADS) { holder[i] = -1; bad[i] = 0; }
+    __syncthreads();
+    int acc = 0;
+    for (int q = tid; q < n; q += RES_THREADS) {
+        const int p = res[q];
+        if (p < 0) continue;
+        acc++;
+        atomicMax(&holder[p], q);
+        if (check_ori) {
+            const int b = rot_bin(Q.angle[q], f.angle[p]);
+            bins[q] = b;
+            atomicAdd(&hist[b], 1);
+        }
+    }
+    int nm = block_sum(acc, &s_acc);
     if (check_ori) {
-        int a1, a2, a3;
-        three_maxima(hist, a1, a2, a3);
+        if (tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
+        __syncthreads();
         int dec = 0;
-        for (int i = lane; i < f1.n; i += 32) {
-            const int b = qbin[i];
-            if (b >= 0 && b != a1 && b != a2 && b != a3 && m12[i] >= 0) { m12[i] = -1; dec++; }   // ref :500-513
+        for (int q = tid; q < n; q += RES_THREADS) {
+            const int p = res[q];
+            if (p < 0) continue;
+            const int b = bins[q];
+            if (b != ind[0] && b != ind[1] && b != ind[2]) { bad[p] = 1; dec++; }
         }
-        if (dec) atomicAdd(&s_dec, dec);
-        __syncwarp();
-        nm -= s_dec;
+        nm -= block_sum(dec, &s_acc);
     }
-    __syncwarp();
-    for (int i = lane; i < f1.n; i += 32)
-        if (m12[i] >= 0) { prev_matched[2 * i] = f2.x[m12[i]]; prev_matched[2 * i + 1] = f2.y[m12[i]]; }   // ref :518-520
-    if (lane == 0) *nmatches = nm;
+    __syncthreads();
+    for (int i = tid; i < nf; i += RES_THREADS) assigned[i] = bad[i] ? -2 : holder[i];
+    if (tid == 0) { out[0] = nm; out[1] = sweeps; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
+}
+
+
+// ORBmatcher::SearchForInitialization (ref :418-520).  Query i1 ignores a candidate i2 at distance d when an earlier query
+// holds i2 at a distance <= d (vMatchedDistance, ref :444-445); a later taker displaces the earlier one (:463-471).  After
+// every sweep the takers of a feature are chained (head / next, with a snapshot of their distances) so that the gate of
+// (q, i2) = min distance over the takers before q; a sweep only reads the chains and only writes its own res / res_dist.
+__global__ void __launch_bounds__(RES_THREADS)
+k_resolve_init(FrameDev f1, FrameDev f2, const int *__restrict__ q_off, const int *__restrict__ q_cnt, const int2 *__restrict__ lists,
+               int *head, int *next, int *tdist, int *res, int *res_dist, int *last, float nnratio, int check_ori, int *m12,
+               const float *prev_in, float *prev_out, int *out, const int *hdr) {
+    __shared__ int hist[HISTO];
+    __shared__ int ind[3];
+    __shared__ int s_changed, s_acc;
+    const int tid = threadIdx.x, n1 = f1.n, n2 = f2.n;
+    for (int i = tid; i < n2; i += RES_THREADS) head[i] = -1;
+    for (int q = tid; q < n1; q += RES_THREADS) { res[q] = -1; res_dist[q] = 0; }
+    if (tid < HISTO) hist[tid] = 0;
+    __syncthreads();
+    int sweeps = 0;
+    for (;;) {
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        bool changed = false;
+        for (int q = tid; q < n1; q += RES_THREADS) {
+            const int cnt = q_cnt[q];
+            int pick = -1, pick_d = 0;
+            if (cnt) {
+                const int2 *L = lists + q_off[q];
+                int bestDist = 0x7fffffff, bestDist2 = 0x7fffffff, bestIdx = -1;
+                for (int j = 0; j < cnt; j++) {
+                    const int2 e = L[j];
+                    int gate = 0x7fffffff;
+                    for (int t = head[e.x]; t >= 0; t = next[t])
+                        if (t < q) gate = min(gate, tdist[t]);
+                    if (gate <= e.y) continue;                          // ref :444-445
+                    if (e.y < bestDist) { bestDist2 = bestDist; bestDist = e.y; bestIdx = e.x; }
+                    else if (e.y < bestDist2) bestDist2 = e.y;
+                }
+                if (bestIdx >= 0 && bestDist <= TH_LOW_M && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) { pick = bestIdx; pick_d = bestDist; }
+            }
+            if (pick != res[q] || pick_d != res_dist[q]) { res[q] = pick; res_dist[q] = pick_d; changed = true; }
+        }
+        if (changed) s_changed = 1;
+        sweeps++;
+        __syncthreads();
+        if (!s_changed) break;
+        for (int i = tid; i < n2; i += RES_THREADS) head[i] = -1;
+        __syncthreads();
+        for (int q = tid; q < n1; q += RES_THREADS) {
+            const int p = res[q];
+            if (p >= 0) { tdist[q] = res_dist[q]; next[q] = atomicExch(&head[p], q); }
+        }
+        __syncthreads();
+    }
+    // ---- vnMatches21 = the last taker; an earlier taker of the same feature was displaced (m12 = -1) but stays in the
+    // rotation histogram (ref :463-486); filter (:492-515); vbPrevMatched update (:518-520)
+    for (int i = tid; i < n2; i += RES_THREADS) last[i] = -1;
+    __syncthreads();
+    for (int q = tid; q < n1; q += RES_THREADS) {
+        const int p = res[q];
+        if (p < 0) continue;
+        atomicMax(&last[p], q);
+        if (check_ori) atomicAdd(&hist[rot_bin(f1.angle[q], f2.angle[p])], 1);
+    }
+    __syncthreads();
+    if (check_ori && tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
+    __syncthreads();
+    int acc = 0;
+    for (int q = tid; q < n1; q += RES_THREADS) {
+        const int p = res[q];
+        int m = (p >= 0 && last[p] == q) ? p : -1;
+        if (m >= 0 && check_ori) {
+            const int b = rot_bin(f1.angle[q], f2.angle[p]);
+            if (b != ind[0] && b != ind[1] && b != ind[2]) m = -1;
+        }
+        m12[q] = m;
+        float px = prev_in[2 * q], py = prev_in[2 * q + 1];
+        if (m >= 0) { px = f2.x[m]; py = f2.y[m]; acc++; }
+        prev_out[2 * q] = px; prev_out[2 * q + 1] = py;
+    }
+    const int nm = block_sum(acc, &s_acc);
+    if (tid == 0) { out[0] = nm; out[1] = sweeps; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
 }
 
 // SearchByBoW: distances of every (KF entry, F entry of the same vocabulary node) pair, one warp per KF entry
@@ -369,74 +426,98 @@ __global__ void k_bow_dist(FrameDev kf, FrameDev f, int nentries, const int *kf_
     for (int j = lane; j < fn; j += 32) dist[po + j] = hamming_rows(d, f.desc + (size_t)f_idx[fo + j] * 32);
 }
 
-__global__ void __launch_bounds__(32)
-k_resolve_bow(FrameDev kf, FrameDev f, int nentries, const int *kf_idx, const int *ent_fo, const int *ent_fn, const int *ent_po,
-              const int *f_idx, const uint8_t *kf_valid, const uint8_t *f_valid, const int *dist, int strict_low, float nnratio,
-              int check_ori, int *acc_feat, int *acc_bin, int *matches, int *nmatches) {
+// ref ORBmatcher.cc:196-262 / 565-636: entries (KF features in FeatureVector order) take F features of the same node;
+// a taken F feature is skipped by later entries (:209-210).  Same sweep scheme: taken_by[fi] = smallest entry holding fi.
+__global__ void __launch_bounds__(RES_THREADS)
+k_resolve_bow(FrameDev kf, FrameDev f, int nentries, const int *__restrict__ kf_idx, const int *__restrict__ ent_fo,
+              const int *__restrict__ ent_fn, const int *__restrict__ ent_po, const int *__restrict__ f_idx,
+              const uint8_t *__restrict__ kf_valid, const uint8_t *__restrict__ f_valid, const int *__restrict__ dist, int strict_low,
+              float nnratio, int check_ori, int *taken_by, int *res, int *matches, int *out) {
     __shared__ int hist[HISTO];
-    __shared__ int s_dec;
-    const int lane = threadIdx.x;
-    if (lane < HISTO) hist[lane] = 0;
-    if (lane == 0) s_dec = 0;
-    __syncwarp();
-    int nm = 0, na = 0;
-    for (int a = 0; a < nentries; a++) {
-        const int ki = kf_idx[a];
-        if (!kf_valid[ki]) continue;
-        const int fo = ent_fo[a], fn = ent_fn[a], po = ent_po[a];
-        uint32_t k1 = SENT, k2 = SENT;
-        for (int j = lane; j < fn; j += 32) {
-            const int fi = f_idx[fo + j];
-            if (matches[fi] >= 0) continue;                       // ref :209-210
-            if (f_valid && !f_valid[fi]) continue;                // ref :577-583
-            top2_push(k1, k2, ((uint32_t)dist[po + j] << 16) | (uint32_t)j);
-        }
-        warp_top2(k1, k2);
-        if (k1 == SENT) continue;
-        const int best1 = (int)(k1 >> 16), best2 = k2 == SENT ? 256 : (int)(k2 >> 16);
-        if (strict_low ? !(best1 < TH_LOW_M) : !(best1 <= TH_LOW_M)) continue;
-        if (!((float)best1 < __fmul_rn(nnratio, (float)best2))) continue;   // ref :230
-        const int fi = f_idx[fo + (k1 & 0xffff)];
-        if (lane == 0) {
-            matches[fi] = ki;
-            if (check_ori) {
-                const int bin = rot_bin(kf.angle[ki], f.angle[fi]);
-                acc_feat[na] = fi; acc_bin[na] = bin;
-                hist[bin]++;
+    __shared__ int ind[3];
+    __shared__ int s_changed, s_acc;
+    const int tid = threadIdx.x, nf = f.n;
+    for (int i = tid; i < nf; i += RES_THREADS) taken_by[i] = FREE_Q;
+    for (int a = tid; a < nentries; a += RES_THREADS) res[a] = -1;
+    if (tid < HISTO) hist[tid] = 0;
+    __syncthreads();
+    int sweeps = 0;
+    for (;;) {
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        bool changed = false;
+        for (int a = tid; a < nentries; a += RES_THREADS) {
+            const int ki = kf_idx[a];
+            int pick = -1;
+            if (kf_valid[ki]) {
+                const int fo = ent_fo[a], fn = ent_fn[a], po = ent_po[a];
+                int best1 = 256, best2 = 256, bestIdx = -1;
+                for (int j = 0; j < fn; j++) {
+                    const int fi = f_idx[fo + j];
+                    if (taken_by[fi] < a) continue;                       // ref :209-210
+                    if (f_valid && !f_valid[fi]) continue;                // ref :577-583
+                    const int d = dist[po + j];
+                    if (d < best1) { best2 = best1; best1 = d; bestIdx = fi; }
+                    else if (d < best2) best2 = d;
+                }
+                if (bestIdx >= 0 && (strict_low ? best1 < TH_LOW_M : best1 <= TH_LOW_M) &&
+                    (float)best1 < __fmul_rn(nnratio, (float)best2)) pick = bestIdx;   // ref :228-230
             }
+            if (pick != res[a]) { res[a] = pick; changed = true; }
         }
-        nm++; na++;
-        __syncwarp();
+        if (changed) s_changed = 1;
+        sweeps++;
+        __syncthreads();
+        if (!s_changed) break;
+        for (int i = tid; i < nf; i += RES_THREADS) taken_by[i] = FREE_Q;
+        __syncthreads();
+        for (int a = tid; a < nentries; a += RES_THREADS)
+            if (res[a] >= 0) atomicMin(&taken_by[res[a]], a);
+        __syncthreads();
     }
-    if (check_ori) {
-        int i1, i2, i3;
-        three_maxima(hist, i1, i2, i3);
-        int dec = 0;
-        for (int a = lane; a < na; a += 32) {
-            const int b = acc_bin[a];
-            if (b != i1 && b != i2 && b != i3) { matches[acc_feat[a]] = -1; dec++; }
+    // at the fixed point every taken feature has exactly one taker
+    for (int i = tid; i < nf; i += RES_THREADS) matches[i] = -1;
+    __syncthreads();
+    int acc = 0;
+    for (int a = tid; a < nentries; a += RES_THREADS) {
+        const int p = res[a];
+        if (p < 0) continue;
+        acc++;
+        if (check_ori) atomicAdd(&hist[rot_bin(kf.angle[kf_idx[a]], f.angle[p])], 1);
+    }
+    int nm = block_sum(acc, &s_acc);
+    if (check_ori && tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
+    __syncthreads();
+    int dec = 0;
+    for (int a = tid; a < nentries; a += RES_THREADS) {
+        const int p = res[a];
+        if (p < 0) continue;
+        const int ki = kf_idx[a];
+        if (check_ori) {
+            const int b = rot_bin(kf.angle[ki], f.angle[p]);
+            if (b != ind[0] && b != ind[1] && b != ind[2]) { dec++; continue; }   // ref :270-281
         }
-        if (dec) atomicAdd(&s_dec, dec);
-        __syncwarp();
-        nm -= s_dec;
+        matches[p] = ki;
     }
-    if (lane == 0) *nmatches = nm;
+    nm -= block_sum(dec, &s_acc);
+    if (tid == 0) { out[0] = nm; out[1] = sweeps; }
 }
 
 // Fuse / SearchBySim3 candidate loop (ref ORBmatcher.cc:895-951, 1052-1072, 1191-1213, 1271-1293): independent queries,
-// closest descriptor of the window, the first one in traversal order on ties.  One warp per query over its CSR list.
-__global__ void k_window_best(int nq, const int *off, const int *cand_idx, const int *cand_dist, int *best_idx, int *best_dist) {
-    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+// closest descriptor of the window, the first one in traversal order on ties.
+__global__ void k_window_best(int nq, const int *__restrict__ q_off, const int *__restrict__ q_cnt, const int2 *__restrict__ lists,
+                              int *best_idx, int *best_dist) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
-    const int o = off[q], n = off[q + 1] - o;
-    unsigned long long key = ~0ull;
-    for (int j = lane; j < n; j += 32) key = min(key, ((unsigned long long)(uint32_t)cand_dist[o + j] << 32) | (uint32_t)j);
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
-    if (lane == 0) {
-        best_idx[q] = key == ~0ull ? -1 : cand_idx[o + (int)(uint32_t)key];
-        best_dist[q] = key == ~0ull ? 0x7fffffff : (int)(key >> 32);
+    const int2 *L = lists + q_off[q];
+    const int n = q_cnt[q];
+    int bd = 0x7fffffff, bi = -1;
+    for (int j = 0; j < n; j++) {
+        const int2 e = L[j];
+        if (e.y < bd) { bd = e.y; bi = e.x; }
     }
+    best_idx[q] = bi;
+    best_dist[q] = bd;
 }
 
 // SearchForTriangulation (ref ORBmatcher.cc:660-826): one warp per KF1 feature of a shared vocabulary node, lanes over
@@ -464,7 +545,7 @@ __global__ void k_triangulate(FrameDev k1, FrameDev k2, int nent, const int *idx
     const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
     const uint8_t *d1 = k1.desc + (size_t)i1 * 32;
     const int o2 = ent_o2[e], n2 = ent_n2[e];
-    uint32_t key = SENT;
+    uint32_t key = 0xffffffffu;
     for (int j = lane; j < n2; j += 32) {
         const int i2 = idx2[o2 + j];
         if (!usable2[i2]) continue;                                      // ref :726-730
@@ -486,7 +567,7 @@ __global__ void k_triangulate(FrameDev k1, FrameDev k2, int nent, const int *idx
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
-    if (lane == 0 && key != SENT) m12[i1] = idx2[o2 + (0xffff - (int)(key & 0xffff))];
+    if (lane == 0 && key != 0xffffffffu) m12[i1] = idx2[o2 + (0xffff - (int)(key & 0xffff))];
 }
 
 // rotation-consistency filter of SearchForTriangulation (ref :764-775, 796-814) and the final count
@@ -535,56 +616,268 @@ __global__ void __launch_bounds__(1024) k_rot_hist_filter(const float *a, const 
     }
 }
 
+// Frame::AssignFeaturesToGrid / PosInGrid (ref Frame.cc:235-250, 387-397) on the device, one CTA: key points (AoS, as the
+// extractor leaves them) -> SoA + the 64x48 CSR grid.  Cell = round((x - minX) * invW) (round, not floor); indices inside a
+// cell ascend (= the reference's insertion order): slots are handed out by atomics, then every cell's short list is sorted.
+struct FrameBuild {
+    float *x, *y, *angle, *uRight;
+    int *octave, *cell_off, *cell_idx, *cell_of;
+    float minX, minY, invW, invH;
+};
+__global__ void __launch_bounds__(1024)
+k_frame_build(const orb_keypoint *__restrict__ kp, int n, const float *__restrict__ u_right, FrameBuild B) {
+    __shared__ int cnt[NCELL];
+    __shared__ int warp_tot[33];
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int c = tid; c < NCELL; c += 1024) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 1024) {
+        const orb_keypoint k = kp[i];
+        B.x[i] = k.x; B.y[i] = k.y; B.angle[i] = k.angle; B.octave[i] = k.octave;
+        B.uRight[i] = u_right ? u_right[i] : -1.0f;
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(k.x, B.minX), B.invW)), py = (int)roundf(__fmul_rn(__fsub_rn(k.y, B.minY), B.invH));
+        const int cell = (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) ? -1 : px * GRID_ROWS + py;
+        B.cell_of[i] = cell;
+        if (cell >= 0) atomicAdd(&cnt[cell], 1);
+    }
+    __syncthreads();
+    // exclusive scan of the 3072 counts: 3 consecutive cells per thread
+    const int c0 = tid * 3;
+    const int a0 = cnt[c0], a1 = cnt[c0 + 1], a2 = cnt[c0 + 2];
+    int tot;
+    const int ex = warp_excl_scan(a0 + a1 + a2, lane, &tot);
+    if (lane == 31) warp_tot[tid >> 5] = tot;
+    __syncthreads();
+    if (tid < 32) {
+        int t;
+        const int e = warp_excl_scan(warp_tot[tid], tid, &t);
+        warp_tot[tid] = e;
+        if (tid == 31) warp_tot[32] = t;
+    }
+    __syncthreads();
+    const int base = warp_tot[tid >> 5] + ex;
+    B.cell_off[c0] = base; B.cell_off[c0 + 1] = base + a0; B.cell_off[c0 + 2] = base + a0 + a1;
+    if (tid == 1023) B.cell_off[NCELL] = warp_tot[32];
+    __syncthreads();
+    cnt[c0] = base; cnt[c0 + 1] = base + a0; cnt[c0 + 2] = base + a0 + a1;   // write cursors
+    __syncthreads();
+    for (int i = tid; i < n; i += 1024) {
+        const int cell = B.cell_of[i];
+        if (cell >= 0) B.cell_idx[atomicAdd(&cnt[cell], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < NCELL; c += 1024) {
+        const int beg = B.cell_off[c], end = cnt[c];
+        for (int i = beg + 1; i < end; i++) {   // insertion sort, cells hold a handful of key points
+            const int v = B.cell_idx[i];
+            int j = i - 1;
+            while (j >= beg && B.cell_idx[j] > v) { B.cell_idx[j + 1] = B.cell_idx[j]; j--; }
+            B.cell_idx[j + 1] = v;
+        }
+    }
+}
+
 }  // namespace orbgpu
 
 using namespace orbgpu;
 
-struct orb_frame {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    int n = 0, nlevels = 0;
-    std::vector<orb_keypoint> keys;
-    std::vector<float> scale;
-    float minX, maxX, minY, maxY;
-    void *d_static = nullptr;   // x,y,angle,uRight,octave,desc,cell_off,cell_idx
-    FrameDev dev;
-    void *d_scratch = nullptr;
-    size_t scratch_bytes = 0;
-    int64_t launches = 0;
-};
-
+// ------------------------------------------------------------------------------------------
+// Host side.  Every orb_frame borrows a FrameRes (stream, event, device blocks, pinned blocks) from a per-process pool, so
+// creating and destroying frames at camera rate allocates nothing once the pool is warm.
+// ------------------------------------------------------------------------------------------
 namespace {
 
-struct Arena {   // carve 256-byte aligned pieces out of the frame's scratch buffer (two-phase: size, then place)
+struct FrameRes {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ready = nullptr;       // recorded after the frame's static data is complete
+    uint8_t *d_static = nullptr; size_t static_bytes = 0;   // x, y, angle, uRight, octave, desc, cell_off, cell_idx
+    uint8_t *d_work = nullptr;   size_t work_bytes = 0;     // per call: upload image | scratch | candidate lists | results
+    uint8_t *h_up = nullptr;     size_t up_bytes = 0;       // pinned: what goes up
+    uint8_t *h_dn = nullptr;     size_t dn_bytes = 0;       // pinned: what comes down
+};
+
+std::mutex g_pool_mu;
+std::vector<FrameRes *> g_pool;
+constexpr size_t POOL_MAX = 64;
+
+int res_acquire(int device, FrameRes **out) {
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        for (size_t i = 0; i < g_pool.size(); i++)
+            if (g_pool[i]->device == device) {
+                *out = g_pool[i];
+                g_pool.erase(g_pool.begin() + i);
+                return ORB_OK;
+            }
+    }
+    FrameRes *r = new FrameRes();
+    r->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ready, cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+        set_error("orb_frame: %s", cudaGetErrorString(e));
+        if (r->stream) cudaStreamDestroy(r->stream);
+        delete r;
+        return ORB_ERR_CUDA;
+    }
+    *out = r;
+    return ORB_OK;
+}
+
+void res_free(FrameRes *r) {
+    cudaFree(r->d_static); cudaFree(r->d_work);
+    if (r->h_up) cudaFreeHost(r->h_up);
+    if (r->h_dn) cudaFreeHost(r->h_dn);
+    cudaEventDestroy(r->ready);
+    cudaStreamDestroy(r->stream);
+    delete r;
+}
+
+void res_release(FrameRes *r) {
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        if (g_pool.size() < POOL_MAX) { g_pool.push_back(r); return; }
+    }
+    res_free(r);
+}
+
+int grow_dev(uint8_t **p, size_t *have, size_t need) {
+    if (*have >= need) return ORB_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    need = need * 3 / 2 + 65536;
+    ORB_CUDA_TRY(cudaMalloc(p, need));
+    *have = need;
+    return ORB_OK;
+}
+int grow_host(uint8_t **p, size_t *have, size_t need) {
+    if (*have >= need) return ORB_OK;
+    if (*p) cudaFreeHost(*p);
+    *p = nullptr; *have = 0;
+    need = need * 3 / 2 + 65536;
+    ORB_CUDA_TRY(cudaMallocHost(p, need));
+    *have = need;
+    return ORB_OK;
+}
+
+constexpr size_t ALIGN = 256;
+inline size_t up256(size_t v) { return (v + ALIGN - 1) / ALIGN * ALIGN; }
+
+struct Arena {   // carve 256-byte aligned pieces out of a device block
     uint8_t *base = nullptr;
     size_t used = 0;
     template <class T> T *take(size_t count) {
-        T *p = base ? reinterpret_cast<T *>(base + used) : nullptr;
-        used += (count * sizeof(T) + 255) / 256 * 256;
+        T *p = reinterpret_cast<T *>(base + used);
+        used += up256(count * sizeof(T));
         return p;
     }
 };
 
-int ensure_scratch(orb_frame *f, size_t bytes) {
-    if (f->scratch_bytes >= bytes) return ORB_OK;
-    if (f->d_scratch) cudaFree(f->d_scratch);
-    f->d_scratch = nullptr; f->scratch_bytes = 0;
-    bytes = bytes * 3 / 2 + 4096;
-    ORB_CUDA_TRY(cudaMalloc(&f->d_scratch, bytes));
-    f->scratch_bytes = bytes;
-    return ORB_OK;
-}
+// What goes up in one copy: pieces are written into the pinned block at the offset they will have in the device block.
+struct Upload {
+    uint8_t *h, *d;
+    size_t used = 0;
+    Upload(uint8_t *host, uint8_t *dev) : h(host), d(dev) {}
+    template <class T> T *put(const T *src, size_t count) {   // returns the DEVICE address
+        if (count) memcpy(h + used, src, count * sizeof(T));
+        T *p = reinterpret_cast<T *>(d + used);
+        used += up256(count * sizeof(T));
+        return p;
+    }
+    template <class T> T *slot(size_t count, T **host) {      // caller fills *host
+        *host = reinterpret_cast<T *>(h + used);
+        T *p = reinterpret_cast<T *>(d + used);
+        used += up256(count * sizeof(T));
+        return p;
+    }
+};
 
-template <class T>
-int upload(T *dst, const T *src, size_t count, cudaStream_t st) {
-    if (count) ORB_CUDA_TRY(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
-    return ORB_OK;
-}
 #define ORB_TRY(expr) do { int _rc = (expr); if (_rc != ORB_OK) return _rc; } while (0)
 
-// Runs count -> scan -> fill for a query set living in `ar` (device pointers already placed).  Returns the
-// total number of candidates; cand arrays are allocated after the count is known.
-struct WindowLists { int *off = nullptr, *idx = nullptr, *dist = nullptr; int total = 0; };
+}  // namespace
+
+struct orb_frame {
+    int device = 0;
+    FrameRes *res = nullptr;
+    cudaStream_t stream = nullptr;
+    int n = 0, nlevels = 0;
+    std::vector<float> scale;
+    float minX = 0, maxX = 0, minY = 0, maxY = 0;
+    FrameDev dev;
+    size_t list_hint = 0;          // candidate pairs the largest call so far reserved
+    bool up_inflight = false;      // an asynchronous build still reads h_up
+    int64_t launches = 0;
+    int64_t last_candidates = 0;
+    int last_sweeps = 0;
+};
+
+namespace {
+
+// carve the static block for n key points; returns the bytes needed (base may be null for sizing)
+struct StaticLayout {
+    float *x, *y, *angle, *uRight;
+    int *octave, *cell_off, *cell_idx, *cell_of;
+    uint8_t *desc;
+    size_t bytes;
+};
+StaticLayout static_layout(uint8_t *base, int n) {
+    Arena ar;
+    ar.base = base;
+    StaticLayout L;
+    const size_t m = (size_t)std::max(n, 1);
+    L.x = ar.take<float>(m); L.y = ar.take<float>(m); L.angle = ar.take<float>(m); L.uRight = ar.take<float>(m);
+    L.octave = ar.take<int>(m);
+    L.desc = ar.take<uint8_t>(m * 32);
+    L.cell_off = ar.take<int>(NCELL + 1); L.cell_idx = ar.take<int>(m); L.cell_of = ar.take<int>(m);
+    L.bytes = ar.used;
+    return L;
+}
+
+int frame_begin(int n, int nlevels, const float *scale_factors, float min_x, float max_x, float min_y, float max_y, orb_frame **out) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
+    orb_frame *f = new orb_frame();
+    cudaGetDevice(&f->device);
+    int rc = res_acquire(f->device, &f->res);
+    if (rc != ORB_OK) { delete f; return rc; }
+    f->stream = f->res->stream;
+    f->n = n; f->nlevels = nlevels;
+    f->scale.assign(scale_factors, scale_factors + nlevels);
+    f->minX = min_x; f->maxX = max_x; f->minY = min_y; f->maxY = max_y;
+    *out = f;
+    return ORB_OK;
+}
+
+void frame_abort(orb_frame *f) {
+    cudaStreamSynchronize(f->stream);
+    res_release(f->res);
+    delete f;
+}
+
+void frame_set_dev(orb_frame *f, const StaticLayout &L, bool keyframe_view) {
+    // ref Frame.cc:217-218; a KeyFrame sees the bounds as `int` copies (KeyFrame.h:190-193) while the grid keeps the Frame's scales
+    const float invW = static_cast<float>(GRID_COLS) / static_cast<float>(f->maxX - f->minX);
+    const float invH = static_cast<float>(GRID_ROWS) / static_cast<float>(f->maxY - f->minY);
+    f->dev = FrameDev{f->n, L.x, L.y, L.angle, L.uRight, L.octave, L.desc, L.cell_off, L.cell_idx,
+                      keyframe_view ? (float)(int)f->minX : f->minX, keyframe_view ? (float)(int)f->minY : f->minY, invW, invH};
+}
+
+// before the host touches h_up again: an asynchronous build may still be reading it
+int settle(orb_frame *f) {
+    if (f->up_inflight) {
+        ORB_CUDA_TRY(cudaStreamSynchronize(f->stream));
+        f->up_inflight = false;
+    }
+    return ORB_OK;
+}
+
+// another frame's static data is produced on that frame's stream
+int wait_for(orb_frame *f, const orb_frame *other) {
+    if (other != f) ORB_CUDA_TRY(cudaStreamWaitEvent(f->stream, other->res->ready, 0));
+    return ORB_OK;
+}
 
 }  // namespace
 
@@ -594,63 +887,107 @@ int orb_frame_create(const orb_frame_desc *d, orb_frame **out) {
     ORB_REQUIRE(d && out && d->n >= 0 && (d->n == 0 || (d->keys_un && d->descriptors)) && d->scale_factors && d->nlevels >= 1,
                 ORB_ERR_INVALID, "bad frame description");
     ORB_REQUIRE(d->max_x > d->min_x && d->max_y > d->min_y, ORB_ERR_INVALID, "empty image bounds");
-    int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
-    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
-    orb_frame *f = new orb_frame();
-    cudaGetDevice(&f->device);
-    f->n = d->n; f->nlevels = d->nlevels;
-    f->keys.assign(d->keys_un, d->keys_un + d->n);
-    f->scale.assign(d->scale_factors, d->scale_factors + d->nlevels);
-    f->minX = d->min_x; f->maxX = d->max_x; f->minY = d->min_y; f->maxY = d->max_y;
-    const int n = d->n, ncell = GRID_COLS * GRID_ROWS;
+    orb_frame *f = nullptr;
+    ORB_TRY(frame_begin(d->n, d->nlevels, d->scale_factors, d->min_x, d->max_x, d->min_y, d->max_y, &f));
+    FrameRes *R = f->res;
+    const int n = d->n;
+    const size_t bytes = static_layout(nullptr, n).bytes;
+    int rc = grow_dev(&R->d_static, &R->static_bytes, bytes);
+    if (rc == ORB_OK) rc = grow_host(&R->h_up, &R->up_bytes, bytes);
+    if (rc != ORB_OK) { frame_abort(f); return rc; }
+    // the static block is assembled in pinned memory (SoA + the grid as CSR) and goes up in one copy.
     // ref Frame.cc:217-218 and AssignFeaturesToGrid / PosInGrid :235-250, 387-397 (round(), not floor)
+    const StaticLayout H = static_layout(R->h_up, n), L = static_layout(R->d_static, n);
     const float invW = static_cast<float>(GRID_COLS) / static_cast<float>(f->maxX - f->minX);
     const float invH = static_cast<float>(GRID_ROWS) / static_cast<float>(f->maxY - f->minY);
-    std::vector<float> hx(n), hy(n), ha(n), hu(n);
-    std::vector<int> ho(n), cell(n), off(ncell + 1, 0), idx;
+    int *off = H.cell_off, *cell = H.cell_of;
+    memset(off, 0, (NCELL + 1) * sizeof(int));
     for (int i = 0; i < n; i++) {
         const orb_keypoint &k = d->keys_un[i];
-        hx[i] = k.x; hy[i] = k.y; ha[i] = k.angle; ho[i] = k.octave;
-        hu[i] = d->u_right ? d->u_right[i] : -1.0f;
+        H.x[i] = k.x; H.y[i] = k.y; H.angle[i] = k.angle; H.octave[i] = k.octave;
+        H.uRight[i] = d->u_right ? d->u_right[i] : -1.0f;
         const int px = (int)roundf((k.x - f->minX) * invW), py = (int)roundf((k.y - f->minY) * invH);
         cell[i] = (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) ? -1 : px * GRID_ROWS + py;
         if (cell[i] >= 0) off[cell[i] + 1]++;
     }
-    for (int c = 0; c < ncell; c++) off[c + 1] += off[c];
-    idx.resize(off[ncell] ? off[ncell] : 1);
+    for (int c = 0; c < NCELL; c++) off[c + 1] += off[c];
     {
-        std::vector<int> cur(off.begin(), off.end() - 1);
-        for (int i = 0; i < n; i++) if (cell[i] >= 0) idx[cur[cell[i]]++] = i;
+        std::vector<int> cur(off, off + NCELL);
+        for (int i = 0; i < n; i++) if (cell[i] >= 0) H.cell_idx[cur[cell[i]]++] = i;
     }
-    Arena ar;
-    for (int phase = 0; phase < 2; phase++) {
-        ar.used = 0;
-        float *dx = ar.take<float>(n), *dy = ar.take<float>(n), *da = ar.take<float>(n), *du = ar.take<float>(n);
-        int *doct = ar.take<int>(n);
-        uint8_t *dd = ar.take<uint8_t>((size_t)n * 32);
-        int *doff = ar.take<int>(ncell + 1), *didx = ar.take<int>(idx.size());
-        if (phase == 0) {
-            e = cudaMalloc(&f->d_static, ar.used + 256);
-            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking);
-            if (e != cudaSuccess) { set_error("orb_frame_create: %s", cudaGetErrorString(e)); if (f->d_static) cudaFree(f->d_static); delete f; return ORB_ERR_CUDA; }
-            ar.base = (uint8_t *)f->d_static;
-            continue;
+    if (n) memcpy(H.desc, d->descriptors, (size_t)n * 32);
+    cudaError_t e = cudaMemcpyAsync(R->d_static, R->h_up, bytes, cudaMemcpyHostToDevice, f->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(R->ready, f->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(f->stream);
+    if (e != cudaSuccess) { set_error("orb_frame_create: %s", cudaGetErrorString(e)); frame_abort(f); return ORB_ERR_CUDA; }
+    frame_set_dev(f, L, d->keyframe_view != 0);
+    *out = f;
+    return ORB_OK;
+}
+
+int orb_frame_from_extractor(orb_extractor *ex, int slot, const orb_frame_source *src, orb_frame **out) {
+    ORB_REQUIRE(ex && src && out, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(ex->last_kp && slot >= 0 && slot < ex->last_batch, ORB_ERR_INVALID, "no extraction result in slot %d", slot);
+    ORB_REQUIRE(src->max_x > src->min_x && src->max_y > src->min_y, ORB_ERR_INVALID, "empty image bounds");
+    ORB_REQUIRE(src->u_right == nullptr || src->u_right_loc == ORB_HOST || src->u_right_loc == ORB_DEVICE, ORB_ERR_INVALID, "bad u_right_loc");
+    ORB_CUDA_TRY(cudaSetDevice(ex->device));
+    int n;
+    if (ex->last_counts_valid) n = ex->last_counts[slot];
+    else {
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->last_n + slot, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+        ORB_CUDA_TRY(cudaStreamSynchronize(ex->stream));
+        n = ex->h_pinned[0];
+    }
+    n = std::min(std::max(n, 0), ex->last_capacity);
+    orb_frame *f = nullptr;
+    ORB_TRY(frame_begin(n, ex->prm.nlevels, ex->scale.data(), src->min_x, src->max_x, src->min_y, src->max_y, &f));
+    FrameRes *R = f->res;
+    const size_t bytes = static_layout(nullptr, n).bytes + up256((size_t)std::max(n, 1) * sizeof(orb_keypoint));
+    int rc = grow_dev(&R->d_static, &R->static_bytes, bytes);
+    if (rc != ORB_OK) { frame_abort(f); return rc; }
+    const StaticLayout L = static_layout(R->d_static, n);
+    orb_keypoint *d_un = reinterpret_cast<orb_keypoint *>(R->d_static + L.bytes);   // mvKeysUn when the camera has distortion
+    cudaStream_t st = f->stream;
+    auto fail = [&](cudaError_t e) { set_error("orb_frame_from_extractor: %s", cudaGetErrorString(e)); frame_abort(f); return ORB_ERR_CUDA; };
+    // the extractor's results are produced on ITS stream
+    cudaError_t e = cudaEventRecord(R->ready, ex->stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(st, R->ready, 0);
+    if (e != cudaSuccess) return fail(e);
+    const orb_keypoint *kp = ex->last_kp + (size_t)slot * ex->last_capacity;
+    const uint8_t *desc = ex->last_desc + (size_t)slot * ex->last_capacity * 32;
+    const float *d_ur = nullptr;
+    if (src->u_right && n) {
+        if (src->u_right_loc == ORB_DEVICE) d_ur = src->u_right;
+        else {
+            rc = grow_host(&R->h_up, &R->up_bytes, (size_t)n * 4);
+            if (rc == ORB_OK) rc = grow_dev(&R->d_work, &R->work_bytes, (size_t)n * 4);
+            if (rc != ORB_OK) { frame_abort(f); return rc; }
+            memcpy(R->h_up, src->u_right, (size_t)n * 4);
+            e = cudaMemcpyAsync(R->d_work, R->h_up, (size_t)n * 4, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return fail(e);
+            d_ur = reinterpret_cast<const float *>(R->d_work);
+            f->up_inflight = true;
         }
-        cudaStream_t st = f->stream;
-        int rc = upload(dx, hx.data(), n, st);
-        if (rc == ORB_OK) rc = upload(dy, hy.data(), n, st);
-        if (rc == ORB_OK) rc = upload(da, ha.data(), n, st);
-        if (rc == ORB_OK) rc = upload(du, hu.data(), n, st);
-        if (rc == ORB_OK) rc = upload(doct, ho.data(), n, st);
-        if (rc == ORB_OK) rc = upload(dd, d->descriptors, (size_t)n * 32, st);
-        if (rc == ORB_OK) rc = upload(doff, off.data(), ncell + 1, st);
-        if (rc == ORB_OK) rc = upload(didx, idx.data(), idx.size(), st);
-        if (rc == ORB_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = ORB_ERR_CUDA;
-        if (rc != ORB_OK) { cudaFree(f->d_static); cudaStreamDestroy(f->stream); delete f; return rc; }
-        const bool kfv = d->keyframe_view != 0;   // the grid above was filled with the Frame's float bounds either way
-        f->dev = FrameDev{n, dx, dy, da, du, doct, dd, doff, didx, kfv ? (float)(int)f->minX : f->minX, kfv ? (float)(int)f->minY : f->minY, invW, invH};
     }
+    if (n && src->ndist > 0 && src->dist_coef[0] != 0.0f) {   // ref Frame.cc:409-439 (mvKeysUn = mvKeys otherwise, :411-415)
+        rc = orbgpu_undistort_keypoints_async(kp, n, src->fx, src->fy, src->cx, src->cy, src->dist_coef, src->ndist, d_un, st);
+        if (rc != ORB_OK) { frame_abort(f); return rc; }
+        kp = d_un;
+        f->launches++;
+    }
+    FrameBuild B;
+    B.x = L.x; B.y = L.y; B.angle = L.angle; B.uRight = L.uRight; B.octave = L.octave;
+    B.cell_off = L.cell_off; B.cell_idx = L.cell_idx; B.cell_of = L.cell_of;
+    B.minX = f->minX; B.minY = f->minY;
+    B.invW = static_cast<float>(GRID_COLS) / static_cast<float>(f->maxX - f->minX);
+    B.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(f->maxY - f->minY);
+    k_frame_build<<<1, 1024, 0, st>>>(kp, n, d_ur, B);
+    f->launches++;
+    e = cudaGetLastError();
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(L.desc, desc, (size_t)n * 32, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaEventRecord(R->ready, st);
+    if (e != cudaSuccess) return fail(e);
+    frame_set_dev(f, L, src->keyframe_view != 0);
     *out = f;
     return ORB_OK;
 }
@@ -659,19 +996,32 @@ void orb_frame_destroy(orb_frame *f) {
     if (!f) return;
     cudaSetDevice(f->device);
     cudaStreamSynchronize(f->stream);
-    cudaFree(f->d_static);
-    if (f->d_scratch) cudaFree(f->d_scratch);
-    cudaStreamDestroy(f->stream);
+    res_release(f->res);
     delete f;
 }
 
+int orb_frame_sync(orb_frame *f) {
+    ORB_REQUIRE(f, ORB_ERR_INVALID, "null handle");
+    ORB_CUDA_TRY(cudaSetDevice(f->device));
+    ORB_CUDA_TRY(cudaStreamSynchronize(f->stream));
+    f->up_inflight = false;
+    return ORB_OK;
+}
+int orb_frame_size(const orb_frame *f) { return f ? f->n : 0; }
 int64_t orb_frame_launch_count(const orb_frame *f) { return f ? f->launches : 0; }
+void *orb_frame_stream(orb_frame *f) { return f ? (void *)f->stream : nullptr; }
+int orb_frame_last_stats(const orb_frame *f, int64_t *candidates, int32_t *sweeps) {
+    ORB_REQUIRE(f, ORB_ERR_INVALID, "null handle");
+    if (candidates) *candidates = f->last_candidates;
+    if (sweeps) *sweeps = f->last_sweeps;
+    return ORB_OK;
+}
 
 }  // extern "C"
 
 namespace {
 
-// Host description of a query set (all pointers host); uploaded into the target frame's scratch.
+// Host description of a query set (all pointers host unless noted); packed into the frame's upload block.
 struct HostQueries {
     int n = 0;
     const uint8_t *valid = nullptr;
@@ -687,76 +1037,95 @@ struct HostQueries {
     double gate_mono = 0, gate_stereo = 0;
 };
 
-// Phase 1 of every windowed search: upload queries, count candidates, scan, fill (idx, dist) lists.
-// Leaves everything in f->d_scratch; `extra_bytes` are reserved after the lists for the caller's state.
-int build_window_lists(orb_frame *f, const HostQueries &H, size_t extra_bytes, WinQ *Qd, WindowLists *WL, uint8_t **extra) {
+size_t queries_upload_bytes(const HostQueries &H) {
+    const size_t n = (size_t)std::max(H.n, 1);
+    return 16 * ALIGN + n * (1 + 4 * 3 + 4 * 2 + 4 * 2 + 32 + 4 + 1 + 4) + (size_t)H.gate_levels * 4 + ALIGN;
+}
+
+WinQ pack_queries(Upload &up, const HostQueries &H) {
     const int n = H.n;
+    WinQ Q;
+    memset(&Q, 0, sizeof(Q));
+    Q.n = n;
+    Q.valid = H.valid ? up.put(H.valid, n) : nullptr;
+    Q.x = up.put(H.x, n); Q.y = up.put(H.y, n); Q.xy_stride = 1;
+    Q.radius = up.put(H.radius, n);
+    Q.min_level = up.put(H.min_level, n); Q.max_level = up.put(H.max_level, n);
+    Q.strict_levels = H.strict_levels;
+    Q.stereo_ref = H.stereo_ref ? up.put(H.stereo_ref, n) : nullptr;
+    Q.stereo_tol = H.stereo_ref ? up.put(H.stereo_tol, n) : nullptr;
+    Q.desc = H.desc ? up.put(H.desc, (size_t)n * 32) : nullptr;
+    Q.angle = H.angle ? up.put(H.angle, n) : nullptr;
+    Q.claims = H.claims ? up.put(H.claims, n) : nullptr;
+    Q.gate_ur = H.gate_inv_sigma2 ? up.put(H.gate_ur, n) : nullptr;
+    Q.gate_inv_sigma2 = H.gate_inv_sigma2 ? up.put(H.gate_inv_sigma2, H.gate_levels) : nullptr;
+    Q.gate_mono = H.gate_mono; Q.gate_stereo = H.gate_stereo;
+    return Q;
+}
+
+size_t list_capacity(const orb_frame *f, int n) { return std::max<size_t>(f->list_hint, (size_t)32 * n + 4096); }
+
+void launch_lists(orb_frame *f, const WinQ &Q, int *q_off, int *q_cnt, int2 *lists, size_t cap, int *hdr, int prune) {
+    if (Q.n == 0) return;
+    k_window_lists<<<(Q.n * 32 + 255) / 256, 256, 0, f->stream>>>(f->dev, Q, q_off, q_cnt, lists, (int)std::min<size_t>(cap, 0x7fffffff), hdr, prune);
+    f->launches++;
+}
+
+// The windowed matcher: upload, lists, resolve, download.  Retries once with a larger candidate pool when the pool overflowed.
+int search_windowed_host(orb_frame *f, const HostQueries &H, const uint8_t *claimed, int select, int th_dist, float nnratio,
+                         int check_ori, int32_t *assigned, int *nmatches) {
+    ORB_CUDA_TRY(cudaSetDevice(f->device));
+    const int n = H.n, nf = f->n;
+    if (nmatches) *nmatches = 0;
+    for (int i = 0; i < nf; i++) assigned[i] = -1;
+    if (n == 0 || nf == 0) return ORB_OK;
+    ORB_TRY(settle(f));
+    FrameRes *R = f->res;
     cudaStream_t st = f->stream;
-    // pass A: queries + counts + offsets
-    Arena a;
-    auto place = [&](Arena &ar) {
-        ar.used = 0;
-        WinQ Q;
-        Q.n = n;
-        Q.valid = H.valid ? ar.take<uint8_t>(n) : nullptr;
-        Q.x = ar.take<float>(n); Q.y = ar.take<float>(n); Q.radius = ar.take<float>(n);
-        Q.min_level = ar.take<int>(n); Q.max_level = ar.take<int>(n);
-        Q.strict_levels = H.strict_levels;
-        Q.stereo_ref = H.stereo_ref ? ar.take<float>(n) : nullptr;
-        Q.stereo_tol = H.stereo_ref ? ar.take<float>(n) : nullptr;
-        Q.desc = ar.take<uint8_t>((size_t)n * 32);
-        Q.angle = H.angle ? ar.take<float>(n) : nullptr;
-        Q.claims = H.claims ? ar.take<uint8_t>(n) : nullptr;
-        Q.gate_ur = H.gate_inv_sigma2 ? ar.take<float>(n) : nullptr;
-        Q.gate_inv_sigma2 = H.gate_inv_sigma2 ? ar.take<float>(H.gate_levels) : nullptr;
-        Q.gate_mono = H.gate_mono; Q.gate_stereo = H.gate_stereo;
-        WL->off = ar.take<int>(n + 1);
-        return Q;
-    };
-    place(a);
-    const size_t fixed = a.used + (size_t)(n + 1) * 4 + 256;
-    // counts live temporarily where the candidate lists will go
-    ORB_TRY(ensure_scratch(f, fixed + (size_t)n * 4 + extra_bytes + 1024));
-    a.base = (uint8_t *)f->d_scratch;
-    WinQ Q = place(a);
-    const size_t lists_pos = a.used;
-    int *counts = a.take<int>(n);
-    if (H.valid) ORB_TRY(upload((uint8_t *)Q.valid, H.valid, n, st));
-    ORB_TRY(upload((float *)Q.x, H.x, n, st)); ORB_TRY(upload((float *)Q.y, H.y, n, st)); ORB_TRY(upload((float *)Q.radius, H.radius, n, st));
-    ORB_TRY(upload((int *)Q.min_level, H.min_level, n, st)); ORB_TRY(upload((int *)Q.max_level, H.max_level, n, st));
-    if (H.stereo_ref) { ORB_TRY(upload((float *)Q.stereo_ref, H.stereo_ref, n, st)); ORB_TRY(upload((float *)Q.stereo_tol, H.stereo_tol, n, st)); }
-    ORB_TRY(upload((uint8_t *)Q.desc, H.desc, (size_t)n * 32, st));
-    if (H.angle) ORB_TRY(upload((float *)Q.angle, H.angle, n, st));
-    if (H.claims) ORB_TRY(upload((uint8_t *)Q.claims, H.claims, n, st));
-    if (H.gate_inv_sigma2) {
-        ORB_TRY(upload((float *)Q.gate_ur, H.gate_ur, n, st));
-        ORB_TRY(upload((float *)Q.gate_inv_sigma2, H.gate_inv_sigma2, H.gate_levels, st));
+    for (int attempt = 0; attempt < 3; attempt++) {
+        const size_t cap = list_capacity(f, n);
+        const size_t up_need = queries_upload_bytes(H) + up256(nf);
+        const size_t scratch = 4 * up256((size_t)n * 4) + 2 * up256((size_t)nf * 4) + up256(nf);
+        const size_t dn_need = up256((size_t)nf * 4) + ALIGN;
+        ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+        ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+        ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + scratch + dn_need + cap * 8 + ALIGN));
+        Upload up(R->h_up, R->d_work);
+        int *h_hdr;
+        int *hdr = up.slot<int>(64, &h_hdr);
+        memset(h_hdr, 0, 64 * sizeof(int));
+        const WinQ Q = pack_queries(up, H);
+        const uint8_t *d_claimed = claimed ? up.put(claimed, nf) : nullptr;
+        Arena ar;
+        ar.base = R->d_work; ar.used = up.used;
+        int *q_off = ar.take<int>(n), *q_cnt = ar.take<int>(n), *res = ar.take<int>(n), *bins = ar.take<int>(n);
+        int *blocked_by = ar.take<int>(nf), *holder = ar.take<int>(nf);
+        uint8_t *bad = ar.take<uint8_t>(nf);
+        int *d_assigned = ar.take<int>(nf), *d_out = ar.take<int>(8);   // contiguous: one copy down
+        int2 *lists = ar.take<int2>(0);
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
+        launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, select == ORB_SELECT_BEST ? th_dist : -1);
+        k_resolve_windowed<<<1, RES_THREADS, 0, st>>>(f->dev, Q, q_off, q_cnt, lists, d_claimed, blocked_by, res, bins, holder, bad, select,
+                                                      th_dist, nnratio, check_ori, d_assigned, d_out, hdr);
+        f->launches++;
+        ORB_CUDA_TRY(cudaGetLastError());
+        const size_t dn_bytes = up256((size_t)nf * 4) + 8 * sizeof(int);
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, d_assigned, dn_bytes, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaStreamSynchronize(st));
+        const int *h_out = reinterpret_cast<const int *>(R->h_dn + up256((size_t)nf * 4));
+        if (h_out[3]) {   // candidate pool too small: h_out[2] slots were asked for
+            f->list_hint = (size_t)h_out[2] * 5 / 4 + 4096;
+            continue;
+        }
+        f->list_hint = std::max(f->list_hint, (size_t)h_out[2] * 5 / 4 + 1024);
+        memcpy(assigned, R->h_dn, (size_t)nf * 4);
+        if (nmatches) *nmatches = h_out[0];
+        f->last_sweeps = h_out[1];
+        f->last_candidates = h_out[4];
+        return ORB_OK;
     }
-    const int blocks = (n * 32 + 255) / 256;
-    if (n) k_window_count<<<blocks, 256, 0, st>>>(f->dev, Q, counts);
-    k_scan_counts<<<1, 1024, 0, st>>>(counts, n, WL->off);
-    f->launches += 2;
-    int total = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(&total, WL->off + n, 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    // pass B: lists.  Growing the scratch would move the queries, so re-run placement if it grows.
-    const size_t need = fixed + (size_t)total * 8 + 512 + extra_bytes + 1024;
-    if (f->scratch_bytes < need) {
-        // preserve nothing: simply rebuild (rare: only when a frame sees its largest query set)
-        ORB_TRY(ensure_scratch(f, need));
-        return build_window_lists(f, H, extra_bytes, Qd, WL, extra);
-    }
-    Arena b;
-    b.base = (uint8_t *)f->d_scratch;
-    b.used = lists_pos;   // the candidate lists reuse the space of `counts`
-    WL->idx = b.take<int>(total);
-    WL->dist = b.take<int>(total);
-    WL->total = total;
-    *extra = b.base + b.used;
-    if (n && total) { k_window_fill<<<blocks, 256, 0, st>>>(f->dev, Q, WL->off, WL->idx, WL->dist); f->launches++; }
-    ORB_CUDA_TRY(cudaGetLastError());
-    *Qd = Q;
-    return ORB_OK;
+    set_error("candidate pool kept overflowing");
+    return ORB_ERR_CAPACITY;
 }
 
 }  // namespace
@@ -767,49 +1136,37 @@ int orb_frame_features_in_area(orb_frame *f, float x, float y, float r, int min_
                                int capacity, int *n_out) {
     ORB_REQUIRE(f && indices && n_out, ORB_ERR_INVALID, "null argument");
     ORB_CUDA_TRY(cudaSetDevice(f->device));
-    HostQueries H;
-    uint8_t zero_desc[32] = {0};
-    H.n = 1; H.x = &x; H.y = &y; H.radius = &r; H.min_level = &min_level; H.max_level = &max_level; H.desc = zero_desc;
-    WinQ Q; WindowLists WL; uint8_t *extra;
-    ORB_TRY(build_window_lists(f, H, 0, &Q, &WL, &extra));
-    *n_out = WL.total;
-    ORB_REQUIRE(WL.total <= capacity, ORB_ERR_CAPACITY, "index buffer too small");
-    if (WL.total) {
-        ORB_CUDA_TRY(cudaMemcpyAsync(indices, WL.idx, (size_t)WL.total * 4, cudaMemcpyDeviceToHost, f->stream));
-        ORB_CUDA_TRY(cudaStreamSynchronize(f->stream));
-    }
-    return ORB_OK;
-}
-
-static int search_windowed_host(orb_frame *f, const HostQueries &H, const uint8_t *claimed, int select, int th_dist, float nnratio,
-                                int check_ori, int32_t *assigned, int *nmatches) {
-    ORB_CUDA_TRY(cudaSetDevice(f->device));
-    const int n = H.n, nf = f->n;
-    if (nmatches) *nmatches = 0;
-    for (int i = 0; i < nf; i++) assigned[i] = -1;
-    if (n == 0 || nf == 0) return ORB_OK;
-    const size_t extra_bytes = (size_t)nf * 4 + nf + (size_t)n * 8 + (size_t)nf * 4 + 4 + 6 * 256;
-    WinQ Q; WindowLists WL; uint8_t *extra;
-    ORB_TRY(build_window_lists(f, H, extra_bytes, &Q, &WL, &extra));
-    Arena ar; ar.base = extra;
-    int *holder = ar.take<int>(nf);
-    uint8_t *blocking = ar.take<uint8_t>(nf);
-    int *acc_feat = ar.take<int>(n), *acc_bin = ar.take<int>(n), *d_assigned = ar.take<int>(nf), *d_nm = ar.take<int>(1);
+    *n_out = 0;
+    if (f->n == 0) return ORB_OK;
+    ORB_TRY(settle(f));
+    FrameRes *R = f->res;
     cudaStream_t st = f->stream;
-    std::vector<int> h_holder(nf, -1);
-    std::vector<uint8_t> h_block(nf, 0);
-    if (claimed) for (int i = 0; i < nf; i++) if (claimed[i]) { h_holder[i] = -2; h_block[i] = 1; }
-    ORB_TRY(upload(holder, h_holder.data(), nf, st));
-    ORB_TRY(upload(blocking, h_block.data(), nf, st));
-    k_resolve_windowed<<<1, 32, 0, st>>>(f->dev, Q, WL.off, WL.idx, WL.dist, holder, blocking, select, th_dist, nnratio, check_ori,
-                                         acc_feat, acc_bin, d_assigned, d_nm);
-    f->launches++;
+    HostQueries H;
+    H.n = 1; H.x = &x; H.y = &y; H.radius = &r; H.min_level = &min_level; H.max_level = &max_level;
+    const size_t cap = (size_t)f->n + 64;
+    const size_t up_need = queries_upload_bytes(H), dn_need = up256(cap * 8) + 2 * ALIGN;
+    ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+    ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+    ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + dn_need + 4 * ALIGN));
+    Upload up(R->h_up, R->d_work);
+    int *h_hdr;
+    int *hdr = up.slot<int>(64, &h_hdr);
+    memset(h_hdr, 0, 64 * sizeof(int));
+    const WinQ Q = pack_queries(up, H);
+    Arena ar;
+    ar.base = R->d_work; ar.used = up.used;
+    int *q_off = ar.take<int>(1), *q_cnt = ar.take<int>(1);   // one 256-byte piece each: [q_off | q_cnt | lists] go down together
+    int2 *lists = ar.take<int2>(cap);
+    ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
+    launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, -1);
     ORB_CUDA_TRY(cudaGetLastError());
-    int nm = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(assigned, d_assigned, (size_t)nf * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, q_off, 2 * ALIGN + cap * 8, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (nmatches) *nmatches = nm;
+    const int off = *reinterpret_cast<const int *>(R->h_dn), cnt = *reinterpret_cast<const int *>(R->h_dn + ALIGN);
+    const int2 *hl = reinterpret_cast<const int2 *>(R->h_dn + 2 * ALIGN) + off;
+    *n_out = cnt;
+    ORB_REQUIRE(cnt <= capacity, ORB_ERR_CAPACITY, "index buffer too small");
+    for (int i = 0; i < cnt; i++) indices[i] = hl[i].x;
     return ORB_OK;
 }
 
@@ -883,46 +1240,65 @@ int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matc
     if (nmatches) *nmatches = 0;
     for (int i = 0; i < n1; i++) matches12[i] = -1;
     if (n1 == 0 || n2 == 0) return ORB_OK;
-    std::vector<uint8_t> valid(n1);
-    std::vector<float> qx(n1), qy(n1), radius(n1, (float)window_size);
-    std::vector<int32_t> lv(n1);
-    std::vector<uint8_t> desc((size_t)n1 * 32);
-    for (int i = 0; i < n1; i++) {
-        valid[i] = f1->keys[i].octave > 0 ? 0 : 1;      // ref :421-423
-        qx[i] = prev_matched[2 * i]; qy[i] = prev_matched[2 * i + 1];
-        lv[i] = f1->keys[i].octave;                      // GetFeaturesInArea(..., level1, level1), ref :425
+    orb_frame *f = f2;   // runs on the second frame's stream and scratch
+    ORB_TRY(settle(f));
+    ORB_TRY(wait_for(f, f1));
+    FrameRes *R = f->res;
+    cudaStream_t st = f->stream;
+    for (int attempt = 0; attempt < 3; attempt++) {
+        const size_t cap = list_capacity(f, n1);
+        const size_t up_need = 2 * ALIGN + up256((size_t)n1 * 8);
+        const size_t scratch = 6 * up256((size_t)n1 * 4) + 2 * up256((size_t)n2 * 4);
+        const size_t dn_need = up256((size_t)n1 * 4) + up256((size_t)n1 * 8) + ALIGN;
+        ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+        ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+        ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + scratch + dn_need + cap * 8 + ALIGN));
+        Upload up(R->h_up, R->d_work);
+        int *h_hdr;
+        int *hdr = up.slot<int>(64, &h_hdr);
+        memset(h_hdr, 0, 64 * sizeof(int));
+        const float *d_prev = up.put(prev_matched, (size_t)n1 * 2);
+        // the queries are F1's own features: octave-0 ones only (ref :421-423), window around vbPrevMatched at that level
+        // (:425), descriptors and levels straight from F1's device arrays
+        WinQ Q;
+        memset(&Q, 0, sizeof(Q));
+        Q.n = n1; Q.valid_if_zero = f1->dev.octave;
+        Q.x = d_prev; Q.y = d_prev + 1; Q.xy_stride = 2;
+        Q.radius_const = (float)window_size;
+        Q.min_level = f1->dev.octave; Q.max_level = f1->dev.octave;
+        Q.desc = f1->dev.desc;
+        Arena ar;
+        ar.base = R->d_work; ar.used = up.used;
+        int *q_off = ar.take<int>(n1), *q_cnt = ar.take<int>(n1), *next = ar.take<int>(n1), *tdist = ar.take<int>(n1);
+        int *res = ar.take<int>(n1), *res_dist = ar.take<int>(n1), *head = ar.take<int>(n2), *last = ar.take<int>(n2);
+        int *m12 = ar.take<int>(n1);                      // contiguous: [m12 | prev | out] go down in one copy
+        float *d_prev_out = ar.take<float>((size_t)n1 * 2);
+        int *d_out = ar.take<int>(8);
+        int2 *lists = ar.take<int2>(0);
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
+        launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, -1);
+        k_resolve_init<<<1, RES_THREADS, 0, st>>>(f1->dev, f2->dev, q_off, q_cnt, lists, head, next, tdist, res, res_dist, last, nnratio,
+                                                  check_orientation, m12, d_prev, d_prev_out, d_out, hdr);
+        f->launches++;
+        ORB_CUDA_TRY(cudaGetLastError());
+        const size_t o_prev = up256((size_t)n1 * 4), o_out = o_prev + up256((size_t)n1 * 8);
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, m12, o_out + 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaStreamSynchronize(st));
+        const int *h_out = reinterpret_cast<const int *>(R->h_dn + o_out);
+        if (h_out[3]) {
+            f->list_hint = (size_t)h_out[2] * 5 / 4 + 4096;
+            continue;
+        }
+        f->list_hint = std::max(f->list_hint, (size_t)h_out[2] * 5 / 4 + 1024);
+        memcpy(matches12, R->h_dn, (size_t)n1 * 4);
+        memcpy(prev_matched, R->h_dn + o_prev, (size_t)n1 * 8);
+        if (nmatches) *nmatches = h_out[0];
+        f->last_sweeps = h_out[1];
+        f->last_candidates = h_out[4];
+        return ORB_OK;
     }
-    // query descriptors are F1's own rows: copy device-to-device after placement
-    HostQueries H;
-    H.n = n1; H.valid = valid.data(); H.x = qx.data(); H.y = qy.data(); H.radius = radius.data(); H.min_level = lv.data();
-    H.max_level = lv.data(); H.desc = desc.data();
-    cudaStream_t st = f2->stream;
-    ORB_CUDA_TRY(cudaMemcpyAsync(desc.data(), f1->dev.desc, (size_t)n1 * 32, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    const size_t extra_bytes = (size_t)n2 * 8 + (size_t)n1 * 8 + (size_t)n1 * 8 + 4 + 6 * 256;
-    WinQ Q; WindowLists WL; uint8_t *extra;
-    ORB_TRY(build_window_lists(f2, H, extra_bytes, &Q, &WL, &extra));
-    Arena ar; ar.base = extra;
-    int *matched_dist = ar.take<int>(n2), *m21 = ar.take<int>(n2), *m12 = ar.take<int>(n1), *qbin = ar.take<int>(n1);
-    float *d_prev = ar.take<float>((size_t)n1 * 2);
-    int *d_nm = ar.take<int>(1);
-    std::vector<int> init2(n2, 0x7fffffff);
-    ORB_TRY(upload(matched_dist, init2.data(), n2, st));
-    ORB_CUDA_TRY(cudaMemsetAsync(m21, 0xff, (size_t)n2 * 4, st));
-    ORB_CUDA_TRY(cudaMemsetAsync(m12, 0xff, (size_t)n1 * 4, st));
-    ORB_CUDA_TRY(cudaMemsetAsync(qbin, 0xff, (size_t)n1 * 4, st));
-    ORB_TRY(upload(d_prev, prev_matched, (size_t)n1 * 2, st));
-    k_resolve_init<<<1, 32, 0, st>>>(f1->dev, f2->dev, WL.off, WL.idx, WL.dist, matched_dist, m21, m12, qbin, nnratio,
-                                     check_orientation, d_prev, d_nm);
-    f2->launches++;
-    ORB_CUDA_TRY(cudaGetLastError());
-    int nm = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(matches12, m12, (size_t)n1 * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(prev_matched, d_prev, (size_t)n1 * 8, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (nmatches) *nmatches = nm;
-    return ORB_OK;
+    set_error("candidate pool kept overflowing");
+    return ORB_ERR_CAPACITY;
 }
 
 int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *kf_off, const int32_t *kf_idx, const int32_t *f_off,
@@ -936,45 +1312,55 @@ int orb_search_by_bow(orb_frame *kf, orb_frame *f, int ngroups, const int32_t *k
     for (int i = 0; i < f->n; i++) matches[i] = -1;
     if (ngroups == 0 || f->n == 0 || kf->n == 0) return ORB_OK;
     const int nent = kf_off[ngroups], nfent = f_off[ngroups];
-    std::vector<int> ent_fo(nent), ent_fn(nent), ent_po(nent);
-    size_t npairs = 0;
-    for (int g = 0; g < ngroups; g++)
-        for (int a = kf_off[g]; a < kf_off[g + 1]; a++) {
-            ORB_REQUIRE(kf_idx[a] >= 0 && kf_idx[a] < kf->n, ORB_ERR_INVALID, "KF feature index out of range");
-            ent_fo[a] = f_off[g]; ent_fn[a] = f_off[g + 1] - f_off[g]; ent_po[a] = (int)npairs;
-            npairs += ent_fn[a];
-            ORB_REQUIRE(ent_fn[a] < 65536, ORB_ERR_INVALID, "vocabulary node with more than 65535 features");
-        }
-    for (int b = 0; b < nfent; b++) ORB_REQUIRE(f_idx[b] >= 0 && f_idx[b] < f->n, ORB_ERR_INVALID, "F feature index out of range");
-    Arena ar;
-    int *d_kfidx = nullptr, *d_fo = nullptr, *d_fn = nullptr, *d_po = nullptr, *d_fidx = nullptr, *d_dist = nullptr, *d_accf = nullptr,
-        *d_accb = nullptr, *d_matches = nullptr, *d_nm = nullptr;
-    uint8_t *d_kv = nullptr, *d_fv = nullptr;
-    for (int phase = 0; phase < 2; phase++) {
-        ar.used = 0;
-        d_kfidx = ar.take<int>(nent); d_fo = ar.take<int>(nent); d_fn = ar.take<int>(nent); d_po = ar.take<int>(nent);
-        d_fidx = ar.take<int>(nfent); d_dist = ar.take<int>(npairs); d_accf = ar.take<int>(nent); d_accb = ar.take<int>(nent);
-        d_matches = ar.take<int>(f->n); d_nm = ar.take<int>(1);
-        d_kv = ar.take<uint8_t>(kf->n); d_fv = ar.take<uint8_t>(f->n);
-        if (phase == 0) { ORB_TRY(ensure_scratch(f, ar.used + 1024)); ar.base = (uint8_t *)f->d_scratch; }
-    }
+    if (nent == 0) return ORB_OK;
+    ORB_TRY(settle(f));
+    ORB_TRY(wait_for(f, kf));
+    FrameRes *R = f->res;
     cudaStream_t st = f->stream;
-    ORB_TRY(upload(d_kfidx, kf_idx, nent, st)); ORB_TRY(upload(d_fo, ent_fo.data(), nent, st)); ORB_TRY(upload(d_fn, ent_fn.data(), nent, st));
-    ORB_TRY(upload(d_po, ent_po.data(), nent, st)); ORB_TRY(upload(d_fidx, f_idx, nfent, st)); ORB_TRY(upload(d_kv, kf_valid, kf->n, st));
-    if (f_valid) ORB_TRY(upload(d_fv, f_valid, f->n, st));
-    ORB_CUDA_TRY(cudaMemsetAsync(d_matches, 0xff, (size_t)f->n * 4, st));
-    if (nent) {
-        k_bow_dist<<<(nent * 32 + 255) / 256, 256, 0, st>>>(kf->dev, f->dev, nent, d_kfidx, d_fo, d_fn, d_po, d_fidx, d_kv, d_dist);
-        k_resolve_bow<<<1, 32, 0, st>>>(kf->dev, f->dev, nent, d_kfidx, d_fo, d_fn, d_po, d_fidx, d_kv, f_valid ? d_fv : nullptr, d_dist,
-                                        strict_low, nnratio, check_orientation, d_accf, d_accb, d_matches, d_nm);
-        f->launches += 2;
+    size_t npairs = 0;
+    for (int g = 0; g < ngroups; g++) npairs += (size_t)(kf_off[g + 1] - kf_off[g]) * (size_t)(f_off[g + 1] - f_off[g]);
+    for (int a = 0; a < nent; a++) ORB_REQUIRE(kf_idx[a] >= 0 && kf_idx[a] < kf->n, ORB_ERR_INVALID, "KF feature index out of range");
+    for (int b = 0; b < nfent; b++) ORB_REQUIRE(f_idx[b] >= 0 && f_idx[b] < f->n, ORB_ERR_INVALID, "F feature index out of range");
+    const size_t up_need = 4 * up256((size_t)nent * 4) + up256((size_t)std::max(nfent, 1) * 4) + up256(kf->n) + up256(f->n) + ALIGN;
+    const size_t scratch = up256(npairs * 4) + up256((size_t)nent * 4) + up256((size_t)f->n * 4);
+    const size_t dn_need = up256((size_t)f->n * 4) + ALIGN;
+    ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+    ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+    ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + scratch + dn_need + ALIGN));
+    uint8_t *D = R->d_work;
+    Upload up(R->h_up, D);
+    const int *d_kfidx = up.put(kf_idx, nent);
+    int *h_fo, *h_fn, *h_po;
+    const int *d_fo = up.slot<int>(nent, &h_fo), *d_fn = up.slot<int>(nent, &h_fn), *d_po = up.slot<int>(nent, &h_po);
+    {
+        size_t pos = 0;
+        for (int g = 0; g < ngroups; g++)
+            for (int a = kf_off[g]; a < kf_off[g + 1]; a++) {
+                h_fo[a] = f_off[g]; h_fn[a] = f_off[g + 1] - f_off[g]; h_po[a] = (int)pos;
+                pos += h_fn[a];
+            }
     }
+    const int *d_fidx = up.put(f_idx, nfent);
+    const uint8_t *d_kv = up.put(kf_valid, kf->n);
+    const uint8_t *d_fv = f_valid ? up.put(f_valid, f->n) : nullptr;
+    Arena ar;
+    ar.base = D; ar.used = up.used;
+    int *d_dist = ar.take<int>(npairs), *res = ar.take<int>(nent), *taken_by = ar.take<int>(f->n);
+    int *d_matches = ar.take<int>(f->n), *d_out = ar.take<int>(8);
+    ORB_CUDA_TRY(cudaMemcpyAsync(D, R->h_up, up.used, cudaMemcpyHostToDevice, st));
+    k_bow_dist<<<(nent * 32 + 255) / 256, 256, 0, st>>>(kf->dev, f->dev, nent, d_kfidx, d_fo, d_fn, d_po, d_fidx, d_kv, d_dist);
+    k_resolve_bow<<<1, RES_THREADS, 0, st>>>(kf->dev, f->dev, nent, d_kfidx, d_fo, d_fn, d_po, d_fidx, d_kv, d_fv, d_dist, strict_low, nnratio,
+                                             check_orientation, taken_by, res, d_matches, d_out);
+    f->launches += 2;
     ORB_CUDA_TRY(cudaGetLastError());
-    int nm = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(matches, d_matches, (size_t)f->n * 4, cudaMemcpyDeviceToHost, st));
-    if (nent) ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
+    const size_t o_out = up256((size_t)f->n * 4);
+    ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, d_matches, o_out + 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (nmatches) *nmatches = nm;
+    const int *h_out = reinterpret_cast<const int *>(R->h_dn + o_out);
+    memcpy(matches, R->h_dn, (size_t)f->n * 4);
+    if (nmatches) *nmatches = h_out[0];
+    f->last_sweeps = h_out[1];
+    f->last_candidates = (int64_t)npairs;
     return ORB_OK;
 }
 
@@ -996,18 +1382,51 @@ int orb_search_window_best(orb_frame *f, const orb_window_queries *q, const orb_
         H.gate_ur = gate->ur; H.gate_inv_sigma2 = gate->inv_level_sigma2; H.gate_levels = f->nlevels;
         H.gate_mono = gate->chi2_mono; H.gate_stereo = gate->chi2_stereo;
     }
-    WinQ Q; WindowLists WL; uint8_t *extra;
-    ORB_TRY(build_window_lists(f, H, (size_t)n * 8 + 512, &Q, &WL, &extra));
-    Arena ar; ar.base = extra;
-    int *d_idx = ar.take<int>(n), *d_dist = ar.take<int>(n);
+    ORB_TRY(settle(f));
+    FrameRes *R = f->res;
     cudaStream_t st = f->stream;
-    k_window_best<<<(n * 32 + 255) / 256, 256, 0, st>>>(n, WL.off, WL.idx, WL.dist, d_idx, d_dist);
-    f->launches++;
-    ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpyAsync(best_idx, d_idx, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, d_dist, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    return ORB_OK;
+    for (int attempt = 0; attempt < 3; attempt++) {
+        const size_t cap = list_capacity(f, n);
+        const size_t up_need = queries_upload_bytes(H);
+        const size_t scratch = 2 * up256((size_t)n * 4);
+        const size_t dn_need = 2 * up256((size_t)n * 4) + ALIGN;
+        ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+        ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+        ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + scratch + dn_need + cap * 8 + ALIGN));
+        Upload up(R->h_up, R->d_work);
+        int *h_hdr;
+        int *hdr = up.slot<int>(64, &h_hdr);
+        memset(h_hdr, 0, 64 * sizeof(int));
+        const WinQ Q = pack_queries(up, H);
+        Arena ar;
+        ar.base = R->d_work; ar.used = up.used;
+        int *q_off = ar.take<int>(n), *q_cnt = ar.take<int>(n);
+        int *d_idx = ar.take<int>(n), *d_dist = ar.take<int>(n);
+        int *d_hdr_copy = ar.take<int>(8);
+        int2 *lists = ar.take<int2>(0);
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
+        launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, -1);
+        k_window_best<<<(n + 255) / 256, 256, 0, st>>>(n, q_off, q_cnt, lists, d_idx, d_dist);
+        f->launches++;
+        ORB_CUDA_TRY(cudaGetLastError());
+        ORB_CUDA_TRY(cudaMemcpyAsync(d_hdr_copy, hdr, 8 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        const size_t o_dist = up256((size_t)n * 4), o_hdr = 2 * o_dist;
+        ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, d_idx, o_hdr + 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaStreamSynchronize(st));
+        const int *h_hdr2 = reinterpret_cast<const int *>(R->h_dn + o_hdr);
+        if (h_hdr2[1]) {
+            f->list_hint = (size_t)h_hdr2[0] * 5 / 4 + 4096;
+            continue;
+        }
+        f->list_hint = std::max(f->list_hint, (size_t)h_hdr2[0] * 5 / 4 + 1024);
+        memcpy(best_idx, R->h_dn, (size_t)n * 4);
+        memcpy(best_dist, R->h_dn + o_dist, (size_t)n * 4);
+        f->last_candidates = h_hdr2[2];
+        f->last_sweeps = 0;
+        return ORB_OK;
+    }
+    set_error("candidate pool kept overflowing");
+    return ORB_ERR_CAPACITY;
 }
 
 int orb_search_for_triangulation(orb_frame *kf1, orb_frame *kf2, int ngroups, const int32_t *off1, const int32_t *idx1,
@@ -1024,32 +1443,36 @@ int orb_search_for_triangulation(orb_frame *kf1, orb_frame *kf2, int ngroups, co
     if (ngroups == 0 || kf1->n == 0 || kf2->n == 0) return ORB_OK;
     const int nent = off1[ngroups], nent2 = off2[ngroups];
     if (nent == 0 || nent2 == 0) return ORB_OK;
-    std::vector<int> ent_o2(nent), ent_n2(nent);
+    orb_frame *f = kf1;   // scratch and stream of the first key frame
+    ORB_TRY(settle(f));
+    ORB_TRY(wait_for(f, kf2));
+    FrameRes *R = f->res;
+    cudaStream_t st = f->stream;
+    const int nl = kf2->nlevels;
+    const size_t up_need = 3 * up256((size_t)nent * 4) + up256((size_t)nent2 * 4) + up256(kf1->n) + up256(kf2->n) + 2 * up256((size_t)nl * 4) + ALIGN;
+    const size_t dn_need = up256((size_t)kf1->n * 4) + ALIGN;
+    ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
+    ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
+    ORB_TRY(grow_dev(&R->d_work, &R->work_bytes, up_need + dn_need + ALIGN));
+    Upload up(R->h_up, R->d_work);
+    const int *d_idx1 = up.put(idx1, nent);
+    int *h_o2, *h_n2;
+    const int *d_o2 = up.slot<int>(nent, &h_o2), *d_n2 = up.slot<int>(nent, &h_n2);
     for (int g = 0; g < ngroups; g++) {
         ORB_REQUIRE(off2[g + 1] - off2[g] < 65536, ORB_ERR_INVALID, "vocabulary node with more than 65535 features");
         for (int a = off1[g]; a < off1[g + 1]; a++) {
             ORB_REQUIRE(idx1[a] >= 0 && idx1[a] < kf1->n, ORB_ERR_INVALID, "KF1 feature index out of range");
-            ent_o2[a] = off2[g]; ent_n2[a] = off2[g + 1] - off2[g];
+            h_o2[a] = off2[g]; h_n2[a] = off2[g + 1] - off2[g];
         }
     }
     for (int b = 0; b < nent2; b++) ORB_REQUIRE(idx2[b] >= 0 && idx2[b] < kf2->n, ORB_ERR_INVALID, "KF2 feature index out of range");
-    orb_frame *f = kf1;   // scratch and stream of the first key frame
+    const int *d_idx2 = up.put(idx2, nent2);
+    const uint8_t *d_u1 = up.put(usable1, kf1->n), *d_u2 = up.put(usable2, kf2->n);
+    const float *d_sigma = up.put(level_sigma2, nl), *d_scale = up.put(kf2->scale.data(), nl);
     Arena ar;
-    int *d_idx1 = nullptr, *d_o2 = nullptr, *d_n2 = nullptr, *d_idx2 = nullptr, *d_m12 = nullptr, *d_nm = nullptr;
-    float *d_sigma = nullptr, *d_scale = nullptr;
-    uint8_t *d_u1 = nullptr, *d_u2 = nullptr;
-    for (int phase = 0; phase < 2; phase++) {
-        ar.used = 0;
-        d_idx1 = ar.take<int>(nent); d_o2 = ar.take<int>(nent); d_n2 = ar.take<int>(nent); d_idx2 = ar.take<int>(nent2);
-        d_m12 = ar.take<int>(kf1->n); d_nm = ar.take<int>(1);
-        d_sigma = ar.take<float>(kf2->nlevels); d_scale = ar.take<float>(kf2->nlevels);
-        d_u1 = ar.take<uint8_t>(kf1->n); d_u2 = ar.take<uint8_t>(kf2->n);
-        if (phase == 0) { ORB_TRY(ensure_scratch(f, ar.used + 1024)); ar.base = (uint8_t *)f->d_scratch; }
-    }
-    cudaStream_t st = f->stream;
-    ORB_TRY(upload(d_idx1, idx1, nent, st)); ORB_TRY(upload(d_o2, ent_o2.data(), nent, st)); ORB_TRY(upload(d_n2, ent_n2.data(), nent, st));
-    ORB_TRY(upload(d_idx2, idx2, nent2, st)); ORB_TRY(upload(d_u1, usable1, kf1->n, st)); ORB_TRY(upload(d_u2, usable2, kf2->n, st));
-    ORB_TRY(upload(d_sigma, level_sigma2, kf2->nlevels, st)); ORB_TRY(upload(d_scale, kf2->scale.data(), kf2->nlevels, st));
+    ar.base = R->d_work; ar.used = up.used;
+    int *d_m12 = ar.take<int>(kf1->n), *d_nm = ar.take<int>(8);
+    ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
     ORB_CUDA_TRY(cudaMemsetAsync(d_m12, 0xff, (size_t)kf1->n * 4, st));
     TriArgs A;
     for (int i = 0; i < 9; i++) A.F[i] = F12[i];
@@ -1058,30 +1481,30 @@ int orb_search_for_triangulation(orb_frame *kf1, orb_frame *kf2, int ngroups, co
     k_tri_filter<<<1, 1024, 0, st>>>(kf1->dev, kf2->dev, d_m12, check_orientation, d_nm);
     f->launches += 2;
     ORB_CUDA_TRY(cudaGetLastError());
-    int nm = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(matches12, d_m12, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
+    const size_t o_nm = up256((size_t)kf1->n * 4);
+    ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, d_m12, o_nm + sizeof(int), cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (nmatches) *nmatches = nm;
+    memcpy(matches12, R->h_dn, (size_t)kf1->n * 4);
+    if (nmatches) *nmatches = *reinterpret_cast<const int *>(R->h_dn + o_nm);
     return ORB_OK;
 }
 
 int orb_rot_hist_filter(const float *angle_a, const float *angle_b, int n, uint8_t *keep) {
     ORB_REQUIRE(n >= 0 && (n == 0 || (angle_a && angle_b && keep)), ORB_ERR_INVALID, "bad argument");
     if (n == 0) return ORB_OK;
-    float *da = nullptr;
-    ORB_CUDA_TRY(cudaMalloc(&da, (size_t)n * 9 + 64));
-    float *db = da + n;
-    uint8_t *dk = (uint8_t *)(db + n);
-    cudaError_t e = cudaMemcpy(da, angle_a, (size_t)n * 4, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(db, angle_b, (size_t)n * 4, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) {
-        k_rot_hist_filter<<<1, 1024>>>(da, db, n, dk);
-        e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpy(keep, dk, n, cudaMemcpyDeviceToHost);
-    cudaFree(da);
-    ORB_CUDA_TRY(e);
+    ThreadCtx *T = nullptr;
+    ORB_TRY(orbgpu_thread_ctx(&T, (size_t)n * 9 + 4 * ALIGN, (size_t)n * 9 + 4 * ALIGN));
+    float *ha = reinterpret_cast<float *>(T->h_buf), *hb = ha + n;
+    memcpy(ha, angle_a, (size_t)n * 4);
+    memcpy(hb, angle_b, (size_t)n * 4);
+    float *da = reinterpret_cast<float *>(T->d_buf), *db = da + n;
+    uint8_t *dk = reinterpret_cast<uint8_t *>(db + n), *hk = reinterpret_cast<uint8_t *>(hb + n);
+    ORB_CUDA_TRY(cudaMemcpyAsync(da, ha, (size_t)n * 8, cudaMemcpyHostToDevice, T->stream));
+    k_rot_hist_filter<<<1, 1024, 0, T->stream>>>(da, db, n, dk);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpyAsync(hk, dk, n, cudaMemcpyDeviceToHost, T->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(T->stream));
+    memcpy(keep, hk, n);
     return ORB_OK;
 }
 

@@ -6,6 +6,9 @@
 // (tests/golden/cv2_undistort.npz: 0 differing floats).  One thread per point; compiled with --fmad=false so that the
 // double expressions are evaluated operation by operation like the host build of OpenCV.
 #include "orb_common.cuh"
+#include "orb_internal.cuh"
+
+#include <cstring>
 
 using namespace orbgpu;
 
@@ -69,6 +72,17 @@ int make_cam(float fx, float fy, float cx, float cy, const float *dist, int ndis
 
 }  // namespace
 
+int orbgpu_undistort_keypoints_async(const orb_keypoint *keys, int n, float fx, float fy, float cx, float cy, const float *dist_coef,
+                                     int ndist, orb_keypoint *keys_un, cudaStream_t stream) {
+    Cam c;
+    int rc = make_cam(fx, fy, cx, cy, dist_coef, ndist, &c);
+    if (rc != ORB_OK) return rc;
+    if (n == 0) return ORB_OK;
+    k_undistort_keypoints<<<(n + 127) / 128, 128, 0, stream>>>(keys, n, c, keys_un);
+    ORB_CUDA_TRY(cudaGetLastError());
+    return ORB_OK;
+}
+
 extern "C" {
 
 int orb_undistort_keypoints(const orb_keypoint *keys, int n, float fx, float fy, float cx, float cy, const float *dist_coef,
@@ -79,22 +93,30 @@ int orb_undistort_keypoints(const orb_keypoint *keys, int n, float fx, float fy,
     if (rc != ORB_OK) return rc;
     if (n == 0) return ORB_OK;
     const size_t bytes = (size_t)n * sizeof(orb_keypoint);
+    ThreadCtx *T = nullptr;
+    rc = orbgpu_thread_ctx(&T, 0, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;   // the thread's call stream (orb_set_call_stream), never the legacy default stream
     if (dist_coef[0] == 0.0f) {   // `mvKeysUn = mvKeys` (Frame.cc:411-415)
-        if (keys != keys_un) ORB_CUDA_TRY(cudaMemcpy(keys_un, keys, bytes, loc == ORB_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToHost));
+        if (keys != keys_un) {
+            if (loc == ORB_DEVICE) ORB_CUDA_TRY(cudaMemcpyAsync(keys_un, keys, bytes, cudaMemcpyDeviceToDevice, st));
+            else memcpy(keys_un, keys, bytes);
+        }
         return ORB_OK;
     }
     if (loc == ORB_DEVICE) {
-        k_undistort_keypoints<<<(n + 127) / 128, 128>>>(keys, n, c, keys_un);
+        k_undistort_keypoints<<<(n + 127) / 128, 128, 0, st>>>(keys, n, c, keys_un);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
     }
     DevBuf a, b;
     ORB_CUDA_TRY(a.alloc(bytes));
     ORB_CUDA_TRY(b.alloc(bytes));
-    ORB_CUDA_TRY(cudaMemcpy(a.p, keys, bytes, cudaMemcpyHostToDevice));
-    k_undistort_keypoints<<<(n + 127) / 128, 128>>>((const orb_keypoint *)a.p, n, c, (orb_keypoint *)b.p);
+    ORB_CUDA_TRY(cudaMemcpyAsync(a.p, keys, bytes, cudaMemcpyHostToDevice, st));
+    k_undistort_keypoints<<<(n + 127) / 128, 128, 0, st>>>((const orb_keypoint *)a.p, n, c, (orb_keypoint *)b.p);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(keys_un, b.p, bytes, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(keys_un, b.p, bytes, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }
 
@@ -106,18 +128,23 @@ int orb_undistort_points(const float *xy, int n, float fx, float fy, float cx, f
     if (rc != ORB_OK) return rc;
     if (n == 0) return ORB_OK;
     const size_t bytes = (size_t)n * 8;
+    ThreadCtx *T = nullptr;
+    rc = orbgpu_thread_ctx(&T, 0, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
     if (loc == ORB_DEVICE) {
-        k_undistort_points<<<(n + 127) / 128, 128>>>((const float2 *)xy, n, c, (float2 *)xy_un);
+        k_undistort_points<<<(n + 127) / 128, 128, 0, st>>>((const float2 *)xy, n, c, (float2 *)xy_un);
         ORB_CUDA_TRY(cudaGetLastError());
         return ORB_OK;
     }
     DevBuf a, b;
     ORB_CUDA_TRY(a.alloc(bytes));
     ORB_CUDA_TRY(b.alloc(bytes));
-    ORB_CUDA_TRY(cudaMemcpy(a.p, xy, bytes, cudaMemcpyHostToDevice));
-    k_undistort_points<<<(n + 127) / 128, 128>>>((const float2 *)a.p, n, c, (float2 *)b.p);
+    ORB_CUDA_TRY(cudaMemcpyAsync(a.p, xy, bytes, cudaMemcpyHostToDevice, st));
+    k_undistort_points<<<(n + 127) / 128, 128, 0, st>>>((const float2 *)a.p, n, c, (float2 *)b.p);
     ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaMemcpy(xy_un, b.p, bytes, cudaMemcpyDeviceToHost));
+    ORB_CUDA_TRY(cudaMemcpyAsync(xy_un, b.p, bytes, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
     return ORB_OK;
 }
 

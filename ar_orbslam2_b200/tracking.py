@@ -13,7 +13,8 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._abi import (KEYPOINT_DTYPE, OrbFrameDesc, OrbLastPoints, OrbReprojGate, OrbTrackPoints, OrbWindowQueries, optr, ptr)
+from ._abi import (KEYPOINT_DTYPE, OrbFrameDesc, OrbFrameSource, OrbLastPoints, OrbReprojGate, OrbTrackPoints, OrbWindowQueries, optr,
+                   ptr)
 
 ORB_SELECT_BEST, ORB_SELECT_RATIO_LEVEL = 0, 1
 
@@ -56,6 +57,46 @@ class Frame:
         self._h = C.c_void_p()
         self.B.check(getattr(self.B.L, self.B.prefix + "frame_create")(C.byref(d), C.byref(self._h)), "frame_create")
         _lib.register(self)
+
+    @classmethod
+    def from_extractor(cls, ex, slot, bounds, camera=None, dist_coef=None, u_right=None, u_right_device=None, keyframe_view=False):
+        """The Frame constructor's tail (ref Frame.cc:196-232: UndistortKeyPoints + AssignFeaturesToGrid) on the device, from the
+        results the extractor's last call left in HBM (orb_frame_from_extractor): no key point or descriptor crosses the host.
+        camera = (fx, fy, cx, cy) and dist_coef only matter for a distorted camera; u_right: host array, or u_right_device: device
+        pointer (int) of mvuRight."""
+        self = cls.__new__(cls)
+        self.B = _GpuBackend()
+        s = OrbFrameSource()
+        s.min_x, s.max_x, s.min_y, s.max_y = [float(b) for b in bounds]
+        if camera is not None:
+            s.fx, s.fy, s.cx, s.cy = [float(np.float32(c)) for c in camera]
+        d = np.zeros(5, np.float32) if dist_coef is None else np.ascontiguousarray(dist_coef, np.float32)
+        s.ndist = 0 if dist_coef is None else len(d)
+        for i in range(min(len(d), 5)):
+            s.dist_coef[i] = float(d[i])
+        self.u_right = _f32(u_right)
+        if self.u_right is not None:
+            s.u_right, s.u_right_loc = self.u_right.ctypes.data, 0
+        elif u_right_device:
+            s.u_right, s.u_right_loc = int(u_right_device), 1
+        s.keyframe_view = 1 if keyframe_view else 0
+        self._h = C.c_void_p()
+        self.B.check(self.B.L.orb_frame_from_extractor(ex._h, int(slot), C.byref(s), C.byref(self._h)), "orb_frame_from_extractor")
+        self.N = int(self.B.L.orb_frame_size(self._h))
+        self.scale = ex.GetScaleFactors()
+        self.bounds = tuple(float(b) for b in bounds)
+        self.keys = self.desc = None
+        _lib.register(self)
+        return self
+
+    def sync(self):
+        self.B.check(self.B.L.orb_frame_sync(self._h), "orb_frame_sync")
+
+    def last_stats(self):
+        """(candidate pairs whose distance was computed, claim-resolution sweeps) of the last matcher call on this frame."""
+        c, s = C.c_int64(), C.c_int32()
+        self.B.check(self.B.L.orb_frame_last_stats(self._h, C.byref(c), C.byref(s)), "orb_frame_last_stats")
+        return c.value, s.value
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:

@@ -27,6 +27,20 @@ extern "C" {
 
 #define ORBGPU_ABI_VERSION 1
 
+/* Streams.  Every handle (extractor, frame, database, vocabulary) owns a non-blocking CUDA stream.  The entry points that take
+ * no handle (orb_descriptor_distance, orb_hamming_top2, orb_top2_merge, orb_search_matches_ratio, orb_is_in_frustum,
+ * orb_undistort_*, orb_distinctive_descriptors, orb_rot_hist_filter, and orb_cvt_color_gray / orb_remap_linear called with
+ * stream == NULL) run on the calling thread's CALL STREAM: by default a non-blocking stream the library creates per thread --
+ * never CUDA's legacy default stream, so threads do not serialise against each other (the reference calls these from
+ * Tracking, LocalMapping and LoopClosing concurrently).  Host-mode (ORB_HOST) calls block until their results are in the
+ * caller's arrays.  Device-mode (ORB_DEVICE) calls are ASYNCHRONOUS on the call stream and are NOT ordered with any handle's
+ * stream: to feed a helper's device output to a handle (e.g. orb_cvt_color_gray -> orb_extract_batch, orb_is_in_frustum ->
+ * a matcher) either make the handle's stream the call stream first -- orb_set_call_stream(orb_extractor_stream(ex), 1) --
+ * or call orb_call_stream_sync() in between.                                                                           */
+int orb_set_call_stream(void *cuda_stream, int use_it);   /* use_it = 0: back to the thread's own stream                 */
+void *orb_get_call_stream(void);                          /* cudaStream_t the next stream-less call of this thread uses  */
+int orb_call_stream_sync(void);
+
 typedef enum orb_status {
     ORB_OK = 0,
     ORB_ERR_INVALID = -1,      /* bad argument (null pointer, size out of range ...)            */
@@ -64,8 +78,9 @@ typedef struct orb_params {
     int32_t max_height;
     int32_t max_batch;     /* frames processed per orb_extract_batch call (>=1)              */
     int32_t device;        /* CUDA ordinal, -1 = current device                              */
-    int32_t blur_taps;     /* 0: OpenCV>=3.4/4.x 8.8 fixed-point taps {18,34,48,56,48,34,18};
-                              1: OpenCV 2.4 rounded-float taps {18,34,49,55,49,34,18}        */
+    int32_t blur_taps;     /* 0: OpenCV>=3.4/4.x 8.8 fixed-point taps {18,34,48,56,48,34,18} (pinned against cv2 4.13.0);
+                              1: OpenCV 2.4 rounded-float taps {18,34,49,55,49,34,18} -- UNVERIFIED: no OpenCV 2.4
+                                 exists on the build box, the taps are derived from its source, not from its output */
 } orb_params;
 
 #define ORB_MAX_LEVELS 16
@@ -196,6 +211,35 @@ typedef struct orb_frame_desc {
 typedef struct orb_frame orb_frame;
 int orb_frame_create(const orb_frame_desc *desc, orb_frame **out);
 void orb_frame_destroy(orb_frame *f);
+
+/* The same index built ON THE DEVICE from the results the extractor's last call left in HBM, with no host round trip
+ * (ref: the Frame constructors run ExtractORB, UndistortKeyPoints and AssignFeaturesToGrid back to back,
+ * src/Frame.cc:83-95,196-232).  slot = batch slot of the last orb_extract / orb_extract_batch / orb_stereo_frame call of
+ * `ex` (0 = left, 1 = right for orb_stereo_frame).  The bounds are Frame::mnMinX.. (ComputeImageBounds, :441-468); key points
+ * are undistorted on the device when ndist > 0 and dist_coef[0] != 0 (`mvKeysUn = mvKeys` otherwise, :411-415).  u_right =
+ * mvuRight (n floats, host or device per u_right_loc; NULL = monocular, all -1; orb_extractor_stereo_result gives the device
+ * array orb_stereo_frame left).  Asynchronous on the new frame's stream, ordered after the extraction; the extractor may
+ * start its next frame only after the first matcher call on this frame returned, or after orb_frame_sync.  Frames borrow
+ * their stream and buffers from a pool: creating one per camera frame allocates nothing once the pool is warm.        */
+typedef struct orb_frame_source {
+    float min_x, max_x, min_y, max_y;
+    float fx, fy, cx, cy;
+    float dist_coef[5];
+    int32_t ndist;
+    const float *u_right;
+    int32_t u_right_loc;
+    int32_t keyframe_view;
+} orb_frame_source;
+int orb_frame_from_extractor(orb_extractor *ex, int slot, const orb_frame_source *src, orb_frame **out);
+int orb_frame_sync(orb_frame *f);
+int orb_frame_size(const orb_frame *f);                   /* number of key points                                       */
+void *orb_frame_stream(orb_frame *f);
+int64_t orb_frame_launch_count(const orb_frame *f);
+/* Of the last matcher call on this frame: candidate (query, feature) pairs whose distance was computed, and the number of
+ * claim-resolution sweeps (see csrc/orb_track.cu).                                                                   */
+int orb_frame_last_stats(const orb_frame *f, int64_t *candidates, int32_t *sweeps);
+/* Device arrays orb_stereo_frame left in the handle: mvuRight / mvDepth of the left frame (capacity floats each).       */
+int orb_extractor_stereo_result(orb_extractor *ex, const float **dev_u_right, const float **dev_depth);
 
 /* ref: Frame::GetFeaturesInArea, src/Frame.cc:332-385 -- indices in the reference's
  * traversal order (ix outer, iy inner, insertion order).                                   */
@@ -401,10 +445,11 @@ int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *q
  * Tracking::GrabImageStereo / GrabImageRGBD / GrabImageMonocular (src/Tracking.cc:510-526,545-556,567-577).  8-bit
  * interleaved input with `channels` = 3 or 4; rgb_order = 1 for RGB(A) (mbRGB), 0 for BGR(A).  variant 0 = OpenCV
  * 3.x/4.x arithmetic `(R*9798 + G*19235 + B*3735 + 16384) >> 15` (pinned against cv2 4.13.0), variant 1 = OpenCV
- * 2.4's `(R*4899 + G*9617 + B*1868 + 8192) >> 14` (the version the reference was built with; unverifiable here).
- * `batch` images, image b at src + b*src_stride / dst + b*dst_stride.  loc = where src and dst live; `stream` is a
- * cudaStream_t (NULL = default stream); ORB_DEVICE calls are asynchronous on it, so the grey image can be handed to
- * orb_extract_batch(image_loc = ORB_DEVICE) without touching the host.                                           */
+ * 2.4's `(R*4899 + G*9617 + B*1868 + 8192) >> 14` (the version the reference was built with; UNVERIFIED: no OpenCV 2.4
+ * on the build box).  `batch` images, image b at src + b*src_stride / dst + b*dst_stride.  loc = where src and dst live;
+ * `stream` is a cudaStream_t (NULL = the thread's call stream, see "Streams" at the top); ORB_DEVICE calls are asynchronous
+ * on it.  To hand the grey image to orb_extract_batch(image_loc = ORB_DEVICE) without touching the host pass
+ * stream = orb_extractor_stream(ex): the conversion is then ordered in front of the extraction.                      */
 int orb_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch, size_t src_stride, int channels,
                        int rgb_order, int variant, int batch, uint8_t *dst, int dst_pitch, size_t dst_stride, int loc,
                        void *stream);
@@ -414,7 +459,8 @@ int orb_cvt_color_gray(const uint8_t *src, int width, int height, int src_pitch,
  * channel; map_x / map_y hold one source coordinate per destination pixel (map_pitch floats per row).  Arithmetic = OpenCV's
  * fixed-point bilinear remap (1/32-pixel coordinates, 15-bit weights, zero outside the source), pinned against cv2 4.13.0.
  * `batch` images share the maps (image b at src + b*src_stride / dst + b*dst_stride); loc = where src, maps and dst live;
- * `stream` is a cudaStream_t (NULL = default), ORB_DEVICE calls are asynchronous on it.                                */
+ * `stream` is a cudaStream_t (NULL = the thread's call stream), ORB_DEVICE calls are asynchronous on it; pass
+ * orb_extractor_stream(ex) to order the rectification in front of that handle's extraction.                            */
 int orb_remap_linear(const uint8_t *src, int src_width, int src_height, int src_pitch, size_t src_stride,
                      const float *map_x, const float *map_y, int map_pitch, uint8_t *dst, int dst_width, int dst_height,
                      int dst_pitch, size_t dst_stride, int batch, int loc, void *stream);
@@ -424,7 +470,8 @@ int orb_remap_linear(const uint8_t *src, int src_width, int src_height, int src_
  * fx, fy, cx, cy are mK's float entries, dist_coef = mDistCoef (k1, k2, p1, p2 [, k3]; src/Tracking.cc:427-438).
  * Arithmetic = OpenCV >= 3.x (double precision, 5 iterations, gives up on a point whose radial factor turns negative);
  * pinned against cv2 4.13.0.  orb_undistort_points is the same on bare (x,y) pairs: the four image corners of
- * Frame::ComputeImageBounds (src/Frame.cc:441-468).  loc = where the arrays live (ORB_DEVICE: asynchronous, default stream). */
+ * Frame::ComputeImageBounds (src/Frame.cc:441-468).  loc = where the arrays live (ORB_DEVICE: asynchronous on the thread's
+ * call stream, see "Streams").                                                                                        */
 int orb_undistort_keypoints(const orb_keypoint *keys, int n, float fx, float fy, float cx, float cy,
                             const float *dist_coef, int ndist, orb_keypoint *keys_un, int loc);
 int orb_undistort_points(const float *xy, int n, float fx, float fy, float cx, float cy,
@@ -465,7 +512,7 @@ int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *p
  * the row with the smallest median, first row on ties (`median < BestMedian`, :272-275).  Any number of map points
  * per call: point p owns rows [offsets[p], offsets[p+1]).  best_row[p] = index of the chosen row inside its group
  * (-1 for an empty group: the reference returns early and keeps the old descriptor), best_median[p] = its median.
- * loc = where all four arrays live; ORB_DEVICE calls are asynchronous on the default stream.                      */
+ * loc = where all four arrays live; ORB_DEVICE calls are asynchronous on the thread's call stream (see "Streams").  */
 int orb_distinctive_descriptors(const uint8_t *descriptors, const int32_t *offsets, int npoints, int loc,
                                 int32_t *best_row, int32_t *best_median);
 

@@ -251,3 +251,62 @@ def test_pitched_host_inputs(oracle, gpu_lib):
         rk, rd = ref.extract(imgs[b])
         assert n[b] == len(rk) and kps[b, : n[b]].tobytes() == rk.tobytes() and np.array_equal(desc[b, : n[b]], rd), b
     ex.close()
+
+
+def test_two_live_handles_with_different_quotas(oracle, gpu_lib):
+    """the quadtree's dynamic shared-memory limit is a per-function attribute.  A smaller handle created AFTER a
+    larger one (the reverse of Tracking.cc:455-463) must not lower it under the larger handle's launches."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h = 640, 480
+    big = ORBextractor(2000, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    small = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    rb, rs = oracle.RefExtractor(2000), oracle.RefExtractor(1000)
+    for seed in (1, 2, 3):
+        img = synth_frame(w, h, seed)
+        for ex, ref in ((big, rb), (small, rs), (big, rb)):
+            gk, gd = ex(img)
+            rk, rd = ref.extract(img)
+            assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
+    big.close(); small.close()
+
+
+def test_too_many_features_is_a_clear_error(gpu_lib):
+    from ar_orbslam2_b200 import _lib
+    from ar_orbslam2_b200.extractor import ORBextractor
+    with pytest.raises(_lib.OrbGpuError) as e:
+        ORBextractor(40000, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    assert e.value.code == -1 and "shared memory" in str(e.value)
+
+
+def test_cvtcolor_chained_in_front_of_extraction(oracle, gpu_lib):
+    """a device-mode helper feeding a handle.  The documented way -- pass the handle's stream -- and the thread's
+    call stream + orb_call_stream_sync both give the oracle's key points."""
+    import ctypes as C
+    import torch
+    from ar_orbslam2_b200.color import cvtColorGray_device
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h = 640, 480
+    g = synth_frame(w, h, 4)
+    rgb = np.stack([g, g, g], 2).copy()
+    rk, rd = oracle.RefExtractor(1000).extract(g)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    dev = torch.device("cuda", 0)
+    d_rgb = torch.from_numpy(rgb).to(dev)
+    cap = ex.default_capacity
+    for mode in ("handle_stream", "call_stream"):
+        d_grey = torch.zeros((h, w), dtype=torch.uint8, device=dev)
+        d_k = torch.zeros((cap, 28), dtype=torch.uint8, device=dev)
+        d_d = torch.zeros((cap, 32), dtype=torch.uint8, device=dev)
+        d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+        if mode == "handle_stream":
+            cvtColorGray_device(d_rgb.data_ptr(), w, h, 3 * w, 3 * w * h, 3, True, 1, d_grey.data_ptr(), w, w * h, stream=ex.stream)
+        else:
+            cvtColorGray_device(d_rgb.data_ptr(), w, h, 3 * w, 3 * w * h, 3, True, 1, d_grey.data_ptr(), w, w * h, stream=None)
+            assert gpu_lib.orb_call_stream_sync() == 0
+        ex.extract_batch_device(d_grey.data_ptr(), 1, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap, d_n.data_ptr())
+        ex.sync()
+        n = int(d_n.item())
+        assert n == len(rk)
+        assert d_k[:n].cpu().numpy().tobytes() == rk.tobytes() and np.array_equal(d_d[:n].cpu().numpy(), rd)
+    ex.close()

@@ -221,3 +221,142 @@ def test_gpu_windowed_equals_reference_kf_and_sim3(scene, oracle, gpu_lib):
         ng, ag = ORBmatcher(0.9, False).SearchWindowed(g, R["u"], R["v"], radius, lvl - 1, lvl, scene["da"], ORB_SELECT_BEST, 50, valid=R["valid"],
                                                        strict_levels=True, claimed=c["claimed"], check_orientation=False)
         assert R["nmatches"] > 100 and ng == R["nmatches"] and np.array_equal(ag, R["assigned"])
+
+
+# ---- round 2: device-built frame index, contention stress for the sweep-based claim resolution ----------------------
+
+def test_frame_from_extractor_equals_host_frame(scene, oracle, gpu_lib):
+    """orb_frame_from_extractor (grid built on the device from the extractor's resident results) must behave exactly like
+    the frame built from host arrays: same GetFeaturesInArea lists, same SearchForInitialization result."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+    a = synth_frame(W, H, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    bounds = (0.0, float(W), 0.0, float(H))
+    ex = ORBextractor(2000, 1.2, 8, 20, 7, max_width=W, max_height=H)
+    ka, da = ex(a)
+    assert ka.tobytes() == scene["ka"].tobytes() and np.array_equal(da, scene["da"])
+    fa = Frame.from_extractor(ex, 0, bounds)
+    fa.sync()
+    kb, db = ex(b)
+    fb = Frame.from_extractor(ex, 0, bounds)
+    assert fa.N == len(ka) and fb.N == len(kb)
+    ha, hb = Frame(ka, da, scene["scale"], bounds), Frame(kb, db, scene["scale"], bounds)
+    rng = SplitMix64(77)
+    for _ in range(40):
+        x, y = rng.next() % (W + 40) - 20.0, rng.next() % (H + 40) - 20.0
+        rad = 3.0 + rng.next() % 120
+        lo, hi = int(rng.next() % 9) - 1, int(rng.next() % 9) - 1
+        assert np.array_equal(fa.GetFeaturesInArea(x, y, rad, lo, hi), ha.GetFeaturesInArea(x, y, rad, lo, hi)), (x, y, rad, lo, hi)
+    prev = np.stack([ka["x"], ka["y"]], 1).astype(np.float32).copy()
+    p1, p2 = prev.copy(), prev.copy()
+    n1, m1 = ORBmatcher(0.9, True).SearchForInitialization(fa, fb, p1, 100)
+    n2, m2 = ORBmatcher(0.9, True).SearchForInitialization(ha, hb, p2, 100)
+    assert n2 > 100 and n1 == n2 and np.array_equal(m1, m2) and np.array_equal(p1, p2)
+    cand, sweeps = fb.last_stats()
+    assert cand > 0 and sweeps >= 1
+    for f in (fa, fb, ha, hb):
+        f.close()
+    ex.close()
+
+
+def test_frame_from_extractor_stereo_and_distortion(oracle, gpu_lib):
+    """Stereo frame: mvuRight handed over on the device (orb_extractor_stereo_result); distorted camera: key points
+    undistorted on the device.  Both against the host-array frame fed with the same numbers."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.stereo import StereoFrame
+    from ar_orbslam2_b200.synth import synth_stereo_pair
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher, UndistortKeyPoints, ComputeImageBounds
+    import ctypes as C
+    w, h = 1241, 376
+    l, r = synth_stereo_pair(w, h, 9)
+    mbf, mb = 386.1448, float(np.float32(386.1448) / np.float32(718.856))
+    ex = ORBextractor(2000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=2)
+    kl, dl, kr, dr, ur, dp = StereoFrame(ex, l, r, mbf, mb)
+    d_ur = C.c_void_p()
+    assert gpu_lib.orb_extractor_stereo_result(ex._h, C.byref(d_ur), None) == 0
+    cam = (718.856, 718.856, 607.1928, 185.2157)
+    dist = np.array([-0.28, 0.07, 0.0002, 0.00002], np.float32)
+    bounds = ComputeImageBounds(w, h, *cam, dist)
+    fdev = Frame.from_extractor(ex, 0, bounds, camera=cam, dist_coef=dist, u_right_device=d_ur.value)
+    kun = UndistortKeyPoints(kl, *cam, dist)
+    fhost = Frame(kun, dl, ex.GetScaleFactors(), bounds, u_right=ur)
+    n = len(kl)
+    rng = SplitMix64(3)
+    in_view = np.array([rng.next() % 10 != 0 for _ in range(n)], np.uint8)
+    px, py = (kun["x"] + 1.5).astype(np.float32), (kun["y"] - 1.0).astype(np.float32)
+    pxr = np.where(ur > 0, ur + 1.5, px - 30).astype(np.float32)
+    lvl = kl["octave"].astype(np.int32)
+    vc = np.full(n, 0.95, np.float32)
+    a = ORBmatcher(0.8).SearchByProjectionPoints(fdev, in_view, px, py, pxr, lvl, vc, dl, 3.0)
+    b = ORBmatcher(0.8).SearchByProjectionPoints(fhost, in_view, px, py, pxr, lvl, vc, dl, 3.0)
+    assert b[0] > 200 and a[0] == b[0] and np.array_equal(a[1], b[1])
+    fdev.close(); fhost.close(); ex.close()
+
+
+@pytest.mark.parametrize("select", [0, 1])
+def test_windowed_contention_stress(scene, oracle, gpu_lib, select):
+    """Three copies of every query (slightly moved, alternating `claims`) fight for the same features: long chains of
+    'an earlier query took it' dependencies.  The sweep-based resolution must leave the reference's sequential result."""
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    g, r = both(scene, oracle, "b")
+    k = scene["ka"]
+    n = len(k)
+    reps = 3
+    x = np.concatenate([(k["x"] + 7 + 0.5 * j).astype(np.float32) for j in range(reps)])
+    y = np.concatenate([(k["y"] + 4 - 0.5 * j).astype(np.float32) for j in range(reps)])
+    # interleave so that copies of one point are far apart in query order as well as adjacent ones
+    perm = np.argsort((np.arange(reps * n) * 7919) % (reps * n), kind="stable")
+    x, y = x[perm], y[perm]
+    oct_ = np.tile(k["octave"].astype(np.int32), reps)[perm]
+    desc = np.tile(scene["da"], (reps, 1))[perm]
+    ang = np.tile(k["angle"].astype(np.float32), reps)[perm]
+    rad = (6.0 * scene["scale"][oct_]).astype(np.float32)
+    claims = (np.arange(reps * n) % 3 != 1).astype(np.uint8)
+    claimed = (np.arange(g.N) % 17 == 0).astype(np.uint8)
+    kw = dict(select=select, th_dist=100, angle=ang, claims=claims, claimed=claimed, check_orientation=True, raw=True)
+    ng, ag = ORBmatcher(0.9).SearchWindowed(g, x, y, rad, oct_ - 1, oct_ + 1, desc, **kw)
+    nr, ar = ORBmatcher(0.9, backend=oracle.OracleBackend()).SearchWindowed(r, x, y, rad, oct_ - 1, oct_ + 1, desc, **kw)
+    assert nr > 500 and ng == nr and np.array_equal(ag, ar)
+    assert g.last_stats()[1] >= 3, "the scenario is meant to need several sweeps"
+
+
+def test_initialization_contention_stress(scene, oracle, gpu_lib):
+    """F1 holds every key point of A twice (identical descriptors): the second copy meets vMatchedDistance <= dist (ref
+    ORBmatcher.cc:444-445) on its best candidate and must fall back exactly as the sequential loop does."""
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+    bounds = (0.0, float(W), 0.0, float(H))
+    k2 = np.concatenate([scene["ka"], scene["ka"]])
+    k2["x"][len(scene["ka"]):] += 1.0
+    d2 = np.concatenate([scene["da"], scene["da"]])
+    d2[len(scene["da"]):, 0] ^= 1      # one bit off: the copy is slightly worse or better on its rivals
+    mk = lambda be: (Frame(k2, d2, scene["scale"], bounds, backend=be), Frame(scene["kb"], scene["db"], scene["scale"], bounds, backend=be))
+    g1, g2 = mk(None)
+    r1, r2 = mk(oracle.OracleBackend())
+    prev = np.stack([k2["x"], k2["y"]], 1).astype(np.float32).copy()
+    for ori in (True, False):
+        pg, pr = prev.copy(), prev.copy()
+        ng, mg = ORBmatcher(0.9, ori).SearchForInitialization(g1, g2, pg, 100)
+        nr, mr = ORBmatcher(0.9, ori, backend=oracle.OracleBackend()).SearchForInitialization(r1, r2, pr, 100)
+        assert nr > 100 and ng == nr and np.array_equal(mg, mr) and np.array_equal(pg, pr)
+
+
+def test_bow_contention_stress(scene, oracle, gpu_lib):
+    """Few, large vocabulary nodes: many KF features of a node want the same F feature (ref ORBmatcher.cc:209-210)."""
+    from ar_orbslam2_b200.tracking import ORBmatcher
+    gk, rk = both(scene, oracle, "a")
+    gf, rf = both(scene, oracle, "a")      # the same frame on both sides: every feature has a perfect rival-free match ...
+    ka = scene["ka"]
+    node = (ka["y"] // 160).astype(np.int64) * 5 + (ka["x"] // 160).astype(np.int64)
+    order = np.argsort(node, kind="stable")
+    kf_off, f_off, kf_idx, f_idx = [0], [0], [], []
+    for c in np.unique(node):
+        members = order[node[order] == c].tolist()
+        kf_idx += members + members[: len(members) // 2]    # ... and half of them are listed twice: the repeat must lose it
+        f_idx += members
+        kf_off.append(len(kf_idx)); f_off.append(len(f_idx))
+    kv = np.ones(gk.N, np.uint8)
+    args = (kf_off, kf_idx, f_off, f_idx, kv, None, False)
+    ng, mg = ORBmatcher(0.9, True).SearchByBoW(gk, gf, *args)
+    nr, mr = ORBmatcher(0.9, True, backend=oracle.OracleBackend()).SearchByBoW(rk, rf, *args)
+    assert nr > 1000 and ng == nr and np.array_equal(mg, mr)
