@@ -23,11 +23,15 @@
 #include "orb_common.cuh"
 #include "orb_internal.cuh"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <mutex>
 #include <vector>
+
+namespace cg = cooperative_groups;
 
 namespace orbgpu {
 
@@ -44,6 +48,7 @@ struct FrameDev {
     const uint8_t *desc;
     const int *cell_off;   // [GRID_COLS*GRID_ROWS + 1], cell = ix*GRID_ROWS + iy
     const int *cell_idx;   // keypoint indices, ascending inside a cell (= insertion order)
+    const int4 *rec;       // one record per grid entry, in cell_idx order: {x, y, uRight (float bits), index | octave << 24}
     float minX, minY, invW, invH;   // minX/minY as GetFeaturesInArea sees them (truncated to int for a KeyFrame view)
 };
 
@@ -92,21 +97,18 @@ struct WinTest {
     bool check, strict, stereo, gate;
     const float *inv_sigma2;
     double chi_mono, chi_stereo;
-    __device__ __forceinline__ bool ok(const FrameDev &f, int idx) const {
-        const int oct = f.octave[idx];
+    __device__ __forceinline__ bool ok(float kx, float ky, float ur, int oct) const {
         if (strict) { if (oct < minL || oct > maxL) return false; }
         else if (check) { if (oct < minL || (maxL >= 0 && oct > maxL)) return false; }
-        const float kx = f.x[idx], ky = f.y[idx];
         if (!(fabsf(__fsub_rn(kx, x)) < r && fabsf(__fsub_rn(ky, y)) < r)) return false;
         if (stereo) {
-            const float ur = f.uRight[idx];
             if (ur > 0 && fabsf(__fsub_rn(sref, ur)) > stol) return false;
         }
         if (gate) {   // ref :917-945: squared reprojection error, scaled by the level's inverse sigma^2, against chi^2 (double compare)
-            const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky), kr = f.uRight[idx];
+            const float ex = __fsub_rn(x, kx), ey = __fsub_rn(y, ky);
             float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
-            if (kr >= 0) {
-                const float er = __fsub_rn(gur, kr);
+            if (ur >= 0) {
+                const float er = __fsub_rn(gur, ur);
                 e2 = __fadd_rn(e2, __fmul_rn(er, er));
                 if ((double)__fmul_rn(e2, inv_sigma2[oct]) > chi_stereo) return false;
             } else if ((double)__fmul_rn(e2, inv_sigma2[oct]) > chi_mono) return false;
@@ -115,16 +117,27 @@ struct WinTest {
     }
 };
 
-// hdr[0] = candidate slots reserved so far (upper bounds), hdr[1] = overflow flag, hdr[2] = candidates written
-// One warp per query.  Lanes own grid cells in traversal order (ix outer, iy inner); pass 1 adds up the cells' populations
-// (an upper bound of the list) and reserves that range with one atomic, pass 2 tests the features and writes the admitted
-// ones -- a warp prefix sum per 32-cell round keeps the reference's order.  prune >= 0 drops candidates farther than
-// `prune` bits (a matcher that only ever takes the best candidate under a threshold never looks at them).
+// hdr[0] = candidate slots reserved so far (upper bounds), hdr[1] = overflow flag, hdr[2] = candidates written,
+// hdr[3] = queries with a non-empty list, hdr[8..10] = the resolve kernels' "something changed" flags (all zero on entry)
+//
+// A group of G threads (a warp, or a whole CTA for wide windows) per query.  The grid stores the cells of one grid COLUMN
+// back to back, so the window is <= 64 contiguous ranges of grid entries, one per column, and the reference's traversal
+// order (ix outer, iy inner, insertion order) is simply "ranges in column order".  The group scans the range lengths, reserves
+// their sum with one atomic, and then tests G entries per step -- one 16-byte record per entry, then the descriptor -- with a
+// ballot / prefix compaction that keeps the order.  prune >= 0 drops candidates farther than `prune` bits (a matcher that only
+// ever takes the best candidate under a threshold never looks at them).
+template <int G>
 __global__ void __launch_bounds__(256)
 k_window_lists(FrameDev f, WinQ Q, int *__restrict__ q_off, int *__restrict__ q_cnt, int2 *__restrict__ lists, int cap, int *hdr, int prune) {
-    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (q >= Q.n) return;
-    bool valid = !Q.valid || Q.valid[q];
+    constexpr int GPB = 256 / G, WPG = G / 32;
+    __shared__ int s_pref[GPB][GRID_COLS + 1], s_beg[GPB][GRID_COLS];
+    __shared__ int s_wcnt[GPB][WPG + 1];
+    __shared__ int s_off[GPB];
+    const int g = threadIdx.x / G, t = threadIdx.x % G, lane = threadIdx.x & 31, wg = t >> 5;
+    const int q = blockIdx.x * GPB + g;
+    auto gsync = [&]() { if (G == 32) __syncwarp(); else __syncthreads(); };
+    if (G == 32 && q >= Q.n) return;                 // (a CTA-wide group never diverges on q: blockIdx.x < Q.n)
+    bool valid = q < Q.n && (!Q.valid || Q.valid[q]);
     if (valid && Q.valid_if_zero) valid = Q.valid_if_zero[q] == 0;
     int cx0 = 0, cx1 = -1, cy0 = 0, cy1 = -1;
     WinTest T;
@@ -137,8 +150,8 @@ k_window_lists(FrameDev f, WinQ Q, int *__restrict__ q_off, int *__restrict__ q_
         cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
         if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0 || cx1 < cx0 || cy1 < cy0) valid = false;
     }
-    if (!valid) {
-        if (lane == 0) { q_off[q] = 0; q_cnt[q] = 0; }
+    if (!valid) {                                    // uniform over the group
+        if (t == 0 && q < Q.n) { q_off[q] = 0; q_cnt[q] = 0; }
         return;
     }
     T.minL = Q.min_level[q]; T.maxL = Q.max_level[q];
@@ -149,64 +162,75 @@ k_window_lists(FrameDev f, WinQ Q, int *__restrict__ q_off, int *__restrict__ q_
     T.gate = Q.gate_inv_sigma2 != nullptr;
     T.gur = T.gate && Q.gate_ur ? Q.gate_ur[q] : 0.f;
     T.inv_sigma2 = Q.gate_inv_sigma2; T.chi_mono = Q.gate_mono; T.chi_stereo = Q.gate_stereo;
-    const int ny = cy1 - cy0 + 1, ncells = (cx1 - cx0 + 1) * ny;
-    // pass 1: upper bound.  Cells of one grid column are consecutive in cell_off, so a column of the window is one range.
-    int ub = 0;
-    for (int c = lane; c <= cx1 - cx0; c += 32) {
-        const int cell = (cx0 + c) * GRID_ROWS + cy0;
-        ub += f.cell_off[cell + ny] - f.cell_off[cell];
+    const int ny = cy1 - cy0 + 1, ncol = cx1 - cx0 + 1;
+    // column ranges and their exclusive prefix sums: the group's first warp, two columns per lane
+    if (t < 32) {
+        const int c0 = 2 * t, c1 = c0 + 1;
+        int b0 = 0, l0 = 0, b1 = 0, l1 = 0;
+        if (c0 < ncol) { const int cell = (cx0 + c0) * GRID_ROWS + cy0; b0 = f.cell_off[cell]; l0 = f.cell_off[cell + ny] - b0; }
+        if (c1 < ncol) { const int cell = (cx0 + c1) * GRID_ROWS + cy0; b1 = f.cell_off[cell]; l1 = f.cell_off[cell + ny] - b1; }
+        int tot;
+        const int ex = warp_excl_scan(l0 + l1, t, &tot);
+        s_pref[g][c0] = ex; s_beg[g][c0] = b0;
+        s_pref[g][c1] = ex + l0; s_beg[g][c1] = b1;
+        if (t == 0) {
+            s_pref[g][GRID_COLS] = tot;
+            int off = 0;
+            if (tot) off = atomicAdd(&hdr[0], tot);
+            s_off[g] = off;
+        }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ub += __shfl_xor_sync(0xffffffffu, ub, o);
-    if (ub == 0) {
-        if (lane == 0) { q_off[q] = 0; q_cnt[q] = 0; }
+    gsync();
+    const int ub = s_pref[g][GRID_COLS], off = s_off[g];
+    if (ub == 0 || off + ub > cap) {
+        if (t == 0) { if (ub) hdr[1] = 1; q_off[q] = 0; q_cnt[q] = 0; }
         return;
     }
-    int off = 0;
-    if (lane == 0) off = atomicAdd(&hdr[0], ub);
-    off = __shfl_sync(0xffffffffu, off, 0);
-    if (off + ub > cap) {
-        if (lane == 0) { hdr[1] = 1; q_off[q] = 0; q_cnt[q] = 0; }
-        return;
+    uint4 qa = make_uint4(0, 0, 0, 0), qb = qa;
+    if (Q.desc) {
+        const uint4 *qd = reinterpret_cast<const uint4 *>(Q.desc + (size_t)q * 32);
+        qa = __ldg(qd); qb = __ldg(qd + 1);
     }
-    const uint8_t *qd = Q.desc ? Q.desc + (size_t)q * 32 : nullptr;
     int base = off;
-    for (int c0 = 0; c0 < ncells; c0 += 32) {
-        const int c = c0 + lane;
-        int beg = 0, end = 0;
-        if (c < ncells) {
-            const int cell = (cx0 + c / ny) * GRID_ROWS + cy0 + c % ny;
-            beg = f.cell_off[cell]; end = f.cell_off[cell + 1];
-        }
-        int cnt = 0;
-        unsigned pass = 0;   // cells hold few keypoints; entries beyond the 32nd of a cell are re-tested when written
-        for (int e = beg; e < end; e++) {
-            const int idx = f.cell_idx[e];
-            bool ok = T.ok(f, idx);
-            if (ok && prune >= 0 && qd) ok = hamming_rows(qd, f.desc + (size_t)idx * 32) <= prune;
-            if (ok) { if (e - beg < 32) pass |= 1u << (e - beg); cnt++; }
-        }
-        int total;
-        const int o = warp_excl_scan(cnt, lane, &total);
-        if (cnt) {
-            int w = base + o;
-            for (int e = beg; e < end; e++) {
-                const int idx = f.cell_idx[e];
-                bool ok;
-                int d = 0;
-                if (e - beg < 32) {
-                    ok = (pass >> (e - beg)) & 1;
-                    if (ok && qd) d = hamming_rows(qd, f.desc + (size_t)idx * 32);
-                } else {
-                    ok = T.ok(f, idx);
-                    if (ok && qd) { d = hamming_rows(qd, f.desc + (size_t)idx * 32); if (prune >= 0 && d > prune) ok = false; }
-                }
-                if (ok) lists[w++] = make_int2(idx, d);
+    for (int e0 = 0; e0 < ub; e0 += G) {
+        const int e = e0 + t;
+        bool ok = false;
+        int idx = 0, d = 0;
+        if (e < ub) {
+            int lo = 0, hi = ncol - 1;               // largest column c with pref[c] <= e
+#pragma unroll
+            for (int it = 0; it < 6; it++) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (s_pref[g][mid] <= e) lo = mid; else hi = mid - 1;
+            }
+            const int4 rc = __ldg(f.rec + s_beg[g][lo] + (e - s_pref[g][lo]));
+            idx = rc.w & 0xffffff;
+            ok = T.ok(__int_as_float(rc.x), __int_as_float(rc.y), __int_as_float(rc.z), (int)((unsigned)rc.w >> 24));
+            if (ok && Q.desc) {
+                const uint4 *fd = reinterpret_cast<const uint4 *>(f.desc + (size_t)idx * 32);
+                const uint4 fa = __ldg(fd), fb = __ldg(fd + 1);
+                d = __popc(qa.x ^ fa.x) + __popc(qa.y ^ fa.y) + __popc(qa.z ^ fa.z) + __popc(qa.w ^ fa.w) + __popc(qb.x ^ fb.x) +
+                    __popc(qb.y ^ fb.y) + __popc(qb.z ^ fb.z) + __popc(qb.w ^ fb.w);
+                if (prune >= 0 && d > prune) ok = false;
             }
         }
+        const unsigned bal = __ballot_sync(0xffffffffu, ok);
+        int wbase = 0, total = __popc(bal);
+        if (G > 32) {
+            if (lane == 0) s_wcnt[g][wg] = total;
+            __syncthreads();
+            total = 0;
+#pragma unroll
+            for (int w = 0; w < WPG; w++) { if (w == wg) wbase = total; total += s_wcnt[g][w]; }
+            __syncthreads();
+        }
+        if (ok) lists[base + wbase + __popc(bal & ((1u << lane) - 1u))] = make_int2(idx, d);
         base += total;
     }
-    if (lane == 0) { q_off[q] = off; q_cnt[q] = base - off; atomicAdd(&hdr[2], base - off); }
+    if (t == 0) {
+        q_off[q] = off; q_cnt[q] = base - off;
+        if (base > off) { atomicAdd(&hdr[2], base - off); atomicAdd(&hdr[3], 1); }
+    }
 }
 
 __device__ __forceinline__ int rot_bin(float a, float b) {   // ref ORBmatcher.cc:238-243, factor = 1/HISTO_LENGTH
@@ -241,68 +265,106 @@ __device__ __forceinline__ int block_sum(int v, int *s_acc) {   // every thread 
     return *s_acc;
 }
 
-// The query loop of ORBmatcher.cc:51-126 / 1354-1448 / 1491-1578 / 312-400 (see the file header for the sweep scheme).
-//   blocked_by[i]: smallest query index that holds feature i with a blocking map point; -1 = blocked on entry (`claimed`),
-//   FREE_Q = free.  Query q skips feature i iff blocked_by[i] < q -- exactly "an earlier query put a map point with
-//   Observations()>0 there" (ref :87-89, 1406-1408, 1544-1545).
-// out[0] = nmatches, out[1] = sweeps
-__global__ void __launch_bounds__(RES_THREADS)
+// ---- claim resolution (see the file header for the sweep scheme) ---------------------------------------------------------
+// Both kernels are COOPERATIVE launches: a sweep hands every query to a group of L lanes (L = 1..32, chosen from the
+// average list length so that long lists -- SearchForInitialization's 100-px windows -- are scanned by several lanes and short
+// ones by one), sweeps are separated by grid-wide barriers, and block 0 does the bookkeeping at the end.
+// "Who holds feature i" is a 64-bit word (sweep tag << 32 | ~query): picks of sweep s are posted with tag s + 1 by atomicMax,
+// so the newest tag wins, within it the smallest query, and nothing has to be cleared between sweeps.
+constexpr int RES_BLOCK = 1024;
+
+__device__ __forceinline__ int lanes_per_query(const int *hdr) {
+    const int nonempty = max(hdr[3], 1), avg = hdr[2] / nonempty;
+    int L = 1;
+    while (L < 32 && 4 * L < avg) L <<= 1;   // ~4 candidates per lane
+    return L;
+}
+// top-2 of (distance << 32 | rank) keys over the L lanes of a group (L a power of two, groups aligned inside a warp)
+__device__ __forceinline__ void group_top2(unsigned long long &k1, unsigned long long &k2, int L) {
+    for (int o = L >> 1; o > 0; o >>= 1) {
+        const unsigned long long a1 = __shfl_xor_sync(0xffffffffu, k1, o), a2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const unsigned long long n1 = min(k1, a1), n2 = min(max(k1, a1), min(k2, a2));
+        k1 = n1; k2 = n2;
+    }
+}
+constexpr unsigned long long NOKEY = ~0ull;
+__device__ __forceinline__ unsigned long long holder_key(int tag, int q) { return ((unsigned long long)tag << 32) | (0xffffffffu - (unsigned)q); }
+// query that holds the feature in sweep `tag`, or FREE_Q
+__device__ __forceinline__ int holder_of(unsigned long long key, int tag) {   // tags start at 1: sweep 0 sees nobody
+    return (tag != 0 && (int)(key >> 32) == tag) ? (int)(0xffffffffu - (unsigned)key) : FREE_Q;
+}
+
+// The query loop of ORBmatcher.cc:51-126 / 1354-1448 / 1491-1578 / 312-400.  Query q skips feature i iff it was blocked on
+// entry (`claimed`) or a query before q holds it with a blocking map point -- exactly "an earlier query put a map point with
+// Observations()>0 there" (ref :87-89, 1406-1408, 1544-1545).
+// out[0] = nmatches, out[1] = sweeps, out[2..4] = hdr[0..2]
+__global__ void __launch_bounds__(RES_BLOCK)
 k_resolve_windowed(FrameDev f, WinQ Q, const int *__restrict__ q_off, const int *__restrict__ q_cnt, const int2 *__restrict__ lists,
-                   const uint8_t *__restrict__ claimed, int *blocked_by, int *res, int *bins, int *holder, uint8_t *bad, int select,
-                   int th_dist, float nnratio, int check_ori, int *assigned, int *out, const int *hdr) {
+                   const uint8_t *__restrict__ claimed, unsigned long long *held, int *res, int *bins, int *holder, uint8_t *bad, int select,
+                   int th_dist, float nnratio, int check_ori, int *assigned, int *out, int *hdr) {
+    cg::grid_group grid = cg::this_grid();
+    const bool one_cta = gridDim.x == 1;   // small problems run as ONE CTA (plain launch): barriers are __syncthreads then
+    auto gsync = [&]() { if (one_cta) __syncthreads(); else grid.sync(); };
     __shared__ int hist[HISTO];
     __shared__ int ind[3];
-    __shared__ int s_changed, s_acc;
+    __shared__ int s_acc;
     const int tid = threadIdx.x, n = Q.n, nf = f.n;
-    for (int i = tid; i < nf; i += RES_THREADS) blocked_by[i] = (claimed && claimed[i]) ? -1 : FREE_Q;
-    for (int q = tid; q < n; q += RES_THREADS) res[q] = -1;
-    if (tid < HISTO) hist[tid] = 0;
-    __syncthreads();
-    int sweeps = 0;
+    const int gtid = blockIdx.x * RES_BLOCK + tid, nthreads = gridDim.x * RES_BLOCK;
+    for (int i = gtid; i < nf; i += nthreads) held[i] = 0;
+    for (int q = gtid; q < n; q += nthreads) res[q] = -1;
+    const int L = lanes_per_query(hdr), ngroups = nthreads / L, gid = gtid / L, gl = gtid % L;
+    int *changed = hdr + 8;
+    gsync();
+    int sweep = 0;
     for (;;) {
-        if (tid == 0) s_changed = 0;
-        __syncthreads();
-        bool changed = false;
-        for (int q = tid; q < n; q += RES_THREADS) {
-            const int cnt = q_cnt[q];
-            int pick = -1;
-            if (cnt) {
-                const int2 *L = lists + q_off[q];
-                int bestDist = 256, bestDist2 = 256, bestIdx = -1, idx2 = -1;
-                for (int j = 0; j < cnt; j++) {
-                    const int2 e = L[j];
-                    if (blocked_by[e.x] < q) continue;
-                    if (e.y < bestDist) { bestDist2 = bestDist; idx2 = bestIdx; bestDist = e.y; bestIdx = e.x; }
-                    else if (e.y < bestDist2) { bestDist2 = e.y; idx2 = e.x; }
-                }
-                if (bestIdx >= 0 && bestDist <= th_dist) {
-                    pick = bestIdx;
-                    if (select == ORB_SELECT_RATIO_LEVEL) {   // ref :118-121
-                        const int bestLevel = f.octave[bestIdx], bestLevel2 = idx2 >= 0 ? f.octave[idx2] : -1;
-                        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) pick = -1;
+        if (gtid == 0) changed[(sweep + 1) % 3] = 0;
+        for (int q0 = 0; q0 < n; q0 += ngroups) {          // uniform trip count: the shuffles below need whole warps
+            const int q = q0 + gid;
+            const int cnt = q < n ? q_cnt[q] : 0;
+            unsigned long long k1 = NOKEY, k2 = NOKEY;
+            const int2 *Lq = lists + (cnt ? q_off[q] : 0);
+            for (int j = gl; j < cnt; j += L) {
+                const int2 e = Lq[j];
+                if (claimed && claimed[e.x]) continue;
+                if (holder_of(held[e.x], sweep) < q) continue;
+                const unsigned long long key = ((unsigned long long)(unsigned)e.y << 32) | (unsigned)j;
+                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+            }
+            group_top2(k1, k2, L);
+            if (gl == 0 && q < n) {
+                int pick = -1;
+                if (k1 != NOKEY) {
+                    const int bestDist = (int)(k1 >> 32);
+                    if (bestDist <= th_dist && bestDist < 256) {
+                        pick = Lq[(unsigned)k1].x;
+                        if (select == ORB_SELECT_RATIO_LEVEL) {   // ref :118-121
+                            const int bestLevel = f.octave[pick], bestLevel2 = k2 != NOKEY ? f.octave[Lq[(unsigned)k2].x] : -1;
+                            const int bestDist2 = k2 != NOKEY ? (int)(k2 >> 32) : 256;
+                            if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) pick = -1;
+                        }
                     }
                 }
+                if (pick != res[q]) { res[q] = pick; changed[sweep % 3] = 1; }
             }
-            if (pick != res[q]) { res[q] = pick; changed = true; }
         }
-        if (changed) s_changed = 1;
-        sweeps++;
-        __syncthreads();
-        if (!s_changed) break;
-        for (int i = tid; i < nf; i += RES_THREADS) blocked_by[i] = (claimed && claimed[i]) ? -1 : FREE_Q;
-        __syncthreads();
-        for (int q = tid; q < n; q += RES_THREADS) {
+        gsync();
+        const bool again = changed[sweep % 3] != 0;
+        sweep++;
+        if (!again) break;
+        for (int q = gtid; q < n; q += nthreads) {
             const int p = res[q];
-            if (p >= 0 && (!Q.claims || Q.claims[q])) atomicMin(&blocked_by[p], q);
+            if (p >= 0 && (!Q.claims || Q.claims[q])) atomicMax(&held[p], holder_key(sweep, q));
         }
-        __syncthreads();
+        gsync();
     }
-    // ---- bookkeeping: who ends up in mvpMapPoints[i] (the last taker), rotation histogram over EVERY accepted query (an
-    // overwritten assignment still counts, F7), three maxima, reset of the takers outside them (ref :1451-1470)
-    for (int i = tid; i < nf; i += RES_THREADS) { holder[i] = -1; bad[i] = 0; }
+    if (blockIdx.x != 0) return;
+    // ---- bookkeeping (block 0): who ends up in mvpMapPoints[i] (the last taker), rotation histogram over EVERY accepted query
+    // (an overwritten assignment still counts, F7), three maxima, reset of the takers outside them (ref :1451-1470)
+    if (tid < HISTO) hist[tid] = 0;
+    for (int i = tid; i < nf; i += RES_BLOCK) { holder[i] = -1; bad[i] = 0; }
     __syncthreads();
     int acc = 0;
-    for (int q = tid; q < n; q += RES_THREADS) {
+    for (int q = tid; q < n; q += RES_BLOCK) {
         const int p = res[q];
         if (p < 0) continue;
         acc++;
@@ -318,7 +380,7 @@ k_resolve_windowed(FrameDev f, WinQ Q, const int *__restrict__ q_off, const int 
         if (tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
         __syncthreads();
         int dec = 0;
-        for (int q = tid; q < n; q += RES_THREADS) {
+        for (int q = tid; q < n; q += RES_BLOCK) {
             const int p = res[q];
             if (p < 0) continue;
             const int b = bins[q];
@@ -327,68 +389,81 @@ k_resolve_windowed(FrameDev f, WinQ Q, const int *__restrict__ q_off, const int 
         nm -= block_sum(dec, &s_acc);
     }
     __syncthreads();
-    for (int i = tid; i < nf; i += RES_THREADS) assigned[i] = bad[i] ? -2 : holder[i];
-    if (tid == 0) { out[0] = nm; out[1] = sweeps; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
+    for (int i = tid; i < nf; i += RES_BLOCK) assigned[i] = bad[i] ? -2 : holder[i];
+    if (tid == 0) { out[0] = nm; out[1] = sweep; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
 }
-
 
 // ORBmatcher::SearchForInitialization (ref :418-520).  Query i1 ignores a candidate i2 at distance d when an earlier query
 // holds i2 at a distance <= d (vMatchedDistance, ref :444-445); a later taker displaces the earlier one (:463-471).  After
 // every sweep the takers of a feature are chained (head / next, with a snapshot of their distances) so that the gate of
 // (q, i2) = min distance over the takers before q; a sweep only reads the chains and only writes its own res / res_dist.
-__global__ void __launch_bounds__(RES_THREADS)
+__global__ void __launch_bounds__(RES_BLOCK)
 k_resolve_init(FrameDev f1, FrameDev f2, const int *__restrict__ q_off, const int *__restrict__ q_cnt, const int2 *__restrict__ lists,
-               int *head, int *next, int *tdist, int *res, int *res_dist, int *last, float nnratio, int check_ori, int *m12,
-               const float *prev_in, float *prev_out, int *out, const int *hdr) {
+               unsigned long long *head, int *next, int *tdist, int *res, int *res_dist, int *last, float nnratio, int check_ori, int *m12,
+               const float *prev_in, float *prev_out, int *out, int *hdr) {
+    cg::grid_group grid = cg::this_grid();
+    const bool one_cta = gridDim.x == 1;   // small problems run as ONE CTA (plain launch): barriers are __syncthreads then
+    auto gsync = [&]() { if (one_cta) __syncthreads(); else grid.sync(); };
     __shared__ int hist[HISTO];
     __shared__ int ind[3];
-    __shared__ int s_changed, s_acc;
+    __shared__ int s_acc;
     const int tid = threadIdx.x, n1 = f1.n, n2 = f2.n;
-    for (int i = tid; i < n2; i += RES_THREADS) head[i] = -1;
-    for (int q = tid; q < n1; q += RES_THREADS) { res[q] = -1; res_dist[q] = 0; }
-    if (tid < HISTO) hist[tid] = 0;
-    __syncthreads();
-    int sweeps = 0;
+    const int gtid = blockIdx.x * RES_BLOCK + tid, nthreads = gridDim.x * RES_BLOCK;
+    for (int i = gtid; i < n2; i += nthreads) head[i] = 0;
+    for (int q = gtid; q < n1; q += nthreads) { res[q] = -1; res_dist[q] = 0; }
+    const int L = lanes_per_query(hdr), ngroups = nthreads / L, gid = gtid / L, gl = gtid % L;
+    int *changed = hdr + 8;
+    gsync();
+    int sweep = 0;
     for (;;) {
-        if (tid == 0) s_changed = 0;
-        __syncthreads();
-        bool changed = false;
-        for (int q = tid; q < n1; q += RES_THREADS) {
-            const int cnt = q_cnt[q];
-            int pick = -1, pick_d = 0;
-            if (cnt) {
-                const int2 *L = lists + q_off[q];
-                int bestDist = 0x7fffffff, bestDist2 = 0x7fffffff, bestIdx = -1;
-                for (int j = 0; j < cnt; j++) {
-                    const int2 e = L[j];
-                    int gate = 0x7fffffff;
-                    for (int t = head[e.x]; t >= 0; t = next[t])
-                        if (t < q) gate = min(gate, tdist[t]);
-                    if (gate <= e.y) continue;                          // ref :444-445
-                    if (e.y < bestDist) { bestDist2 = bestDist; bestDist = e.y; bestIdx = e.x; }
-                    else if (e.y < bestDist2) bestDist2 = e.y;
-                }
-                if (bestIdx >= 0 && bestDist <= TH_LOW_M && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) { pick = bestIdx; pick_d = bestDist; }
+        if (gtid == 0) changed[(sweep + 1) % 3] = 0;
+        for (int q0 = 0; q0 < n1; q0 += ngroups) {
+            const int q = q0 + gid;
+            const int cnt = q < n1 ? q_cnt[q] : 0;
+            unsigned long long k1 = NOKEY, k2 = NOKEY;
+            const int2 *Lq = lists + (cnt ? q_off[q] : 0);
+            for (int j = gl; j < cnt; j += L) {
+                const int2 e = Lq[j];
+                int gate = 0x7fffffff;
+                for (int t = holder_of(head[e.x], sweep); t != FREE_Q && t >= 0; t = next[t])
+                    if (t < q) gate = min(gate, tdist[t]);
+                if (gate <= e.y) continue;                          // ref :444-445
+                const unsigned long long key = ((unsigned long long)(unsigned)e.y << 32) | (unsigned)j;
+                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
             }
-            if (pick != res[q] || pick_d != res_dist[q]) { res[q] = pick; res_dist[q] = pick_d; changed = true; }
+            group_top2(k1, k2, L);
+            if (gl == 0 && q < n1) {
+                int pick = -1, pick_d = 0;
+                if (k1 != NOKEY) {
+                    const int bestDist = (int)(k1 >> 32);
+                    const float second = k2 != NOKEY ? (float)(int)(k2 >> 32) : (float)0x7fffffff;
+                    if (bestDist <= TH_LOW_M && (float)bestDist < __fmul_rn(second, nnratio)) { pick = Lq[(unsigned)k1].x; pick_d = bestDist; }
+                }
+                if (pick != res[q] || pick_d != res_dist[q]) { res[q] = pick; res_dist[q] = pick_d; changed[sweep % 3] = 1; }
+            }
         }
-        if (changed) s_changed = 1;
-        sweeps++;
-        __syncthreads();
-        if (!s_changed) break;
-        for (int i = tid; i < n2; i += RES_THREADS) head[i] = -1;
-        __syncthreads();
-        for (int q = tid; q < n1; q += RES_THREADS) {
+        gsync();
+        const bool again = changed[sweep % 3] != 0;
+        sweep++;
+        if (!again) break;
+        for (int q = gtid; q < n1; q += nthreads) {
             const int p = res[q];
-            if (p >= 0) { tdist[q] = res_dist[q]; next[q] = atomicExch(&head[p], q); }
+            if (p >= 0) {
+                tdist[q] = res_dist[q];
+                const unsigned long long old = atomicExch(&head[p], holder_key(sweep, q));
+                const int t = holder_of(old, sweep);
+                next[q] = t == FREE_Q ? -1 : t;
+            }
         }
-        __syncthreads();
+        gsync();
     }
+    if (blockIdx.x != 0) return;
     // ---- vnMatches21 = the last taker; an earlier taker of the same feature was displaced (m12 = -1) but stays in the
     // rotation histogram (ref :463-486); filter (:492-515); vbPrevMatched update (:518-520)
-    for (int i = tid; i < n2; i += RES_THREADS) last[i] = -1;
+    if (tid < HISTO) hist[tid] = 0;
+    for (int i = tid; i < n2; i += RES_BLOCK) last[i] = -1;
     __syncthreads();
-    for (int q = tid; q < n1; q += RES_THREADS) {
+    for (int q = tid; q < n1; q += RES_BLOCK) {
         const int p = res[q];
         if (p < 0) continue;
         atomicMax(&last[p], q);
@@ -398,7 +473,7 @@ k_resolve_init(FrameDev f1, FrameDev f2, const int *__restrict__ q_off, const in
     if (check_ori && tid == 0) three_maxima(hist, ind[0], ind[1], ind[2]);
     __syncthreads();
     int acc = 0;
-    for (int q = tid; q < n1; q += RES_THREADS) {
+    for (int q = tid; q < n1; q += RES_BLOCK) {
         const int p = res[q];
         int m = (p >= 0 && last[p] == q) ? p : -1;
         if (m >= 0 && check_ori) {
@@ -411,7 +486,7 @@ k_resolve_init(FrameDev f1, FrameDev f2, const int *__restrict__ q_off, const in
         prev_out[2 * q] = px; prev_out[2 * q + 1] = py;
     }
     const int nm = block_sum(acc, &s_acc);
-    if (tid == 0) { out[0] = nm; out[1] = sweeps; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
+    if (tid == 0) { out[0] = nm; out[1] = sweep; out[2] = hdr[0]; out[3] = hdr[1]; out[4] = hdr[2]; }
 }
 
 // SearchByBoW: distances of every (KF entry, F entry of the same vocabulary node) pair, one warp per KF entry
@@ -621,6 +696,7 @@ __global__ void __launch_bounds__(1024) k_rot_hist_filter(const float *a, const 
 // cell ascend (= the reference's insertion order): slots are handed out by atomics, then every cell's short list is sorted.
 struct FrameBuild {
     float *x, *y, *angle, *uRight;
+    int4 *rec;
     int *octave, *cell_off, *cell_idx, *cell_of;
     float minX, minY, invW, invH;
 };
@@ -673,6 +749,10 @@ k_frame_build(const orb_keypoint *__restrict__ kp, int n, const float *__restric
             int j = i - 1;
             while (j >= beg && B.cell_idx[j] > v) { B.cell_idx[j + 1] = B.cell_idx[j]; j--; }
             B.cell_idx[j + 1] = v;
+        }
+        for (int i = beg; i < end; i++) {
+            const int v = B.cell_idx[i];
+            B.rec[i] = make_int4(__float_as_int(B.x[v]), __float_as_int(B.y[v]), __float_as_int(B.uRight[v]), v | (B.octave[v] << 24));
         }
     }
 }
@@ -817,6 +897,7 @@ namespace {
 // carve the static block for n key points; returns the bytes needed (base may be null for sizing)
 struct StaticLayout {
     float *x, *y, *angle, *uRight;
+    int4 *rec;
     int *octave, *cell_off, *cell_idx, *cell_of;
     uint8_t *desc;
     size_t bytes;
@@ -830,6 +911,7 @@ StaticLayout static_layout(uint8_t *base, int n) {
     L.octave = ar.take<int>(m);
     L.desc = ar.take<uint8_t>(m * 32);
     L.cell_off = ar.take<int>(NCELL + 1); L.cell_idx = ar.take<int>(m); L.cell_of = ar.take<int>(m);
+    L.rec = ar.take<int4>(m);
     L.bytes = ar.used;
     return L;
 }
@@ -860,7 +942,7 @@ void frame_set_dev(orb_frame *f, const StaticLayout &L, bool keyframe_view) {
     // ref Frame.cc:217-218; a KeyFrame sees the bounds as `int` copies (KeyFrame.h:190-193) while the grid keeps the Frame's scales
     const float invW = static_cast<float>(GRID_COLS) / static_cast<float>(f->maxX - f->minX);
     const float invH = static_cast<float>(GRID_ROWS) / static_cast<float>(f->maxY - f->minY);
-    f->dev = FrameDev{f->n, L.x, L.y, L.angle, L.uRight, L.octave, L.desc, L.cell_off, L.cell_idx,
+    f->dev = FrameDev{f->n, L.x, L.y, L.angle, L.uRight, L.octave, L.desc, L.cell_off, L.cell_idx, L.rec,
                       keyframe_view ? (float)(int)f->minX : f->minX, keyframe_view ? (float)(int)f->minY : f->minY, invW, invH};
 }
 
@@ -887,6 +969,8 @@ int orb_frame_create(const orb_frame_desc *d, orb_frame **out) {
     ORB_REQUIRE(d && out && d->n >= 0 && (d->n == 0 || (d->keys_un && d->descriptors)) && d->scale_factors && d->nlevels >= 1,
                 ORB_ERR_INVALID, "bad frame description");
     ORB_REQUIRE(d->max_x > d->min_x && d->max_y > d->min_y, ORB_ERR_INVALID, "empty image bounds");
+    ORB_REQUIRE(d->n < (1 << 24), ORB_ERR_INVALID, "more than 16M key points in one frame");
+    for (int i = 0; i < d->n; i++) ORB_REQUIRE(d->keys_un[i].octave >= 0 && d->keys_un[i].octave < 128, ORB_ERR_INVALID, "key point octave out of range");
     orb_frame *f = nullptr;
     ORB_TRY(frame_begin(d->n, d->nlevels, d->scale_factors, d->min_x, d->max_x, d->min_y, d->max_y, &f));
     FrameRes *R = f->res;
@@ -914,6 +998,13 @@ int orb_frame_create(const orb_frame_desc *d, orb_frame **out) {
     {
         std::vector<int> cur(off, off + NCELL);
         for (int i = 0; i < n; i++) if (cell[i] >= 0) H.cell_idx[cur[cell[i]]++] = i;
+    }
+    for (int e = 0; e < off[NCELL]; e++) {   // one 16-byte record per grid entry: what the window test reads
+        const int i = H.cell_idx[e];
+        int4 r;
+        memcpy(&r.x, &H.x[i], 4); memcpy(&r.y, &H.y[i], 4); memcpy(&r.z, &H.uRight[i], 4);
+        r.w = i | (H.octave[i] << 24);
+        H.rec[e] = r;
     }
     if (n) memcpy(H.desc, d->descriptors, (size_t)n * 32);
     cudaError_t e = cudaMemcpyAsync(R->d_static, R->h_up, bytes, cudaMemcpyHostToDevice, f->stream);
@@ -977,7 +1068,7 @@ int orb_frame_from_extractor(orb_extractor *ex, int slot, const orb_frame_source
     }
     FrameBuild B;
     B.x = L.x; B.y = L.y; B.angle = L.angle; B.uRight = L.uRight; B.octave = L.octave;
-    B.cell_off = L.cell_off; B.cell_idx = L.cell_idx; B.cell_of = L.cell_of;
+    B.cell_off = L.cell_off; B.cell_idx = L.cell_idx; B.cell_of = L.cell_of; B.rec = L.rec;
     B.minX = f->minX; B.minY = f->minY;
     B.invW = static_cast<float>(GRID_COLS) / static_cast<float>(f->maxX - f->minX);
     B.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(f->maxY - f->minY);
@@ -1065,10 +1156,29 @@ WinQ pack_queries(Upload &up, const HostQueries &H) {
 
 size_t list_capacity(const orb_frame *f, int n) { return std::max<size_t>(f->list_hint, (size_t)32 * n + 4096); }
 
-void launch_lists(orb_frame *f, const WinQ &Q, int *q_off, int *q_cnt, int2 *lists, size_t cap, int *hdr, int prune) {
+// wide = the windows hold hundreds of grid entries (SearchForInitialization's 100-px windows): a whole CTA per query
+void launch_lists(orb_frame *f, const WinQ &Q, int *q_off, int *q_cnt, int2 *lists, size_t cap, int *hdr, int prune, bool wide = false) {
     if (Q.n == 0) return;
-    k_window_lists<<<(Q.n * 32 + 255) / 256, 256, 0, f->stream>>>(f->dev, Q, q_off, q_cnt, lists, (int)std::min<size_t>(cap, 0x7fffffff), hdr, prune);
+    const int icap = (int)std::min<size_t>(cap, 0x7fffffff);
+    if (wide) k_window_lists<256><<<Q.n, 256, 0, f->stream>>>(f->dev, Q, q_off, q_cnt, lists, icap, hdr, prune);
+    else k_window_lists<32><<<(Q.n + 7) / 8, 256, 0, f->stream>>>(f->dev, Q, q_off, q_cnt, lists, icap, hdr, prune);
     f->launches++;
+}
+
+// CTAs of a resolve kernel: ~2 queries per thread with short lists (one CTA up to ~2000 queries: block barriers instead of
+// grid barriers), 16 lanes per query with the long lists of wide windows
+int resolve_grid(const orb_frame *f, int nqueries, bool wide) {
+    static int sms[64] = {};
+    int &n = sms[f->device & 63];
+    if (!n) { if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, f->device) != cudaSuccess || n <= 0) n = 1; }
+    const long long lanes = (long long)nqueries * (wide ? 16 : 1);
+    return (int)std::max<long long>(1, std::min<long long>(n, (lanes + 2 * RES_BLOCK - 1) / (2 * RES_BLOCK)));
+}
+int launch_resolve(const void *kernel, int grid, void **args, cudaStream_t st) {
+    // one CTA: an ordinary launch (the kernel then never touches the grid barrier); more: cooperative, all CTAs co-resident
+    if (grid == 1) ORB_CUDA_TRY(cudaLaunchKernel(kernel, dim3(1), dim3(RES_BLOCK), args, 0, st));
+    else ORB_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(RES_BLOCK), args, 0, st));
+    return ORB_OK;
 }
 
 // The windowed matcher: upload, lists, resolve, download.  Retries once with a larger candidate pool when the pool overflowed.
@@ -1085,7 +1195,7 @@ int search_windowed_host(orb_frame *f, const HostQueries &H, const uint8_t *clai
     for (int attempt = 0; attempt < 3; attempt++) {
         const size_t cap = list_capacity(f, n);
         const size_t up_need = queries_upload_bytes(H) + up256(nf);
-        const size_t scratch = 4 * up256((size_t)n * 4) + 2 * up256((size_t)nf * 4) + up256(nf);
+        const size_t scratch = 4 * up256((size_t)n * 4) + 3 * up256((size_t)nf * 4) + up256(nf);
         const size_t dn_need = up256((size_t)nf * 4) + ALIGN;
         ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
         ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
@@ -1099,20 +1209,29 @@ int search_windowed_host(orb_frame *f, const HostQueries &H, const uint8_t *clai
         Arena ar;
         ar.base = R->d_work; ar.used = up.used;
         int *q_off = ar.take<int>(n), *q_cnt = ar.take<int>(n), *res = ar.take<int>(n), *bins = ar.take<int>(n);
-        int *blocked_by = ar.take<int>(nf), *holder = ar.take<int>(nf);
+        unsigned long long *held = ar.take<unsigned long long>(nf);
+        int *holder = ar.take<int>(nf);
         uint8_t *bad = ar.take<uint8_t>(nf);
-        int *d_assigned = ar.take<int>(nf), *d_out = ar.take<int>(8);   // contiguous: one copy down
+        // results are written by the kernel straight into the pinned block (mapped into the device's address space): no copy down
+        int *d_assigned = reinterpret_cast<int *>(R->h_dn), *d_out = reinterpret_cast<int *>(R->h_dn + up256((size_t)nf * 4));
         int2 *lists = ar.take<int2>(0);
         ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
         launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, select == ORB_SELECT_BEST ? th_dist : -1);
-        k_resolve_windowed<<<1, RES_THREADS, 0, st>>>(f->dev, Q, q_off, q_cnt, lists, d_claimed, blocked_by, res, bins, holder, bad, select,
-                                                      th_dist, nnratio, check_ori, d_assigned, d_out, hdr);
+        {
+            FrameDev fd = f->dev;
+            WinQ Qa = Q;
+            const int *a_off = q_off, *a_cnt = q_cnt;
+            const int2 *a_lists = lists;
+            float ratio = nnratio;
+            int sel = select, th = th_dist, ori = check_ori;
+            void *args[] = {&fd, &Qa, &a_off, &a_cnt, &a_lists, &d_claimed, &held, &res, &bins, &holder, &bad, &sel, &th, &ratio, &ori, &d_assigned,
+                            &d_out, &hdr};
+            ORB_TRY(launch_resolve((const void *)k_resolve_windowed, resolve_grid(f, n, false), args, st));
+        }
         f->launches++;
         ORB_CUDA_TRY(cudaGetLastError());
-        const size_t dn_bytes = up256((size_t)nf * 4) + 8 * sizeof(int);
-        ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, d_assigned, dn_bytes, cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaStreamSynchronize(st));
-        const int *h_out = reinterpret_cast<const int *>(R->h_dn + up256((size_t)nf * 4));
+        const int *h_out = d_out;
         if (h_out[3]) {   // candidate pool too small: h_out[2] slots were asked for
             f->list_hint = (size_t)h_out[2] * 5 / 4 + 4096;
             continue;
@@ -1248,7 +1367,7 @@ int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matc
     for (int attempt = 0; attempt < 3; attempt++) {
         const size_t cap = list_capacity(f, n1);
         const size_t up_need = 2 * ALIGN + up256((size_t)n1 * 8);
-        const size_t scratch = 6 * up256((size_t)n1 * 4) + 2 * up256((size_t)n2 * 4);
+        const size_t scratch = 6 * up256((size_t)n1 * 4) + 3 * up256((size_t)n2 * 4);
         const size_t dn_need = up256((size_t)n1 * 4) + up256((size_t)n1 * 8) + ALIGN;
         ORB_TRY(grow_host(&R->h_up, &R->up_bytes, up_need));
         ORB_TRY(grow_host(&R->h_dn, &R->dn_bytes, dn_need));
@@ -1270,21 +1389,32 @@ int orb_search_for_initialization(orb_frame *f1, orb_frame *f2, float *prev_matc
         Arena ar;
         ar.base = R->d_work; ar.used = up.used;
         int *q_off = ar.take<int>(n1), *q_cnt = ar.take<int>(n1), *next = ar.take<int>(n1), *tdist = ar.take<int>(n1);
-        int *res = ar.take<int>(n1), *res_dist = ar.take<int>(n1), *head = ar.take<int>(n2), *last = ar.take<int>(n2);
-        int *m12 = ar.take<int>(n1);                      // contiguous: [m12 | prev | out] go down in one copy
-        float *d_prev_out = ar.take<float>((size_t)n1 * 2);
-        int *d_out = ar.take<int>(8);
+        int *res = ar.take<int>(n1), *res_dist = ar.take<int>(n1), *last = ar.take<int>(n2);
+        unsigned long long *head = ar.take<unsigned long long>(n2);
+        // [m12 | prev | out]: written by the kernel straight into the pinned block (mapped into the device's address space)
+        const size_t o_prev = up256((size_t)n1 * 4), o_out = o_prev + up256((size_t)n1 * 8);
+        int *m12 = reinterpret_cast<int *>(R->h_dn);
+        float *d_prev_out = reinterpret_cast<float *>(R->h_dn + o_prev);
+        int *d_out = reinterpret_cast<int *>(R->h_dn + o_out);
         int2 *lists = ar.take<int2>(0);
         ORB_CUDA_TRY(cudaMemcpyAsync(R->d_work, R->h_up, up.used, cudaMemcpyHostToDevice, st));
-        launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, -1);
-        k_resolve_init<<<1, RES_THREADS, 0, st>>>(f1->dev, f2->dev, q_off, q_cnt, lists, head, next, tdist, res, res_dist, last, nnratio,
-                                                  check_orientation, m12, d_prev, d_prev_out, d_out, hdr);
+        // a window of r px holds about n2 * (2r)^2 / (image area) grid entries
+        const double pop = (double)n2 * 4.0 * window_size * window_size / ((double)(f2->maxX - f2->minX) * (f2->maxY - f2->minY));
+        launch_lists(f, Q, q_off, q_cnt, lists, cap, hdr, -1, pop > 96.0);
+        {
+            FrameDev d1 = f1->dev, d2 = f2->dev;
+            const int *a_off = q_off, *a_cnt = q_cnt;
+            const int2 *a_lists = lists;
+            float ratio = nnratio;
+            int ori = check_orientation;
+            void *args[] = {&d1, &d2, &a_off, &a_cnt, &a_lists, &head, &next, &tdist, &res, &res_dist, &last, &ratio, &ori, &m12, &d_prev,
+                            &d_prev_out, &d_out, &hdr};
+            ORB_TRY(launch_resolve((const void *)k_resolve_init, resolve_grid(f, n1, pop > 96.0), args, st));
+        }
         f->launches++;
         ORB_CUDA_TRY(cudaGetLastError());
-        const size_t o_prev = up256((size_t)n1 * 4), o_out = o_prev + up256((size_t)n1 * 8);
-        ORB_CUDA_TRY(cudaMemcpyAsync(R->h_dn, m12, o_out + 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaStreamSynchronize(st));
-        const int *h_out = reinterpret_cast<const int *>(R->h_dn + o_out);
+        const int *h_out = d_out;
         if (h_out[3]) {
             f->list_hint = (size_t)h_out[2] * 5 / 4 + 4096;
             continue;

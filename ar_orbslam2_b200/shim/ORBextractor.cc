@@ -19,8 +19,9 @@ static void Check(int rc, const char *what) {
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
       mpHandle(nullptr), mpStereoHandle(nullptr), mStereoMaxWidth(0), mStereoMaxHeight(0), mMaxWidth(0), mMaxHeight(0),
-      mbMirrorPyramid(true) {
+      mbMirrorPyramid(false) {
     mvImagePyramid.resize(nlevels);
+    mvImagePyramid.mpOwner = this;
     EnsureHandle(1920, 1080);
 }
 
@@ -74,19 +75,27 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     _keypoints.resize(n);                             // ref :1012-1043
     if (n) std::memcpy((void *)_keypoints.data(), mKpBuf.data(), (size_t)n * sizeof(orb_keypoint));
 
-    if (mbMirrorPyramid) {
-        for (int l = 0; l < nlevels; l++) {
-            int w = 0, h = 0, pitch = 0;
-            Check(orb_pyramid_level(mpHandle, 0, l, nullptr, &w, &h, &pitch), "orb_pyramid_level");
-            // the reference's level is the interior ROI of a (w+38)x(h+38) plane (ref :1052-1056): keep that layout
-            // so code that walks into the 19-px border (Frame.cc:583) finds the same bytes
-            cv::Mat plane(h + 2 * ORB_EDGE_THRESHOLD, w + 2 * ORB_EDGE_THRESHOLD, CV_8UC1);
-            Check(orb_pyramid_download(mpHandle, 0, l, 1, plane.data, (int)plane.step), "orb_pyramid_download");
-            mPlanes.resize(nlevels);
-            mPlanes[l] = plane;
-            mvImagePyramid[l] = cv::Mat(h, w, CV_8UC1, plane.data + (size_t)ORB_EDGE_THRESHOLD * plane.step + ORB_EDGE_THRESHOLD,
-                                        plane.step);
-        }
+    mvImagePyramid.mbStale = true;                    // the host mirror is refreshed when somebody reads it
+    if (mbMirrorPyramid) DownloadPyramid();
+}
+
+void PyramidMirror::Fill() const {
+    if (mbStale && mpOwner) mpOwner->DownloadPyramid();
+}
+
+void ORBextractor::DownloadPyramid() {
+    mvImagePyramid.mbStale = false;
+    mPlanes.resize(nlevels);
+    for (int l = 0; l < nlevels; l++) {
+        int w = 0, h = 0, pitch = 0;
+        Check(orb_pyramid_level(mpHandle, 0, l, nullptr, &w, &h, &pitch), "orb_pyramid_level");
+        // the reference's level is the interior ROI of a (w+38)x(h+38) plane (ref :1052-1056): keep that layout
+        // so code that walks into the 19-px border (Frame.cc:583) finds the same bytes
+        cv::Mat plane(h + 2 * ORB_EDGE_THRESHOLD, w + 2 * ORB_EDGE_THRESHOLD, CV_8UC1);
+        Check(orb_pyramid_download(mpHandle, 0, l, 1, plane.data, (int)plane.step), "orb_pyramid_download");
+        mPlanes[l] = plane;
+        mvImagePyramid.mvLevels[l] = cv::Mat(h, w, CV_8UC1, plane.data + (size_t)ORB_EDGE_THRESHOLD * plane.step + ORB_EDGE_THRESHOLD,
+                                             plane.step);
     }
 }
 

@@ -5,9 +5,11 @@
 // Differences a maintainer should know about:
 //   * the extractor owns CUDA buffers sized for max_width x max_height (defaults fit 1920x1080; larger frames
 //     re-create the handle transparently);
-//   * mvImagePyramid is a host mirror of the device pyramid.  It is refreshed after every call unless
-//     SetMirrorPyramid(false): Frame::ComputeStereoMatches (the only reader, ref Frame.cc:476,566,578,583)
-//     goes through ORBGPU_ComputeStereoMatches, which reads the device pyramid in place;
+//   * mvImagePyramid is a LAZY host mirror of the device pyramid: nothing is copied until somebody indexes it; the first
+//     read after an extraction downloads the eight levels (with the reference's 19-px border around each, ref :1052-1056).
+//     Frame::ComputeStereoMatches, the reference's only reader (Frame.cc:476,566,578,583), is replaced by Frame_stereo.cc,
+//     which reads the device pyramid in place, so a drop-in build never pays for the mirror; the reference's own
+//     ComputeStereoMatches keeps working against it.  SetMirrorPyramid(true) restores the eager copy after every call;
 //   * without a CUDA device the constructor throws std::runtime_error -- there is no CPU fallback.
 #ifndef ORBEXTRACTOR_H
 #define ORBEXTRACTOR_H
@@ -20,6 +22,30 @@
 struct orb_extractor;
 
 namespace ORB_SLAM2 {
+
+class ORBextractor;
+
+// What readers of the reference's `std::vector<cv::Mat> mvImagePyramid` use of it -- indexing, size(), iteration, conversion
+// to the vector -- with the download from the device deferred to the first such access after an extraction.
+class PyramidMirror {
+public:
+    PyramidMirror() : mpOwner(nullptr), mbStale(false) {}
+    const cv::Mat &operator[](size_t level) const { Fill(); return mvLevels[level]; }
+    cv::Mat &operator[](size_t level) { Fill(); return mvLevels[level]; }
+    size_t size() const { return mvLevels.size(); }
+    bool empty() const { return mvLevels.empty(); }
+    void resize(size_t n) { mvLevels.resize(n); }
+    std::vector<cv::Mat>::const_iterator begin() const { Fill(); return mvLevels.begin(); }
+    std::vector<cv::Mat>::const_iterator end() const { Fill(); return mvLevels.end(); }
+    operator const std::vector<cv::Mat> &() const { Fill(); return mvLevels; }
+
+private:
+    friend class ORBextractor;
+    void Fill() const;
+    ORBextractor *mpOwner;
+    mutable std::vector<cv::Mat> mvLevels;
+    mutable bool mbStale;   // the device pyramid is newer than mvLevels
+};
 
 class ORBextractor {
 public:
@@ -41,15 +67,17 @@ public:
     std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
     std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
-    std::vector<cv::Mat> mvImagePyramid;
+    PyramidMirror mvImagePyramid;   // ref :88 `std::vector<cv::Mat> mvImagePyramid`
 
     // --- additions (not in the reference)
-    void SetMirrorPyramid(bool on) { mbMirrorPyramid = on; }
+    void SetMirrorPyramid(bool on) { mbMirrorPyramid = on; }   // true: copy the pyramid to the host after EVERY call (default: lazily)
+    void DownloadPyramid();                                     // fills mvImagePyramid's levels from the device now
     orb_extractor *Handle() { return mpHandle; }   // for ORBGPU_ComputeStereoMatches
     int DefaultCapacity() const { return nfeatures + 4 * nlevels + 256; }   // output slots handed to the library (grown on demand)
     orb_extractor *StereoHandle(int width, int height);   // two-frame handle of ORBGPU_ExtractStereo, created on first use
 
 protected:
+    friend class PyramidMirror;
     void EnsureHandle(int width, int height);
 
     int nfeatures;

@@ -1,7 +1,16 @@
 // See ORBmatcher_gpu.h.  Line references are to ORB_SLAM2/src/ORBmatcher.cc of the reference.
+//
+// PROVENANCE.  This file is meant to be compiled INSIDE the ORB-SLAM2 tree as the body of ORB_SLAM2::ORBmatcher (see
+// ORBmatcher.cc next to it).  The candidate loops -- the hot path -- are liborbgpu calls.  What remains on the host is the
+// reference's per-point set-up in front of each loop (projection of a map point with the frame pose, frustum / distance /
+// PredictScale gates) and the map bookkeeping behind it (AddObservation / Replace / AddMapPoint).  Those statements operate on
+// the reference's own cv::Mat members and must produce the same floats as ORBmatcher.cc to keep the match lists bit-identical,
+// so they follow ORB_SLAM2/src/ORBmatcher.cc (Raul Mur-Artal et al., GPLv3) statement for statement; each block cites the
+// lines it restates.  They are derived work of that file and carry its licence (GPLv3) when distributed with it.
 #include "ORBmatcher_gpu.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <set>
 #include <stdexcept>
@@ -16,19 +25,74 @@ static void Check(int rc, const char *what) {
     if (rc != ORB_OK) throw std::runtime_error(std::string("liborbgpu: ") + what + ": " + orb_last_error());
 }
 
-// The part of a Frame the matchers read, uploaded as an orb_frame (mvKeysUn, mDescriptors, mvuRight, the image bounds that
-// define the 64x48 grid, mvScaleFactors).  Built per call; a production integration caches it in the Frame right after
-// AssignFeaturesToGrid() (ref Frame.cc:232).
+// The part of a Frame / KeyFrame the matchers read (mvKeysUn, mDescriptors, mvuRight, the image bounds that define the 64x48
+// grid, mvScaleFactors) as an orb_frame on the device.  Built the first time a matcher sees the object and kept in a small
+// per-thread LRU cache afterwards: Tracking calls two or three matchers on mCurrentFrame per camera frame, LocalMapping and
+// LoopClosing revisit the same key frames many times.  The cache key is the identity of the object's buffers (the vectors'
+// and the descriptor matrix's data pointers -- a Frame copy gets new vectors, a KeyFrame keeps its own for life) plus the
+// view flags; a hit is confirmed by a fingerprint of the contents, so an address reused by a later frame (Tracking::Reset
+// restarts the ids, frames come and go) cannot alias.  Key points, descriptors and mvuRight never change after the Frame /
+// KeyFrame constructor in the reference (Frame.cc:62-233, KeyFrame.cc:31-63).  ORBGPU_SHIM_NO_CACHE=1 builds per call.
+namespace {
+
+struct CacheEntry {
+    const void *keys, *desc, *ur;
+    int flags, n;
+    uint64_t fp, stamp;
+    orb_frame *h;
+};
+struct FrameCache {
+    std::vector<CacheEntry> e;
+    uint64_t clock = 0;
+    ~FrameCache() { for (size_t i = 0; i < e.size(); i++) orb_frame_destroy(e[i].h); }
+};
+thread_local FrameCache t_cache;
+const size_t CACHE_MAX = 48;
+
+inline uint64_t mix(uint64_t h, const void *p, size_t n) {   // FNV-1a
+    const unsigned char *b = static_cast<const unsigned char *>(p);
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+
+}  // namespace
+
 struct GpuFrame {
     orb_frame *h = nullptr;
-    std::vector<orb_keypoint> keys;
-    std::vector<uint8_t> desc;
+    bool owned = false;
     template <class KeyVec>
     GpuFrame(const KeyVec &keysUn, const cv::Mat &descriptors, const std::vector<float> &uRight, const std::vector<float> &scaleFactors,
              bool keyframeView = false) {
         const int n = (int)keysUn.size();
-        keys.resize(n);
-        desc.resize((size_t)n * 32 + 32);
+        const bool withUr = (int)uRight.size() == n && n > 0;
+        static const bool noCache = std::getenv("ORBGPU_SHIM_NO_CACHE") != nullptr;
+        const void *kp = n ? (const void *)&keysUn[0] : nullptr, *dp = n ? (const void *)descriptors.ptr(0) : nullptr;
+        const void *up = withUr ? (const void *)uRight.data() : nullptr;
+        const int flags = (keyframeView ? 1 : 0) | (withUr ? 2 : 0);
+        uint64_t fp = 1469598103934665603ull;
+        if (n) {
+            const int pick[3] = {0, n / 2, n - 1};
+            for (int k = 0; k < 3; k++) {
+                const cv::KeyPoint &q = keysUn[pick[k]];
+                fp = mix(fp, &q.pt.x, 4); fp = mix(fp, &q.pt.y, 4); fp = mix(fp, &q.angle, 4); fp = mix(fp, &q.octave, 4);
+                fp = mix(fp, descriptors.ptr(pick[k]), 32);
+                if (withUr) fp = mix(fp, &uRight[pick[k]], 4);
+            }
+        }
+        const float bounds[4] = {Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY};
+        fp = mix(fp, bounds, sizeof(bounds));
+        FrameCache &C = t_cache;
+        if (!noCache)
+            for (size_t i = 0; i < C.e.size(); i++) {
+                CacheEntry &c = C.e[i];
+                if (c.keys == kp && c.desc == dp && c.ur == up && c.flags == flags && c.n == n && c.fp == fp) {
+                    c.stamp = ++C.clock;
+                    h = c.h;
+                    return;
+                }
+            }
+        std::vector<orb_keypoint> keys(n);
+        std::vector<uint8_t> desc((size_t)n * 32 + 32);
         for (int i = 0; i < n; i++) {
             const cv::KeyPoint &k = keysUn[i];
             keys[i].x = k.pt.x; keys[i].y = k.pt.y; keys[i].size = k.size; keys[i].angle = k.angle; keys[i].response = k.response;
@@ -37,13 +101,22 @@ struct GpuFrame {
         }
         orb_frame_desc d;
         d.n = n; d.keys_un = keys.data(); d.descriptors = desc.data();
-        d.u_right = ((int)uRight.size() == n && n > 0) ? uRight.data() : nullptr;
+        d.u_right = withUr ? uRight.data() : nullptr;
         d.min_x = Frame::mnMinX; d.max_x = Frame::mnMaxX; d.min_y = Frame::mnMinY; d.max_y = Frame::mnMaxY;
         d.nlevels = (int)scaleFactors.size(); d.scale_factors = scaleFactors.data();
         d.keyframe_view = keyframeView ? 1 : 0;
         Check(orb_frame_create(&d, &h), "orb_frame_create");
+        if (noCache) { owned = true; return; }
+        if (C.e.size() >= CACHE_MAX) {   // drop the least recently used entry
+            size_t lru = 0;
+            for (size_t i = 1; i < C.e.size(); i++) if (C.e[i].stamp < C.e[lru].stamp) lru = i;
+            orb_frame_destroy(C.e[lru].h);
+            C.e.erase(C.e.begin() + lru);
+        }
+        CacheEntry c = {kp, dp, up, flags, n, fp, ++C.clock, h};
+        C.e.push_back(c);
     }
-    ~GpuFrame() { orb_frame_destroy(h); }
+    ~GpuFrame() { if (owned) orb_frame_destroy(h); }
     GpuFrame(const GpuFrame &) = delete;
     GpuFrame &operator=(const GpuFrame &) = delete;
 };

@@ -65,7 +65,6 @@ int main(int argc, char **argv) {
     if (argc > 7) {   // latency of the calls a Tracking thread makes, without the host mirror of the pyramid (median of 50)
         auto med = [](std::vector<double> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
         auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-        exL.SetMirrorPyramid(false); exR.SetMirrorPyramid(false);
         std::vector<double> t1, t2, t3;
         for (int i = 0; i < 55; i++) {
             double t0 = now();

@@ -360,6 +360,115 @@ def bench_c4(args, torch, dev, local):
                          500, with_stages=True)
 
 
+def bench_c3(args, popc_rate=None):
+    """Config C3 (BASELINE.json configs[2]): 752x480, frame B = frame A shifted by (+7,+4), init extractor (2000
+    features).  Per-call latency of the three tracking matchers through the C ABI from host arrays, measured by a C++ caller
+    (ar_orbslam2_b200/shim/c3_bench: steady_clock around each call, median of `reps`), beside the reference's own
+    ORBmatcher.cc (oracle/_ref/liborbmatcher_ref.so, compiled unmodified) on one host core with a timer around the same
+    method call, on the same inputs; results compared array for array."""
+    import tempfile
+    from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.synth import SplitMix64, shifted_frame, synth_frame
+    W3, H3, reps = 752, 480, 50
+    FX3 = FY3 = np.float32(435.2); CX3, CY3 = np.float32(367.2), np.float32(252.2)   # ref Examples/Stereo/EuRoC.yaml:8-11
+    a = synth_frame(W3, H3, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    ex = ORBextractor(2000, 1.2, 8, 20, 7, max_width=W3, max_height=H3)
+    ka, da = ex(a)
+    kb, db = ex(b)
+    scale = ex.GetScaleFactors()
+    ex.close()
+    n = len(ka)
+    # map points of the Last frame: depth z = 2 + (hash(i) mod 1000)/100 m, Last pose I, Cur pose translated by (0.05, 0.02, 0) m
+    z = np.array([2 + (SplitMix64(i).next() % 1000) / 100 for i in range(n)], np.float32)
+    xyz = np.stack([(ka["x"] - CX3) * z / FX3, (ka["y"] - CY3) * z / FY3, z], 1).astype(np.float32)
+    has = (np.arange(n) % 17 != 0).astype(np.uint8)
+    obs = np.ones(n, np.uint8)
+    claimed_last = np.zeros(n, np.uint8)
+    Tl = np.eye(4, dtype=np.float32)
+    Tc = np.eye(4, dtype=np.float32); Tc[:3, 3] = (0.05, 0.02, 0.0)
+    # local map points for SearchByProjection(Frame, MapPoints): A's features projected into B
+    rng = SplitMix64(9)
+    in_view = np.array([rng.next() % 10 != 0 for _ in range(n)], np.uint8)
+    px, py = (ka["x"] + 7).astype(np.float32), (ka["y"] + 4).astype(np.float32)
+    pxr = (px - 6).astype(np.float32)
+    lvl = ka["octave"].astype(np.int32)
+    vc = np.full(n, 0.9, np.float32)
+    claimed_pts = np.zeros(len(kb), np.uint8)
+    out = {"workload": f"C3: {W3}x{H3}, frame B = A shifted (+7,+4), 2000-feature init extractor: {n} / {len(kb)} key points",
+           "how": "GPU: C++ caller, steady_clock around each C-ABI call from host arrays, frame indices cached (as the C++ shim does); "
+                  "reference: the reference's own ORBmatcher.cc compiled unmodified, timer around the method call, one core"}
+    # ---- reference (CPU) side
+    ref = None
+    try:
+        from oracle import orbref
+        from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+        if orbref.ref_matcher_available():
+            rb = orbref.ReferenceSourceBackend()
+            rb.L.refm_last_call_us.restype = C.c_double
+            bounds = (0.0, float(W3), 0.0, float(H3))
+            mk = lambda k, d: Frame(k, d, scale, bounds, backend=rb)
+            r1, r2 = mk(ka, da), mk(kb, db)
+            prev0 = np.stack([ka["x"], ka["y"]], 1).astype(np.float32)
+            t = []
+            for _ in range(12):
+                pr = prev0.copy()
+                nm_i, m12_ref = ORBmatcher(0.9, True, backend=rb).SearchForInitialization(r1, r2, pr, 100)
+                t.append(rb.L.refm_last_call_us())
+            ref = {"search_for_initialization": {"us_median": float(np.median(t)), "nmatches": nm_i}}
+            prev_ref = pr
+            rc, rl = mk(ka, da), mk(ka, da)
+            t = []
+            for _ in range(12):
+                R = orbref.refm_search_by_projection_last(rc, rl, xyz, has, obs, claimed_last, Tc, Tl, FX3, FY3, CX3, CY3, 40.0, 0.11, 15.0, True,
+                                                          0.9, True)
+                t.append(rb.L.refm_last_call_us())
+            ref["search_by_projection_last"] = {"us_median": float(np.median(t)), "nmatches": R["nmatches"]}
+            t = []
+            for _ in range(12):
+                nm_p, asg_p_ref = ORBmatcher(0.8, backend=rb).SearchByProjectionPoints(r2, in_view, px, py, pxr, lvl, vc, da, 3.0, claimed_pts, obs)
+                t.append(rb.L.refm_last_call_us())
+            ref["search_by_projection_points"] = {"us_median": float(np.median(t)), "nmatches": nm_p}
+    except Exception as exc:   # the checker's leg must not cost the line
+        ref = {"unavailable": repr(exc)}
+    if not ref or "unavailable" in ref:
+        out["reference"] = ref or {"unavailable": "oracle/_ref/liborbmatcher_ref.so not built"}
+        return out
+    # ---- GPU side: the C++ caller
+    exe = os.path.join(ROOT, "ar_orbslam2_b200", "shim", "c3_bench")
+    with tempfile.TemporaryDirectory() as td:
+        w = lambda name, arr: np.ascontiguousarray(arr).tofile(os.path.join(td, name))
+        w("a.raw", a); w("b.raw", b); w("ka.bin", ka); w("da.bin", da); w("kb.bin", kb); w("db.bin", db); w("scale.bin", scale.astype(np.float32))
+        w("last_valid.bin", R["valid"]); w("last_u.bin", R["u"]); w("last_v.bin", R["v"]); w("last_invz.bin", R["invz"])
+        w("last_octave.bin", ka["octave"].astype(np.int32)); w("last_angle.bin", ka["angle"].astype(np.float32)); w("last_obs.bin", obs)
+        w("last_claimed.bin", claimed_last); w("last_uright.bin", np.full(n, -1, np.float32))
+        w("pts_in_view.bin", in_view); w("pts_x.bin", px); w("pts_y.bin", py); w("pts_xr.bin", pxr); w("pts_level.bin", lvl)
+        w("pts_view_cos.bin", vc); w("pts_obs.bin", obs); w("pts_claimed.bin", claimed_pts)
+        p = subprocess.run([exe, td, str(W3), str(H3), str(reps)], capture_output=True, text=True)
+        if p.returncode != 0:
+            out["gpu"] = {"failed": p.stderr[-400:]}
+            return out
+        g = json.loads(p.stdout.strip().splitlines()[-1])
+        rd = lambda name, dt: np.fromfile(os.path.join(td, name), dt)
+        same = {"search_for_initialization": bool(np.array_equal(rd("init_m12.bin", np.int32), m12_ref) and
+                                                  np.array_equal(rd("init_prev.bin", np.float32).reshape(-1, 2), prev_ref)),
+                "search_by_projection_last": bool(np.array_equal(np.where(rd("last_assigned.bin", np.int32) < 0, -1, rd("last_assigned.bin", np.int32)),
+                                                                 R["assigned"])),
+                "search_by_projection_points": bool(np.array_equal(rd("pts_assigned.bin", np.int32), asg_p_ref))}
+    for k in ("search_for_initialization", "search_by_projection_last", "search_by_projection_points"):
+        e = g[k]
+        e["reference_us_median_1core"] = ref[k]["us_median"]
+        e["speedup_vs_reference"] = ref[k]["us_median"] / e["us_median"]
+        e["equals_reference"] = same[k] and e["nmatches"] == ref[k]["nmatches"]
+        e["compares_per_s"] = e["candidates"] / (e["us_median"] * 1e-6)
+        if popc_rate:
+            e["frac_of_popc_peak"] = e["compares_per_s"] * 8 / (popc_rate * 1e9)
+    out.update(g)
+    out["note"] = ("candidates = (query, feature) pairs whose 256-bit distance is computed (nnz of SURVEY 8d); these calls are latency-bound "
+                   "(two kernels + two copies), the POPC fraction is reported for completeness")
+    return out
+
+
 def bench_bow(args, torch, dev, local):
     """SURVEY 8f-1: DBoW2 transform (Frame::ComputeBoW) on an ORBvoc-shaped tree (k=10, L=6, 1.1 M nodes, levelsup 4):
     `frames` frames x 2000 descriptors per call, device-resident, CUDA events on the vocabulary's stream; the oracle
@@ -441,7 +550,7 @@ def bench_presteps(args, torch, dev):
     mx[:, :W] = xx + 2.3 * torch.sin(yy / 40.0) + 0.37
     my[:, :W] = yy + 1.7 * torch.cos(xx / 55.0) + 0.21
     torch.cuda.synchronize()
-    st = torch.cuda.current_stream()
+    st = torch.cuda.Stream(dev)   # an explicit stream: NULL now means the calling thread's own call stream (include/orbgpu.h "Streams")
     L = _lib.lib()
     vp = C.c_void_p
     def cvt():
@@ -768,6 +877,7 @@ def run_ours(args):
         extra["c1_mono"] = bench_c1(args, torch, dev, local)
         extra["c4_1080p"] = bench_c4(args, torch, dev, local)
         extra["latency"] = bench_latency(args)
+        extra["c3_tracking"] = bench_c3(args, extra.get("hamming", {}).get("popc_peak_gpopc32_per_s_measured"))
         if not os.environ.get("ORB_BENCH_SKIP_BOW"):
             extra["bow_transform"] = bench_bow(args, torch, dev, local)
             extra["presteps"] = bench_presteps(args, torch, dev)

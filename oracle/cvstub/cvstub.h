@@ -75,6 +75,10 @@ public:
     Mat() : rows(0), cols(0), data(nullptr), step{0}, type_(CV_8UC1), esz(1) {}
     Mat(Size sz, int t) { alloc(sz.height, sz.width, t); }
     Mat(int r, int c, int t) { alloc(r, c, t); }
+    Mat(int r, int c, int t, void *ext, size_t stp = 0) : rows(r), cols(c), data((uchar *)ext), type_(t), esz(t == CV_32F ? 4 : 1) {   // header over caller-owned pixels
+        step.v = stp ? stp : (size_t)c * esz;
+    }
+    bool isContinuous() const { return step.v == (size_t)cols * esz; }
     Mat(const MatZeros &z) : rows(0), cols(0), data(nullptr), step{0}, type_(CV_8UC1), esz(1) { *this = z; }   // cv::Mat m = cv::Mat::zeros(..), MapPoint.cc:322
     void alloc(int r, int c, int t = CV_8UC1) {
         rows = r; cols = c; type_ = t; esz = (t == CV_32F) ? 4 : 1;

@@ -332,10 +332,18 @@ def refm_descriptor_distance(a, b):
     return out
 
 
-def refm_stereo_match(img_left, img_right, nfeatures, keys_l, desc_l, keys_r, desc_r, mbf, mb, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+def refm_stereo_match(img_left, img_right, nfeatures, keys_l, desc_l, keys_r, desc_r, mbf, mb, scale=1.2, nlevels=8, ini_th=20, min_th=7,
+                      shim=False):
     """The reference's own Frame::ComputeStereoMatches (Frame.cc compiled into oracle/_ref) on the reference's own
-    pyramids.  Returns (mvuRight, mvDepth)."""
+    pyramids.  Returns (mvuRight, mvDepth).  shim=True: the same driver lines through liborbmatcher_shim.so, where
+    ORBextractor is the product's drop-in class and Frame::ComputeStereoMatches is shim/Frame_stereo.cc (needs a GPU)."""
     global _REFM
+    if shim:
+        _REFM_saved, _REFM = _REFM, ShimBackend().L
+        try:
+            return refm_stereo_match(img_left, img_right, nfeatures, keys_l, desc_l, keys_r, desc_r, mbf, mb, scale, nlevels, ini_th, min_th)
+        finally:
+            _REFM = _REFM_saved
     if _REFM is None:
         _REFM = C.CDLL(REF_MATCHER_PATH)
     il, ir = np.ascontiguousarray(img_left, np.uint8), np.ascontiguousarray(img_right, np.uint8)

@@ -3,12 +3,13 @@
 // (see oracle/Makefile.ref).  Each function builds the stub Frame / KeyFrame / MapPoint objects from the same flat
 // arrays the C ABI of include/orbgpu.h takes, calls the reference method, and flattens the result the same way, so
 // tests can compare reference source == restated oracle == GPU.
+// With -DUSE_GPU_SHIM the SAME driver is compiled with ar_orbslam2_b200/shim in front of the reference's include directory:
+// "ORBmatcher.h" / "ORBextractor.h" then resolve to the product's drop-in classes and every call below -- unchanged --
+// runs on liborbgpu (oracle/_ref/liborbmatcher_shim.so).  That is the drop-in claim, tested.
 #include "ORBmatcher.h"
 #include "../include/orbgpu.h"
-#ifdef USE_GPU_SHIM   // same driver, but the four tracking entry points go through the product shim (ar_orbslam2_b200/shim)
-#include "ORBmatcher_gpu.h"
-#endif
 
+#include <chrono>
 #include <cstring>
 #include <memory>
 
@@ -19,6 +20,13 @@ float Frame::fx, Frame::fy, Frame::cx, Frame::cy;
 float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
 float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
 #endif
+
+// bench.py's C3 leg: wall time of the last matcher call alone (the stub object set-up around it is not the reference's cost)
+static double g_call_us = 0;
+struct CallTimer {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    ~CallTimer() { g_call_us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(); }
+};
 
 struct refm_frame {
     Frame F;
@@ -85,6 +93,7 @@ int refm_frame_create(const orb_frame_desc *d, refm_frame **out) {
     return 0;
 }
 void refm_frame_destroy(refm_frame *f) { delete f; }
+double refm_last_call_us(void) { return g_call_us; }
 
 int refm_frame_features_in_area(refm_frame *f, float x, float y, float r, int min_level, int max_level, int32_t *indices, int capacity,
                                 int *n_out) {
@@ -104,11 +113,10 @@ int refm_search_for_initialization(refm_frame *f1, refm_frame *f2, float *prev_m
     for (int i = 0; i < f1->F.N; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
     std::vector<int> m12;
     ORBmatcher matcher(nnratio, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchForInitialization(f1->F, f2->F, prev, m12, window_size, nnratio, check_orientation != 0);
-#else
-    *nmatches = matcher.SearchForInitialization(f1->F, f2->F, prev, m12, window_size);
-#endif
+    {
+        CallTimer t;
+        *nmatches = matcher.SearchForInitialization(f1->F, f2->F, prev, m12, window_size);
+    }
     for (int i = 0; i < f1->F.N; i++) {
         matches12[i] = m12[i];
         prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
@@ -138,11 +146,10 @@ int refm_search_by_projection_points(refm_frame *f, const orb_track_points *P, c
     pre.id = -2; pre.nObs = 1;
     for (int i = 0; i < F.N; i++) F.mvpMapPoints[i] = (claimed && claimed[i]) ? &pre : nullptr;
     ORBmatcher matcher(nnratio, true);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByProjection(F, pts, th, nnratio);
-#else
-    *nmatches = matcher.SearchByProjection(F, pts, th);
-#endif
+    {
+        CallTimer t;
+        *nmatches = matcher.SearchByProjection(F, pts, th);
+    }
     for (int i = 0; i < F.N; i++) {
         MapPoint *m = F.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -215,11 +222,10 @@ int refm_search_by_projection_last(refm_frame *cur, refm_frame *last, const floa
         }
     }
     ORBmatcher matcher(nnratio, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByProjection(C, L, th, mono != 0, check_orientation != 0);
-#else
-    *nmatches = matcher.SearchByProjection(C, L, th, mono != 0);
-#endif
+    {
+        CallTimer t;
+        *nmatches = matcher.SearchByProjection(C, L, th, mono != 0);
+    }
     for (int i = 0; i < C.N; i++) {
         MapPoint *m = C.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -286,11 +292,7 @@ int refm_search_by_projection_kf(refm_frame *cur, refm_frame *kf, const float *w
         }
     }
     ORBmatcher matcher(nnratio, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByProjection(C, K.get(), already, th, orb_dist, check_orientation != 0);
-#else
     *nmatches = matcher.SearchByProjection(C, K.get(), already, th, orb_dist);
-#endif
     for (int i = 0; i < C.N; i++) {
         MapPoint *m = C.mvpMapPoints[i];
         assigned[i] = (m && m->id >= 0) ? m->id : -1;
@@ -361,11 +363,7 @@ int refm_search_by_projection_sim3(refm_frame *kf, const float *Scw, int n, cons
         }
     }
     ORBmatcher matcher(nnratio, true);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByProjection(K.get(), S, pts, matched, th);
-#else
     *nmatches = matcher.SearchByProjection(K.get(), S, pts, matched, th);
-#endif
     for (int i = 0; i < K->N; i++) assigned[i] = (matched[i] && matched[i]->id >= 0) ? matched[i]->id : -1;
     return 0;
 }
@@ -396,11 +394,7 @@ int refm_search_by_bow(refm_frame *kf, refm_frame *f, int ngroups, const int32_t
     fill_featvec(f->F.mFeatVec, ngroups, f_off, f_idx);
     std::vector<MapPoint *> out;
     ORBmatcher matcher(nnratio, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByBoW(K.get(), f->F, out, nnratio, check_orientation != 0);
-#else
     *nmatches = matcher.SearchByBoW(K.get(), f->F, out);
-#endif
     for (int i = 0; i < f->F.N; i++) matches[i] = out[i] ? out[i]->id : -1;
     return 0;
 }
@@ -421,11 +415,7 @@ int refm_search_by_bow_kfkf(refm_frame *kf1, refm_frame *kf2, int ngroups, const
     fill_featvec(K2->mFeatVec, ngroups, off2, idx2);
     std::vector<MapPoint *> out;
     ORBmatcher matcher(nnratio, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchByBoW(K1.get(), K2.get(), out, nnratio, check_orientation != 0);
-#else
     *nmatches = matcher.SearchByBoW(K1.get(), K2.get(), out);
-#endif
     for (int i = 0; i < K2->N; i++) matches[i] = -1;
     for (int i1 = 0; i1 < K1->N; i1++)
         if (out[i1]) matches[out[i1]->id] = i1;
@@ -503,11 +493,7 @@ int refm_search_for_triangulation(refm_frame *kf1, refm_frame *kf2, int ngroups,
     memcpy(F.data, F12, 36);
     std::vector<std::pair<size_t, size_t>> pairs;
     ORBmatcher matcher(0.6f, check_orientation != 0);
-#ifdef USE_GPU_SHIM
-    *nmatches = orbgpu_shim::SearchForTriangulation(K1.get(), K2.get(), F, pairs, only_stereo != 0, check_orientation != 0);
-#else
     *nmatches = matcher.SearchForTriangulation(K1.get(), K2.get(), F, pairs, only_stereo != 0);
-#endif
     for (int i = 0; i < K1->N; i++) matches12[i] = -1;
     for (size_t k = 0; k < pairs.size(); k++) matches12[pairs[k].first] = (int32_t)pairs[k].second;
     return 0;
@@ -549,19 +535,11 @@ int refm_fuse(refm_frame *kf, int variant, const float *Rcw9, const float *tcw3,
     std::vector<MapPoint *> repl(n, nullptr);
     ORBmatcher matcher(0.6f, true);
     if (variant == 0) {
-#ifdef USE_GPU_SHIM
-        *nfused = orbgpu_shim::Fuse(K.get(), pts, th);
-#else
         *nfused = matcher.Fuse(K.get(), pts, th);
-#endif
     } else {
         cv::Mat S(4, 4, CV_32F);
         memcpy(S.data, Scw16, 64);
-#ifdef USE_GPU_SHIM
-        *nfused = orbgpu_shim::Fuse(K.get(), S, pts, th, repl);
-#else
         *nfused = matcher.Fuse(K.get(), S, pts, th, repl);
-#endif
     }
     for (int idx = 0; idx < K->N; idx++) {
         kf_state[idx] = K->mvpMapPoints[idx] ? K->mvpMapPoints[idx]->id : -1;
@@ -612,11 +590,7 @@ int refm_search_by_sim3(refm_frame *kf1, refm_frame *kf2, float s12, const float
     cv::Mat R(3, 3, CV_32F), t = vec3(t12);
     memcpy(R.data, R12, 36);
     ORBmatcher matcher(0.6f, true);
-#ifdef USE_GPU_SHIM
-    *nfound = orbgpu_shim::SearchBySim3(K1.get(), K2.get(), m12, s12, R, t, th);
-#else
     *nfound = matcher.SearchBySim3(K1.get(), K2.get(), m12, s12, R, t, th);
-#endif
     for (int i = 0; i < K1->N; i++) matches12[i] = m12[i] ? m12[i]->id : -1;
     return 0;
 }

@@ -145,3 +145,53 @@ def test_cpp_projection_shims_m4_m5(oracle, gpu_lib):
         R, S = [oracle.refm_search_by_projection_sim3(mk(be), c["S"], c["xyz"], c["nrm"], c["usable"], c["maxd"], c["mind"], c["claimed"],
                                                       T.FX, T.FY, T.CX, T.CY, th, 0.9) for be in (rb, sb)]
         assert R["nmatches"] > 100 and S["nmatches"] == R["nmatches"] and np.array_equal(S["assigned"], R["assigned"]), th
+
+
+def test_cpp_frame_stereo_dropin(oracle, gpu_lib):
+    """The reference's Frame (its own Frame.h / Frame.cc, unmodified) linked with the product's ORBextractor class and
+    shim/Frame_stereo.cc: `F.ComputeStereoMatches()` -- the call the stereo constructor makes (ref Frame.cc:95) -- leaves the
+    mvuRight / mvDepth of the reference's own member function."""
+    if not (oracle.ref_matcher_available() and os.path.exists(oracle.REF_SHIM_PATH)):
+        pytest.skip("oracle/_ref shim library not built")
+    w, h, nf = 1241, 376, 2000
+    left, right = synth_stereo_pair(w, h, 41)
+    rl, rr = oracle.RefExtractor(nf), oracle.RefExtractor(nf)
+    kl, dl = rl.extract(left)
+    kr, dr = rr.extract(right)
+    mbf = np.float32(386.1448)
+    mb = mbf / np.float32(718.856)
+    ur_ref, dp_ref = oracle.refm_stereo_match(left, right, nf, kl, dl, kr, dr, mbf, mb)
+    ur, dp = oracle.refm_stereo_match(left, right, nf, kl, dl, kr, dr, mbf, mb, shim=True)
+    assert (ur_ref >= 0).sum() > 500
+    assert np.array_equal(ur.view(np.uint32), ur_ref.view(np.uint32)) and np.array_equal(dp.view(np.uint32), dp_ref.view(np.uint32))
+
+
+def test_cpp_matcher_class_frame_cache(oracle, gpu_lib):
+    """The per-thread cache of device frame indices inside the shim: repeated matcher calls on the same Frame objects (what
+    Tracking does with mCurrentFrame) reuse one index and keep returning the reference's result."""
+    import test_reference_matcher_cpu as T
+    from ar_orbslam2_b200.synth import shifted_frame, synth_frame
+    from ar_orbslam2_b200.tracking import Frame, ORBmatcher
+    if not (oracle.ref_matcher_available() and os.path.exists(oracle.REF_SHIM_PATH)):
+        pytest.skip("oracle/_ref shim library not built")
+    W, H = T.W, T.H
+    a = synth_frame(W, H, 31)
+    b = shifted_frame(a, 7, 4, 32)
+    ex = oracle.RefExtractor(2000)
+    ka, da = ex.extract(a)
+    kb, db = ex.extract(b)
+    scale = ex.tables()["scale"]
+    bounds = (0.0, float(W), 0.0, float(H))
+    rb, sb = oracle.ReferenceSourceBackend(), oracle.ShimBackend()
+    r1, r2 = Frame(ka, da, scale, bounds, backend=rb), Frame(kb, db, scale, bounds, backend=rb)
+    s1, s2 = Frame(ka, da, scale, bounds, backend=sb), Frame(kb, db, scale, bounds, backend=sb)
+    prev = np.stack([ka["x"], ka["y"]], 1).astype(np.float32).copy()
+    pr, ps = prev.copy(), prev.copy()
+    us = []
+    for it in range(6):   # vbPrevMatched evolves call by call, as in Tracking::MonocularInitialization
+        nr, mr = ORBmatcher(0.9, True, backend=rb).SearchForInitialization(r1, r2, pr, 100)
+        ns, ms = ORBmatcher(0.9, True, backend=sb).SearchForInitialization(s1, s2, ps, 100)
+        assert ns == nr and np.array_equal(ms, mr) and np.array_equal(ps, pr)
+        sb.L.refm_last_call_us.restype = __import__("ctypes").c_double
+        us.append(sb.L.refm_last_call_us())
+    assert min(us[1:]) < us[0], f"cached calls should be faster than the first: {us}"
