@@ -242,6 +242,8 @@ struct FastLevel {   // what k_fast_cells needs of one level, passed by value (c
     int pitch, maxBX, maxBY, wCell, hCell, cand_off, cand_cap, cand_frame;
     int off_vmap, off_flags, off_survH, off_survL;   // byte offsets into dynamic shared memory (16-aligned)
     long long interior_off, pyr_frame;
+    // the streamed path (k_fast_compass / k_fast_arc / k_fast_nms / k_fast_retry)
+    int w, h, ncx, ncy, cell_begin, total_cells, flag_off, flag_cap, flag_frame;
 };
 
 // magic[d] = floor((2^32 - 1) / d) + 1: n / d == umulhi(n, magic[d]) for the small n used here (d = 0, 1 unused)
@@ -304,9 +306,11 @@ __device__ __forceinline__ uint32_t fast_arc_pair(const uint8_t *p0, const uint8
 // out-of-line copy for the rare both-type pixels (a second inlined copy doubles the kernel's register count)
 __device__ __noinline__ uint32_t fast_arc_pair_call(const uint8_t *p, const uint32_t sgn) { return fast_arc_pair(p, p, sgn); }
 
-__global__ void __launch_bounds__(FAST_T)
-k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
-             int *__restrict__ err) {
+// One cell, start to finish, by the whole CTA; `thr0` is the threshold of the first pass (iniThFAST, or minThFAST when the
+// caller already knows the cell is empty at iniThFAST).
+__device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const FastLevel &g, uint32_t *__restrict__ cand,
+                                          uint32_t *__restrict__ cand_count, int *__restrict__ err, const int b, const int ci,
+                                          const int cj, const int thr0) {
     extern __shared__ __align__(16) unsigned char fsm[];
     __shared__ int s_nkp, s_cnt, s_nB, s_nW;
 
@@ -317,7 +321,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     const int listTop = g.wCell * g.hCell - 1;
     uint32_t *wlist = reinterpret_cast<uint32_t *>(fsm + g.off_flags);   // code0 | brighter nibble << 16 | darker nibble << 20
 
-    const int b = blockIdx.z, ci = blockIdx.y, cj = blockIdx.x, level = g.level;
+    const int level = g.level;
     const int minB = EDGE - 3;
     // ROI handed to cv::FAST by the reference (ref :759-773)
     const int iniX = minB + cj * g.wCell, iniY = minB + ci * g.hCell;
@@ -368,7 +372,7 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
     // the first / last word column also clears the score word beside it (the apron column may sit there)
     const bool edgeL = w == w0 && w0 > 0, edgeR = w == w0 + nWc - 1;
 
-    int thr = g.ini_th, nH = 0, nL = 0;
+    int thr = thr0, nH = 0, nL = 0;
     for (;;) {
         // ---- 2. compass test at thr, 4 pixels per thread and step.  Lanes: A = (px0, px2), B = (px1, px3).
         //   H <=> c - max(min(U, D), min(L, R)) > t        L <=> min(max(U, D), max(L, R)) - c > t
@@ -488,6 +492,271 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
         thr = g.min_th;   // empty cell: once more at the lower threshold (ref :780-784)
         if (tid == 0) { s_cnt = 0; s_nB = 0; s_nW = 0; }
         __syncthreads();
+    }
+}
+
+
+__global__ void __launch_bounds__(FAST_T)
+k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
+             int *__restrict__ err) {
+    fast_cell(pyr, g, cand, cand_count, err, blockIdx.z, blockIdx.y, blockIdx.x, g.ini_th);
+}
+
+// ------------------------------------------------------------------------------------------
+// Streamed FAST for large batches: the same candidates as k_fast_cells (any order), without a shared-memory tile per cell.
+// The computed regions of a level's cells tile the window interior [EDGE, w - EDGE) x [EDGE, h - EDGE) without overlap, and
+// the compass test does not depend on the cell, so it runs over the whole plane as a stream:
+//   k_fast_compass  a thread owns one aligned word column (4 pixels) and walks FS_ROWS rows.  The rows y - 3 .. y + 3 of
+//                   its column stay unpacked in registers (each row is unpacked once and serves as "down", "centre" and
+//                   "up"); the words beside the column are loaded with their row and wait in registers as well.  Words
+//                   with survivors at iniThFAST go to the thread's private slots in shared memory; at the end the CTA
+//                   reserves one range in the level's brighter-type and darker-type survivor lists (two global atomics)
+//                   and writes the survivors' coordinates.  The same pass zeroes the frame's score plane.
+//   k_fast_arc      exact arc strength, a thread per PAIR of same-type survivors (16x2 lanes), written into the score plane.
+//   k_fast_nms      a thread per survivor: threshold + 3x3 non-max suppression; a neighbour counts only if it lies in the
+//                   same cell's computed region (ref :759-790: cv::FAST runs per cell ROI).  What passes goes to the
+//                   candidate list and marks its cell as non-empty.
+//   k_fast_retry    the cells that stayed empty run k_fast_cells' routine at minThFAST (ref :780-784); persistent CTAs
+//                   pick them out of the level's cell flags.
+// ------------------------------------------------------------------------------------------
+constexpr int FS_ROWS = 42;        // rows per thread of the compass pass
+constexpr int FS_T = 128;
+
+// survivor code: x | y << 12 (interior coordinates) | 1 << 31 (brighter-type list only: the pixel is of the darker type as
+// well).  One array per (frame, level), as long as the level has computed pixels: brighter-type codes grow from the bottom,
+// darker-type codes from the top; every survivor is on exactly one of the two.
+__global__ void __launch_bounds__(FS_T)
+k_fast_compass(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ score, const FastLevel g, uint32_t *__restrict__ surv,
+               uint32_t *__restrict__ surv_count) {
+    __shared__ uint32_t s_list[FS_ROWS * FS_T];   // flagged words, a private column of slots per thread: [slot][thread]
+    __shared__ int s_warp[FS_T / 32], s_base[2];
+    const int b = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
+    const int x_lo = EDGE, x_hi = g.w - EDGE;                       // computed columns (interior coordinates)
+    const int wfirst = (XOFF + x_lo) >> 2, wlast = (XOFF + x_hi - 1) >> 2;
+    const int wq = wfirst + blockIdx.x * FS_T + tid, w = min(wq, wlast);
+    const int ys = EDGE + blockIdx.y * FS_ROWS, nrows = min(FS_ROWS, g.h - EDGE - ys);
+    uint32_t vm = 0;                                                 // bytes of this word that are computed pixels
+    if (wq <= wlast) {
+        const int lo = XOFF + x_lo - 4 * w, hi = XOFF + x_hi - 4 * w;
+        vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
+    }
+    const size_t pitch = (size_t)g.pitch;
+    const size_t o0 = (size_t)b * g.pyr_frame + g.interior_off - XOFF + (size_t)(ys - 3) * pitch + (size_t)w * 4;
+    const uint8_t *p = pyr + o0;                 // this thread's word in row y + 3 (the row that enters the window)
+    uint8_t *sp = score + o0 + 3 * pitch;        // ... and in row y of the score plane
+    const uint32_t tb = (uint32_t)g.ini_th * 0x00010001u + 0x80008000u;
+    // rows y - 3 .. y + 3 of the column, unpacked: lanes A = (px0, px2), B = (px1, px3); slot = (row - (ys - 3)) % 7.  The
+    // words beside the column are loaded with their row (one pointer, immediate offsets) and wait three rows in Pq / Nq.
+    uint32_t A[7], B[7], Pq[4], Nq[4];
+#pragma unroll
+    for (int i = 0; i < 6; i++, p += pitch) {
+        const uint32_t C = __ldg(reinterpret_cast<const uint32_t *>(p));
+        A[i] = __byte_perm(C, 0, 0x4240); B[i] = __byte_perm(C, 0, 0x4341);
+        if (i >= 3) {
+            Pq[i & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) - 1);
+            Nq[i & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) + 1);
+        }
+    }
+    int cnt = 0;
+#pragma unroll
+    for (int k = 0; k < FS_ROWS; k++, p += pitch, sp += pitch) {
+        if (k >= nrows) break;
+        const uint32_t Cn = __ldg(reinterpret_cast<const uint32_t *>(p));
+        Pq[(k + 6) & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) - 1);
+        Nq[(k + 6) & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) + 1);
+        *reinterpret_cast<uint32_t *>(sp) = 0;
+        A[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4240); B[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4341);
+        const uint32_t P = Pq[(k + 3) & 3], N = Nq[(k + 3) & 3];
+        const uint32_t cA = A[(k + 3) % 7], cB = B[(k + 3) % 7], uA = A[k % 7], uB = B[k % 7], dA = A[(k + 6) % 7], dB = B[(k + 6) % 7];
+        // left = pixels x - 3, right = x + 3: (P1, P3) (P2, C0) and (C3, N1) (N0, N2); byte 1 of an unpacked word is zero
+        const uint32_t lA = __byte_perm(P, 0, 0x4341), lB = __byte_perm(P, cA, 0x5452);
+        const uint32_t rA = __byte_perm(cB, N, 0x1512), rB = __byte_perm(N, 0, 0x4240);
+        const uint32_t mA = __vmaxs2(__vmins2(uA, dA), __vmins2(lA, rA)), mB = __vmaxs2(__vmins2(uB, dB), __vmins2(lB, rB));
+        const uint32_t nA = __vmins2(__vmaxs2(uA, dA), __vmaxs2(lA, rA)), nB = __vmins2(__vmaxs2(uB, dB), __vmaxs2(lB, rB));
+        // lane bit 15 set <=> NOT a survivor (no carries between lanes: every lane stays in [0x7f01, 0x81fe])
+        const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
+        const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
+        const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
+        if (fH | fL) {   // brighter-type bits 0 / 8 / 16 / 24, darker-type bits 1 / 9 / 17 / 25, row in bits 2..7
+            s_list[cnt * FS_T + tid] = (fH >> 7) | (fL >> 6) | (uint32_t)(k << 2);
+            cnt++;
+        }
+    }
+    // ---- survivors of the CTA's flagged words -> the level's two lists: count, reserve one range per list, write
+    int nh = 0, nl = 0;
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = s_list[i * FS_T + tid], hm = e & 0x01010101u, lm = (e >> 1) & 0x01010101u & ~hm;
+        nh += __popc(hm); nl += __popc(lm);
+    }
+    int v = nh | (nl << 16), incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[tid >> 5] = incl;
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int q = 0; q < FS_T / 32; q++) {
+        if (q < (tid >> 5)) before += s_warp[q];
+        total += s_warp[q];
+    }
+    if (total == 0) return;
+    uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
+    if (tid == 0) {
+        s_base[0] = (total & 0xffff) ? (int)atomicAdd(cnts, (uint32_t)(total & 0xffff)) : 0;
+        s_base[1] = (total >> 16) ? (int)atomicAdd(cnts + 1, (uint32_t)(total >> 16)) : 0;
+    }
+    __syncthreads();
+    const int ex = before + incl - v;
+    uint32_t *dst = surv + (size_t)b * g.flag_frame + g.flag_off;
+    int ph = s_base[0] + (ex & 0xffff), pl = g.flag_cap - 1 - (s_base[1] + (ex >> 16));
+    const uint32_t xy0 = (uint32_t)(4 * w - XOFF) | (uint32_t)ys << 12;
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = s_list[i * FS_T + tid];
+        const uint32_t xy = xy0 + (((e >> 2) & 63u) << 12);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t f = (e >> (8 * j)) & 3u;
+            if (f & 1u) dst[ph++] = (xy + j) | (f >> 1) << 31;
+            else if (f) dst[pl--] = xy + j;
+        }
+    }
+}
+
+// fast_arc_pair on the plane itself: the circle offsets depend on the level's pitch
+__device__ __forceinline__ uint32_t fast_arc_pair_g(const uint8_t *__restrict__ p0, const uint8_t *__restrict__ p1, const uint32_t sgn,
+                                                    const int PB) {
+    const uint32_t cp = __byte_perm(p0[0], p1[0], 0x5410);
+    const uint32_t base = 0x01000100u + cp * sgn, nsgn = 0u - sgn;
+    const int off[16] = {3 * PB, 3 * PB + 1, 2 * PB + 2, PB + 3, 3, -PB + 3, -2 * PB + 2, -3 * PB + 1,
+                         -3 * PB, -3 * PB - 1, -2 * PB - 2, -PB - 3, -3, PB - 3, 2 * PB - 2, 3 * PB - 1};
+    uint32_t e[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const uint32_t q = __byte_perm(__ldg(p0 + off[k]), __ldg(p1 + off[k]), 0x5410);
+        e[k] = q * nsgn + base;
+    }
+    uint32_t m3[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    uint32_t a = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k += 2)
+        a = __vimax3_s16x2(a, __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]),
+                           __vimin3_s16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]));
+    return a;
+}
+__device__ __noinline__ uint32_t fast_arc_pair_g_call(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn, const int PB) {
+    return fast_arc_pair_g(p0, p1, sgn, PB);
+}
+
+constexpr int FA_T = 128;
+// one thread per pair of same-type survivors (the type is a run-time sign): dense warps whatever the flagged words look like
+__global__ void __launch_bounds__(FA_T)
+k_fast_arc(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ score, const FastLevel g, const uint32_t *__restrict__ surv,
+           const uint32_t *__restrict__ surv_count) {
+    const int b = blockIdx.y;
+    const uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
+    const int nH = (int)cnts[0], nL = (int)cnts[1], top = g.flag_cap - 1;
+    const int nPH = (nH + 1) >> 1, nPP = nPH + ((nL + 1) >> 1);
+    const uint32_t *src = surv + (size_t)b * g.flag_frame + g.flag_off;
+    const size_t plane = (size_t)b * g.pyr_frame + g.interior_off;
+    for (int s = blockIdx.x * FA_T + threadIdx.x; s < nPP; s += gridDim.x * FA_T) {
+        uint32_t c0, c1, sgn = 1u;
+        if (s < nPH) { const int i0 = 2 * s; c0 = src[i0]; c1 = i0 + 1 < nH ? src[i0 + 1] : c0; }
+        else { const int i0 = 2 * (s - nPH); sgn = 0xffffffffu; c0 = src[top - i0]; c1 = i0 + 1 < nL ? src[top - i0 - 1] : c0; }
+        const size_t o0 = plane + (size_t)((c0 >> 12) & 4095u) * g.pitch + (c0 & 4095u);
+        const size_t o1 = plane + (size_t)((c1 >> 12) & 4095u) * g.pitch + (c1 & 4095u);
+        uint32_t a = fast_arc_pair_g(pyr + o0, pyr + o1, sgn, g.pitch);
+        if ((c0 | c1) >> 31) {   // rare: brighter than one compass pair and darker than the other -> the larger of the two strengths
+            const uint32_t a2 = fast_arc_pair_g_call(pyr + o0, pyr + o1, 0xffffffffu, g.pitch);
+            const uint32_t keep = ((c0 >> 31) ? 0xffffu : 0u) | ((c1 >> 31) ? 0xffff0000u : 0u);
+            a = __vmaxs2(a, a2 & keep);
+        }
+        score[o0] = (uint8_t)max((int)(a & 0xffff) - 256, 0);
+        score[o1] = (uint8_t)max((int)(a >> 16) - 256, 0);
+    }
+}
+
+// one thread per survivor: threshold, 3x3 non-max suppression inside the survivor's cell, candidate list, cell flag
+__global__ void __launch_bounds__(FA_T)
+k_fast_nms(const uint8_t *__restrict__ score, const FastLevel g, const uint32_t *__restrict__ surv,
+           const uint32_t *__restrict__ surv_count, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
+           uint8_t *__restrict__ cell_found, int *__restrict__ err) {
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    const uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
+    const int nH = (int)cnts[0], n = nH + (int)cnts[1], top = g.flag_cap - 1;
+    const uint32_t *src = surv + (size_t)b * g.flag_frame + g.flag_off;
+    const size_t plane = (size_t)b * g.pyr_frame + g.interior_off;
+    const FastDiv dW(g.wCell), dH(g.hCell);
+    const int PB = g.pitch, thr = g.ini_th;
+    const int stride = gridDim.x * FA_T, nIt = (n + stride - 1) / stride;
+    for (int it = 0; it < nIt; it++) {
+        const int s = it * stride + blockIdx.x * FA_T + threadIdx.x;
+        bool pass = false;
+        int x = 0, y = 0, V = 0;
+        if (s < n) {
+            const uint32_t c = s < nH ? src[s] : src[top - (s - nH)];
+            x = (int)(c & 4095u); y = (int)((c >> 12) & 4095u);
+            const uint8_t *v = score + plane + (size_t)y * PB + x;
+            V = v[0];
+            if (V > thr) {
+                const int ci = dH.div(y - EDGE), cj = dW.div(x - EDGE);
+                const int ly = y - EDGE - ci * g.hCell, lx = x - EDGE - cj * g.wCell;
+                const int chh = min(g.hCell, g.h - 2 * EDGE - ci * g.hCell), cww = min(g.wCell, g.w - 2 * EDGE - cj * g.wCell);
+                // a neighbour outside the cell's computed region counts as 0 (cv::FAST ran on the cell's ROI alone)
+                const int oL = lx > 0 ? -1 : 0, oR = lx < cww - 1 ? 1 : 0, oU = ly > 0 ? -PB : 0, oD = ly < chh - 1 ? PB : 0;
+                const int m = max(max(max(oL ? v[oL] : 0, oR ? v[oR] : 0), max(oU ? v[oU] : 0, oD ? v[oD] : 0)),
+                                  max(max(oL && oU ? v[oU + oL] : 0, oR && oU ? v[oU + oR] : 0),
+                                      max(oL && oD ? v[oD + oL] : 0, oR && oD ? v[oD + oR] : 0)));
+                pass = V > m;
+                if (pass) cell_found[(size_t)b * g.total_cells + g.cell_begin + ci * g.ncx + cj] = 1;
+            }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, pass);
+        if (bal == 0) continue;
+        int base = 0;
+        if (lane == 0) base = (int)atomicAdd(cand_count + (size_t)b * g.nlevels + g.level, (uint32_t)__popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (pass) {
+            const int slot = base + __popc(bal & ((1u << lane) - 1u));
+            if (slot < g.cand_cap)
+                cand[(size_t)b * g.cand_frame + g.cand_off + slot] =
+                    (uint32_t)(x - (EDGE - 3)) | ((uint32_t)(y - (EDGE - 3)) << 12) | ((uint32_t)(V - 1) << 24);
+            else
+                atomicOr(err, ERRF_CAND_OVERFLOW);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(FAST_T)
+k_fast_retry(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
+             const uint8_t *__restrict__ cell_found, int *__restrict__ err, const int batch) {
+    __shared__ unsigned s_empty[FAST_T / 32];
+    const int ncl = g.ncx * g.ncy, total = ncl * batch, tid = threadIdx.x;
+    for (int c0 = blockIdx.x * FAST_T; c0 < total; c0 += gridDim.x * FAST_T) {
+        const int c = c0 + tid;
+        bool empty = false;
+        if (c < total) {
+            const int b = c / ncl, rem = c - b * ncl;
+            empty = cell_found[(size_t)b * g.total_cells + g.cell_begin + rem] == 0;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, empty);
+        __syncthreads();           // the previous round's masks have been read by everyone
+        if ((tid & 31) == 0) s_empty[tid >> 5] = bal;
+        __syncthreads();
+        for (int wv = 0; wv < FAST_T / 32; wv++) {
+            unsigned m = s_empty[wv];
+            while (m) {
+                const int k = __ffs(m) - 1;
+                m &= m - 1;
+                const int cc = c0 + wv * 32 + k, b = cc / ncl, rem = cc - b * ncl, ci = rem / g.ncx, cj = rem - ci * g.ncx;
+                fast_cell(pyr, g, cand, cand_count, err, b, ci, cj, g.min_th);
+                __syncthreads();   // the cell's shared memory is free again
+            }
+        }
     }
 }
 
@@ -1152,7 +1421,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
     G->nlevels = p.nlevels; G->width = width; G->height = height;
     G->ini_th = p.ini_th_fast; G->min_th = p.min_th_fast; G->blur_taps = p.blur_taps;
     long long off = 0;
-    int cells = 0, cand = 0, kept = 0, maxn = 0, tapoff = 0;
+    int cells = 0, cand = 0, kept = 0, maxn = 0, tapoff = 0, flagw = 0;
     if (taps) taps->clear();
     for (int l = 0; l < p.nlevels; l++) {
         LevelGeom &g = G->lv[l];
@@ -1186,6 +1455,10 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
         g.cand_off = cand;
         g.cand_cap = ((g.win_w - 6) * (g.win_h - 6)) / 4 + 64;
         cand += (g.cand_cap + 63) / 64 * 64;
+        // survivor lists of the streamed FAST path: every computed pixel can be one
+        g.flag_off = flagw;
+        g.flag_cap = (g.w - 2 * EDGE) * (g.h - 2 * EDGE);
+        flagw += (g.flag_cap + 63) / 64 * 64;
         g.kept_off = kept;
         g.kept_cap = std::max(g.quota + 3, 4 * g.nIni) + 1;
         kept += g.kept_cap;
@@ -1218,7 +1491,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
             }
         }
     }
-    G->total_cells = cells; G->cand_frame = cand; G->kept_frame = kept; G->pyr_frame = off; G->max_nodes = maxn;
+    G->total_cells = cells; G->flag_frame = flagw; G->cand_frame = cand; G->kept_frame = kept; G->pyr_frame = off; G->max_nodes = maxn;
     return ORB_OK;
 }
 
@@ -1230,6 +1503,7 @@ static size_t octree_smem_bytes(int maxn) {
 
 static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_wtab); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
+    cudaFree(ex->d_score); cudaFree(ex->d_flags); cudaFree(ex->d_found);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch); cudaFree(ex->d_stereo_out);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
@@ -1447,7 +1721,21 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     ex->cand_elems = B * (size_t)(G.cand_frame + 64 * params->nlevels);
     TRY_ALLOC(cudaMalloc(&ex->d_cand, ex->cand_elems * 4));
     TRY_ALLOC(cudaMalloc(&ex->d_node_of, ex->cand_elems * 2));
-    TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 2 * sizeof(uint32_t)));
+    TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 4 * sizeof(uint32_t)));
+    // Measured on B200, 288 frames of 1241x376 (profiles/r2_fast_streamed_launches.txt): the streamed path needs 0.76 G warp
+    // instructions against the per-cell kernel's 0.83 G, but its arc pass gathers 34 scattered bytes per survivor pair from
+    // L1/L2 instead of shared memory (0.98 ms at 18 % issue utilisation), 2.2 ms in all against 1.02 ms: it stays opt-in.
+    ex->fast_streamed = getenv("ORBGPU_FAST_STREAMED") != nullptr;
+    if (ex->fast_streamed && B * (size_t)params->max_width * params->max_height > ((size_t)4 << 20) && params->max_width <= 4000 &&
+        params->max_height <= 4000) {
+        // only handles that can see a large batch carry the streamed path's buffers
+        TRY_ALLOC(cudaMalloc(&ex->d_score, ex->pyr_bytes));
+        TRY_ALLOC(cudaMemsetAsync(ex->d_score, 0, ex->pyr_bytes, ex->stream));
+        ex->flag_elems = B * (size_t)(G.flag_frame + 64 * params->nlevels);
+        TRY_ALLOC(cudaMalloc(&ex->d_flags, ex->flag_elems * 4));
+        ex->found_bytes = B * ex->cells_cap;
+        TRY_ALLOC(cudaMalloc(&ex->d_found, ex->found_bytes));
+    }
     ex->kept_elems = B * kept_frame;
     TRY_ALLOC(cudaMalloc(&ex->d_kept, ex->kept_elems * sizeof(Kept)));
     ex->out_cap_elems = B * kept_frame;
@@ -1580,6 +1868,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
 
     uint32_t *d_cand_count = ex->d_counts;
     uint32_t *d_kept_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels;
+    uint32_t *d_flag_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels * 2;
 
     auto launch_pyr = [&](int l) {
         const LevelGeom &g = G.lv[l];
@@ -1600,6 +1889,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         }
         ex->launches++;
     };
+    const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
+    const bool streamed = !small_call && ex->d_score && (size_t)batch * G.flag_frame <= ex->flag_elems &&
+                          (size_t)batch * G.total_cells <= ex->found_bytes && G.ini_th != G.min_th;
     auto launch_fast = [&](int l, cudaStream_t s) {
         const LevelGeom &g = G.lv[l];
         FastLevel fl;
@@ -1607,9 +1899,25 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         fl.pitch = g.pitch; fl.maxBX = g.maxBX; fl.maxBY = g.maxBY; fl.wCell = g.wCell; fl.hCell = g.hCell;
         fl.cand_off = g.cand_off; fl.cand_cap = g.cand_cap; fl.cand_frame = G.cand_frame;
         fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
+        fl.w = g.w; fl.h = g.h; fl.ncx = g.ncx; fl.ncy = g.ncy; fl.cell_begin = g.cell_begin; fl.total_cells = G.total_cells;
+        fl.flag_off = g.flag_off; fl.flag_cap = g.flag_cap; fl.flag_frame = G.flag_frame;
         const size_t smem = fast_smem_layout(fl);
-        k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
-        ex->launches++;
+        if (!streamed) {
+            k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
+            ex->launches++;
+            return;
+        }
+        const int nwc = ((XOFF + g.w - EDGE - 1) >> 2) - ((XOFF + EDGE) >> 2) + 1, rows = g.h - 2 * EDGE;
+        k_fast_compass<<<dim3((nwc + FS_T - 1) / FS_T, (rows + FS_ROWS - 1) / FS_ROWS, batch), FS_T, 0, s>>>(
+            ex->d_pyr, ex->d_score, fl, ex->d_flags, d_flag_count);
+        // 5 % (level 0) to 40 % (level 7) of the pixels survive the compass test on textured frames
+        const int nb = std::max(1, std::min(512, g.flag_cap / (24 * FA_T)));
+        k_fast_arc<<<dim3(nb, batch), FA_T, 0, s>>>(ex->d_pyr, ex->d_score, fl, ex->d_flags, d_flag_count);
+        k_fast_nms<<<dim3(nb, batch), FA_T, 0, s>>>(ex->d_score, fl, ex->d_flags, d_flag_count, ex->d_cand, d_cand_count, ex->d_found, ex->d_err);
+        const int ncells = g.ncx * g.ncy * batch;
+        k_fast_retry<<<std::min((ncells + FAST_T - 1) / FAST_T, 148 * 16), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count,
+                                                                                             ex->d_found, ex->d_err, batch);
+        ex->launches += 4;
     };
     auto launch_blur = [&](int l, cudaStream_t s) {
         const LevelGeom &g = G.lv[l];
@@ -1622,9 +1930,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err, l0);
         ex->launches++;
     };
-    const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
     auto enqueue = [&]() -> int {   // everything of one extraction between the input copy and the output copy
-        ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
+        ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 4 * sizeof(uint32_t), st));
+        if (streamed) ORB_CUDA_TRY(cudaMemsetAsync(ex->d_found, 0, (size_t)batch * G.total_cells, st));
         ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
         if (ex->overlap && !ex->profiling) {
             // level l's FAST cells and blur depend only on level l: they go to two side streams behind an event per level and

@@ -310,3 +310,64 @@ def test_cvtcolor_chained_in_front_of_extraction(oracle, gpu_lib):
         assert n == len(rk)
         assert d_k[:n].cpu().numpy().tobytes() == rk.tobytes() and np.array_equal(d_d[:n].cpu().numpy(), rd)
     ex.close()
+
+
+def _edge_frames(w, h, seed):
+    rng = np.random.default_rng(seed)
+    flat = np.full((h, w), 77, np.uint8)
+    noise = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    soft = (128 + 20 * rng.standard_normal((h, w))).clip(0, 255).astype(np.uint8)
+    ramp = ((np.arange(w)[None, :] * 9 + np.arange(h)[:, None] * 11) % 256).astype(np.uint8)
+    half = synth_frame(w, h, seed + 1).copy()
+    half[:, w // 2:] = 90   # textured left half, flat right half: non-empty and empty cells side by side
+    return [flat, noise, soft, ramp, half]
+
+
+@pytest.mark.parametrize("w,h,nf,nb", [(752, 480, 1000, 12), (1241, 376, 2000, 10), (640, 480, 1500, 14)])
+def test_streamed_fast_path_large_batches(oracle, gpu_lib, monkeypatch, w, h, nf, nb):
+    """The opt-in streamed FAST kernels for batches above the latency-mode limit (compass stream, arc, NMS, retry of empty
+    cells) instead of one CTA per cell: same candidates per level and same final output as the reference, frame by frame."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    monkeypatch.setenv("ORBGPU_FAST_STREAMED", "1")
+    assert nb * w * h > (4 << 20)
+    frames = _edge_frames(w, h, 40) + [synth_frame(w, h, 100 + s) for s in range(nb - 5)]
+    frames = np.stack(frames)
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    out = ex.extract_batch(frames)
+    ref = oracle.RefExtractor(nf)
+    for b in range(nb):
+        rk, rd = ref.extract(frames[b])
+        for l in range(8):
+            a, c = ex.candidates(l, slot=b), ref.candidates(l)
+            assert len(a) == len(c), f"frame {b} level {l}: {len(a)} candidates vs {len(c)}"
+            assert np.array_equal(a, c), f"frame {b} level {l}: candidate lists differ"
+        gk, gd = out[b]
+        assert len(gk) == len(rk), (b, len(gk), len(rk))
+        assert gk.tobytes() == rk.tobytes(), b
+        assert np.array_equal(gd, rd), b
+    # a second call on the same handle (stale scores / flags of the first must not leak), frames in another order
+    perm = np.roll(np.arange(nb), 3)
+    out2 = ex.extract_batch(np.ascontiguousarray(frames[perm]))
+    for i, b in enumerate(perm):
+        assert out2[i][0].tobytes() == out[b][0].tobytes() and np.array_equal(out2[i][1], out[b][1]), (i, b)
+    ex.close()
+
+
+def test_streamed_fast_equals_cell_kernel_and_geometry_change(gpu_lib, monkeypatch):
+    """The streamed path against the per-cell kernel on the same handle geometry, then a smaller geometry on the same handle."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h, nb = 960, 540, 10
+    frames = np.stack([synth_frame(w, h, 300 + s) for s in range(nb)])
+    monkeypatch.setenv("ORBGPU_FAST_STREAMED", "1")
+    ex = ORBextractor(1500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    monkeypatch.delenv("ORBGPU_FAST_STREAMED")
+    ex_cells = ORBextractor(1500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    for ww, hh in ((w, h), (900, 500), (w, h)):
+        sub = np.ascontiguousarray(frames[:, :hh, :ww])
+        a, b = ex.extract_batch(sub), ex_cells.extract_batch(sub)
+        for i in range(nb):
+            for l in range(8):
+                assert np.array_equal(ex.candidates(l, slot=i), ex_cells.candidates(l, slot=i)), (ww, i, l)
+            assert a[i][0].tobytes() == b[i][0].tobytes() and np.array_equal(a[i][1], b[i][1]), (ww, i)
+    assert ex.launch_count > ex_cells.launch_count
+    ex.close(); ex_cells.close()
