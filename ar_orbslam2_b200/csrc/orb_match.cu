@@ -36,10 +36,18 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 // grid = (query blocks, database chunks).  Each CTA scans rows [chunk*rows_per_chunk, ...) in order for
 // its 256 queries and writes one partial top-2 per (chunk, query).
+//
+// KF = true: the rows are keyframes of `kf.rows` consecutive rows each (chunks start and end on keyframe boundaries).  The scan
+// keeps the top-2 of the CURRENT keyframe; at a keyframe's last row it counts the query for that keyframe if its best is
+// <= th_low and (float)best < ratio * (float)second (ref ORBmatcher.cc:228-231, second = 256 when the keyframe has one
+// row), one atomic per warp, and folds the keyframe's top-2 into the chunk's (same lexicographic order as one scan).
+struct KfParams { int rows, th_low; float ratio; int32_t *counts; };
+
+template <bool KF>
 __global__ void __launch_bounds__(T2_THREADS)
 k_hamming_top2(const uint8_t *__restrict__ queries, int nq, const uint8_t *__restrict__ db, long long ndb,
                long long rows_per_chunk, int32_t *__restrict__ pd1, int32_t *__restrict__ pd2,
-               int64_t *__restrict__ pi1, int64_t *__restrict__ pi2, long long idx_base) {
+               int64_t *__restrict__ pi1, int64_t *__restrict__ pi2, long long idx_base, const KfParams kf) {
     __shared__ __align__(16) uint4 tile[T2_STAGES][T2_TILE * 2];
     const int tid = threadIdx.x;
     const int q = blockIdx.x * T2_THREADS + tid;
@@ -53,6 +61,8 @@ k_hamming_top2(const uint8_t *__restrict__ queries, int nq, const uint8_t *__res
     }
     int d1 = 256, d2 = 256;
     long long i1 = -1, i2 = -1;
+    int k1 = 256, k2 = 256;                  // KF: top-2 inside the current keyframe
+    long long j1 = -1, j2 = -1, kf_end = KF ? r0 + kf.rows : 0;
     const long long nrows = r1 - r0;
     const int ntiles = nrows > 0 ? (int)((nrows + T2_TILE - 1) / T2_TILE) : 0;
     const uint4 *src = reinterpret_cast<const uint4 *>(db) + r0 * 2;
@@ -78,14 +88,43 @@ k_hamming_top2(const uint8_t *__restrict__ queries, int nq, const uint8_t *__res
         const uint4 *rows = tile[t % T2_STAGES];
         const int nr = (int)min((long long)T2_TILE, nrows - (long long)t * T2_TILE);
         const long long rbase = r0 + (long long)t * T2_TILE;
+        if (!KF) {
 #pragma unroll 4
-        for (int r = 0; r < nr; r++) {
-            const uint4 a = rows[2 * r], b = rows[2 * r + 1];   // broadcast: every lane reads the same row
-            const int d = __popc(qa[0] ^ a.x) + __popc(qa[1] ^ a.y) + __popc(qa[2] ^ a.z) + __popc(qa[3] ^ a.w) +
-                          __popc(qa[4] ^ b.x) + __popc(qa[5] ^ b.y) + __popc(qa[6] ^ b.z) + __popc(qa[7] ^ b.w);
-            if (d < d2) {   // strict '<': the first row seen wins ties, as the reference's sequential scan
-                if (d < d1) { d2 = d1; i2 = i1; d1 = d; i1 = rbase + r; }
-                else { d2 = d; i2 = rbase + r; }
+            for (int r = 0; r < nr; r++) {
+                const uint4 a = rows[2 * r], b = rows[2 * r + 1];   // broadcast: every lane reads the same row
+                const int d = __popc(qa[0] ^ a.x) + __popc(qa[1] ^ a.y) + __popc(qa[2] ^ a.z) + __popc(qa[3] ^ a.w) +
+                              __popc(qa[4] ^ b.x) + __popc(qa[5] ^ b.y) + __popc(qa[6] ^ b.z) + __popc(qa[7] ^ b.w);
+                if (d < d2) {   // strict '<': the first row seen wins ties, as the reference's sequential scan
+                    if (d < d1) { d2 = d1; i2 = i1; d1 = d; i1 = rbase + r; }
+                    else { d2 = d; i2 = rbase + r; }
+                }
+            }
+        } else {
+            int r = 0;
+            while (r < nr) {
+                const int seg = (int)min((long long)nr, kf_end - rbase);   // rows of this tile that belong to the current keyframe
+#pragma unroll 4
+                for (; r < seg; r++) {
+                    const uint4 a = rows[2 * r], b = rows[2 * r + 1];
+                    const int d = __popc(qa[0] ^ a.x) + __popc(qa[1] ^ a.y) + __popc(qa[2] ^ a.z) + __popc(qa[3] ^ a.w) +
+                                  __popc(qa[4] ^ b.x) + __popc(qa[5] ^ b.y) + __popc(qa[6] ^ b.z) + __popc(qa[7] ^ b.w);
+                    if (d < k2) {
+                        if (d < k1) { k2 = k1; j2 = j1; k1 = d; j1 = rbase + r; }
+                        else { k2 = d; j2 = rbase + r; }
+                    }
+                }
+                if (rbase + r == kf_end) {   // the keyframe is complete (uniform over the CTA)
+                    const bool ok = q < nq && j1 >= 0 && k1 <= kf.th_low && (float)k1 < kf.ratio * (float)k2;
+                    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                    if (bal && (tid & 31) == 0) atomicAdd(kf.counts + (kf_end / kf.rows - 1), __popc(bal));
+                    if (k1 < d2) {
+                        if (k1 < d1) { d2 = d1; i2 = i1; d1 = k1; i1 = j1; }
+                        else { d2 = k1; i2 = j1; }
+                    }
+                    if (j2 >= 0 && k2 < d2) { d2 = k2; i2 = j2; }   // k2 >= k1 >= d1 here: it can only be the second
+                    k1 = k2 = 256; j1 = j2 = -1;
+                    kf_end += kf.rows;
+                }
             }
         }
         __syncthreads();
@@ -163,7 +202,8 @@ struct Top2Scratch {
 
 // scans db[0..ndb) for nq queries on `st`; all pointers are device pointers
 static int top2_device(const uint8_t *d_q, int nq, const uint8_t *d_db, long long ndb, long long idx_base, int32_t *d_d1,
-                       int64_t *d_i1, int32_t *d_d2, int64_t *d_i2, cudaStream_t st, Top2Scratch *scratch) {
+                       int64_t *d_i1, int32_t *d_d2, int64_t *d_i2, cudaStream_t st, Top2Scratch *scratch,
+                       const KfParams *kf = nullptr) {
     int dev = 0, sms = 148;
     ORB_CUDA_TRY(cudaGetDevice(&dev));
     ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -172,7 +212,8 @@ static int top2_device(const uint8_t *d_q, int nq, const uint8_t *d_db, long lon
     long long chunks = std::max<long long>(1, (long long)sms * 8 / qblocks);
     chunks = std::min<long long>(chunks, std::max<long long>(1, (ndb + T2_TILE - 1) / T2_TILE));
     chunks = std::min<long long>(chunks, 65535);
-    const long long rows_per_chunk = (std::max<long long>(ndb, 1) + chunks - 1) / chunks;
+    long long rows_per_chunk = (std::max<long long>(ndb, 1) + chunks - 1) / chunks;
+    if (kf) rows_per_chunk = (rows_per_chunk + kf->rows - 1) / kf->rows * kf->rows;   // chunks hold whole keyframes
     chunks = std::max<long long>(1, (ndb + rows_per_chunk - 1) / rows_per_chunk);
     const size_t per = (size_t)chunks * nq;
     const size_t need = per * (4 + 4 + 8 + 8) + 1024;
@@ -184,8 +225,14 @@ static int top2_device(const uint8_t *d_q, int nq, const uint8_t *d_db, long lon
     }
     int64_t *pi1 = (int64_t *)scratch->buf, *pi2 = pi1 + per;
     int32_t *pd1 = (int32_t *)(pi2 + per), *pd2 = pd1 + per;
-    k_hamming_top2<<<dim3(qblocks, (unsigned)chunks), T2_THREADS, 0, st>>>(d_q, nq, d_db, ndb, rows_per_chunk, pd1, pd2, pi1, pi2,
-                                                                          idx_base);
+    if (kf) {
+        ORB_CUDA_TRY(cudaMemsetAsync(kf->counts, 0, (size_t)(ndb / kf->rows) * sizeof(int32_t), st));
+        k_hamming_top2<true><<<dim3(qblocks, (unsigned)chunks), T2_THREADS, 0, st>>>(d_q, nq, d_db, ndb, rows_per_chunk, pd1, pd2, pi1,
+                                                                                    pi2, idx_base, *kf);
+    } else {
+        k_hamming_top2<false><<<dim3(qblocks, (unsigned)chunks), T2_THREADS, 0, st>>>(d_q, nq, d_db, ndb, rows_per_chunk, pd1, pd2, pi1,
+                                                                                     pi2, idx_base, KfParams{});
+    }
     k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>((int)chunks, nq, pd1, pi1, pd2, pi2, d_d1, d_i1, d_d2, d_i2);
     ORB_CUDA_TRY(cudaGetLastError());
     return ORB_OK;
@@ -491,6 +538,47 @@ int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist,
     ORB_CUDA_TRY(cudaMemcpyAsync(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost, db->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    return ORB_OK;
+}
+
+int orb_db_query_keyframes(orb_db *db, const uint8_t *queries, int nq, int rows_per_keyframe, int th_low, float ratio,
+                           int32_t *best_dist, int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int32_t *kf_counts,
+                           int loc) {
+    ORB_REQUIRE(db && queries && nq >= 1 && best_dist && best_idx && second_dist && second_idx && kf_counts, ORB_ERR_INVALID, "bad argument");
+    const long long n = db->row_end - db->row_begin;
+    ORB_REQUIRE(rows_per_keyframe >= 1 && n % rows_per_keyframe == 0 && db->row_begin % rows_per_keyframe == 0, ORB_ERR_INVALID,
+                "the shard [%lld, %lld) must hold whole keyframes of %d rows", db->row_begin, db->row_end, rows_per_keyframe);
+    ORB_CUDA_TRY(cudaSetDevice(db->device));
+    const long long nkf = n / rows_per_keyframe;
+    KfParams kf{rows_per_keyframe, th_low, ratio, kf_counts};
+    if (loc == ORB_DEVICE) {
+        int rc = top2_device(queries, nq, db->d_rows, n, db->row_begin, best_dist, best_idx, second_dist, second_idx, db->stream,
+                             &db->scratch, &kf);
+        db->launches += 2;
+        return rc;
+    }
+    const size_t need = (size_t)nq * (32 + 24) + (size_t)nkf * 4 + 512;
+    if (db->io_bytes < need) {
+        if (db->d_io) cudaFree(db->d_io);
+        db->d_io = nullptr; db->io_bytes = 0;
+        ORB_CUDA_TRY(cudaMalloc(&db->d_io, need));
+        db->io_bytes = need;
+    }
+    int64_t *o_i1 = (int64_t *)db->d_io, *o_i2 = o_i1 + nq;
+    int32_t *o_d1 = (int32_t *)(o_i2 + nq), *o_d2 = o_d1 + nq;
+    uint8_t *dq = (uint8_t *)(o_d2 + nq);
+    dq = (uint8_t *)(((uintptr_t)dq + 15) & ~(uintptr_t)15);
+    kf.counts = (int32_t *)(((uintptr_t)(dq + (size_t)nq * 32) + 15) & ~(uintptr_t)15);
+    ORB_CUDA_TRY(cudaMemcpyAsync(dq, queries, (size_t)nq * 32, cudaMemcpyHostToDevice, db->stream));
+    int rc = top2_device(dq, nq, db->d_rows, n, db->row_begin, o_d1, o_i1, o_d2, o_i2, db->stream, &db->scratch, &kf);
+    db->launches += 2;
+    if (rc != ORB_OK) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_idx, o_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_idx, o_i2, (size_t)nq * 8, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(kf_counts, kf.counts, (size_t)nkf * 4, cudaMemcpyDeviceToHost, db->stream));
     ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
     return ORB_OK;
 }

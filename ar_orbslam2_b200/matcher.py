@@ -125,6 +125,25 @@ class DescriptorDB:
         vp = C.c_void_p
         _lib.check(self._L.orb_db_query(self._h, vp(d_q), nq, vp(d_d1), vp(d_i1), vp(d_d2), vp(d_i2), ORB_DEVICE), "orb_db_query")
 
+    def query_keyframes(self, queries: np.ndarray, rows_per_keyframe: int, th_low: int = 50, ratio: float = 0.75):
+        """Shard top-2 plus, per keyframe of the shard, the number of queries it matches (best <= th_low and
+        best < ratio * second inside the keyframe; ref ORBmatcher.cc:216-231).  Host arrays in, host arrays out."""
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+        nq = q.shape[0]
+        d1, d2 = np.zeros(nq, np.int32), np.zeros(nq, np.int32)
+        i1, i2 = np.zeros(nq, np.int64), np.zeros(nq, np.int64)
+        counts = np.zeros((self.row_end - self.row_begin) // rows_per_keyframe, np.int32)
+        _lib.check(self._L.orb_db_query_keyframes(self._h, ptr(q), nq, rows_per_keyframe, th_low, C.c_float(ratio), ptr(d1), ptr(i1),
+                                                  ptr(d2), ptr(i2), ptr(counts), ORB_HOST), "orb_db_query_keyframes")
+        return d1, i1, d2, i2, counts
+
+    def query_keyframes_device(self, d_q: int, nq: int, rows_per_keyframe: int, th_low: int, ratio: float, d_d1: int, d_i1: int,
+                               d_d2: int, d_i2: int, d_counts: int):
+        """Asynchronous on the shard's stream; raw device pointers."""
+        vp = C.c_void_p
+        _lib.check(self._L.orb_db_query_keyframes(self._h, vp(d_q), nq, rows_per_keyframe, th_low, C.c_float(ratio), vp(d_d1), vp(d_i1),
+                                                  vp(d_d2), vp(d_i2), vp(d_counts), ORB_DEVICE), "orb_db_query_keyframes")
+
     def merge_top2_device(self, nshards: int, nq: int, d_bd: int, d_bi: int, d_sd: int, d_si: int, o_bd: int, o_bi: int, o_sd: int, o_si: int):
         """[nshards, nq] partial lists (device pointers, shard order) -> single-scan result, on the shard's stream."""
         vp = C.c_void_p

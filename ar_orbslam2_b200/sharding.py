@@ -40,3 +40,24 @@ def sharded_top2(local, merge_fn, group=None):
     """all-gather + merge: every rank ends with the global top-2 (== one scan over the whole database)."""
     parts = allgather_top2(local, group)
     return merge_fn(*parts)
+
+
+def shard_keyframes(n_keyframes: int, rows_per_keyframe: int, rank: int, world: int) -> tuple[int, int]:
+    """Row range [begin, end) of the keyframe-range shard of `rank`: whole keyframes only (BASELINE config 5)."""
+    b, e = shard_range(n_keyframes, rank, world)
+    return b * rows_per_keyframe, e * rows_per_keyframe
+
+
+def allgather_keyframe_counts(local_counts, n_keyframes: int, group=None):
+    """Per-keyframe accepted-match counts are local to a shard: concatenation in rank order is the whole answer.
+    local_counts: int32 torch tensor of this rank's keyframes; shards may differ by one keyframe, so the gather is padded."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    sizes = [shard_range(n_keyframes, r, world) for r in range(world)]
+    width = max(e - b for b, e in sizes)
+    padded = torch.zeros(width, dtype=torch.int32, device=local_counts.device)
+    padded[: local_counts.numel()] = local_counts
+    gathered = torch.empty(world * width, dtype=torch.int32, device=local_counts.device)
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    return torch.cat([gathered[r * width: r * width + (e - b)] for r, (b, e) in enumerate(sizes)])

@@ -16,6 +16,7 @@ The oracle is used ONLY for the cpu_baseline leg and the reference arm.
 import argparse
 import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
@@ -32,10 +33,28 @@ MBF, FX = 386.1448, 718.856   # ref: ORB_SLAM2/Examples/Stereo/KITTI00-02.yaml:8
 STAGES = ["h2d", "pyramid", "fast_cells", "octree", "describe", "d2h"]
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376), from the committed ncu
-# launch list profiles/r1m_launches.csv (same command as this bench, serial schedule).  Scaled by frames when --batch differs.
-NCU_DRAM_BYTES_PER_288_FRAMES = {"pyramid": (134.4 + 117.3 + 447.6 + 167.9) * 1e6, "fast_cells": (391.8 + 2.7) * 1e6,
-                                 "octree": (15.8 + 10.6) * 1e6, "describe": (475.6 + 193.8 + 840.5 + 31.9) * 1e6}
+STAGE_KERNELS = {"pyramid": ("k_pyr_",), "fast_cells": ("k_fast_",), "octree": ("k_octree",), "describe": ("k_blur_", "k_describe"),
+                 "stereo_match": ("k_stereo_",)}
+
+
+def measured_stage_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376), read from the newest
+    committed ncu launch list of this same command (profiles/r*_launch_shares.csv, written by tools/ncu_launch_list.py from an
+    `ncu --metrics ...dram__bytes...` run of bench.py; regenerated whenever a kernel changes).  Returns ({stage: bytes}, file)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_launch_shares.csv")), key=os.path.getmtime)
+    files = sorted(files, key=lambda f: os.path.basename(f))   # r1e < r1m < r2a ...: the name carries the round and the revision
+    if not files:
+        return {}, None
+    out = {k: 0.0 for k in STAGE_KERNELS}
+    for ln in open(files[-1]):
+        f = ln.strip().split(",")
+        if len(f) < 7 or not f[0].startswith("k_"):
+            continue
+        for stage, prefixes in STAGE_KERNELS.items():
+            if f[0].startswith(prefixes):
+                out[stage] += (float(f[5]) + float(f[6])) * 1e6
+    return out, os.path.relpath(files[-1], ROOT)
 
 
 _JSON_FD = None
@@ -102,7 +121,8 @@ class SmiClockSampler:
                     reasons.add(name)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_min_mhz": float(min(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
 
 
 class ClockSampler:
@@ -158,7 +178,7 @@ class ClockSampler:
             mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
         except Exception:
             mx = max(self.sm)
-        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": mx, "reasons": sorted(n for b, n in names.items() if self.bits & b),
+        return {"sm_mhz": float(np.median(self.sm)), "sm_min_mhz": float(min(self.sm)), "sm_max_mhz": mx, "reasons": sorted(n for b, n in names.items() if self.bits & b),
                 "samples": len(self.sm), "source": "nvml, 2 ms period inside the timed region"}
 
 
@@ -234,7 +254,7 @@ def run_reference(args):
         "impl": "reference", "metric": "orb_stereo_extract_frames_per_s", "value": v, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": workload_config(sample_pairs),
+        "config": workload_config(args.batch),
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "reference_source": ref_src,
@@ -253,88 +273,232 @@ def workload_config(batch_pairs):
             "parallelism": "independent frames sharded one batch per GPU, no collective"}
 
 
-def bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier):
-    """Config C5 shape: brute-force top-2 of 2000 queries against a descriptor database sharded by row range, one shard of
-    `--db-rows` rows per GPU (weak scaling; > L2), local scan + all-gather of the partial top-2 + merge.  Gcompares/s is
-    the whole-job rate; the roofline is the measured POPC issue rate (8 popc32 per compare)."""
-    from ar_orbslam2_b200.matcher import DescriptorDB, measure_popc_rate
-    from ar_orbslam2_b200.synth import synth_queries
-    rows, nq, reps = args.db_rows, 2000, 5
-    db = DescriptorDB(rank * rows, (rank + 1) * rows, device=local)
-    db.fill_synthetic(7)
-    q_host = synth_queries(lambda idx: db.rows([rank * rows + int(i) % rows for i in idx]), rows, nq, 3)
-    q = torch.from_numpy(q_host).to(dev)
-    if world > 1:
-        dist.broadcast(q, 0)            # every rank searches the same queries
-    st = torch.cuda.ExternalStream(db.stream, device=dev)
-    loc = [torch.zeros(nq, dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
-    out = [torch.zeros(nq, dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
-    packed = torch.zeros((4, nq), dtype=torch.int64, device=dev)
-    gathered = torch.zeros((world, 4, nq), dtype=torch.int64, device=dev)
-    parts = [torch.zeros((world, nq), dtype=dt, device=dev) for dt in (torch.int32, torch.int64, torch.int32, torch.int64)]
+def golden_sweeps():
+    path = os.path.join(ROOT, "tests", "golden", "oracle_sweep_hashes.json")
+    return json.load(open(path)) if os.path.exists(path) else None
 
-    def one():
-        db.query_device(q.data_ptr(), nq, *[t.data_ptr() for t in loc])
+
+def host_copy_rate(torch, dev, host_t, dev_t, reps=3):
+    """GB/s of the same pinned-host -> device copy the end-to-end arms issue (the ceiling of an H2D-bound step)."""
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dev_t.copy_(host_t, non_blocking=True)
+    torch.cuda.synchronize()
+    s.record()
+    for _ in range(reps):
+        dev_t.copy_(host_t, non_blocking=True)
+    e.record()
+    e.synchronize()
+    return host_t.numel() * host_t.element_size() * reps / (s.elapsed_time(e) * 1e-3) / 1e9
+
+
+def bench_c5(args, torch, dist, dev, local, rank, world, reduce_max, barrier):
+    """Config C5 as BASELINE.json states it: brute-force top-2 of one frame's 2000 descriptors against a database of
+    `--db-keyframes` keyframes x 2000 descriptors (50 000 x 2000 = 100 M rows = 3.2 GB), sharded by keyframe range over the
+    ranks (STRONG scaling: the database is fixed, a rank holds K/N keyframes), local scan + NCCL all-gather of the partial
+    top-2 (48 KB/rank) and of the per-keyframe accepted-match counts (4 B x K/N per rank) + device merge.  Gcompares/s is the
+    whole-job rate; the roofline is the measured POPC issue rate (8 popc32 per compare).  N > 1: the merged result is compared
+    with a one-GPU scan of the whole database on rank 0 and the run FAILS on any difference.  The CPU leg
+    (__builtin_popcountll, all host cores) runs a 1/100 slice of the database and is extrapolated x100."""
+    from ar_orbslam2_b200.matcher import DescriptorDB, measure_popc_rate
+    from ar_orbslam2_b200.sharding import shard_keyframes, shard_range
+    from ar_orbslam2_b200.synth import synth_descriptors, synth_queries
+    K, KR, nq, reps, seed = args.db_keyframes, 2000, 2000, 3, 7
+    TH_LOW, RATIO = 50, 0.75
+    rb, re = shard_keyframes(K, KR, rank, world)
+    db = DescriptorDB(rb, re, device=local)
+    db.fill_synthetic(seed)
+    nkf_local = (re - rb) // KR
+    # queries: even rows are database rows (rank 0's shard) with 0..40 flipped bits, odd rows random
+    q_host = torch.zeros((nq, 32), dtype=torch.uint8).pin_memory()
+    if rank == 0:
+        n0 = re - rb
+        q_host.numpy()[:] = synth_queries(lambda idx: db.rows([int(i) % n0 for i in idx]), n0, nq, 3)
+    q = q_host.to(dev)
+    if world > 1:
+        dist.broadcast(q, 0)
+        q_host.copy_(q)
+    st = torch.cuda.ExternalStream(db.stream, device=dev)
+    i32, i64 = torch.int32, torch.int64
+    loc = [torch.zeros(nq, dtype=dt, device=dev) for dt in (i32, i64, i32, i64)]
+    out = [torch.zeros(nq, dtype=dt, device=dev) for dt in (i32, i64, i32, i64)]
+    cnt_local = torch.zeros(nkf_local, dtype=i32, device=dev)
+    width = max(e - b for b, e in (shard_range(K, r, world) for r in range(world)))
+    cnt_pad = torch.zeros(width, dtype=i32, device=dev)
+    cnt_all = torch.zeros(world * width, dtype=i32, device=dev)
+    packed = torch.zeros((4, nq), dtype=i64, device=dev)
+    gathered = torch.zeros((world, 4, nq), dtype=i64, device=dev)
+    parts = [torch.zeros((world, nq), dtype=dt, device=dev) for dt in (i32, i64, i32, i64)]
+    h_out = [torch.zeros(nq, dtype=dt).pin_memory() for dt in (i32, i64, i32, i64)]
+    h_cnt = torch.zeros(world * width, dtype=i32).pin_memory()
+
+    def one(q_dev):
+        db.query_keyframes_device(q_dev.data_ptr(), nq, KR, TH_LOW, RATIO, *[t.data_ptr() for t in loc], cnt_local.data_ptr())
         if world == 1:
             return
         with torch.cuda.stream(st):
-            packed[0].copy_(loc[0]); packed[1].copy_(loc[1]); packed[2].copy_(loc[2]); packed[3].copy_(loc[3])
+            for k in range(4):
+                packed[k].copy_(loc[k])
             dist.all_gather_into_tensor(gathered, packed)
             for k in range(4):
                 parts[k].copy_(gathered[:, k])   # preallocated: nothing is allocated on the library's stream
             db.merge_top2_device(world, nq, *[t.data_ptr() for t in parts], *[t.data_ptr() for t in out])
+            cnt_pad[:nkf_local].copy_(cnt_local)
+            dist.all_gather_into_tensor(cnt_all, cnt_pad)
 
     for _ in range(2):
-        one()
+        one(q)
     st.synchronize()
     l0 = db.launch_count
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     s.record(st)
     for _ in range(reps):
-        one()
+        one(q)
     e.record(st)
     e.synchronize()
     barrier()
     ms = reduce_max(s.elapsed_time(e))
+    launches = int(db.launch_count - l0)
     res = out if world > 1 else loc
-    planted_found = bool((res[0][0::2] <= 40).all().item())
+
+    def counts_now():
+        if world == 1:
+            return cnt_local.cpu().numpy()
+        a = cnt_all.cpu().numpy()
+        owned = [shard_range(K, rr, world) for rr in range(world)]
+        return np.concatenate([a[rr * width: rr * width + (ke - kb)] for rr, (kb, ke) in enumerate(owned)])
+
+    # end to end: the queries come from pinned host memory and the merged top-2 + all keyframe counts go back to it
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    q2 = torch.empty_like(q)
+    barrier()
+    with torch.cuda.stream(st):
+        s2.record(st)
+        for _ in range(reps):
+            q2.copy_(q_host, non_blocking=True)
+            one(q2)
+            for k in range(4):
+                h_out[k].copy_(res[k], non_blocking=True)
+            if world == 1:
+                h_cnt[:nkf_local].copy_(cnt_local, non_blocking=True)
+            else:
+                h_cnt.copy_(cnt_all, non_blocking=True)
+        e2.record(st)
+    e2.synchronize()
+    barrier()
+    ms_e2e = reduce_max(s2.elapsed_time(e2))
+    total_rows = K * KR
+    gcmp = total_rows * nq * reps / (ms * 1e-3) / 1e9
     popc = measure_popc_rate()
-    gcmp = world * rows * nq * reps / (ms * 1e-3) / 1e9
-    r = {"gcompares_per_s": gcmp, "queries": nq, "db_rows_per_gpu": rows, "db_bytes_per_gpu": rows * 32, "ms_per_query_batch": ms / reps,
-         "popc_peak_gpopc32_per_s_measured": popc, "frac_of_popc_peak": gcmp * 8 / (popc * world), "launches": int(db.launch_count - l0),
-         "exchange": "none" if world == 1 else "nccl all_gather of 64 KB/rank + device merge", "planted_queries_found": planted_found}
-    db.close()
-    return r
+    counts = counts_now()
+    r = {"workload": f"C5: {K} keyframes x {KR} descriptors = {total_rows} rows ({total_rows * 32 / 1e9:.2f} GB), {nq} queries, "
+                     f"sharded by keyframe range over {world} GPU(s)",
+         "scaling": "strong", "gcompares_per_s": gcmp, "queries": nq, "db_rows_total": total_rows, "db_rows_per_gpu": (re - rb),
+         "ms_per_query_batch": ms / reps,
+         "e2e": {"gcompares_per_s": total_rows * nq * reps / (ms_e2e * 1e-3) / 1e9, "ms_per_query_batch": ms_e2e / reps,
+                 "h2d_bytes_per_step": nq * 32, "d2h_bytes_per_step": nq * 24 + 4 * K},
+         "roofline": {"bound": "int/popc issue", "achieved": gcmp * 8 / world, "peak": popc, "unit": "Gpopc32/s per GPU",
+                      "frac": gcmp * 8 / (popc * world), "peak_source": "measured in this run (orb_measure_popc_rate)",
+                      "note": "HBM traffic is 32 B per row per 256 queries: 0.4 % of the HBM roofline, the scan is POPC-issue bound"},
+         "launches": launches,
+         "exchange": "none" if world == 1 else "nccl all_gather of 48 KB/rank (top-2) + 4 B x K/N per rank (keyframe counts) + device merge",
+         "planted_queries_found": bool((res[0][0::2] <= 40).all().item()),
+         "keyframe_counts": {"rule": "best <= 50 and best < 0.75 * second inside the keyframe (ORBmatcher.cc:216-231)",
+                             "keyframes_with_matches": int((counts > 0).sum()), "accepted_pairs": int(counts.sum()),
+                             "max_per_keyframe": int(counts.max(initial=0))}}
+    if world > 1 and rank == 0:   # the same rows on ONE GPU: the merged result must be identical
+        full = DescriptorDB(0, total_rows, device=local)
+        full.fill_synthetic(seed)
+        d1, i1, d2, i2, c1 = full.query_keyframes(q_host.numpy(), KR, TH_LOW, RATIO)
+        full.close()
+        same = (np.array_equal(d1, out[0].cpu().numpy()) and np.array_equal(i1, out[1].cpu().numpy()) and
+                np.array_equal(d2, out[2].cpu().numpy()) and np.array_equal(i2, out[3].cpu().numpy()) and np.array_equal(c1, counts))
+        r["merged_equals_one_gpu_scan"] = bool(same)
+        if not same:
+            raise SystemExit("bench.py: the sharded top-2 / keyframe counts differ from a one-GPU scan of the same database")
+    if rank == 0 and not args.skip_cpu:
+        # CPU leg on a 1/100 slice (whole keyframes), and the GPU against it on the same slice
+        from oracle import orbref
+        cores = os.cpu_count() or 1
+        ks = max(1, K // 100)
+        rows = synth_descriptors(ks * KR, seed)
+        qh = q_host.numpy()
+        t0 = time.perf_counter()
+        want = orbref.hamming_top2(qh, rows, fast=True, threads=cores)
+        t1 = time.perf_counter()
+        wc = orbref.db_keyframe_counts(qh, rows, KR, TH_LOW, RATIO, threads=cores)
+        t2 = time.perf_counter()
+        sl = DescriptorDB(0, ks * KR, device=local)
+        sl.fill_synthetic(seed)
+        got = sl.query_keyframes(qh, KR, TH_LOW, RATIO)
+        sl.close()
+        r["cpu_baseline"] = {"value": ks * KR * nq / (t1 - t0) / 1e9, "unit": "Gcompares/s", "cores": cores, "kind": "port",
+                             "sample": f"1/{K // ks} slice ({ks} keyframes = {ks * KR} rows) x {nq} queries, __builtin_popcountll top-2 scan; "
+                                       f"whole database extrapolated: {(t1 - t0) * K / ks:.1f} s per query batch",
+                             "keyframe_counts_gcompares_per_s": ks * KR * nq / (t2 - t1) / 1e9}
+        r["slice_equals_oracle"] = bool(all(np.array_equal(a, b) for a, b in zip(got[:4], want)) and np.array_equal(got[4], wc))
+        if not r["slice_equals_oracle"]:
+            raise SystemExit("bench.py: GPU top-2 / keyframe counts differ from the CPU oracle on the 1/100 slice")
+    _KEEP.append(db)   # its stream must outlive the pinned buffers that were copied on it (see the note in run_ours)
+    return r, popc
 
 
-def bench_batched(torch, dev, local, w, h, nfeat, nb, steps, label, seed0, with_stages=False):
-    """Device-resident batched extraction of nb frames of w x h, frames/s (configs C1 and C4)."""
+def bench_frames_leg(args, torch, dist, dev, local, rank, world, reduce_max, barrier, *, w, h, nfeat, total, chunk, steps,
+                     golden_key, label, stages=False, cpu_seconds=5.0):
+    """`total` independent frames of w x h, total / N per rank (config C4: 256 frames of 1920x1080; config C1: 640x480), no
+    collective.  Two arms: device-resident (one batched call per step) and end to end FROM HOST MEMORY (pinned frames ->
+    device in chunks of `chunk` frames on a copy stream while the previous chunk computes -> results back to pinned host
+    memory per chunk).  Every frame of the end-to-end arm is checked by SHA-256 against the oracle's hashes
+    (tests/golden/oracle_sweep_hashes.json); the CPU oracle runs a bounded sample on all host cores on rank 0."""
     from ar_orbslam2_b200 import _lib
     from ar_orbslam2_b200.extractor import ORBextractor
+    from ar_orbslam2_b200.hashing import frame_hash
     from ar_orbslam2_b200.synth import synth_frame
-    frames = np.stack([synth_frame(w, h, seed0 + i) for i in range(16)])
-    d_img = torch.from_numpy(np.ascontiguousarray(np.tile(frames, (nb // 16, 1, 1)))).to(dev)   # > L2 (126 MB)
+    gold = (golden_sweeps() or {}).get(golden_key)
+    nseeds = len(gold) if gold else 16
+    assert total % world == 0, "frames must divide over the ranks"
+    nb, b0 = total // world, rank * (total // world)
+    seeds = [(b0 + i) % nseeds for i in range(nb)]
+    distinct = {sd: synth_frame(w, h, sd) for sd in sorted(set(seeds))}
+    host = torch.empty((nb, h, w), dtype=torch.uint8).pin_memory()
+    hv = host.numpy()
+    for i, sd in enumerate(seeds):
+        hv[i] = distinct[sd]
     ex = ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb, device=local)
+    _KEEP.append(ex)
     cap = ex.default_capacity
     d_k = torch.zeros((nb, cap, 28), dtype=torch.uint8, device=dev)
     d_d = torch.zeros((nb, cap, 32), dtype=torch.uint8, device=dev)
     d_n = torch.zeros(nb, dtype=torch.int32, device=dev)
-    st = torch.cuda.ExternalStream(ex.stream, device=dev)
+    h_k, h_d, h_n = (torch.zeros(tuple(t.shape), dtype=t.dtype).pin_memory() for t in (d_k, d_d, d_n))
+    cs = torch.cuda.ExternalStream(ex.stream, device=dev)
+    d_img = host.to(dev)
     run = lambda: ex.extract_batch_device(d_img.data_ptr(), nb, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap, d_n.data_ptr())
     for _ in range(3):
         run()
     ex.check()
+    l0 = ex.launch_count
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record(st)
+    barrier()
+    s.record(cs)
     for _ in range(steps):
         run()
-    e.record(st)
+    e.record(cs)
     e.synchronize()
-    ms = s.elapsed_time(e)
-    r = {"frames_per_s": nb * steps / (ms * 1e-3), "workload": label, "ms_per_batch": ms / steps,
-         "keypoints_per_frame": float(d_n.sum().item()) / nb}
-    if with_stages:   # serial schedule with the library's stage events: where a batch of large frames spends its time
+    barrier()
+    ms = reduce_max(s.elapsed_time(e))
+    launches = int(ex.launch_count - l0)
+    n_kp = float(d_n.sum().item()) / nb
+    sizes = [ex.level_size(l) for l in range(8)]
+    S_px = sum(a * b for a, b in sizes)
+    alg_frame = w * h + 2 * S_px + 60 * n_kp            # SURVEY 8(d): P(1 + 2S) + 60 N
+    hbm_peak, peak_src = load_peaks()
+    r = {"workload": label, "frames_total": total, "frames_per_gpu": nb, "scaling": "strong" if world > 1 else "single GPU",
+         "frames_per_s": total * steps / (ms * 1e-3), "ms_per_batch": ms / steps, "keypoints_per_frame": n_kp, "launches": launches,
+         "roofline_step": {"bound": "hbm", "achieved": alg_frame * total * steps / (ms * 1e-3) / 1e9 / world, "peak": hbm_peak,
+                           "unit": "GB/s per GPU", "frac": alg_frame * total * steps / (ms * 1e-3) / 1e9 / world / hbm_peak,
+                           "algorithmic_bytes_per_frame": alg_frame, "formula": "P*(1+2S)+60N (SURVEY 8d)", "peak_source": peak_src}}
+    if stages and rank == 0:   # serial schedule with the library's stage events: where a batch of large frames spends its time
         L = _lib.lib()
         L.orb_extractor_set_profiling(ex._h, 1)
         for _ in range(steps):
@@ -345,19 +509,98 @@ def bench_batched(torch, dev, local, w, h, nfeat, nb, steps, label, seed0, with_
         L.orb_extractor_stage_times(ex._h, sm, C.byref(calls))
         L.orb_extractor_set_profiling(ex._h, 0)
         r["stage_ms_per_batch_serial"] = {STAGES[i]: sm[i] / max(calls.value, 1) for i in range(6)}
-    ex.close()
+    # ---- end to end from host memory, chunked
+    nch = (nb + chunk - 1) // chunk
+    sin, sout = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    d_in = [torch.empty((min(chunk, nb), h, w), dtype=torch.uint8, device=dev) for _ in range(2)]
+    ev = lambda n: [torch.cuda.Event() for _ in range(n)]
+    in_ready, in_free, out_ready, out_free = ev(2), ev(2), ev(nch), ev(nch)
+    used_in, used_out = [False, False], [False] * nch
+
+    def e2e_step():
+        for c in range(nch):
+            c0, c1, sl = c * chunk, min((c + 1) * chunk, nb), c % 2
+            if used_in[sl]:
+                sin.wait_event(in_free[sl])
+            with torch.cuda.stream(sin):
+                d_in[sl][: c1 - c0].copy_(host[c0:c1], non_blocking=True)
+                in_ready[sl].record(sin)
+            cs.wait_event(in_ready[sl])
+            if used_out[c]:
+                cs.wait_event(out_free[c])         # the previous step's results of this chunk have left the device arrays
+            ex.extract_batch_device(d_in[sl].data_ptr(), c1 - c0, w, h, w, w * h, d_k[c0:].data_ptr(), d_d[c0:].data_ptr(), cap,
+                                    d_n[c0:].data_ptr())
+            in_free[sl].record(cs)
+            out_ready[c].record(cs)
+            sout.wait_event(out_ready[c])
+            with torch.cuda.stream(sout):
+                h_k[c0:c1].copy_(d_k[c0:c1], non_blocking=True)
+                h_d[c0:c1].copy_(d_d[c0:c1], non_blocking=True)
+                h_n[c0:c1].copy_(d_n[c0:c1], non_blocking=True)
+                out_free[c].record(sout)
+            used_in[sl] = used_out[c] = True
+
+    e2e_step()
+    torch.cuda.synchronize()
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    s2.record(sin)
+    cs.wait_event(s2)
+    for _ in range(steps):
+        e2e_step()
+    sout.wait_stream(cs)
+    e2.record(sout)
+    e2.synchronize()
+    barrier()
+    ms_e2e = reduce_max(s2.elapsed_time(e2))
+    ex.check()
+    link = host_copy_rate(torch, dev, host, d_img)
+    d2h = sum(t.numel() * t.element_size() for t in (h_k, h_d, h_n))
+    r["e2e"] = {"frames_per_s": total * steps / (ms_e2e * 1e-3), "ms_per_batch": ms_e2e / steps, "h2d_bytes_per_step": host.numel(),
+                "d2h_bytes_per_step": d2h, "chunk_frames": chunk, "host_link_GBps": link,
+                "copy_only_frames_per_s": world * link * 1e9 / (w * h),
+                "pipeline": f"pinned host frames -> device in chunks of {chunk} on a copy stream while the previous chunk computes; "
+                            "results -> pinned host per chunk on a second copy stream"}
+    if gold:
+        n, K_, D_ = h_n.numpy(), h_k.numpy(), h_d.numpy()
+        bad = [i for i in range(nb) if int(n[i]) != gold[seeds[i]]["n"] or frame_hash(K_[i], D_[i], int(n[i])) != gold[seeds[i]]["sha256"]]
+        ok = torch.tensor([0 if bad else 1], device=dev)
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        r["all_frames_equal_oracle_sha256"] = bool(ok.item())
+        if bad:
+            raise SystemExit(f"bench.py: {golden_key} frames {bad[:8]} of rank {rank} differ from the oracle's hashes")
+    if rank == 0 and not args.skip_cpu:
+        from oracle import orbref
+        cores = os.cpu_count() or 1
+        frames = [distinct[sd] for sd in sorted(distinct)]
+        one = orbref.RefExtractor(nfeat)
+        t1 = []
+        for f in frames[:8]:
+            t0 = time.perf_counter(); one.extract(f); t1.append(time.perf_counter() - t0)
+        lock, done = threading.Lock(), [0]
+        t_end = time.perf_counter() + cpu_seconds
+
+        def worker(tid):
+            exr, i = orbref.RefExtractor(nfeat), tid
+            while time.perf_counter() < t_end:
+                exr.extract(frames[i % len(frames)])
+                i += cores
+                with lock:
+                    done[0] += 1
+
+        ths = [threading.Thread(target=worker, args=(t,)) for t in range(cores)]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t0
+        r["cpu_baseline"] = {"value": done[0] / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": f"{done[0]} extractions of the leg's frames in {dt:.1f} s, one RefExtractor per thread",
+                             "one_thread_ms_median": 1e3 * float(np.median(t1)),
+                             "one_thread_pattern": "per-frame wall time around the extractor call, median (Examples/Monocular/mono_tum.cc:79-88)"}
     return r
-
-
-def bench_c1(args, torch, dev, local):
-    """Config C1: monocular 640x480, nFeatures 1000 -- device-resident batched extraction, frames/s."""
-    return bench_batched(torch, dev, local, 640, 480, 1000, 512, 5, "640x480, 1000 features, batch 512 device-resident", 300)
-
-
-def bench_c4(args, torch, dev, local):
-    """Config C4: 256 independent 1920x1080 frames, 2000 features, one batch per GPU -- device-resident, frames/s."""
-    return bench_batched(torch, dev, local, 1920, 1080, 2000, 256, 3, "C4: 256 frames of 1920x1080, 2000 features, one batch, device-resident",
-                         500, with_stages=True)
 
 
 def bench_c3(args, popc_rate=None):
@@ -787,6 +1030,23 @@ def run_ours(args):
     launches = ex.launch_count - launches0
     ex.check()
     value = NF * args.steps * world / (ms * 1e-3)
+    # the same step for at least one second (more steps, not bigger ones): clocks settle, the sampler sees hundreds of samples
+    sustained = None
+    if ms < 1000.0:
+        n_sus = int(math.ceil(1100.0 / (ms / args.steps)))
+        sampler2 = ClockSampler(local)
+        if rank == 0:
+            sampler2.start()
+        barrier()
+        s.record(stream)
+        for _ in range(n_sus):
+            A.step_device(d_img)
+        e.record(stream)
+        e.synchronize()
+        barrier()
+        ms_sus = reduce_max(s.elapsed_time(e))
+        sustained = {"steps": n_sus, "timed_region_s": ms_sus * 1e-3, "value": NF * n_sus * world / (ms_sus * 1e-3), "unit": "frames/s",
+                     "ms_per_step": ms_sus / n_sus, "clocks": sampler2.stop() if rank == 0 else None}
     # per-stage device times: a separate, untimed pass with the library's stage events on.  Profiling serialises the
     # schedule (the timed pass above overlaps each level's FAST and blur with the rest of the resize cascade on side
     # streams), so the stage times add up to more than ms_per_step.
@@ -870,14 +1130,32 @@ def run_ours(args):
     # allocator records an event on every stream a pinned buffer was copied on when that buffer is freed, so the
     # library streams must outlive the buffers.
 
+    # the timed step's outputs by hash: every frame and every pair of the e2e arm's last results against the oracle
+    gold = golden_sweeps()
+    step_hash_ok = None
+    if gold and str(rank) in gold["bench"] and args.distinct <= 16:
+        from ar_orbslam2_b200.hashing import check_stereo_batch
+        step_hash_ok = True
+        for r in results:
+            bad = check_stereo_batch(gold["bench"][str(rank)][: args.distinct], r["n"].numpy(), r["kps"].numpy(), r["desc"].numpy(),
+                                     r["ur"].numpy(), r["dp"].numpy(), r["nm"].numpy())
+            if bad:
+                raise SystemExit(f"bench.py: rank {rank}: (pair, part) {bad[:6]} of the timed step differ from the oracle's SHA-256")
+
     extra = {}
+    popc = None
     if not os.environ.get("ORB_BENCH_SKIP_HAMMING"):
-        extra["hamming"] = bench_hamming(args, torch, dist, dev, local, rank, world, reduce_max, barrier)
+        extra["c5_hamming"], popc = bench_c5(args, torch, dist, dev, local, rank, world, reduce_max, barrier)
+    if not os.environ.get("ORB_BENCH_SKIP_C4"):
+        extra["c4_1080p"] = bench_frames_leg(args, torch, dist, dev, local, rank, world, reduce_max, barrier, w=1920, h=1080, nfeat=2000,
+                                             total=256, chunk=32, steps=3, golden_key="C4", stages=True,
+                                             label="C4: 256 independent frames of 1920x1080, 2000 features, 256/N per GPU")
     if rank == 0 and not os.environ.get("ORB_BENCH_SKIP_C1"):
-        extra["c1_mono"] = bench_c1(args, torch, dev, local)
-        extra["c4_1080p"] = bench_c4(args, torch, dev, local)
+        extra["c1_mono"] = bench_frames_leg(args, torch, None, dev, local, 0, 1, lambda v: v, torch.cuda.synchronize, w=640, h=480,
+                                            nfeat=1000, total=512, chunk=128, steps=5, golden_key="C1",
+                                            label="C1: 640x480, 1000 features (mono_tum ORBextractor), 512 frames per step on one GPU")
         extra["latency"] = bench_latency(args)
-        extra["c3_tracking"] = bench_c3(args, extra.get("hamming", {}).get("popc_peak_gpopc32_per_s_measured"))
+        extra["c3_tracking"] = bench_c3(args, popc)
         if not os.environ.get("ORB_BENCH_SKIP_BOW"):
             extra["bow_transform"] = bench_bow(args, torch, dev, local)
             extra["presteps"] = bench_presteps(args, torch, dev)
@@ -901,6 +1179,7 @@ def run_ours(args):
         "octree": 4 * 6 * kp_per_frame + 8 * kp_per_frame,
         "describe": 2 * S_px + 60 * kp_per_frame,   # blur: read the 8 levels, write the 8 blurred levels; then 60 B per keypoint
     }
+    traffic, traffic_file = measured_stage_traffic()
     kern = {k: per_call[STAGES.index(k)] for k in alg}
     dom = max(kern, key=kern.get)
     achieved = alg[dom] * NF / (kern[dom] * 1e-3) / 1e9
@@ -935,10 +1214,12 @@ def run_ours(args):
                                      "also holds the first upload (no compute to hide behind) and the last download"},
         "gpu_launches": int(launches),
         "clocks": clocks,
+        "sustained": sustained,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak,
-                     "traffic": NCU_DRAM_BYTES_PER_288_FRAMES.get(dom, 0) * NF / 288.0 or None,
-                     "traffic_source": "profiles/r1m_launches.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches)",
+                     "traffic": traffic.get(dom, 0) * NF / 288.0 or None,
+                     "traffic_source": f"{traffic_file}: ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches in one "
+                                       "288-frame step of this command, scaled by frames",
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom]},
         "roofline_step": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak,
@@ -947,6 +1228,7 @@ def run_ours(args):
                                   stereo_match=ms_serial / args.steps - sum(per_call)),
         "ms_per_step_serial_schedule": ms_serial / args.steps,
         "keypoints_per_frame": kp_per_frame, "stereo_matches_per_pair": n_matched / B,
+        "timed_step_outputs_equal_oracle_sha256": step_hash_ok,
         "extra": extra,
         "cpu_baseline": {"value": cpu_value, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{sample_pairs} synthetic stereo pairs x{reps} through the oracle, one pair per thread"},
@@ -959,7 +1241,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=400, help="timed steps (the default keeps the timed region above one second; a "
+                                                           "shorter run adds a `sustained` block of >= 1.1 s of the same steps)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=144, help="stereo pairs per step per GPU")
@@ -967,7 +1250,7 @@ def main():
     ap.add_argument("--lanes", type=int, default=2, help="e2e arm: steps in flight (each lane = one extractor handle + stream + buffers)")
     ap.add_argument("--distinct", type=int, default=16, help="distinct synthetic pairs tiled into the batch")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: skip the CPU baseline leg")
-    ap.add_argument("--db-rows", type=int, default=8_000_000, help="descriptor-database rows per GPU for the Hamming leg (256 MB)")
+    ap.add_argument("--db-keyframes", type=int, default=50_000, help="C5: keyframes of 2000 descriptors in the whole database (50 000 = 3.2 GB)")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON: anything libraries print there at the C level (NCCL's version banner under
     # torchrun, for one) goes to stderr instead.  The JSON line is written to the saved descriptor.

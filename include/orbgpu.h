@@ -422,6 +422,16 @@ int64_t orb_db_launch_count(const orb_db *db);
 int orb_db_query(orb_db *db, const uint8_t *queries, int nq, int32_t *best_dist,
                  int64_t *best_idx, int32_t *second_dist, int64_t *second_idx, int loc);
 
+/* The same scan over a shard made of keyframes of `rows_per_keyframe` consecutive rows (BASELINE config 5: 50 000 keyframes x
+ * 2000 descriptors; the shard must begin and end on keyframe boundaries).  Besides the shard's top-2 it returns, per
+ * keyframe of the shard, how many queries that keyframe matches by the reference's acceptance rule for a (query, keyframe)
+ * pair -- best distance inside the keyframe <= th_low and (float)best < ratio * (float)second, second = 256 with a single row
+ * (ref: src/ORBmatcher.cc:216-231, TH_LOW = 50, mfNNratio): the relocalisation candidate score.  kf_counts holds
+ * (row_end - row_begin) / rows_per_keyframe int32; counts are local to a shard, ranks concatenate them.   */
+int orb_db_query_keyframes(orb_db *db, const uint8_t *queries, int nq, int rows_per_keyframe, int th_low, float ratio,
+                           int32_t *best_dist, int64_t *best_idx, int32_t *second_dist, int64_t *second_idx,
+                           int32_t *kf_counts, int loc);
+
 /* Device-resident merge of [nshards][nq] partial lists (e.g. the result of an all-gather across ranks), asynchronous
  * on the shard's stream -- the exchange step of the sharded search.                                  */
 int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx,

@@ -57,6 +57,27 @@ struct KeyPoint {
         : pt(x, y), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
 };
 
+template <typename T> struct Point3_ { T x, y, z; Point3_() : x(0), y(0), z(0) {} Point3_(T a, T b, T c) : x(a), y(b), z(c) {} };
+typedef Point3_<float> Point3f;
+
+struct DMatch {   // features2d.hpp (OpenCV 2.4): Marker.cc:341 uses the 4-argument form (queryIdx, trainIdx, imgIdx, distance)
+    int queryIdx, trainIdx, imgIdx;
+    float distance;
+    DMatch() : queryIdx(-1), trainIdx(-1), imgIdx(-1), distance(3.402823466e+38f) {}
+    DMatch(int q, int t, float d) : queryIdx(q), trainIdx(t), imgIdx(-1), distance(d) {}
+    DMatch(int q, int t, int i, float d) : queryIdx(q), trainIdx(t), imgIdx(i), distance(d) {}
+};
+
+struct HammingLUT {   // features2d.hpp (OpenCV 2.4): number of differing bits of two byte strings (Marker.cc:353-356)
+    typedef unsigned char ValueType;
+    typedef int ResultType;
+    ResultType operator()(const unsigned char *a, const unsigned char *b, int size) const {
+        int r = 0;
+        for (int i = 0; i < size; i++) r += __builtin_popcount((unsigned)(a[i] ^ b[i]));
+        return r;
+    }
+};
+
 struct MatZeros { int rows, cols, type; };
 
 class Mat {

@@ -180,6 +180,16 @@ def hamming_top2(queries, db, idx_base=0, fast=False, threads=1):
     return d1, i1, d2, i2
 
 
+def db_keyframe_counts(queries, db, kf_rows, th_low=50, ratio=0.75, threads=1):
+    """Per keyframe (kf_rows consecutive rows of db): queries accepted by ORBmatcher.cc:216-231's rule inside that keyframe."""
+    q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+    d = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+    counts = np.zeros(len(d) // kf_rows, np.int32)
+    _check(lib().orbref_db_keyframe_counts(ptr(q), len(q), ptr(d), C.c_int64(len(d)), kf_rows, th_low, C.c_float(ratio), ptr(counts),
+                                           threads), "db_keyframe_counts")
+    return counts
+
+
 def rot_hist_filter(angle_a, angle_b):
     a = np.ascontiguousarray(angle_a, np.float32)
     b = np.ascontiguousarray(angle_b, np.float32)
@@ -630,13 +640,42 @@ def undistort_points(xy, fx, fy, cx, cy, dist):
 
 
 def search_matches_ratio(train, query, ratio=0.8, max_dist=50):
-    """Marker::searchMatches / naive_nn_search2 (restatement; parity unpinned, see orbref_mappoint.cpp)."""
+    """Marker::searchMatches / naive_nn_search2 (restatement; pinned to the reference's compiled Marker::searchMatches by
+    tests/test_reference_cpu.py::test_search_matches_ratio_equals_marker_cc through ref_marker_search_matches below)."""
     t = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
     q = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
     idx, dist = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
     _check(lib().orbref_search_matches_ratio(ptr(t), len(t), ptr(q), len(q), C.c_double(ratio), max_dist, ptr(idx), ptr(dist)),
            "search_matches_ratio")
     return idx, dist
+
+
+REF_MARKER_PATH = os.path.join(_HERE, "_ref", "libmarker_ref.so")
+_REFMK = None
+
+
+def ref_marker_available() -> bool:
+    if os.path.exists(REF_MARKER_PATH):
+        return True
+    if os.path.isdir("/root/reference/ORB_SLAM2/src"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-f", "Makefile.ref"])
+        return os.path.exists(REF_MARKER_PATH)
+    return False
+
+
+def ref_marker_search_matches(train, query):
+    """The reference's own Marker::searchMatches (src/Marker.cc:314-349, compiled by Makefile.ref into _ref/libmarker_ref.so):
+    DMatch list as (queryIdx, trainIdx, distance)."""
+    global _REFMK
+    if _REFMK is None:
+        _REFMK = C.CDLL(REF_MARKER_PATH)
+    t = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
+    q = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
+    cap = max(len(q), 1)
+    qi, ti, d = np.zeros(cap, np.int32), np.zeros(cap, np.int32), np.zeros(cap, np.float32)
+    n = C.c_int()
+    _check(_REFMK.refmk_search_matches(ptr(t), len(t), ptr(q), len(q), ptr(qi), ptr(ti), ptr(d), cap, C.byref(n)), "refmk_search_matches")
+    return qi[: n.value].copy(), ti[: n.value].copy(), d[: n.value].copy()
 
 
 # ---- Frame::isInFrustum: the restated oracle and the reference's compiled Frame.cc ----

@@ -58,6 +58,36 @@ int orbref_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64
     return ORB_OK;
 }
 
+// Relocalisation candidate score of a database made of keyframes of `kf_rows` consecutive rows: counts[k] = number of queries
+// whose best row inside keyframe k passes the reference's acceptance for a (query, keyframe) pair, ORBmatcher.cc:216-231:
+// bestDist1 <= TH_LOW and (float)bestDist1 < mfNNratio * (float)bestDist2, both initialised to 256, strict '<' updates.
+int orbref_db_keyframe_counts(const uint8_t *queries, int nq, const uint8_t *db, int64_t ndb, int kf_rows, int th_low, float ratio,
+                              int32_t *counts, int threads) {
+    if (kf_rows < 1 || ndb % kf_rows) return ORB_ERR_INVALID;
+    const int64_t nkf = ndb / kf_rows;
+    auto work = [&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; k++) {
+            int c = 0;
+            for (int q = 0; q < nq; q++) {
+                const uint8_t *dq = queries + (size_t)q * 32;
+                int bestDist1 = 256, bestDist2 = 256;
+                for (int64_t r = k * kf_rows; r < (k + 1) * kf_rows; r++) {
+                    const int dist = descriptor_distance_popcnt(dq, db + (size_t)r * 32);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; }
+                    else if (dist < bestDist2) { bestDist2 = dist; }
+                }
+                if (bestDist1 <= th_low && static_cast<float>(bestDist1) < ratio * static_cast<float>(bestDist2)) c++;
+            }
+            counts[k] = c;
+        }
+    };
+    if (threads <= 1) { work(0, nkf); return ORB_OK; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++) th.emplace_back(work, nkf * t / threads, nkf * (t + 1) / threads);
+    for (auto &t : th) t.join();
+    return ORB_OK;
+}
+
 // ref ORBmatcher::ComputeThreeMaxima, ORBmatcher.cc:1604-1645, on bin counts
 void orbref_three_maxima(const int *sizes, int L, int *ind1, int *ind2, int *ind3) {
     int max1 = 0, max2 = 0, max3 = 0;

@@ -32,3 +32,15 @@ def test_gpu_equals_oracle(seed, nt, nq):
     assert np.array_equal(qi, keep) and np.array_equal(ti, oi[keep]) and np.array_equal(d, od[keep].astype(np.float32))
     if nt >= 2:
         assert len(keep) > 0 or nq < 20
+
+
+@pytest.mark.parametrize("seed,nt,nq", [(10, 500, 2000), (11, 3, 100), (12, 1, 7)])
+def test_gpu_equals_reference_marker_cc(seed, nt, nq):
+    """liborbgpu directly against the reference's compiled Marker::searchMatches (oracle/_ref/libmarker_ref.so travels to the
+    GPU box as a prebuilt file)."""
+    if not orbref.ref_marker_available():
+        pytest.skip("oracle/_ref/libmarker_ref.so not built")
+    train, query = marker_case(seed, nt, nq)
+    qi, ti, d = searchMatches(train, query)
+    rq, rt, rd = orbref.ref_marker_search_matches(train, query)
+    assert np.array_equal(qi, rq) and np.array_equal(ti, rt) and np.array_equal(d, rd)

@@ -85,3 +85,28 @@ def test_popc_rate(gpu_lib):
     from ar_orbslam2_b200.matcher import measure_popc_rate
     r = measure_popc_rate()
     assert 500 < r < 50000, r
+
+
+@pytest.mark.parametrize("n_kf,kf_rows,nq", [(300, 173, 500), (12, 2000, 700), (1, 5, 3), (40, 256, 257)])
+def test_db_keyframe_counts(oracle, gpu_lib, n_kf, kf_rows, nq):
+    """orb_db_query_keyframes: per-keyframe accepted-match counts (ORBmatcher.cc:216-231 per (query, keyframe)) and the
+    shard top-2, against the oracle; keyframe boundaries fall inside the kernel's 256-row tiles."""
+    from ar_orbslam2_b200.matcher import DescriptorDB
+    n = n_kf * kf_rows
+    full = synth_descriptors(n, 5)
+    if kf_rows > 3:
+        o = kf_rows if n_kf > 1 else 0
+        full[o + 3] = full[o + 2]                                         # duplicate rows inside a keyframe
+    q = synth_queries(lambda idx: full[idx], n, nq, 8)
+    base = 7 * kf_rows                                                    # a shard that does not start at row 0
+    db = DescriptorDB(base, base + n)
+    db.upload(base, full)
+    d1, i1, d2, i2, counts = db.query_keyframes(q, kf_rows, 50, 0.75)
+    p1, pi1, p2, pi2 = db.query(q)
+    assert np.array_equal(d1, p1) and np.array_equal(i1, pi1) and np.array_equal(d2, p2) and np.array_equal(i2, pi2)
+    want = oracle.db_keyframe_counts(q, full, kf_rows, 50, 0.75, threads=8)
+    assert np.array_equal(counts, want), np.flatnonzero(counts != want)[:8]
+    assert counts.sum() >= nq // 2 - 2 or kf_rows < 10
+    with pytest.raises(Exception):
+        DescriptorDB(1, 1 + n).query_keyframes(q, kf_rows)               # shard not on a keyframe boundary
+    db.close()

@@ -143,3 +143,19 @@ def test_rotation_histogram_quirk(oracle):
     bins = {L.orbref_rot_bin(C.c_float(a), C.c_float(0.0)) for a in np.arange(0, 360, 0.25)}
     assert bins == set(range(13))
     assert L.orbref_rot_bin(C.c_float(10.0), C.c_float(350.0)) == 1   # -340 + 360 = 20 deg -> round(0.667) = 1
+
+
+def test_sweep_hashes_reproduce(oracle):
+    """tests/golden/oracle_sweep_hashes.json (the GPU box's yardstick for the seed sweeps) is what the oracle produces here:
+    a sample of every section is regenerated."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_sweeps", os.path.join(HERE, "..", "tools", "make_golden_sweeps.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    want = json.load(open(os.path.join(HERE, "golden", "oracle_sweep_hashes.json")))
+    assert len(want["C1"]) == 100 and len(want["C2"]) == 32 and len(want["C4"]) == 16 and len(want["bench"]) == 8
+    for s in (0, 41, 99):
+        assert mod.one_frame((640, 480, 1000, s)) == want["C1"][s]
+    assert mod.one_pair((1241, 376, 2000, 13)) == want["C2"][13]
+    assert mod.one_frame((1920, 1080, 2000, 7)) == want["C4"][7]
+    assert mod.one_pair((1241, 376, 2000, 17 + 3000 + 5)) == want["bench"]["3"][5]

@@ -63,3 +63,51 @@ def test_sharded_db_world2_gloo():
     q[5] = full[10]; full_dup = full.copy()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     mp.spawn(_worker, args=(2, port, n, nq, seed, q), nprocs=2, join=True)
+
+
+def _kf_case(n_kf, kf_rows, nq, seed):
+    full = synth_descriptors(n_kf * kf_rows, seed)
+    q = synth_queries(lambda idx: full[idx], n_kf * kf_rows, nq, seed + 1)
+    return full, q
+
+
+def test_keyframe_counts_oracle_against_numpy():
+    """orbref_db_keyframe_counts (ORBmatcher.cc:216-231's acceptance per (query, keyframe)) against a numpy restatement."""
+    from oracle import orbref
+    n_kf, kf_rows, nq = 23, 37, 90
+    full, q = _kf_case(n_kf, kf_rows, nq, 31)
+    full[5 * kf_rows + 3] = full[5 * kf_rows + 2]          # duplicate rows inside a keyframe: best == second -> rejected
+    q[1] = full[5 * kf_rows + 2]
+    got = orbref.db_keyframe_counts(q, full, kf_rows, 50, 0.75, threads=3)
+    bits = np.unpackbits(full, axis=1).astype(np.int32)
+    qb = np.unpackbits(q, axis=1).astype(np.int32)
+    dist = (qb[:, None, :] != bits[None, :, :]).sum(-1).reshape(nq, n_kf, kf_rows)
+    srt = np.sort(dist, axis=2)
+    ok = (srt[:, :, 0] <= 50) & (srt[:, :, 0].astype(np.float32) < np.float32(0.75) * srt[:, :, 1].astype(np.float32))
+    assert np.array_equal(got, ok.sum(0).astype(np.int32))
+    assert got.sum() >= nq // 2 - 2, "planted queries are counted"
+    assert orbref.db_keyframe_counts(q, full[:kf_rows], kf_rows)[0] == got[0]
+
+
+def _kf_worker(rank, world, port, n_kf, kf_rows, nq, seed, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from ar_orbslam2_b200.sharding import allgather_keyframe_counts, shard_keyframes
+    from oracle import orbref
+    b, e = shard_keyframes(n_kf, kf_rows, rank, world)
+    rows = synth_descriptors(e - b, seed, first_row=b)
+    local = torch.from_numpy(orbref.db_keyframe_counts(q, rows, kf_rows))
+    allc = allgather_keyframe_counts(local, n_kf).numpy()
+    want = orbref.db_keyframe_counts(q, synth_descriptors(n_kf * kf_rows, seed), kf_rows)
+    t = torch.tensor([1 if np.array_equal(allc, want) else 0])
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    assert t.item() == 1
+
+
+def test_keyframe_counts_world2_gloo():
+    """Keyframe-range shards of unequal size (7 keyframes over 2 ranks): concatenated counts == one pass over the database."""
+    n_kf, kf_rows, nq, seed = 7, 50, 40, 77
+    full, q = _kf_case(n_kf, kf_rows, nq, seed)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(_kf_worker, args=(2, port, n_kf, kf_rows, nq, seed, q), nprocs=2, join=True)
