@@ -11,6 +11,7 @@
 // steps use explicit round-to-nearest intrinsics so nothing is contracted into an FMA.
 #include "orb_common.cuh"
 #include "orb_internal.cuh"
+#include <nvtx3/nvToolsExt.h>   // header-only; the ranges cost a function-pointer test when no tool is attached
 #include "orb_pattern.h"
 
 #include <algorithm>
@@ -1495,6 +1496,11 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
     return ORB_OK;
 }
 
+struct NvtxRange {   // host-side range around the enqueue of one stage (ncu --nvtx / any NVTX consumer)
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
 static size_t octree_smem_bytes(int maxn) {
     int sort_n = 1;
     while (sort_n < maxn) sort_n <<= 1;
@@ -1840,6 +1846,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     size_t d_stride = frame_stride;
     int d_pitch = pitch;
     if (image_loc == ORB_HOST) {
+        NvtxRange nv("orbgpu:h2d");
         if (((size_t)pitch * height == frame_stride || batch == 1) && (size_t)pitch * height * batch <= ex->src_bytes) {
             // the frames as they lie in host memory, row pitch included, in ONE linear copy (k_pyr_level0 takes any pitch): a
             // pitched copy from pageable memory goes row by row through the driver (measured 182 us for one 1241x376 frame)
@@ -1871,6 +1878,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     uint32_t *d_flag_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels * 2;
 
     auto launch_pyr = [&](int l) {
+        NvtxRange nv("orbgpu:pyramid");
         const LevelGeom &g = G.lv[l];
         if (l == 0) {
             const int qL = (XOFF + 16) / 16, qR = std::max(qL, (g.w - 19 + XOFF) / 16 + 1);   // as in the kernel
@@ -1893,6 +1901,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     const bool streamed = !small_call && ex->d_score && (size_t)batch * G.flag_frame <= ex->flag_elems &&
                           (size_t)batch * G.total_cells <= ex->found_bytes && G.ini_th != G.min_th;
     auto launch_fast = [&](int l, cudaStream_t s) {
+        NvtxRange nv("orbgpu:fast_cells");
         const LevelGeom &g = G.lv[l];
         FastLevel fl;
         fl.level = l; fl.nlevels = G.nlevels; fl.ini_th = G.ini_th; fl.min_th = G.min_th;
@@ -1920,12 +1929,14 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->launches += 4;
     };
     auto launch_blur = [&](int l, cudaStream_t s) {
+        NvtxRange nv("orbgpu:blur");
         const LevelGeom &g = G.lv[l];
         dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, batch);
         k_blur_planes<<<grid, 128, 0, s>>>(ex->d_pyr, ex->d_blur, ex->d_geom, l);
         ex->launches++;
     };
     auto launch_octree = [&](int l0, int nl, cudaStream_t s) {
+        NvtxRange nv("orbgpu:octree");
         k_octree<<<dim3(nl, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), s>>>(
             ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err, l0);
         ex->launches++;
@@ -1972,6 +1983,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             prof_mark(ex, 4);
             for (int l = 0; l < G.nlevels; l++) launch_blur(l, st);
         }
+        NvtxRange nv("orbgpu:describe");
         DescParams dp;
         dp.nlevels = G.nlevels; dp.kept_frame = G.kept_frame; dp.pyr_frame = G.pyr_frame;
         for (int l = 0, acc = 0; l < ORB_MAX_LEVELS; l++) {
@@ -2034,6 +2046,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     ex->last_counts_valid = false;
 
     if (out_loc == ORB_HOST) {
+        NvtxRange nv("orbgpu:d2h");
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         // results: small ones (single frames, stereo pairs) land in the handle's pinned buffer with asynchronous copies and

@@ -35,3 +35,25 @@ kn, dn = a(noise)
 ramp = ((np.arange(w)[None, :] * 9 + np.arange(h)[:, None] * 11) % 256).astype(np.uint8)   # steep ramps: both-type compass survivors
 kq, dq = a(ramp)
 print("ok2", a.graph_replays, len(out[0]), len(kn), len(kq))
+# round 2: frame index built on the device, SearchByProjection(Cur, Last), BoW groups, keyframe-count scan, streamed FAST batch
+from ar_orbslam2_b200.matcher import DescriptorDB
+a(l)
+fd = Frame.from_extractor(a, 0, (0, w, 0, h))
+n0, m0 = ORBmatcher(0.9, True).SearchForInitialization(fd, f2, prev.copy(), 100)
+N = len(kl)
+n3, asg3 = ORBmatcher(0.9, True).SearchByProjectionLast(f2, np.ones(N, np.uint8), kl["x"] - 2, kl["y"] + 1, np.full(N, 0.2, np.float32),
+                                                        kl["octave"], kl["angle"], dl, 15.0, obs_positive=np.ones(N, np.uint8))
+g = 8   # 8 vocabulary groups: feature i of either frame falls in group i % 8
+ko = np.cumsum([0] + [len(range(k, len(kl), g)) for k in range(g)]).astype(np.int32)
+ki = np.concatenate([np.arange(k, len(kl), g) for k in range(g)]).astype(np.int32)
+fo = np.cumsum([0] + [len(range(k, len(kr), g)) for k in range(g)]).astype(np.int32)
+fi = np.concatenate([np.arange(k, len(kr), g) for k in range(g)]).astype(np.int32)
+n4, m4 = ORBmatcher(0.7, True).SearchByBoW(f1, f2, ko, ki, fo, fi, np.ones(len(kl), np.uint8))
+db = DescriptorDB(600, 600 + 4 * 300)
+db.upload(600, synth_descriptors(1200, 4))
+kfres = db.query_keyframes(synth_descriptors(70, 5), 300)
+db.close()
+os.environ["ORBGPU_FAST_STREAMED"] = "1"
+big = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=18)
+outs = big.extract_batch(np.stack([l, r, noise, ramp] * 4 + [l, r]))
+print("ok3", n0, n3, n4, int(kfres[4].sum()), sum(len(o[0]) for o in outs))
