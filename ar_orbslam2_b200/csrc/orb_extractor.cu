@@ -243,8 +243,7 @@ struct FastLevel {   // what k_fast_cells needs of one level, passed by value (c
     int pitch, maxBX, maxBY, wCell, hCell, cand_off, cand_cap, cand_frame;
     int off_vmap, off_flags, off_survH, off_survL;   // byte offsets into dynamic shared memory (16-aligned)
     long long interior_off, pyr_frame;
-    // the streamed path (k_fast_compass / k_fast_arc / k_fast_nms / k_fast_retry)
-    int w, h, ncx, ncy, cell_begin, total_cells, flag_off, flag_cap, flag_frame;
+    int w, h, ncx, ncy;   // level size and cell grid (k_fast_rows)
 };
 
 // magic[d] = floor((2^32 - 1) / d) + 1: n / d == umulhi(n, magic[d]) for the small n used here (d = 0, 1 unused)
@@ -281,8 +280,8 @@ static size_t fast_smem_layout(FastLevel &fl) {
 // always in [1, 511], so packed adds never carry between lanes.  Returns 256 + V per lane.  The sign is a run-time
 // multiplier (sgn = 1 or -1 as a 32-bit word: q * -1 + base is base - q in packed arithmetic as well), so brighter-
 // and darker-type pairs share one instruction stream and the multiplies go to the FMA pipe.
+template <int PB = FT_PB>
 __device__ __forceinline__ uint32_t fast_arc_pair(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn) {
-    constexpr int PB = FT_PB;
     const uint32_t cp = __byte_perm(p0[0], p1[0], 0x5410);
     const uint32_t base = 0x01000100u + cp * sgn, nsgn = 0u - sgn;
     const int off[16] = {3 * PB, 3 * PB + 1, 2 * PB + 2, PB + 3, 3, -PB + 3, -2 * PB + 2, -3 * PB + 1,
@@ -309,6 +308,7 @@ __device__ __noinline__ uint32_t fast_arc_pair_call(const uint8_t *p, const uint
 
 // One cell, start to finish, by the whole CTA; `thr0` is the threshold of the first pass (iniThFAST, or minThFAST when the
 // caller already knows the cell is empty at iniThFAST).
+template <int NT>
 __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const FastLevel &g, uint32_t *__restrict__ cand,
                                           uint32_t *__restrict__ cand_count, int *__restrict__ err, const int b, const int ci,
                                           const int cj, const int thr0) {
@@ -337,9 +337,9 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
     const int sft = (iniX + XOFF) & 15;   // plane rows are 128-byte aligned and interior column 0 sits at byte XOFF
     {
         const int nQ = (tw + sft + 15) >> 4;   // <= 5 chunks of 16 bytes per row
-        // thread -> (chunk q, row): 4 chunk slots per row (8 for the rare 5-chunk rows), rows FAST_T / slots apart
+        // thread -> (chunk q, row): 4 chunk slots per row (8 for the rare 5-chunk rows), rows NT / slots apart
         const int lg = nQ > 4 ? 3 : 2;
-        const int q = tid & ((1 << lg) - 1), ystep = FAST_T >> lg;
+        const int q = tid & ((1 << lg) - 1), ystep = NT >> lg;
         if (q < nQ) {
             int y = tid >> lg;
             const uint8_t *src = pyr + (size_t)b * g.pyr_frame + g.interior_off + (ptrdiff_t)(iniY + y) * g.pitch + (iniX - sft) + q * 16;
@@ -360,9 +360,9 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
 
     // words of a tile row that hold computed pixels: bytes [3 + sft, 3 + sft + cw)
     const int w0 = (3 + sft) >> 2, nWc = ((2 + sft + cw) >> 2) - w0 + 1;
-    // thread -> (word column w, row group rg): nRg = FAST_T / nWc row groups, the few threads beyond nRg * nWc idle in stage 2
+    // thread -> (word column w, row group rg): nRg = NT / nWc row groups, the few threads beyond nRg * nWc idle in stage 2
     const FastDiv dU(nWc);
-    const int nRg = dU.div(FAST_T);
+    const int nRg = dU.div(NT);
     const int rg0 = dU.div(tid), w = tid - rg0 * nWc + w0;
     const int rg = rg0 < nRg ? rg0 : ch;   // idle threads start past the last row
     uint32_t vm;                           // bytes of this column's words that are computed pixels: [lo, hi)
@@ -407,7 +407,7 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
         }
         __syncthreads();
         // ---- 2b. flagged words -> survivor lists, one word per thread (dense lanes; at compass time ~4 lanes of a warp hold one)
-        for (int t = tid, nW = s_nW; t < nW; t += FAST_T) {
+        for (int t = tid, nW = s_nW; t < nW; t += NT) {
             const uint32_t e = wlist[t];
             const int code0 = (int)(e & 0xffff);
             const uint32_t nH4 = (e >> 16) & 15u, nL4 = (e >> 20) & 15u, fB = nH4 & nL4, f1 = (nH4 | nL4) ^ fB, oL = nL4 & f1;
@@ -438,7 +438,7 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
         // one per thread.  Every pixel is on exactly one list, so every score byte has one writer.
         {
             const int nPH = (nH + 1) >> 1, nPP = nPH + ((nL + 1) >> 1);
-            for (int s = tid; s < nPP + nB; s += FAST_T) {
+            for (int s = tid; s < nPP + nB; s += NT) {
                 int c0, c1;
                 uint32_t sgn = 1u;
                 if (s < nPH) { const int i0 = 2 * s; c0 = surv[i0]; c1 = i0 + 1 < nH ? surv[i0 + 1] : c0; }
@@ -458,7 +458,7 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
         // window-relative coordinates (ref :789-790: ROI x + j*wCell).
         bool found = false;
         const int nS = nH + nL + nB;
-        for (int s0 = 0; s0 < nS; s0 += FAST_T) {
+        for (int s0 = 0; s0 < nS; s0 += NT) {
             const int s = s0 + tid;
             bool pass = false;
             int code = 0, V = 0;
@@ -500,265 +500,259 @@ __device__ __forceinline__ void fast_cell(const uint8_t *__restrict__ pyr, const
 __global__ void __launch_bounds__(FAST_T)
 k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
              int *__restrict__ err) {
-    fast_cell(pyr, g, cand, cand_count, err, blockIdx.z, blockIdx.y, blockIdx.x, g.ini_th);
+    fast_cell<FAST_T>(pyr, g, cand, cand_count, err, blockIdx.z, blockIdx.y, blockIdx.x, g.ini_th);
 }
 
 // ------------------------------------------------------------------------------------------
-// Streamed FAST for large batches: the same candidates as k_fast_cells (any order), without a shared-memory tile per cell.
-// The computed regions of a level's cells tile the window interior [EDGE, w - EDGE) x [EDGE, h - EDGE) without overlap, and
-// the compass test does not depend on the cell, so it runs over the whole plane as a stream:
-//   k_fast_compass  a thread owns one aligned word column (4 pixels) and walks FS_ROWS rows.  The rows y - 3 .. y + 3 of
-//                   its column stay unpacked in registers (each row is unpacked once and serves as "down", "centre" and
-//                   "up"); the words beside the column are loaded with their row and wait in registers as well.  Words
-//                   with survivors at iniThFAST go to the thread's private slots in shared memory; at the end the CTA
-//                   reserves one range in the level's brighter-type and darker-type survivor lists (two global atomics)
-//                   and writes the survivors' coordinates.  The same pass zeroes the frame's score plane.
-//   k_fast_arc      exact arc strength, a thread per PAIR of same-type survivors (16x2 lanes), written into the score plane.
-//   k_fast_nms      a thread per survivor: threshold + 3x3 non-max suppression; a neighbour counts only if it lies in the
-//                   same cell's computed region (ref :759-790: cv::FAST runs per cell ROI).  What passes goes to the
-//                   candidate list and marks its cell as non-empty.
-//   k_fast_retry    the cells that stayed empty run k_fast_cells' routine at minThFAST (ref :780-784); persistent CTAs
-//                   pick them out of the level's cell flags.
+// FAST for large batches: one CTA per (segment of a cell row, frame).  A segment is up to FR_COLS aligned word columns
+// (<= 512 pixels) of whole cells; its borders are cell borders, so the 3x3 suppression never looks outside the CTA's tile
+// (a neighbour outside the cell counts as 0, ref :759-790) and the cells only show up as column masks.  Same stages as
+// fast_cell, with the per-cell fixed costs paid once per segment and a 3-px halo around ~14 cells instead of around each:
+//   1. the tile (segment + halo) is staged as 16-byte chunks (cp.async);
+//   2. compass test at iniThFAST: a thread owns one word column of one half of the rows and walks down with the rows
+//      y - 3 .. y + 3 unpacked in registers (a row is unpacked once and serves as "down", "centre" and "up"; all shared
+//      memory offsets are immediates).  The words of a warp's row that hold survivors go to a dense list with one
+//      shared-memory atomic per warp and row (ballot + prefix);
+//   3. flagged words -> the two survivor lists, one word per thread on dense lanes;
+//   4. exact arc strength, one thread per pair of same-type survivors; 5. threshold + suppression per survivor, candidates
+//      appended with one global atomic per warp; 6. the columns of cells that stayed empty repeat 2-5 at minThFAST on the
+//      tile that is already staged.
+// A segment with more survivors than the lists hold (dense noise) runs its cells through fast_cell instead.
 // ------------------------------------------------------------------------------------------
-constexpr int FS_ROWS = 42;        // rows per thread of the compass pass
-constexpr int FS_T = 128;
+constexpr int FR_LOGC = 5;
+constexpr int FR_COLS = 1 << FR_LOGC;   // word columns of a segment
+constexpr int FR_T = 2 * FR_COLS;       // threads: FR_COLS word columns x 2 row halves
+constexpr int FR_TPW = FR_COLS + 8;     // tile pitch in words: the columns + one word either side + 16-byte alignment slack
+constexpr int FR_TPB = FR_TPW * 4;
+constexpr int FR_ROWS = 30;          // rows per thread (cells are < 60 px high)
 
-// survivor code: x | y << 12 (interior coordinates) | 1 << 31 (brighter-type list only: the pixel is of the darker type as
-// well).  One array per (frame, level), as long as the level has computed pixels: brighter-type codes grow from the bottom,
-// darker-type codes from the top; every survivor is on exactly one of the two.
-__global__ void __launch_bounds__(FS_T)
-k_fast_compass(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ score, const FastLevel g, uint32_t *__restrict__ surv,
-               uint32_t *__restrict__ surv_count) {
-    __shared__ uint32_t s_list[FS_ROWS * FS_T];   // flagged words, a private column of slots per thread: [slot][thread]
-    __shared__ int s_warp[FS_T / 32], s_base[2];
-    const int b = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
-    const int x_lo = EDGE, x_hi = g.w - EDGE;                       // computed columns (interior coordinates)
-    const int wfirst = (XOFF + x_lo) >> 2, wlast = (XOFF + x_hi - 1) >> 2;
-    const int wq = wfirst + blockIdx.x * FS_T + tid, w = min(wq, wlast);
-    const int ys = EDGE + blockIdx.y * FS_ROWS, nrows = min(FS_ROWS, g.h - EDGE - ys);
-    uint32_t vm = 0;                                                 // bytes of this word that are computed pixels
-    if (wq <= wlast) {
-        const int lo = XOFF + x_lo - 4 * w, hi = XOFF + x_hi - 4 * w;
+struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells; };   // byte offsets into dynamic shared memory
+
+__device__ __noinline__ uint32_t fast_arc_pair_rows_call(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn) {
+    return fast_arc_pair<FR_TPB>(p0, p1, sgn);
+}
+
+// (out of line: the per-cell routine inlined twice drove k_fast_rows to 101 registers)
+__device__ __noinline__ void fast_cell_rows_call(const uint8_t *pyr, const FastLevel &g, uint32_t *cand, uint32_t *cand_count, int *err,
+                                                 int b, int ci, int cj, int thr) {
+    fast_cell<FR_T>(pyr, g, cand, cand_count, err, b, ci, cj, thr);
+}
+
+__global__ void __launch_bounds__(FR_T, 12)
+k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLayout lay, uint32_t *__restrict__ cand,
+            uint32_t *__restrict__ cand_count, int *__restrict__ err) {
+    extern __shared__ __align__(16) unsigned char fsm[];
+    __shared__ int s_found[32], s_cnt, s_nW, s_over;
+    uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
+    uint32_t *scoreW = reinterpret_cast<uint32_t *>(fsm + lay.off_score);    // row r + 1 <-> computed row r, tile columns
+    // flagged words: type bits of the four pixels (brighter 0 / 8 / 16 / 24, darker 1 / 9 / 17 / 25) | row << 2 | column (low six
+    // bits << 10, bit 6 << 18); as many entries as the segment has words
+    uint32_t *wlist = reinterpret_cast<uint32_t *>(fsm + lay.off_slots);
+    uint16_t *list = reinterpret_cast<uint16_t *>(fsm + lay.off_list);       // x | row << 9 | both-type << 15; brighter up, darker down
+    const int b = blockIdx.z, ci = blockIdx.y, cj0 = blockIdx.x * lay.seg_cells, tid = threadIdx.x, lane = tid & 31;
+    const int ncell = min(lay.seg_cells, g.ncx - cj0);
+    const int y0 = EDGE + ci * g.hCell, hc = min(g.hCell, g.h - EDGE - y0);                    // computed rows [y0, y0 + hc)
+    const int xs = EDGE + cj0 * g.wCell, xe = min(xs + ncell * g.wCell, g.w - EDGE), rw = xe - xs;   // computed columns [xs, xe)
+    if (hc <= 0 || rw <= 0) return;
+    const int w0 = (XOFF + xs) >> 2, wl = (XOFF + xe - 1) >> 2, nW = wl - w0 + 1;              // plane words with computed pixels
+    const int cbase = (w0 - 1) & ~3;                                                            // tile word 0 <-> plane word cbase
+    const int lead = XOFF + xs - 4 * w0, xoff = 4 * (w0 - cbase);                               // list x = tile byte column - xoff
+    // ---- 1. stage tile rows y0 - 3 .. y0 + hc + 2, words cbase .. wl + 1: thread = (16-byte chunk of a row, row group)
+    {
+        const int nQ = ((wl + 1) >> 2) - (cbase >> 2) + 1;     // <= FR_COLS / 4 + 2 chunks per row
+        const int lg = nQ > 32 ? 6 : nQ > 16 ? 5 : 4, q = tid & ((1 << lg) - 1), rstep = FR_T >> lg;
+        if (q < nQ) {
+            int r = tid >> lg;
+            const uint8_t *src = pyr + (size_t)b * g.pyr_frame + g.interior_off - XOFF + (ptrdiff_t)(y0 - 3 + r) * g.pitch +
+                                 (size_t)cbase * 4 + q * 16;
+            uint32_t dst = (uint32_t)__cvta_generic_to_shared(tileW) + (uint32_t)(r * FR_TPB + q * 16);
+            const size_t sstep = (size_t)rstep * g.pitch;
+            for (; r < hc + 6; r += rstep, src += sstep, dst += rstep * FR_TPB)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+        }
+        asm volatile("cp.async.commit_group;");
+        for (int i = tid; i < 2 * FR_TPW; i += FR_T) scoreW[i < FR_TPW ? i : (hc + 1) * FR_TPW + i - FR_TPW] = 0;   // apron rows -1 and hc
+        if (tid < 32) s_found[tid] = 0;
+        if (tid == 0) { s_over = 0; s_cnt = 0; s_nW = 0; }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW);
+    uint8_t *score = reinterpret_cast<uint8_t *>(scoreW);
+    const FastDiv dW(g.wCell);
+
+    // thread = (word column, half of the rows); the rows of a warp are uniform (columns past the segment run masked)
+    const int col = tid & (FR_COLS - 1), half = (hc + 1) >> 1, r0 = (tid >> FR_LOGC) * half;
+    const int nrows = min(half, hc - r0);
+    const int tw = w0 + col - cbase;
+    uint32_t vm;                          // bytes of this thread's words that are computed pixels (of cells still to do)
+    {
+        const int lo = lead - 4 * col, hi = lo + rw;
         vm = (0x80808080u << (8 * max(lo, 0))) & (0x80808080u >> (8 * max(4 - hi, 0)));
+        if (col >= nW) vm = 0;
     }
-    const size_t pitch = (size_t)g.pitch;
-    const size_t o0 = (size_t)b * g.pyr_frame + g.interior_off - XOFF + (size_t)(ys - 3) * pitch + (size_t)w * 4;
-    const uint8_t *p = pyr + o0;                 // this thread's word in row y + 3 (the row that enters the window)
-    uint8_t *sp = score + o0 + 3 * pitch;        // ... and in row y of the score plane
-    const uint32_t tb = (uint32_t)g.ini_th * 0x00010001u + 0x80008000u;
-    // rows y - 3 .. y + 3 of the column, unpacked: lanes A = (px0, px2), B = (px1, px3); slot = (row - (ys - 3)) % 7.  The
-    // words beside the column are loaded with their row (one pointer, immediate offsets) and wait three rows in Pq / Nq.
-    uint32_t A[7], B[7], Pq[4], Nq[4];
-#pragma unroll
-    for (int i = 0; i < 6; i++, p += pitch) {
-        const uint32_t C = __ldg(reinterpret_cast<const uint32_t *>(p));
-        A[i] = __byte_perm(C, 0, 0x4240); B[i] = __byte_perm(C, 0, 0x4341);
-        if (i >= 3) {
-            Pq[i & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) - 1);
-            Nq[i & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) + 1);
-        }
-    }
-    int cnt = 0;
-#pragma unroll
-    for (int k = 0; k < FS_ROWS; k++, p += pitch, sp += pitch) {
-        if (k >= nrows) break;
-        const uint32_t Cn = __ldg(reinterpret_cast<const uint32_t *>(p));
-        Pq[(k + 6) & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) - 1);
-        Nq[(k + 6) & 3] = __ldg(reinterpret_cast<const uint32_t *>(p) + 1);
-        *reinterpret_cast<uint32_t *>(sp) = 0;
-        A[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4240); B[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4341);
-        const uint32_t P = Pq[(k + 3) & 3], N = Nq[(k + 3) & 3];
-        const uint32_t cA = A[(k + 3) % 7], cB = B[(k + 3) % 7], uA = A[k % 7], uB = B[k % 7], dA = A[(k + 6) % 7], dB = B[(k + 6) % 7];
-        // left = pixels x - 3, right = x + 3: (P1, P3) (P2, C0) and (C3, N1) (N0, N2); byte 1 of an unpacked word is zero
-        const uint32_t lA = __byte_perm(P, 0, 0x4341), lB = __byte_perm(P, cA, 0x5452);
-        const uint32_t rA = __byte_perm(cB, N, 0x1512), rB = __byte_perm(N, 0, 0x4240);
-        const uint32_t mA = __vmaxs2(__vmins2(uA, dA), __vmins2(lA, rA)), mB = __vmaxs2(__vmins2(uB, dB), __vmins2(lB, rB));
-        const uint32_t nA = __vmins2(__vmaxs2(uA, dA), __vmaxs2(lA, rA)), nB = __vmins2(__vmaxs2(uB, dB), __vmaxs2(lB, rB));
-        // lane bit 15 set <=> NOT a survivor (no carries between lanes: every lane stays in [0x7f01, 0x81fe])
-        const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
-        const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
-        const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
-        if (fH | fL) {   // brighter-type bits 0 / 8 / 16 / 24, darker-type bits 1 / 9 / 17 / 25, row in bits 2..7
-            s_list[cnt * FS_T + tid] = (fH >> 7) | (fL >> 6) | (uint32_t)(k << 2);
-            cnt++;
-        }
-    }
-    // ---- survivors of the CTA's flagged words -> the level's two lists: count, reserve one range per list, write
-    int nh = 0, nl = 0;
-    for (int i = 0; i < cnt; i++) {
-        const uint32_t e = s_list[i * FS_T + tid], hm = e & 0x01010101u, lm = (e >> 1) & 0x01010101u & ~hm;
-        nh += __popc(hm); nl += __popc(lm);
-    }
-    int v = nh | (nl << 16), incl = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += t;
-    }
-    if (lane == 31) s_warp[tid >> 5] = incl;
-    __syncthreads();
-    int before = 0, total = 0;
-#pragma unroll
-    for (int q = 0; q < FS_T / 32; q++) {
-        if (q < (tid >> 5)) before += s_warp[q];
-        total += s_warp[q];
-    }
-    if (total == 0) return;
-    uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
-    if (tid == 0) {
-        s_base[0] = (total & 0xffff) ? (int)atomicAdd(cnts, (uint32_t)(total & 0xffff)) : 0;
-        s_base[1] = (total >> 16) ? (int)atomicAdd(cnts + 1, (uint32_t)(total >> 16)) : 0;
-    }
-    __syncthreads();
-    const int ex = before + incl - v;
-    uint32_t *dst = surv + (size_t)b * g.flag_frame + g.flag_off;
-    int ph = s_base[0] + (ex & 0xffff), pl = g.flag_cap - 1 - (s_base[1] + (ex >> 16));
-    const uint32_t xy0 = (uint32_t)(4 * w - XOFF) | (uint32_t)ys << 12;
-    for (int i = 0; i < cnt; i++) {
-        const uint32_t e = s_list[i * FS_T + tid];
-        const uint32_t xy = xy0 + (((e >> 2) & 63u) << 12);
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const uint32_t f = (e >> (8 * j)) & 3u;
-            if (f & 1u) dst[ph++] = (xy + j) | (f >> 1) << 31;
-            else if (f) dst[pl--] = xy + j;
-        }
-    }
-}
+    const uint32_t slot_tag = ((uint32_t)(col & 63) << 10) | ((uint32_t)(col >> 6) << 18) | ((uint32_t)r0 << 2);
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int top = lay.list_cap - 1;
 
-// fast_arc_pair on the plane itself: the circle offsets depend on the level's pitch
-__device__ __forceinline__ uint32_t fast_arc_pair_g(const uint8_t *__restrict__ p0, const uint8_t *__restrict__ p1, const uint32_t sgn,
-                                                    const int PB) {
-    const uint32_t cp = __byte_perm(p0[0], p1[0], 0x5410);
-    const uint32_t base = 0x01000100u + cp * sgn, nsgn = 0u - sgn;
-    const int off[16] = {3 * PB, 3 * PB + 1, 2 * PB + 2, PB + 3, 3, -PB + 3, -2 * PB + 2, -3 * PB + 1,
-                         -3 * PB, -3 * PB - 1, -2 * PB - 2, -PB - 3, -3, PB - 3, 2 * PB - 2, 3 * PB - 1};
-    uint32_t e[16];
+    for (int thr = g.ini_th;;) {
+        // ---- 2. compass test at thr: the column walks down with the rows y - 3 .. y + 3 unpacked in registers; the flagged
+        // words of a warp's row go to the dense list with one shared-memory atomic (ballot + prefix)
+        if (nrows > 0 && __any_sync(0xffffffffu, vm != 0)) {
+            const uint32_t tb = (uint32_t)thr * 0x00010001u + 0x80008000u;
+            const uint32_t *tp = tileW + r0 * FR_TPW + tw;      // tile row t <-> image row y0 - 3 + t: computed row r looks at rows r .. r + 6
+            uint32_t *sp = scoreW + (r0 + 1) * FR_TPW + tw;
+            uint32_t A[7], B[7], Pq[4], Nq[4];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const uint32_t q = __byte_perm(__ldg(p0 + off[k]), __ldg(p1 + off[k]), 0x5410);
-        e[k] = q * nsgn + base;
-    }
-    uint32_t m3[16];
+            for (int i = 0; i < 6; i++) {
+                const uint32_t C = tp[i * FR_TPW];
+                A[i] = __byte_perm(C, 0, 0x4240); B[i] = __byte_perm(C, 0, 0x4341);
+                if (i >= 3) { Pq[i & 3] = tp[i * FR_TPW - 1]; Nq[i & 3] = tp[i * FR_TPW + 1]; }
+            }
 #pragma unroll
-    for (int k = 0; k < 16; k++) m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
-    uint32_t a = 0;
-#pragma unroll
-    for (int k = 0; k < 16; k += 2)
-        a = __vimax3_s16x2(a, __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]),
-                           __vimin3_s16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]));
-    return a;
-}
-__device__ __noinline__ uint32_t fast_arc_pair_g_call(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn, const int PB) {
-    return fast_arc_pair_g(p0, p1, sgn, PB);
-}
-
-constexpr int FA_T = 128;
-// one thread per pair of same-type survivors (the type is a run-time sign): dense warps whatever the flagged words look like
-__global__ void __launch_bounds__(FA_T)
-k_fast_arc(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ score, const FastLevel g, const uint32_t *__restrict__ surv,
-           const uint32_t *__restrict__ surv_count) {
-    const int b = blockIdx.y;
-    const uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
-    const int nH = (int)cnts[0], nL = (int)cnts[1], top = g.flag_cap - 1;
-    const int nPH = (nH + 1) >> 1, nPP = nPH + ((nL + 1) >> 1);
-    const uint32_t *src = surv + (size_t)b * g.flag_frame + g.flag_off;
-    const size_t plane = (size_t)b * g.pyr_frame + g.interior_off;
-    for (int s = blockIdx.x * FA_T + threadIdx.x; s < nPP; s += gridDim.x * FA_T) {
-        uint32_t c0, c1, sgn = 1u;
-        if (s < nPH) { const int i0 = 2 * s; c0 = src[i0]; c1 = i0 + 1 < nH ? src[i0 + 1] : c0; }
-        else { const int i0 = 2 * (s - nPH); sgn = 0xffffffffu; c0 = src[top - i0]; c1 = i0 + 1 < nL ? src[top - i0 - 1] : c0; }
-        const size_t o0 = plane + (size_t)((c0 >> 12) & 4095u) * g.pitch + (c0 & 4095u);
-        const size_t o1 = plane + (size_t)((c1 >> 12) & 4095u) * g.pitch + (c1 & 4095u);
-        uint32_t a = fast_arc_pair_g(pyr + o0, pyr + o1, sgn, g.pitch);
-        if ((c0 | c1) >> 31) {   // rare: brighter than one compass pair and darker than the other -> the larger of the two strengths
-            const uint32_t a2 = fast_arc_pair_g_call(pyr + o0, pyr + o1, 0xffffffffu, g.pitch);
-            const uint32_t keep = ((c0 >> 31) ? 0xffffu : 0u) | ((c1 >> 31) ? 0xffff0000u : 0u);
-            a = __vmaxs2(a, a2 & keep);
-        }
-        score[o0] = (uint8_t)max((int)(a & 0xffff) - 256, 0);
-        score[o1] = (uint8_t)max((int)(a >> 16) - 256, 0);
-    }
-}
-
-// one thread per survivor: threshold, 3x3 non-max suppression inside the survivor's cell, candidate list, cell flag
-__global__ void __launch_bounds__(FA_T)
-k_fast_nms(const uint8_t *__restrict__ score, const FastLevel g, const uint32_t *__restrict__ surv,
-           const uint32_t *__restrict__ surv_count, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
-           uint8_t *__restrict__ cell_found, int *__restrict__ err) {
-    const int b = blockIdx.y, lane = threadIdx.x & 31;
-    const uint32_t *cnts = surv_count + 2 * ((size_t)b * g.nlevels + g.level);
-    const int nH = (int)cnts[0], n = nH + (int)cnts[1], top = g.flag_cap - 1;
-    const uint32_t *src = surv + (size_t)b * g.flag_frame + g.flag_off;
-    const size_t plane = (size_t)b * g.pyr_frame + g.interior_off;
-    const FastDiv dW(g.wCell), dH(g.hCell);
-    const int PB = g.pitch, thr = g.ini_th;
-    const int stride = gridDim.x * FA_T, nIt = (n + stride - 1) / stride;
-    for (int it = 0; it < nIt; it++) {
-        const int s = it * stride + blockIdx.x * FA_T + threadIdx.x;
-        bool pass = false;
-        int x = 0, y = 0, V = 0;
-        if (s < n) {
-            const uint32_t c = s < nH ? src[s] : src[top - (s - nH)];
-            x = (int)(c & 4095u); y = (int)((c >> 12) & 4095u);
-            const uint8_t *v = score + plane + (size_t)y * PB + x;
-            V = v[0];
-            if (V > thr) {
-                const int ci = dH.div(y - EDGE), cj = dW.div(x - EDGE);
-                const int ly = y - EDGE - ci * g.hCell, lx = x - EDGE - cj * g.wCell;
-                const int chh = min(g.hCell, g.h - 2 * EDGE - ci * g.hCell), cww = min(g.wCell, g.w - 2 * EDGE - cj * g.wCell);
-                // a neighbour outside the cell's computed region counts as 0 (cv::FAST ran on the cell's ROI alone)
-                const int oL = lx > 0 ? -1 : 0, oR = lx < cww - 1 ? 1 : 0, oU = ly > 0 ? -PB : 0, oD = ly < chh - 1 ? PB : 0;
-                const int m = max(max(max(oL ? v[oL] : 0, oR ? v[oR] : 0), max(oU ? v[oU] : 0, oD ? v[oD] : 0)),
-                                  max(max(oL && oU ? v[oU + oL] : 0, oR && oU ? v[oU + oR] : 0),
-                                      max(oL && oD ? v[oD + oL] : 0, oR && oD ? v[oD + oR] : 0)));
-                pass = V > m;
-                if (pass) cell_found[(size_t)b * g.total_cells + g.cell_begin + ci * g.ncx + cj] = 1;
+            for (int k = 0; k < FR_ROWS; k++) {
+                if (k >= nrows) break;
+                const uint32_t Cn = tp[(k + 6) * FR_TPW];
+                Pq[(k + 6) & 3] = tp[(k + 6) * FR_TPW - 1];
+                Nq[(k + 6) & 3] = tp[(k + 6) * FR_TPW + 1];
+                A[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4240); B[(k + 6) % 7] = __byte_perm(Cn, 0, 0x4341);
+                const uint32_t P = Pq[(k + 3) & 3], N = Nq[(k + 3) & 3];
+                const uint32_t cA = A[(k + 3) % 7], cB = B[(k + 3) % 7], uA = A[k % 7], uB = B[k % 7], dA = A[(k + 6) % 7], dB = B[(k + 6) % 7];
+                // left = pixels x - 3, right = x + 3: (P1, P3) (P2, C0) and (C3, N1) (N0, N2); byte 1 of an unpacked word is zero
+                const uint32_t lA = __byte_perm(P, 0, 0x4341), lB = __byte_perm(P, cA, 0x5452);
+                const uint32_t rA = __byte_perm(cB, N, 0x1512), rB = __byte_perm(N, 0, 0x4240);
+                const uint32_t mA = __vmaxs2(__vmins2(uA, dA), __vmins2(lA, rA)), mB = __vmaxs2(__vmins2(uB, dB), __vmins2(lB, rB));
+                const uint32_t nA = __vmins2(__vmaxs2(uA, dA), __vmaxs2(lA, rA)), nB = __vmins2(__vmaxs2(uB, dB), __vmaxs2(lB, rB));
+                // lane bit 15 set <=> NOT a survivor (no carries between lanes: every lane stays in [0x7f01, 0x81fe])
+                const uint32_t xA = mA + tb - cA, xB = mB + tb - cB, yA = cA + tb - nA, yB = cB + tb - nB;
+                const uint32_t Hb = __byte_perm(xA, xB, 0x7351), Lb = __byte_perm(yA, yB, 0x7351);   // byte j <- pixel j
+                const uint32_t fH = ~Hb & vm, fL = ~Lb & vm;
+                if (vm) sp[k * FR_TPW] = 0;
+                const bool f = (fH | fL) != 0;
+                const unsigned bal = __ballot_sync(0xffffffffu, f);
+                if (bal) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&s_nW, __popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (f) wlist[base + __popc(bal & lt_mask)] = ((fH >> 7) | (fL >> 6)) + (slot_tag + 4u * k);
+                }
             }
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, pass);
-        if (bal == 0) continue;
-        int base = 0;
-        if (lane == 0) base = (int)atomicAdd(cand_count + (size_t)b * g.nlevels + g.level, (uint32_t)__popc(bal));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (pass) {
-            const int slot = base + __popc(bal & ((1u << lane) - 1u));
-            if (slot < g.cand_cap)
-                cand[(size_t)b * g.cand_frame + g.cand_off + slot] =
-                    (uint32_t)(x - (EDGE - 3)) | ((uint32_t)(y - (EDGE - 3)) << 12) | ((uint32_t)(V - 1) << 24);
-            else
-                atomicOr(err, ERRF_CAND_OVERFLOW);
-        }
-    }
-}
-
-__global__ void __launch_bounds__(FAST_T)
-k_fast_retry(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count,
-             const uint8_t *__restrict__ cell_found, int *__restrict__ err, const int batch) {
-    __shared__ unsigned s_empty[FAST_T / 32];
-    const int ncl = g.ncx * g.ncy, total = ncl * batch, tid = threadIdx.x;
-    for (int c0 = blockIdx.x * FAST_T; c0 < total; c0 += gridDim.x * FAST_T) {
-        const int c = c0 + tid;
-        bool empty = false;
-        if (c < total) {
-            const int b = c / ncl, rem = c - b * ncl;
-            empty = cell_found[(size_t)b * g.total_cells + g.cell_begin + rem] == 0;
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, empty);
-        __syncthreads();           // the previous round's masks have been read by everyone
-        if ((tid & 31) == 0) s_empty[tid >> 5] = bal;
         __syncthreads();
-        for (int wv = 0; wv < FAST_T / 32; wv++) {
-            unsigned m = s_empty[wv];
-            while (m) {
-                const int k = __ffs(m) - 1;
-                m &= m - 1;
-                const int cc = c0 + wv * 32 + k, b = cc / ncl, rem = cc - b * ncl, ci = rem / g.ncx, cj = rem - ci * g.ncx;
-                fast_cell(pyr, g, cand, cand_count, err, b, ci, cj, g.min_th);
-                __syncthreads();   // the cell's shared memory is free again
+        const int nFw = s_nW;
+        // ---- 3b. flagged words -> survivor lists on dense lanes.  A pixel of both types goes on the brighter-type list, bit 15 set.
+        {
+            for (int t = tid; t < nFw; t += FR_T) {
+                const uint32_t e = wlist[t], hm = e & 0x01010101u, lm = (e >> 1) & 0x01010101u, lo = lm & ~hm;
+                const int p = atomicAdd(&s_cnt, __popc(hm) + (__popc(lo) << 16));
+                int ph = p & 0xffff, pl = p >> 16;
+                if (ph + __popc(hm) + pl + __popc(lo) > lay.list_cap) { s_over = 1; continue; }   // (a bound: both counts only grow)
+                pl = top - pl;
+                const uint32_t code0 = (((e >> 10) & 63u) | ((e >> 12) & 64u)) * 4u | ((e >> 2) & 63u) << 9;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if ((hm >> (8 * j)) & 1u) list[ph++] = (uint16_t)(code0 + j + (((lm >> (8 * j)) & 1u) << 15));
+                    else if ((lm >> (8 * j)) & 1u) list[pl--] = (uint16_t)(code0 + j);
+                }
             }
         }
+        __syncthreads();
+        const int nH = s_cnt & 0xffff, nL = s_cnt >> 16;
+        if (s_over) {
+            // dense frame: more survivors than the lists hold -> the cells concerned one by one through the per-cell routine
+            for (int c = 0; c < ncell; c++) {
+                if (thr != g.ini_th && s_found[c]) continue;
+                __syncthreads();
+                fast_cell_rows_call(pyr, g, cand, cand_count, err, b, ci, cj0 + c, thr);
+            }
+            return;
+        }
+        // ---- 4. exact arc strength, a thread per pair of same-type survivors
+        {
+            const int nPH = (nH + 1) >> 1, nPP = nPH + ((nL + 1) >> 1);
+            for (int s = tid; s < nPP; s += FR_T) {
+                uint32_t c0, c1, sgn = 1u;
+                if (s < nPH) { const int i0 = 2 * s; c0 = list[i0]; c1 = i0 + 1 < nH ? list[i0 + 1] : c0; }
+                else { const int i0 = 2 * (s - nPH); sgn = 0xffffffffu; c0 = list[top - i0]; c1 = i0 + 1 < nL ? list[top - i0 - 1] : c0; }
+                const int o0 = (int)((c0 >> 9) & 63u) * FR_TPB + (int)(c0 & 511u) + xoff, o1 = (int)((c1 >> 9) & 63u) * FR_TPB + (int)(c1 & 511u) + xoff;
+                uint32_t a = fast_arc_pair<FR_TPB>(tile + 3 * FR_TPB + o0, tile + 3 * FR_TPB + o1, sgn);
+                if ((c0 | c1) >> 15) {   // rare: brighter than one compass pair and darker than the other -> the larger strength
+                    const uint32_t a2 = fast_arc_pair_rows_call(tile + 3 * FR_TPB + o0, tile + 3 * FR_TPB + o1, 0xffffffffu);
+                    a = __vmaxs2(a, a2 & (((c0 >> 15) ? 0xffffu : 0u) | ((c1 >> 15) ? 0xffff0000u : 0u)));
+                }
+                score[FR_TPB + o0] = (uint8_t)max((int)(a & 0xffff) - 256, 0);
+                score[FR_TPB + o1] = (uint8_t)max((int)(a >> 16) - 256, 0);
+            }
+        }
+        __syncthreads();
+        // ---- 5. threshold + 3x3 suppression inside the survivor's cell; candidates straight to the level's list
+        {
+            const int n = nH + nL;
+            for (int s0 = 0; s0 < n; s0 += FR_T) {
+                const int s = s0 + tid;
+                bool pass = false;
+                int px = 0, row = 0, V = 0;
+                if (s < n) {
+                    const uint32_t c = s < nH ? list[s] : list[top - (s - nH)];
+                    row = (int)((c >> 9) & 63u);
+                    const int xl = (int)(c & 511u);
+                    px = xl - lead;                                            // pixel offset inside the segment
+                    const uint8_t *v = score + (row + 1) * FR_TPB + xl + xoff;
+                    V = v[0];
+                    if (V > thr) {
+                        const int cjl = dW.div(px), lx = px - cjl * g.wCell, cww = min(g.wCell, rw - cjl * g.wCell);
+                        // the rows above / below the cell are the zero apron rows; columns of the neighbouring cells count as 0
+                        const int m = max(v[-FR_TPB], v[FR_TPB]);
+                        const int mL = lx > 0 ? max(max(v[-1], v[-FR_TPB - 1]), v[FR_TPB - 1]) : 0;
+                        const int mR = lx < cww - 1 ? max(max(v[1], v[-FR_TPB + 1]), v[FR_TPB + 1]) : 0;
+                        pass = V > max(m, max(mL, mR));
+                        if (pass) s_found[cjl] = 1;
+                    }
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, pass);
+                if (bal) {
+                    int base = 0;
+                    if (lane == 0) base = (int)atomicAdd(cand_count + (size_t)b * g.nlevels + g.level, (uint32_t)__popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (pass) {
+                        const int slot = base + __popc(bal & ((1u << lane) - 1u));
+                        if (slot < g.cand_cap)
+                            cand[(size_t)b * g.cand_frame + g.cand_off + slot] =
+                                (uint32_t)(xs + px - (EDGE - 3)) | ((uint32_t)(y0 + row - (EDGE - 3)) << 12) | ((uint32_t)(V - 1) << 24);
+                        else
+                            atomicOr(err, ERRF_CAND_OVERFLOW);
+                    }
+                }
+            }
+        }
+        // ---- 6. cells that stayed empty once more at the lower threshold (ref :780-784): the same stages on their columns only
+        if (thr == g.min_th) break;
+        __syncthreads();
+        {
+            uint32_t keep = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int px = 4 * col + j - lead;
+                if (((vm >> (8 * j + 7)) & 1u) && !s_found[dW.div(max(px, 0))]) keep |= 0x80u << (8 * j);
+            }
+            vm = keep;
+        }
+        if (!__syncthreads_or(vm != 0)) break;
+        if (tid == 0) { s_cnt = 0; s_nW = 0; }
+        thr = g.min_th;
+        __syncthreads();
     }
+}
+
+static size_t fast_rows_layout(const FastLevel &fl, FastRowsLayout &lay) {
+    lay.seg_cells = std::max(1, (4 * FR_COLS - 3) / fl.wCell);           // whole cells in <= 128 word columns at any alignment
+    auto up = [](size_t v) { return (v + 15) & ~(size_t)15; };
+    size_t off = up((size_t)(fl.hCell + 6) * FR_TPB);
+    lay.off_score = (int)off; off = up(off + (size_t)(fl.hCell + 2) * FR_TPB);
+    lay.off_slots = (int)off; off = up(off + (size_t)fl.hCell * FR_COLS * 4);   // flagged words: one per word of the segment at most
+    lay.list_cap = 2 * FR_COLS * fl.hCell;                               // half of the segment's pixels
+    lay.off_list = (int)off; off = up(off + (size_t)lay.list_cap * 2);
+    return off;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1422,7 +1416,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
     G->nlevels = p.nlevels; G->width = width; G->height = height;
     G->ini_th = p.ini_th_fast; G->min_th = p.min_th_fast; G->blur_taps = p.blur_taps;
     long long off = 0;
-    int cells = 0, cand = 0, kept = 0, maxn = 0, tapoff = 0, flagw = 0;
+    int cells = 0, cand = 0, kept = 0, maxn = 0, tapoff = 0;
     if (taps) taps->clear();
     for (int l = 0; l < p.nlevels; l++) {
         LevelGeom &g = G->lv[l];
@@ -1456,10 +1450,6 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
         g.cand_off = cand;
         g.cand_cap = ((g.win_w - 6) * (g.win_h - 6)) / 4 + 64;
         cand += (g.cand_cap + 63) / 64 * 64;
-        // survivor lists of the streamed FAST path: every computed pixel can be one
-        g.flag_off = flagw;
-        g.flag_cap = (g.w - 2 * EDGE) * (g.h - 2 * EDGE);
-        flagw += (g.flag_cap + 63) / 64 * 64;
         g.kept_off = kept;
         g.kept_cap = std::max(g.quota + 3, 4 * g.nIni) + 1;
         kept += g.kept_cap;
@@ -1492,7 +1482,7 @@ static int compute_geometry(const orb_extractor *ex, int width, int height, Geom
             }
         }
     }
-    G->total_cells = cells; G->flag_frame = flagw; G->cand_frame = cand; G->kept_frame = kept; G->pyr_frame = off; G->max_nodes = maxn;
+    G->total_cells = cells; G->cand_frame = cand; G->kept_frame = kept; G->pyr_frame = off; G->max_nodes = maxn;
     return ORB_OK;
 }
 
@@ -1509,7 +1499,6 @@ static size_t octree_smem_bytes(int maxn) {
 
 static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_geom); cudaFree(ex->d_taps); cudaFree(ex->d_wtab); cudaFree(ex->d_cells); cudaFree(ex->d_src); cudaFree(ex->d_pyr); cudaFree(ex->d_blur); cudaFree(ex->d_cand);
-    cudaFree(ex->d_score); cudaFree(ex->d_flags); cudaFree(ex->d_found);
     cudaFree(ex->d_node_of); cudaFree(ex->d_counts); cudaFree(ex->d_kept); cudaFree(ex->d_out_kp);
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch); cudaFree(ex->d_stereo_out);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
@@ -1727,20 +1716,18 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     ex->cand_elems = B * (size_t)(G.cand_frame + 64 * params->nlevels);
     TRY_ALLOC(cudaMalloc(&ex->d_cand, ex->cand_elems * 4));
     TRY_ALLOC(cudaMalloc(&ex->d_node_of, ex->cand_elems * 2));
-    TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 4 * sizeof(uint32_t)));
-    // Measured on B200, 288 frames of 1241x376 (profiles/r2_fast_streamed_launches.txt): the streamed path needs 0.76 G warp
-    // instructions against the per-cell kernel's 0.83 G, but its arc pass gathers 34 scattered bytes per survivor pair from
-    // L1/L2 instead of shared memory (0.98 ms at 18 % issue utilisation), 2.2 ms in all against 1.02 ms: it stays opt-in.
-    ex->fast_streamed = getenv("ORBGPU_FAST_STREAMED") != nullptr;
-    if (ex->fast_streamed && B * (size_t)params->max_width * params->max_height > ((size_t)4 << 20) && params->max_width <= 4000 &&
-        params->max_height <= 4000) {
-        // only handles that can see a large batch carry the streamed path's buffers
-        TRY_ALLOC(cudaMalloc(&ex->d_score, ex->pyr_bytes));
-        TRY_ALLOC(cudaMemsetAsync(ex->d_score, 0, ex->pyr_bytes, ex->stream));
-        ex->flag_elems = B * (size_t)(G.flag_frame + 64 * params->nlevels);
-        TRY_ALLOC(cudaMalloc(&ex->d_flags, ex->flag_elems * 4));
-        ex->found_bytes = B * ex->cells_cap;
-        TRY_ALLOC(cudaMalloc(&ex->d_found, ex->found_bytes));
+    TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 2 * sizeof(uint32_t)));
+    ex->fast_rows = getenv("ORBGPU_FAST_CELLS") == nullptr;   // large batches: one CTA per cell-row segment on the big levels
+    if (const char *e = getenv("ORBGPU_FAST_ROWS_MIN_PX")) ex->fast_rows_min_px = atoll(e);
+    {
+        static std::mutex mu_rows;
+        static bool rows_attr[64] = {};
+        std::lock_guard<std::mutex> lk(mu_rows);
+        if (!rows_attr[ex->device & 63]) {   // cells are < 60 px high: (65 + 61) * 544 + 30 * 512 + 59 * 512 bytes at most
+            TRY_ALLOC(cudaFuncSetAttribute(k_fast_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024));
+            TRY_ALLOC(cudaFuncSetAttribute(k_fast_rows, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            rows_attr[ex->device & 63] = true;
+        }
     }
     ex->kept_elems = B * kept_frame;
     TRY_ALLOC(cudaMalloc(&ex->d_kept, ex->kept_elems * sizeof(Kept)));
@@ -1875,7 +1862,6 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
 
     uint32_t *d_cand_count = ex->d_counts;
     uint32_t *d_kept_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels;
-    uint32_t *d_flag_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels * 2;
 
     auto launch_pyr = [&](int l) {
         NvtxRange nv("orbgpu:pyramid");
@@ -1898,8 +1884,10 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->launches++;
     };
     const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
-    const bool streamed = !small_call && ex->d_score && (size_t)batch * G.flag_frame <= ex->flag_elems &&
-                          (size_t)batch * G.total_cells <= ex->found_bytes && G.ini_th != G.min_th;
+    // Large batches: levels with many pixels go through k_fast_rows (one CTA per segment of a cell row: 26 % fewer warp
+    // instructions at level 0 of a 1241x376 frame, 236 us against 274 us per 288 frames); the small, corner-dense levels stay on
+    // the per-cell kernel, whose many 2-warp CTAs keep more warps in flight (profiles/r2_fast_cells_vs_rows.txt).
+    const bool rows_path = !small_call && ex->fast_rows;
     auto launch_fast = [&](int l, cudaStream_t s) {
         NvtxRange nv("orbgpu:fast_cells");
         const LevelGeom &g = G.lv[l];
@@ -1908,25 +1896,17 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         fl.pitch = g.pitch; fl.maxBX = g.maxBX; fl.maxBY = g.maxBY; fl.wCell = g.wCell; fl.hCell = g.hCell;
         fl.cand_off = g.cand_off; fl.cand_cap = g.cand_cap; fl.cand_frame = G.cand_frame;
         fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
-        fl.w = g.w; fl.h = g.h; fl.ncx = g.ncx; fl.ncy = g.ncy; fl.cell_begin = g.cell_begin; fl.total_cells = G.total_cells;
-        fl.flag_off = g.flag_off; fl.flag_cap = g.flag_cap; fl.flag_frame = G.flag_frame;
+        fl.w = g.w; fl.h = g.h; fl.ncx = g.ncx; fl.ncy = g.ncy;
         const size_t smem = fast_smem_layout(fl);
-        if (!streamed) {
+        if (rows_path && (long long)(g.w - 2 * EDGE) * (g.h - 2 * EDGE) >= ex->fast_rows_min_px) {
+            FastRowsLayout lay;
+            const size_t smem_rows = std::max(smem, fast_rows_layout(fl, lay));
+            k_fast_rows<<<dim3((g.ncx + lay.seg_cells - 1) / lay.seg_cells, g.ncy, batch), FR_T, smem_rows, s>>>(
+                ex->d_pyr, fl, lay, ex->d_cand, d_cand_count, ex->d_err);
+        } else {
             k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
-            ex->launches++;
-            return;
         }
-        const int nwc = ((XOFF + g.w - EDGE - 1) >> 2) - ((XOFF + EDGE) >> 2) + 1, rows = g.h - 2 * EDGE;
-        k_fast_compass<<<dim3((nwc + FS_T - 1) / FS_T, (rows + FS_ROWS - 1) / FS_ROWS, batch), FS_T, 0, s>>>(
-            ex->d_pyr, ex->d_score, fl, ex->d_flags, d_flag_count);
-        // 5 % (level 0) to 40 % (level 7) of the pixels survive the compass test on textured frames
-        const int nb = std::max(1, std::min(512, g.flag_cap / (24 * FA_T)));
-        k_fast_arc<<<dim3(nb, batch), FA_T, 0, s>>>(ex->d_pyr, ex->d_score, fl, ex->d_flags, d_flag_count);
-        k_fast_nms<<<dim3(nb, batch), FA_T, 0, s>>>(ex->d_score, fl, ex->d_flags, d_flag_count, ex->d_cand, d_cand_count, ex->d_found, ex->d_err);
-        const int ncells = g.ncx * g.ncy * batch;
-        k_fast_retry<<<std::min((ncells + FAST_T - 1) / FAST_T, 148 * 16), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count,
-                                                                                             ex->d_found, ex->d_err, batch);
-        ex->launches += 4;
+        ex->launches++;
     };
     auto launch_blur = [&](int l, cudaStream_t s) {
         NvtxRange nv("orbgpu:blur");
@@ -1942,8 +1922,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         ex->launches++;
     };
     auto enqueue = [&]() -> int {   // everything of one extraction between the input copy and the output copy
-        ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 4 * sizeof(uint32_t), st));
-        if (streamed) ORB_CUDA_TRY(cudaMemsetAsync(ex->d_found, 0, (size_t)batch * G.total_cells, st));
+        ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
         ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
         if (ex->overlap && !ex->profiling) {
             // level l's FAST cells and blur depend only on level l: they go to two side streams behind an event per level and

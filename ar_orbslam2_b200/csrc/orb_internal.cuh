@@ -34,7 +34,6 @@ struct LevelGeom {
     int ini_x[MAX_INI + 1];
     int win_w, win_h;            // maxBorder - minBorder
     int cand_off, cand_cap;      // into the per-frame candidate pool (elements)
-    int flag_off, flag_cap;      // into the per-frame survivor pool of the streamed FAST path (elements)
     int kept_off, kept_cap;      // into the per-frame kept pool
     float scale;                 // mvScaleFactor[level]
     float inv_scale;             // mvInvScaleFactor[level]
@@ -45,7 +44,6 @@ struct Geom {
     int nlevels, width, height;
     int total_cells;
     int cand_frame, kept_frame;          // pool elements per frame
-    int flag_frame;                      // survivor pool elements per frame (streamed FAST path)
     long long pyr_frame;                 // pyramid bytes per frame
     int max_nodes;                       // smem sizing for k_octree
     int ini_th, min_th, blur_taps;
@@ -80,10 +78,9 @@ struct orb_extractor {
     uint8_t *d_pyr = nullptr;  size_t pyr_bytes = 0;
     uint8_t *d_blur = nullptr;         // 7x7 Gaussian of every level (same plane layout as d_pyr)
     uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
-    uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept, then [B][nlevels][2] survivors (brighter, darker)
-    // streamed FAST path (large batches): score planes (same layout as d_pyr), survivor lists, per-cell "has a corner" bytes
-    uint8_t *d_score = nullptr; uint32_t *d_flags = nullptr; uint8_t *d_found = nullptr; size_t flag_elems = 0, found_bytes = 0;
-    bool fast_streamed = true;
+    uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
+    bool fast_rows = true;             // large batches: k_fast_rows on levels of at least fast_rows_min_px computed pixels
+    long long fast_rows_min_px = 200000;
     orbgpu::Kept *d_kept = nullptr; size_t kept_elems = 0;
     orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
     size_t out_cap_elems = 0;

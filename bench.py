@@ -964,6 +964,26 @@ class Pipe:
         self.out_free[k % self.NB].synchronize()
 
 
+def bind_near_gpu(torch, local):
+    """Pin this process to the cores next to its GPU (sysfs local_cpulist of the GPU's PCI function) BEFORE the pinned host
+    buffers are allocated, so first touch places them on the GPU's NUMA node.  Best effort; returns what was done."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        path = f"/sys/bus/pci/devices/{bdf}/local_cpulist"
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = (cpus & allowed) or allowed
+        os.sched_setaffinity(0, use)
+        node = open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip()
+        return {"pci": bdf, "numa_node": int(node), "cpus_bound": len(use), "cpus_allowed": len(allowed)}, allowed
+    except Exception as exc:
+        return {"unavailable": repr(exc)[:120]}, None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -979,6 +999,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
+    numa, affinity0 = bind_near_gpu(torch, local)
     B = args.batch                       # stereo pairs per step (per GPU: weak scaling)
     NF = 2 * B
     pairs = make_pairs(args.distinct, 17 + 1000 * rank)
@@ -1119,6 +1140,28 @@ def run_ours(args):
         results = [ln.h for ln in lanes]
         pipeline = f"{NL} extractor handles take turns; a handle is synchronised before reuse"
     ms_e2e = reduce_max(s2.elapsed_time(e2))
+    # copy-only leg: the end-to-end arm's transfers (frames in, results out, both directions at once) with no kernel in between:
+    # the rate the host link gives this rank while every other rank does the same -- the ceiling of a copy-bound e2e step
+    c_in, c_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    sc, ec, jc = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event()
+    h_res = results[0]
+    for _ in range(2):
+        A.d_in.copy_(host, non_blocking=True)
+    barrier()
+    sc.record(c_in)
+    c_out.wait_event(sc)
+    for _ in range(e2e_steps):
+        with torch.cuda.stream(c_in):
+            A.d_in.copy_(host, non_blocking=True)
+        with torch.cuda.stream(c_out):
+            for key in A.d:
+                h_res[key].copy_(A.d[key], non_blocking=True)
+    jc.record(c_out)
+    c_in.wait_event(jc)
+    ec.record(c_in)
+    ec.synchronize()
+    barrier()
+    ms_copy = reduce_max(sc.elapsed_time(ec))
     steady = None
     if args.e2e == "pipe" and e2e_steps > 2:
         steady = NF * world / (reduce_max(ss.elapsed_time(se)) / (e2e_steps - 2) * 1e-3)
@@ -1142,6 +1185,8 @@ def run_ours(args):
             if bad:
                 raise SystemExit(f"bench.py: rank {rank}: (pair, part) {bad[:6]} of the timed step differ from the oracle's SHA-256")
 
+    if affinity0:
+        os.sched_setaffinity(0, affinity0)   # the CPU baselines below use every core again
     extra = {}
     popc = None
     if not os.environ.get("ORB_BENCH_SKIP_HAMMING"):
@@ -1209,6 +1254,11 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps, "wall_s": wall_e2e, "steps": e2e_steps,
                 "pipeline": pipeline,
+                "copy_only_value": NF * e2e_steps * world / (ms_copy * 1e-3),
+                "host_link_GBps": (h2d + d2h) * e2e_steps / (ms_copy * 1e-3) / 1e9,
+                "host_link_note": "per rank, all ranks copying at once: this step's H2D + D2H bytes with no kernels, both directions "
+                                  "concurrently; e2e cannot exceed min(value, copy_only_value)",
+                "numa": numa,
                 "steady_state_value": steady,
                 "steady_state_note": "same run, compute-stream events after step 1 and after the last step: the timed region above "
                                      "also holds the first upload (no compute to hide behind) and the last download"},

@@ -323,12 +323,16 @@ def _edge_frames(w, h, seed):
     return [flat, noise, soft, ramp, half]
 
 
+@pytest.mark.parametrize("mode", ["hybrid", "rows"])
 @pytest.mark.parametrize("w,h,nf,nb", [(752, 480, 1000, 12), (1241, 376, 2000, 10), (640, 480, 1500, 14)])
-def test_streamed_fast_path_large_batches(oracle, gpu_lib, monkeypatch, w, h, nf, nb):
-    """The opt-in streamed FAST kernels for batches above the latency-mode limit (compass stream, arc, NMS, retry of empty
-    cells) instead of one CTA per cell: same candidates per level and same final output as the reference, frame by frame."""
+def test_large_batch_fast_paths(oracle, gpu_lib, monkeypatch, w, h, nf, nb, mode):
+    """Batches above the latency-mode limit run their large levels through k_fast_rows (one CTA per cell-row segment) and the
+    small ones through the per-cell kernel ("hybrid", the default); "rows" forces every level through k_fast_rows.  Same
+    candidates per level and same final output as the reference, frame by frame -- flat, dense-noise (list overflow -> per-cell
+    routine), soft-noise, both-type ramps and half-empty frames (in-tile retry at minThFAST) included."""
     from ar_orbslam2_b200.extractor import ORBextractor
-    monkeypatch.setenv("ORBGPU_FAST_STREAMED", "1")
+    if mode == "rows":
+        monkeypatch.setenv("ORBGPU_FAST_ROWS_MIN_PX", "0")
     assert nb * w * h > (4 << 20)
     frames = _edge_frames(w, h, 40) + [synth_frame(w, h, 100 + s) for s in range(nb - 5)]
     frames = np.stack(frames)
@@ -345,7 +349,7 @@ def test_streamed_fast_path_large_batches(oracle, gpu_lib, monkeypatch, w, h, nf
         assert len(gk) == len(rk), (b, len(gk), len(rk))
         assert gk.tobytes() == rk.tobytes(), b
         assert np.array_equal(gd, rd), b
-    # a second call on the same handle (stale scores / flags of the first must not leak), frames in another order
+    # a second call on the same handle, frames in another order
     perm = np.roll(np.arange(nb), 3)
     out2 = ex.extract_batch(np.ascontiguousarray(frames[perm]))
     for i, b in enumerate(perm):
@@ -353,21 +357,23 @@ def test_streamed_fast_path_large_batches(oracle, gpu_lib, monkeypatch, w, h, nf
     ex.close()
 
 
-def test_streamed_fast_equals_cell_kernel_and_geometry_change(gpu_lib, monkeypatch):
-    """The streamed path against the per-cell kernel on the same handle geometry, then a smaller geometry on the same handle."""
+def test_large_batch_fast_equals_cell_kernel_and_geometry_change(gpu_lib, monkeypatch):
+    """k_fast_rows on every level against the per-cell kernel on the same handle geometry, then a smaller geometry on the same
+    handle; 25-px-high last cell rows and segments that end inside a word included."""
     from ar_orbslam2_b200.extractor import ORBextractor
     w, h, nb = 960, 540, 10
     frames = np.stack([synth_frame(w, h, 300 + s) for s in range(nb)])
-    monkeypatch.setenv("ORBGPU_FAST_STREAMED", "1")
+    monkeypatch.setenv("ORBGPU_FAST_ROWS_MIN_PX", "0")
     ex = ORBextractor(1500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
-    monkeypatch.delenv("ORBGPU_FAST_STREAMED")
+    monkeypatch.delenv("ORBGPU_FAST_ROWS_MIN_PX")
+    monkeypatch.setenv("ORBGPU_FAST_CELLS", "1")
     ex_cells = ORBextractor(1500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
-    for ww, hh in ((w, h), (900, 500), (w, h)):
+    monkeypatch.delenv("ORBGPU_FAST_CELLS")
+    for ww, hh in ((w, h), (900, 500), (933, 517), (w, h)):
         sub = np.ascontiguousarray(frames[:, :hh, :ww])
         a, b = ex.extract_batch(sub), ex_cells.extract_batch(sub)
         for i in range(nb):
             for l in range(8):
                 assert np.array_equal(ex.candidates(l, slot=i), ex_cells.candidates(l, slot=i)), (ww, i, l)
             assert a[i][0].tobytes() == b[i][0].tobytes() and np.array_equal(a[i][1], b[i][1]), (ww, i)
-    assert ex.launch_count > ex_cells.launch_count
     ex.close(); ex_cells.close()

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
-"""Stage times of one large batch (serial schedule, the library's stage events), per-cell FAST kernel vs the streamed FAST
-path, plus the overlapped whole-step time of each.  usage: python tools/fast_ab.py [width height nfeatures batch]"""
+"""Stage times of one large batch (serial schedule, the library's stage events), per-cell FAST kernel vs k_fast_rows on every level vs
+the default hybrid, plus the overlapped whole-step time of each.  usage: python tools/fast_ab.py [width height nfeatures batch]"""
 import ctypes as C
 import os
 import sys
@@ -18,11 +18,13 @@ L = _lib.lib()
 frames = np.stack([synth_frame(w, h, s % 16) for s in range(nb)])
 d = torch.from_numpy(frames).cuda()
 names = ["h2d", "pyramid", "fast", "octree", "blur+describe", "d2h"]
-for mode in os.environ.get("FAST_AB_MODES", "cells,streamed").split(","):
-    if mode == "streamed":
-        os.environ["ORBGPU_FAST_STREAMED"] = "1"
-    else:
-        os.environ.pop("ORBGPU_FAST_STREAMED", None)
+for mode in os.environ.get("FAST_AB_MODES", "cells,rows,hybrid").split(","):
+    os.environ.pop("ORBGPU_FAST_ROWS_MIN_PX", None)
+    os.environ.pop("ORBGPU_FAST_CELLS", None)
+    if mode == "rows":
+        os.environ["ORBGPU_FAST_ROWS_MIN_PX"] = "0"
+    elif mode == "cells":
+        os.environ["ORBGPU_FAST_CELLS"] = "1"
     ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
     cap = nf + 200
     kp = torch.empty(nb * cap * 28, dtype=torch.uint8, device="cuda")

@@ -35,7 +35,7 @@ kn, dn = a(noise)
 ramp = ((np.arange(w)[None, :] * 9 + np.arange(h)[:, None] * 11) % 256).astype(np.uint8)   # steep ramps: both-type compass survivors
 kq, dq = a(ramp)
 print("ok2", a.graph_replays, len(out[0]), len(kn), len(kq))
-# round 2: frame index built on the device, SearchByProjection(Cur, Last), BoW groups, keyframe-count scan, streamed FAST batch
+# round 2: frame index built on the device, SearchByProjection(Cur, Last), BoW groups, keyframe-count scan, k_fast_rows batch
 from ar_orbslam2_b200.matcher import DescriptorDB
 a(l)
 fd = Frame.from_extractor(a, 0, (0, w, 0, h))
@@ -53,7 +53,7 @@ db = DescriptorDB(600, 600 + 4 * 300)
 db.upload(600, synth_descriptors(1200, 4))
 kfres = db.query_keyframes(synth_descriptors(70, 5), 300)
 db.close()
-os.environ["ORBGPU_FAST_STREAMED"] = "1"
+os.environ["ORBGPU_FAST_ROWS_MIN_PX"] = "0"
 big = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=18)
 outs = big.extract_batch(np.stack([l, r, noise, ramp] * 4 + [l, r]))
 print("ok3", n0, n3, n4, int(kfres[4].sum()), sum(len(o[0]) for o in outs))
