@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(FR_T, 12)
 k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLayout lay, uint32_t *__restrict__ cand,
             uint32_t *__restrict__ cand_count, int *__restrict__ err) {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ int s_found[32], s_cnt, s_nW, s_over;
+    __shared__ int s_found[32], s_wcnt[FR_T / 32], s_cnt, s_over;
     uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
     uint32_t *scoreW = reinterpret_cast<uint32_t *>(fsm + lay.off_score);    // row r + 1 <-> computed row r, tile columns
     // flagged words: type bits of the four pixels (brighter 0 / 8 / 16 / 24, darker 1 / 9 / 17 / 25) | row << 2 | column (low six
@@ -573,7 +573,7 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
         asm volatile("cp.async.commit_group;");
         for (int i = tid; i < 2 * FR_TPW; i += FR_T) scoreW[i < FR_TPW ? i : (hc + 1) * FR_TPW + i - FR_TPW] = 0;   // apron rows -1 and hc
         if (tid < 32) s_found[tid] = 0;
-        if (tid == 0) { s_over = 0; s_cnt = 0; s_nW = 0; }
+        if (tid == 0) { s_over = 0; s_cnt = 0; }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
@@ -593,11 +593,14 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
     }
     const uint32_t slot_tag = ((uint32_t)(col & 63) << 10) | ((uint32_t)(col >> 6) << 18) | ((uint32_t)r0 << 2);
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const int wcap = 32 * half;                       // flagged words a warp can produce: its 32 columns x its rows
     const int top = lay.list_cap - 1;
 
     for (int thr = g.ini_th;;) {
         // ---- 2. compass test at thr: the column walks down with the rows y - 3 .. y + 3 unpacked in registers; the flagged
         // words of a warp's row go to the dense list with one shared-memory atomic (ballot + prefix)
+        int wcount = 0;
+        uint32_t *wreg = wlist + (tid >> 5) * wcap;
         if (nrows > 0 && __any_sync(0xffffffffu, vm != 0)) {
             const uint32_t tb = (uint32_t)thr * 0x00010001u + 0x80008000u;
             const uint32_t *tp = tileW + r0 * FR_TPW + tw;      // tile row t <-> image row y0 - 3 + t: computed row r looks at rows r .. r + 6
@@ -630,20 +633,21 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
                 if (vm) sp[k * FR_TPW] = 0;
                 const bool f = (fH | fL) != 0;
                 const unsigned bal = __ballot_sync(0xffffffffu, f);
-                if (bal) {
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(&s_nW, __popc(bal));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (f) wlist[base + __popc(bal & lt_mask)] = ((fH >> 7) | (fL >> 6)) + (slot_tag + 4u * k);
-                }
+                if (f) wreg[wcount + __popc(bal & lt_mask)] = ((fH >> 7) | (fL >> 6)) + (slot_tag + 4u * k);
+                wcount += __popc(bal);   // warp-uniform: the warp appends to its own region of the list, no atomic
             }
         }
+        if (lane == 0) s_wcnt[tid >> 5] = wcount;
         __syncthreads();
-        const int nFw = s_nW;
+        int nFw = 0;
+#pragma unroll
+        for (int q = 0; q < FR_T / 32; q++) nFw += s_wcnt[q];
         // ---- 3b. flagged words -> survivor lists on dense lanes.  A pixel of both types goes on the brighter-type list, bit 15 set.
         {
             for (int t = tid; t < nFw; t += FR_T) {
-                const uint32_t e = wlist[t], hm = e & 0x01010101u, lm = (e >> 1) & 0x01010101u, lo = lm & ~hm;
+                int u = t, q = 0;                      // entry t of the warps' regions taken one after the other
+                while (u >= s_wcnt[q]) { u -= s_wcnt[q]; q++; }
+                const uint32_t e = wlist[q * wcap + u], hm = e & 0x01010101u, lm = (e >> 1) & 0x01010101u, lo = lm & ~hm;
                 const int p = atomicAdd(&s_cnt, __popc(hm) + (__popc(lo) << 16));
                 int ph = p & 0xffff, pl = p >> 16;
                 if (ph + __popc(hm) + pl + __popc(lo) > lay.list_cap) { s_over = 1; continue; }   // (a bound: both counts only grow)
@@ -738,7 +742,7 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
             vm = keep;
         }
         if (!__syncthreads_or(vm != 0)) break;
-        if (tid == 0) { s_cnt = 0; s_nW = 0; }
+        if (tid == 0) s_cnt = 0;
         thr = g.min_th;
         __syncthreads();
     }
@@ -749,7 +753,7 @@ static size_t fast_rows_layout(const FastLevel &fl, FastRowsLayout &lay) {
     auto up = [](size_t v) { return (v + 15) & ~(size_t)15; };
     size_t off = up((size_t)(fl.hCell + 6) * FR_TPB);
     lay.off_score = (int)off; off = up(off + (size_t)(fl.hCell + 2) * FR_TPB);
-    lay.off_slots = (int)off; off = up(off + (size_t)fl.hCell * FR_COLS * 4);   // flagged words: one per word of the segment at most
+    lay.off_slots = (int)off; off = up(off + (size_t)(fl.hCell + 1) * FR_COLS * 4);   // flagged words: a region of 32 columns x its rows per warp
     lay.list_cap = 2 * FR_COLS * fl.hCell;                               // half of the segment's pixels
     lay.off_list = (int)off; off = up(off + (size_t)lay.list_cap * 2);
     return off;

@@ -80,7 +80,7 @@ struct orb_extractor {
     uint32_t *d_cand = nullptr; uint16_t *d_node_of = nullptr; size_t cand_elems = 0;
     uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
     bool fast_rows = true;             // large batches: k_fast_rows on levels of at least fast_rows_min_px computed pixels
-    long long fast_rows_min_px = 200000;
+    long long fast_rows_min_px = 100000;
     orbgpu::Kept *d_kept = nullptr; size_t kept_elems = 0;
     orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
     size_t out_cap_elems = 0;

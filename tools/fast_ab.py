@@ -23,6 +23,8 @@ for mode in os.environ.get("FAST_AB_MODES", "cells,rows,hybrid").split(","):
     os.environ.pop("ORBGPU_FAST_CELLS", None)
     if mode == "rows":
         os.environ["ORBGPU_FAST_ROWS_MIN_PX"] = "0"
+    elif mode.startswith("min"):
+        os.environ["ORBGPU_FAST_ROWS_MIN_PX"] = mode[3:]
     elif mode == "cells":
         os.environ["ORBGPU_FAST_CELLS"] = "1"
     ex = ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
