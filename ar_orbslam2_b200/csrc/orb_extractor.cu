@@ -11,6 +11,7 @@
 // steps use explicit round-to-nearest intrinsics so nothing is contracted into an FMA.
 #include "orb_common.cuh"
 #include "orb_internal.cuh"
+#include <cuda.h>                // CUtensorMap (the encoder is fetched with cudaGetDriverEntryPoint: no link against libcuda)
 #include <nvtx3/nvToolsExt.h>   // header-only; the ranges cost a function-pointer test when no tool is attached
 #include "orb_pattern.h"
 
@@ -526,7 +527,7 @@ constexpr int FR_TPW = FR_COLS + 8;     // tile pitch in words: the columns + on
 constexpr int FR_TPB = FR_TPW * 4;
 constexpr int FR_ROWS = 30;          // rows per thread (cells are < 60 px high)
 
-struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells; };   // byte offsets into dynamic shared memory
+struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells, use_tma; };   // byte offsets into dynamic shared memory
 
 __device__ __noinline__ uint32_t fast_arc_pair_rows_call(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn) {
     return fast_arc_pair<FR_TPB>(p0, p1, sgn);
@@ -539,10 +540,11 @@ __device__ __noinline__ void fast_cell_rows_call(const uint8_t *pyr, const FastL
 }
 
 __global__ void __launch_bounds__(FR_T, 12)
-k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLayout lay, uint32_t *__restrict__ cand,
-            uint32_t *__restrict__ cand_count, int *__restrict__ err) {
-    extern __shared__ __align__(16) unsigned char fsm[];
+k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLayout lay, const __grid_constant__ CUtensorMap tmap,
+            uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count, int *__restrict__ err) {
+    extern __shared__ __align__(128) unsigned char fsm[];
     __shared__ int s_found[32], s_wcnt[FR_T / 32], s_cnt, s_over;
+    __shared__ __align__(8) unsigned long long s_mbar;
     uint32_t *tileW = reinterpret_cast<uint32_t *>(fsm);
     uint32_t *scoreW = reinterpret_cast<uint32_t *>(fsm + lay.off_score);    // row r + 1 <-> computed row r, tile columns
     // flagged words: type bits of the four pixels (brighter 0 / 8 / 16 / 24, darker 1 / 9 / 17 / 25) | row << 2 | column (low six
@@ -557,8 +559,30 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
     const int w0 = (XOFF + xs) >> 2, wl = (XOFF + xe - 1) >> 2, nW = wl - w0 + 1;              // plane words with computed pixels
     const int cbase = (w0 - 1) & ~3;                                                            // tile word 0 <-> plane word cbase
     const int lead = XOFF + xs - 4 * w0, xoff = 4 * (w0 - cbase);                               // list x = tile byte column - xoff
-    // ---- 1. stage tile rows y0 - 3 .. y0 + hc + 2, words cbase .. wl + 1: thread = (16-byte chunk of a row, row group)
-    {
+    // ---- 1. stage tile rows y0 - 3 .. y0 + hc + 2, words cbase .. cbase + FR_TPW - 1.  With a tensor map of the level (use_tma):
+    // ONE 3-D tiled TMA load (cp.async.bulk.tensor, box = FR_TPB bytes x hCell + 6 rows x 1 frame; what lies outside the plane
+    // arrives as zeros) issued by one thread, completion counted in bytes on an mbarrier -- no thread moves data.  Otherwise
+    // 16-byte cp.async chunks, thread = (chunk of a row, row group).
+    if (lay.use_tma) {
+        const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"((uint32_t)(FR_TPB * (g.hCell + 6))) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                             (uint32_t)__cvta_generic_to_shared(tileW)),
+                         "l"(&tmap), "r"(4 * cbase), "r"(EDGE + y0 - 3), "r"(b), "r"(mbar)
+                         : "memory");
+        }
+        for (int i = tid; i < 2 * FR_TPW; i += FR_T) scoreW[i < FR_TPW ? i : (hc + 1) * FR_TPW + i - FR_TPW] = 0;   // apron rows -1 and hc
+        if (tid < 32) s_found[tid] = 0;
+        if (tid == 0) { s_over = 0; s_cnt = 0; }
+        __syncthreads();   // the barrier's initialisation is visible to the waiting threads
+        uint32_t done;
+        do {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mbar) : "memory");
+        } while (!done);
+    } else {
         const int nQ = ((wl + 1) >> 2) - (cbase >> 2) + 1;     // <= FR_COLS / 4 + 2 chunks per row
         const int lg = nQ > 32 ? 6 : nQ > 16 ? 5 : 4, q = tid & ((1 << lg) - 1), rstep = FR_T >> lg;
         if (q < nQ) {
@@ -575,8 +599,8 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
         if (tid < 32) s_found[tid] = 0;
         if (tid == 0) { s_over = 0; s_cnt = 0; }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
     }
-    __syncthreads();
     const uint8_t *tile = reinterpret_cast<const uint8_t *>(tileW);
     uint8_t *score = reinterpret_cast<uint8_t *>(scoreW);
     const FastDiv dW(g.wCell);
@@ -1537,6 +1561,37 @@ static int upload_constants_once() {
     return ORB_OK;
 }
 
+// One 3-D tensor map per level for k_fast_rows' tile loads: {plane row bytes, plane rows, frame slots} of u8, box = FR_TPB bytes x
+// (hCell + 6) rows x 1 frame.  Levels where the driver refuses (or ORBGPU_NO_TMA=1) keep the cp.async staging.
+static void build_tensor_maps(orb_extractor *ex, const Geom &G) {
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                 CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    static bool looked = false;
+    if (!looked) {
+        looked = true;
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (!getenv("ORBGPU_NO_TMA") && cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            encode = (EncodeFn)fn;
+        (void)cudaGetLastError();
+    }
+    for (int l = 0; l < ORB_MAX_LEVELS; l++) ex->tmap_ok[l] = false;
+    if (!encode) return;
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom &g = G.lv[l];
+        const cuuint64_t dims[3] = {(cuuint64_t)g.pitch, (cuuint64_t)(g.h + 2 * EDGE), (cuuint64_t)ex->prm.max_batch};
+        const cuuint64_t strides[2] = {(cuuint64_t)g.pitch, (cuuint64_t)G.pyr_frame};
+        const cuuint32_t box[3] = {(cuuint32_t)FR_TPB, (cuuint32_t)(g.hCell + 6), 1u}, estr[3] = {1u, 1u, 1u};
+        if (g.hCell + 6 > 256 || (G.pyr_frame % 16) != 0) continue;
+        ex->tmap_ok[l] = encode(&ex->tmap[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, ex->d_pyr + g.plane_off, dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    }
+}
+
 static int set_geometry(orb_extractor *ex, int width, int height) {
     if (ex->geom.width == width && ex->geom.height == height && ex->geom.nlevels == ex->prm.nlevels) return ORB_OK;
     if (ex->gexec) { cudaGraphExecDestroy(ex->gexec); ex->gexec = nullptr; }   // the captured launches hold the old geometry
@@ -1548,6 +1603,7 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
                 rc == ORB_ERR_TOO_SMALL ? "a pyramid level is too small for the 30-px cell grid (reference divides by zero)"
                                         : "unsupported geometry");
     ORB_REQUIRE(taps.size() <= ex->taps_cap, ORB_ERR_INVALID, "internal: tap pool too small");
+    build_tensor_maps(ex, G);
     // per-output-word resize records (fast path), two uint4 per word: weights and byte selectors (see k_pyr_resize).  A
     // level where some pixel's two source bytes do not fit the selectors' reach keeps the generic kernel.
     std::vector<uint4> wtab;
@@ -1905,8 +1961,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         if (rows_path && (long long)(g.w - 2 * EDGE) * (g.h - 2 * EDGE) >= ex->fast_rows_min_px) {
             FastRowsLayout lay;
             const size_t smem_rows = std::max(smem, fast_rows_layout(fl, lay));
+            lay.use_tma = ex->tmap_ok[l] ? 1 : 0;
             k_fast_rows<<<dim3((g.ncx + lay.seg_cells - 1) / lay.seg_cells, g.ncy, batch), FR_T, smem_rows, s>>>(
-                ex->d_pyr, fl, lay, ex->d_cand, d_cand_count, ex->d_err);
+                ex->d_pyr, fl, lay, ex->tmap[l], ex->d_cand, d_cand_count, ex->d_err);
         } else {
             k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
         }

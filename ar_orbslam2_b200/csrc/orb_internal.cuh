@@ -1,5 +1,6 @@
 // liborbgpu internals shared by the .cu translation units: level geometry, the extractor handle.
 #pragma once
+#include <cuda.h>
 #include "orb_common.cuh"
 
 #include <vector>
@@ -81,6 +82,8 @@ struct orb_extractor {
     uint32_t *d_counts = nullptr;      // [B][nlevels] candidates, then [B][nlevels] kept
     bool fast_rows = true;             // large batches: k_fast_rows on levels of at least fast_rows_min_px computed pixels
     long long fast_rows_min_px = 100000;
+    CUtensorMap tmap[ORB_MAX_LEVELS];  // per level: the pyramid planes of all frame slots as a 3-D tensor (k_fast_rows' tile loads)
+    bool tmap_ok[ORB_MAX_LEVELS] = {};
     orbgpu::Kept *d_kept = nullptr; size_t kept_elems = 0;
     orb_keypoint *d_out_kp = nullptr; uint8_t *d_out_desc = nullptr; int32_t *d_out_n = nullptr;
     size_t out_cap_elems = 0;
