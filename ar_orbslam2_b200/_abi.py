@@ -107,6 +107,38 @@ def frustum_args(cam: dict, world_pos, normal, max_distance, min_distance, consi
     return c, p, [wp, nr, mx, mn, co]
 
 
+class OrbProjection(C.Structure):
+    _fields_ = [("R1", C.c_float * 9), ("t1", C.c_float * 3), ("R2", C.c_float * 9), ("t2", C.c_float * 3), ("Ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("two_stage", C.c_int32), ("reject_negative_z", C.c_int32), ("invz_rule", C.c_int32), ("uv_rule", C.c_int32),
+                ("bounds_rule", C.c_int32), ("dist_rule", C.c_int32), ("check_view_angle", C.c_int32)]
+
+
+def projection_args(proj: dict, world_pos, normal, max_distance, min_distance, consider=None):
+    """(OrbProjection, OrbFrustumPoints, keep-alive list): proj holds R1[9], t1[3] (and R2, t2, Ow where used), the camera scalars
+    and the rule switches of include/orbgpu.h: orb_projection."""
+    c = OrbProjection()
+    for k, m in (("R1", 9), ("t1", 3), ("R2", 9), ("t2", 3), ("Ow", 3)):
+        getattr(c, k)[:] = [float(x) for x in np.asarray(proj.get(k, np.zeros(m)), np.float32).reshape(m)]
+    for k in ("fx", "fy", "cx", "cy", "bf", "min_x", "max_x", "min_y", "max_y"):
+        setattr(c, k, float(np.float32(proj.get(k, 0.0))))
+    for k in ("two_stage", "reject_negative_z", "invz_rule", "uv_rule", "bounds_rule", "dist_rule", "check_view_angle"):
+        setattr(c, k, int(proj.get(k, 0)))
+    wp = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+    nr = None if normal is None else np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    mx = np.ascontiguousarray(max_distance, np.float32)
+    mn = np.ascontiguousarray(min_distance, np.float32)
+    co = None if consider is None else np.ascontiguousarray(consider, np.uint8)
+    p = OrbFrustumPoints(wp.shape[0], wp.ctypes.data, None if nr is None else nr.ctypes.data, mx.ctypes.data, mn.ctypes.data,
+                         None if co is None else co.ctypes.data)
+    return c, p, [wp, nr, mx, mn, co]
+
+
+def projection_outputs(n):
+    return (np.zeros(n, np.uint8), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32))
+
+
 def frustum_outputs(n):
     return (np.zeros(n, np.uint8), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32),
             np.zeros(n, np.float32))

@@ -84,6 +84,72 @@ __global__ void k_is_in_frustum(const orb_frustum_camera cam, int n, const float
     level[i] = ok ? lvl : 0;
 }
 
+// The projection pre-loops of the mapping / loop-closing matchers (ref src/ORBmatcher.cc:1491-1531 SearchByProjection(Frame&,
+// KeyFrame*), :311-360 SearchByProjection(KeyFrame*, Scw), :846-893 and :1004-1048 Fuse, :1150-1226 SearchBySim3): the same shape
+// as isInFrustum with the reference's small differences between the sites kept as rules (how 1/z is rounded, how u is
+// associated, which bounds test, which distance, whether the viewing angle is tested).  MapPoint::PredictScale stays with the
+// caller: it is a public method of the reference's MapPoint, the raw mfMaxDistance it needs is not.
+__global__ void k_project_points(const orb_projection P, int n, const float *__restrict__ wp, const float *__restrict__ nrm,
+                                 const float *__restrict__ maxd, const float *__restrict__ mind, const uint8_t *__restrict__ consider,
+                                 uint8_t *__restrict__ ok_out, float *__restrict__ pu, float *__restrict__ pv, float *__restrict__ pur,
+                                 float *__restrict__ pdist) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bool ok = !consider || consider[i];
+    float u = 0, v = 0, ur = 0, dist = 0;
+    if (ok) {
+        const float X[3] = {wp[3 * i], wp[3 * i + 1], wp[3 * i + 2]};
+        float a[3], c[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) {   // R * X + t: the product in double (cv::gemm), then a float addition
+            double s = 0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) s += (double)P.R1[3 * r + k] * (double)X[k];
+            a[r] = __fadd_rn((float)s, P.t1[r]);
+        }
+        if (P.two_stage) {
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                double s = 0;
+#pragma unroll
+                for (int k = 0; k < 3; k++) s += (double)P.R2[3 * r + k] * (double)a[k];
+                c[r] = __fadd_rn((float)s, P.t2[r]);
+            }
+        } else {
+            c[0] = a[0]; c[1] = a[1]; c[2] = a[2];
+        }
+        if (P.reject_negative_z) ok = !(c[2] < 0.0f);
+        const float invz = P.invz_rule == 0 ? (float)(1.0 / (double)c[2]) : __fdiv_rn(1.0f, c[2]);
+        if (P.uv_rule == 0) {
+            u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, c[0]), invz), P.cx);
+            v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, c[1]), invz), P.cy);
+        } else {
+            u = __fadd_rn(__fmul_rn(P.fx, __fmul_rn(c[0], invz)), P.cx);
+            v = __fadd_rn(__fmul_rn(P.fy, __fmul_rn(c[1], invz)), P.cy);
+        }
+        if (P.bounds_rule == 0) ok = ok && !(u < P.min_x || u > P.max_x) && !(v < P.min_y || v > P.max_y);
+        else ok = ok && (u >= P.min_x && u < P.max_x && v >= P.min_y && v < P.max_y);
+        ur = __fsub_rn(u, __fmul_rn(P.bf, invz));
+        double s2 = 0, sd = 0;
+        if (P.dist_rule == 0) {
+            const float PO[3] = {__fsub_rn(X[0], P.Ow[0]), __fsub_rn(X[1], P.Ow[1]), __fsub_rn(X[2], P.Ow[2])};
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                s2 += (double)PO[k] * (double)PO[k];
+                if (P.check_view_angle) sd += (double)PO[k] * (double)nrm[3 * i + k];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; k++) s2 += (double)c[k] * (double)c[k];
+        }
+        dist = (float)sqrt(s2);                                                       // cv::norm
+        ok = ok && !(dist < mind[i] || dist > maxd[i]);
+        if (P.check_view_angle) ok = ok && !(sd < 0.5 * (double)dist);                // PO.dot(Pn) < 0.5 * dist
+    }
+    ok_out[i] = ok ? 1 : 0;
+    pu[i] = ok ? u : 0.0f; pv[i] = ok ? v : 0.0f; pur[i] = ok ? ur : 0.0f; pdist[i] = ok ? dist : 0.0f;
+}
+
 struct DevBuf {
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -137,5 +203,49 @@ extern "C" int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustu
     ORB_CUDA_TRY(cudaMemcpyAsync(level, o_lv, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaMemcpyAsync(in_view, o_in, (size_t)n, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
+}
+
+extern "C" int orb_project_points(const orb_projection *proj, const orb_projection_points *pts, int loc, uint8_t *ok, float *u, float *v,
+                                  float *u_right, float *dist) {
+    ORB_REQUIRE(proj && pts && pts->n >= 0, ORB_ERR_INVALID, "bad argument");
+    const int n = pts->n;
+    if (n == 0) return ORB_OK;
+    ORB_REQUIRE(pts->world_pos && pts->max_distance && pts->min_distance && ok && u && v && u_right && dist, ORB_ERR_INVALID, "null array");
+    ORB_REQUIRE(!(proj->check_view_angle && proj->dist_rule == 0) || pts->normal, ORB_ERR_INVALID, "the viewing-angle test needs the normals");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    ORB_REQUIRE(e == cudaSuccess && ndev > 0, ORB_ERR_CUDA, "no CUDA device (%s); liborbgpu has no CPU fallback", cudaGetErrorString(e));
+    const int blocks = (n + 127) / 128;
+    const size_t N = (size_t)n, a = (N * 4 + 255) / 256 * 256;   // one float array, 256-byte aligned
+    const size_t need_d = 3 * a + 3 * a + 2 * a + a + 4 * a + a, need_h = need_d;
+    ThreadCtx *T = nullptr;
+    { int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? need_d : 0, loc == ORB_HOST ? need_h : 0); if (rc != ORB_OK) return rc; }
+    cudaStream_t st = T->stream;
+    if (loc == ORB_DEVICE) {
+        k_project_points<<<blocks, 128, 0, st>>>(*proj, n, pts->world_pos, pts->normal, pts->max_distance, pts->min_distance, pts->consider, ok,
+                                               u, v, u_right, dist);
+        ORB_CUDA_TRY(cudaGetLastError());
+        return ORB_OK;
+    }
+    // host arrays: packed into the thread's pinned block, one copy in, one copy out
+    uint8_t *h = T->h_buf, *d = T->d_buf;
+    const size_t o_wp = 0, o_nr = 3 * a, o_mx = 6 * a, o_mn = 7 * a, o_cons = 8 * a, o_out = 9 * a;   // outputs: u, v, ur, dist, ok
+    memcpy(h + o_wp, pts->world_pos, N * 12);
+    if (pts->normal) memcpy(h + o_nr, pts->normal, N * 12);
+    memcpy(h + o_mx, pts->max_distance, N * 4);
+    memcpy(h + o_mn, pts->min_distance, N * 4);
+    if (pts->consider) memcpy(h + o_cons, pts->consider, N);
+    ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_out, cudaMemcpyHostToDevice, st));
+    float *du = (float *)(d + o_out), *dv = (float *)(d + o_out + a), *dur = (float *)(d + o_out + 2 * a), *dd = (float *)(d + o_out + 3 * a);
+    uint8_t *dok = d + o_out + 4 * a;
+    k_project_points<<<blocks, 128, 0, st>>>(*proj, n, (const float *)(d + o_wp), pts->normal ? (const float *)(d + o_nr) : nullptr,
+                                           (const float *)(d + o_mx), (const float *)(d + o_mn), pts->consider ? d + o_cons : nullptr, dok, du,
+                                           dv, dur, dd);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpyAsync(h + o_out, d + o_out, 5 * a, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(u, h + o_out, N * 4); memcpy(v, h + o_out + a, N * 4); memcpy(u_right, h + o_out + 2 * a, N * 4);
+    memcpy(dist, h + o_out + 3 * a, N * 4); memcpy(ok, h + o_out + 4 * a, N);
     return ORB_OK;
 }

@@ -282,6 +282,53 @@ int SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint *> &vpMatch
     return nmatches;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Geometry of a batch of map points on the device (orb_project_points): transform, projection, image test, distance range and
+// viewing angle with the rounding of the site that is being replaced (the rule switches).  What stays here is what only the
+// reference's objects can answer: which points take part, their positions / normals / ranges through the public getters, and
+// MapPoint::PredictScale.
+// ---------------------------------------------------------------------------------------------------------------
+struct Projected {
+    std::vector<uint8_t> ok;
+    std::vector<float> u, v, ur, dist;
+};
+
+static void SetPose(float *R9, float *t3, const cv::Mat &R, const cv::Mat &t) {
+    for (int r = 0; r < 3; r++) {
+        for (int c = 0; c < 3; c++) R9[3 * r + c] = R.at<float>(r, c);
+        t3[r] = t.at<float>(r);
+    }
+}
+
+static orb_projection MakeProjection(float fx, float fy, float cx, float cy, float bf, float minX, float maxX, float minY, float maxY) {
+    orb_projection P;
+    std::memset(&P, 0, sizeof(P));
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.bf = bf;
+    P.min_x = minX; P.max_x = maxX; P.min_y = minY; P.max_y = maxY;
+    return P;
+}
+
+static void Project(const orb_projection &P, const std::vector<MapPoint *> &pts, const std::vector<uint8_t> &consider, Projected &out) {
+    const int n = (int)pts.size();
+    out.ok.assign(n, 0); out.u.assign(n, 0.f); out.v.assign(n, 0.f); out.ur.assign(n, 0.f); out.dist.assign(n, 0.f);
+    if (n == 0) return;
+    std::vector<float> X((size_t)n * 3, 0.f), Nrm((size_t)n * 3, 0.f), maxD(n, 0.f), minD(n, 0.f);
+    for (int i = 0; i < n; i++) {
+        if (!consider[i]) continue;
+        MapPoint *pMP = pts[i];
+        const cv::Mat x = pMP->GetWorldPos();
+        for (int k = 0; k < 3; k++) X[3 * i + k] = x.at<float>(k);
+        if (P.check_view_angle) {
+            const cv::Mat nn = pMP->GetNormal();
+            for (int k = 0; k < 3; k++) Nrm[3 * i + k] = nn.at<float>(k);
+        }
+        maxD[i] = pMP->GetMaxDistanceInvariance();
+        minD[i] = pMP->GetMinDistanceInvariance();
+    }
+    orb_projection_points Q = {n, X.data(), P.check_view_angle ? Nrm.data() : NULL, maxD.data(), minD.data(), consider.data()};
+    Check(orb_project_points(&P, &Q, ORB_HOST, out.ok.data(), out.u.data(), out.v.data(), out.ur.data(), out.dist.data()), "orb_project_points");
+}
+
 // Relocalisation refinement (Tracking::Relocalization): project the key frame's map points with the current pose and search
 // the current frame; any map point already in the frame blocks its feature (:1544-1545).
 int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const std::set<MapPoint *> &sAlreadyFound, float th, int ORBdist,
@@ -293,42 +340,39 @@ int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const std::set<MapPoi
     const int n = (int)vpMPs.size();
     if (n == 0 || CurrentFrame.N == 0) return 0;
     const int nlev = (int)CurrentFrame.mvScaleFactors.size();
-    std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32 + 32, 0), claimed(CurrentFrame.N, 0);
-    std::vector<float> u(n, 0.f), v(n, 0.f), radius(n, 0.f), angle(n, 0.f);
+    std::vector<uint8_t> valid(n, 0), consider(n, 0), desc((size_t)n * 32 + 32, 0), claimed(CurrentFrame.N, 0);
+    std::vector<float> radius(n, 0.f), angle(n, 0.f);
     std::vector<int32_t> minL(n, 0), maxL(n, 0), assigned(CurrentFrame.N);
-    for (int i = 0; i < n; i++) {                                      // :1491-1531
+    for (int i = 0; i < n; i++) {                                      // who takes part, :1491-1497
         MapPoint *pMP = vpMPs[i];
         angle[i] = pKF->mvKeysUn[i].angle;
-        if (!pMP) continue;
-        if (pMP->isBad() || sAlreadyFound.count(pMP)) continue;
-        cv::Mat x3Dw = pMP->GetWorldPos();
-        cv::Mat x3Dc = Rcw * x3Dw + tcw;
-        const float xc = x3Dc.at<float>(0);
-        const float yc = x3Dc.at<float>(1);
-        const float invzc = 1.0 / x3Dc.at<float>(2);
-        const float uu = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
-        const float vv = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
-        if (uu < CurrentFrame.mnMinX || uu > CurrentFrame.mnMaxX) continue;
-        if (vv < CurrentFrame.mnMinY || vv > CurrentFrame.mnMaxY) continue;
-        cv::Mat PO = x3Dw - Ow;
-        float dist3D = cv::norm(PO);
-        const float maxDistance = pMP->GetMaxDistanceInvariance();
-        const float minDistance = pMP->GetMinDistanceInvariance();
-        if (dist3D < minDistance || dist3D > maxDistance) continue;
-        int nPredictedLevel = pMP->PredictScale(dist3D, CurrentFrame.mfLogScaleFactor);
+        consider[i] = pMP && !pMP->isBad() && !sAlreadyFound.count(pMP);
+    }
+    // :1499-1524 on the device: 1.0/z in double, fx*xc*invz, the frame's bounds, no z test, no viewing angle
+    orb_projection P = MakeProjection(CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy, 0.f, CurrentFrame.mnMinX,
+                                      CurrentFrame.mnMaxX, CurrentFrame.mnMinY, CurrentFrame.mnMaxY);
+    SetPose(P.R1, P.t1, Rcw, tcw);
+    for (int k = 0; k < 3; k++) P.Ow[k] = Ow.at<float>(k);
+    Projected G;
+    Project(P, vpMPs, consider, G);
+    for (int i = 0; i < n; i++) {
+        if (!G.ok[i]) continue;
+        MapPoint *pMP = vpMPs[i];
+        const int nPredictedLevel = pMP->PredictScale(G.dist[i], CurrentFrame.mfLogScaleFactor);
         if (nPredictedLevel < 0 || nPredictedLevel >= nlev) continue;   // the reference indexes mvScaleFactors out of range here
-        valid[i] = 1; u[i] = uu; v[i] = vv;
+        valid[i] = 1;
         radius[i] = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
         minL[i] = nPredictedLevel - 1; maxL[i] = nPredictedLevel + 1;   // GetFeaturesInArea's own level arguments (:1533)
         cv::Mat d = pMP->GetDescriptor();
         std::memcpy(&desc[(size_t)i * 32], d.ptr(0), 32);
     }
+    const std::vector<float> &u = G.u, &v = G.v;
     for (int i = 0; i < CurrentFrame.N; i++) claimed[i] = CurrentFrame.mvpMapPoints[i] != NULL;   // :1544-1545
     GpuFrame g(CurrentFrame.mvKeysUn, CurrentFrame.mDescriptors, CurrentFrame.mvuRight, CurrentFrame.mvScaleFactors);
     orb_window_queries Q;
     std::memset(&Q, 0, sizeof(Q));
-    Q.n = n; Q.valid = valid.data(); Q.x = u.data(); Q.y = v.data(); Q.radius = radius.data(); Q.min_level = minL.data();
-    Q.max_level = maxL.data(); Q.strict_levels = 0; Q.descriptors = desc.data(); Q.angle = angle.data();
+    Q.n = n; Q.valid = valid.data(); Q.x = u.data(); Q.y = v.data(); Q.radius = radius.data();
+    Q.min_level = minL.data(); Q.max_level = maxL.data(); Q.strict_levels = 0; Q.descriptors = desc.data(); Q.angle = angle.data();
     int nmatches = 0;
     Check(orb_search_windowed(g.h, &Q, claimed.data(), ORB_SELECT_BEST, ORBdist, 0.f, mbCheckOrientation, assigned.data(), &nmatches),
           "orb_search_windowed");
@@ -356,36 +400,29 @@ int SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *>
     const int n = (int)vpPoints.size();
     if (n == 0 || pKF->N == 0) return 0;
     const int nlev = (int)pKF->mvScaleFactors.size();
-    std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32 + 32, 0), claimed(pKF->N, 0);
-    std::vector<float> u(n, 0.f), v(n, 0.f), radius(n, 0.f);
+    std::vector<uint8_t> valid(n, 0), consider(n, 0), desc((size_t)n * 32 + 32, 0), claimed(pKF->N, 0);
+    std::vector<float> radius(n, 0.f);
     std::vector<int32_t> minL(n, 0), maxL(n, 0), assigned(pKF->N);
-    for (int iMP = 0; iMP < n; iMP++) {                                // :311-360
+    for (int iMP = 0; iMP < n; iMP++) consider[iMP] = !vpPoints[iMP]->isBad() && !spAlreadyFound.count(vpPoints[iMP]);   // :316
+    // :318-353 on the device: z < 0 rejected, 1/z in float, x = xc*invz, IsInImage, viewing angle
+    orb_projection P = MakeProjection(fx, fy, cx, cy, 0.f, pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY, pKF->mnMaxY);
+    SetPose(P.R1, P.t1, Rcw, tcw);
+    for (int k = 0; k < 3; k++) P.Ow[k] = Ow.at<float>(k);
+    P.reject_negative_z = 1; P.invz_rule = 1; P.uv_rule = 1; P.bounds_rule = 1; P.check_view_angle = 1;
+    Projected G;
+    Project(P, vpPoints, consider, G);
+    for (int iMP = 0; iMP < n; iMP++) {
+        if (!G.ok[iMP]) continue;
         MapPoint *pMP = vpPoints[iMP];
-        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
-        cv::Mat p3Dw = pMP->GetWorldPos();
-        cv::Mat p3Dc = Rcw * p3Dw + tcw;
-        if (p3Dc.at<float>(2) < 0.0) continue;
-        const float invz = 1 / p3Dc.at<float>(2);
-        const float x = p3Dc.at<float>(0) * invz;
-        const float y = p3Dc.at<float>(1) * invz;
-        const float uu = fx * x + cx;
-        const float vv = fy * y + cy;
-        if (!pKF->IsInImage(uu, vv)) continue;
-        const float maxDistance = pMP->GetMaxDistanceInvariance();
-        const float minDistance = pMP->GetMinDistanceInvariance();
-        cv::Mat PO = p3Dw - Ow;
-        const float dist = cv::norm(PO);
-        if (dist < minDistance || dist > maxDistance) continue;
-        cv::Mat Pn = pMP->GetNormal();
-        if (PO.dot(Pn) < 0.5 * dist) continue;
-        int nPredictedLevel = pMP->PredictScale(dist, pKF->mfLogScaleFactor);
+        const int nPredictedLevel = pMP->PredictScale(G.dist[iMP], pKF->mfLogScaleFactor);
         if (nPredictedLevel < 0 || nPredictedLevel >= nlev) continue;
-        valid[iMP] = 1; u[iMP] = uu; v[iMP] = vv;
+        valid[iMP] = 1;
         radius[iMP] = th * pKF->mvScaleFactors[nPredictedLevel];
         minL[iMP] = nPredictedLevel - 1; maxL[iMP] = nPredictedLevel;   // the in-loop filter of :378-381
         cv::Mat d = pMP->GetDescriptor();
         std::memcpy(&desc[(size_t)iMP * 32], d.ptr(0), 32);
     }
+    const std::vector<float> &u = G.u, &v = G.v;
     for (int i = 0; i < pKF->N; i++) claimed[i] = vpMatched[i] != NULL;
     GpuFrame g(pKF->mvKeysUn, pKF->mDescriptors, pKF->mvuRight, pKF->mvScaleFactors, true);
     orb_window_queries Q;
@@ -494,29 +531,22 @@ int Fuse(KeyFrame *pKF, const std::vector<MapPoint *> &vpMapPoints, float th) {
     cv::Mat Ow = pKF->GetCameraCenter();
     const int nMPs = (int)vpMapPoints.size();
     WindowSet W(nMPs);
-    for (int i = 0; i < nMPs; i++) {                                   // the geometry of :846-893 (none of it changes during the loop)
+    std::vector<uint8_t> consider(nMPs, 0);
+    for (int i = 0; i < nMPs; i++) consider[i] = vpMapPoints[i] != NULL;
+    // the geometry of :855-888 on the device (none of it changes during the loop): z < 0 rejected, 1/z in float, x = xc*invz,
+    // IsInImage, u_right = u - bf*invz, viewing angle
+    orb_projection P = MakeProjection(fx, fy, cx, cy, bf, pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY, pKF->mnMaxY);
+    SetPose(P.R1, P.t1, Rcw, tcw);
+    for (int k = 0; k < 3; k++) P.Ow[k] = Ow.at<float>(k);
+    P.reject_negative_z = 1; P.invz_rule = 1; P.uv_rule = 1; P.bounds_rule = 1; P.check_view_angle = 1;
+    Projected G;
+    Project(P, vpMapPoints, consider, G);
+    for (int i = 0; i < nMPs; i++) {
+        if (!G.ok[i]) continue;
         MapPoint *pMP = vpMapPoints[i];
-        if (!pMP) continue;
-        cv::Mat p3Dw = pMP->GetWorldPos();
-        cv::Mat p3Dc = Rcw * p3Dw + tcw;
-        if (p3Dc.at<float>(2) < 0.0f) continue;
-        const float invz = 1 / p3Dc.at<float>(2);
-        const float x = p3Dc.at<float>(0) * invz;
-        const float y = p3Dc.at<float>(1) * invz;
-        const float u = fx * x + cx;
-        const float v = fy * y + cy;
-        if (!pKF->IsInImage(u, v)) continue;
-        const float ur = u - bf * invz;
-        const float maxDistance = pMP->GetMaxDistanceInvariance();
-        const float minDistance = pMP->GetMinDistanceInvariance();
-        cv::Mat PO = p3Dw - Ow;
-        const float dist3D = cv::norm(PO);
-        if (dist3D < minDistance || dist3D > maxDistance) continue;
-        cv::Mat Pn = pMP->GetNormal();
-        if (PO.dot(Pn) < 0.5 * dist3D) continue;
-        int nPredictedLevel = pMP->PredictScale(dist3D, pKF->mfLogScaleFactor);
+        const int nPredictedLevel = pMP->PredictScale(G.dist[i], pKF->mfLogScaleFactor);
         if (!LevelOk(nPredictedLevel, pKF)) continue;
-        W.Set(i, u, v, ur, nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
+        W.Set(i, G.u[i], G.v[i], G.ur[i], nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
     }
     W.Search(pKF, true);
     int nFused = 0;
@@ -557,28 +587,22 @@ int Fuse(KeyFrame *pKF, cv::Mat Scw, const std::vector<MapPoint *> &vpPoints, fl
     const std::set<MapPoint *> spAlreadyFound = pKF->GetMapPoints();   // :997
     const int nPoints = (int)vpPoints.size();
     WindowSet W(nPoints);
-    for (int iMP = 0; iMP < nPoints; iMP++) {                          // :1004-1048
+    std::vector<uint8_t> consider(nPoints, 0);
+    for (int iMP = 0; iMP < nPoints; iMP++)                            // :1009 (neither changes inside this function)
+        consider[iMP] = !vpPoints[iMP]->isBad() && !spAlreadyFound.count(vpPoints[iMP]);
+    // :1012-1043 on the device: z < 0 rejected, 1.0/z in double, x = xc*invz, IsInImage, viewing angle
+    orb_projection P = MakeProjection(fx, fy, cx, cy, 0.f, pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY, pKF->mnMaxY);
+    SetPose(P.R1, P.t1, Rcw, tcw);
+    for (int k = 0; k < 3; k++) P.Ow[k] = Ow.at<float>(k);
+    P.reject_negative_z = 1; P.invz_rule = 0; P.uv_rule = 1; P.bounds_rule = 1; P.check_view_angle = 1;
+    Projected G;
+    Project(P, vpPoints, consider, G);
+    for (int iMP = 0; iMP < nPoints; iMP++) {
+        if (!G.ok[iMP]) continue;
         MapPoint *pMP = vpPoints[iMP];
-        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;       // neither changes inside this function
-        cv::Mat p3Dw = pMP->GetWorldPos();
-        cv::Mat p3Dc = Rcw * p3Dw + tcw;
-        if (p3Dc.at<float>(2) < 0.0f) continue;
-        const float invz = 1.0 / p3Dc.at<float>(2);
-        const float x = p3Dc.at<float>(0) * invz;
-        const float y = p3Dc.at<float>(1) * invz;
-        const float u = fx * x + cx;
-        const float v = fy * y + cy;
-        if (!pKF->IsInImage(u, v)) continue;
-        const float maxDistance = pMP->GetMaxDistanceInvariance();
-        const float minDistance = pMP->GetMinDistanceInvariance();
-        cv::Mat PO = p3Dw - Ow;
-        const float dist3D = cv::norm(PO);
-        if (dist3D < minDistance || dist3D > maxDistance) continue;
-        cv::Mat Pn = pMP->GetNormal();
-        if (PO.dot(Pn) < 0.5 * dist3D) continue;
-        const int nPredictedLevel = pMP->PredictScale(dist3D, pKF->mfLogScaleFactor);
+        const int nPredictedLevel = pMP->PredictScale(G.dist[iMP], pKF->mfLogScaleFactor);
         if (!LevelOk(nPredictedLevel, pKF)) continue;
-        W.Set(iMP, u, v, 0.f, nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
+        W.Set(iMP, G.u[iMP], G.v[iMP], 0.f, nPredictedLevel, th * pKF->mvScaleFactors[nPredictedLevel], pMP);
     }
     W.Search(pKF, false);
     int nFused = 0;
@@ -627,32 +651,27 @@ int SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint *> &vpMatc
             if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
         }
     }
-    // both directions share one shape: project the map points of KF `a` into KF `b` (:1150-1226 and :1229-1305)
+    // both directions share one shape: the map points of KF `a` into KF `b` (:1150-1226 and :1229-1305), on the device: camera a, then
+    // the similarity into camera b, z < 0 rejected, 1.0/z in double, x = xc*invz, IsInImage, the distance measured in camera b
     struct Dir {
         static void Gather(const std::vector<MapPoint *> &pts, const std::vector<bool> &already, const cv::Mat &Raw, const cv::Mat &taw,
                            const cv::Mat &sRba, const cv::Mat &tba, KeyFrame *pKFb, float fx, float fy, float cx, float cy, float th,
                            WindowSet &W) {
-            for (int i = 0, n = (int)pts.size(); i < n; i++) {
+            const int n = (int)pts.size();
+            std::vector<uint8_t> consider(n, 0);
+            for (int i = 0; i < n; i++) consider[i] = pts[i] && !already[i] && !pts[i]->isBad();
+            orb_projection P = MakeProjection(fx, fy, cx, cy, 0.f, pKFb->mnMinX, pKFb->mnMaxX, pKFb->mnMinY, pKFb->mnMaxY);
+            SetPose(P.R1, P.t1, Raw, taw);
+            SetPose(P.R2, P.t2, sRba, tba);
+            P.two_stage = 1; P.reject_negative_z = 1; P.invz_rule = 0; P.uv_rule = 1; P.bounds_rule = 1; P.dist_rule = 1;
+            Projected G;
+            Project(P, pts, consider, G);
+            for (int i = 0; i < n; i++) {
+                if (!G.ok[i]) continue;
                 MapPoint *pMP = pts[i];
-                if (!pMP || already[i]) continue;
-                if (pMP->isBad()) continue;
-                cv::Mat p3Dw = pMP->GetWorldPos();
-                cv::Mat p3Dca = Raw * p3Dw + taw;
-                cv::Mat p3Dcb = sRba * p3Dca + tba;
-                if (p3Dcb.at<float>(2) < 0.0) continue;
-                const float invz = 1.0 / p3Dcb.at<float>(2);
-                const float x = p3Dcb.at<float>(0) * invz;
-                const float y = p3Dcb.at<float>(1) * invz;
-                const float u = fx * x + cx;
-                const float v = fy * y + cy;
-                if (!pKFb->IsInImage(u, v)) continue;
-                const float maxDistance = pMP->GetMaxDistanceInvariance();
-                const float minDistance = pMP->GetMinDistanceInvariance();
-                const float dist3D = cv::norm(p3Dcb);
-                if (dist3D < minDistance || dist3D > maxDistance) continue;
-                const int nPredictedLevel = pMP->PredictScale(dist3D, pKFb->mfLogScaleFactor);
+                const int nPredictedLevel = pMP->PredictScale(G.dist[i], pKFb->mfLogScaleFactor);
                 if (!LevelOk(nPredictedLevel, pKFb)) continue;
-                W.Set(i, u, v, 0.f, nPredictedLevel, th * pKFb->mvScaleFactors[nPredictedLevel], pMP);
+                W.Set(i, G.u[i], G.v[i], 0.f, nPredictedLevel, th * pKFb->mvScaleFactors[nPredictedLevel], pMP);
             }
         }
     };

@@ -277,3 +277,16 @@ def isInFrustum(cam: dict, world_pos, normal, max_distance, min_distance, viewin
     _lib.check(_lib.lib().orb_is_in_frustum(C.byref(c), C.byref(p), C.c_float(viewing_cos_limit), 0, *[ptr(a) for a in o]),
                "orb_is_in_frustum")
     return o
+
+
+def ProjectMapPoints(proj: dict, world_pos, normal, max_distance, min_distance, consider=None):
+    """The projection pre-loop of SearchByProjection(Frame&, KeyFrame*) / SearchByProjection(KeyFrame*, Scw) / Fuse / SearchBySim3
+    (ref ORBmatcher.cc:1491-1531, :311-360, :846-893, :1004-1048, :1150-1226) for all map points at once on the GPU.  proj: dict
+    with R1, t1 (R2, t2, Ow where used), fx, fy, cx, cy, bf, the bounds and the rule switches of include/orbgpu.h: orb_projection;
+    max_distance / min_distance = MapPoint::GetMaxDistanceInvariance / GetMinDistanceInvariance.  Returns (ok, u, v, u_right, dist);
+    the caller applies MapPoint::PredictScale to dist."""
+    from ._abi import projection_args, projection_outputs
+    c, p, keep = projection_args(proj, world_pos, normal, max_distance, min_distance, consider)
+    o = projection_outputs(p.n)
+    _lib.check(_lib.lib().orb_project_points(C.byref(c), C.byref(p), 0, *[ptr(a) for a in o]), "orb_project_points")
+    return o

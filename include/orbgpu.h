@@ -514,6 +514,38 @@ typedef struct orb_frustum_points {
 int orb_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float viewing_cos_limit, int loc,
                       uint8_t *in_view, float *proj_x, float *proj_y, float *proj_xr, int32_t *level, float *view_cos);
 
+/* ref: the projection pre-loops of the mapping / loop-closing matchers -- SearchByProjection(Frame&, KeyFrame*, ...)
+ * src/ORBmatcher.cc:1491-1531, SearchByProjection(KeyFrame*, Scw, ...) :311-360, Fuse :846-893 and :1004-1048, SearchBySim3
+ * :1150-1226 / :1229-1305: per map point the transform into the camera, the pinhole projection, the image test, the distance
+ * range and (where the reference has it) the viewing-angle test, with cv::Mat's rounding (3x3 products and norms accumulate in
+ * double).  The sites differ in small ways that change the last bit; each is a rule:
+ *   invz_rule          0: (float)(1.0 / z) (`1.0/z`, :1503, :1021, :1166)      1: 1.0f / z (`1/z`, :323, :861)
+ *   uv_rule            0: fx*xc*invz + cx (:1505)                               1: x = xc*invz; fx*x + cx (:325-329 and the others)
+ *   bounds_rule        0: reject u < min || u > max (Frame bounds, :1508-1511)  1: KeyFrame::IsInImage, min <= u < max (:332)
+ *   reject_negative_z  the `z < 0` test (all sites but :1491-1531)
+ *   dist_rule          0: |X - Ow|                                              1: |x| in the second camera (SearchBySim3 :1177)
+ *   check_view_angle   PO.dot(Pn) < 0.5 * dist rejected (:350-353, :885-888, :1040-1043); needs dist_rule 0 and the normals
+ *   two_stage          x = R2 * (R1 * X + t1) + t2 (SearchBySim3: camera a, then the similarity into camera b)
+ * max_distance / min_distance are what MapPoint::GetMaxDistanceInvariance / GetMinDistanceInvariance return.  Outputs per point:
+ * ok, u, v, u_right = u - bf * invz (:865), dist.  MapPoint::PredictScale(dist, logScaleFactor) stays with the caller (a public
+ * method of the reference's class; the raw mfMaxDistance it reads is not public).  loc as in orb_is_in_frustum.             */
+typedef struct orb_projection {
+    float R1[9], t1[3], R2[9], t2[3], Ow[3];
+    float fx, fy, cx, cy, bf;
+    float min_x, max_x, min_y, max_y;
+    int32_t two_stage, reject_negative_z, invz_rule, uv_rule, bounds_rule, dist_rule, check_view_angle;
+} orb_projection;
+typedef struct orb_projection_points {
+    int32_t n;
+    const float *world_pos;      /* [n][3] */
+    const float *normal;         /* [n][3] or NULL */
+    const float *max_distance;   /* [n] GetMaxDistanceInvariance() */
+    const float *min_distance;   /* [n] GetMinDistanceInvariance() */
+    const uint8_t *consider;     /* [n] or NULL = all */
+} orb_projection_points;
+int orb_project_points(const orb_projection *proj, const orb_projection_points *pts, int loc, uint8_t *ok, float *u, float *v,
+                       float *u_right, float *dist);
+
 /* ---- map-point descriptor selection ------------------------------------------ */
 
 /* ref: MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:224-285: among the N descriptors observing a map

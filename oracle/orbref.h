@@ -70,6 +70,9 @@ int orbref_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t
 /* Frame::isInFrustum + MapPoint::PredictScale (orbref_frustum.cpp) */
 int orbref_is_in_frustum(const orb_frustum_camera *cam, const orb_frustum_points *pts, float limit, uint8_t *in_view, float *proj_x,
                          float *proj_y, float *proj_xr, int32_t *level, float *view_cos);
+/* projection pre-loops of the mapping / loop matchers (orbref_frustum.cpp) */
+int orbref_project_points(const orb_projection *P, const orb_projection_points *pts, uint8_t *ok, float *pu, float *pv, float *pur,
+                          float *pdist);
 /* cv::remap INTER_LINEAR, 8-bit, CV_32F maps (orbref_remap.cpp) */
 int orbref_remap_linear(const uint8_t *src, int sw, int sh, int spitch, const float *mapx, const float *mapy, int mpitch, uint8_t *dst,
                         int dw, int dh, int dpitch);

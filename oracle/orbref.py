@@ -687,6 +687,15 @@ def is_in_frustum(cam, world_pos, normal, max_distance, min_distance, limit=0.5,
     return o
 
 
+def project_points(proj, world_pos, normal, max_distance, min_distance, consider=None):
+    """The projection pre-loops of the mapping / loop matchers (restatement; rules as include/orbgpu.h: orb_projection)."""
+    from ar_orbslam2_b200._abi import projection_args, projection_outputs
+    c, p, keep = projection_args(proj, world_pos, normal, max_distance, min_distance, consider)
+    o = projection_outputs(p.n)
+    _check(lib().orbref_project_points(C.byref(c), C.byref(p), *[ptr(a) for a in o]), "project_points")
+    return o
+
+
 def refm_is_in_frustum(frame, Tcw, fx, fy, cx, cy, mbf, log_scale_factor, world_pos, normal, max_distance, min_distance, limit=0.5,
                        consider=None):
     """The reference's own Frame::isInFrustum (compiled Frame.cc).  `frame` = a Frame built with ReferenceSourceBackend.

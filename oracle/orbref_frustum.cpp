@@ -39,3 +39,47 @@ extern "C" int orbref_is_in_frustum(const orb_frustum_camera *cam, const orb_fru
     }
     return ORB_OK;
 }
+
+// The projection pre-loops of SearchByProjection(Frame&, KeyFrame*) (src/ORBmatcher.cc:1491-1531), SearchByProjection(KeyFrame*,
+// Scw) (:311-360), Fuse (:846-893, :1004-1048) and SearchBySim3 (:1150-1226) on flat arrays, the sites' differences as the rules
+// of orb_projection (include/orbgpu.h).  Pinned against the reference's lines replayed by oracle/ref_matcher_driver.cpp
+// (refm_search_by_projection_kf / _sim3 return u, v, valid of every point) in tests/test_projection_cpu.py.
+extern "C" int orbref_project_points(const orb_projection *P, const orb_projection_points *pts, uint8_t *ok, float *pu, float *pv,
+                                     float *pur, float *pdist) {
+    for (int i = 0; i < pts->n; i++) {
+        ok[i] = 0; pu[i] = pv[i] = pur[i] = pdist[i] = 0.0f;
+        if (pts->consider && !pts->consider[i]) continue;
+        const float *X = pts->world_pos + 3 * i;
+        float a[3], c[3];
+        for (int r = 0; r < 3; r++) {
+            double s = 0;
+            for (int k = 0; k < 3; k++) s += (double)P->R1[3 * r + k] * (double)X[k];
+            a[r] = (float)s + P->t1[r];
+        }
+        for (int r = 0; r < 3; r++) {
+            if (!P->two_stage) { c[r] = a[r]; continue; }
+            double s = 0;
+            for (int k = 0; k < 3; k++) s += (double)P->R2[3 * r + k] * (double)a[k];
+            c[r] = (float)s + P->t2[r];
+        }
+        if (P->reject_negative_z && c[2] < 0.0f) continue;
+        const float invz = P->invz_rule == 0 ? (float)(1.0 / c[2]) : 1.0f / c[2];
+        float u, v;
+        if (P->uv_rule == 0) { u = P->fx * c[0] * invz + P->cx; v = P->fy * c[1] * invz + P->cy; }
+        else { const float x = c[0] * invz, y = c[1] * invz; u = P->fx * x + P->cx; v = P->fy * y + P->cy; }
+        if (P->bounds_rule == 0) { if (u < P->min_x || u > P->max_x || v < P->min_y || v > P->max_y) continue; }
+        else if (!(u >= P->min_x && u < P->max_x && v >= P->min_y && v < P->max_y)) continue;
+        double s2 = 0, sd = 0;
+        if (P->dist_rule == 0) {
+            const float PO[3] = {X[0] - P->Ow[0], X[1] - P->Ow[1], X[2] - P->Ow[2]};
+            for (int k = 0; k < 3; k++) { s2 += (double)PO[k] * (double)PO[k]; if (P->check_view_angle) sd += (double)PO[k] * (double)pts->normal[3 * i + k]; }
+        } else {
+            for (int k = 0; k < 3; k++) s2 += (double)c[k] * (double)c[k];
+        }
+        const float dist = (float)std::sqrt(s2);
+        if (dist < pts->min_distance[i] || dist > pts->max_distance[i]) continue;
+        if (P->check_view_angle && sd < 0.5 * dist) continue;
+        ok[i] = 1; pu[i] = u; pv[i] = v; pur[i] = u - P->bf * invz; pdist[i] = dist;
+    }
+    return ORB_OK;
+}

@@ -52,3 +52,33 @@ def test_feeds_search_by_projection():
     got = isInFrustum(cam_dict(cam_from_pose(np.eye(4, dtype=np.float32))), np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32),
                       np.zeros(0, np.float32), np.zeros(0, np.float32))
     assert all(len(a) == 0 for a in got)
+
+
+RULES = [  # (name, rule switches) = the five call sites of the reference
+    ("SearchByProjection(Frame,KF) :1491-1531", dict(invz_rule=0, uv_rule=0, bounds_rule=0, reject_negative_z=0, dist_rule=0, check_view_angle=0)),
+    ("SearchByProjection(KF,Scw) :311-360", dict(invz_rule=1, uv_rule=1, bounds_rule=1, reject_negative_z=1, dist_rule=0, check_view_angle=1)),
+    ("Fuse(KF,points) :846-893", dict(invz_rule=1, uv_rule=1, bounds_rule=1, reject_negative_z=1, dist_rule=0, check_view_angle=1)),
+    ("Fuse(KF,Scw) :1004-1048", dict(invz_rule=0, uv_rule=1, bounds_rule=1, reject_negative_z=1, dist_rule=0, check_view_angle=1)),
+    ("SearchBySim3 :1150-1226", dict(invz_rule=0, uv_rule=1, bounds_rule=1, reject_negative_z=1, dist_rule=1, check_view_angle=0, two_stage=1)),
+]
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+@pytest.mark.parametrize("name,rules", RULES)
+def test_project_points_gpu_equals_oracle(seed, name, rules):
+    """orb_project_points (the projection pre-loops of the mapping / loop matchers) against the oracle, whose rule sets for the
+    first two sites are pinned to the reference's replayed lines in tests/test_reference_matcher_cpu.py; the other three are pinned
+    through the whole-method tests of tests/test_m9_gpu.py.  Every output bit for bit."""
+    from ar_orbslam2_b200.tracking import ProjectMapPoints
+    wp, nr, maxd, mind, consider = points(seed, 6000)
+    T1, T2 = pose(seed), pose(seed + 10)
+    R, t = T1[:3, :3], T1[:3, 3]
+    proj = dict(R1=R, t1=t, R2=(np.float32(0.9) * T2[:3, :3]).astype(np.float32), t2=T2[:3, 3], Ow=cam_from_pose(T1)[12:15], fx=FX, fy=FY, cx=CX,
+                cy=CY, bf=MBF, min_x=0, max_x=752, min_y=0, max_y=480, **rules)
+    mx, mn = (np.float32(1.2) * maxd).astype(np.float32), (np.float32(0.8) * mind).astype(np.float32)
+    got = ProjectMapPoints(proj, wp, nr, mx, mn, consider)
+    want = orbref.project_points(proj, wp, nr, mx, mn, consider)
+    same(got, want)
+    assert 30 < int(got[0].sum()) < len(wp) - 30, name
+    if not rules.get("check_view_angle"):
+        same(ProjectMapPoints(proj, wp, None, mx, mn, None), orbref.project_points(proj, wp, None, mx, mn, None))

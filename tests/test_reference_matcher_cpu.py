@@ -221,3 +221,72 @@ def test_search_by_projection_sim3(scene, ref, th):
         ok, R["u"], R["v"], radius, lvl - 1, lvl, scene["da"], ORB_SELECT_BEST, 50, valid=R["valid"], strict_levels=True, claimed=c["claimed"],
         check_orientation=False)
     assert no == R["nmatches"] and np.array_equal(ao, R["assigned"])
+
+
+# ---- the projection pre-loops as one flat routine (orb_project_points / orbref_project_points) ----
+def _neg_Rt_t(R, t):
+    """-R^T t with cv::Mat's rounding: the product accumulates in double, the result is float (negation is exact)."""
+    return (-(R.T.astype(np.float64) @ t.astype(np.float64))).astype(np.float32)
+
+
+def _predict_scale(maxd_raw, dist, logs):
+    """MapPoint::PredictScale (MapPoint.cc:357-366) with the host libm's logf."""
+    import ctypes as C
+    libm = C.CDLL("libm.so.6")
+    libm.logf.restype = C.c_float
+    libm.logf.argtypes = [C.c_float]
+    out = np.zeros(len(dist), np.int32)
+    for i in range(len(dist)):
+        if dist[i] > 0:
+            ratio = np.float32(maxd_raw[i]) / np.float32(dist[i])
+            out[i] = int(np.ceil(np.float32(libm.logf(float(ratio))) / np.float32(logs)))
+    return out
+
+
+def _rot(seed, amount):
+    rng = np.random.default_rng(seed)
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    return (np.eye(3) + np.sin(amount) * K + (1 - np.cos(amount)) * K @ K).astype(np.float32)
+
+
+@pytest.mark.parametrize("rot", [0.0, 0.05])
+def test_project_points_equals_reference_lines_kf(scene, ref, rot):
+    """orbref_project_points with the rules of SearchByProjection(Frame&, KeyFrame*) against the reference's lines :1491-1531 as
+    the driver replays them: valid set, u and v bit for bit."""
+    _, rc = frames(scene, ref, "a")
+    _, rk = frames(scene, ref, "a")
+    c = kf_projection_case(scene, ref, None)
+    Tc = c["Tc"].copy(); Tc[:3, :3] = _rot(3, rot)
+    R = ref.refm_search_by_projection_kf(rc, rk, c["xyz"], c["usable"], c["maxd"], c["mind"], c["claimed"], Tc, FX, FY, CX, CY, 10.0, 100, 0.9, True)
+    Rcw, tcw = Tc[:3, :3], Tc[:3, 3]
+    proj = dict(R1=Rcw, t1=tcw, Ow=_neg_Rt_t(Rcw, tcw), fx=FX, fy=FY, cx=CX, cy=CY, min_x=0, max_x=W, min_y=0, max_y=H,
+                invz_rule=0, uv_rule=0, bounds_rule=0, reject_negative_z=0, dist_rule=0, check_view_angle=0)
+    ok, u, v, ur, dist = ref.project_points(proj, c["xyz"], None, np.float32(1.2) * c["maxd"], np.float32(0.8) * c["mind"], c["usable"])
+    lvl = _predict_scale(c["maxd"], dist, np.log(np.float32(1.2)))
+    valid = (ok == 1) & (lvl >= 0) & (lvl < 8)
+    assert np.array_equal(valid.astype(np.uint8), R["valid"]) and valid.sum() > 500
+    assert np.array_equal(u[valid].view(np.uint32), R["u"][valid].view(np.uint32))
+    assert np.array_equal(v[valid].view(np.uint32), R["v"][valid].view(np.uint32))
+    assert np.array_equal(lvl[valid], R["level"][valid])
+
+
+@pytest.mark.parametrize("rot", [0.0, 0.04])
+def test_project_points_equals_reference_lines_sim3(scene, ref, rot):
+    """... with the rules of SearchByProjection(KeyFrame*, Scw, ...) against :298-360 (Sim3 decomposition included)."""
+    _, rk = frames(scene, ref, "a")
+    c = sim3_projection_case(scene)
+    S = c["S"].copy(); S[:3, :3] = (np.float32(1.1) * _rot(5, rot)).astype(np.float32)
+    R = ref.refm_search_by_projection_sim3(rk, S, c["xyz"], c["nrm"], c["usable"], c["maxd"], c["mind"], c["claimed"], FX, FY, CX, CY, 10, 0.9)
+    sR = S[:3, :3]
+    scw = np.float32(np.sqrt(np.sum(sR[0].astype(np.float64) * sR[0].astype(np.float64))))     # const float scw = sqrt(row.dot(row))
+    Rcw = (sR.astype(np.float64) / np.float64(scw)).astype(np.float32)                          # Mat / scalar: double, then float
+    tcw = (S[:3, 3].astype(np.float64) / np.float64(scw)).astype(np.float32)
+    proj = dict(R1=Rcw, t1=tcw, Ow=_neg_Rt_t(Rcw, tcw), fx=FX, fy=FY, cx=CX, cy=CY, min_x=0, max_x=W, min_y=0, max_y=H,
+                invz_rule=1, uv_rule=1, bounds_rule=1, reject_negative_z=1, dist_rule=0, check_view_angle=1)
+    ok, u, v, ur, dist = ref.project_points(proj, c["xyz"], c["nrm"], np.float32(1.2) * c["maxd"], np.float32(0.8) * c["mind"], c["usable"])
+    lvl = _predict_scale(c["maxd"], dist, np.log(np.float32(1.2)))
+    valid = (ok == 1) & (lvl >= 0) & (lvl < 8)
+    assert np.array_equal(valid.astype(np.uint8), R["valid"]) and valid.sum() > 150
+    assert np.array_equal(u[valid].view(np.uint32), R["u"][valid].view(np.uint32))
+    assert np.array_equal(v[valid].view(np.uint32), R["v"][valid].view(np.uint32))
