@@ -527,7 +527,7 @@ constexpr int FR_TPW = FR_COLS + 8;     // tile pitch in words: the columns + on
 constexpr int FR_TPB = FR_TPW * 4;
 constexpr int FR_ROWS = 30;          // rows per thread (cells are < 60 px high)
 
-struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells, use_tma; };   // byte offsets into dynamic shared memory
+struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells, use_tma, frame0; };   // byte offsets into dynamic shared memory
 
 __device__ __noinline__ uint32_t fast_arc_pair_rows_call(const uint8_t *p0, const uint8_t *p1, const uint32_t sgn) {
     return fast_arc_pair<FR_TPB>(p0, p1, sgn);
@@ -571,7 +571,7 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"((uint32_t)(FR_TPB * (g.hCell + 6))) : "memory");
             asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
                              (uint32_t)__cvta_generic_to_shared(tileW)),
-                         "l"(&tmap), "r"(4 * cbase), "r"(EDGE + y0 - 3), "r"(b), "r"(mbar)
+                         "l"(&tmap), "r"(4 * cbase), "r"(EDGE + y0 - 3), "r"(b + lay.frame0), "r"(mbar)
                          : "memory");
         }
         for (int i = tid; i < 2 * FR_TPW; i += FR_T) scoreW[i < FR_TPW ? i : (hc + 1) * FR_TPW + i - FR_TPW] = 0;   // apron rows -1 and hc
@@ -1542,6 +1542,7 @@ static void free_all(orb_extractor *ex) {
     if (ex->s_blur) cudaStreamDestroy(ex->s_blur);
     for (auto &e : ex->ev_fl) if (e) cudaEventDestroy(e);
     for (auto &e : ex->ev_ol) if (e) cudaEventDestroy(e);
+    for (auto &e : ex->ev_chunk) if (e) cudaEventDestroy(e);
     for (auto &q : ex->s_oct) if (q) cudaStreamDestroy(q);
     if (ex->stream) cudaStreamDestroy(ex->stream);
 }
@@ -1779,6 +1780,8 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 2 * sizeof(uint32_t)));
     ex->fast_rows = getenv("ORBGPU_FAST_CELLS") == nullptr;   // large batches: one CTA per cell-row segment on the big levels
     if (const char *e = getenv("ORBGPU_FAST_ROWS_MIN_PX")) ex->fast_rows_min_px = atoll(e);
+    if (const char *e = getenv("ORBGPU_CHUNK_MB")) ex->chunk_bytes = (size_t)std::max(0ll, atoll(e)) << 20;
+    for (auto &e : ex->ev_chunk) TRY_ALLOC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     {
         static std::mutex mu_rows;
         static bool rows_attr[64] = {};
@@ -1923,23 +1926,26 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     uint32_t *d_cand_count = ex->d_counts;
     uint32_t *d_kept_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels;
 
-    auto launch_pyr = [&](int l) {
+    // every per-frame array is addressed as base + frame * stride inside the kernels, so a sub-batch [b0, b0 + nb) of the call
+    // is the same launch with the bases moved (only the TMA tile of k_fast_rows takes the first frame as a coordinate)
+    auto launch_pyr = [&](int l, int b0, int nb) {
         NvtxRange nv("orbgpu:pyramid");
         const LevelGeom &g = G.lv[l];
+        uint8_t *pyr = ex->d_pyr + (size_t)b0 * G.pyr_frame;
         if (l == 0) {
             const int qL = (XOFF + 16) / 16, qR = std::max(qL, (g.w - 19 + XOFF) / 16 + 1);   // as in the kernel
-            dim3 grid((qR - qL + 31) / 32 + 1, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), batch);
-            k_pyr_level0<<<grid, 128, 0, st>>>(d_images, d_stride, d_pitch, ex->d_pyr, ex->d_geom);
+            dim3 grid((qR - qL + 31) / 32 + 1, (g.h + 2 * EDGE + 4 * L0_ROWS - 1) / (4 * L0_ROWS), nb);
+            k_pyr_level0<<<grid, 128, 0, st>>>(d_images + (size_t)b0 * d_stride, d_stride, d_pitch, pyr, ex->d_geom);
         } else if (g.fast_resize) {
             const int nw = g.pitch / 4;
             int bx = 128;   // CTA width that wastes the fewest threads on this level's row
             for (int c = 96; c >= 32; c -= 32)
                 if ((nw + c - 1) / c * c < (nw + bx - 1) / bx * bx) bx = c;
-            dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + PYR_ROWS - 1) / PYR_ROWS, batch);
-            k_pyr_resize<<<grid, bx, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + PYR_ROWS - 1) / PYR_ROWS, nb);
+            k_pyr_resize<<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
         } else {
-            dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, batch);
-            k_pyr_resize_generic<<<grid, 128, 0, st>>>(ex->d_pyr, ex->d_geom, ex->d_taps, l);
+            dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, nb);
+            k_pyr_resize_generic<<<grid, 128, 0, st>>>(pyr, ex->d_geom, ex->d_taps, l);
         }
         ex->launches++;
     };
@@ -1948,7 +1954,7 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     // instructions at level 0 of a 1241x376 frame, 236 us against 274 us per 288 frames); the small, corner-dense levels stay on
     // the per-cell kernel, whose many 2-warp CTAs keep more warps in flight (profiles/r2_fast_cells_vs_rows.txt).
     const bool rows_path = !small_call && ex->fast_rows;
-    auto launch_fast = [&](int l, cudaStream_t s) {
+    auto launch_fast = [&](int l, cudaStream_t s, int b0, int nb) {
         NvtxRange nv("orbgpu:fast_cells");
         const LevelGeom &g = G.lv[l];
         FastLevel fl;
@@ -1958,51 +1964,106 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         fl.interior_off = g.interior_off; fl.pyr_frame = G.pyr_frame;
         fl.w = g.w; fl.h = g.h; fl.ncx = g.ncx; fl.ncy = g.ncy;
         const size_t smem = fast_smem_layout(fl);
+        const uint8_t *pyr = ex->d_pyr + (size_t)b0 * G.pyr_frame;
+        uint32_t *cand = ex->d_cand + (size_t)b0 * G.cand_frame, *cnt = d_cand_count + (size_t)b0 * G.nlevels;
         if (rows_path && (long long)(g.w - 2 * EDGE) * (g.h - 2 * EDGE) >= ex->fast_rows_min_px) {
             FastRowsLayout lay;
             const size_t smem_rows = std::max(smem, fast_rows_layout(fl, lay));
             lay.use_tma = ex->tmap_ok[l] ? 1 : 0;
-            k_fast_rows<<<dim3((g.ncx + lay.seg_cells - 1) / lay.seg_cells, g.ncy, batch), FR_T, smem_rows, s>>>(
-                ex->d_pyr, fl, lay, ex->tmap[l], ex->d_cand, d_cand_count, ex->d_err);
+            lay.frame0 = b0;
+            k_fast_rows<<<dim3((g.ncx + lay.seg_cells - 1) / lay.seg_cells, g.ncy, nb), FR_T, smem_rows, s>>>(
+                pyr, fl, lay, ex->tmap[l], cand, cnt, ex->d_err);
         } else {
-            k_fast_cells<<<dim3(g.ncx, g.ncy, batch), FAST_T, smem, s>>>(ex->d_pyr, fl, ex->d_cand, d_cand_count, ex->d_err);
+            k_fast_cells<<<dim3(g.ncx, g.ncy, nb), FAST_T, smem, s>>>(pyr, fl, cand, cnt, ex->d_err);
         }
         ex->launches++;
     };
-    auto launch_blur = [&](int l, cudaStream_t s) {
+    auto launch_blur = [&](int l, cudaStream_t s, int b0, int nb) {
         NvtxRange nv("orbgpu:blur");
         const LevelGeom &g = G.lv[l];
-        dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, batch);
-        k_blur_planes<<<grid, 128, 0, s>>>(ex->d_pyr, ex->d_blur, ex->d_geom, l);
+        dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, nb);
+        k_blur_planes<<<grid, 128, 0, s>>>(ex->d_pyr + (size_t)b0 * G.pyr_frame, ex->d_blur + (size_t)b0 * G.pyr_frame, ex->d_geom, l);
         ex->launches++;
     };
-    auto launch_octree = [&](int l0, int nl, cudaStream_t s) {
+    auto launch_octree = [&](int l0, int nl, cudaStream_t s, int b0, int nb) {
         NvtxRange nv("orbgpu:octree");
-        k_octree<<<dim3(nl, batch), OCT_THREADS, octree_smem_bytes(G.max_nodes), s>>>(
-            ex->d_geom, ex->d_cand, d_cand_count, ex->d_node_of, ex->d_kept, d_kept_count, ex->d_err, l0);
+        k_octree<<<dim3(nl, nb), OCT_THREADS, octree_smem_bytes(G.max_nodes), s>>>(
+            ex->d_geom, ex->d_cand + (size_t)b0 * G.cand_frame, d_cand_count + (size_t)b0 * G.nlevels,
+            ex->d_node_of + (size_t)b0 * G.cand_frame, ex->d_kept + (size_t)b0 * G.kept_frame, d_kept_count + (size_t)b0 * G.nlevels,
+            ex->d_err, l0);
         ex->launches++;
     };
+    DescParams dp;
+    dp.nlevels = G.nlevels; dp.kept_frame = G.kept_frame; dp.pyr_frame = G.pyr_frame;
+    for (int l = 0, acc = 0; l < ORB_MAX_LEVELS; l++) {
+        const LevelGeom &lg = G.lv[l < G.nlevels ? l : G.nlevels - 1];
+        if (l < G.nlevels) acc += lg.kept_cap;
+        dp.lv[l].interior_off = lg.interior_off; dp.lv[l].cap_end = acc; dp.lv[l].kept_off = lg.kept_off; dp.lv[l].pitch = lg.pitch;
+        dp.lv[l].scale = lg.scale; dp.lv[l].size = lg.size;
+    }
+    auto launch_describe = [&](cudaStream_t s, int b0, int nb) {
+        NvtxRange nv("orbgpu:describe");
+        k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, nb), DESC_WARPS * 32, 0, s>>>(
+            ex->d_pyr + (size_t)b0 * G.pyr_frame, ex->d_blur + (size_t)b0 * G.pyr_frame, dp, ex->d_kept + (size_t)b0 * G.kept_frame,
+            d_kept_count + (size_t)b0 * G.nlevels, o_kp + (size_t)b0 * capacity, o_desc + (size_t)b0 * capacity * 32, o_n + b0, capacity,
+            ex->d_err);
+        ex->launches++;
+    };
+    // Large batches run as sub-batches whose planes (pyramid + blurred pyramid) stay in L2 from the kernel that writes them to
+    // the kernels that read them: the resize cascade of sub-batch c+1 runs on the handle's stream while FAST, the quadtree and
+    // blur + describe of sub-batch c run on three side streams; at most two sub-batches are in flight.
+    int chunk = 0;
+    if (!small_call && ex->overlap && !ex->profiling && ex->chunk_bytes > 0) {
+        chunk = (int)std::max<size_t>(8, ex->chunk_bytes / (2 * (size_t)G.pyr_frame));
+        if (chunk >= batch) chunk = 0;
+        else chunk = (batch + (batch + chunk - 1) / chunk - 1) / ((batch + chunk - 1) / chunk);   // equal sub-batches
+    }
     auto enqueue = [&]() -> int {   // everything of one extraction between the input copy and the output copy
         ORB_CUDA_TRY(cudaMemsetAsync(ex->d_counts, 0, (size_t)ex->prm.max_batch * G.nlevels * 2 * sizeof(uint32_t), st));
         ORB_CUDA_TRY(cudaMemsetAsync(o_n, 0, batch * sizeof(int32_t), st));
+        if (chunk > 0) {
+            cudaStream_t s_oct = ex->s_oct[0];
+            for (int b0 = 0, c = 0; b0 < batch; b0 += chunk, c++) {
+                const int nb = std::min(chunk, batch - b0);
+                if (c >= 2) ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_chunk[c & 1], 0));   // describe of sub-batch c-2 is done
+                for (int l = 0; l < G.nlevels; l++) {
+                    launch_pyr(l, b0, nb);
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
+                    launch_fast(l, ex->s_fast, b0, nb);
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
+                    launch_blur(l, ex->s_blur, b0, nb);
+                }
+                ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
+                ORB_CUDA_TRY(cudaStreamWaitEvent(s_oct, ex->ev_fast, 0));
+                launch_octree(0, G.nlevels, s_oct, b0, nb);
+                ORB_CUDA_TRY(cudaEventRecord(ex->ev_ol[0], s_oct));
+                ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_ol[0], 0));
+                launch_describe(ex->s_blur, b0, nb);
+                ORB_CUDA_TRY(cudaEventRecord(ex->ev_chunk[c & 1], ex->s_blur));
+            }
+            ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));   // the last describe: everything before it is ordered in front
+            ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
+            return ORB_OK;
+        }
         if (ex->overlap && !ex->profiling) {
             // level l's FAST cells and blur depend only on level l: they go to two side streams behind an event per level and
             // overlap the rest of the resize cascade (and each other); the handle's stream joins them where their results are read
             for (int l = 0; l < G.nlevels; l++) {
-                launch_pyr(l);
+                launch_pyr(l, 0, batch);
                 ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
                 ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
-                launch_fast(l, ex->s_fast);
+                launch_fast(l, ex->s_fast, 0, batch);
                 if (small_call) {
                     // latency mode: level l's quadtree (one CTA per frame, 34 us for a VGA level 0, 200 us for a 1080p one)
                     // starts on its own stream as soon as that level's candidates exist, beside the rest of the cascade
                     ORB_CUDA_TRY(cudaEventRecord(ex->ev_fl[l], ex->s_fast));
                     ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_oct[l], ex->ev_fl[l], 0));
-                    launch_octree(l, 1, ex->s_oct[l]);
+                    launch_octree(l, 1, ex->s_oct[l], 0, batch);
                     ORB_CUDA_TRY(cudaEventRecord(ex->ev_ol[l], ex->s_oct[l]));
                 }
                 ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
-                launch_blur(l, ex->s_blur);
+                launch_blur(l, ex->s_blur, 0, batch);
             }
             ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));
             if (small_call) {
@@ -2010,31 +2071,20 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             } else {
                 ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
                 ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fast, 0));
-                launch_octree(0, G.nlevels, st);   // (one launch per level on a side stream was measured at 288 frames: no gain)
+                launch_octree(0, G.nlevels, st, 0, batch);   // (one launch per level on a side stream was measured at 288 frames: no gain)
             }
             ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
         } else {
             prof_mark(ex, 1);
-            for (int l = 0; l < G.nlevels; l++) launch_pyr(l);
+            for (int l = 0; l < G.nlevels; l++) launch_pyr(l, 0, batch);
             prof_mark(ex, 2);
-            for (int l = 0; l < G.nlevels; l++) launch_fast(l, st);
+            for (int l = 0; l < G.nlevels; l++) launch_fast(l, st, 0, batch);
             prof_mark(ex, 3);
-            launch_octree(0, G.nlevels, st);
+            launch_octree(0, G.nlevels, st, 0, batch);
             prof_mark(ex, 4);
-            for (int l = 0; l < G.nlevels; l++) launch_blur(l, st);
+            for (int l = 0; l < G.nlevels; l++) launch_blur(l, st, 0, batch);
         }
-        NvtxRange nv("orbgpu:describe");
-        DescParams dp;
-        dp.nlevels = G.nlevels; dp.kept_frame = G.kept_frame; dp.pyr_frame = G.pyr_frame;
-        for (int l = 0, acc = 0; l < ORB_MAX_LEVELS; l++) {
-            const LevelGeom &lg = G.lv[l < G.nlevels ? l : G.nlevels - 1];
-            if (l < G.nlevels) acc += lg.kept_cap;
-            dp.lv[l].interior_off = lg.interior_off; dp.lv[l].cap_end = acc; dp.lv[l].kept_off = lg.kept_off; dp.lv[l].pitch = lg.pitch;
-            dp.lv[l].scale = lg.scale; dp.lv[l].size = lg.size;
-        }
-        k_describe<<<dim3((G.kept_frame + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(
-            ex->d_pyr, ex->d_blur, dp, ex->d_kept, d_kept_count, o_kp, o_desc, o_n, capacity, ex->d_err);
-        ex->launches++;
+        launch_describe(st, 0, batch);
         return ORB_OK;
     };
     const orb_extractor::GraphKey key = {d_images, d_stride, d_pitch, batch, width, height, capacity, o_kp, o_desc, o_n};

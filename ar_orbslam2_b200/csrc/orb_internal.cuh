@@ -117,6 +117,8 @@ struct orb_extractor {
     bool overlap = true;               // off while per-stage profiling is on (stage times need a serial schedule)
     // small calls (latency mode): the quadtree of level l runs on its own stream as soon as that level's FAST cells are done
     cudaStream_t s_oct[ORB_MAX_LEVELS] = {};
+    cudaEvent_t ev_chunk[2] = {};      // describe of a sub-batch is done (large batches run as L2-sized sub-batches)
+    size_t chunk_bytes = 0;             // pyramid + blurred planes of one sub-batch (ORBGPU_CHUNK_MB); 0 = whole batch at once
     cudaEvent_t ev_fl[ORB_MAX_LEVELS] = {}, ev_ol[ORB_MAX_LEVELS] = {};
     // CUDA graph of one extraction (two memsets + the 26 launches with their fork/join on the side streams): captured the
     // second time a call repeats the previous call's arguments, replayed from then on; any other call runs the plain

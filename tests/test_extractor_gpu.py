@@ -377,3 +377,23 @@ def test_large_batch_fast_equals_cell_kernel_and_geometry_change(gpu_lib, monkey
                 assert np.array_equal(ex.candidates(l, slot=i), ex_cells.candidates(l, slot=i)), (ww, i, l)
             assert a[i][0].tobytes() == b[i][0].tobytes() and np.array_equal(a[i][1], b[i][1]), (ww, i)
     ex.close(); ex_cells.close()
+
+
+def test_l2_sub_batches_give_the_same_bytes(oracle, gpu_lib, monkeypatch):
+    """ORBGPU_CHUNK_MB: a large batch run as sub-batches over four streams (ragged last sub-batch, k_fast_rows with a first-frame
+    coordinate in its TMA tile) against the whole batch at once and against the oracle's hash of every frame."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h, nb = 752, 480, 27
+    frames = np.stack([synth_frame(w, h, 500 + s) for s in range(nb)])
+    monkeypatch.setenv("ORBGPU_CHUNK_MB", "16")
+    monkeypatch.setenv("ORBGPU_FAST_ROWS_MIN_PX", "0")
+    ex = ORBextractor(1200, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    monkeypatch.delenv("ORBGPU_CHUNK_MB")
+    ex_whole = ORBextractor(1200, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    a, b = ex.extract_batch(frames), ex_whole.extract_batch(frames)
+    assert ex.launch_count > 2 * ex_whole.launch_count          # it did run as several sub-batches
+    for i in range(nb):
+        assert a[i][0].tobytes() == b[i][0].tobytes() and np.array_equal(a[i][1], b[i][1]), i
+    k, d = oracle.RefExtractor(1200).extract(frames[26])
+    assert a[26][0].tobytes() == k.tobytes() and np.array_equal(a[26][1], d)
+    ex.close(); ex_whole.close()
