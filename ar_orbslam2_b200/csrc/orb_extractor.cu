@@ -11,7 +11,8 @@
 // steps use explicit round-to-nearest intrinsics so nothing is contracted into an FMA.
 #include "orb_common.cuh"
 #include "orb_internal.cuh"
-#include <cuda.h>                // CUtensorMap (the encoder is fetched with cudaGetDriverEntryPoint: no link against libcuda)
+#include <cuda.h>
+#include <ctime>                // CUtensorMap (the encoder is fetched with cudaGetDriverEntryPoint: no link against libcuda)
 #include <nvtx3/nvToolsExt.h>   // header-only; the ranges cost a function-pointer test when no tool is attached
 #include "orb_pattern.h"
 
@@ -170,19 +171,15 @@ k_pyr_resize_generic(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, cons
 // row above and the one below, so the horizontally interpolated source rows are kept in registers across output rows:
 // ~1.2 source rows (3 aligned loads, 4 PRMT, 4 IDP2A) per output row instead of 2.
 constexpr int PYR_ROWS = 8;
-__global__ void __launch_bounds__(128)
-k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
-             const uint4 *__restrict__ wtab, int level) {
+template <int ROWS>
+__device__ __forceinline__ void pyr_resize_column(uint8_t *frame, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
+                                                  const uint4 *__restrict__ wtab, int level, int word, int py0) {
     const LevelGeom &g = G->lv[level];
     const LevelGeom &p = G->lv[level - 1];
-    const int word = blockIdx.x * blockDim.x + threadIdx.x;
-    const int b = blockIdx.z;
-    if (word * 4 >= g.pitch) return;
-    uint8_t *frame = pyr + (size_t)b * G->pyr_frame;
     const uint4 Wt = __ldg(wtab + 2 * (g.wtab_off + word)), St = __ldg(wtab + 2 * (g.wtab_off + word) + 1);
     const uint8_t *srcw = frame + p.interior_off + (size_t)St.z * 4;       // the window's first word in source row 0
     uint8_t *dst = frame + g.plane_off + (size_t)word * 4;
-    const int rows = g.h + 2 * EDGE, py0 = blockIdx.y * PYR_ROWS;
+    const int rows = g.h + 2 * EDGE;
     int rA = -1, rB = -1;
     uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
     auto hrow = [&](int sy, uint32_t *h) {   // (S[x]*a0 + S[x+1]*a1) >> 4 of source row sy for the four pixels
@@ -194,7 +191,7 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
         h[2] = __dp2a_lo(Wt.z, x23, 0u) >> 4; h[3] = __dp2a_hi(Wt.w, x23, 0u) >> 4;
     };
 #pragma unroll 2
-    for (int rr = 0; rr < PYR_ROWS; rr++) {
+    for (int rr = 0; rr < ROWS; rr++) {
         const int py = py0 + rr;
         if (py >= rows) break;
         const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
@@ -217,6 +214,16 @@ k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const Resize
         }
         *reinterpret_cast<uint32_t *>(dst + (size_t)py * g.pitch) = v;
     }
+}
+
+template <int ROWS>   // plane rows per thread: PYR_ROWS for batches (source rows reused in registers); fewer for single frames, where
+                      // the seven dependent launches are a latency chain and a thread's rows are its serial part
+__global__ void __launch_bounds__(128)
+k_pyr_resize(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
+             const uint4 *__restrict__ wtab, int level) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    if (word * 4 >= G->lv[level].pitch) return;
+    pyr_resize_column<ROWS>(pyr + (size_t)blockIdx.z * G->pyr_frame, G, taps, wtab, level, word, blockIdx.y * ROWS);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -849,7 +856,8 @@ __device__ __forceinline__ int quadrant_of(int x, int y, int nx0, int ny0, int n
     return (x < hx ? 0 : 1) + (y < hy ? 0 : 2);
 }
 
-__global__ void __launch_bounds__(OCT_THREADS)
+template <int NT>   // CTA size: 256 for batches (throughput), more for single frames (latency of the candidate loops)
+__global__ void __launch_bounds__(NT)
 k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const uint32_t *__restrict__ cand_count,
          uint16_t *__restrict__ node_of_pool, Kept *__restrict__ kept, uint32_t *__restrict__ kept_count,
          int *__restrict__ err, int level0) {
@@ -892,13 +900,13 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 
     int cur = 0;
     // ---- initial nodes (ref :530-567)
-    for (int i = tid; i < g.nIni; i += OCT_THREADS) {
+    for (int i = tid; i < g.nIni; i += NT) {
         S.x0[0][i] = (uint16_t)g.ini_x[i]; S.x1[0][i] = (uint16_t)g.ini_x[i + 1];
         S.y0[0][i] = 0; S.y1[0][i] = (uint16_t)g.win_h;
         S.cnt[0][i] = 0;
     }
     __syncthreads();
-    for (int c = tid; c < n; c += OCT_THREADS) {
+    for (int c = tid; c < n; c += NT) {
         const int x = C[c] & 0xfff;
         int node = (int)__fdiv_rn((float)x, g.hX);   // vpIniNodes[kp.pt.x / hX]
         node = min(node, g.nIni - 1);
@@ -907,10 +915,10 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
     }
     __syncthreads();
     // drop empty initial nodes, keep order
-    for (int i = tid; i < g.nIni; i += OCT_THREADS) S.scanA[i] = S.cnt[0][i] > 0 ? 1 : 0;
+    for (int i = tid; i < g.nIni; i += NT) S.scanA[i] = S.cnt[0][i] > 0 ? 1 : 0;
     __syncthreads();
     int m = block_exclusive_scan(S.scanA, g.nIni, warp_tot);
-    for (int i = tid; i < g.nIni; i += OCT_THREADS) {
+    for (int i = tid; i < g.nIni; i += NT) {
         if (S.cnt[0][i] > 0) {
             const int p = S.scanA[i];
             S.x0[1][p] = S.x0[0][i]; S.x1[1][p] = S.x1[0][i]; S.y0[1][p] = S.y0[0][i]; S.y1[1][p] = S.y1[0][i];
@@ -918,7 +926,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
         }
     }
     __syncthreads();
-    for (int c = tid; c < n; c += OCT_THREADS) node_of[c] = (uint16_t)S.scanA[node_of[c]];
+    for (int c = tid; c < n; c += NT) node_of[c] = (uint16_t)S.scanA[node_of[c]];
     cur = 1;
     if (tid == 0) { s_phase = 1; s_done = 0; }
     __syncthreads();
@@ -928,11 +936,11 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
         const int nxt = cur ^ 1;
         uint32_t *cnt = S.cnt[cur];
         const int phase = s_phase;
-        for (int i = tid; i < 4 * m; i += OCT_THREADS) S.ccount[i] = 0;
+        for (int i = tid; i < 4 * m; i += NT) S.ccount[i] = 0;
         if (tid == 0) { s_nexpand = 0; s_jstar = 0x7fffffff; }
         __syncthreads();
         // child occupancy of every divisible node
-        for (int c = tid; c < n; c += OCT_THREADS) {
+        for (int c = tid; c < n; c += NT) {
             const int a = node_of[c];
             if (cnt[a] > 1) {
                 const uint32_t pc = C[c];
@@ -944,7 +952,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 
         int K;   // children created in this pass
         if (phase == 1) {
-            for (int a = tid; a < m; a += OCT_THREADS) {
+            for (int a = tid; a < m; a += NT) {
                 const bool dv = cnt[a] > 1;
                 S.divided[a] = dv;
                 const uint32_t *cc = &S.ccount[4 * a];
@@ -957,7 +965,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             // walked from the back with (size, creation order) keys.
             int sort_n = 1;
             while (sort_n < m) sort_n <<= 1;
-            for (int a = tid; a < sort_n; a += OCT_THREADS) {
+            for (int a = tid; a < sort_n; a += NT) {
                 unsigned long long key = 0;
                 if (a < m) {
                     S.divided[a] = 0;
@@ -968,7 +976,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             __syncthreads();
             for (int k = 2; k <= sort_n; k <<= 1)
                 for (int j = k >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < sort_n; i += OCT_THREADS) {
+                    for (int i = tid; i < sort_n; i += NT) {
                         const int ixj = i ^ j;
                         if (ixj > i) {
                             const unsigned long long A = S.keys[i], B = S.keys[ixj];
@@ -979,7 +987,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
                     __syncthreads();
                 }
             // sorted index j -> node a_j; running list size after dividing j: m + sum_{i<=j}(k_i - 1)
-            for (int j = tid; j < m; j += OCT_THREADS) {
+            for (int j = tid; j < m; j += NT) {
                 const unsigned long long key = S.keys[j];
                 int kk = 0;
                 if (key) {
@@ -993,7 +1001,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             }
             __syncthreads();
             block_exclusive_scan(S.scanB, m, warp_tot);   // exclusive: growth before j
-            for (int j = tid; j < m; j += OCT_THREADS) {
+            for (int j = tid; j < m; j += NT) {
                 const unsigned long long key = S.keys[j];
                 if (key) {
                     const int after = m + S.scanB[j] + S.scanA[j] - 1;
@@ -1002,14 +1010,14 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             }
             __syncthreads();
             const int jstar = s_jstar;
-            for (int j = tid; j < m; j += OCT_THREADS) {
+            for (int j = tid; j < m; j += NT) {
                 const unsigned long long key = S.keys[j];
                 if (!key || j > jstar) S.scanA[j] = 0;
             }
             __syncthreads();
             K = block_exclusive_scan(S.scanA, m, warp_tot);   // creation base per sorted index
             // scatter the creation bases from sorted order back to list positions
-            for (int j = tid; j < m; j += OCT_THREADS) {
+            for (int j = tid; j < m; j += NT) {
                 const unsigned long long key = S.keys[j];
                 if (key && j <= jstar) {
                     const int a = 0xffff - (int)(key & 0xffff);
@@ -1018,11 +1026,11 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
                 }
             }
             __syncthreads();
-            for (int a = tid; a < m; a += OCT_THREADS) S.scanA[a] = S.divided[a] ? S.scanB[a] : 0;
+            for (int a = tid; a < m; a += NT) S.scanA[a] = S.divided[a] ? S.scanB[a] : 0;
             __syncthreads();
         }
         // rank of undivided nodes
-        for (int a = tid; a < m; a += OCT_THREADS) S.scanB[a] = S.divided[a] ? 0 : 1;
+        for (int a = tid; a < m; a += NT) S.scanB[a] = S.divided[a] ? 0 : 1;
         __syncthreads();
         const int U = block_exclusive_scan(S.scanB, m, warp_tot);
         const int m_new = K + U;
@@ -1031,7 +1039,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             return;
         }
         // build the new list
-        for (int a = tid; a < m; a += OCT_THREADS) {
+        for (int a = tid; a < m; a += NT) {
             const int ax0 = S.x0[cur][a], ay0 = S.y0[cur][a], ax1 = S.x1[cur][a], ay1 = S.y1[cur][a];
             if (S.divided[a]) {
                 const int hx = ax0 + ((ax1 - ax0 + 1) >> 1), hy = ay0 + ((ay1 - ay0 + 1) >> 1);
@@ -1062,7 +1070,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
             }
         }
         __syncthreads();
-        for (int c = tid; c < n; c += OCT_THREADS) {
+        for (int c = tid; c < n; c += NT) {
             const int a = node_of[c];
             if (S.divided[a]) {
                 const uint32_t pc = C[c];
@@ -1085,9 +1093,9 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 
     // ---- best keypoint per node (ref :713-730): max response, first in candidate order wins.
     unsigned long long *best = S.keys;
-    for (int a = tid; a < m; a += OCT_THREADS) best[a] = 0;
+    for (int a = tid; a < m; a += NT) best[a] = 0;
     __syncthreads();
-    for (int c = tid; c < n; c += OCT_THREADS) {
+    for (int c = tid; c < n; c += NT) {
         const uint32_t pc = C[c];
         const uint32_t x = pc & 0xfff, y = (pc >> 12) & 0xfff, r = pc >> 24;
         // candidate order = cells row-major, then row-major inside the cell (ref :758-793)
@@ -1097,7 +1105,7 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
         atomicMax(&best[node_of[c]], key);
     }
     __syncthreads();
-    for (int a = tid; a < m; a += OCT_THREADS) {
+    for (int a = tid; a < m; a += NT) {
         const unsigned long long key = best[a];
         const unsigned long long ord = ~key & 0xffffffffffull;
         if (a < g.kept_cap) {
@@ -1384,6 +1392,31 @@ using namespace orbgpu;
 // ------------------------------------------------------------------------------------------
 // Host side
 // ------------------------------------------------------------------------------------------
+// Results of a small call to the host without DMA copies: every D2H cudaMemcpyAsync costs 6-8 us of latency on the stream and a
+// blocking single-frame call made four of them (flags, counts, key points, descriptors).  One kernel writes the flags, the counts
+// and the n valid entries of every frame into pinned host memory (coalesced 4-byte stores across PCIe) instead.
+__global__ void __launch_bounds__(256)
+k_export_results(const uint32_t *__restrict__ kp, const uint32_t *__restrict__ desc, const int32_t *__restrict__ n, const int *__restrict__ err,
+                 int capacity, int batch, const uint32_t *__restrict__ ur, const uint32_t *__restrict__ dp, const int32_t *__restrict__ nm,
+                 int *__restrict__ h_head, uint32_t *__restrict__ h_land) {
+    const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+    const int nb = min(max(n[b], 0), capacity);
+    const size_t kp_words = (size_t)batch * capacity * 7, desc_words = (size_t)batch * capacity * 8;
+    const uint32_t *sk = kp + (size_t)b * capacity * 7, *sd = desc + (size_t)b * capacity * 8;
+    uint32_t *dk = h_land + (size_t)b * capacity * 7, *dd = h_land + kp_words + (size_t)b * capacity * 8;
+    for (int i = t; i < nb * 7; i += nt) dk[i] = sk[i];
+    for (int i = t; i < nb * 8; i += nt) dd[i] = sd[i];
+    if (b == 0) {
+        if (ur) {   // mvuRight / mvDepth of the left frame and the accepted-match count
+            uint32_t *du = h_land + kp_words + desc_words;
+            for (int i = t; i < nb; i += nt) { du[i] = ur[i]; du[capacity + i] = dp[i]; }
+            if (t == 0) du[2 * capacity] = (uint32_t)*nm;
+        }
+        if (t == 0) h_head[0] = *err;
+        if (t >= 1 && t <= batch) h_head[t] = n[t - 1];
+    }
+}
+
 static void prof_mark(orb_extractor *ex, int i) {
     if (ex->profiling) cudaEventRecord(ex->ev[i], ex->stream);
 }
@@ -1531,6 +1564,7 @@ static void free_all(orb_extractor *ex) {
     cudaFree(ex->d_out_desc); cudaFree(ex->d_out_n); cudaFree(ex->d_err); cudaFree(ex->stereo_scratch); cudaFree(ex->d_stereo_out);
     if (ex->h_pinned) cudaFreeHost(ex->h_pinned);
     if (ex->h_bounce) cudaFreeHost(ex->h_bounce);
+    if (ex->h_src) cudaFreeHost(ex->h_src);
     if (ex->gexec) cudaGraphExecDestroy(ex->gexec);
     for (auto &e : ex->ev) if (e) cudaEventDestroy(e);
     for (auto &e : ex->ev_lvl) if (e) cudaEventDestroy(e);
@@ -1544,6 +1578,7 @@ static void free_all(orb_extractor *ex) {
     for (auto &e : ex->ev_ol) if (e) cudaEventDestroy(e);
     for (auto &e : ex->ev_chunk) if (e) cudaEventDestroy(e);
     for (auto &q : ex->s_oct) if (q) cudaStreamDestroy(q);
+    for (auto &q : ex->s_bl) if (q) cudaStreamDestroy(q);
     if (ex->stream) cudaStreamDestroy(ex->stream);
 }
 
@@ -1682,6 +1717,14 @@ int orbgpu_ensure_out_staging(orb_extractor *ex, int batch, int capacity) {
     return ORB_OK;
 }
 
+void orbgpu_export_results(orb_extractor *ex, const orb_keypoint *kp, const uint8_t *desc, const int32_t *n, int batch, int capacity,
+                           const float *u_right, const float *depth, const int32_t *n_matched, cudaStream_t st) {
+    k_export_results<<<dim3(8, batch), 256, 0, st>>>((const uint32_t *)kp, (const uint32_t *)desc, n, ex->d_err, capacity, batch,
+                                                     (const uint32_t *)u_right, (const uint32_t *)depth, n_matched, ex->h_pinned,
+                                                     (uint32_t *)ex->h_bounce);
+    ex->launches++;
+}
+
 extern "C" {
 
 const char *orb_last_error(void) { return g_err; }
@@ -1730,6 +1773,7 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_blur, cudaEventDisableTiming));
     for (int l = 0; l < ORB_MAX_LEVELS; l++) {
         TRY_ALLOC(cudaStreamCreateWithFlags(&ex->s_oct[l], cudaStreamNonBlocking));
+        TRY_ALLOC(cudaStreamCreateWithFlags(&ex->s_bl[l], cudaStreamNonBlocking));
         TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_fl[l], cudaEventDisableTiming));
         TRY_ALLOC(cudaEventCreateWithFlags(&ex->ev_ol[l], cudaEventDisableTiming));
     }
@@ -1780,6 +1824,9 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaMalloc(&ex->d_counts, B * params->nlevels * 2 * sizeof(uint32_t)));
     ex->fast_rows = getenv("ORBGPU_FAST_CELLS") == nullptr;   // large batches: one CTA per cell-row segment on the big levels
     if (const char *e = getenv("ORBGPU_FAST_ROWS_MIN_PX")) ex->fast_rows_min_px = atoll(e);
+    ex->host_trace = getenv("ORBGPU_HOST_TRACE") != nullptr;
+    if (const char *e = getenv("ORBGPU_PYR_SMALL_ROWS")) ex->pyr_small_rows = atoi(e);
+    if (const char *e = getenv("ORBGPU_OCT_SMALL_THREADS")) ex->oct_small_threads = atoi(e);
     if (const char *e = getenv("ORBGPU_CHUNK_MB")) ex->chunk_bytes = (size_t)std::max(0ll, atoll(e)) << 20;
     for (auto &e : ex->ev_chunk) TRY_ALLOC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     {
@@ -1802,6 +1849,7 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     TRY_ALLOC(cudaMemsetAsync(ex->d_err, 0, sizeof(int), ex->stream));
     TRY_ALLOC(cudaMallocHost(&ex->h_pinned, (1 + B) * sizeof(int)));
     TRY_ALLOC(cudaMallocHost(&ex->h_bounce, ORB_BOUNCE_BYTES));
+    if (getenv("ORBGPU_NO_MAPPED_INPUT") == nullptr) TRY_ALLOC(cudaMallocHost(&ex->h_src, ORB_HSRC_BYTES));
     ex->oct_smem = octree_smem_bytes(maxn);
     {
         // cudaFuncAttributeMaxDynamicSharedMemorySize is per function and per device, not per handle: keep the largest request
@@ -1819,7 +1867,9 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
         std::lock_guard<std::mutex> lk(mu);
         size_t &cur = dev_max[ex->device & 63];
         if (ex->oct_smem > cur) {
-            TRY_ALLOC(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+            TRY_ALLOC(cudaFuncSetAttribute(k_octree<OCT_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+            TRY_ALLOC(cudaFuncSetAttribute(k_octree<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
+            TRY_ALLOC(cudaFuncSetAttribute(k_octree<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->oct_smem));
             cur = ex->oct_smem;
         }
     }
@@ -1830,6 +1880,10 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
 }
 
 void orb_extractor_destroy(orb_extractor *ex) {
+    if (ex && ex->host_trace && ex->trace_calls)
+        fprintf(stderr, "orbgpu host trace (us per host-output call over %lld calls): input %.1f | enqueue %.1f | wait %.1f | unpack %.1f\n",
+                (long long)ex->trace_calls, ex->trace_us[0] / ex->trace_calls, ex->trace_us[1] / ex->trace_calls,
+                ex->trace_us[2] / ex->trace_calls, ex->trace_us[3] / ex->trace_calls);
     if (!ex) return;
     cudaSetDevice(ex->device);
     cudaStreamSynchronize(ex->stream);
@@ -1892,28 +1946,43 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
 
     prof_collect(ex);
     prof_mark(ex, 0);
+    const bool trace = ex->host_trace;
+    auto now_us = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double tr0 = trace ? now_us() : 0;
     const uint8_t *d_images = images;
     size_t d_stride = frame_stride;
     int d_pitch = pitch;
+    const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
     if (image_loc == ORB_HOST) {
         NvtxRange nv("orbgpu:h2d");
-        if (((size_t)pitch * height == frame_stride || batch == 1) && (size_t)pitch * height * batch <= ex->src_bytes) {
+        const bool linear = (size_t)pitch * height == frame_stride || batch == 1;
+        const size_t lin_bytes = (size_t)pitch * height * (batch - 1) + (size_t)pitch * (height - 1) + width;
+        if (linear && small_call && out_loc == ORB_HOST && ex->h_src && lin_bytes <= ORB_HSRC_BYTES) {   // (a blocking call)
+            // latency mode: the frame goes into the handle's pinned, device-mapped buffer with a plain memcpy and k_pyr_level0
+            // reads it across PCIe -- no DMA copy in front of the first kernel (a pageable cudaMemcpyAsync of a VGA frame was
+            // 29 us of the call: the driver's staging copy plus the copy's own latency on the stream)
+            memcpy(ex->h_src, images, lin_bytes);
+            d_pitch = pitch;
+            d_stride = (size_t)pitch * height;
+            d_images = ex->h_src;
+        } else if (linear && (size_t)pitch * height * batch <= ex->src_bytes) {
             // the frames as they lie in host memory, row pitch included, in ONE linear copy (k_pyr_level0 takes any pitch): a
             // pitched copy from pageable memory goes row by row through the driver (measured 182 us for one 1241x376 frame)
             d_pitch = pitch;
             d_stride = (size_t)pitch * height;
             // (the last row of a view into a larger buffer holds `width` bytes, not `pitch`)
-            ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, images, (size_t)pitch * height * (batch - 1) + (size_t)pitch * (height - 1) + width,
-                                         cudaMemcpyHostToDevice, st));
+            ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, images, lin_bytes, cudaMemcpyHostToDevice, st));
+            d_images = ex->d_src;
         } else {
             d_pitch = (width + 127) / 128 * 128;
             d_stride = (size_t)d_pitch * height;
             for (int b = 0; b < batch; b++)
                 ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src + b * d_stride, d_pitch, images + b * frame_stride, pitch, width, height,
                                                cudaMemcpyHostToDevice, st));
+            d_images = ex->d_src;
         }
-        d_images = ex->d_src;
     }
+    const double tr1 = trace ? now_us() : 0;
     orb_keypoint *o_kp = keypoints;
     uint8_t *o_desc = descriptors;
     int32_t *o_n = n_out;
@@ -1922,6 +1991,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         if (rc != ORB_OK) return rc;
         o_kp = ex->d_out_kp; o_desc = ex->d_out_desc; o_n = ex->d_out_n;
     }
+    // small host-output calls: the results reach pinned host memory by one kernel at the end of the launch sequence
+    const bool export_host = out_loc == ORB_HOST && ex->h_bounce && (size_t)batch * capacity * (sizeof(orb_keypoint) + 32) <= ORB_BOUNCE_BYTES;
 
     uint32_t *d_cand_count = ex->d_counts;
     uint32_t *d_kept_count = ex->d_counts + (size_t)ex->prm.max_batch * G.nlevels;
@@ -1941,15 +2012,25 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             int bx = 128;   // CTA width that wastes the fewest threads on this level's row
             for (int c = 96; c >= 32; c -= 32)
                 if ((nw + c - 1) / c * c < (nw + bx - 1) / bx * bx) bx = c;
-            dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + PYR_ROWS - 1) / PYR_ROWS, nb);
-            k_pyr_resize<<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            if (small_call && ex->pyr_small_rows == 1) {
+                dim3 grid((nw + bx - 1) / bx, g.h + 2 * EDGE, nb);
+                k_pyr_resize<1><<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            } else if (small_call && ex->pyr_small_rows == 2) {
+                dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + 1) / 2, nb);
+                k_pyr_resize<2><<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            } else if (small_call && ex->pyr_small_rows == 4) {
+                dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + 3) / 4, nb);
+                k_pyr_resize<4><<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            } else {
+                dim3 grid((nw + bx - 1) / bx, (g.h + 2 * EDGE + PYR_ROWS - 1) / PYR_ROWS, nb);
+                k_pyr_resize<PYR_ROWS><<<grid, bx, 0, st>>>(pyr, ex->d_geom, ex->d_taps, ex->d_wtab, l);
+            }
         } else {
             dim3 grid((g.pitch / 4 + 127) / 128, g.h + 2 * EDGE, nb);
             k_pyr_resize_generic<<<grid, 128, 0, st>>>(pyr, ex->d_geom, ex->d_taps, l);
         }
         ex->launches++;
     };
-    const bool small_call = (size_t)batch * width * height <= ((size_t)4 << 20);   // launches, not kernels, are the wait
     // Large batches: levels with many pixels go through k_fast_rows (one CTA per segment of a cell row: 26 % fewer warp
     // instructions at level 0 of a 1241x376 frame, 236 us against 274 us per 288 frames); the small, corner-dense levels stay on
     // the per-cell kernel, whose many 2-warp CTAs keep more warps in flight (profiles/r2_fast_cells_vs_rows.txt).
@@ -1987,7 +2068,9 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
     };
     auto launch_octree = [&](int l0, int nl, cudaStream_t s, int b0, int nb) {
         NvtxRange nv("orbgpu:octree");
-        k_octree<<<dim3(nl, nb), OCT_THREADS, octree_smem_bytes(G.max_nodes), s>>>(
+        auto kern = small_call && ex->oct_small_threads == 1024 ? k_octree<1024> : small_call && ex->oct_small_threads == 512 ? k_octree<512> : k_octree<OCT_THREADS>;
+        const int nt = small_call && (ex->oct_small_threads == 1024 || ex->oct_small_threads == 512) ? ex->oct_small_threads : OCT_THREADS;
+        kern<<<dim3(nl, nb), nt, octree_smem_bytes(G.max_nodes), s>>>(
             ex->d_geom, ex->d_cand + (size_t)b0 * G.cand_frame, d_cand_count + (size_t)b0 * G.nlevels,
             ex->d_node_of + (size_t)b0 * G.cand_frame, ex->d_kept + (size_t)b0 * G.kept_frame, d_kept_count + (size_t)b0 * G.nlevels,
             ex->d_err, l0);
@@ -2049,31 +2132,44 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         if (ex->overlap && !ex->profiling) {
             // level l's FAST cells and blur depend only on level l: they go to two side streams behind an event per level and
             // overlap the rest of the resize cascade (and each other); the handle's stream joins them where their results are read
-            for (int l = 0; l < G.nlevels; l++) {
-                launch_pyr(l, 0, batch);
-                ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
-                ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
-                launch_fast(l, ex->s_fast, 0, batch);
-                if (small_call) {
-                    // latency mode: level l's quadtree (one CTA per frame, 34 us for a VGA level 0, 200 us for a 1080p one)
-                    // starts on its own stream as soon as that level's candidates exist, beside the rest of the cascade
-                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_fl[l], ex->s_fast));
-                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_oct[l], ex->ev_fl[l], 0));
+            if (small_call) {
+                // latency mode: the launches of one level are a chain of their own -- FAST cells, then that level's quadtree (one CTA
+                // per frame, 34 us for a VGA level 0) on stream l, the blur on stream l of a second set -- so a level waits for
+                // nothing but its own plane; on one side stream the eight FAST launches alone were a 60-us serial chain.
+                auto level_chains = [&](int l, cudaEvent_t ready) -> int {
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_oct[l], ready, 0));
+                    launch_fast(l, ex->s_oct[l], 0, batch);
                     launch_octree(l, 1, ex->s_oct[l], 0, batch);
                     ORB_CUDA_TRY(cudaEventRecord(ex->ev_ol[l], ex->s_oct[l]));
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_bl[l], ready, 0));
+                    launch_blur(l, ex->s_bl[l], 0, batch);
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_fl[l], ex->s_bl[l]));
+                    return ORB_OK;
+                };
+                for (int l = 0; l < G.nlevels; l++) {
+                    launch_pyr(l, 0, batch);
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
+                    if (int r = level_chains(l, ex->ev_lvl[l])) return r;
                 }
-                ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
-                launch_blur(l, ex->s_blur, 0, batch);
-            }
-            ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));
-            if (small_call) {
-                for (int l = 0; l < G.nlevels; l++) ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_ol[l], 0));
+                for (int l = 0; l < G.nlevels; l++) {
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_ol[l], 0));
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fl[l], 0));
+                }
             } else {
+                for (int l = 0; l < G.nlevels; l++) {
+                    launch_pyr(l, 0, batch);
+                    ORB_CUDA_TRY(cudaEventRecord(ex->ev_lvl[l], st));
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_fast, ex->ev_lvl[l], 0));
+                    launch_fast(l, ex->s_fast, 0, batch);
+                    ORB_CUDA_TRY(cudaStreamWaitEvent(ex->s_blur, ex->ev_lvl[l], 0));
+                    launch_blur(l, ex->s_blur, 0, batch);
+                }
+                ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));
                 ORB_CUDA_TRY(cudaEventRecord(ex->ev_fast, ex->s_fast));
                 ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_fast, 0));
                 launch_octree(0, G.nlevels, st, 0, batch);   // (one launch per level on a side stream was measured at 288 frames: no gain)
+                ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
             }
-            ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
         } else {
             prof_mark(ex, 1);
             for (int l = 0; l < G.nlevels; l++) launch_pyr(l, 0, batch);
@@ -2085,9 +2181,10 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             for (int l = 0; l < G.nlevels; l++) launch_blur(l, st, 0, batch);
         }
         launch_describe(st, 0, batch);
+        if (export_host) orbgpu_export_results(ex, o_kp, o_desc, o_n, batch, capacity, nullptr, nullptr, nullptr, st);
         return ORB_OK;
     };
-    const orb_extractor::GraphKey key = {d_images, d_stride, d_pitch, batch, width, height, capacity, o_kp, o_desc, o_n};
+    const orb_extractor::GraphKey key = {d_images, d_stride, d_pitch, batch, width, height, capacity, o_kp, o_desc, o_n, export_host ? 1 : 0};
     // a graph pays where the launches themselves are the wait (single frames, stereo pairs); large batches measured 1 %
     // slower as a graph than as stream launches (92.5 -> 91.7 k frames/s at 288 frames), so they keep the streams
     const bool graphable = ex->use_graph && ex->overlap && !ex->profiling && small_call;
@@ -2137,25 +2234,34 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
 
     if (out_loc == ORB_HOST) {
         NvtxRange nv("orbgpu:d2h");
-        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
-        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        // results: small ones (single frames, stereo pairs) land in the handle's pinned buffer with asynchronous copies and
-        // only the n valid entries of each frame are handed on; copies straight into pageable caller memory are synchronous
-        // staging round trips in the driver (measured 54 us of a 238 us VGA call).  Large batches copy straight to the caller.
+        // results: small ones (single frames, stereo pairs) are already on their way into the handle's pinned buffers (the export
+        // kernel above) and only the n valid entries of each frame are handed on; copies straight into pageable caller memory
+        // are synchronous staging round trips in the driver (measured 54 us of a 238 us VGA call).  Large batches copy straight
+        // to the caller.
         const size_t kp_bytes = (size_t)batch * capacity * sizeof(orb_keypoint), desc_bytes = (size_t)batch * capacity * 32;
-        const bool bounce = ex->h_bounce && kp_bytes + desc_bytes <= ORB_BOUNCE_BYTES;
-        ORB_CUDA_TRY(cudaMemcpyAsync(bounce ? (void *)ex->h_bounce : (void *)keypoints, o_kp, kp_bytes, cudaMemcpyDeviceToHost, st));
-        ORB_CUDA_TRY(cudaMemcpyAsync(bounce ? (void *)(ex->h_bounce + kp_bytes) : (void *)descriptors, o_desc, desc_bytes,
-                                     cudaMemcpyDeviceToHost, st));
+        const bool bounce = export_host;
+        if (!bounce) {
+            ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+            ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            ORB_CUDA_TRY(cudaMemcpyAsync((void *)keypoints, o_kp, kp_bytes, cudaMemcpyDeviceToHost, st));
+            ORB_CUDA_TRY(cudaMemcpyAsync((void *)descriptors, o_desc, desc_bytes, cudaMemcpyDeviceToHost, st));
+        }
         prof_mark(ex, 6);
         ex->ev_pending = ex->profiling;
+        const double tr2 = trace ? now_us() : 0;
         ORB_CUDA_TRY(cudaStreamSynchronize(st));
+        const double tr3 = trace ? now_us() : 0;
         if (bounce)
             for (int b = 0; b < batch; b++) {
                 const size_t n = (size_t)std::min(std::max(ex->h_pinned[1 + b], 0), capacity);
                 memcpy(keypoints + (size_t)b * capacity, ex->h_bounce + (size_t)b * capacity * sizeof(orb_keypoint), n * sizeof(orb_keypoint));
                 memcpy(descriptors + (size_t)b * capacity * 32, ex->h_bounce + kp_bytes + (size_t)b * capacity * 32, n * 32);
             }
+        if (trace) {
+            const double tr4 = now_us();
+            ex->trace_us[0] += tr1 - tr0; ex->trace_us[1] += tr2 - tr1; ex->trace_us[2] += tr3 - tr2; ex->trace_us[3] += tr4 - tr3;
+            ex->trace_calls++;
+        }
         for (int b = 0; b < batch; b++) n_out[b] = ex->h_pinned[1 + b];
         ex->last_counts.assign(ex->h_pinned + 1, ex->h_pinned + 1 + batch);
         ex->last_counts_valid = true;

@@ -59,6 +59,7 @@ struct Kept {   // a keypoint retained by the quadtree, level coordinates
 }  // namespace orbgpu
 
 constexpr size_t ORB_BOUNCE_BYTES = (size_t)1 << 20;
+constexpr size_t ORB_HSRC_BYTES = ((size_t)4 << 20) + ((size_t)1 << 19);   // frames of a small call (<= 4 MB of pixels) incl. row pitch
 
 struct orb_extractor {
     orb_params prm;
@@ -89,6 +90,7 @@ struct orb_extractor {
     size_t out_cap_elems = 0;
     int *d_err = nullptr;
     int *h_pinned = nullptr;           // [0]=err flags, [1..] counts
+    uint8_t *h_src = nullptr;          // pinned, device-mapped input buffer of small host-input calls (k_pyr_level0 reads it across PCIe)
     uint8_t *h_bounce = nullptr;       // pinned landing buffer for the results of small host-output calls
     float *d_stereo_out = nullptr;     // orb_stereo_frame: uRight[cap] | depth[cap] | n_matched
     size_t stereo_out_cap = 0;
@@ -116,7 +118,10 @@ struct orb_extractor {
     cudaEvent_t ev_lvl[ORB_MAX_LEVELS] = {}, ev_fast = nullptr, ev_blur = nullptr;
     bool overlap = true;               // off while per-stage profiling is on (stage times need a serial schedule)
     // small calls (latency mode): the quadtree of level l runs on its own stream as soon as that level's FAST cells are done
-    cudaStream_t s_oct[ORB_MAX_LEVELS] = {};
+    cudaStream_t s_oct[ORB_MAX_LEVELS] = {}, s_bl[ORB_MAX_LEVELS] = {};   // small calls: FAST + quadtree / blur of level l
+    bool host_trace = false; double trace_us[4] = {}; int64_t trace_calls = 0;   // ORBGPU_HOST_TRACE=1: where a blocking call's host time goes
+    int pyr_small_rows = 2;            // plane rows per thread of the resize in small calls (ORBGPU_PYR_SMALL_ROWS: 2 / 4 / 8)
+    int oct_small_threads = 512;       // CTA size of the quadtree in small calls (ORBGPU_OCT_SMALL_THREADS: 256 / 512 / 1024)
     cudaEvent_t ev_chunk[2] = {};      // describe of a sub-batch is done (large batches run as L2-sized sub-batches)
     size_t chunk_bytes = 0;             // pyramid + blurred planes of one sub-batch (ORBGPU_CHUNK_MB); 0 = whole batch at once
     cudaEvent_t ev_fl[ORB_MAX_LEVELS] = {}, ev_ol[ORB_MAX_LEVELS] = {};
@@ -124,10 +129,10 @@ struct orb_extractor {
     // second time a call repeats the previous call's arguments, replayed from then on; any other call runs the plain
     // launches.  One graph launch instead of 28 enqueues + 20 event operations is what a single-frame call waits for.
     struct GraphKey {
-        const void *images; size_t stride; int pitch, batch, width, height, capacity; void *kp, *desc, *n;
+        const void *images; size_t stride; int pitch, batch, width, height, capacity; void *kp, *desc, *n; int export_host;
         bool operator==(const GraphKey &o) const {
             return images == o.images && stride == o.stride && pitch == o.pitch && batch == o.batch && width == o.width &&
-                   height == o.height && capacity == o.capacity && kp == o.kp && desc == o.desc && n == o.n;
+                   height == o.height && capacity == o.capacity && kp == o.kp && desc == o.desc && n == o.n && export_host == o.export_host;
         }
     };
     GraphKey gkey = {}, glast = {};
@@ -143,3 +148,8 @@ int orbgpu_undistort_keypoints_async(const orb_keypoint *keys, int n, float fx, 
 
 // grows the handle's device staging for `batch` x `capacity` keypoints + descriptors (drops a captured graph that holds the old pointers)
 int orbgpu_ensure_out_staging(orb_extractor *ex, int batch, int capacity);
+/* Results of a small host-output call straight into the handle's pinned landing buffers by ONE kernel (the valid entries of every
+ * frame only): h_pinned = {err flags, n[batch]}, h_bounce = key points | descriptors [| uRight | depth | n_matched], the layout the
+ * host side unpacks.  u_right == nullptr: extraction only. */
+void orbgpu_export_results(orb_extractor *ex, const orb_keypoint *kp, const uint8_t *desc, const int32_t *n, int batch, int capacity,
+                           const float *u_right, const float *depth, const int32_t *n_matched, cudaStream_t st);

@@ -450,8 +450,14 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
     // both frames into the handle's source slots 0 and 1 (linear copies when the two pitches agree and fit)
     int d_pitch = pitch_left;
     size_t d_stride = (size_t)pitch_left * height;
-    if (pitch_left == pitch_right && 2 * d_stride <= ex->src_bytes) {
-        const size_t used = (size_t)pitch_left * (height - 1) + width;   // the last row of a view holds `width` bytes, not `pitch`
+    const uint8_t *src = ex->d_src;
+    const size_t used = (size_t)pitch_left * (height - 1) + width;   // the last row of a view holds `width` bytes, not `pitch`
+    if (pitch_left == pitch_right && ex->h_src && d_stride + used <= ORB_HSRC_BYTES && 2 * (size_t)width * height <= ((size_t)4 << 20)) {
+        // both frames into the pinned, device-mapped input buffer: k_pyr_level0 reads them across PCIe (see orb_extract_batch)
+        memcpy(ex->h_src, image_left, used);
+        memcpy(ex->h_src + d_stride, image_right, used);
+        src = ex->h_src;
+    } else if (pitch_left == pitch_right && 2 * d_stride <= ex->src_bytes) {
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src, image_left, used, cudaMemcpyHostToDevice, st));
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_src + d_stride, image_right, used, cudaMemcpyHostToDevice, st));
     } else {
@@ -460,7 +466,7 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
         ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src, d_pitch, image_left, pitch_left, width, height, cudaMemcpyHostToDevice, st));
         ORB_CUDA_TRY(cudaMemcpy2DAsync(ex->d_src + d_stride, d_pitch, image_right, pitch_right, width, height, cudaMemcpyHostToDevice, st));
     }
-    rc = orb_extract_batch(ex, ex->d_src, 2, width, height, d_pitch, d_stride, ORB_DEVICE, ex->d_out_kp, ex->d_out_desc, capacity,
+    rc = orb_extract_batch(ex, src, 2, width, height, d_pitch, d_stride, ORB_DEVICE, ex->d_out_kp, ex->d_out_desc, capacity,
                            ex->d_out_n, ORB_DEVICE);
     if (rc != ORB_OK) return rc;
     float *d_ur = ex->d_stereo_out, *d_dp = d_ur + capacity;
@@ -469,17 +475,22 @@ int orb_stereo_frame(orb_extractor *ex, const uint8_t *image_left, const uint8_t
     rc = orb_stereo_match_batch(ex, 0, ex, 1, 1, ex->d_out_kp, ex->d_out_desc, ex->d_out_n, ex->d_out_kp + capacity,
                                 ex->d_out_desc + (size_t)capacity * 32, ex->d_out_n + 1, capacity, mbf, mb, d_ur, d_dp, d_nm, ORB_DEVICE);
     if (rc != ORB_OK) return rc;
-    // everything back with asynchronous copies into pinned memory, one synchronisation
+    // everything back into pinned memory, one synchronisation
     const size_t kp_bytes = (size_t)2 * capacity * sizeof(orb_keypoint), desc_bytes = (size_t)2 * capacity * 32, f_bytes = (size_t)capacity * 4;
     const bool bounce = ex->h_bounce && kp_bytes + desc_bytes + 2 * f_bytes + 4 <= ORB_BOUNCE_BYTES;
     std::vector<uint8_t> big;
     uint8_t *land = ex->h_bounce;
     if (!bounce) { big.resize(kp_bytes + desc_bytes + 2 * f_bytes + 4); land = big.data(); }
-    ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, ex->d_out_n, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(land, ex->d_out_kp, kp_bytes, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes, ex->d_out_desc, desc_bytes, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes + desc_bytes, d_ur, 2 * f_bytes + 4, cudaMemcpyDeviceToHost, st));
+    if (bounce) {   // one kernel writes flags, counts and the valid entries of all five arrays into the pinned buffers
+        orbgpu_export_results(ex, ex->d_out_kp, ex->d_out_desc, ex->d_out_n, 2, capacity, d_ur, d_dp, d_nm, st);
+        ORB_CUDA_TRY(cudaGetLastError());
+    } else {
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned, ex->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(ex->h_pinned + 1, ex->d_out_n, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(land, ex->d_out_kp, kp_bytes, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes, ex->d_out_desc, desc_bytes, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(land + kp_bytes + desc_bytes, d_ur, 2 * f_bytes + 4, cudaMemcpyDeviceToHost, st));
+    }
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
     const int flags = ex->h_pinned[0];
     *n_left = ex->h_pinned[1]; *n_right = ex->h_pinned[2];

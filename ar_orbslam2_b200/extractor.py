@@ -27,6 +27,7 @@ class ORBextractor:
         _lib.check(self._L.orb_extractor_tables(self._h, ptr(self._scale), ptr(self._inv_scale), ptr(self._sigma2),
                                                 ptr(self._inv_sigma2), ptr(self._per_level)), "orb_extractor_tables")
         self.default_capacity = nfeatures + 4 * nlevels + 256
+        self._landing = {}
         _lib.register(self)
 
     def close(self):
@@ -59,12 +60,14 @@ class ORBextractor:
         if image.strides[1] != 1:
             image = np.ascontiguousarray(image)
         cap = capacity or self.default_capacity
-        kps = np.zeros(cap, KEYPOINT_DTYPE)
-        desc = np.zeros((cap, 32), np.uint8)
-        n = C.c_int(0)
+        land = self._landing.get(cap)
+        if land is None:   # landing arrays (and their ctypes pointers) are made once per capacity: the call is latency-critical
+            kps, desc, n = np.zeros(cap, KEYPOINT_DTYPE), np.zeros((cap, 32), np.uint8), C.c_int(0)
+            land = self._landing[cap] = (kps, desc, n, ptr(kps), ptr(desc), C.byref(n))
+        kps, desc, n, p_kps, p_desc, p_n = land
         h, w = image.shape
-        _lib.check(self._L.orb_extract(self._h, ptr(image), w, h, image.strides[0], ORB_HOST, ptr(kps), ptr(desc), cap,
-                                       C.byref(n)), "orb_extract")
+        _lib.check(self._L.orb_extract(self._h, C.c_void_p(image.ctypes.data), w, h, image.strides[0], ORB_HOST, p_kps, p_desc, cap, p_n),
+                   "orb_extract")
         return kps[: n.value].copy(), desc[: n.value].copy()
 
     def extract_batch(self, images: np.ndarray, capacity: int | None = None):

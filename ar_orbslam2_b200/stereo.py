@@ -58,12 +58,15 @@ def StereoFrame(extractor, image_left, image_right, mbf: float, mb: float, capac
         ir = np.ascontiguousarray(ir)
     h, w = il.shape
     cap = capacity or extractor.default_capacity
-    kl, kr = np.zeros(cap, KEYPOINT_DTYPE), np.zeros(cap, KEYPOINT_DTYPE)
-    dl, dr = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
-    ur, dp = np.full(cap, -1, np.float32), np.full(cap, -1, np.float32)
-    nl, nr, nm = C.c_int(0), C.c_int(0), C.c_int(0)
-    rc = L.orb_stereo_frame(extractor._h, ptr(il), ptr(ir), w, h, il.strides[0], ir.strides[0], ptr(kl), ptr(dl), C.byref(nl),
-                            ptr(kr), ptr(dr), C.byref(nr), cap, C.c_float(mbf), C.c_float(mb), ptr(ur), ptr(dp), C.byref(nm))
+    land = extractor._landing.get(("stereo", cap))
+    if land is None:   # landing arrays and their ctypes pointers are made once per capacity: the call is latency-critical
+        arrs = (np.zeros(cap, KEYPOINT_DTYPE), np.zeros((cap, 32), np.uint8), np.zeros(cap, KEYPOINT_DTYPE), np.zeros((cap, 32), np.uint8),
+                np.full(cap, -1, np.float32), np.full(cap, -1, np.float32))
+        cnt = (C.c_int(0), C.c_int(0), C.c_int(0))
+        land = extractor._landing[("stereo", cap)] = (arrs, cnt, tuple(ptr(a) for a in arrs), tuple(C.byref(c) for c in cnt))
+    (kl, dl, kr, dr, ur, dp), (nl, nr, nm), (p_kl, p_dl, p_kr, p_dr, p_ur, p_dp), (p_nl, p_nr, p_nm) = land
+    rc = L.orb_stereo_frame(extractor._h, C.c_void_p(il.ctypes.data), C.c_void_p(ir.ctypes.data), w, h, il.strides[0], ir.strides[0],
+                            p_kl, p_dl, p_nl, p_kr, p_dr, p_nr, cap, C.c_float(mbf), C.c_float(mb), p_ur, p_dp, p_nm)
     if not (rc == ORB_ERR_EMPTY and allow_empty):
         _lib.check(rc, "orb_stereo_frame")
     a, b = nl.value, nr.value

@@ -190,7 +190,7 @@ def test_graph_replay_matches_oracle(oracle, gpu_lib, monkeypatch):
         rk, rd = ref.extract(img)
         assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd), f"call {i}"
         per_call = per_call or ex.launch_count - l0
-        assert ex.launch_count - l0 == per_call == 33       # 8 x (pyramid, FAST, quadtree, blur) + describe; replays count too
+        assert ex.launch_count - l0 == per_call == 34       # 8 x (pyramid, FAST, quadtree, blur) + describe + result export; replays count too
     assert ex.graph_replays == 3                             # call 0 plain, call 1 captured, calls 2-4 replayed
     img = synth_frame(400, 300, 36)                          # other geometry: graph dropped, plain launches
     gk, gd = ex(img)
@@ -211,7 +211,7 @@ def test_graph_replay_matches_oracle(oracle, gpu_lib, monkeypatch):
         gk, gd = ex(img)
         rk, rd = ref.extract(img)
         assert gk.tobytes() == rk.tobytes() and np.array_equal(gd, rd)
-    assert ex.graph_replays == 0 and ex.launch_count == 3 * 33
+    assert ex.graph_replays == 0 and ex.launch_count == 3 * 34
     ex.close()
 
 
