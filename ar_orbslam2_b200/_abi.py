@@ -147,3 +147,10 @@ def frustum_outputs(n):
 def optr(a):
     """pointer or NULL"""
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class OrbCvOrbParams(C.Structure):
+    """orb_cvorb_params (include/orbgpu.h): the arguments of OpenCV's cv::ORB constructor the marker path uses."""
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32), ("edge_threshold", C.c_int32),
+                ("score_type", C.c_int32), ("fast_threshold", C.c_int32), ("max_width", C.c_int32), ("max_height", C.c_int32),
+                ("device", C.c_int32)]

@@ -449,6 +449,45 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
 int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio,
                              int max_dist, int loc, int32_t *train_idx, int32_t *dist);
 
+/* ---- OpenCV-style cv::ORB (Harris score) for the marker pipeline --------------- */
+
+/* ref: `ORB orb; orb(mImage1, Mat(), mvKeys1, mDescriptors1);` in Marker::setTargetImage (src/Marker.cc:83-84) and the same
+ * call on the camera image in Marker::Match (:107-108).  This is OpenCV's own ORB (features2d/src/orb.cpp), NOT
+ * ORBextractor: whole-layer FAST-9/16 with 3x3 non-maximum suppression at `fast_threshold`, key points closer than
+ * `edge_threshold` to the layer edge dropped, the 2*quota best by FAST score kept (KeyPointsFilter::retainBest: everything
+ * tied with the boundary response stays), Harris response (7x7 block, k = 0.04) of those, the quota best by Harris kept,
+ * intensity-centroid angle, 7x7 sigma-2 blur, 256 rotated tests (double cos/sin of the angle).  Layers: level l has
+ * cvRound(cols / (float)pow(scale, l)) columns, built by a cascade of resize(INTER_LINEAR_EXACT).  Arithmetic and key-point
+ * ORDER (what std::nth_element + std::partition leave behind) are pinned against cv2 4.13.0's ORB_create(); OpenCV 2.4's
+ * ORB (the version the reference was built with) resizes with INTER_LINEAR and is UNVERIFIED here (no OpenCV 2.4 on the
+ * build box).  Defaults of `ORB orb;` : 500, 1.2f, 8, 31, score_type 0 (HARRIS_SCORE; 1 = FAST_SCORE), fast_threshold 20;
+ * firstLevel 0, WTA_K 2 and patchSize 31 are fixed.                                                                   */
+typedef struct orb_cvorb_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;         /* 1..ORB_MAX_LEVELS */
+    int32_t edge_threshold;  /* >= 31 (the descriptor and moment windows must stay inside the layer) */
+    int32_t score_type;      /* 0 HARRIS_SCORE, 1 FAST_SCORE */
+    int32_t fast_threshold;
+    int32_t max_width;       /* largest image this handle will see */
+    int32_t max_height;
+    int32_t device;          /* CUDA device ordinal, -1 = current */
+} orb_cvorb_params;
+typedef struct orb_cvorb orb_cvorb;
+int orb_cvorb_create(const orb_cvorb_params *params, orb_cvorb **out);
+void orb_cvorb_destroy(orb_cvorb *h);
+/* capacity that always suffices for an image of the handle's maximum size (FAST ties can keep more than nfeatures) */
+int orb_cvorb_capacity(const orb_cvorb *h);
+/* `cv::ORB::operator()(image, noArray(), keypoints, descriptors)`: 8-bit single-channel image (image_loc = ORB_HOST or
+ * ORB_DEVICE), results to host arrays; *n_out key points in OpenCV's order, descriptors n_out x 32.  An empty image or
+ * one without key points gives *n_out = 0.  ORB_ERR_CAPACITY (with *n_out = the needed size) if capacity is too small. */
+int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, int height, int pitch, int image_loc,
+                                 orb_keypoint *keypoints, uint8_t *descriptors, int capacity, int *n_out);
+/* debugging / tests: layer `level` of the last call (blurred = what the descriptors sampled), its size */
+int orb_cvorb_level(orb_cvorb *h, int level, uint8_t *dst, int dst_pitch, int *width, int *height);
+void *orb_cvorb_stream(orb_cvorb *h);
+int64_t orb_cvorb_launch_count(const orb_cvorb *h);
+
 /* ---- colour -> grey in front of the extractor ---------------------------------- */
 
 /* ref: cvtColor(mImGray, mImGray, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) in

@@ -81,6 +81,13 @@ int orbref_cvt_color_gray(const uint8_t *src, int width, int height, int src_pit
                           uint8_t *dst, int dst_pitch);
 /* cv::undistortPoints(src, dst, K, D, noArray(), K) (orbref_undistort.cpp) */
 int orbref_undistort_points(const float *xy, int n, float fx, float fy, float cx, float cy, const float *dist, int ndist, float *out);
+/* OpenCV's cv::ORB with Harris score (orbref_cvorb.cpp), pinned to cv2 4.13 */
+int orbref_cvorb_detect_and_compute(const orb_cvorb_params *p, const uint8_t *image, int width, int height, int pitch,
+                                    orb_keypoint *kps, uint8_t *desc, int capacity, int *n_out);
+int orbref_cvorb_level(const orb_cvorb_params *p, const uint8_t *image, int width, int height, int pitch, int level, int blurred,
+                       uint8_t *dst, int dst_pitch, int *w, int *h);
+int orbref_gaussian_blur7_sep32f(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch);
+int orbref_resize_linear_exact(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 /* primitives (golden-vector tests against cv2) */
 int orbref_resize_linear(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 int orbref_gaussian_blur7(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch, int taps);

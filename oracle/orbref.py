@@ -724,3 +724,51 @@ def remap_linear(src, map_x, map_y):
     out = np.zeros((dh, dw), np.uint8)
     _check(lib().orbref_remap_linear(ptr(s), s.shape[1], s.shape[0], s.strides[0], ptr(mx), ptr(my), dw, ptr(out), dw, dh, dw), "remap_linear")
     return out
+
+
+def resize_linear_exact(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    """cv::resize(..., INTER_LINEAR_EXACT), 8UC1."""
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    _check(lib().orbref_resize_linear_exact(ptr(src), src.shape[1], src.shape[0], src.strides[0], ptr(dst), dw, dh, dw), "resize_exact")
+    return dst
+
+
+def cv_orb(img, nfeatures=500, scale_factor=1.2, nlevels=8, edge_threshold=31, score_type=0, fast_threshold=20):
+    """OpenCV's cv::ORB (Harris score) detectAndCompute as Marker.cc:83-84,107-108 calls it."""
+    from ar_orbslam2_b200._abi import OrbCvOrbParams
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    p = OrbCvOrbParams(nfeatures, scale_factor, nlevels, edge_threshold, score_type, fast_threshold, w, h, -1)
+    cap = nfeatures + 4096
+    while True:
+        kps = np.zeros(cap, KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        rc = lib().orbref_cvorb_detect_and_compute(C.byref(p), ptr(img), w, h, img.strides[0], ptr(kps), ptr(desc), cap, C.byref(n))
+        if rc == -4:
+            cap = n.value
+            continue
+        _check(rc, "cvorb")
+        return kps[: n.value].copy(), desc[: n.value].copy()
+
+
+def cv_orb_level(img, level, blurred=False, nfeatures=500, scale_factor=1.2, nlevels=8, edge_threshold=31, score_type=0,
+                 fast_threshold=20):
+    from ar_orbslam2_b200._abi import OrbCvOrbParams
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    p = OrbCvOrbParams(nfeatures, scale_factor, nlevels, edge_threshold, score_type, fast_threshold, w, h, -1)
+    lw, lh = C.c_int(), C.c_int()
+    _check(lib().orbref_cvorb_level(C.byref(p), ptr(img), w, h, img.strides[0], level, int(blurred), None, 0, C.byref(lw), C.byref(lh)), "lvl")
+    out = np.zeros((lh.value, lw.value), np.uint8)
+    _check(lib().orbref_cvorb_level(C.byref(p), ptr(img), w, h, img.strides[0], level, int(blurred), ptr(out), lw.value, None, None), "lvl")
+    return out
+
+
+def gaussian_blur7_sep32f(src: np.ndarray) -> np.ndarray:
+    """GaussianBlur(7x7, sigma 2, REFLECT_101) through OpenCV's float sepFilter2D path (what cv::ORB's layers get)."""
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros_like(src)
+    _check(lib().orbref_gaussian_blur7_sep32f(ptr(src), src.shape[1], src.shape[0], src.strides[0], ptr(dst), dst.strides[0]), "blur32f")
+    return dst
