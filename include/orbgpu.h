@@ -485,6 +485,10 @@ int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, 
                                  orb_keypoint *keypoints, uint8_t *descriptors, int capacity, int *n_out);
 /* debugging / tests: layer `level` of the last call (blurred = what the descriptors sampled), its size */
 int orb_cvorb_level(orb_cvorb *h, int level, uint8_t *dst, int dst_pitch, int *width, int *height);
+/* tests: KeyPointsFilter::retainBest alone, on `n` host responses: order_out receives the surviving original indices in the
+ * order std::nth_element + std::partition leave them (depth_limit < 0: libstdc++'s own 2*floor(log2 n); >= 0 forces the
+ * heap-select fallback of __introselect after that many partitions).                                                */
+int orb_debug_retain_best(const float *responses, int n, int n_points, int depth_limit, int32_t *order_out, int *n_out);
 void *orb_cvorb_stream(orb_cvorb *h);
 int64_t orb_cvorb_launch_count(const orb_cvorb *h);
 

@@ -86,6 +86,7 @@ int orbref_cvorb_detect_and_compute(const orb_cvorb_params *p, const uint8_t *im
                                     orb_keypoint *kps, uint8_t *desc, int capacity, int *n_out);
 int orbref_cvorb_level(const orb_cvorb_params *p, const uint8_t *image, int width, int height, int pitch, int level, int blurred,
                        uint8_t *dst, int dst_pitch, int *w, int *h);
+int orbref_retain_best(const float *responses, int n, int n_points, int depth_limit, int32_t *order_out, int *n_out);
 int orbref_gaussian_blur7_sep32f(const uint8_t *src, int w, int h, int spitch, uint8_t *dst, int dpitch);
 int orbref_resize_linear_exact(const uint8_t *src, int sw, int sh, int spitch, uint8_t *dst, int dw, int dh, int dpitch);
 /* primitives (golden-vector tests against cv2) */

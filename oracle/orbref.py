@@ -772,3 +772,12 @@ def gaussian_blur7_sep32f(src: np.ndarray) -> np.ndarray:
     dst = np.zeros_like(src)
     _check(lib().orbref_gaussian_blur7_sep32f(ptr(src), src.shape[1], src.shape[0], src.strides[0], ptr(dst), dst.strides[0]), "blur32f")
     return dst
+
+
+def retain_best(responses, n_points, depth_limit=-1):
+    """KeyPointsFilter::retainBest: surviving original indices in the order std::nth_element + std::partition leave."""
+    r = np.ascontiguousarray(responses, np.float32)
+    order = np.zeros(max(len(r), 1), np.int32)
+    n = C.c_int(0)
+    _check(lib().orbref_retain_best(ptr(r), len(r), int(n_points), int(depth_limit), ptr(order), C.byref(n)), "retain_best")
+    return order[: n.value].copy()

@@ -348,6 +348,26 @@ int orbref_cvorb_detect_and_compute(const orb_cvorb_params *p, const uint8_t *im
     return ORB_OK;
 }
 
+/* KeyPointsFilter::retainBest on bare responses: std::nth_element + std::partition of this libstdc++ (depth_limit < 0), or
+ * libstdc++'s own __introselect with a forced depth limit (the heap-select fallback the device restates). */
+int orbref_retain_best(const float *responses, int n, int n_points, int depth_limit, int32_t *order_out, int *n_out) {
+    std::vector<KP> k(n);
+    for (int i = 0; i < n; i++) k[i] = KP{0, 0, 0, 0, responses[i], i, 0};
+    if (depth_limit < 0) retain_best(k, n_points);
+    else if (n_points >= 0 && k.size() > (size_t)n_points) {
+        if (n_points == 0) k.clear();
+        else {
+            std::__introselect(k.begin(), k.begin() + n_points - 1, k.end(), depth_limit, __gnu_cxx::__ops::__iter_comp_iter(ResponseGreater()));
+            const float amb = k[n_points - 1].response;
+            auto new_end = std::partition(k.begin() + n_points, k.end(), [amb](const KP &p) { return p.response >= amb; });
+            k.resize(new_end - k.begin());
+        }
+    }
+    for (size_t i = 0; i < k.size(); i++) order_out[i] = k[i].octave;
+    *n_out = (int)k.size();
+    return ORB_OK;
+}
+
 /* layer `level` after detectAndCompute (blurred = 1) or of the pyramid alone (blurred = 0) */
 int orbref_cvorb_level(const orb_cvorb_params *p, const uint8_t *image, int width, int height, int pitch, int level, int blurred,
                        uint8_t *dst, int dst_pitch, int *w, int *h) {
