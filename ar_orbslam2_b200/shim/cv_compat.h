@@ -47,6 +47,15 @@ struct KeyPoint {   // 28 bytes, same field order as OpenCV's (and as orb_keypoi
     KeyPoint() : size(0), angle(-1), response(0), octave(0), class_id(-1) {}
 };
 
+struct DMatch {   // features2d.hpp
+    int queryIdx, trainIdx, imgIdx;
+    float distance;
+    DMatch() : queryIdx(-1), trainIdx(-1), imgIdx(-1), distance(3.402823466e+38f) {}
+    DMatch(int q, int t, float d) : queryIdx(q), trainIdx(t), imgIdx(-1), distance(d) {}
+    DMatch(int q, int t, int i, float d) : queryIdx(q), trainIdx(t), imgIdx(i), distance(d) {}
+    bool operator<(const DMatch &m) const { return distance < m.distance; }
+};
+
 // Reference-counted byte matrix: enough of cv::Mat for images (8UC1) and descriptor tables.
 class Mat {
 public:

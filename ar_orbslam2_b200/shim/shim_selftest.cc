@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "ORBextractor.h"
+#include "MarkerORB.h"
 
 static std::vector<unsigned char> slurp(const char *p, size_t n) {
     std::vector<unsigned char> b(n);
@@ -62,6 +63,22 @@ int main(int argc, char **argv) {
     dump(pre + "_fur.bin", fuR.data(), fuR.size() * 4);
     dump(pre + "_fdp.bin", fdepth.data(), fdepth.size() * 4);
     printf("fused ok=%d\n", (int)fok);
+    {   // the marker pipeline's front end as Marker::setTargetImage / Match write it (ref Marker.cc:83-84,107-121,314-349)
+        std::vector<cv::KeyPoint> mk1, mk2;
+        cv::Mat md1, md2;
+        { orbgpu_shim::ORB orb; orb(imLeft, cv::Mat(), mk1, md1); }    // `ORB orb; orb(mImage1, Mat(), mvKeys1, mDescriptors1);`
+        { orbgpu_shim::ORB orb; orb(imRight, cv::Mat(), mk2, md2); }
+        std::vector<cv::DMatch> bf, rm;
+        orbgpu_shim::BruteForceMatchHamming(md1, md2, bf);
+        orbgpu_shim::SearchMatches(md1, md2, rm);
+        dump(pre + "_mk1.bin", mk1.data(), mk1.size() * sizeof(cv::KeyPoint));
+        dump(pre + "_mk2.bin", mk2.data(), mk2.size() * sizeof(cv::KeyPoint));
+        dump(pre + "_md1.bin", md1.data, (size_t)md1.rows * 32);
+        dump(pre + "_md2.bin", md2.data, (size_t)md2.rows * 32);
+        dump(pre + "_mbf.bin", bf.data(), bf.size() * sizeof(cv::DMatch));
+        dump(pre + "_mrm.bin", rm.data(), rm.size() * sizeof(cv::DMatch));
+        printf("marker ok n1=%zu n2=%zu bf=%zu ratio=%zu\n", mk1.size(), mk2.size(), bf.size(), rm.size());
+    }
     if (argc > 7) {   // latency of the calls a Tracking thread makes, without the host mirror of the pyramid (median of 50)
         auto med = [](std::vector<double> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
         auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };

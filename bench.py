@@ -775,6 +775,60 @@ def bench_bow(args, torch, dev, local):
     return r
 
 
+def bench_marker(args):
+    """SURVEY 8f-4, the marker pipeline's front end (ref: Marker::setTargetImage / Match, ORB_SLAM2/src/Marker.cc:83-84,107-130):
+    OpenCV's cv::ORB (Harris score, 500 features) on the target image and on a camera frame, then the brute-force ratio matcher
+    (Marker::searchMatches).  Blocking host calls (pageable image in, key points + descriptors out), wall clock; beside it the
+    oracle restatement on one core and -- where cv2 is importable -- cv2's own ORB_create().detectAndCompute, the library the
+    reference links (other version), with its threads."""
+    import time
+    from ar_orbslam2_b200 import cvorb, matcher
+    from ar_orbslam2_b200.synth import synth_frame
+    r = {"workload": "cv::ORB defaults (500 features, 8 levels, Harris score, FAST 20) on 640x480 and 1920x1080 frames + ratio matcher"}
+    for name, (w, h) in (("vga", (640, 480)), ("hd1080", (1920, 1080))):
+        orb = cvorb.ORB(max_width=w, max_height=h)
+        target, frame = synth_frame(w, h, 100), synth_frame(w, h, 101)
+        k1, d1 = orb(target)
+        l0 = orb.launch_count
+        k2, d2 = orb(frame)
+        launches = orb.launch_count - l0
+        for _ in range(5):
+            orb(frame)
+        t = []
+        for _ in range(40):
+            t0 = time.perf_counter(); orb(frame); t.append(time.perf_counter() - t0)
+        leg = {"gpu_ms_median": float(np.median(t) * 1e3), "gpu_ms_min": float(np.min(t) * 1e3), "keypoints": int(len(k2)), "launches": int(launches)}
+        t = []
+        for _ in range(20):
+            t0 = time.perf_counter(); matcher.searchMatches(d1, d2); t.append(time.perf_counter() - t0)
+        leg["ratio_match_ms_median"] = float(np.median(t) * 1e3)
+        if not args.skip_cpu:
+            from oracle import orbref
+            t = []
+            for _ in range(3 if w > 1000 else 8):
+                t0 = time.perf_counter(); rk, rd = orbref.cv_orb(frame); t.append(time.perf_counter() - t0)
+            leg["cpu_port_ms_median_1core"] = float(np.median(t) * 1e3)
+            leg["equals_oracle"] = bool(rk.tobytes() == k2.tobytes() and np.array_equal(rd, d2))
+            try:
+                import cv2
+                o = cv2.ORB_create()
+                o.detectAndCompute(frame, None)
+                t = []
+                for _ in range(10):
+                    t0 = time.perf_counter(); ck, cd = o.detectAndCompute(frame, None); t.append(time.perf_counter() - t0)
+                leg["cv2_ms_median"] = float(np.median(t) * 1e3)
+                leg["cv2_threads"] = int(cv2.getNumThreads())
+                leg["cv2_version"] = cv2.__version__
+                leg["equals_cv2"] = bool(len(ck) == len(k2) and np.array_equal(cd, d2) and
+                                         all(abs(a.pt[0] - b["x"]) == 0 and abs(a.pt[1] - b["y"]) == 0 and a.response == b["response"] and
+                                             a.angle == b["angle"] and a.octave == b["octave"] for a, b in zip(ck, k2)))
+            except ImportError:
+                leg["cv2_ms_median"] = None
+        orb.close()
+        r[name] = leg
+    return r
+
+
 def bench_presteps(args, torch, dev):
     """SURVEY 8f-3 pre-steps on device-resident batches of KITTI-shaped frames, CUDA events on the launching stream, against the
     measured HBM peak: cvtColor RGB->grey (reads 3P, writes P) and the stereo-rectification remap (8 map bytes + ~1 source byte
@@ -1204,6 +1258,7 @@ def run_ours(args):
         if not os.environ.get("ORB_BENCH_SKIP_BOW"):
             extra["bow_transform"] = bench_bow(args, torch, dev, local)
             extra["presteps"] = bench_presteps(args, torch, dev)
+            extra["marker_orb"] = bench_marker(args)
 
     if rank != 0:
         if world > 1:

@@ -130,3 +130,41 @@ def test_reference_call_sites_compile_against_the_shim_headers(tmp_path):
     dep = subprocess.run(cmd[:2] + ["-M"] + cmd[3:], capture_output=True, text=True).stdout
     assert os.path.join(SHIM, "ORBmatcher.h") in os.path.realpath(os.path.join(ov, "ORBmatcher.h"))
     assert "overlay/ORBmatcher.h" in dep and "overlay/ORBextractor.h" in dep and REF + "/include/ORBmatcher.h" not in dep
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="reference checkout not present (GPU box)")
+def test_marker_call_sites_compile_against_the_marker_shim(tmp_path):
+    """Marker::setTargetImage / Match (Marker.cc:83-84, 107-108) call OpenCV's `ORB` directly; lifted unedited they compile
+    against shim/MarkerORB.h once `ORB` names orbgpu_shim::ORB (the one-word edit INTEGRATION.md asks for, here a block-scope
+    using-declaration), and so do the brute-force matcher replacements with the reference's member types (Marker.h)."""
+    def lift(a, b):
+        with open(os.path.join(REF, "src", "Marker.cc"), errors="replace") as f:
+            return "".join(f.readlines()[a - 1:b])
+    set_target, match = lift(83, 84), lift(107, 108)
+    assert "ORB orb;" in set_target and "orb(mImage1" in set_target and "orb(mImage2" in match
+    src = r'''
+#include "MarkerORB.h"
+#include <vector>
+using namespace std;
+using namespace cv;
+struct MarkerMembers {   // Marker.h: the members the lifted lines touch
+    Mat mImage1, mImage2, mDescriptors1, mDescriptors2;
+    vector<KeyPoint> mvKeys1, mvKeys2;
+    void setTargetImage() {
+        using orbgpu_shim::ORB;
+%s
+    }
+    void Match() {
+        using orbgpu_shim::ORB;
+%s
+        vector<DMatch> matches, good;
+        orbgpu_shim::BruteForceMatchHamming(mDescriptors1, mDescriptors2, matches);   // BruteForceMatcher<HammingLUT>::match, :111-121
+        orbgpu_shim::SearchMatches(mDescriptors1, mDescriptors2, good);                // Marker::searchMatches, :314-349
+    }
+};
+''' % (set_target, match)
+    tu = tmp_path / "marker_sites.cc"
+    tu.write_text(src)
+    p = subprocess.run(["g++", "-std=gnu++11", "-fsyntax-only", "-Wall", "-I" + SHIM, "-I" + os.path.join(ROOT, "include"), str(tu)],
+                       capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr[-3000:] + "\n---- generated TU ----\n" + src

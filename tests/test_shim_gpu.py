@@ -42,6 +42,20 @@ def test_cpp_shim_stereo_frame(oracle, gpu_lib, tmp_path):
     assert np.array_equal(g("fur", np.uint32), ur.view(np.uint32)) and np.array_equal(g("fdp", np.uint32), dp.view(np.uint32))
     # mvImagePyramid mirror keeps the reference's padded-plane layout (19-px reflect border around the ROI)
     assert np.array_equal(g("l3", np.uint8), rl.pyramid_level(3, True).ravel())
+    # the marker pipeline's calls (Marker.cc:83-84,107-121,314-349) through orbgpu_shim::ORB / BruteForceMatchHamming / SearchMatches
+    assert "marker ok" in out.stdout
+    mk1, md1 = oracle.cv_orb(left)
+    mk2, md2 = oracle.cv_orb(right)
+    assert g("mk1", KEYPOINT_DTYPE).tobytes() == mk1.tobytes() and g("mk2", KEYPOINT_DTYPE).tobytes() == mk2.tobytes()
+    assert np.array_equal(g("md1", np.uint8).reshape(-1, 32), md1) and np.array_equal(g("md2", np.uint8).reshape(-1, 32), md2)
+    dmatch = np.dtype([("queryIdx", "<i4"), ("trainIdx", "<i4"), ("imgIdx", "<i4"), ("distance", "<f4")])
+    bf = g("mbf", dmatch)
+    bd, bi, _, _ = oracle.hamming_top2(md1, md2)
+    assert np.array_equal(bf["queryIdx"], np.arange(len(md1))) and np.array_equal(bf["trainIdx"], bi) and np.array_equal(bf["distance"], bd)
+    rm = g("mrm", dmatch)
+    tidx, dist = oracle.search_matches_ratio(md1, md2)
+    keep = np.nonzero(tidx >= 0)[0]
+    assert np.array_equal(rm["queryIdx"], keep) and np.array_equal(rm["trainIdx"], tidx[keep]) and np.array_equal(rm["distance"], dist[keep])
 
 
 def test_cpp_matcher_shim_equals_reference(oracle, gpu_lib):
