@@ -1018,6 +1018,29 @@ class Pipe:
         self.out_free[k % self.NB].synchronize()
 
 
+def pinned_frames(torch, shape):
+    """Pinned host buffer for the input frames.  ORB_BENCH_WC=1: write-combined (cudaHostAllocWriteCombined) -- the CPU only ever
+    writes the frames (a camera driver's DMA target), the GPU's PCIe reads then skip the host's cache snoops."""
+    if os.environ.get("ORB_BENCH_WC") != "1":
+        return torch.empty(shape, dtype=torch.uint8).pin_memory(), "pinned"
+    import ctypes
+    rt = None
+    for name in ("libcudart.so.12", "libcudart.so"):
+        try:
+            rt = ctypes.CDLL(name)
+            break
+        except OSError:
+            pass
+    if rt is None:
+        return torch.empty(shape, dtype=torch.uint8).pin_memory(), "pinned (no libcudart for write-combined)"
+    n = int(np.prod(shape))
+    ptr = ctypes.c_void_p()
+    if rt.cudaHostAlloc(ctypes.byref(ptr), ctypes.c_size_t(n), ctypes.c_uint(4)) != 0:
+        return torch.empty(shape, dtype=torch.uint8).pin_memory(), "pinned (cudaHostAlloc failed)"
+    arr = np.ctypeslib.as_array((ctypes.c_uint8 * n).from_address(ptr.value)).reshape(shape)
+    return torch.from_numpy(arr), "pinned write-combined"
+
+
 def bind_near_gpu(torch, local):
     """Pin this process to the cores next to its GPU (sysfs local_cpulist of the GPU's PCI function) BEFORE the pinned host
     buffers are allocated, so first touch places them on the GPU's NUMA node.  Best effort; returns what was done."""
@@ -1057,7 +1080,7 @@ def run_ours(args):
     B = args.batch                       # stereo pairs per step (per GPU: weak scaling)
     NF = 2 * B
     pairs = make_pairs(args.distinct, 17 + 1000 * rank)
-    host = torch.empty((NF, H, W), dtype=torch.uint8).pin_memory()
+    host, host_kind = pinned_frames(torch, (NF, H, W))
     hv = host.numpy()
     for b in range(B):
         l, r = pairs[b % len(pairs)]
@@ -1311,7 +1334,7 @@ def run_ours(args):
                 "pipeline": pipeline,
                 "copy_only_value": NF * e2e_steps * world / (ms_copy * 1e-3),
                 "host_link_GBps": (h2d + d2h) * e2e_steps / (ms_copy * 1e-3) / 1e9,
-                "host_link_note": "per rank, all ranks copying at once: this step's H2D + D2H bytes with no kernels, both directions "
+                "host_frames_memory": host_kind, "host_link_note": "per rank, all ranks copying at once: this step's H2D + D2H bytes with no kernels, both directions "
                                   "concurrently; e2e cannot exceed min(value, copy_only_value)",
                 "numa": numa,
                 "steady_state_value": steady,
