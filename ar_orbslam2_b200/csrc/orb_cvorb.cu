@@ -602,9 +602,8 @@ struct orb_cvorb {
     int *d_rowcount = nullptr, *d_cand_n = nullptr, *d_scratch = nullptr, *d_hdr = nullptr;   // hdr: [0] n_out, [1] error flags
     CvElem *d_cand = nullptr;
     CvGeom *d_geom = nullptr;
-    orb_keypoint *d_kps = nullptr;
-    uint8_t *d_desc = nullptr;
-    uint8_t *h_pin = nullptr;       // pinned landing block: header + key points + descriptors
+    uint8_t *h_pin = nullptr;       // pinned block the describe kernel writes straight into: header, key points [out_cap], descriptors
+    uint8_t *h_in = nullptr;        // pinned staging of a host image (one memcpy, then a true DMA instead of the driver's pageable path)
     size_t plane_bytes = 0, rows_floats = 0, mask_words = 0, tap_count = 0, cand_total = 0, rows_total = 0;
     int out_cap = 0;
     int64_t launches = 0;
@@ -697,8 +696,8 @@ void cv_free(orb_cvorb *h) {
     if (h->s_blur) cudaStreamSynchronize(h->s_blur);
     cudaFree(h->d_img); cudaFree(h->d_blur); cudaFree(h->d_score); cudaFree(h->d_rows); cudaFree(h->d_taps); cudaFree(h->d_masks);
     cudaFree(h->d_rowcount); cudaFree(h->d_cand_n); cudaFree(h->d_scratch); cudaFree(h->d_hdr); cudaFree(h->d_cand); cudaFree(h->d_geom);
-    cudaFree(h->d_kps); cudaFree(h->d_desc);
     if (h->h_pin) cudaFreeHost(h->h_pin);
+    if (h->h_in) cudaFreeHost(h->h_in);
     if (h->ev_pyr) cudaEventDestroy(h->ev_pyr);
     if (h->ev_blur) cudaEventDestroy(h->ev_blur);
     if (h->s_blur) cudaStreamDestroy(h->s_blur);
@@ -777,9 +776,8 @@ int orb_cvorb_create(const orb_cvorb_params *params, orb_cvorb **out) {
     CV_TRY(cudaMalloc(&h->d_hdr, 4 * sizeof(int)));
     CV_TRY(cudaMalloc(&h->d_cand, h->cand_total * sizeof(CvElem)));
     CV_TRY(cudaMalloc(&h->d_geom, sizeof(CvGeom)));
-    CV_TRY(cudaMalloc(&h->d_kps, (size_t)h->out_cap * sizeof(orb_keypoint)));
-    CV_TRY(cudaMalloc(&h->d_desc, (size_t)h->out_cap * 32));
     CV_TRY(cudaMallocHost(&h->h_pin, 16 + (size_t)h->out_cap * (sizeof(orb_keypoint) + 32)));
+    CV_TRY(cudaMallocHost(&h->h_in, (size_t)p.max_width * p.max_height));
     CV_TRY(cudaMemsetAsync(h->d_score, 0, h->plane_bytes, h->stream));
     CV_TRY(cudaMemsetAsync(h->d_hdr, 0, 4 * sizeof(int), h->stream));
     CV_TRY(cudaStreamSynchronize(h->stream));
@@ -807,8 +805,13 @@ int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, 
     if (rc != ORB_OK) return rc;
     const CvGeom &G = h->G;
     cudaStream_t st = h->stream;
-    ORB_CUDA_TRY(cudaMemcpy2DAsync(h->d_img + G.lv[0].off, G.lv[0].pitch, image, pitch, width, height,
-                                   image_loc == ORB_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    if (image_loc == ORB_HOST && (size_t)width * height <= (1u << 20)) {   // small frames: one memcpy + a true DMA beats the driver's pageable path (larger ones: measured slower)
+        for (int y = 0; y < height; y++) memcpy(h->h_in + (size_t)y * width, image + (size_t)y * pitch, width);
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(h->d_img + G.lv[0].off, G.lv[0].pitch, h->h_in, width, width, height, cudaMemcpyHostToDevice, st));
+    } else {
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(h->d_img + G.lv[0].off, G.lv[0].pitch, image, pitch, width, height,
+                                       image_loc == ORB_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    }
     for (int l = 1; l < G.nlevels; l++) {
         const CvLevel &S = G.lv[l - 1], &D = G.lv[l];
         dim3 grid((D.w + 4 * 256 - 1) / (4 * 256), D.h);
@@ -850,7 +853,8 @@ int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, 
         }
         ORB_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_blur, 0));
         dim3 gd((maxq + 7) / 8, G.nlevels);
-        k_cv_describe<<<gd, 256, 0, st>>>(h->d_img, h->d_blur, h->d_cand, h->d_cand_n, h->d_geom, h->d_kps, h->d_desc, h->d_hdr, h->d_hdr + 1);
+        k_cv_describe<<<gd, 256, 0, st>>>(h->d_img, h->d_blur, h->d_cand, h->d_cand_n, h->d_geom, (orb_keypoint *)(h->h_pin + 16),
+                                          h->h_pin + 16 + (size_t)h->out_cap * sizeof(orb_keypoint), h->d_hdr, h->d_hdr + 1);   // results go straight to pinned host memory
         h->launches++;
     } else {
         ORB_CUDA_TRY(cudaStreamWaitEvent(st, h->ev_blur, 0));
@@ -869,10 +873,7 @@ int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, 
     *n_out = n;
     if (n == 0) return ORB_OK;
     ORB_REQUIRE(n <= capacity && keypoints && descriptors, ORB_ERR_CAPACITY, "capacity %d < %d key points", capacity, n);
-    uint8_t *hk = h->h_pin + 16, *hd = hk + (size_t)n * sizeof(orb_keypoint);
-    ORB_CUDA_TRY(cudaMemcpyAsync(hk, h->d_kps, (size_t)n * sizeof(orb_keypoint), cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaMemcpyAsync(hd, h->d_desc, (size_t)n * 32, cudaMemcpyDeviceToHost, st));
-    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    const uint8_t *hk = h->h_pin + 16, *hd = hk + (size_t)h->out_cap * sizeof(orb_keypoint);   // written by k_cv_describe, complete before the header copy
     memcpy(keypoints, hk, (size_t)n * sizeof(orb_keypoint));
     memcpy(descriptors, hd, (size_t)n * 32);
     return ORB_OK;

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
-from make_golden_cvorb import CASES, PRIMITIVE_CASES, image, orb_kwargs, sha  # noqa: E402
+from make_golden_cvorb import CASES, PRIMITIVE_CASES, SWEEP, image, orb_kwargs, result_sha, sha  # noqa: E402
 from ar_orbslam2_b200.synth import synth_frame  # noqa: E402
 from oracle import orbref  # noqa: E402
 
@@ -56,3 +56,10 @@ def test_oracle_equals_cv2_live():
         got = np.array([(p.pt[0], p.pt[1], p.size, p.angle, p.response, p.octave, p.class_id) for p in kps], dtype=rk.dtype)
         assert got.tobytes() == rk.tobytes()
         assert np.array_equal(desc, rd)
+
+
+def test_oracle_equals_cv2_sweep_hashes():
+    """40 further frames: SHA-256 of cv2's key points + descriptors (default parameters)"""
+    g = np.load(GOLDEN)
+    for (w, h, seed), want in zip(SWEEP, g["sweep_sha256"]):
+        assert result_sha(*oracle_orb(synth_frame(w, h, seed), {})) == str(want), (w, h, seed)

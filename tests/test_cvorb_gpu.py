@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
-from make_golden_cvorb import CASES, image, orb_kwargs  # noqa: E402
+from make_golden_cvorb import CASES, SWEEP, image, orb_kwargs, result_sha  # noqa: E402
 from ar_orbslam2_b200 import cvorb  # noqa: E402
 from ar_orbslam2_b200.synth import synth_frame  # noqa: E402
 from oracle import orbref  # noqa: E402
@@ -108,3 +108,12 @@ def test_retain_best_depth_limit_fallback():
                     got = cvorb.retain_best(r, npts, depth)
                     want = orbref.retain_best(r, npts, depth)
                     assert np.array_equal(got, want), (n, kind, npts, depth)
+
+
+def test_gpu_equals_cv2_sweep_hashes():
+    """40 further frames on one handle: SHA-256 of key points + descriptors equal cv2's"""
+    g = np.load(GOLDEN)
+    orb = gpu_orb({}, 752, 480)
+    for (w, h, seed), want in zip(SWEEP, g["sweep_sha256"]):
+        assert result_sha(*orb(synth_frame(w, h, seed))) == str(want), (w, h, seed)
+    orb.close()
