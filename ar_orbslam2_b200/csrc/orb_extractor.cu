@@ -172,6 +172,13 @@ k_pyr_resize_generic(uint8_t *__restrict__ pyr, const Geom *__restrict__ G, cons
 // row above and the one below, so the horizontally interpolated source rows are kept in registers across output rows:
 // ~1.2 source rows (3 aligned loads, 4 PRMT, 4 IDP2A) per output row instead of 2.
 constexpr int PYR_ROWS = 8;
+// Row records (one uint4 per plane row, after the word records in the same pool): x = byte offset of source row s0 | bit 0: s0 is the
+// previous plane row's s1 | bit 1: s1 == s0;  y = byte offset of source row s1;  z, w = the vertical weights << 16
+// (umulhi(a << 16, h) == (a * h) >> 16).  Reflection, row pitch and the reuse decision are resolved on the host: the row loop
+// holds no address arithmetic beyond two additions.  The two horizontally interpolated source rows live in X and Y with
+// ALTERNATING roles -- row r reads (n0, n1) = (X, Y), row r + 1 reads (Y, X) -- so "n0 is the previous row's n1" (4 rows in 5 at
+// scale 1.2) costs nothing, and no register is ever moved (the previous version spent 40 of its 124 instructions per row on the
+// moves and compare chains of a two-entry cache: profiles/r2c_resize_sass_counts.txt).
 template <int ROWS>
 __device__ __forceinline__ void pyr_resize_column(uint8_t *frame, const Geom *__restrict__ G, const ResizeTap *__restrict__ taps,
                                                   const uint4 *__restrict__ wtab, int level, int word, int py0) {
@@ -179,41 +186,45 @@ __device__ __forceinline__ void pyr_resize_column(uint8_t *frame, const Geom *__
     const LevelGeom &p = G->lv[level - 1];
     const uint4 Wt = __ldg(wtab + 2 * (g.wtab_off + word)), St = __ldg(wtab + 2 * (g.wtab_off + word) + 1);
     const uint8_t *srcw = frame + p.interior_off + (size_t)St.z * 4;       // the window's first word in source row 0
-    uint8_t *dst = frame + g.plane_off + (size_t)word * 4;
-    const int rows = g.h + 2 * EDGE;
-    int rA = -1, rB = -1;
-    uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
-    auto hrow = [&](int sy, uint32_t *h) {   // (S[x]*a0 + S[x+1]*a1) >> 4 of source row sy for the four pixels
-        const uint32_t *r = reinterpret_cast<const uint32_t *>(srcw + (size_t)sy * p.pitch);
+    const int nr = min(ROWS, g.h + 2 * EDGE - py0);
+    const uint4 *rt = wtab + g.rtab_off + py0;
+    uint8_t *dst = frame + g.plane_off + (size_t)word * 4 + (size_t)py0 * g.pitch;
+    const int dpitch = g.pitch;
+    const uint32_t selA = St.x, selB = St.x >> 16, selC = St.y, selD = St.y >> 16;
+    uint32_t X[4], Y[4];
+    auto hrow = [&](uint32_t off, uint32_t *h) {   // (S[x]*a0 + S[x+1]*a1) >> 4 of the source row at byte offset `off` for the four pixels
+        const uint32_t *r = reinterpret_cast<const uint32_t *>(srcw + off);
         const uint32_t a0 = __ldg(r), a1 = __ldg(r + 1), a2 = __ldg(r + 2);
-        const uint32_t x01 = __byte_perm(__byte_perm(a0, a1, St.x), a2, St.x >> 16);
-        const uint32_t x23 = __byte_perm(__byte_perm(a0, a1, St.y), a2, St.y >> 16);
+        const uint32_t x01 = __byte_perm(__byte_perm(a0, a1, selA), a2, selB);
+        const uint32_t x23 = __byte_perm(__byte_perm(a0, a1, selC), a2, selD);
         h[0] = __dp2a_lo(Wt.x, x01, 0u) >> 4; h[1] = __dp2a_hi(Wt.y, x01, 0u) >> 4;
         h[2] = __dp2a_lo(Wt.z, x23, 0u) >> 4; h[3] = __dp2a_hi(Wt.w, x23, 0u) >> 4;
     };
-#pragma unroll 2
-    for (int rr = 0; rr < ROWS; rr++) {
-        const int py = py0 + rr;
-        if (py >= rows) break;
-        const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
-        const int s0 = ty.s0, s1 = ty.s1;
-        uint32_t n0[4], n1[4];
-        if (s0 == rA) { n0[0] = hA[0]; n0[1] = hA[1]; n0[2] = hA[2]; n0[3] = hA[3]; }
-        else if (s0 == rB) { n0[0] = hB[0]; n0[1] = hB[1]; n0[2] = hB[2]; n0[3] = hB[3]; }
-        else hrow(s0, n0);
-        if (s1 == s0) { n1[0] = n0[0]; n1[1] = n0[1]; n1[2] = n0[2]; n1[3] = n0[3]; }
-        else if (s1 == rB) { n1[0] = hB[0]; n1[1] = hB[1]; n1[2] = hB[2]; n1[3] = hB[3]; }
-        else if (s1 == rA) { n1[0] = hA[0]; n1[1] = hA[1]; n1[2] = hA[2]; n1[3] = hA[3]; }
-        else hrow(s1, n1);
-        rA = s0; rB = s1;
-        const uint32_t A0 = (uint32_t)ty.a0 << 16, A1 = (uint32_t)ty.a1 << 16;   // umulhi(a << 16, h) == (a * h) >> 16
+    auto emit = [&](const uint32_t *n0, const uint32_t *n1, uint32_t A0, uint32_t A1) {
         uint32_t v = 0;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            hA[k] = n0[k]; hB[k] = n1[k];
-            v |= ((__umulhi(A0, n0[k]) + __umulhi(A1, n1[k]) + 2u) >> 2) << (8 * k);
+        for (int k = 0; k < 4; k++) v |= ((__umulhi(A0, n0[k]) + __umulhi(A1, n1[k]) + 2u) >> 2) << (8 * k);
+        *reinterpret_cast<uint32_t *>(dst) = v;
+        dst += dpitch;
+    };
+#pragma unroll 1
+    for (int rr = 0; rr < ROWS; rr += 2) {
+        if (rr >= nr) break;
+        {   // even row of the strip: (n0, n1) = (X, Y)
+            const uint4 t = __ldg(rt + rr);
+            if (rr == 0 || !(t.x & 1u)) hrow(t.x & ~3u, X);
+            if (t.x & 2u) { Y[0] = X[0]; Y[1] = X[1]; Y[2] = X[2]; Y[3] = X[3]; }
+            else hrow(t.y, Y);
+            emit(X, Y, t.z, t.w);
         }
-        *reinterpret_cast<uint32_t *>(dst + (size_t)py * g.pitch) = v;
+        if (ROWS == 1 || rr + 1 >= nr) break;
+        {   // odd row: (n0, n1) = (Y, X)
+            const uint4 t = __ldg(rt + rr + 1);
+            if (!(t.x & 1u)) hrow(t.x & ~3u, Y);
+            if (t.x & 2u) { X[0] = Y[0]; X[1] = Y[1]; X[2] = Y[2]; X[3] = Y[3]; }
+            else hrow(t.y, X);
+            emit(Y, X, t.z, t.w);
+        }
     }
 }
 
@@ -1622,6 +1633,21 @@ static int set_geometry(orb_extractor *ex, int width, int height) {
             wtab.push_back(make_uint4(selectors(o[0], o[1]), selectors(o[2], o[3]), (uint32_t)(base / 4), 0u));
         }
     }
+    // row records of the fast path (see pyr_resize_column)
+    for (int l = 1; l < G.nlevels; l++) {
+        LevelGeom &g = G.lv[l];
+        const LevelGeom &sl = G.lv[l - 1];
+        g.rtab_off = (int)wtab.size();
+        int prev_s1 = -1;
+        for (int py = 0; py < g.h + 2 * EDGE; py++) {
+            const ResizeTap ty = taps[g.tap_y_off + reflect101(py - EDGE, g.h)];
+            uint32_t x = (uint32_t)ty.s0 * (uint32_t)sl.pitch, y = (uint32_t)ty.s1 * (uint32_t)sl.pitch;
+            if (py > 0 && ty.s0 == prev_s1) x |= 1u;
+            if (ty.s1 == ty.s0) x |= 2u;
+            prev_s1 = ty.s1;
+            wtab.push_back(make_uint4(x, y, (uint32_t)(uint16_t)ty.a0 << 16, (uint32_t)(uint16_t)ty.a1 << 16));
+        }
+    }
     ORB_REQUIRE(wtab.size() <= ex->wtab_cap, ORB_ERR_INVALID, "internal: resize word table too small");
     if (!wtab.empty())
         ORB_CUDA_TRY(cudaMemcpyAsync(ex->d_wtab, wtab.data(), wtab.size() * sizeof(uint4), cudaMemcpyHostToDevice, ex->stream));
@@ -1744,7 +1770,7 @@ int orb_extractor_create(const orb_params *params, orb_extractor **out) {
     }
     ex->taps_cap = (size_t)(params->max_width + params->max_height + 64) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_taps, ex->taps_cap * sizeof(ResizeTap)));
-    ex->wtab_cap = 2 * (size_t)((params->max_width + XOFF + EDGE + 127) / 128 * 32 + 32) * params->nlevels;
+    ex->wtab_cap = (2 * (size_t)((params->max_width + XOFF + EDGE + 127) / 128 * 32 + 32) + (size_t)params->max_height + 2 * EDGE) * params->nlevels;
     TRY_ALLOC(cudaMalloc(&ex->d_wtab, ex->wtab_cap * sizeof(uint4)));
     ex->cells_cap = (size_t)(params->max_width / 30 + 2) * (params->max_height / 30 + 2) * 4 + 64;   // sum over levels < 3.1x level 0
     TRY_ALLOC(cudaMalloc(&ex->d_cells, ex->cells_cap * 4));

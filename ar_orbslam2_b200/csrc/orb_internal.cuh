@@ -27,6 +27,7 @@ struct LevelGeom {
     long long interior_off;      // byte offset of interior pixel (0,0)
     int tap_x_off, tap_y_off;    // offsets into the ResizeTap pool (level >= 1)
     int wtab_off, fast_resize;   // per-output-word resize records (fast path) and whether the level may use them
+    int rtab_off;                // per-plane-row records of the fast path (uint4 index into the same pool)
     // FAST cell grid (ref :742-773)
     int maxBX, maxBY, wCell, hCell, ncx, ncy, cell_begin;
     // quadtree (ref :530-549)
