@@ -541,10 +541,15 @@ k_fast_cells(const uint8_t *__restrict__ pyr, const FastLevel g, uint32_t *__res
 // ------------------------------------------------------------------------------------------
 constexpr int FR_LOGC = 5;
 constexpr int FR_COLS = 1 << FR_LOGC;   // word columns of a segment
-constexpr int FR_T = 2 * FR_COLS;       // threads: FR_COLS word columns x 2 row halves
+#ifndef ORBGPU_FR_PARTS
+#define ORBGPU_FR_PARTS 2
+#endif
+constexpr int FR_PARTS = ORBGPU_FR_PARTS;   // row parts per word column (3 parts = 27 instead of 22 resident warps per SM but 16 % more compass
+                                            // warm-up rows: measured 0.880 vs 0.870 ms per 288 C2 frames, so 2 stays)
+constexpr int FR_T = FR_PARTS * FR_COLS;   // threads: FR_COLS word columns x FR_PARTS row parts
 constexpr int FR_TPW = FR_COLS + 8;     // tile pitch in words: the columns + one word either side + 16-byte alignment slack
 constexpr int FR_TPB = FR_TPW * 4;
-constexpr int FR_ROWS = 30;          // rows per thread (cells are < 60 px high)
+constexpr int FR_ROWS = (60 + FR_PARTS - 1) / FR_PARTS;   // rows per thread (cells are < 60 px high)
 
 struct FastRowsLayout { int off_score, off_slots, off_list, list_cap, seg_cells, use_tma, frame0; };   // byte offsets into dynamic shared memory
 
@@ -558,7 +563,7 @@ __device__ __noinline__ void fast_cell_rows_call(const uint8_t *pyr, const FastL
     fast_cell<FR_T>(pyr, g, cand, cand_count, err, b, ci, cj, thr);
 }
 
-__global__ void __launch_bounds__(FR_T, 12)
+__global__ void __launch_bounds__(FR_T, FR_PARTS == 2 ? 12 : 9)
 k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLayout lay, const __grid_constant__ CUtensorMap tmap,
             uint32_t *__restrict__ cand, uint32_t *__restrict__ cand_count, int *__restrict__ err) {
     extern __shared__ __align__(128) unsigned char fsm[];
@@ -625,7 +630,7 @@ k_fast_rows(const uint8_t *__restrict__ pyr, const FastLevel g, const FastRowsLa
     const FastDiv dW(g.wCell);
 
     // thread = (word column, half of the rows); the rows of a warp are uniform (columns past the segment run masked)
-    const int col = tid & (FR_COLS - 1), half = (hc + 1) >> 1, r0 = (tid >> FR_LOGC) * half;
+    const int col = tid & (FR_COLS - 1), half = (hc + FR_PARTS - 1) / FR_PARTS, r0 = (tid >> FR_LOGC) * half;   // `half`: rows of one part
     const int nrows = min(half, hc - r0);
     const int tw = w0 + col - cbase;
     uint32_t vm;                          // bytes of this thread's words that are computed pixels (of cells still to do)
@@ -796,7 +801,7 @@ static size_t fast_rows_layout(const FastLevel &fl, FastRowsLayout &lay) {
     auto up = [](size_t v) { return (v + 15) & ~(size_t)15; };
     size_t off = up((size_t)(fl.hCell + 6) * FR_TPB);
     lay.off_score = (int)off; off = up(off + (size_t)(fl.hCell + 2) * FR_TPB);
-    lay.off_slots = (int)off; off = up(off + (size_t)(fl.hCell + 1) * FR_COLS * 4);   // flagged words: a region of 32 columns x its rows per warp
+    lay.off_slots = (int)off; off = up(off + (size_t)(fl.hCell + FR_PARTS - 1) * FR_COLS * 4);   // flagged words: a region of 32 columns x its rows per warp
     lay.list_cap = 2 * FR_COLS * fl.hCell;                               // half of the segment's pixels
     lay.off_list = (int)off; off = up(off + (size_t)lay.list_cap * 2);
     return off;
