@@ -1149,6 +1149,8 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 // ------------------------------------------------------------------------------------------
 constexpr int BLUR_ROWS = 16;
 
+template <int TAPS>   // 0: OpenCV 3.x / 4.x fixed-point taps, 1: OpenCV 2.4's (compile-time: the tap vectors are immediates and the
+                      // 2.4-only clamp disappears from the default build -- they were ~10 of 84 instructions per word-row)
 __global__ void __launch_bounds__(128)
 k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const Geom *__restrict__ G, int level) {
     const LevelGeom &g = G->lv[level];
@@ -1156,28 +1158,33 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
     const int x0 = wx * 4;
     if (x0 >= g.w) return;
     const int y0 = blockIdx.y * BLUR_ROWS, b = blockIdx.z;
-    const uint32_t k0 = 18, k1 = 34, k2 = G->blur_taps == 1 ? 49 : 48, k3 = G->blur_taps == 1 ? 55 : 56;
+    constexpr uint32_t k0 = 18, k1 = 34, k2 = TAPS == 1 ? 49 : 48, k3 = TAPS == 1 ? 55 : 56;
     // taps as byte vectors: horizontal pass = two 4-byte dot products (IDP4A) over bytes j+1..j+4 and j+5..j+8 of the window;
     // vertical pass = 16-bit x 8-bit dot products (IDP2A) over row PAIRS (H[2m], H[2m+1]) packed into one register
-    const uint32_t KLO = k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), KHI = k2 | (k1 << 8) | (k0 << 16);
-    const uint32_t T01 = k0 | (k1 << 8), T23 = k2 | (k3 << 8), T21 = k2 | (k1 << 8), T10 = k1 | (k0 << 8), T32 = k3 | (k2 << 8),
-                   T12 = k1 | (k2 << 8), T_0 = k0 << 8;
+    constexpr uint32_t KLO = k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), KHI = k2 | (k1 << 8) | (k0 << 16);
+    constexpr uint32_t T01 = k0 | (k1 << 8), T23 = k2 | (k3 << 8), T21 = k2 | (k1 << 8), T10 = k1 | (k0 << 8), T32 = k3 | (k2 << 8),
+                       T12 = k1 | (k2 << 8), T_0 = k0 << 8;
     const uint8_t *src = pyr + (size_t)b * G->pyr_frame + g.interior_off + x0 - 4;
     uint8_t *dst = blur + (size_t)b * G->pyr_frame + g.interior_off + x0;
     uint32_t P[4][4];        // ring of row pairs: P[m & 3][j] = H[2m][j] | H[2m+1][j] << 16   (H <= 255 * 256 fits 16 bits)
     uint32_t hprev[4];       // H of the last even row, waiting for its partner
     // source rows -3.. and ..H+2 live in the 19-px frame.  Row indices are clamped (not predicated) and the next row's
     // words are requested before the current row is consumed; rows past H+2 only feed outputs that are never stored.
+    // (source rows y0 - 3 .. y0 + BLUR_ROWS + 2 <= H + 17 all lie inside the padded plane, whose frame reaches row H + 18: no clamp)
     uint32_t n0, n1, n2;
+    const int pitch = g.pitch;
+    const uint8_t *sp = src + (ptrdiff_t)(y0 - 3) * pitch;
+    uint8_t *dp = dst + (ptrdiff_t)y0 * pitch;
     {
-        const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)min(y0 - 3, g.h + 2) * g.pitch);
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(sp);
         n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2);
     }
 #pragma unroll
     for (int r = 0; r < BLUR_ROWS + 6; r++) {
         const uint32_t w0 = n0, w1 = n1, w2 = n2;
         if (r + 1 < BLUR_ROWS + 6) {
-            const uint32_t *p = reinterpret_cast<const uint32_t *>(src + (ptrdiff_t)min(y0 + r - 2, g.h + 2) * g.pitch);
+            sp += pitch;
+            const uint32_t *p = reinterpret_cast<const uint32_t *>(sp);
             n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2);
         }
         uint32_t hc[4];      // horizontal pass of source row r for pixels x0 .. x0+3: pixel j reads window bytes j+1 .. j+7
@@ -1219,8 +1226,9 @@ k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const
                     for (int j = 0; j < 4; j++) v[j] = min(v[j], 0x00ffffffu);
                 }
                 const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
-                *reinterpret_cast<uint32_t *>(dst + (ptrdiff_t)yo * g.pitch) = o;
+                *reinterpret_cast<uint32_t *>(dp) = o;
             }
+            dp += pitch;
         }
     }
 }
@@ -2031,7 +2039,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
         NvtxRange nv("orbgpu:blur");
         const LevelGeom &g = G.lv[l];
         dim3 grid(((g.w + 3) / 4 + 127) / 128, (g.h + BLUR_ROWS - 1) / BLUR_ROWS, nb);
-        k_blur_planes<<<grid, 128, 0, s>>>(ex->d_pyr + (size_t)b0 * G.pyr_frame, ex->d_blur + (size_t)b0 * G.pyr_frame, ex->d_geom, l);
+        if (G.blur_taps == 1) k_blur_planes<1><<<grid, 128, 0, s>>>(ex->d_pyr + (size_t)b0 * G.pyr_frame, ex->d_blur + (size_t)b0 * G.pyr_frame, ex->d_geom, l);
+        else k_blur_planes<0><<<grid, 128, 0, s>>>(ex->d_pyr + (size_t)b0 * G.pyr_frame, ex->d_blur + (size_t)b0 * G.pyr_frame, ex->d_geom, l);
         ex->launches++;
     };
     auto launch_octree = [&](int l0, int nl, cudaStream_t s, int b0, int nb) {
