@@ -9,7 +9,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._abi import KEYPOINT_DTYPE, ORB_HOST, OrbCvOrbParams, ptr
+from ._abi import KEYPOINT_DTYPE, ORB_DEVICE, ORB_HOST, OrbCvOrbParams, ptr
 
 HARRIS_SCORE = 0
 FAST_SCORE = 1
@@ -67,6 +67,15 @@ class ORB:
         return self._kps[: n.value].copy(), self._desc[: n.value].copy()
 
     detectAndCompute = __call__
+
+    def detect_and_compute_device(self, dev_ptr: int, width: int, height: int, pitch: int):
+        """The same call on an 8-bit image that already lives on the device (e.g. the output of orb_cvt_color_gray /
+        orb_remap_linear); results come back to the host."""
+        n = C.c_int(0)
+        _lib.check(self._L.orb_cvorb_detect_and_compute(self._h, C.c_void_p(dev_ptr), width, height, pitch, ORB_DEVICE,
+                                                        ptr(self._kps), ptr(self._desc), self.capacity, C.byref(n)),
+                   "orb_cvorb_detect_and_compute")
+        return self._kps[: n.value].copy(), self._desc[: n.value].copy()
 
     def blurred_level(self, level: int, which: int = 0) -> np.ndarray:
         """Layer `level` of the last call as the descriptors sampled it (tests); which = 1: unblurred, 2: FAST score map."""

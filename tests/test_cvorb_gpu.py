@@ -117,3 +117,21 @@ def test_gpu_equals_cv2_sweep_hashes():
     for (w, h, seed), want in zip(SWEEP, g["sweep_sha256"]):
         assert result_sha(*orb(synth_frame(w, h, seed))) == str(want), (w, h, seed)
     orb.close()
+
+
+def test_device_resident_image_and_large_host_image():
+    """image_loc = ORB_DEVICE (pitched device buffer) and a host image above the pinned-staging threshold give the host path's bytes"""
+    import torch
+    orb = gpu_orb({}, 1920, 1080)
+    for w, h, seed in [(640, 480, 60), (1920, 1080, 61)]:
+        img = synth_frame(w, h, seed)
+        hk, hd = orb(img)
+        pitch = (w + 255) // 256 * 256
+        d = torch.zeros((h, pitch), dtype=torch.uint8, device="cuda")
+        d[:, :w] = torch.from_numpy(img).cuda()
+        torch.cuda.synchronize()
+        dk, dd = orb.detect_and_compute_device(d.data_ptr(), w, h, pitch)
+        assert dk.tobytes() == hk.tobytes() and np.array_equal(dd, hd), (w, h)
+        rk, rd = oracle_orb(img, {})
+        assert hk.tobytes() == rk.tobytes() and np.array_equal(hd, rd), (w, h)
+    orb.close()
