@@ -224,10 +224,16 @@ def run_reference(args):
     for _ in range(args.warmup):
         cpu_reference_run(pairs[: max(1, cores // 2)], cores)
     t_total, frames = 0.0, 0
-    for _ in range(args.steps):
+    budget_s = 100.0   # the whole --steps K run stays within a couple of minutes whatever K the caller asks for
+    for k in range(args.steps):
         dt, n = cpu_reference_run(pairs, cores)
         t_total += dt
         frames += n
+        if k == 0 and args.steps * dt > budget_s:   # shrink the per-step sample (never below one pair per core)
+            keep = max(cores, int(len(pairs) * budget_s / (args.steps * dt)))
+            if keep < len(pairs):
+                pairs = pairs[:keep]
+                sample_pairs = f"{sample_pairs} (first step), then {keep}"
     v = frames / t_total
     # beside it, on ONE core (its driver's allocator is process-global): the reference's own ORBextractor.cc compiled unmodified
     # (oracle/_ref, OpenCV primitives = the cv2-pinned restatements) against the port on the same frames, extraction only
