@@ -267,6 +267,31 @@ thread_local Top2Scratch t_scratch;   // chunk partials of top2_device, per thre
 inline size_t a256(size_t v) { return (v + 255) / 256 * 256; }
 }  // namespace
 
+// smallest and largest distance over ALL (query, train) pairs: the `minD` / `maxD` bookkeeping of naive_nn_search2
+// (ref AR-1.3/src/ORBMatcher.cpp:92-93).  One warp per query, lanes stride over the train rows.
+__global__ void __launch_bounds__(256)
+k_dist_minmax(const uint8_t *__restrict__ query, int nq, const uint8_t *__restrict__ train, int nt, int *__restrict__ out) {
+    const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const uint4 *pq = reinterpret_cast<const uint4 *>(query + (size_t)q * 32);
+    const uint4 a0 = __ldg(pq), a1 = __ldg(pq + 1);
+    int mn = 0x7fffffff, mx = -1;
+    for (int j = lane; j < nt; j += 32) {
+        const uint4 *pt = reinterpret_cast<const uint4 *>(train + (size_t)j * 32);
+        const uint4 b0 = __ldg(pt), b1 = __ldg(pt + 1);
+        const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                      __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+        mn = min(mn, d);
+        mx = max(mx, d);
+    }
+#pragma unroll
+    for (int s = 16; s; s >>= 1) {
+        mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, s));
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+    }
+    if (lane == 0 && nt > 0) { atomicMin(out, mn); atomicMax(out + 1, mx); }
+}
+
 extern "C" {
 
 int orb_descriptor_distance(const uint8_t *a, const uint8_t *b, int n, int32_t *dist, int loc) {
@@ -334,6 +359,30 @@ __global__ void k_ratio_accept(int nq, const int32_t *__restrict__ d1, const int
     const bool ok = i1[q] >= 0 && min_dist <= (unsigned int)(sec_dist * ratio) && min_dist <= (unsigned int)max_dist;
     train_idx[q] = ok ? (int32_t)i1[q] : -1;
     dist[q] = i1[q] < 0 ? 0x7fffffff : d1[q];
+}
+
+int orb_hamming_minmax(const uint8_t *train, int n_train, const uint8_t *query, int n_query, int loc, int32_t *min_max) {
+    ORB_REQUIRE(n_query >= 0 && n_train >= 0 && min_max && (n_query == 0 || query) && (n_train == 0 || train), ORB_ERR_INVALID, "bad argument");
+    min_max[0] = 0x7fffffff; min_max[1] = -1;
+    if (n_query == 0 || n_train == 0) return ORB_OK;
+    const size_t o_q = a256(16), o_t = o_q + a256((size_t)n_query * 32);
+    ThreadCtx *T = nullptr;
+    int rc = orbgpu_thread_ctx(&T, loc == ORB_HOST ? o_t + a256((size_t)n_train * 32) : o_q, 0);
+    if (rc != ORB_OK) return rc;
+    cudaStream_t st = T->stream;
+    const uint8_t *d_q = query, *d_t = train;
+    if (loc == ORB_HOST) {
+        ORB_CUDA_TRY(cudaMemcpyAsync(T->d_buf + o_q, query, (size_t)n_query * 32, cudaMemcpyHostToDevice, st));
+        ORB_CUDA_TRY(cudaMemcpyAsync(T->d_buf + o_t, train, (size_t)n_train * 32, cudaMemcpyHostToDevice, st));
+        d_q = T->d_buf + o_q; d_t = T->d_buf + o_t;
+    }
+    int *d_out = (int *)T->d_buf;
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_out, min_max, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
+    k_dist_minmax<<<(n_query + 7) / 8, 256, 0, st>>>(d_q, n_query, d_t, n_train, d_out);
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaMemcpyAsync(min_max, d_out, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
 }
 
 int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio, int max_dist,

@@ -175,3 +175,13 @@ def searchMatches(descp1: np.ndarray, descp2: np.ndarray, ratio: float = 0.8, ma
                                                    ptr(dist)), "orb_search_matches_ratio")
     keep = np.nonzero(idx >= 0)[0].astype(np.int32)
     return keep, idx[keep], dist[keep].astype(np.float32)
+
+
+def hamming_minmax(descp1: np.ndarray, descp2: np.ndarray):
+    """Smallest / largest Hamming distance over all (query = descp2, train = descp1) pairs: naive_nn_search2's minD / maxD
+    bookkeeping (ref AR-1.3/src/ORBMatcher.cpp:92-93).  (INT_MAX, -1) without a pair."""
+    t = np.ascontiguousarray(descp1, np.uint8).reshape(-1, 32)
+    q = np.ascontiguousarray(descp2, np.uint8).reshape(-1, 32)
+    mm = np.zeros(2, np.int32)
+    _lib.check(_lib.lib().orb_hamming_minmax(ptr(t), len(t), ptr(q), len(q), ORB_HOST, ptr(mm)), "orb_hamming_minmax")
+    return int(mm[0]), int(mm[1])

@@ -95,4 +95,23 @@ bool SearchMatches(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv:
     return true;
 }
 
+void NaiveNNSearch(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches) {
+    std::vector<cv::DMatch> all;
+    BruteForceMatchHamming(descp2, descp1, all);   // query = frame (keys2), train = marker (keys1)
+    for (size_t i = 0; i < all.size(); i++)
+        if (all[i].trainIdx >= 0 && all[i].distance <= 50.f) matches.push_back(all[i]);
+}
+
+void NaiveNNSearch2(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches, unsigned int &minD, unsigned int &maxD) {
+    SearchMatches(descp1, descp2, matches);
+    cv::Mat tc = descp1.isContinuous() ? descp1 : descp1.clone(), qc = descp2.isContinuous() ? descp2 : descp2.clone();
+    int32_t mm[2];
+    if (orb_hamming_minmax(tc.data, descp1.rows, qc.data, descp2.rows, ORB_HOST, mm) != ORB_OK)
+        throw std::runtime_error(std::string("orbgpu_shim::NaiveNNSearch2: ") + orb_last_error());
+    if (mm[1] >= 0) {   // `if (dist <= minD) minD = dist; if (dist > maxD) maxD = dist;` over every pair
+        if ((unsigned int)mm[0] <= minD) minD = (unsigned int)mm[0];
+        if ((unsigned int)mm[1] > maxD) maxD = (unsigned int)mm[1];
+    }
+}
+
 }  // namespace orbgpu_shim

@@ -39,5 +39,11 @@ void BruteForceMatchHamming(const cv::Mat &queryDescriptors, const cv::Mat &trai
 // DMatch(i, trainIdx, 0, min_dist) for every accepted query i (ratio 0.8, distance <= 50).  Returns true as the reference does.
 bool SearchMatches(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches);
 
+// AR-1.3's copies (AR-1.3/src/ORBMatcher.cpp): naive_nn_search (:44-68, nearest train row, kept when distance <= 50) and
+// naive_nn_search2 (:70-102, the ratio matcher above plus the file-scope `minD` / `maxD` bookkeeping over all pairs that
+// ORBMatcher::Match filters with, :147-152): pass the reference's two globals.
+void NaiveNNSearch(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches);
+void NaiveNNSearch2(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches, unsigned int &minD, unsigned int &maxD);
+
 }  // namespace orbgpu_shim
 #endif

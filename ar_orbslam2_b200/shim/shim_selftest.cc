@@ -77,7 +77,15 @@ int main(int argc, char **argv) {
         dump(pre + "_md2.bin", md2.data, (size_t)md2.rows * 32);
         dump(pre + "_mbf.bin", bf.data(), bf.size() * sizeof(cv::DMatch));
         dump(pre + "_mrm.bin", rm.data(), rm.size() * sizeof(cv::DMatch));
-        printf("marker ok n1=%zu n2=%zu bf=%zu ratio=%zu\n", mk1.size(), mk2.size(), bf.size(), rm.size());
+        // AR-1.3's naive_nn_search / naive_nn_search2 with its file-scope minD / maxD (ORBMatcher.cpp:17-18)
+        std::vector<cv::DMatch> n1, n2;
+        unsigned int minD = 100, maxD = 0;
+        orbgpu_shim::NaiveNNSearch(md1, md2, n1);
+        orbgpu_shim::NaiveNNSearch2(md1, md2, n2, minD, maxD);
+        dump(pre + "_mn1.bin", n1.data(), n1.size() * sizeof(cv::DMatch));
+        dump(pre + "_mn2.bin", n2.data(), n2.size() * sizeof(cv::DMatch));
+        printf("marker ok n1=%zu n2=%zu bf=%zu ratio=%zu nn=%zu nn2=%zu minD=%u maxD=%u\n", mk1.size(), mk2.size(), bf.size(), rm.size(), n1.size(),
+               n2.size(), minD, maxD);
     }
     if (argc > 7) {   // latency of the calls a Tracking thread makes, without the host mirror of the pyramid (median of 50)
         auto med = [](std::vector<double> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };

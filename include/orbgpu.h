@@ -449,6 +449,12 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
 int orb_search_matches_ratio(const uint8_t *train, int n_train, const uint8_t *query, int n_query, double ratio,
                              int max_dist, int loc, int32_t *train_idx, int32_t *dist);
 
+/* ref: the `minD` / `maxD` bookkeeping inside naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:92-93), which ORBMatcher::Match uses
+ * for its `distance <= 0.5 * maxD` filter (:147-152): min_max[0] / [1] = the smallest / largest Hamming distance over ALL
+ * (query, train) pairs (INT_MAX / -1 when there is no pair).  The reference keeps them in globals across calls (initial 100 / 0,
+ * `if (dist <= minD) minD = dist; if (dist > maxD) maxD = dist;`): the caller merges the same way.  min_max is a host array. */
+int orb_hamming_minmax(const uint8_t *train, int n_train, const uint8_t *query, int n_query, int loc, int32_t *min_max);
+
 /* ---- OpenCV-style cv::ORB (Harris score) for the marker pipeline --------------- */
 
 /* ref: `ORB orb; orb(mImage1, Mat(), mvKeys1, mDescriptors1);` in Marker::setTargetImage (src/Marker.cc:83-84) and the same

@@ -44,3 +44,19 @@ def test_gpu_equals_reference_marker_cc(seed, nt, nq):
     qi, ti, d = searchMatches(train, query)
     rq, rt, rd = orbref.ref_marker_search_matches(train, query)
     assert np.array_equal(qi, rq) and np.array_equal(ti, rt) and np.array_equal(d, rd)
+
+
+@pytest.mark.parametrize("seed,nt,nq", [(20, 300, 1200), (21, 1, 50), (22, 0, 10), (23, 40, 0), (24, 1000, 33)])
+def test_minmax_over_all_pairs(seed, nt, nq):
+    """naive_nn_search2's minD / maxD bookkeeping (AR-1.3/src/ORBMatcher.cpp:92-93): min and max distance over every pair"""
+    from ar_orbslam2_b200.matcher import hamming_minmax
+    train, query = marker_case(seed, nt, max(nq, 1))
+    query = query[:nq]
+    got = hamming_minmax(train, query)
+    if nt == 0 or nq == 0:
+        assert got == (0x7fffffff, -1)
+        return
+    d = np.unpackbits(query[:, None, :] ^ train[None, :, :], axis=2).sum(axis=2)   # numpy restatement of hamdist2 over all pairs
+    assert got == (int(d.min()), int(d.max()))
+    bd, _, _, _ = orbref.hamming_top2(query, train)
+    assert got[0] == int(bd.min())

@@ -163,6 +163,22 @@ struct MarkerMembers {   // Marker.h: the members the lifted lines touch
     }
 };
 ''' % (set_target, match)
+    # AR-1.3/src/ORBMatcher.cpp:124-131: the constructor with all eight arguments and operator() with useProvidedKeypoints
+    ar = "".join(open("/root/reference/AR-1.3/src/ORBMatcher.cpp", errors="replace").readlines()[124:126])
+    assert "ORB orb1(300" in ar
+    src += r"""
+int ar13(Mat img1, Mat img2) {
+    using orbgpu_shim::ORB;
+%s
+    vector<KeyPoint> keys1, keys2; Mat descriptors1, descriptors2;
+    orb1.operator()(img1, Mat(), keys1, descriptors1, false);
+    orb2(img2, Mat(), keys2, descriptors2, false);
+    vector<DMatch> matches; unsigned int minD = 100, maxD = 0;
+    orbgpu_shim::NaiveNNSearch(descriptors1, descriptors2, matches);
+    orbgpu_shim::NaiveNNSearch2(descriptors1, descriptors2, matches, minD, maxD);
+    return (int)matches.size();
+}
+""" % ar
     tu = tmp_path / "marker_sites.cc"
     tu.write_text(src)
     p = subprocess.run(["g++", "-std=gnu++11", "-fsyntax-only", "-Wall", "-I" + SHIM, "-I" + os.path.join(ROOT, "include"), str(tu)],

@@ -56,6 +56,16 @@ def test_cpp_shim_stereo_frame(oracle, gpu_lib, tmp_path):
     tidx, dist = oracle.search_matches_ratio(md1, md2)
     keep = np.nonzero(tidx >= 0)[0]
     assert np.array_equal(rm["queryIdx"], keep) and np.array_equal(rm["trainIdx"], tidx[keep]) and np.array_equal(rm["distance"], dist[keep])
+    # AR-1.3's naive_nn_search (nearest marker row per frame row, kept when <= 50) and naive_nn_search2 (= the ratio matcher) + minD / maxD
+    nd, ni, _, _ = oracle.hamming_top2(md2, md1)
+    k1 = np.nonzero(nd <= 50)[0]
+    n1 = g("mn1", dmatch)
+    assert np.array_equal(n1["queryIdx"], k1) and np.array_equal(n1["trainIdx"], ni[k1]) and np.array_equal(n1["distance"], nd[k1])
+    assert g("mn2", dmatch).tobytes() == rm.tobytes()
+    alld = np.unpackbits(md2[:, None, :] ^ md1[None, :, :], axis=2).sum(axis=2)
+    import re
+    m = re.search(r"minD=(\d+) maxD=(\d+)", out.stdout)
+    assert m and int(m.group(1)) == min(100, int(alld.min())) and int(m.group(2)) == int(alld.max())
 
 
 def test_cpp_matcher_shim_equals_reference(oracle, gpu_lib):
