@@ -71,3 +71,19 @@ def StereoFrame(extractor, image_left, image_right, mbf: float, mb: float, capac
         _lib.check(rc, "orb_stereo_frame")
     a, b = nl.value, nr.value
     return kl[:a].copy(), dl[:a].copy(), kr[:b].copy(), dr[:b].copy(), ur[:a].copy(), dp[:a].copy()
+
+
+def ComputeStereoFromRGBD(keys, keys_un, im_depth: np.ndarray, mbf: float, depth_factor: float = 1.0):
+    """Frame::ComputeStereoFromRGBD (ref Frame.cc:645-667) with the convertTo of Tracking.cc:553-554 folded in: im_depth is the
+    CV_32F or CV_16U depth image, depth_factor = mDepthMapFactor.  Returns (mvuRight, mvDepth)."""
+    import ctypes as C
+    from . import _lib
+    from ._abi import KEYPOINT_DTYPE, ORB_HOST, ptr
+    k = np.ascontiguousarray(keys, KEYPOINT_DTYPE)
+    ku = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+    assert im_depth.ndim == 2 and im_depth.dtype in (np.float32, np.uint16) and im_depth.strides[1] == im_depth.itemsize
+    ur, dp = np.zeros(len(k), np.float32), np.zeros(len(k), np.float32)
+    _lib.check(_lib.lib().orb_depth_from_rgbd(ptr(k), ptr(ku), len(k), C.c_void_p(im_depth.ctypes.data), int(im_depth.dtype == np.uint16),
+                                              im_depth.shape[1], im_depth.shape[0], im_depth.strides[0], C.c_float(depth_factor),
+                                              C.c_float(mbf), ORB_HOST, ptr(ur), ptr(dp)), "orb_depth_from_rgbd")
+    return ur, dp

@@ -438,6 +438,18 @@ int orb_db_merge_top2(orb_db *db, int nshards, int nq, const int32_t *best_dist,
                       const int32_t *second_dist, const int64_t *second_idx, int32_t *out_best_dist,
                       int64_t *out_best_idx, int32_t *out_second_dist, int64_t *out_second_idx);
 
+/* ---- RGB-D depth association ------------------------------------------------------------------ */
+
+/* ref: Frame::ComputeStereoFromRGBD (src/Frame.cc:645-667), the RGB-D Frame constructor's counterpart of ComputeStereoMatches
+ * (:151), with `imDepth.convertTo(imDepth, CV_32F, mDepthMapFactor)` (src/Tracking.cc:553-554) folded in: for key point i,
+ * d = depth(v, u) at (int)mvKeys[i].pt; when d > 0: depth[i] = d and u_right[i] = mvKeysUn[i].pt.x - mbf / d, else both -1.
+ * depth_type 0: CV_32F map (multiplied by depth_factor unless it is exactly 1), 1: CV_16U map (d = (float)raw * depth_factor,
+ * OpenCV's convertTo arithmetic).  loc applies to keys, keys_un, the depth map and the outputs; ORB_DEVICE calls are
+ * asynchronous on the thread's call stream.                                                                          */
+int orb_depth_from_rgbd(const orb_keypoint *keys, const orb_keypoint *keys_un, int n, const void *depth_map, int depth_type,
+                        int width, int height, int pitch_bytes, float depth_factor, float mbf, int loc, float *u_right,
+                        float *depth);
+
 /* ---- marker / AR brute-force matching ------------------------------------------ */
 
 /* ref: Marker::searchMatches (src/Marker.cc:314-349) and naive_nn_search2 (AR-1.3/src/ORBMatcher.cpp:70-102): for every

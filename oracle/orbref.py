@@ -781,3 +781,28 @@ def retain_best(responses, n_points, depth_limit=-1):
     n = C.c_int(0)
     _check(lib().orbref_retain_best(ptr(r), len(r), int(n_points), int(depth_limit), ptr(order), C.byref(n)), "retain_best")
     return order[: n.value].copy()
+
+
+def refm_stereo_from_rgbd(keys, keys_un, depth_f32, mbf):
+    """Frame::ComputeStereoFromRGBD run from the reference's own Frame.cc (oracle/_ref/liborbmatcher_ref.so)."""
+    lib_ = ReferenceSourceBackend().L
+    k = np.ascontiguousarray(keys, KEYPOINT_DTYPE); ku = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+    d = np.ascontiguousarray(depth_f32, np.float32)
+    ur, dp = np.zeros(len(k), np.float32), np.zeros(len(k), np.float32)
+    _check(lib_.refm_stereo_from_rgbd(ptr(k), ptr(ku), len(k), ptr(d), d.shape[1], d.shape[0], C.c_float(mbf), ptr(ur), ptr(dp)), "refm rgbd")
+    return ur, dp
+
+
+def stereo_from_rgbd(keys, keys_un, im_depth, mbf, depth_factor=1.0):
+    """Restatement of Frame::ComputeStereoFromRGBD (Frame.cc:645-667) + the convertTo of Tracking.cc:553-554 in numpy fp32."""
+    k = np.ascontiguousarray(keys, KEYPOINT_DTYPE); ku = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+    d = im_depth
+    if d.dtype != np.float32 or np.float32(depth_factor) != np.float32(1):
+        d = (d.astype(np.float32) * np.float32(depth_factor)).astype(np.float32)   # convertTo(CV_32F, alpha): (float)src * alpha
+    v, u = k["y"].astype(np.int32), k["x"].astype(np.int32)                        # at<float>(float, float): truncation
+    dd = d[v, u]
+    ok = dd > 0
+    ur, dp = np.full(len(k), -1, np.float32), np.full(len(k), -1, np.float32)
+    dp[ok] = dd[ok]
+    ur[ok] = ku["x"][ok] - (np.float32(mbf) / dd[ok]).astype(np.float32)
+    return ur, dp

@@ -459,6 +459,24 @@ int refm_stereo_match(const uint8_t *img_left, const uint8_t *img_right, int wid
     for (int i = 0; i < N; i++) { uRight[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
     return 0;
 }
+// ref Frame::ComputeStereoFromRGBD, Frame.cc:645-667, run from the reference's own Frame.cc on a CV_32F depth image
+int refm_stereo_from_rgbd(const orb_keypoint *keys, const orb_keypoint *keys_un, int N, const float *depth_map, int width, int height,
+                          float mbf, float *uRight, float *depth) {
+    Frame F;
+    F.N = N;
+    auto conv = [](const orb_keypoint *k, int n) {
+        std::vector<cv::KeyPoint> v(n);
+        for (int i = 0; i < n; i++) v[i] = cv::KeyPoint(k[i].x, k[i].y, k[i].size, k[i].angle, k[i].response, k[i].octave, k[i].class_id);
+        return v;
+    };
+    F.mvKeys = conv(keys, N); F.mvKeysUn = conv(keys_un, N);
+    F.mbf = mbf;
+    cv::Mat imDepth(height, width, CV_32F);
+    memcpy(imDepth.data, depth_map, (size_t)width * height * 4);
+    F.ComputeStereoFromRGBD(imDepth);
+    for (int i = 0; i < N; i++) { uRight[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+    return 0;
+}
 #endif
 
 static void set_pose(KeyFrame *K, const float *R9, const float *t3) {
