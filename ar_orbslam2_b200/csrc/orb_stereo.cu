@@ -245,40 +245,69 @@ __global__ void __launch_bounds__(ST_WARPS * 32) k_stereo_match(StereoArgs A) {
 
 // Median-SAD rejection (ref :629-642): thDist = 1.5f*1.4f*median, where median is element size/2 of
 // the ascending (SAD, iL) list.
-__global__ void __launch_bounds__(1024) k_stereo_filter(StereoArgs A, int sort_n) {
-    extern __shared__ int s_keys[];
-    __shared__ int s_count;
+// The reference sorts the (SAD, index) pairs only to read the median SAD and to drop everything at or above 2.1 x median (ref
+// :629-642): an order statistic, found here by a two-level radix select over the 16-bit SAD range (121 pixels x 510 < 2^16) -- a
+// histogram of the high bytes, a scan to the bucket that holds rank count / 2, a histogram of that bucket's low bytes -- instead of
+// a bitonic sort of `capacity` keys (48 -> ~6 us per batch of 144 pairs; the kernel runs one CTA per pair, i.e. on a mostly
+// empty GPU).
+__global__ void __launch_bounds__(1024) k_stereo_filter(StereoArgs A) {
+    __shared__ int s_hist[256], s_count, s_bucket, s_rank, s_median;
     const int b = blockIdx.x, tid = threadIdx.x;
     const int N = min(A.nL[b], A.capacity);
-    if (tid == 0) s_count = 0;
-    for (int i = tid; i < sort_n; i += 1024) s_keys[i] = 0x7fffffff;
-    __syncthreads();
     const int32_t *sad = A.sad + (size_t)b * A.capacity;
-    for (int i = tid; i < N; i += 1024)
-        if (sad[i] >= 0) s_keys[atomicAdd(&s_count, 1)] = sad[i];
+    auto select = [&](int rank) {   // thread-uniform: bucket of s_hist that holds the element of 0-based rank `rank`; sets s_bucket, s_rank
+        if (tid < 32) {
+            int c[8], tot = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) { c[i] = s_hist[tid * 8 + i]; tot += c[i]; }
+            int incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (tid >= o) incl += t;
+            }
+            int before = incl - tot;
+            if (rank >= before && rank < incl) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    if (rank >= before && rank < before + c[i]) { s_bucket = tid * 8 + i; s_rank = rank - before; }
+                    before += c[i];
+                }
+            }
+        }
+    };
+    if (tid < 256) s_hist[tid] = 0;
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int i = tid; i < N; i += 1024) {
+        const int v = sad[i];
+        if (v >= 0) { atomicAdd(&s_hist[(v >> 8) & 255], 1); mine++; }
+    }
+    if (mine) atomicAdd(&s_count, mine);
     __syncthreads();
     const int count = s_count;
     if (count == 0) {
         if (tid == 0) A.n_matched[b] = 0;
         return;
     }
-    for (int k = 2; k <= sort_n; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < sort_n; i += 1024) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const int a = s_keys[i], c = s_keys[ixj];
-                    const bool asc = (i & k) == 0;
-                    if (asc ? (a > c) : (a < c)) { s_keys[i] = c; s_keys[ixj] = a; }
-                }
-            }
-            __syncthreads();
-        }
-    const float median = (float)s_keys[count / 2];
+    select(count / 2);                       // median = vDistIdx[vDistIdx.size() / 2].first
+    __syncthreads();
+    const int hi = s_bucket, rank2 = s_rank;
+    __syncthreads();
+    if (tid < 256) s_hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < N; i += 1024) {
+        const int v = sad[i];
+        if (v >= 0 && ((v >> 8) & 255) == hi) atomicAdd(&s_hist[v & 255], 1);
+    }
+    __syncthreads();
+    select(rank2);
+    __syncthreads();
+    if (tid == 0) { s_median = (hi << 8) | s_bucket; s_count = 0; }
+    __syncthreads();
+    const float median = (float)s_median;
     const float thDist = __fmul_rn(1.5f * 1.4f, median);
-    __syncthreads();
-    if (tid == 0) s_count = 0;
-    __syncthreads();
     int kept = 0;
     for (int i = tid; i < N; i += 1024) {
         if (sad[i] >= 0) {
@@ -304,7 +333,6 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     ORB_REQUIRE(left && right && keys_left && desc_left && n_left && keys_right && desc_right && n_right && u_right && depth,
                 ORB_ERR_INVALID, "null argument");
     ORB_REQUIRE(batch >= 1 && capacity >= 1, ORB_ERR_INVALID, "bad batch/capacity");
-    ORB_REQUIRE(capacity <= 32768, ORB_ERR_INVALID, "capacity %d: the median filter sorts up to 32768 matches per pair in shared memory", capacity);
     ORB_REQUIRE(left->device == right->device, ORB_ERR_INVALID, "left and right extractors must live on one device");
     ORB_REQUIRE(left->geom.width > 0 && right->geom.width > 0, ORB_ERR_INVALID, "extract the pair before matching");
     ORB_REQUIRE(left->geom.nlevels == right->geom.nlevels && left->geom.width == right->geom.width &&
@@ -364,18 +392,7 @@ int orb_stereo_match_batch(orb_extractor *left, int left_slot, orb_extractor *ri
     }
     k_stereo_rowtable<<<batch, ROWTAB_THREADS, (nrows + 1) * sizeof(int), st>>>(A);
     k_stereo_match<<<dim3((capacity + ST_WARPS - 1) / ST_WARPS, batch), ST_WARPS * 32, 0, st>>>(A);
-    int sort_n = 1;
-    while (sort_n < capacity) sort_n <<= 1;
-    if (sort_n * 4 > 48 * 1024) {   // per function and device, not per call: raised once to the largest size the check above admits
-        static std::mutex mu;
-        static bool raised[64] = {};
-        std::lock_guard<std::mutex> lk(mu);
-        if (!raised[left->device & 63]) {
-            ORB_CUDA_TRY(cudaFuncSetAttribute(k_stereo_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4));
-            raised[left->device & 63] = true;
-        }
-    }
-    k_stereo_filter<<<batch, 1024, sort_n * 4, st>>>(A, sort_n);
+    k_stereo_filter<<<batch, 1024, 0, st>>>(A);
     left->launches += 3;
     ORB_CUDA_TRY(cudaGetLastError());
     if (right != left) {   // the right handle's next extraction must not overwrite its pyramid while these kernels read it
