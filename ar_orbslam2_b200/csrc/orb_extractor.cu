@@ -1257,9 +1257,10 @@ k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, co
     // flat slot -> (level, index) over the per-level kept capacities
     int slot = blockIdx.x * DESC_WARPS + warp;
     if (slot >= P.lv[P.nlevels - 1].cap_end) return;
-    int level = 0;
+    int level = 0;   // number of l in [0, 15) with slot >= cap_end[l] (cap_end ascends; beyond nlevels - 2 it is the total > slot): 4 probes
 #pragma unroll
-    for (int l = 0; l < ORB_MAX_LEVELS - 1; l++) level += (slot >= P.lv[l].cap_end);   // cap_end of the levels beyond nlevels - 2 = the total > slot
+    for (int step = ORB_MAX_LEVELS / 2; step >= 1; step >>= 1)
+        if (slot >= P.lv[level + step - 1].cap_end) level += step;
     if (level > 0) slot -= P.lv[level - 1].cap_end;
     // kept counts of all levels: lane l holds level l's, an inclusive warp scan gives this level's output base and the total
     const uint32_t *kc = kept_count + (size_t)b * P.nlevels;
