@@ -1149,9 +1149,14 @@ k_octree(const Geom *__restrict__ G, const uint32_t *__restrict__ cand, const ui
 // ------------------------------------------------------------------------------------------
 constexpr int BLUR_ROWS = 16;
 
+// (16 resident CTAs of 128 threads = every warp slot, 32 registers without spills: 0.923 -> 0.915 ms for blur + describe against 12 CTAs
+// at 40 registers; an explicit minimum of 1 made ptxas take 48 registers: 0.928)
+#ifndef ORBGPU_BLUR_MINB
+#define ORBGPU_BLUR_MINB 16
+#endif
 template <int TAPS>   // 0: OpenCV 3.x / 4.x fixed-point taps, 1: OpenCV 2.4's (compile-time: the tap vectors are immediates and the
                       // 2.4-only clamp disappears from the default build -- they were ~10 of 84 instructions per word-row)
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, ORBGPU_BLUR_MINB)
 k_blur_planes(const uint8_t *__restrict__ pyr, uint8_t *__restrict__ blur, const Geom *__restrict__ G, int level) {
     const LevelGeom &g = G->lv[level];
     const int wx = blockIdx.x * blockDim.x + threadIdx.x;     // word column of the interior
@@ -1248,7 +1253,9 @@ struct DescParams {   // by value: lives in the constant bank, no dependent glob
     DescLevel lv[ORB_MAX_LEVELS];
 };
 
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+// (8 resident CTAs = every warp slot of the SM: the kernel waits for its gathers -- 0.940 -> 0.903 ms for blur + describe per 288 frames
+// against 6 CTAs at 38 registers; 32 registers, no spills)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 8)
 k_describe(const uint8_t *__restrict__ pyr, const uint8_t *__restrict__ blur, const DescParams P,
            const Kept *__restrict__ kept, const uint32_t *__restrict__ kept_count, orb_keypoint *__restrict__ out_kp,
            uint8_t *__restrict__ out_desc, int32_t *__restrict__ out_n, int capacity, int *__restrict__ err) {
