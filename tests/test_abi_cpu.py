@@ -61,6 +61,16 @@ def test_no_cpu_fallback(lib):
         hamming_top2(np.zeros((1, 32), np.uint8), np.zeros((4, 32), np.uint8))
     from ar_orbslam2_b200.synth import synth_vocabulary
     from ar_orbslam2_b200.vocabulary import ORBVocabulary
+    from ar_orbslam2_b200 import cvorb
+    from ar_orbslam2_b200.stereo import ComputeStereoFromRGBD
+    from ar_orbslam2_b200._abi import KEYPOINT_DTYPE
+    with pytest.raises(_lib.OrbGpuError) as e:
+        cvorb.ORB()
+    assert e.value.code == -2
+    with pytest.raises(_lib.OrbGpuError):
+        cvorb.retain_best(np.arange(10, dtype=np.float32), 3)
+    with pytest.raises(_lib.OrbGpuError):
+        ComputeStereoFromRGBD(np.zeros(4, KEYPOINT_DTYPE), np.zeros(4, KEYPOINT_DTYPE), np.ones((8, 8), np.float32), 40.0)
     voc = synth_vocabulary(3, 2, seed=0)
     with pytest.raises(_lib.OrbGpuError) as e:
         ORBVocabulary.from_arrays(3, 2, voc["parent"], voc["descriptors"], voc["weight"], voc["word_id"])
