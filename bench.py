@@ -1356,6 +1356,9 @@ def run_ours(args):
                                        "288-frame step of this command, scaled by frames",
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom]},
+        "roofline_stages": {k: {"ms": kern[k], "achieved_GBps": alg[k] * NF / (kern[k] * 1e-3) / 1e9,
+                                "frac": alg[k] * NF / (kern[k] * 1e-3) / 1e9 / hbm_peak,
+                                "traffic": traffic.get(k, 0) * NF / 288.0 or None} for k in alg},
         "roofline_step": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak,
                           "algorithmic_bytes_per_frame": step_alg_bytes, "formula": "P*(1+2S)+60N (SURVEY 8d)"},
         "stage_ms_per_step": dict({STAGES[i]: per_call[i] for i in range(6)},
