@@ -501,7 +501,8 @@ int orb_cvorb_capacity(const orb_cvorb *h);
  * one without key points gives *n_out = 0.  ORB_ERR_CAPACITY (with *n_out = the needed size) if capacity is too small. */
 int orb_cvorb_detect_and_compute(orb_cvorb *h, const uint8_t *image, int width, int height, int pitch, int image_loc,
                                  orb_keypoint *keypoints, uint8_t *descriptors, int capacity, int *n_out);
-/* debugging / tests: layer `level` of the last call (blurred = what the descriptors sampled), its size */
+/* debugging / tests: layer `level` of the last call as the descriptors sampled it (blurred), and its size; level | 256 selects the
+ * unblurred layer, level | 512 the FAST score map (score = arc strength - 1 inside the region the detector evaluates, else stale) */
 int orb_cvorb_level(orb_cvorb *h, int level, uint8_t *dst, int dst_pitch, int *width, int *height);
 /* tests: KeyPointsFilter::retainBest alone, on `n` host responses: order_out receives the surviving original indices in the
  * order std::nth_element + std::partition leave them (depth_limit < 0: libstdc++'s own 2*floor(log2 n); >= 0 forces the
