@@ -13,6 +13,8 @@
 #include "orb_common.cuh"
 
 #include <algorithm>
+#include <cstdint>
+#include <mutex>
 #include <vector>
 
 namespace orbgpu {
@@ -343,6 +345,83 @@ int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t 
     ORB_CUDA_TRY(cudaMemcpyAsync(best_dist, o_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaMemcpyAsync(second_dist, o_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
     ORB_CUDA_TRY(cudaStreamSynchronize(st));
+    return ORB_OK;
+}
+
+}  // extern "C"
+
+// ---- orb_hamming_top2_static: the same scan for callers that must not allocate ---------------------------------------
+//
+// Who this is for: code that runs where device allocation is off the table -- a relocalisation or loop-closing query issued from
+// a real-time tracking loop whose memory was sized at start-up, a host that has handed the whole GPU heap to another allocator
+// (a torch caching pool, a fixed arena) and does not want a second one growing beside it, or a process close to its memory limit
+// where a cudaMalloc in the middle of a frame may fail or stall every stream on the device while the driver maps memory.
+// orb_hamming_top2 grows a per-thread scratch block with cudaMalloc whenever a query needs more chunk partials than the last one;
+// this variant keeps those partials in a fixed array that is part of the library image instead.
+//
+// The array below is 6 MiB and exists once per GPU that loads liborbgpu, from module load to process exit, whether or not this
+// entry point is ever called.  Every call on a device uses the same array, so two calls whose kernels can run at the same time on
+// that device (different streams, different host threads) overwrite each other's partials: order them on one stream or with events.
+// The array keeps whatever the previous call left in it.  Nothing has to be cleared for the next call: the scan kernel writes
+// every (chunk, query) partial that the merge kernel of the same call reads, and nothing else is read.
+namespace {
+constexpr size_t TOP2_STATIC_BYTES = (size_t)ORB_TOP2_STATIC_MAX_PARTIALS * (8 + 8 + 4 + 4);
+static __device__ __align__(256) unsigned char g_top2_static[TOP2_STATIC_BYTES];
+
+// In host code `g_top2_static` is only the host-side shadow the runtime registers for the symbol -- passing it to a kernel would
+// hand the GPU a host address.  The device address differs per GPU and is looked up once per device, with that device current.
+constexpr int TOP2_STATIC_MAX_DEVICES = 64;
+std::mutex g_top2_static_mu;
+void *g_top2_static_addr[TOP2_STATIC_MAX_DEVICES] = {};
+
+int top2_static_address(int dev, void **out) {
+    ORB_REQUIRE(dev >= 0 && dev < TOP2_STATIC_MAX_DEVICES, ORB_ERR_INVALID, "orb_hamming_top2_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_top2_static_mu);
+    if (!g_top2_static_addr[dev]) {
+        void *p = nullptr;
+        ORB_CUDA_TRY(cudaGetSymbolAddress(&p, g_top2_static));   // device `dev` is current: the caller made it so
+        ORB_REQUIRE(p && ((uintptr_t)p & 255) == 0, ORB_ERR_CUDA, "orb_hamming_top2_static: bad scratch address");
+        g_top2_static_addr[dev] = p;
+    }
+    *out = g_top2_static_addr[dev];
+    return ORB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int orb_hamming_top2_static(const uint8_t *dev_queries, int nq, const uint8_t *dev_db, int64_t ndb, int64_t idx_base,
+                            int32_t *dev_best_dist, int64_t *dev_best_idx, int32_t *dev_second_dist, int64_t *dev_second_idx,
+                            void *cuda_stream) {
+    ORB_REQUIRE(dev_queries && dev_best_dist && dev_best_idx && dev_second_dist && dev_second_idx, ORB_ERR_INVALID, "null argument");
+    ORB_REQUIRE(nq >= 1 && ndb >= 0 && (dev_db || ndb == 0), ORB_ERR_INVALID, "bad sizes");
+    ORB_REQUIRE(nq <= ORB_TOP2_STATIC_MAX_QUERIES, ORB_ERR_CAPACITY,
+                "orb_hamming_top2_static: %d queries exceed the fixed scratch (at most %d per call; split the query set, or use "
+                "orb_hamming_top2, which allocates)", nq, ORB_TOP2_STATIC_MAX_QUERIES);
+    int dev = 0, sms = 148;
+    ORB_CUDA_TRY(cudaGetDevice(&dev));
+    ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    void *scratch = nullptr;
+    const int rc = top2_static_address(dev, &scratch);
+    if (rc != ORB_OK) return rc;
+    // same chunking rule as top2_device, with the chunk count additionally held to what the fixed array can take; the merged
+    // result does not depend on how the rows are cut into chunks
+    const int qblocks = (nq + T2_THREADS - 1) / T2_THREADS;
+    long long chunks = std::max<long long>(1, (long long)sms * 8 / qblocks);
+    chunks = std::min<long long>(chunks, std::max<long long>(1, (ndb + T2_TILE - 1) / T2_TILE));
+    chunks = std::min<long long>(chunks, ORB_TOP2_STATIC_MAX_PARTIALS / nq);
+    const long long rows_per_chunk = (std::max<long long>(ndb, 1) + chunks - 1) / chunks;
+    chunks = std::max<long long>(1, (ndb + rows_per_chunk - 1) / rows_per_chunk);
+    const size_t per = (size_t)chunks * nq;
+    ORB_REQUIRE(per <= (size_t)ORB_TOP2_STATIC_MAX_PARTIALS, ORB_ERR_CAPACITY, "orb_hamming_top2_static: internal chunking overflow");
+    int64_t *pi1 = (int64_t *)scratch, *pi2 = pi1 + per;
+    int32_t *pd1 = (int32_t *)(pi2 + per), *pd2 = pd1 + per;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    k_hamming_top2<false><<<dim3(qblocks, (unsigned)chunks), T2_THREADS, 0, st>>>(dev_queries, nq, dev_db, ndb, rows_per_chunk, pd1, pd2,
+                                                                                 pi1, pi2, idx_base, KfParams{});
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>((int)chunks, nq, pd1, pi1, pd2, pi2, dev_best_dist, dev_best_idx, dev_second_dist,
+                                                   dev_second_idx);
+    ORB_CUDA_TRY(cudaGetLastError());
     return ORB_OK;
 }
 

@@ -38,6 +38,20 @@ def hamming_top2(queries: np.ndarray, db: np.ndarray, idx_base: int = 0):
     return d1, i1, d2, i2
 
 
+TOP2_STATIC_MAX_QUERIES = 8192   # ORB_TOP2_STATIC_MAX_QUERIES of include/orbgpu.h
+
+
+def hamming_top2_static_device(d_queries, nq, d_db, ndb, idx_base, o_bd, o_bi, o_sd, o_si, stream=0):
+    """orb_hamming_top2_static: the brute-force top-2 scan for callers that must not allocate device memory while they
+    run (a tracking loop with memory fixed at start-up, a host whose own pool owns the GPU heap).  Every argument is a raw
+    device address; the chunk partials go to a fixed 6 MiB array inside liborbgpu instead of a cudaMalloc'ed block, so at
+    most TOP2_STATIC_MAX_QUERIES queries per call, and calls that can overlap on one GPU must be ordered by the caller.
+    Enqueues on `stream` (a cudaStream_t handle) and returns without waiting."""
+    vp = C.c_void_p
+    _lib.check(_lib.lib().orb_hamming_top2_static(vp(d_queries), int(nq), vp(d_db), C.c_int64(ndb), C.c_int64(idx_base), vp(o_bd),
+                                                  vp(o_bi), vp(o_sd), vp(o_si), vp(stream)), "orb_hamming_top2_static")
+
+
 def top2_merge(best_dist, best_idx, second_dist, second_idx):
     """Merge [nshards, nq] partial lists (shards in database order) into the single-scan result."""
     bd = np.ascontiguousarray(best_dist, np.int32)

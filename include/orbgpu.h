@@ -178,6 +178,30 @@ int orb_hamming_top2(const uint8_t *queries, int nq, const uint8_t *db, int64_t 
                      int64_t idx_base, int32_t *best_dist, int64_t *best_idx,
                      int32_t *second_dist, int64_t *second_idx, int loc);
 
+/* The scan of orb_hamming_top2 for callers that cannot allocate device memory.  (No counterpart in the reference: its
+ * matchers run on the CPU and never own GPU memory.)
+ *
+ * Use it from code that may not call cudaMalloc while it runs: a query made inside a real-time tracking loop whose memory
+ * was fixed at start-up, a host that gave the whole GPU heap to its own pool, a process near its memory limit where an
+ * allocation in mid-frame can fail or stall the other streams.  orb_hamming_top2 grows a per-thread scratch block on
+ * demand; this variant allocates nothing and calls no allocating routine.  Its chunk partials live in a 6 MiB array that
+ * is part of the library image: every GPU that loads liborbgpu holds those 6 MiB until the process exits, used or not.
+ *
+ * All five buffers are DEVICE pointers on the current device; the result is bit-identical to orb_hamming_top2
+ * (256 / -1 where absent, idx_base added).  The two kernels are enqueued on `cuda_stream` (a cudaStream_t; NULL = the
+ * default stream) and the call returns without synchronising: wait on that stream before reading the outputs.
+ * Limits: nq <= ORB_TOP2_STATIC_MAX_QUERIES, else ORB_ERR_CAPACITY and nothing is launched; ndb is unlimited.
+ * The first call on each device looks up the array's address on that device (the device must be current, as for every
+ * call); make that first call during set-up, before any stream capture is begun.
+ * The array is shared by every call on a device and keeps the previous call's partials; each call overwrites all the
+ * entries it reads, so nothing needs clearing -- but two calls whose kernels can overlap on one GPU (different streams or
+ * threads without an ordering between them) race on it.  Serialise them on one stream or with events.               */
+#define ORB_TOP2_STATIC_MAX_QUERIES 8192
+#define ORB_TOP2_STATIC_MAX_PARTIALS (ORB_TOP2_STATIC_MAX_QUERIES * 32)   /* x 24 bytes = 6 MiB of scratch */
+int orb_hamming_top2_static(const uint8_t *dev_queries, int nq, const uint8_t *dev_db, int64_t ndb,
+                            int64_t idx_base, int32_t *dev_best_dist, int64_t *dev_best_idx,
+                            int32_t *dev_second_dist, int64_t *dev_second_idx, void *cuda_stream);
+
 /* Merge of per-shard top-2 lists in shard order, identical to one scan over the
  * concatenated database.  parts laid out [shard][nq].                         */
 int orb_top2_merge(int nshards, int nq, const int32_t *best_dist, const int64_t *best_idx,
