@@ -2112,6 +2112,8 @@ int orb_extract_batch(orb_extractor *ex, const uint8_t *images, int batch, int w
             }
             ORB_CUDA_TRY(cudaEventRecord(ex->ev_blur, ex->s_blur));   // the last describe: everything before it is ordered in front
             ORB_CUDA_TRY(cudaStreamWaitEvent(st, ex->ev_blur, 0));
+            // the host-output tail below copies nothing when export_host is set (it expects the pinned block to be filled here)
+            if (export_host) orbgpu_export_results(ex, o_kp, o_desc, o_n, batch, capacity, nullptr, nullptr, nullptr, st);
             return ORB_OK;
         }
         if (ex->overlap && !ex->profiling) {

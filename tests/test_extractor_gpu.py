@@ -397,3 +397,27 @@ def test_l2_sub_batches_give_the_same_bytes(oracle, gpu_lib, monkeypatch):
     k, d = oracle.RefExtractor(1200).extract(frames[26])
     assert a[26][0].tobytes() == k.tobytes() and np.array_equal(a[26][1], d)
     ex.close(); ex_whole.close()
+
+
+def test_l2_sub_batches_with_pinned_export(oracle, gpu_lib, monkeypatch):
+    """A sub-batched call whose results are small enough for the pinned export block (12 frames, capacity 788: 567 KB <= 1 MB):
+    the sub-batch branch has to fill that block itself, because the host-output tail then copies nothing else.  Run twice with
+    different frames so stale contents of the block would show."""
+    from ar_orbslam2_b200.extractor import ORBextractor
+    w, h, nb = 752, 480, 12
+    monkeypatch.setenv("ORBGPU_CHUNK_MB", "1")
+    ex = ORBextractor(500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    monkeypatch.delenv("ORBGPU_CHUNK_MB")
+    ex_whole = ORBextractor(500, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nb)
+    assert nb * ex.default_capacity * 60 <= 1 << 20 and nb * w * h > 4 << 20
+    for first in (700, 740):
+        frames = np.stack([synth_frame(w, h, first + s) for s in range(nb)])
+        l0 = ex.launch_count, ex_whole.launch_count
+        a, b = ex.extract_batch(frames), ex_whole.extract_batch(frames)
+        assert ex.launch_count - l0[0] > ex_whole.launch_count - l0[1]      # it did run as sub-batches
+        for i in range(nb):
+            assert len(a[i][0]) > 400
+            assert a[i][0].tobytes() == b[i][0].tobytes() and np.array_equal(a[i][1], b[i][1]), i
+        k, d = oracle.RefExtractor(500).extract(frames[nb - 1])
+        assert a[nb - 1][0].tobytes() == k.tobytes() and np.array_equal(a[nb - 1][1], d)
+    ex.close(); ex_whole.close()
