@@ -200,6 +200,7 @@ __global__ void k_popc_rate(unsigned *out, int iters) {
 struct Top2Scratch {
     void *buf = nullptr;
     size_t bytes = 0;
+    int device = -1;   // the device `buf` lives on: a thread that moves to another device gets a new block there
 };
 
 // scans db[0..ndb) for nq queries on `st`; all pointers are device pointers
@@ -219,11 +220,11 @@ static int top2_device(const uint8_t *d_q, int nq, const uint8_t *d_db, long lon
     chunks = std::max<long long>(1, (ndb + rows_per_chunk - 1) / rows_per_chunk);
     const size_t per = (size_t)chunks * nq;
     const size_t need = per * (4 + 4 + 8 + 8) + 1024;
-    if (scratch->bytes < need) {
-        if (scratch->buf) cudaFree(scratch->buf);
-        scratch->buf = nullptr; scratch->bytes = 0;
+    if (scratch->bytes < need || scratch->device != dev) {
+        if (scratch->buf) cudaFree(scratch->buf);   // (unified addressing: frees the block on whichever device owns it)
+        scratch->buf = nullptr; scratch->bytes = 0; scratch->device = -1;
         ORB_CUDA_TRY(cudaMalloc(&scratch->buf, need));
-        scratch->bytes = need;
+        scratch->bytes = need; scratch->device = dev;
     }
     int64_t *pi1 = (int64_t *)scratch->buf, *pi2 = pi1 + per;
     int32_t *pd1 = (int32_t *)(pi2 + per), *pd2 = pd1 + per;
