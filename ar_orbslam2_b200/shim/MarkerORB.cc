@@ -22,14 +22,16 @@ struct Cached {
 typedef std::tuple<int, float, int, int, int> Key;
 struct Cache {
     std::map<Key, Cached> m;
-    ~Cache() {
-        for (auto &kv : m) orb_cvorb_destroy(kv.second.h);
-    }
 };
-thread_local Cache g_cache;
+// never deleted: no CUDA call may run from a thread_local destructor at thread / process exit (see ORBmatcher_gpu.cc);
+// ReleaseThreadHandles() frees the calling thread's handles explicitly
+Cache &thread_cache() {
+    thread_local Cache *c = new Cache;
+    return *c;
+}
 
 orb_cvorb *handle_for(const Key &k, int w, int h) {
-    Cached &c = g_cache.m[k];
+    Cached &c = thread_cache().m[k];
     if (c.h && w <= c.max_w && h <= c.max_h) return c.h;
     if (c.h) orb_cvorb_destroy(c.h);
     c.h = nullptr;
@@ -44,6 +46,12 @@ orb_cvorb *handle_for(const Key &k, int w, int h) {
     return c.h;
 }
 }  // namespace
+
+void ReleaseThreadHandles() {
+    Cache &C = thread_cache();
+    for (auto &kv : C.m) orb_cvorb_destroy(kv.second.h);
+    C.m.clear();
+}
 
 ORB::ORB(int nf, float sf, int nl, int et, int firstLevel, int WTA_K, int st, int patchSize)
     : nfeatures(nf), nlevels(nl), edgeThreshold(et), scoreType(st), scaleFactor(sf) {

@@ -45,5 +45,9 @@ bool SearchMatches(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv:
 void NaiveNNSearch(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches);
 void NaiveNNSearch2(const cv::Mat &descp1, const cv::Mat &descp2, std::vector<cv::DMatch> &matches, unsigned int &minD, unsigned int &maxD);
 
+// The ORB objects above share per-thread device handles that are NOT freed at thread or process exit (no CUDA call may run from
+// an exit-time destructor).  A thread that ends while the process continues calls this first.  No reference counterpart.
+void ReleaseThreadHandles();
+
 }  // namespace orbgpu_shim
 #endif

@@ -30,7 +30,7 @@ static void Check(int rc, const char *what) {
 // per-thread LRU cache afterwards: Tracking calls two or three matchers on mCurrentFrame per camera frame, LocalMapping and
 // LoopClosing revisit the same key frames many times.  The cache key is the identity of the object's buffers (the vectors'
 // and the descriptor matrix's data pointers -- a Frame copy gets new vectors, a KeyFrame keeps its own for life) plus the
-// view flags; a hit is confirmed by a fingerprint of the contents, so an address reused by a later frame (Tracking::Reset
+// view flags; a hit is confirmed by a 64-bit fingerprint of the WHOLE contents, so an address reused by a later frame (Tracking::Reset
 // restarts the ids, frames come and go) cannot alias.  Key points, descriptors and mvuRight never change after the Frame /
 // KeyFrame constructor in the reference (Frame.cc:62-233, KeyFrame.cc:31-63).  ORBGPU_SHIM_NO_CACHE=1 builds per call.
 namespace {
@@ -44,15 +44,38 @@ struct CacheEntry {
 struct FrameCache {
     std::vector<CacheEntry> e;
     uint64_t clock = 0;
-    ~FrameCache() { for (size_t i = 0; i < e.size(); i++) orb_frame_destroy(e[i].h); }
 };
-thread_local FrameCache t_cache;
+// One cache per thread, held through a pointer that is never deleted: a thread_local destructor would call cudaFree /
+// cudaStreamDestroy at thread or process exit, possibly after the CUDA runtime has been torn down (liborbgpu's own per-thread
+// state is left alone at exit for the same reason, csrc/orb_runtime.cu).  A thread that ends while the process goes on calls
+// ReleaseThreadFrameCache() first; otherwise its <= CACHE_MAX device frames (about 0.4 MB each at 2000 key points: SoA key
+// points, descriptors, the 64x48 grid) stay allocated until the process exits.
+FrameCache &thread_cache() {
+    thread_local FrameCache *c = new FrameCache;
+    return *c;
+}
 const size_t CACHE_MAX = 48;
 
 inline uint64_t mix(uint64_t h, const void *p, size_t n) {   // FNV-1a
     const unsigned char *b = static_cast<const unsigned char *>(p);
     for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
     return h;
+}
+
+// the same for whole arrays: four independent multiply-xorshift lanes over 8-byte words (about 0.1 ns per byte on one core,
+// ~10 us for a 2000-point frame), the tail through the byte loop above
+inline uint64_t mix_block(uint64_t h, const void *p, size_t n) {
+    const unsigned char *b = static_cast<const unsigned char *>(p);
+    uint64_t l[4] = {h, h ^ 0x9E3779B97F4A7C15ull, h ^ 0xBF58476D1CE4E5B9ull, h ^ 0x94D049BB133111EBull};
+    size_t i = 0;
+    for (; i + 32 <= n; i += 32) {
+        uint64_t w[4];
+        std::memcpy(w, b + i, 32);
+        for (int k = 0; k < 4; k++) { l[k] = (l[k] ^ w[k]) * 0xD6E8FEB86659FD93ull; l[k] ^= l[k] >> 32; }
+    }
+    h = l[0];
+    for (int k = 1; k < 4; k++) h = (h ^ l[k]) * 1099511628211ull;
+    return mix(h, b + i, n - i);
 }
 
 }  // namespace
@@ -71,17 +94,18 @@ struct GpuFrame {
         const int flags = (keyframeView ? 1 : 0) | (withUr ? 2 : 0);
         uint64_t fp = 1469598103934665603ull;
         if (n) {
-            const int pick[3] = {0, n / 2, n - 1};
-            for (int k = 0; k < 3; k++) {
-                const cv::KeyPoint &q = keysUn[pick[k]];
-                fp = mix(fp, &q.pt.x, 4); fp = mix(fp, &q.pt.y, 4); fp = mix(fp, &q.angle, 4); fp = mix(fp, &q.octave, 4);
-                fp = mix(fp, descriptors.ptr(pick[k]), 32);
-                if (withUr) fp = mix(fp, &uRight[pick[k]], 4);
-            }
+            // EVERY key point, descriptor and uRight goes into the fingerprint: buffer addresses are reused as a matter of course
+            // (Frame copy-assignment keeps the vectors' storage, equal-sized cv::Mat clones get the same block back), so the
+            // contents are the only guard against matching a later frame with a stale device index
+            static_assert(sizeof(cv::KeyPoint) == 28, "cv::KeyPoint is hashed as raw bytes: it must have no padding");
+            fp = mix_block(fp, &keysUn[0], (size_t)n * sizeof(cv::KeyPoint));
+            if (descriptors.isContinuous()) fp = mix_block(fp, descriptors.ptr(0), (size_t)n * 32);
+            else for (int i = 0; i < n; i++) fp = mix_block(fp, descriptors.ptr(i), 32);
+            if (withUr) fp = mix_block(fp, uRight.data(), (size_t)n * 4);
         }
         const float bounds[4] = {Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY};
         fp = mix(fp, bounds, sizeof(bounds));
-        FrameCache &C = t_cache;
+        FrameCache &C = thread_cache();
         if (!noCache)
             for (size_t i = 0; i < C.e.size(); i++) {
                 CacheEntry &c = C.e[i];
@@ -120,6 +144,12 @@ struct GpuFrame {
     GpuFrame(const GpuFrame &) = delete;
     GpuFrame &operator=(const GpuFrame &) = delete;
 };
+
+void ReleaseThreadFrameCache() {
+    FrameCache &C = thread_cache();
+    for (size_t i = 0; i < C.e.size(); i++) orb_frame_destroy(C.e[i].h);
+    C.e.clear();
+}
 
 int SearchByProjection(Frame &F, const std::vector<MapPoint *> &vpMapPoints, float th, float mfNNratio) {
     const int n = (int)vpMapPoints.size();

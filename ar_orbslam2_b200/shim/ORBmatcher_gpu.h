@@ -17,6 +17,12 @@
 namespace ORB_SLAM2 {
 namespace orbgpu_shim {
 
+// Every thread that calls a matcher below keeps up to 48 device-resident frame indices (about 0.4 MB each) in a per-thread cache.
+// Nothing is freed at thread or process exit (CUDA objects must not be destroyed from exit-time destructors); a thread that ends
+// while the process continues -- System::Shutdown joining LocalMapping / LoopClosing, say -- calls this first.  No reference
+// counterpart.
+void ReleaseThreadFrameCache();
+
 // ref ORBmatcher::SearchByProjection(Frame &F, const std::vector<MapPoint*> &vpMapPoints, const float th), ORBmatcher.cc:45-129
 int SearchByProjection(Frame &F, const std::vector<MapPoint *> &vpMapPoints, float th, float mfNNratio);
 
