@@ -243,7 +243,12 @@ void orb_frame_destroy(orb_frame *f);
  * are undistorted on the device when ndist > 0 and dist_coef[0] != 0 (`mvKeysUn = mvKeys` otherwise, :411-415).  u_right =
  * mvuRight (n floats, host or device per u_right_loc; NULL = monocular, all -1; orb_extractor_stereo_result gives the device
  * array orb_stereo_frame left).  Asynchronous on the new frame's stream, ordered after the extraction; the extractor may
- * start its next frame only after the first matcher call on this frame returned, or after orb_frame_sync.  Frames borrow
+ * start its next frame only after the first matcher call on this frame returned, or after orb_frame_sync.
+ * Lifetime: the call reads the key points / descriptors / counts where the extraction LEFT them.  For an extraction with
+ * ORB_DEVICE outputs those are the caller's own device buffers -- keep them allocated and unmodified (no free, no reuse as
+ * the output of another call) over the same span; for ORB_HOST outputs they are the handle's internal buffers, which the
+ * handle's next extraction overwrites.  Only the LAST extraction of `ex` can be indexed: a second orb_extract* on `ex`
+ * before this call makes the slot refer to the newer result.  Frames borrow
  * their stream and buffers from a pool: creating one per camera frame allocates nothing once the pool is warm.        */
 typedef struct orb_frame_source {
     float min_x, max_x, min_y, max_y;
