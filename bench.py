@@ -38,23 +38,29 @@ STAGE_KERNELS = {"pyramid": ("k_pyr_",), "fast_cells": ("k_fast_",), "octree": (
 
 
 def measured_stage_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376), read from the newest
-    committed ncu launch list of this same command (profiles/r*_launch_shares.csv, written by tools/ncu_launch_list.py from an
-    `ncu --metrics ...dram__bytes...` run of bench.py; regenerated whenever a kernel changes).  Returns ({stage: bytes}, file)."""
-    import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_launch_shares.csv")), key=os.path.getmtime)
-    files = sorted(files, key=lambda f: os.path.basename(f))   # r1e < r1m < r2a ...: the name carries the round and the revision
-    if not files:
-        return {}, None
+    """dram__bytes_read.sum + dram__bytes_write.sum per stage of one default step (288 frames of 1241x376) and the step's warp
+    instruction count, read from the ncu launch list that profiles/CURRENT.json NAMES (`launch_shares`: a file written by
+    tools/ncu_launch_list.py from an `ncu --metrics ...dram__bytes...` run of this same command; the entry is changed by hand in
+    the commit that changes a kernel, so a stale list lying around under a later name is never picked up).
+    Returns ({stage: bytes}, file, warp_instructions_per_288_frames)."""
+    cur = os.path.join(ROOT, "profiles", "CURRENT.json")
+    if not os.path.exists(cur):
+        return {}, None, None
+    name = json.load(open(cur)).get("launch_shares")
+    path = os.path.join(ROOT, "profiles", name) if name else None
+    if not path or not os.path.exists(path):
+        return {}, None, None
     out = {k: 0.0 for k in STAGE_KERNELS}
-    for ln in open(files[-1]):
+    winst = 0.0
+    for ln in open(path):
         f = ln.strip().split(",")
         if len(f) < 7 or not f[0].startswith("k_"):
             continue
+        winst += float(f[4])
         for stage, prefixes in STAGE_KERNELS.items():
             if f[0].startswith(prefixes):
                 out[stage] += (float(f[5]) + float(f[6])) * 1e6
-    return out, os.path.relpath(files[-1], ROOT)
+    return out, os.path.relpath(path, ROOT), winst
 
 
 _JSON_FD = None
@@ -515,7 +521,9 @@ def bench_frames_leg(args, torch, dist, dev, local, rank, world, reduce_max, bar
         L.orb_extractor_stage_times(ex._h, sm, C.byref(calls))
         L.orb_extractor_set_profiling(ex._h, 0)
         r["stage_ms_per_batch_serial"] = {STAGES[i]: sm[i] / max(calls.value, 1) for i in range(6)}
-    # ---- end to end from host memory, chunked
+    # ---- end to end from host memory, chunked: at least four chunks per rank whatever the share, so that uploads, kernels and
+    # downloads overlap even when total / N is as small as the nominal chunk (C4 at N = 8: 32 frames per rank)
+    chunk = max(1, min(chunk, (nb + 3) // 4))
     nch = (nb + chunk - 1) // chunk
     sin, sout = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     d_in = [torch.empty((min(chunk, nb), h, w), dtype=torch.uint8, device=dev) for _ in range(2)]
@@ -1308,7 +1316,7 @@ def run_ours(args):
         "octree": 4 * 6 * kp_per_frame + 8 * kp_per_frame,
         "describe": 2 * S_px + 60 * kp_per_frame,   # blur: read the 8 levels, write the 8 blurred levels; then 60 B per keypoint
     }
-    traffic, traffic_file = measured_stage_traffic()
+    traffic, traffic_file, warp_inst_288 = measured_stage_traffic()
     kern = {k: per_call[STAGES.index(k)] for k in alg}
     dom = max(kern, key=kern.get)
     achieved = alg[dom] * NF / (kern[dom] * 1e-3) / 1e9
@@ -1329,6 +1337,29 @@ def run_ours(args):
             reps *= 2
             dt, nfr = cpu_reference_run(cpu_pairs, cores, reps)
         cpu_value = nfr / dt
+
+    # the ceiling that actually binds (DESIGN.md "Why the HBM fraction is small"): warp instructions of one step, from the named
+    # ncu launch list, over the issue slots the step had = 148 SMs x 4 schedulers x SM clock x step time
+    issue_frac = None
+    if warp_inst_288 and clocks and clocks.get("sm_mhz"):
+        issue_frac = warp_inst_288 * NF / 288.0 / (148 * 4 * clocks["sm_mhz"] * 1e6 * (ms / args.steps) * 1e-3)
+
+    def brief(leg, rate_key):   # one config in ~100 bytes, for records that keep `roofline` whole but only the key names of `extra`
+        if not leg:
+            return None
+        o = {"rate": leg.get(rate_key), "e2e": (leg.get("e2e") or {}).get(rate_key),
+             "frac": (leg.get("roofline_step") or leg.get("roofline") or {}).get("frac"),
+             "cpu": (leg.get("cpu_baseline") or {}).get("value"), "cpu_cores": (leg.get("cpu_baseline") or {}).get("cores")}
+        for k in ("all_frames_equal_oracle_sha256", "slice_equals_oracle", "planted_queries_found"):
+            if k in leg:
+                o[k] = leg[k]
+        return o
+    c3 = extra.get("c3_tracking") or {}
+    configs = {"c1": brief(extra.get("c1_mono"), "frames_per_s"), "c4": brief(extra.get("c4_1080p"), "frames_per_s"),
+               "c5": brief(extra.get("c5_hamming"), "gcompares_per_s"),
+               "c3_us": {k: (c3.get(k) or {}).get("us_median") for k in ("search_for_initialization", "search_by_projection_last",
+                                                                        "search_by_projection_points")} if c3 else None,
+               "units": "c1/c4 frames/s, c5 Gcompares/s, c3 median microseconds per C-ABI call"}
 
     line = {
         "metric": "orb_stereo_extract_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -1355,7 +1386,11 @@ def run_ours(args):
                      "traffic_source": f"{traffic_file}: ncu dram__bytes_read.sum + dram__bytes_write.sum of the stage's launches in one "
                                        "288-frame step of this command, scaled by frames",
                      "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom]},
+                     "algorithmic_bytes_per_launch": alg[dom] * NF, "kernel_ms": kern[dom],
+                     "issue_frac": issue_frac,
+                     "issue_frac_note": "warp instructions of one step (ncu launch list named in profiles/CURRENT.json) / "
+                                        "(148 SMs x 4 schedulers x median SM clock x ms_per_step)",
+                     "sustained": sustained, "configs": configs},
         "roofline_stages": {k: {"ms": kern[k], "achieved_GBps": alg[k] * NF / (kern[k] * 1e-3) / 1e9,
                                 "frac": alg[k] * NF / (kern[k] * 1e-3) / 1e9 / hbm_peak,
                                 "traffic": traffic.get(k, 0) * NF / 288.0 or None} for k in alg},
