@@ -721,6 +721,51 @@ def bench_c3(args, popc_rate=None):
         if popc_rate:
             e["frac_of_popc_peak"] = e["compares_per_s"] * 8 / (popc_rate * 1e9)
     out.update(g)
+    # ---- class boundary: the SAME driver and timer as the reference leg above, but the ORB_SLAM2::ORBmatcher methods are the
+    # product's C++ shim (shim/ORBmatcher_gpu.cc over liborbgpu, compiled against the reference's Frame.h / MapPoint.h): the timed
+    # region holds what Tracking waits for -- the gathers under the reference's getters (GetWorldPos, GetDescriptor, Observations),
+    # the per-thread device-frame cache lookup, the C-ABI call and the write-back into Frame::mvpMapPoints
+    try:
+        if os.path.exists(orbref.REF_SHIM_PATH):
+            sb = orbref.ShimBackend()
+            sb.L.refm_last_call_us.restype = C.c_double
+            mks = lambda k, d: Frame(k, d, scale, bounds, backend=sb)
+            s1, s2, sc, sl = mks(ka, da), mks(kb, db), mks(ka, da), mks(ka, da)
+            node = lambda k, dx, dy: ((k["y"] - dy) // 40).astype(np.int64) * 19 + ((k["x"] - dx) // 40).astype(np.int64)
+            na_, nb_ = node(ka, 0, 0), node(kb, 7, 4)          # stand-in for two DBoW2 FeatureVectors: node = 40-px cell
+            oa_, ob_ = np.argsort(na_, kind="stable"), np.argsort(nb_, kind="stable")
+            ko, ki, fo_, fi = [0], [], [0], []
+            for c in np.intersect1d(na_, nb_):
+                ki += oa_[na_[oa_] == c].tolist(); fi += ob_[nb_[ob_] == c].tolist()
+                ko.append(len(ki)); fo_.append(len(fi))
+            kv = np.ones(n, np.uint8)
+            calls = {
+                "search_for_initialization": lambda B_, f1, f2: ORBmatcher(0.9, True, backend=B_).SearchForInitialization(f1, f2, prev0.copy(), 100),
+                "search_by_projection_last": lambda B_, f1, f2: (lambda r: (r["nmatches"], r["assigned"]))(orbref.refm_search_by_projection_last(
+                    f1, f2, xyz, has, obs, claimed_last, Tc, Tl, FX3, FY3, CX3, CY3, 40.0, 0.11, 15.0, True, 0.9, True)),
+                "search_by_projection_points": lambda B_, f1, f2: ORBmatcher(0.8, backend=B_).SearchByProjectionPoints(
+                    f2, in_view, px, py, pxr, lvl, vc, da, 3.0, claimed_pts, obs),
+                "search_by_bow": lambda B_, f1, f2: orbref.refm_search_by_bow(f1, f2, ko, ki, fo_, fi, kv, None, False, 0.7, True),
+            }
+            cls = {}
+            for name, call in calls.items():
+                tr, ts = [], []
+                for _ in range(12):
+                    want = call(rb, r1 if name != "search_by_projection_last" else rc, r2 if name != "search_by_projection_last" else rl)
+                    tr.append(rb.L.refm_last_call_us())
+                for _ in range(reps + 3):
+                    got = call(sb, s1 if name != "search_by_projection_last" else sc, s2 if name != "search_by_projection_last" else sl)
+                    ts.append(sb.L.refm_last_call_us())
+                ts = ts[3:]                                    # the first calls build the thread's device-frame cache
+                cls[name] = {"us_median": float(np.median(ts)), "us_min": float(np.min(ts)), "reference_us_median_1core": float(np.median(tr)),
+                             "speedup_vs_reference": float(np.median(tr) / np.median(ts)), "nmatches": int(got[0]),
+                             "equals_reference": bool(got[0] == want[0] and np.array_equal(got[1], want[1]))}
+            cls["how"] = ("ORB_SLAM2::ORBmatcher method calls on Frame / MapPoint objects of the reference's own headers, steady_clock around the "
+                          "method: product = shim/ORBmatcher_gpu.cc over liborbgpu (oracle/_ref/liborbmatcher_shim.so), reference = the "
+                          "reference's ORBmatcher.cc (liborbmatcher_ref.so), same driver, same inputs, one host thread")
+            out["class_boundary"] = cls
+    except Exception as exc:   # a checker-side leg: it must not cost the line
+        out["class_boundary"] = {"unavailable": repr(exc)}
     out["note"] = ("candidates = (query, feature) pairs whose 256-bit distance is computed (nnz of SURVEY 8d); these calls are latency-bound "
                    "(two kernels + two copies), the POPC fraction is reported for completeness")
     return out
@@ -1359,7 +1404,10 @@ def run_ours(args):
                "c5": brief(extra.get("c5_hamming"), "gcompares_per_s"),
                "c3_us": {k: (c3.get(k) or {}).get("us_median") for k in ("search_for_initialization", "search_by_projection_last",
                                                                         "search_by_projection_points")} if c3 else None,
-               "units": "c1/c4 frames/s, c5 Gcompares/s, c3 median microseconds per C-ABI call"}
+               "c3_class_us": {k: {"us": round(v["us_median"], 1), "ref_us": round(v["reference_us_median_1core"], 1), "eq": v["equals_reference"]}
+                               for k, v in (c3.get("class_boundary") or {}).items() if isinstance(v, dict) and "us_median" in v} or None,
+               "units": "c1/c4 frames/s, c5 Gcompares/s, c3 median microseconds per C-ABI call; c3_class = per ORBmatcher method call "
+                        "(product shim vs the reference's ORBmatcher.cc on one core)"}
 
     line = {
         "metric": "orb_stereo_extract_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,

@@ -394,7 +394,10 @@ int refm_search_by_bow(refm_frame *kf, refm_frame *f, int ngroups, const int32_t
     fill_featvec(f->F.mFeatVec, ngroups, f_off, f_idx);
     std::vector<MapPoint *> out;
     ORBmatcher matcher(nnratio, check_orientation != 0);
-    *nmatches = matcher.SearchByBoW(K.get(), f->F, out);
+    {
+        CallTimer t;
+        *nmatches = matcher.SearchByBoW(K.get(), f->F, out);
+    }
     for (int i = 0; i < f->F.N; i++) matches[i] = out[i] ? out[i]->id : -1;
     return 0;
 }
